@@ -1,0 +1,301 @@
+"""ctypes bindings for the CPU oracle (liborb_oracle.so) and the compiled reference TU
+(oracle/_ref/liborbref*.so).  TEST INFRASTRUCTURE ONLY: imported by tests/, by
+__graft_entry__.smoke() and by bench.py's cpu_baseline / --impl reference legs, never by the
+product package."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+assert KP_DTYPE.itemsize == 28
+
+_u8p = C.POINTER(C.c_uint8)
+_ip = C.POINTER(C.c_int)
+_fp = C.POINTER(C.c_float)
+
+
+def _p(a, t=_u8p):
+    return a.ctypes.data_as(t)
+
+
+def build(force: bool = False) -> None:
+    """Compile liborb_oracle.so (and oracle/_ref when /root/reference is mounted)."""
+    if force or not os.path.exists(os.path.join(HERE, "liborb_oracle.so")) or os.path.exists("/root/reference/src/ORBextractor.cc"):
+        subprocess.run(["make", "-C", HERE, "all"], check=True, stdout=subprocess.DEVNULL)
+
+
+class FrameView(C.Structure):
+    _fields_ = [("n", C.c_int), ("kps", C.c_void_p), ("desc", C.c_void_p), ("uright", C.c_void_p),
+                ("min_x", C.c_float), ("max_x", C.c_float), ("min_y", C.c_float), ("max_y", C.c_float),
+                ("scale_factors", C.c_void_p), ("nlevels", C.c_int)]
+
+
+class MapPointsView(C.Structure):
+    _fields_ = [("n", C.c_int), ("track_in_view", C.c_void_p), ("proj_x", C.c_void_p),
+                ("proj_y", C.c_void_p), ("proj_xr", C.c_void_p), ("level", C.c_void_p),
+                ("view_cos", C.c_void_p), ("desc", C.c_void_p), ("observations", C.c_void_p)]
+
+
+class PyramidView(C.Structure):
+    _fields_ = [("nlevels", C.c_int), ("data", C.c_void_p), ("w", C.c_void_p), ("h", C.c_void_p),
+                ("stride", C.c_void_p)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        path = os.path.join(HERE, "liborb_oracle.so")
+        if not os.path.exists(path):
+            build()
+        L = C.CDLL(path)
+        L.orc_fast_atan2.restype = C.c_float
+        L.orc_fast_atan2.argtypes = [C.c_float, C.c_float]
+        L.orc_cv_round_f.argtypes = [C.c_float]
+        L.orc_cv_round_d.argtypes = [C.c_double]
+        L.orc_extractor_create.restype = C.c_void_p
+        L.orc_extractor_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        L.orc_extractor_destroy.argtypes = [C.c_void_p]
+        L.orc_extractor_tables.argtypes = [C.c_void_p] + [C.c_void_p] * 6
+        L.orc_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_ssize_t, C.c_void_p, C.c_void_p, C.c_int]
+        L.orc_level_size.argtypes = [C.c_void_p, C.c_int, _ip, _ip]
+        L.orc_level_image.restype = C.c_void_p
+        L.orc_level_image.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_ssize_t)]
+        L.orc_level_blurred.restype = C.c_void_p
+        L.orc_level_blurred.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_ssize_t)]
+        L.orc_level_raw.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]
+        L.orc_resize_linear_u8.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_ssize_t, C.c_void_p, C.c_int, C.c_int, C.c_ssize_t]
+        L.orc_copy_make_border_reflect101.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_ssize_t, C.c_void_p, C.c_ssize_t, C.c_int]
+        L.orc_fast9_16.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_ssize_t, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orc_gaussian_blur_7x7_s2.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_ssize_t, C.c_void_p, C.c_ssize_t]
+        L.orc_distribute_octtree.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orc_descriptor_distance.argtypes = [C.c_void_p, C.c_void_p]
+        L.orc_assign_grid.argtypes = [C.POINTER(FrameView), C.c_void_p, C.c_void_p]
+        L.orc_features_in_area.argtypes = [C.POINTER(FrameView), C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orc_three_maxima.argtypes = [C.c_void_p, C.c_int, _ip, _ip, _ip]
+        L.orc_search_for_initialization.argtypes = [C.POINTER(FrameView), C.POINTER(FrameView), C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int]
+        L.orc_search_by_projection.argtypes = [C.POINTER(FrameView), C.POINTER(MapPointsView), C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+        L.orc_compute_stereo_matches.argtypes = [C.POINTER(FrameView), C.POINTER(FrameView), C.POINTER(PyramidView), C.POINTER(PyramidView), C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+        L.orc_knn2.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+        _lib = L
+    return _lib
+
+
+# ----------------------------------------------------------------------------- primitives
+def resize_linear(src: np.ndarray, dw: int, dh: int) -> np.ndarray:
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.empty((dh, dw), np.uint8)
+    lib().orc_resize_linear_u8(src.ctypes.data, src.shape[1], src.shape[0], src.strides[0], dst.ctypes.data, dw, dh, dw)
+    return dst
+
+
+def copy_make_border(src: np.ndarray, b: int) -> np.ndarray:
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.empty((src.shape[0] + 2 * b, src.shape[1] + 2 * b), np.uint8)
+    lib().orc_copy_make_border_reflect101(src.ctypes.data, src.shape[1], src.shape[0], src.strides[0], dst.ctypes.data, dst.strides[0], b)
+    return dst
+
+
+def fast(img: np.ndarray, threshold: int, nonmax: bool = True) -> np.ndarray:
+    """-> int32 [n,3] (x,y,score) row-major."""
+    assert img.dtype == np.uint8 and img.strides[1] == 1
+    cap = max(1, img.shape[0] * img.shape[1])
+    out = np.empty((cap, 3), np.int32)
+    n = lib().orc_fast9_16(img.ctypes.data, img.shape[1], img.shape[0], img.strides[0], threshold, int(nonmax), out.ctypes.data, cap)
+    return out[:n].copy()
+
+
+def gaussian_blur(src: np.ndarray) -> np.ndarray:
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.empty_like(src)
+    lib().orc_gaussian_blur_7x7_s2(src.ctypes.data, src.shape[1], src.shape[0], src.strides[0], dst.ctypes.data, dst.strides[0])
+    return dst
+
+
+def fast_atan2(y: float, x: float) -> float:
+    return lib().orc_fast_atan2(y, x)
+
+
+def distribute_octtree(xys: np.ndarray, minX, maxX, minY, maxY, N) -> np.ndarray:
+    xys = np.ascontiguousarray(xys, np.int32)
+    n = xys.shape[0]
+    out = np.empty(n + 8, np.int32)
+    c = lib().orc_distribute_octtree(xys.ctypes.data, n, minX, maxX, minY, maxY, N, out.ctypes.data, n + 8)
+    return out[:c].copy()
+
+
+def descriptor_distance(a: np.ndarray, b: np.ndarray) -> int:
+    a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+    return lib().orc_descriptor_distance(a.ctypes.data, b.ctypes.data)
+
+
+# ----------------------------------------------------------------------------- extractor
+class OracleExtractor:
+    """The repo's own CPU restatement of ORBextractor (oracle/orc_extractor.cpp)."""
+
+    def __init__(self, nfeatures=1000, scale=1.2, nlevels=8, ini_th=20, min_th=7):
+        self.nlevels = nlevels
+        self.nfeatures = nfeatures
+        self._h = lib().orc_extractor_create(nfeatures, scale, nlevels, ini_th, min_th)
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orc_extractor_destroy(self._h); self._h = None
+
+    def tables(self):
+        n = self.nlevels
+        s, i, g, ig = (np.empty(n, np.float32) for _ in range(4))
+        f = np.empty(n, np.int32); u = np.empty(16, np.int32)
+        lib().orc_extractor_tables(self._h, s.ctypes.data, i.ctypes.data, g.ctypes.data, ig.ctypes.data, f.ctypes.data, u.ctypes.data)
+        return dict(scale=s, inv_scale=i, sigma2=g, inv_sigma2=ig, features_per_level=f, umax=u)
+
+    def __call__(self, img: np.ndarray):
+        assert img.dtype == np.uint8 and img.ndim == 2 and img.strides[1] == 1
+        cap = 4 * self.nfeatures + 4096
+        kps = np.empty(cap, KP_DTYPE); desc = np.empty((cap, 32), np.uint8)
+        n = lib().orc_extract(self._h, img.ctypes.data, img.shape[1], img.shape[0], img.strides[0], kps.ctypes.data, desc.ctypes.data, cap)
+        assert n >= 0
+        return kps[:n].copy(), desc[:n].copy()
+
+    def level(self, l: int, blurred=False):
+        w = C.c_int(); h = C.c_int(); st = C.c_ssize_t()
+        lib().orc_level_size(self._h, l, C.byref(w), C.byref(h))
+        p = (lib().orc_level_blurred if blurred else lib().orc_level_image)(self._h, l, C.byref(st))
+        if not p:
+            return None
+        buf = (C.c_uint8 * (w.value * h.value)).from_address(p)
+        return np.frombuffer(buf, np.uint8).reshape(h.value, w.value).copy()
+
+    def raw(self, l: int) -> np.ndarray:
+        p = C.c_void_p()
+        n = lib().orc_level_raw(self._h, l, C.byref(p))
+        if n == 0:
+            return np.zeros((0, 3), np.int32)
+        buf = (C.c_int * (3 * n)).from_address(p.value)
+        return np.frombuffer(buf, np.int32).reshape(n, 3).copy()
+
+
+_ref_libs = {}
+
+
+def ref_lib(variant: str = ""):
+    """oracle/_ref/liborbref{variant}.so — the unmodified reference TU. None if not built."""
+    if variant not in _ref_libs:
+        path = os.path.join(HERE, "_ref", f"liborbref{variant}.so")
+        if not os.path.exists(path):
+            _ref_libs[variant] = None
+        else:
+            L = C.CDLL(path)
+            L.ref_extractor_create.restype = C.c_void_p
+            L.ref_extractor_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+            L.ref_extractor_destroy.argtypes = [C.c_void_p]
+            L.ref_tables.argtypes = [C.c_void_p] * 5
+            L.ref_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_ssize_t, C.c_void_p, C.c_void_p, C.c_int]
+            L.ref_level.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), _ip, _ip, C.POINTER(C.c_ssize_t)]
+            _ref_libs[variant] = L
+    return _ref_libs[variant]
+
+
+class RefExtractor:
+    """The reference's own ORB_SLAM2::ORBextractor (compiled against the cv-shim)."""
+
+    def __init__(self, nfeatures=1000, scale=1.2, nlevels=8, ini_th=20, min_th=7, variant=""):
+        self._L = ref_lib(variant)
+        if self._L is None:
+            raise FileNotFoundError("oracle/_ref/liborbref%s.so not built" % variant)
+        self.nlevels = nlevels; self.nfeatures = nfeatures
+        self._h = self._L.ref_extractor_create(nfeatures, scale, nlevels, ini_th, min_th)
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            self._L.ref_extractor_destroy(self._h); self._h = None
+
+    def tables(self):
+        n = self.nlevels
+        s, i, g, ig = (np.empty(n, np.float32) for _ in range(4))
+        self._L.ref_tables(self._h, s.ctypes.data, i.ctypes.data, g.ctypes.data, ig.ctypes.data)
+        return dict(scale=s, inv_scale=i, sigma2=g, inv_sigma2=ig)
+
+    def __call__(self, img: np.ndarray):
+        assert img.dtype == np.uint8 and img.ndim == 2 and img.strides[1] == 1
+        cap = 4 * self.nfeatures + 4096
+        kps = np.empty(cap, KP_DTYPE); desc = np.empty((cap, 32), np.uint8)
+        n = self._L.ref_extract(self._h, img.ctypes.data, img.shape[1], img.shape[0], img.strides[0], kps.ctypes.data, desc.ctypes.data, cap)
+        assert n >= 0
+        return kps[:n].copy(), desc[:n].copy()
+
+    def level(self, l: int) -> np.ndarray:
+        p = C.c_void_p(); w = C.c_int(); h = C.c_int(); st = C.c_ssize_t()
+        self._L.ref_level(self._h, l, C.byref(p), C.byref(w), C.byref(h), C.byref(st))
+        buf = (C.c_uint8 * (st.value * h.value)).from_address(p.value)
+        return np.frombuffer(buf, np.uint8).reshape(h.value, st.value)[:, :w.value].copy()
+
+
+# ----------------------------------------------------------------------------- matcher
+def frame_view(kps: np.ndarray, desc: np.ndarray, width: float, height: float, scale_factors: np.ndarray, uright=None):
+    """Returns (FrameView, keepalive list)."""
+    kps = np.ascontiguousarray(kps); desc = np.ascontiguousarray(desc, np.uint8)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    keep = [kps, desc, sf]
+    v = FrameView(len(kps), kps.ctypes.data, desc.ctypes.data, None, 0.0, float(width), 0.0, float(height), sf.ctypes.data, len(sf))
+    if uright is not None:
+        ur = np.ascontiguousarray(uright, np.float32); keep.append(ur); v.uright = ur.ctypes.data
+    return v, keep
+
+
+def search_for_initialization(f1, f2, prev_matched: np.ndarray, window=100, nnratio=0.9, check_ori=True):
+    """f1,f2 = (FrameView, keep). prev_matched float32[n1,2] is updated in place.
+    -> (nmatches, matches12 int32[n1])"""
+    n1 = f1[0].n
+    m12 = np.empty(max(n1, 1), np.int32)
+    assert prev_matched.dtype == np.float32 and prev_matched.flags.c_contiguous
+    nm = lib().orc_search_for_initialization(C.byref(f1[0]), C.byref(f2[0]), prev_matched.ctypes.data, m12.ctypes.data, window, nnratio, int(check_ori))
+    return nm, m12[:n1]
+
+
+def search_by_projection(f, mps: dict, th: float, nnratio: float, occupied: np.ndarray):
+    """mps: dict of arrays (track_in_view u8, proj_x/proj_y/proj_xr f32, level i32, view_cos f32,
+    desc u8[n,32], observations i32). occupied u8[n] in/out. -> (nmatches, mp_for_kp int32[n])"""
+    arrs = dict(track_in_view=np.uint8, proj_x=np.float32, proj_y=np.float32, proj_xr=np.float32,
+                level=np.int32, view_cos=np.float32, desc=np.uint8, observations=np.int32)
+    keep = {k: np.ascontiguousarray(mps[k], t) for k, t in arrs.items()}
+    v = MapPointsView(len(keep["level"]), *[keep[k].ctypes.data for k in
+                      ("track_in_view", "proj_x", "proj_y", "proj_xr", "level", "view_cos", "desc", "observations")])
+    out = np.full(max(f[0].n, 1), -1, np.int32)
+    nm = lib().orc_search_by_projection(C.byref(f[0]), C.byref(v), th, nnratio, occupied.ctypes.data, out.ctypes.data)
+    return nm, out[:f[0].n]
+
+
+def pyramid_view(levels: list[np.ndarray]):
+    n = len(levels)
+    levels = [np.ascontiguousarray(l, np.uint8) for l in levels]
+    ptrs = (C.c_void_p * n)(*[l.ctypes.data for l in levels])
+    w = np.array([l.shape[1] for l in levels], np.int32); h = np.array([l.shape[0] for l in levels], np.int32)
+    st = np.array([l.strides[0] for l in levels], np.int64)
+    v = PyramidView(n, C.cast(ptrs, C.c_void_p), w.ctypes.data, h.ctypes.data, st.ctypes.data)
+    return v, [levels, ptrs, w, h, st]
+
+
+def compute_stereo_matches(fl, fr, pl, pr, inv_scale: np.ndarray, mbf: float, mb: float):
+    n = fl[0].n
+    ur = np.empty(max(n, 1), np.float32); dp = np.empty(max(n, 1), np.float32)
+    inv = np.ascontiguousarray(inv_scale, np.float32)
+    lib().orc_compute_stereo_matches(C.byref(fl[0]), C.byref(fr[0]), C.byref(pl[0]), C.byref(pr[0]), inv.ctypes.data, mbf, mb, ur.ctypes.data, dp.ctypes.data)
+    return ur[:n], dp[:n]
+
+
+def knn2(q: np.ndarray, t: np.ndarray, th=50, ratio=0.7):
+    q = np.ascontiguousarray(q, np.uint8); t = np.ascontiguousarray(t, np.uint8)
+    m = q.shape[0]
+    idx = np.empty(m, np.int32); d1 = np.empty(m, np.int32); d2 = np.empty(m, np.int32)
+    lib().orc_knn2(q.ctypes.data, m, t.ctypes.data, t.shape[0], th, ratio, idx.ctypes.data, d1.ctypes.data, d2.ctypes.data)
+    return idx, d1, d2

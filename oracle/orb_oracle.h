@@ -1,0 +1,129 @@
+/* orb_oracle.h — CPU ORACLE for the ORB front end.  TEST INFRASTRUCTURE ONLY.
+ *
+ * A plain C/C++ restatement of the reference algorithm (saber/ORB_SLAM2_Annotate:
+ * src/ORBextractor.cc, src/ORBmatcher.cc, src/Frame.cc) and of the OpenCV primitives it
+ * calls (semantics pinned to cv2 4.13.0, see tests/test_oracle_primitives.py and
+ * tests/golden/).  Nothing under orb_slam2_annotate_b200/ may include, link or call this
+ * library: only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl
+ * reference legs use it, and only as the checker / the timed CPU baseline.
+ *
+ * Parity pinning: the reference ships no tests or golden vectors.  The
+ * oracle is pinned against (a) cv2 4.13.0 run live in the build container plus committed
+ * fixtures made from it (tests/golden/make_golden.py) for every OpenCV primitive, and
+ * (b) the UNMODIFIED reference translation unit src/ORBextractor.cc compiled against
+ * oracle/cvshim (oracle/_ref/liborbref.so, built by oracle/Makefile) for the extractor.
+ * The matcher restatements follow the reference line by line but the matcher TUs cannot be
+ * compiled here (they need Eigen/g2o/DBoW2): for those, parity is "unpinned by execution"
+ * and anchored on known-answer tests derived by hand from the cited lines.
+ */
+#ifndef ORB_ORACLE_H
+#define ORB_ORACLE_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* == cv::KeyPoint field-for-field (28 B) == */
+typedef struct {
+    float x, y, size, angle, response;
+    int octave, class_id;
+} orc_keypoint;
+
+/* ---- OpenCV primitive restatements (cv2 4.13.0 semantics) ---- */
+int   orc_cv_round_f(float v);                       /* cvRound(float): round-half-even */
+int   orc_cv_round_d(double v);
+float orc_fast_atan2(float y, float x);              /* cv::fastAtan2, degrees [0,360) */
+void  orc_resize_linear_u8(const uint8_t* src, int sw, int sh, ptrdiff_t sstride,
+                           uint8_t* dst, int dw, int dh, ptrdiff_t dstride);
+void  orc_copy_make_border_reflect101(const uint8_t* src, int w, int h, ptrdiff_t sstride,
+                                      uint8_t* dst, ptrdiff_t dstride, int border);
+/* FAST-9/16 (cv::FAST(img, kps, threshold, nonmax)), row-major output (x,y,score). */
+int   orc_fast9_16(const uint8_t* img, int w, int h, ptrdiff_t stride, int threshold,
+                   int nonmax, int* out_xys, int cap);
+void  orc_gaussian_blur_7x7_s2(const uint8_t* src, int w, int h, ptrdiff_t sstride,
+                               uint8_t* dst, ptrdiff_t dstride);
+
+/* ---- extractor (ORBextractor.cc) ---- */
+typedef struct orc_extractor orc_extractor;
+orc_extractor* orc_extractor_create(int nfeatures, float scaleFactor, int nlevels,
+                                    int iniThFAST, int minThFAST);
+void  orc_extractor_destroy(orc_extractor* e);
+/* tables: out arrays sized nlevels */
+void  orc_extractor_tables(const orc_extractor* e, float* scale, float* inv_scale,
+                           float* sigma2, float* inv_sigma2, int* features_per_level,
+                           int* umax16);
+/* operator(): returns number of keypoints (<= cap) or -1 if cap too small. */
+int   orc_extract(orc_extractor* e, const uint8_t* img, int w, int h, ptrdiff_t stride,
+                  orc_keypoint* kps, uint8_t* desc, int cap);
+/* taps into the last call, for stage-by-stage parity tests */
+int   orc_level_size(const orc_extractor* e, int level, int* w, int* h);
+const uint8_t* orc_level_image(const orc_extractor* e, int level, ptrdiff_t* stride);
+const uint8_t* orc_level_blurred(const orc_extractor* e, int level, ptrdiff_t* stride);
+/* raw per-level FAST list (x,y,score triplets, coordinates relative to minBorder) in
+ * vToDistributeKeys order; returns count */
+int   orc_level_raw(const orc_extractor* e, int level, const int** xys);
+/* quadtree alone (DistributeOctTree): in = (x,y,score) triplets relative to minBorder,
+ * out = indices into the input in result order. returns count. */
+int   orc_distribute_octtree(const int* xys, int n, int minX, int maxX, int minY, int maxY,
+                             int N, int* out_idx, int cap);
+
+/* ---- matcher (ORBmatcher.cc / Frame.cc) ---- */
+int   orc_descriptor_distance(const uint8_t* a, const uint8_t* b);
+
+/* Frame view: what the matcher routines read from a Frame. */
+typedef struct {
+    int n;
+    const orc_keypoint* kps;      /* mvKeysUn (== mvKeys when undistorted input)        */
+    const uint8_t* desc;          /* n x 32                                              */
+    const float* uright;          /* mvuRight or NULL (treated as all -1)                */
+    float min_x, max_x, min_y, max_y;   /* mnMinX.. image bounds                         */
+    const float* scale_factors;   /* mvScaleFactors                                      */
+    int nlevels;
+} orc_frame_view;
+
+/* 64x48 grid as in Frame::AssignFeaturesToGrid; CSR arrays sized 64*48+1 / n */
+void  orc_assign_grid(const orc_frame_view* f, int* cell_start /*3073*/, int* cell_items /*n*/);
+int   orc_features_in_area(const orc_frame_view* f, const int* cell_start,
+                           const int* cell_items, float x, float y, float r, int minLevel,
+                           int maxLevel, int* out, int cap);
+void  orc_three_maxima(const int* hist_counts, int L, int* ind1, int* ind2, int* ind3);
+/* SearchForInitialization: prev_matched in/out (2*n1 floats), matches12 out (n1). */
+int   orc_search_for_initialization(const orc_frame_view* f1, const orc_frame_view* f2,
+                                    float* prev_matched, int* matches12, int window,
+                                    float nnratio, int check_ori);
+/* SearchByProjection(Frame, MapPoints, th). map point arrays of length nmp.
+ * kp_occupied[n]: 1 if F.mvpMapPoints[idx] exists with Observations()>0 (in/out: set when
+ * a map point with observations>0 is assigned). out_mp_for_kp[n]: map point index assigned
+ * to keypoint or -1 (caller initialises to -1). */
+typedef struct {
+    int n;
+    const uint8_t* track_in_view;  /* mbTrackInView && !isBad                            */
+    const float* proj_x; const float* proj_y; const float* proj_xr;
+    const int* level;              /* mnTrackScaleLevel                                  */
+    const float* view_cos;         /* mTrackViewCos                                      */
+    const uint8_t* desc;           /* n x 32                                             */
+    const int* observations;       /* Observations()                                     */
+} orc_mappoints_view;
+int   orc_search_by_projection(const orc_frame_view* f, const orc_mappoints_view* mps,
+                               float th, float nnratio, uint8_t* kp_occupied,
+                               int* out_mp_for_kp);
+/* ComputeStereoMatches. pyramids: arrays of nlevels pointers + dims for left and right. */
+typedef struct {
+    int nlevels;
+    const uint8_t* const* data; const int* w; const int* h; const ptrdiff_t* stride;
+} orc_pyramid_view;
+void  orc_compute_stereo_matches(const orc_frame_view* left, const orc_frame_view* right,
+                                 const orc_pyramid_view* pl, const orc_pyramid_view* pr,
+                                 const float* inv_scale_factors, float mbf, float mb,
+                                 float* uright_out, float* depth_out);
+/* brute-force kNN-2 (+ratio): out_idx[m] = best train index or -1 if rejected,
+ * out_d1/out_d2 best & second distances (always written). */
+void  orc_knn2(const uint8_t* q, int m, const uint8_t* t, int n, int th, float ratio,
+               int* out_idx, int* out_d1, int* out_d2);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
