@@ -1,0 +1,270 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the ORB front end on B200.
+
+Workload (BASELINE.json configs[1]): a monocular stream of 1024 synthetic 640x480 frames per
+GPU, ORBextractor(1000, 1.2, 8, 20, 7) on every frame (+ SearchForInitialization between
+consecutive frames once that kernel is enabled with --match).  One "step" = one pass over the
+1024-frame batch.  `value` = frames/s with the frames already resident in HBM; `e2e` = the same
+through the host-buffer C-ABI call (pinned host images in, keypoints + descriptors out).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl orbfe|reference]
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from orb_slam2_annotate_b200 import synth  # noqa: E402
+
+METRIC = "ORB frames/s @640x480/1000kp/8lvl"
+W, H, NFEAT = 640, 480, 1000
+
+
+def level_sizes(w, h, nlevels=8, sf=1.2):
+    scale = [np.float32(1.0)]
+    for _ in range(1, nlevels):
+        scale.append(np.float32(float(scale[-1]) * float(np.float32(sf))))
+    inv = [np.float32(1.0) / s for s in scale]
+    return [(int(np.rint(np.float32(w) * i)), int(np.rint(np.float32(h) * i))) for i in inv]
+
+
+def algorithmic_bytes(w, h):
+    """Compulsory HBM bytes per frame and kernel."""
+    px = [a * b for a, b in level_sizes(w, h)]
+    return {
+        "pyramid": sum(px[:-1]) + sum(px[1:]),       # read levels 0..6, write levels 1..7
+        "fast": sum(px),                             # read every level once (+ tiny corner lists)
+        "blur": 2 * sum(px),                         # read + write every level
+    }
+
+
+def make_frames(batch, seed):
+    """`batch` distinct frames: crops of one synthetic canvas with per-frame noise."""
+    distinct = min(batch, 256)
+    frames, _ = synth.sequence(distinct, W, H, seed=seed)
+    if distinct < batch:
+        frames = np.concatenate([frames] * ((batch + distinct - 1) // distinct))[:batch]
+    return np.ascontiguousarray(frames)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu, self.rows, self.p = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-lms", "200", "-i", str(self.gpu)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.p.terminate()
+        sm = [float(r[1]) for r in self.rows if len(r) >= 8 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 8 and r[2].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 8 for n, v in zip(names, r[4:8]) if v.lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_reference_fps(frames, seconds_budget=20.0, steps=1, warmup=0):
+    """The reference's own CPU extractor (oracle/_ref, the unmodified ORBextractor.cc built with
+    the reference's -O3 flags against the cv-shim) or, when it was not prebuilt, the oracle
+    port; one extractor instance per thread, one thread per host core."""
+    from oracle import oracle_py as O
+    cores = os.cpu_count() or 1
+    kind = "reference" if O.ref_lib("_native") is not None else "port"
+
+    def make():
+        return O.RefExtractor(NFEAT, variant="_native") if kind == "reference" else O.OracleExtractor(NFEAT)
+
+    exs = [make() for _ in range(cores)]
+    t0 = time.perf_counter()
+    exs[0](frames[0])
+    per_frame = time.perf_counter() - t0
+    n = int(max(cores, min(len(frames), seconds_budget / max(per_frame, 1e-3))))
+    n = (n // cores) * cores
+    sample = [frames[i % len(frames)] for i in range(n)]
+
+    def run_once():
+        def work(t):
+            for i in range(t, n, cores):
+                exs[t](sample[i])
+        th = [threading.Thread(target=work, args=(t,)) for t in range(cores)]
+        t0 = time.perf_counter()
+        [t.start() for t in th]
+        [t.join() for t in th]
+        return time.perf_counter() - t0
+
+    for _ in range(warmup):
+        run_once()
+    times = [run_once() for _ in range(max(steps, 1))]
+    dt = float(np.mean(times))
+    return {"value": n / dt, "unit": "frames/s", "cores": cores, "kind": kind,
+            "sample": f"{n} of the workload's 640x480 frames, {cores} threads x {n // cores} frames, "
+                      f"mean of {max(steps, 1)} pass(es)", "ms_per_step": dt * 1e3, "frames": n}
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    frames = make_frames(64, seed=0)
+    r = cpu_reference_fps(frames, seconds_budget=20.0, steps=args.steps, warmup=min(args.warmup, 1))
+    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": "frames/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "mono_stream 640x480 nfeatures=1000 8lvl (TUM1.yaml), CPU sample of configs[1]",
+                       "frames_per_step": r["frames"]},
+            "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": r["value"], "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="orbfe", choices=["orbfe", "reference"])
+    ap.add_argument("--batch", type=int, default=1024)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    import orb_slam2_annotate_b200 as orbfe
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: liborbfe has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    B = args.batch
+    frames = make_frames(B, seed=1000 * rank)           # every rank its own stream (weak scaling)
+    ex = orbfe.ORBextractor(NFEAT, 1.2, 8, 20, 7, device=local_rank, max_width=W, max_height=H, max_batch=B)
+    d_frames = torch.from_numpy(frames).cuda()
+    stream = torch.cuda.ExternalStream(ex.stream, device=local_rank)
+    ex.set_profiling(True)
+
+    # ---- device-resident timing: K steps, CUDA events on the extractor's stream
+    for _ in range(args.warmup):
+        ex.extract_batch_device(d_frames.data_ptr(), B, W, H)
+    ex.sync()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    stage_sum = {}
+    e0.record(stream)
+    for _ in range(args.steps):
+        ex.extract_batch_device(d_frames.data_ptr(), B, W, H)
+        for k, v in ex.stage_times_ms().items():         # syncs on the step's last event
+            stage_sum[k] = stage_sum.get(k, 0.0) + v
+    e1.record(stream)
+    ex.sync()
+    barrier()
+    dev_ms = e0.elapsed_time(e1)
+    clocks = sampler.stop()
+    launches = ex.last_launches * args.steps
+    _, _, counts = ex.fetch()
+    mean_kp = float(counts.mean())
+
+    # ---- end to end through the host-buffer C-ABI call: pinned frames in, results out
+    h_frames = orbfe.pinned_empty(frames.shape, np.uint8)
+    h_frames[...] = frames
+    cap = ex.max_keypoints()
+    out = (orbfe.pinned_empty((B, cap), orbfe.KP_DTYPE), orbfe.pinned_empty((B, cap, 32), np.uint8),
+           orbfe.pinned_empty((B,), np.int32))
+    for _ in range(max(1, min(args.warmup, 2))):
+        ex.extract_batch(h_frames, out=out)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        ex.extract_batch(h_frames, out=out)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+
+    t = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms = t.tolist()
+
+    if rank == 0:
+        total_frames = B * world * args.steps
+        ab = algorithmic_bytes(W, H)
+        stage_ms = {k: v / args.steps for k, v in stage_sum.items()}
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        dom = max(("pyramid", "fast", "blur"), key=lambda k: stage_ms.get(k, 0.0))
+        achieved = ab[dom] * B / (stage_ms[dom] * 1e-3) / 1e9
+        per_kernel = {k: {"ms": stage_ms[k], "gbs": ab[k] * B / (stage_ms[k] * 1e-3) / 1e9 if k in ab else None}
+                      for k in stage_ms}
+        line = {
+            "metric": METRIC, "value": total_frames / (dev_ms * 1e-3), "unit": "frames/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "configs[1]: monocular stream, 1024 synthetic 640x480 frames per GPU, "
+                                   "ORBextractor(1000,1.2,8,20,7) on every frame",
+                       "frames_per_step_per_gpu": B, "l2": "inputs_larger_than_l2 (315 MB of frames per step)",
+                       "mean_keypoints_per_frame": mean_kp},
+            "e2e": {"value": total_frames / (e2e_ms * 1e-3), "unit": "frames/s",
+                    "h2d_bytes_per_step": int(frames.nbytes),
+                    "d2h_bytes_per_step": int(out[0].nbytes + out[1].nbytes + out[2].nbytes)},
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
+                         "per_kernel": per_kernel},
+        }
+        if not args.no_cpu_baseline:
+            r = cpu_reference_fps(frames[:64], seconds_budget=15.0)
+            line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,205 @@
+/* orbfe.h — C ABI of the B200-native ORB front end (liborbfe.so).
+ *
+ * This is the drop-in boundary for the reference's feature front end: every entry point
+ * below replaces one call the reference makes on its CPU path, and is what a maintainer of
+ * saber/ORB_SLAM2_Annotate binds from Frame.cc / ORBmatcher.cc.  Plain
+ * pointers and sizes only; no torch / OpenCV types.  All functions return 0 on success or a
+ * negative orbfe_status; nothing here ever falls back to a CPU implementation.
+ *
+ * Reference interfaces replaced (paths relative to the reference tree):
+ *   orbfe_extractor_create        ORBextractor::ORBextractor          src/ORBextractor.cc:415-486
+ *   orbfe_extract / _batch        ORBextractor::operator()            src/ORBextractor.cc:1119-1197
+ *                                 (called from Frame::ExtractORB      src/Frame.cc:272-278)
+ *   orbfe_pyramid_level           public member mvImagePyramid        include/ORBextractor.h:86
+ *   orbfe_get_scale_tables        GetScaleFactors() & friends         include/ORBextractor.h:64-84
+ *   orbfe_hamming256              ORBmatcher::DescriptorDistance      src/ORBmatcher.cc:1828-1844
+ *   orbfe_knn2                    best/second-best loop + ratio test  src/ORBmatcher.cc:233-269
+ *   orbfe_search_init             ORBmatcher::SearchForInitialization src/ORBmatcher.cc:469-600
+ *   orbfe_search_local_points     ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th)
+ *                                                                     src/ORBmatcher.cc:51-138
+ *   orbfe_stereo_match            Frame::ComputeStereoMatches         src/Frame.cc:512-686
+ */
+#ifndef ORBFE_H
+#define ORBFE_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    ORBFE_OK = 0,
+    ORBFE_ERR_ARG = -1,       /* null pointer, bad size, unsupported parameter              */
+    ORBFE_ERR_CUDA = -2,      /* a CUDA runtime call failed; see orbfe_last_error()         */
+    ORBFE_ERR_CAPACITY = -3,  /* caller buffer / handle capacity too small                  */
+    ORBFE_ERR_NO_DEVICE = -4  /* no CUDA device: there is no CPU fallback                   */
+} orbfe_status;
+
+/* cv::KeyPoint field-for-field (28 bytes): pt.x pt.y size angle response octave class_id */
+typedef struct {
+    float x, y, size, angle, response;
+    int32_t octave, class_id;
+} orbfe_keypoint;
+
+/* Page-locked host memory for image batches and result buffers: transfers from/to memory
+ * obtained here run at full PCIe rate and asynchronously; ordinary memory also works. */
+void* orbfe_host_alloc(size_t bytes);
+void orbfe_host_free(void* p);
+
+const char* orbfe_last_error(void);          /* thread-local, never NULL                    */
+const char* orbfe_version(void);
+int orbfe_device_count(void);                 /* 0 when no usable CUDA device                */
+
+/* ------------------------------------------------------------------ extractor ---------- */
+typedef struct orbfe_extractor orbfe_extractor;
+
+/* One handle == one CUDA stream + private device scratch sized for max_batch frames of at
+ * most max_width x max_height pixels.  Handles are independent: calls on different handles
+ * may run concurrently from different host threads (the reference runs the left and right
+ * extractor of a stereo frame on two threads, src/Frame.cc:78-81). */
+int orbfe_extractor_create(int nfeatures, float scale_factor, int nlevels, int ini_th_fast,
+                           int min_th_fast, int max_width, int max_height, int max_batch,
+                           int device, orbfe_extractor** out);
+void orbfe_extractor_destroy(orbfe_extractor* e);
+
+/* Scale tables exactly as the reference constructor computes them; any pointer may be NULL.
+ * scale/inv_scale/sigma2/inv_sigma2: nlevels floats; features_per_level: nlevels ints;
+ * umax: 16 ints. */
+int orbfe_get_scale_tables(const orbfe_extractor* e, float* scale, float* inv_scale,
+                           float* sigma2, float* inv_sigma2, int* features_per_level,
+                           int* umax);
+int orbfe_extractor_levels(const orbfe_extractor* e);
+/* upper bound on keypoints one frame can return (sum over levels of budget + 3) */
+int orbfe_extractor_max_keypoints(const orbfe_extractor* e);
+
+/* operator(): one 8-bit grey image in HOST memory -> keypoints + 32-byte descriptors in
+ * caller-owned HOST buffers of capacity `cap` keypoints.  Synchronous.  *n receives the
+ * keypoint count.  Empty image (w<=0 || h<=0 || img==NULL) returns ORBFE_OK with *n = 0,
+ * matching the reference's silent return (src/ORBextractor.cc:1122-1123). */
+int orbfe_extract(orbfe_extractor* e, const uint8_t* img, int width, int height,
+                  ptrdiff_t stride, orbfe_keypoint* kps, uint8_t* desc, int cap, int* n);
+
+/* Batched operator(): `batch` images of identical size, HOST memory, frame b at
+ * imgs + b*frame_stride (rows `stride` bytes apart).  Frame b's results are written to
+ * kps + b*cap and desc + b*cap*32; counts[b] = number of keypoints. */
+int orbfe_extract_batch(orbfe_extractor* e, const uint8_t* imgs, int batch, int width,
+                        int height, ptrdiff_t stride, ptrdiff_t frame_stride,
+                        orbfe_keypoint* kps, uint8_t* desc, int cap, int* counts);
+
+/* Device-resident variant for pipelines that already hold frames in HBM: enqueues the
+ * kernels on the handle's stream and returns without synchronising.  d_imgs is a device
+ * pointer (same layout as above).  Results stay on the device; fetch pointers with
+ * orbfe_extractor_device_results after orbfe_extractor_sync. */
+int orbfe_extract_batch_device(orbfe_extractor* e, const uint8_t* d_imgs, int batch, int width,
+                               int height, ptrdiff_t stride, ptrdiff_t frame_stride);
+int orbfe_extractor_sync(orbfe_extractor* e);
+/* device pointers of the last batch: kps [batch][cap] orbfe_keypoint, desc [batch][cap][32],
+ * counts [batch] int32; *cap = per-frame slot capacity */
+int orbfe_extractor_device_results(orbfe_extractor* e, const orbfe_keypoint** d_kps,
+                                   const uint8_t** d_desc, const int32_t** d_counts, int* cap);
+/* copy the last batch's results to host buffers (same layout as orbfe_extract_batch) */
+int orbfe_extractor_fetch(orbfe_extractor* e, int batch, orbfe_keypoint* kps, uint8_t* desc,
+                          int cap, int* counts);
+void* orbfe_extractor_stream(orbfe_extractor* e);   /* cudaStream_t of the handle          */
+/* number of kernel launches the last extract call enqueued (for bench accounting) */
+int orbfe_extractor_last_launches(const orbfe_extractor* e);
+
+/* Per-stage device time of the last extract call, measured with CUDA events on the handle's
+ * stream (enable before the call).  Stages, in order: level-0 upload/copy, pyramid resize
+ * (all levels), FAST cells, Gaussian blur, quadtree, orientation + descriptors. */
+#define ORBFE_NUM_STAGES 6
+int orbfe_extractor_set_profiling(orbfe_extractor* e, int on);
+int orbfe_extractor_stage_times(orbfe_extractor* e, float* ms, int n);
+
+/* mvImagePyramid[level] of frame `frame` of the last call, copied to HOST (lazy D2H; only
+ * the stereo matcher and tests need it).  dst has room for width*height bytes, rows packed
+ * at `dst_stride`.  Pass dst == NULL to query the level size only.  blurred != 0 returns the
+ * 7x7 Gaussian-blurred working image instead (src/ORBextractor.cc:1169-1175). */
+int orbfe_pyramid_level(orbfe_extractor* e, int frame, int level, int blurred, uint8_t* dst,
+                        ptrdiff_t dst_stride, int* width, int* height);
+/* raw per-level FAST corners of frame `frame` (before the quadtree), reference order
+ * (cell row, cell col, y, x); triplets (x, y, score) relative to minBorder. *n = count.
+ * Test tap for stage-by-stage parity. */
+int orbfe_level_raw_keypoints(orbfe_extractor* e, int frame, int level, int32_t* xys, int cap,
+                              int* n);
+
+/* ------------------------------------------------------------------ matcher ------------ */
+/* Scalar Hamming distance between two 256-bit descriptors, host side, for the reference's
+ * scalar callers (e.g. MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:303-311). */
+int orbfe_hamming256(const void* a, const void* b);
+
+typedef struct orbfe_matcher orbfe_matcher;
+/* One handle == one CUDA stream + scratch; stateless between calls, so one handle per host
+ * thread reproduces the reference's "ORBmatcher is a stack temporary" threading model. */
+int orbfe_matcher_create(int device, orbfe_matcher** out);
+void orbfe_matcher_destroy(orbfe_matcher* m);
+void* orbfe_matcher_stream(orbfe_matcher* m);
+int orbfe_matcher_sync(orbfe_matcher* m);
+
+/* What the matcher routines read from a Frame (all HOST pointers). */
+typedef struct {
+    int32_t n;                        /* N                                                  */
+    const orbfe_keypoint* kps;        /* mvKeysUn                                           */
+    const uint8_t* desc;              /* mDescriptors, n x 32                               */
+    const float* uright;              /* mvuRight or NULL (= all -1)                        */
+    float min_x, max_x, min_y, max_y; /* mnMinX, mnMaxX, mnMinY, mnMaxY                     */
+    const float* scale_factors;       /* mvScaleFactors                                     */
+    int32_t nlevels;
+} orbfe_frame_view;
+
+/* Brute-force 2-nearest-neighbour Hamming search with the reference's acceptance rule
+ * (strict '<' updates so the lowest train index wins ties; accept iff d1 <= th and
+ * (float)d1 < ratio*(float)d2): out_idx[i] = train index or -1, out_d1/out_d2 = best and
+ * second-best distances (256 when absent).  HOST pointers. */
+int orbfe_knn2(orbfe_matcher* m, const uint8_t* query, int nq, const uint8_t* train, int nt,
+               int th, float ratio, int32_t* out_idx, int32_t* out_d1, int32_t* out_d2);
+/* Same with DEVICE pointers, asynchronous on the matcher's stream. */
+int orbfe_knn2_device(orbfe_matcher* m, const uint8_t* d_query, int nq, const uint8_t* d_train,
+                      int nt, int th, float ratio, int32_t* d_out_idx, int32_t* d_out_d1,
+                      int32_t* d_out_d2);
+
+/* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize).
+ * prev_matched: 2*f1->n floats (x,y), in/out; matches12: f1->n ints out; *nmatches out. */
+int orbfe_search_init(orbfe_matcher* m, const orbfe_frame_view* f1, const orbfe_frame_view* f2,
+                      float* prev_matched, int32_t* matches12, int window, float nnratio,
+                      int check_orientation, int* nmatches);
+
+/* Map-point side of SearchByProjection(Frame&, vector<MapPoint*>&, th) (HOST pointers). */
+typedef struct {
+    int32_t n;
+    const uint8_t* track_in_view;     /* mbTrackInView && !isBad()                          */
+    const float* proj_x;              /* mTrackProjX                                        */
+    const float* proj_y;              /* mTrackProjY                                        */
+    const float* proj_xr;             /* mTrackProjXR                                       */
+    const int32_t* level;             /* mnTrackScaleLevel                                  */
+    const float* view_cos;            /* mTrackViewCos                                      */
+    const uint8_t* desc;              /* GetDescriptor(), n x 32                            */
+    const int32_t* observations;      /* Observations()                                     */
+} orbfe_mappoints_view;
+/* kp_occupied[f->n] in/out: 1 where F.mvpMapPoints[idx] holds a point with Observations()>0.
+ * mp_for_kp[f->n] out: map point index assigned to each keypoint, -1 if none (the caller
+ * initialises it to -1 and writes F.mvpMapPoints[idx] = vpMapPoints[mp_for_kp[idx]]). */
+int orbfe_search_local_points(orbfe_matcher* m, const orbfe_frame_view* f,
+                              const orbfe_mappoints_view* mps, float th, float nnratio,
+                              uint8_t* kp_occupied, int32_t* mp_for_kp, int* nmatches);
+
+/* Pyramid of one extractor call, HOST pointers (interior pixels of mvImagePyramid[l]). */
+typedef struct {
+    int32_t nlevels;
+    const uint8_t* const* data;
+    const int32_t* width;
+    const int32_t* height;
+    const ptrdiff_t* stride;
+} orbfe_pyramid_view;
+/* Frame::ComputeStereoMatches: fills uright[left->n] (mvuRight) and depth[left->n]
+ * (mvDepth).  mbf, mb as in Frame (maxD = mbf/mb). */
+int orbfe_stereo_match(orbfe_matcher* m, const orbfe_frame_view* left,
+                       const orbfe_frame_view* right, const orbfe_pyramid_view* pyr_left,
+                       const orbfe_pyramid_view* pyr_right, const float* inv_scale_factors,
+                       float mbf, float mb, float* uright, float* depth);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBFE_H */

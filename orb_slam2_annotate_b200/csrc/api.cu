@@ -1,0 +1,502 @@
+// api.cu — the C ABI of liborbfe (include/orbfe.h): extractor handle, geometry and table
+// construction (the reference constructor, src/ORBextractor.cc:415-486), host<->device
+// plumbing and the kernel schedule of ORBextractor::operator() (:1119-1197).
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "api_common.cuh"
+#include "orbfe_internal.cuh"
+
+namespace orbfe {
+
+thread_local std::string g_err;
+
+int fail(int code, const char* what, cudaError_t ce) {
+    g_err = what;
+    if (ce != cudaSuccess) { g_err += ": "; g_err += cudaGetErrorString(ce); }
+    return code;
+}
+
+static inline int cv_round(float v) { return (int)lrintf(v); }   // round-half-even
+
+}  // namespace orbfe
+
+using namespace orbfe;
+
+struct orbfe_extractor {
+    int nfeatures, nlevels, iniTh, minTh, device;
+    double scaleFactor;
+    std::vector<float> scale, inv_scale, sigma2, inv_sigma2;
+    std::vector<int> per_level;
+    int umax[16];
+    cudaStream_t stream = nullptr;
+    // geometry of the current image size / batch capacity
+    int geomW = 0, geomH = 0, geomBatchCap = 0;
+    FrameSetGeom g;
+    DevBufs d;
+    DevArray<uint8_t> pyr, blur, desc;
+    DevArray<int> cellc, selc, counts, umax_d;
+    DevArray<uint32_t> cellk, sel, qt_xy, qt_node;
+    DevArray<orbfe_keypoint> kps;
+    DevArray<int2> xtab;
+    DevArray<int4> ytab;
+    int lastBatch = 0, lastLaunches = 0;
+    // optional per-stage timing (events on the handle's stream)
+    bool profiling = false;
+    cudaEvent_t ev[8] = {};
+    std::vector<int> h_counts;
+};
+
+namespace orbfe {
+
+// Scale pyramid, per-level feature budget and the circular-patch row extents, exactly as the
+// reference constructor computes them (ORBextractor.cc:415-486).
+static void build_tables(orbfe_extractor* e, int nfeatures, float scaleFactor, int nlevels) {
+    e->scaleFactor = scaleFactor;                         // double member set from a float
+    e->scale.assign(nlevels, 1.0f); e->sigma2.assign(nlevels, 1.0f);
+    e->inv_scale.assign(nlevels, 1.0f); e->inv_sigma2.assign(nlevels, 1.0f);
+    for (int i = 1; i < nlevels; i++) {
+        e->scale[i] = (float)(e->scale[i - 1] * e->scaleFactor);
+        e->sigma2[i] = e->scale[i] * e->scale[i];
+    }
+    for (int i = 0; i < nlevels; i++) {
+        e->inv_scale[i] = 1.0f / e->scale[i];
+        e->inv_sigma2[i] = 1.0f / e->sigma2[i];
+    }
+    e->per_level.assign(nlevels, 0);
+    const float factor = (float)(1.0f / e->scaleFactor);
+    float nDesired = nfeatures * (1 - factor) / (1 - (float)std::pow((double)factor, (double)nlevels));
+    int sum = 0;
+    for (int l = 0; l < nlevels - 1; l++) {
+        e->per_level[l] = cv_round(nDesired);
+        sum += e->per_level[l];
+        nDesired *= factor;
+    }
+    e->per_level[nlevels - 1] = std::max(nfeatures - sum, 0);
+    const int vmax = (int)std::floor(kHalfPatch * std::sqrt(2.f) / 2 + 1);
+    const int vmin = (int)std::ceil(kHalfPatch * std::sqrt(2.f) / 2);
+    const double hp2 = kHalfPatch * kHalfPatch;
+    std::memset(e->umax, 0, sizeof(e->umax));
+    for (int v = 0; v <= vmax; ++v) e->umax[v] = (int)lrint(std::sqrt(hp2 - v * v));
+    for (int v = kHalfPatch, v0 = 0; v >= vmin; --v) {
+        while (e->umax[v0] == e->umax[v0 + 1]) ++v0;
+        e->umax[v] = v0;
+        ++v0;
+    }
+}
+
+// cv::resize INTER_LINEAR coefficient tables for one level
+static void resize_tables(int sw, int sh, int dw, int dh, std::vector<int2>& xt, std::vector<int4>& yt) {
+    const double scale_x = 1.0 / ((double)dw / sw), scale_y = 1.0 / ((double)dh / sh);
+    xt.resize(dw); yt.resize(dh);
+    for (int dx = 0; dx < dw; dx++) {
+        float fx = (float)((dx + 0.5) * scale_x - 0.5);
+        int sx = (int)std::floor(fx);
+        fx -= sx;
+        if (sx < 0) { fx = 0; sx = 0; }
+        if (sx >= sw - 1) { fx = 0; sx = sw - 1; }
+        const int sx1 = sx + 1 < sw ? sx + 1 : sx;
+        const int a0 = (short)cv_round((1.f - fx) * 2048.f), a1 = (short)cv_round(fx * 2048.f);
+        xt[dx] = make_int2(sx | (sx1 << 16), (a0 & 0xFFFF) | (a1 << 16));
+    }
+    for (int dy = 0; dy < dh; dy++) {
+        float fy = (float)((dy + 0.5) * scale_y - 0.5);
+        int sy = (int)std::floor(fy);
+        fy -= sy;
+        const int b0 = (short)cv_round((1.f - fy) * 2048.f), b1 = (short)cv_round(fy * 2048.f);
+        const int r0 = sy < 0 ? 0 : (sy >= sh ? sh - 1 : sy);
+        const int r1 = sy + 1 < 0 ? 0 : (sy + 1 >= sh ? sh - 1 : sy + 1);
+        yt[dy] = make_int4(r0, r1, b0, b1);
+    }
+}
+
+static inline long long align_up(long long v, long long a) { return (v + a - 1) / a * a; }
+
+// Per-level geometry for a w x h input at batch capacity B: level sizes (:1208), FAST cell
+// grid (:823-842), quadtree roots (:570-572), slot capacities and buffer offsets.
+static int build_geometry(orbfe_extractor* e, int w, int h, int batchCap, FrameSetGeom& g) {
+    std::memset(&g, 0, sizeof(g));
+    g.nlevels = e->nlevels; g.iniTh = e->iniTh; g.minTh = e->minTh;
+    long long pyrOff = 0, slotOff = 0;
+    int cellBase = 0, selBase = 0;
+    for (int l = 0; l < e->nlevels; l++) {
+        LevelGeom& L = g.lv[l];
+        L.w = cv_round((float)w * e->inv_scale[l]);
+        L.h = cv_round((float)h * e->inv_scale[l]);
+        if (L.w < 1 || L.h < 1) return fail(ORBFE_ERR_ARG, "image too small for the number of pyramid levels");
+        L.pitch = (int)align_up(L.w, 16);
+        L.lvBytes = (long long)L.pitch * L.h;
+        L.pyrOff = pyrOff;
+        pyrOff = align_up(pyrOff + L.lvBytes * batchCap, 256);
+        L.minBX = kEdgeThreshold - 3; L.minBY = L.minBX;
+        L.maxBX = L.w - kEdgeThreshold + 3; L.maxBY = L.h - kEdgeThreshold + 3;
+        const float width = (float)(L.maxBX - L.minBX), height = (float)(L.maxBY - L.minBY);
+        L.nCols = (int)(width / kCellW); L.nRows = (int)(height / kCellW);
+        if (L.nCols > 0 && L.nRows > 0) {
+            L.wCell = (int)std::ceil(width / L.nCols);
+            L.hCell = (int)std::ceil(height / L.nRows);
+        } else {
+            L.nCols = L.nRows = 0; L.wCell = L.hCell = 1;
+        }
+        if (L.wCell + 6 > kFastMaxWin || L.hCell + 6 > kFastMaxWin)
+            return fail(ORBFE_ERR_ARG, "FAST cell window exceeds the kernel's shared-memory tile");
+        L.cellBase = cellBase;
+        cellBase += L.nCols * L.nRows;
+        // strict 3x3 maxima cannot be 8-neighbours: at most ceil(zw/2)*ceil(zh/2) per zone
+        L.cellCap = ((L.wCell + 1) / 2) * ((L.hCell + 1) / 2);
+        L.cellSlotOff = slotOff;
+        if ((long long)L.nCols * L.nRows * L.cellCap > (1 << 20))
+            return fail(ORBFE_ERR_ARG, "level too large: more than 2^20 candidate corners");
+        slotOff += (long long)L.nCols * L.nRows * L.cellCap;
+        L.nFeat = e->per_level[l];
+        L.nIni = 1; L.hX = width;
+        if (L.nCols > 0) {
+            L.nIni = (int)std::round(width / (L.maxBY - L.minBY));                     // :570
+            if (L.nIni < 1) return fail(ORBFE_ERR_ARG, "image more than twice as tall as wide: the reference divides by zero here");
+            L.hX = width / L.nIni;                                                    // :572
+        }
+        L.selCap = std::max(L.nFeat + 3, 4 * L.nIni) + 5;
+        L.selBase = selBase;
+        selBase += L.selCap;
+        L.scale = e->scale[l];
+        L.scaledPatch = (int)(kPatchSize * e->scale[l]);                              // :905
+    }
+    g.pyrBytes = pyrOff;
+    g.ncells = cellBase;
+    g.cellSlots = slotOff;
+    g.selTotal = selBase;
+    g.outCap = selBase;
+    return 0;
+}
+
+}  // namespace orbfe
+
+namespace orbfe {
+
+// (re)build geometry, device buffers and resize tables for w x h images, `batch` frames
+static int ensure_geometry(orbfe_extractor* e, int w, int h, int batch) {
+    if (w == e->geomW && h == e->geomH && batch <= e->geomBatchCap) {
+        e->g.batch = batch;
+        return 0;
+    }
+    const int cap = std::max(batch, (w == e->geomW && h == e->geomH) ? e->geomBatchCap : 0);
+    FrameSetGeom g;
+    int rc = build_geometry(e, w, h, cap, g);
+    if (rc) return rc;
+    CU(cudaSetDevice(e->device));
+    CU(cudaStreamSynchronize(e->stream));
+    if ((rc = e->pyr.ensure(g.pyrBytes))) return rc;
+    if ((rc = e->blur.ensure(g.pyrBytes))) return rc;
+    if ((rc = e->cellc.ensure((size_t)cap * g.ncells + 1))) return rc;
+    if ((rc = e->cellk.ensure((size_t)cap * g.cellSlots + 1))) return rc;
+    if ((rc = e->qt_xy.ensure((size_t)cap * g.cellSlots + 1))) return rc;
+    if ((rc = e->qt_node.ensure((size_t)cap * g.cellSlots + 1))) return rc;
+    if ((rc = e->sel.ensure((size_t)cap * g.selTotal))) return rc;
+    if ((rc = e->selc.ensure((size_t)cap * g.nlevels))) return rc;
+    if ((rc = e->kps.ensure((size_t)cap * g.outCap))) return rc;
+    if ((rc = e->desc.ensure((size_t)cap * g.outCap * 32))) return rc;
+    if ((rc = e->counts.ensure(cap))) return rc;
+    // resize tables
+    std::vector<int2> xall; std::vector<int4> yall;
+    std::vector<size_t> xo(e->nlevels, 0), yo(e->nlevels, 0);
+    for (int l = 1; l < e->nlevels; l++) {
+        std::vector<int2> xt; std::vector<int4> yt;
+        resize_tables(g.lv[l - 1].w, g.lv[l - 1].h, g.lv[l].w, g.lv[l].h, xt, yt);
+        xo[l] = xall.size(); yo[l] = yall.size();
+        xall.insert(xall.end(), xt.begin(), xt.end());
+        yall.insert(yall.end(), yt.begin(), yt.end());
+    }
+    if ((rc = e->xtab.ensure(xall.size() + 1))) return rc;
+    if ((rc = e->ytab.ensure(yall.size() + 1))) return rc;
+    if (!xall.empty()) {
+        CU(cudaMemcpy(e->xtab.p, xall.data(), xall.size() * sizeof(int2), cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(e->ytab.p, yall.data(), yall.size() * sizeof(int4), cudaMemcpyHostToDevice));
+    }
+    DevBufs& d = e->d;
+    std::memset(&d, 0, sizeof(d));
+    d.pyr = e->pyr.p; d.blur = e->blur.p; d.cellc = e->cellc.p; d.cellk = e->cellk.p;
+    d.sel = e->sel.p; d.selc = e->selc.p; d.kps = e->kps.p; d.desc = e->desc.p;
+    d.counts = e->counts.p; d.qt_xy = e->qt_xy.p; d.qt_node = e->qt_node.p; d.qtCap = g.cellSlots;
+    for (int l = 1; l < e->nlevels; l++) { d.xtab[l] = e->xtab.p + xo[l]; d.ytab[l] = e->ytab.p + yo[l]; }
+    g.batch = batch;
+    e->g = g;
+    e->geomW = w; e->geomH = h; e->geomBatchCap = cap;
+    if (octree_smem_bytes(g) > 200 * 1024) return fail(ORBFE_ERR_ARG, "nfeatures too large for the quadtree kernel's shared memory");
+    cudaError_t ce = (cudaError_t)octree_prepare(g);
+    if (ce != cudaSuccess) return fail(ORBFE_ERR_CUDA, "cudaFuncSetAttribute(octree)", ce);
+    return 0;
+}
+
+// the kernel schedule of operator() on the handle's stream; level 0 is already in d.pyr
+static int enqueue_extract(orbfe_extractor* e) {
+    int launches = 0;
+    const bool prof = e->profiling;
+    if (prof) cudaEventRecord(e->ev[1], e->stream);
+    launches += launch_pyramid(e->g, e->d, e->stream);
+    if (prof) cudaEventRecord(e->ev[2], e->stream);
+    launches += launch_fast(e->g, e->d, e->stream);
+    if (prof) cudaEventRecord(e->ev[3], e->stream);
+    launches += launch_blur(e->g, e->d, e->stream);
+    if (prof) cudaEventRecord(e->ev[4], e->stream);
+    launches += launch_octree(e->g, e->d, e->stream);
+    if (prof) cudaEventRecord(e->ev[5], e->stream);
+    launches += launch_orient_desc(e->g, e->d, e->umax_d.p, e->stream);
+    if (prof) cudaEventRecord(e->ev[6], e->stream);
+    e->lastLaunches = launches;
+    CU(cudaGetLastError());
+    return 0;
+}
+
+// copy `batch` frames into level 0 of the pyramid (kind: H2D or D2D)
+static int upload_level0(orbfe_extractor* e, const uint8_t* imgs, int batch, int w, int h,
+                         ptrdiff_t stride, ptrdiff_t frame_stride, cudaMemcpyKind kind) {
+    const LevelGeom& L0 = e->g.lv[0];
+    uint8_t* dst = e->d.pyr + L0.pyrOff;
+    if (e->profiling) cudaEventRecord(e->ev[0], e->stream);
+    if (batch == 1 || frame_stride == (ptrdiff_t)h * stride) {
+        CU(cudaMemcpy2DAsync(dst, L0.pitch, imgs, stride, w, (size_t)h * batch, kind, e->stream));
+    } else {
+        for (int b = 0; b < batch; b++)
+            CU(cudaMemcpy2DAsync(dst + (long long)b * L0.lvBytes, L0.pitch, imgs + b * frame_stride,
+                                 stride, w, h, kind, e->stream));
+    }
+    return 0;
+}
+
+}  // namespace orbfe
+
+extern "C" {
+
+const char* orbfe_last_error(void) { return g_err.c_str(); }
+const char* orbfe_version(void) { return "orbfe 0.1 (sm_100a)"; }
+
+void* orbfe_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+void orbfe_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+int orbfe_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int orbfe_extractor_create(int nfeatures, float scale_factor, int nlevels, int ini_th, int min_th,
+                           int max_width, int max_height, int max_batch, int device,
+                           orbfe_extractor** out) {
+    if (!out) return fail(ORBFE_ERR_ARG, "out is NULL");
+    *out = nullptr;
+    if (nfeatures < 1 || nlevels < 1 || nlevels > kMaxLevels || !(scale_factor > 1.0f) ||
+        ini_th < 0 || min_th < 0 || ini_th > 255 || min_th > 255)
+        return fail(ORBFE_ERR_ARG, "bad extractor parameters");
+    if (max_width > kMaxDim || max_height > kMaxDim) return fail(ORBFE_ERR_ARG, "image larger than 4096 px");
+    if (orbfe_device_count() <= device || device < 0)
+        return fail(ORBFE_ERR_NO_DEVICE, "no CUDA device: liborbfe has no CPU fallback");
+    orbfe_extractor* e = new (std::nothrow) orbfe_extractor();
+    if (!e) return fail(ORBFE_ERR_ARG, "out of host memory");
+    e->nfeatures = nfeatures; e->nlevels = nlevels; e->iniTh = ini_th; e->minTh = min_th;
+    e->device = device;
+    build_tables(e, nfeatures, scale_factor, nlevels);
+    cudaError_t ce = cudaSetDevice(device);
+    if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
+    if (ce != cudaSuccess) { delete e; return fail(ORBFE_ERR_CUDA, "cudaStreamCreate", ce); }
+    int rc = e->umax_d.ensure(16);
+    if (!rc) {
+        ce = cudaMemcpy(e->umax_d.p, e->umax, sizeof(e->umax), cudaMemcpyHostToDevice);
+        if (ce != cudaSuccess) rc = fail(ORBFE_ERR_CUDA, "cudaMemcpy(umax)", ce);
+    }
+    if (!rc && max_width > 0 && max_height > 0 && max_batch > 0)
+        rc = ensure_geometry(e, max_width, max_height, max_batch);
+    if (rc) { orbfe_extractor_destroy(e); return rc; }
+    *out = e;
+    return ORBFE_OK;
+}
+
+void orbfe_extractor_destroy(orbfe_extractor* e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    if (e->stream) { cudaStreamSynchronize(e->stream); cudaStreamDestroy(e->stream); }
+    for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);
+    e->pyr.release(); e->blur.release(); e->desc.release(); e->cellc.release(); e->selc.release();
+    e->counts.release(); e->umax_d.release(); e->cellk.release(); e->sel.release();
+    e->qt_xy.release(); e->qt_node.release(); e->kps.release(); e->xtab.release(); e->ytab.release();
+    delete e;
+}
+
+int orbfe_get_scale_tables(const orbfe_extractor* e, float* scale, float* inv_scale, float* sigma2,
+                           float* inv_sigma2, int* features_per_level, int* umax) {
+    if (!e) return fail(ORBFE_ERR_ARG, "extractor is NULL");
+    for (int i = 0; i < e->nlevels; i++) {
+        if (scale) scale[i] = e->scale[i];
+        if (inv_scale) inv_scale[i] = e->inv_scale[i];
+        if (sigma2) sigma2[i] = e->sigma2[i];
+        if (inv_sigma2) inv_sigma2[i] = e->inv_sigma2[i];
+        if (features_per_level) features_per_level[i] = e->per_level[i];
+    }
+    if (umax) for (int i = 0; i < 16; i++) umax[i] = e->umax[i];
+    return ORBFE_OK;
+}
+
+int orbfe_extractor_levels(const orbfe_extractor* e) { return e ? e->nlevels : 0; }
+
+int orbfe_extractor_max_keypoints(const orbfe_extractor* e) {
+    if (!e) return 0;
+    if (e->geomW) return e->g.outCap;
+    int n = 0;
+    for (int l = 0; l < e->nlevels; l++) n += std::max(e->per_level[l] + 3, 64) + 5;
+    return n;
+}
+
+}  // extern "C"
+
+extern "C" {
+
+int orbfe_extract_batch_device(orbfe_extractor* e, const uint8_t* d_imgs, int batch, int width,
+                               int height, ptrdiff_t stride, ptrdiff_t frame_stride) {
+    if (!e || !d_imgs || batch < 1 || width < 1 || height < 1 || stride < width)
+        return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_extract_batch_device");
+    if (width > kMaxDim || height > kMaxDim) return fail(ORBFE_ERR_ARG, "image larger than 4096 px");
+    CU(cudaSetDevice(e->device));
+    int rc = ensure_geometry(e, width, height, batch);
+    if (rc) return rc;
+    if ((rc = upload_level0(e, d_imgs, batch, width, height, stride, frame_stride, cudaMemcpyDeviceToDevice))) return rc;
+    e->lastBatch = batch;
+    return enqueue_extract(e);
+}
+
+int orbfe_extractor_sync(orbfe_extractor* e) {
+    if (!e) return fail(ORBFE_ERR_ARG, "extractor is NULL");
+    CU(cudaSetDevice(e->device));
+    CU(cudaStreamSynchronize(e->stream));
+    return ORBFE_OK;
+}
+
+int orbfe_extractor_device_results(orbfe_extractor* e, const orbfe_keypoint** d_kps,
+                                   const uint8_t** d_desc, const int32_t** d_counts, int* cap) {
+    if (!e || !e->geomW) return fail(ORBFE_ERR_ARG, "no extraction has run on this handle");
+    if (d_kps) *d_kps = e->d.kps;
+    if (d_desc) *d_desc = e->d.desc;
+    if (d_counts) *d_counts = e->d.counts;
+    if (cap) *cap = e->g.outCap;
+    return ORBFE_OK;
+}
+
+int orbfe_extractor_fetch(orbfe_extractor* e, int batch, orbfe_keypoint* kps, uint8_t* desc, int cap,
+                          int* counts) {
+    if (!e || !kps || !desc || !counts || batch < 1 || batch > e->lastBatch)
+        return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_extractor_fetch");
+    CU(cudaSetDevice(e->device));
+    const int oc = e->g.outCap;
+    CU(cudaMemcpyAsync(counts, e->d.counts, sizeof(int) * batch, cudaMemcpyDeviceToHost, e->stream));
+    if (cap >= oc) {
+        // one strided copy each: rows of oc slots into rows of cap slots
+        CU(cudaMemcpy2DAsync(kps, (size_t)cap * sizeof(orbfe_keypoint), e->d.kps, (size_t)oc * sizeof(orbfe_keypoint),
+                             (size_t)oc * sizeof(orbfe_keypoint), batch, cudaMemcpyDeviceToHost, e->stream));
+        CU(cudaMemcpy2DAsync(desc, (size_t)cap * 32, e->d.desc, (size_t)oc * 32, (size_t)oc * 32, batch,
+                             cudaMemcpyDeviceToHost, e->stream));
+        CU(cudaStreamSynchronize(e->stream));
+        return ORBFE_OK;
+    }
+    CU(cudaStreamSynchronize(e->stream));
+    for (int b = 0; b < batch; b++)
+        if (counts[b] > cap) return fail(ORBFE_ERR_CAPACITY, "keypoint capacity too small (see orbfe_extractor_max_keypoints)");
+    CU(cudaMemcpy2DAsync(kps, (size_t)cap * sizeof(orbfe_keypoint), e->d.kps, (size_t)oc * sizeof(orbfe_keypoint),
+                         (size_t)cap * sizeof(orbfe_keypoint), batch, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaMemcpy2DAsync(desc, (size_t)cap * 32, e->d.desc, (size_t)oc * 32, (size_t)cap * 32, batch,
+                         cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    return ORBFE_OK;
+}
+
+int orbfe_extract_batch(orbfe_extractor* e, const uint8_t* imgs, int batch, int width, int height,
+                        ptrdiff_t stride, ptrdiff_t frame_stride, orbfe_keypoint* kps,
+                        uint8_t* desc, int cap, int* counts) {
+    if (!e || !imgs || !kps || !desc || !counts || batch < 1 || width < 1 || height < 1 || stride < width)
+        return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_extract_batch");
+    if (width > kMaxDim || height > kMaxDim) return fail(ORBFE_ERR_ARG, "image larger than 4096 px");
+    CU(cudaSetDevice(e->device));
+    int rc = ensure_geometry(e, width, height, batch);
+    if (rc) return rc;
+    if ((rc = upload_level0(e, imgs, batch, width, height, stride, frame_stride, cudaMemcpyHostToDevice))) return rc;
+    e->lastBatch = batch;
+    if ((rc = enqueue_extract(e))) return rc;
+    return orbfe_extractor_fetch(e, batch, kps, desc, cap, counts);
+}
+
+int orbfe_extract(orbfe_extractor* e, const uint8_t* img, int width, int height, ptrdiff_t stride,
+                  orbfe_keypoint* kps, uint8_t* desc, int cap, int* n) {
+    if (!e || !n) return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_extract");
+    *n = 0;
+    if (!img || width <= 0 || height <= 0) return ORBFE_OK;   // ORBextractor.cc:1122-1123
+    return orbfe_extract_batch(e, img, 1, width, height, stride, (ptrdiff_t)height * stride, kps, desc, cap, n);
+}
+
+int orbfe_extractor_set_profiling(orbfe_extractor* e, int on) {
+    if (!e) return fail(ORBFE_ERR_ARG, "extractor is NULL");
+    CU(cudaSetDevice(e->device));
+    if (on && !e->ev[0])
+        for (auto& ev : e->ev) CU(cudaEventCreate(&ev));
+    e->profiling = on != 0;
+    return ORBFE_OK;
+}
+
+int orbfe_extractor_stage_times(orbfe_extractor* e, float* ms, int n) {
+    if (!e || !ms || n < ORBFE_NUM_STAGES || !e->ev[0]) return fail(ORBFE_ERR_ARG, "profiling was not enabled");
+    CU(cudaSetDevice(e->device));
+    CU(cudaEventSynchronize(e->ev[6]));
+    for (int i = 0; i < ORBFE_NUM_STAGES; i++) CU(cudaEventElapsedTime(&ms[i], e->ev[i], e->ev[i + 1]));
+    return ORBFE_OK;
+}
+
+void* orbfe_extractor_stream(orbfe_extractor* e) { return e ? (void*)e->stream : nullptr; }
+int orbfe_extractor_last_launches(const orbfe_extractor* e) { return e ? e->lastLaunches : 0; }
+
+int orbfe_pyramid_level(orbfe_extractor* e, int frame, int level, int blurred, uint8_t* dst,
+                        ptrdiff_t dst_stride, int* width, int* height) {
+    if (!e || !e->geomW || level < 0 || level >= e->nlevels || frame < 0 || frame >= e->lastBatch)
+        return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_pyramid_level");
+    const LevelGeom& L = e->g.lv[level];
+    if (width) *width = L.w;
+    if (height) *height = L.h;
+    if (!dst) return ORBFE_OK;
+    if (dst_stride < L.w) return fail(ORBFE_ERR_ARG, "dst_stride smaller than the level width");
+    CU(cudaSetDevice(e->device));
+    const uint8_t* src = (blurred ? e->d.blur : e->d.pyr) + L.pyrOff + (long long)frame * L.lvBytes;
+    CU(cudaMemcpy2DAsync(dst, dst_stride, src, L.pitch, L.w, L.h, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    return ORBFE_OK;
+}
+
+int orbfe_level_raw_keypoints(orbfe_extractor* e, int frame, int level, int32_t* xys, int cap, int* n) {
+    if (!e || !e->geomW || !n || level < 0 || level >= e->nlevels || frame < 0 || frame >= e->lastBatch)
+        return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_level_raw_keypoints");
+    const LevelGeom& L = e->g.lv[level];
+    const int ncell = L.nCols * L.nRows;
+    *n = 0;
+    if (!ncell) return ORBFE_OK;
+    CU(cudaSetDevice(e->device));
+    std::vector<int> cc(ncell);
+    std::vector<uint32_t> ck((size_t)ncell * L.cellCap);
+    CU(cudaMemcpyAsync(cc.data(), e->d.cellc + (long long)frame * e->g.ncells + L.cellBase, sizeof(int) * ncell,
+                       cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaMemcpyAsync(ck.data(), e->d.cellk + (long long)frame * e->g.cellSlots + L.cellSlotOff,
+                       sizeof(uint32_t) * ck.size(), cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    int cnt = 0;
+    for (int c = 0; c < ncell; c++)
+        for (int k = 0; k < cc[c]; k++, cnt++)
+            if (xys && cnt < cap) {
+                const uint32_t p = ck[(size_t)c * L.cellCap + k];
+                xys[3 * cnt] = kp_x(p); xys[3 * cnt + 1] = kp_y(p); xys[3 * cnt + 2] = kp_score(p);
+            }
+    *n = cnt;
+    return (xys && cnt > cap) ? fail(ORBFE_ERR_CAPACITY, "raw keypoint capacity too small") : ORBFE_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,165 @@
+// fast.cu — K2: per-cell FAST-9/16 with score, per-cell 3x3 non-max suppression and the
+// iniThFAST -> minThFAST retry (reference src/ORBextractor.cc:815-896 calling cv::FAST twice
+// per 30-px cell; cv::FAST semantics restated in SURVEY.md §8c).
+//
+// One CTA per cell, one launch for all cells of all levels of all frames.  The CTA stages the
+// cell window (cell + 3-px ring radius on each side) in shared memory, computes for every
+// pixel of the detection zone the threshold-independent corner strength
+//     S = max( max_arc min_{9 contiguous} (v - ring), max_arc min_{9 contiguous} (ring - v) )
+// (a pixel is a FAST corner at threshold t iff S > t, and cv::FAST's score is S - 1), keeps
+// S where S > t, and applies the strict 3x3 maximum test inside the zone only — exactly what
+// running cv::FAST on the cell sub-image does, because its score rows are zero outside the
+// sub-image's 3-px inset.  If no corner survives at iniThFAST the same window is re-evaluated
+// at minThFAST.  Survivors are emitted in row-major order through a ballot/popc ordered
+// compaction, packed x | y<<12 | score<<24 with coordinates relative to (minBorderX,
+// minBorderY) as the reference stores them (:889-890).
+#include "orbfe_internal.cuh"
+
+namespace orbfe {
+
+namespace {
+
+constexpr int kThreads = 128;
+constexpr int WIN = kFastMaxWin;        // max window side
+constexpr int ZONE = WIN - 6;           // max zone side
+
+// cv::FAST ring order, (dx,dy): (0,3) (1,3) (2,2) (3,1) (3,0) (3,-1) (2,-2) (1,-3) (0,-3)
+// (-1,-3) (-2,-2) (-3,-1) (-3,0) (-3,1) (-2,2) (-1,3)
+
+// packs (d, -d) as two signed 16-bit lanes
+__device__ __forceinline__ uint32_t pack_pm(int d) {
+    return ((uint32_t)d & 0xFFFFu) | ((uint32_t)(-d) << 16);
+}
+
+// corner strength S of the pixel at p (row stride `st`), or 0 when S <= t is already certain
+__device__ __forceinline__ int corner_strength(const uint8_t* p, int st, int t) {
+    const int v = p[0];
+    int r[16];
+    // opposing pairs first: a 9-arc contains at least one pixel of every pair (k, k+8)
+    r[0] = p[3 * st];  r[8] = p[-3 * st];
+    const int lo = v - t, hi = v + t;
+    int m = ((r[0] < lo || r[8] < lo) ? 1 : 0) | ((r[0] > hi || r[8] > hi) ? 2 : 0);
+    if (!m) return 0;
+    r[4] = p[3];  r[12] = p[-3];
+    m &= ((r[4] < lo || r[12] < lo) ? 1 : 0) | ((r[4] > hi || r[12] > hi) ? 2 : 0);
+    if (!m) return 0;
+    r[2] = p[2 * st + 2];  r[10] = p[-2 * st - 2];
+    m &= ((r[2] < lo || r[10] < lo) ? 1 : 0) | ((r[2] > hi || r[10] > hi) ? 2 : 0);
+    if (!m) return 0;
+    r[6] = p[-2 * st + 2];  r[14] = p[2 * st - 2];
+    m &= ((r[6] < lo || r[14] < lo) ? 1 : 0) | ((r[6] > hi || r[14] > hi) ? 2 : 0);
+    if (!m) return 0;
+    r[1] = p[3 * st + 1];   r[9] = p[-3 * st - 1];
+    r[3] = p[st + 3];       r[11] = p[-st - 3];
+    r[5] = p[-st + 3];      r[13] = p[st - 3];
+    r[7] = p[-3 * st + 1];  r[15] = p[3 * st - 1];
+    uint32_t d[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) d[k] = pack_pm(v - r[k]);
+    // sliding minimum over 9 contiguous ring positions (circular), both polarities at once
+    uint32_t m2[16], m4[16], m8[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) m2[k] = __vmins2(d[k], d[(k + 1) & 15]);
+#pragma unroll
+    for (int k = 0; k < 16; k++) m4[k] = __vmins2(m2[k], m2[(k + 2) & 15]);
+#pragma unroll
+    for (int k = 0; k < 16; k++) m8[k] = __vmins2(m4[k], m4[(k + 4) & 15]);
+    uint32_t best = __vmins2(m8[0], d[8]);
+#pragma unroll
+    for (int k = 1; k < 16; k++) best = __vmaxs2(best, __vmins2(m8[k], d[(k + 8) & 15]));
+    const int A = (int)(short)(best & 0xFFFFu), B = (int)(short)(best >> 16);
+    const int S = max(A, B);
+    return S > t ? S : 0;
+}
+
+__global__ void __launch_bounds__(kThreads)
+fast_cells_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __restrict__ pyr,
+                  int* __restrict__ cellc, uint32_t* __restrict__ cellk) {
+    __shared__ uint8_t win[WIN][WIN + 8];
+    __shared__ uint8_t sc[ZONE + 2][ZONE + 2 + 2];
+    __shared__ int warp_cnt[kThreads / 32];
+    __shared__ int s_total;
+
+    const int cell = blockIdx.x, frame = blockIdx.y;
+    int l = 0;
+    while (l + 1 < g.nlevels && cell >= g.lv[l + 1].cellBase) l++;
+    const LevelGeom& L = g.lv[l];
+    const int c = cell - L.cellBase;
+    const int ci = c / L.nCols, cj = c - ci * L.nCols;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    int* out_cnt = cellc + (long long)frame * g.ncells + cell;
+    uint32_t* out = cellk + (long long)frame * g.cellSlots + L.cellSlotOff + (long long)c * L.cellCap;
+
+    // cell window — ORBextractor.cc:846-869 (integer-valued floats there)
+    const int iniY = L.minBY + ci * L.hCell, iniX = L.minBX + cj * L.wCell;
+    int maxY = iniY + L.hCell + 6, maxX = iniX + L.wCell + 6;
+    if (maxY > L.maxBY) maxY = L.maxBY;
+    if (maxX > L.maxBX) maxX = L.maxBX;
+    const int ww = maxX - iniX, wh = maxY - iniY;
+    if (iniY >= L.maxBY - 3 || iniX >= L.maxBX - 6 || ww < 7 || wh < 7) {
+        if (tid == 0) *out_cnt = 0;
+        return;
+    }
+    const int zw = ww - 6, zh = wh - 6;
+    const uint8_t* src = pyr + L.pyrOff + (long long)frame * L.lvBytes +
+                         (long long)iniY * L.pitch + iniX;
+    for (int i = tid; i < ww * wh; i += kThreads) {
+        const int r = i / ww, cc = i - r * ww;
+        win[r][cc] = src[(long long)r * L.pitch + cc];
+    }
+    for (int i = tid; i < (zh + 2) * (zw + 2); i += kThreads) {   // zero ring of the score map
+        const int r = i / (zw + 2), cc = i - r * (zw + 2);
+        if (r == 0 || r == zh + 1 || cc == 0 || cc == zw + 1) sc[r][cc] = 0;
+    }
+    if (tid == 0) s_total = 0;
+    __syncthreads();
+
+    const int npx = zw * zh;
+    for (int pass = 0; pass < 2; pass++) {
+        const int t = pass == 0 ? g.iniTh : g.minTh;
+        for (int i = tid; i < npx; i += kThreads) {
+            const int r = i / zw, cc = i - r * zw;
+            sc[r + 1][cc + 1] = (uint8_t)corner_strength(&win[r + 3][cc + 3], WIN + 8, t);
+        }
+        __syncthreads();
+        // 3x3 strict maximum + ordered (row-major) compaction
+        for (int base = 0; base < npx; base += kThreads) {
+            const int i = base + tid;
+            bool keep = false;
+            int r = 0, cc = 0, s = 0;
+            if (i < npx) {
+                r = i / zw; cc = i - r * zw;
+                s = sc[r + 1][cc + 1];
+                keep = s > 0 && s > sc[r][cc] && s > sc[r][cc + 1] && s > sc[r][cc + 2] &&
+                       s > sc[r + 1][cc] && s > sc[r + 1][cc + 2] && s > sc[r + 2][cc] &&
+                       s > sc[r + 2][cc + 1] && s > sc[r + 2][cc + 2];
+            }
+            const unsigned b = __ballot_sync(0xFFFFFFFFu, keep);
+            if (lane == 0) warp_cnt[wid] = __popc(b);
+            __syncthreads();
+            int pos = s_total;
+            for (int w = 0; w < wid; w++) pos += warp_cnt[w];
+            pos += __popc(b & ((1u << lane) - 1u));
+            if (keep && pos < L.cellCap)
+                out[pos] = pack_kp(cc + 3 + cj * L.wCell, r + 3 + ci * L.hCell, s - 1);
+            __syncthreads();
+            if (tid == 0) {
+                int tot = s_total;
+                for (int w = 0; w < kThreads / 32; w++) tot += warp_cnt[w];
+                s_total = tot;
+            }
+            __syncthreads();
+        }
+        if (s_total > 0) break;
+    }
+    if (tid == 0) *out_cnt = min(s_total, L.cellCap);
+}
+
+}  // namespace
+
+int launch_fast(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
+    fast_cells_kernel<<<dim3(g.ncells, g.batch), kThreads, 0, s>>>(g, d.pyr, d.cellc, d.cellk);
+    return 1;
+}
+
+}  // namespace orbfe

@@ -1,0 +1,145 @@
+"""Python mirror of ``ORB_SLAM2::ORBmatcher`` (reference include/ORBmatcher.h:51-117) for the
+routines on the hot path, on top of the C ABI.  Frames and map points are passed as plain
+arrays (the "views" of include/orbfe.h); results come back as index arrays the caller writes
+into its own Frame / MapPoint objects, exactly what the C++ adapter does.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import KP_DTYPE, FrameView, MapPointsView, PyramidView, check
+
+
+class Frame:
+    """The fields of ``ORB_SLAM2::Frame`` the matcher reads (include/Frame.h): undistorted
+    keypoints, descriptors, optional ``mvuRight``, image bounds and scale factors."""
+
+    def __init__(self, keypoints: np.ndarray, descriptors: np.ndarray, width: float, height: float,
+                 scale_factors: np.ndarray, uright: np.ndarray | None = None,
+                 min_x: float = 0.0, min_y: float = 0.0):
+        self.kps = np.ascontiguousarray(keypoints, KP_DTYPE)
+        self.desc = np.ascontiguousarray(descriptors if descriptors is not None else np.zeros((0, 32)), np.uint8).reshape(-1, 32)
+        assert len(self.kps) == len(self.desc)
+        self.scale_factors = np.ascontiguousarray(scale_factors, np.float32)
+        self.uright = None if uright is None else np.ascontiguousarray(uright, np.float32)
+        self.min_x, self.max_x, self.min_y, self.max_y = float(min_x), float(width), float(min_y), float(height)
+
+    @property
+    def N(self) -> int:
+        return len(self.kps)
+
+    def view(self) -> FrameView:
+        return FrameView(self.N, self.kps.ctypes.data, self.desc.ctypes.data,
+                         None if self.uright is None else self.uright.ctypes.data,
+                         self.min_x, self.max_x, self.min_y, self.max_y,
+                         self.scale_factors.ctypes.data, len(self.scale_factors))
+
+
+class ORBmatcher:
+    """``ORBmatcher(nnratio=0.6, checkOri=True)`` (src/ORBmatcher.cc:41)."""
+
+    TH_HIGH, TH_LOW, HISTO_LENGTH = 100, 50, 30   # src/ORBmatcher.cc:37-39
+
+    def __init__(self, nnratio: float = 0.6, checkOri: bool = True, *, device: int = 0):
+        self._L = _lib.lib()
+        self.mfNNratio, self.mbCheckOrientation = float(nnratio), bool(checkOri)
+        self._h = C.c_void_p()
+        check(self._L.orbfe_matcher_create(device, C.byref(self._h)), "orbfe_matcher_create")
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._L.orbfe_matcher_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def stream(self) -> int:
+        return int(self._L.orbfe_matcher_stream(self._h) or 0)
+
+    def sync(self) -> None:
+        check(self._L.orbfe_matcher_sync(self._h))
+
+    @staticmethod
+    def DescriptorDistance(a: np.ndarray, b: np.ndarray) -> int:
+        """src/ORBmatcher.cc:1828-1844 (host scalar, as in the reference)."""
+        a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+        assert a.size == 32 and b.size == 32
+        return _lib.lib().orbfe_hamming256(a.ctypes.data, b.ctypes.data)
+
+    def knn2(self, query: np.ndarray, train: np.ndarray, th: int | None = None, ratio: float | None = None):
+        """Brute-force best/second-best search + TH_LOW/ratio acceptance (src/ORBmatcher.cc:233-269).
+        -> (idx int32[M] (-1 = rejected), d1 int32[M], d2 int32[M])"""
+        q = np.ascontiguousarray(query, np.uint8).reshape(-1, 32)
+        t = np.ascontiguousarray(train, np.uint8).reshape(-1, 32)
+        th = self.TH_LOW if th is None else th
+        ratio = self.mfNNratio if ratio is None else ratio
+        m = len(q)
+        idx, d1, d2 = (np.empty(m, np.int32) for _ in range(3))
+        check(self._L.orbfe_knn2(self._h, q.ctypes.data, m, t.ctypes.data, len(t), th, ratio,
+                                 idx.ctypes.data, d1.ctypes.data, d2.ctypes.data), "orbfe_knn2")
+        return idx, d1, d2
+
+    def knn2_device(self, q_ptr: int, m: int, t_ptr: int, n: int, idx_ptr: int, d1_ptr: int, d2_ptr: int,
+                    th: int | None = None, ratio: float | None = None) -> None:
+        th = self.TH_LOW if th is None else th
+        ratio = self.mfNNratio if ratio is None else ratio
+        check(self._L.orbfe_knn2_device(self._h, q_ptr, m, t_ptr, n, th, ratio, idx_ptr, d1_ptr, d2_ptr),
+              "orbfe_knn2_device")
+
+    def SearchForInitialization(self, F1: Frame, F2: Frame, vbPrevMatched: np.ndarray, windowSize: int = 10):
+        """src/ORBmatcher.cc:469-600.  vbPrevMatched float32 [N1,2] is updated in place.
+        -> (nmatches, vnMatches12 int32[N1])"""
+        assert vbPrevMatched.dtype == np.float32 and vbPrevMatched.flags.c_contiguous and vbPrevMatched.shape == (F1.N, 2)
+        m12 = np.empty(max(F1.N, 1), np.int32)
+        n = C.c_int()
+        v1, v2 = F1.view(), F2.view()
+        check(self._L.orbfe_search_init(self._h, C.byref(v1), C.byref(v2), vbPrevMatched.ctypes.data,
+                                        m12.ctypes.data, windowSize, self.mfNNratio,
+                                        int(self.mbCheckOrientation), C.byref(n)), "orbfe_search_init")
+        return n.value, m12[:F1.N]
+
+    def SearchByProjection(self, F: Frame, mappoints: dict, th: float = 3.0, occupied: np.ndarray | None = None):
+        """SearchByProjection(Frame&, vector<MapPoint*>&, th) — src/ORBmatcher.cc:51-138.
+        mappoints: dict of arrays track_in_view u8, proj_x/proj_y/proj_xr f32, level i32,
+        view_cos f32, desc u8[n,32], observations i32.  occupied u8[N] in/out.
+        -> (nmatches, mp_for_kp int32[N])"""
+        spec = dict(track_in_view=np.uint8, proj_x=np.float32, proj_y=np.float32, proj_xr=np.float32,
+                    level=np.int32, view_cos=np.float32, desc=np.uint8, observations=np.int32)
+        keep = {k: np.ascontiguousarray(mappoints[k], t) for k, t in spec.items()}
+        v = MapPointsView(len(keep["level"]), *[keep[k].ctypes.data for k in
+                          ("track_in_view", "proj_x", "proj_y", "proj_xr", "level", "view_cos", "desc", "observations")])
+        if occupied is None:
+            occupied = np.zeros(max(F.N, 1), np.uint8)
+        out = np.full(max(F.N, 1), -1, np.int32)
+        n = C.c_int()
+        fv = F.view()
+        check(self._L.orbfe_search_local_points(self._h, C.byref(fv), C.byref(v), th, self.mfNNratio,
+                                                occupied.ctypes.data, out.ctypes.data, C.byref(n)),
+              "orbfe_search_local_points")
+        return n.value, out[:F.N]
+
+    def ComputeStereoMatches(self, left: Frame, right: Frame, pyr_left: list, pyr_right: list,
+                             inv_scale_factors: np.ndarray, mbf: float, mb: float):
+        """Frame::ComputeStereoMatches — src/Frame.cc:512-686. -> (mvuRight f32[N], mvDepth f32[N])"""
+        def pv(levels):
+            lv = [np.ascontiguousarray(l, np.uint8) for l in levels]
+            ptrs = (C.c_void_p * len(lv))(*[l.ctypes.data for l in lv])
+            w = np.array([l.shape[1] for l in lv], np.int32); h = np.array([l.shape[0] for l in lv], np.int32)
+            st = np.array([l.strides[0] for l in lv], np.int64)
+            return PyramidView(len(lv), C.cast(ptrs, C.c_void_p), w.ctypes.data, h.ctypes.data, st.ctypes.data), (lv, ptrs, w, h, st)
+        pl, k1 = pv(pyr_left); pr, k2 = pv(pyr_right)
+        inv = np.ascontiguousarray(inv_scale_factors, np.float32)
+        ur = np.empty(max(left.N, 1), np.float32); dp = np.empty(max(left.N, 1), np.float32)
+        lv, rv = left.view(), right.view()
+        check(self._L.orbfe_stereo_match(self._h, C.byref(lv), C.byref(rv), C.byref(pl), C.byref(pr),
+                                         inv.ctypes.data, mbf, mb, ur.ctypes.data, dp.ctypes.data),
+              "orbfe_stereo_match")
+        return ur[:left.N], dp[:left.N]
