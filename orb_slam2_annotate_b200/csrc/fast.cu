@@ -84,6 +84,7 @@ fast_cells_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __restr
     int l = 0;
     while (l + 1 < g.nlevels && cell >= g.lv[l + 1].cellBase) l++;
     const LevelGeom& L = g.lv[l];
+    if (L.wCell + 6 <= 48 && L.hCell + 6 <= 48) return;       // done by fast_cells_warp_kernel
     const int c = cell - L.cellBase;
     const int ci = c / L.nCols, cj = c - ci * L.nCols;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -155,11 +156,207 @@ fast_cells_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __restr
     if (tid == 0) *out_cnt = min(s_total, L.cellCap);
 }
 
+
+// ---------------------------------------------------------------------------------------
+// Warp-per-cell kernel (all cells whose window fits 48x48, i.e. every level of the usual
+// camera sizes).  Stage 1 rejects pixels four at a time with byte-SIMD arithmetic: a 9-arc
+// always contains one pixel of each opposing ring pair, so a corner needs, for every pair,
+// |ring - v| > t on at least one side; VABSDIFF4 plus a carry-free SWAR compare evaluate that
+// for the pairs (0,8), (4,12), (2,10), (6,14) on whole 32-bit words of the aligned window.
+// Stage 2 runs the exact polarity-aware test and the corner strength only on the survivors
+// (a dense work list in shared memory).  Stage 3 applies the per-cell 3x3 strict maximum and
+// marks survivors in a bitmap; popc prefix sums over the bitmap give every survivor its
+// row-major output rank, so the emitted order equals cv::FAST's.
+constexpr int WWIN = 48;                 // max window side of the warp kernel
+constexpr int WS = 16;                   // window row stride in 32-bit words (1 pad word left)
+constexpr int WZ = WWIN - 6;             // max zone side
+constexpr int SCS = 48;                  // score-map row stride in bytes
+constexpr int kWarpsPerCta = 4;
+constexpr int BMW = (WZ * WZ + 31) / 32; // bitmap words
+
+struct WarpSmem {
+    uint32_t win[WWIN][WS];
+    uint8_t sc[WZ + 2][SCS];
+    unsigned short list[WZ * WZ];
+    uint32_t bitmap[BMW + 1];
+    int bmpre[BMW + 1];
+    int counter;
+};
+
+__device__ __forceinline__ uint32_t swar_gt(uint32_t d, uint32_t c, bool small_t) {
+    const uint32_t m = (d & 0x7F7F7F7Fu) + c;       // per byte, no carry across bytes
+    return (small_t ? (m | d) : (m & d)) & 0x80808080u;
+}
+
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __restrict__ pyr,
+                       int* __restrict__ cellc, uint32_t* __restrict__ cellk) {
+    __shared__ WarpSmem smem[kWarpsPerCta];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    WarpSmem& S = smem[wid];
+    const long long gcell = (long long)blockIdx.x * kWarpsPerCta + wid;
+    if (gcell >= (long long)g.ncells * g.batch) return;
+    const int frame = (int)(gcell / g.ncells), cell = (int)(gcell - (long long)frame * g.ncells);
+    int l = 0;
+    while (l + 1 < g.nlevels && cell >= g.lv[l + 1].cellBase) l++;
+    const LevelGeom& L = g.lv[l];
+    if (L.wCell + 6 > WWIN || L.hCell + 6 > WWIN) return;     // handled by the generic kernel
+    const int c = cell - L.cellBase;
+    const int ci = c / L.nCols, cj = c - ci * L.nCols;
+    int* out_cnt = cellc + (long long)frame * g.ncells + cell;
+    uint32_t* out = cellk + (long long)frame * g.cellSlots + L.cellSlotOff + (long long)c * L.cellCap;
+
+    const int iniY = L.minBY + ci * L.hCell, iniX = L.minBX + cj * L.wCell;     // :846-869
+    int maxY = iniY + L.hCell + 6, maxX = iniX + L.wCell + 6;
+    if (maxY > L.maxBY) maxY = L.maxBY;
+    if (maxX > L.maxBX) maxX = L.maxBX;
+    const int ww = maxX - iniX, wh = maxY - iniY;
+    if (iniY >= L.maxBY - 3 || iniX >= L.maxBX - 6 || ww < 7 || wh < 7) {
+        if (lane == 0) *out_cnt = 0;
+        return;
+    }
+    const int zw = ww - 6, zh = wh - 6;
+    const int ax0 = iniX & ~3;                       // aligned window origin (level coordinates)
+    const int nw = ((maxX + 3) >> 2) - (ax0 >> 2);   // words per window row (<= 14)
+    const int zx0 = iniX + 3 - ax0, zx1 = maxX - 3 - ax0;   // zone columns in window bytes
+    const int zc0 = zx0 >> 2, nzc = ((zx1 - 1) >> 2) - zc0 + 1;
+    const uint8_t* src = pyr + L.pyrOff + (long long)frame * L.lvBytes + (long long)iniY * L.pitch + ax0;
+    for (int i = lane; i < wh * nw; i += 32) {
+        const int r = i / nw, cc = i - r * nw;
+        S.win[r][cc + 1] = __ldg(reinterpret_cast<const uint32_t*>(src + (long long)r * L.pitch) + cc);
+    }
+    const uint8_t* wb = reinterpret_cast<const uint8_t*>(&S.win[0][0]) + 4;   // byte (r, x) = wb[r*WS*4 + x]
+
+    int total = 0;
+    for (int pass = 0; pass < 2; pass++) {
+        const int t = pass == 0 ? g.iniTh : g.minTh;
+        const bool small_t = t < 128;
+        const uint32_t cmpc = (uint32_t)(small_t ? 0x7F - t : 0x7F - (t - 128)) * 0x01010101u;
+        // zero score map, bitmap, counters
+        for (int i = lane; i < (zh + 2) * (SCS / 4); i += 32) reinterpret_cast<uint32_t*>(&S.sc[0][0])[i] = 0;
+        for (int i = lane; i <= BMW; i += 32) S.bitmap[i] = 0;
+        if (lane == 0) S.counter = 0;
+        __syncwarp();
+        // ---- stage 1: SIMD rejection, 4 pixels per task
+        for (int i = lane; i < zh * nzc; i += 32) {
+            const int r = i / nzc, cc = i - r * nzc;
+            const int y = r + 3, wc = zc0 + cc + 1;          // window row, word column (+1 pad)
+            const uint32_t v = S.win[y][wc];
+            uint32_t gmask = swar_gt(__vabsdiffu4(S.win[y + 3][wc], v), cmpc, small_t) |
+                             swar_gt(__vabsdiffu4(S.win[y - 3][wc], v), cmpc, small_t);
+            // bytes of this word inside the zone
+            const int xb = (zc0 + cc) * 4;
+            uint32_t zm = 0x80808080u;
+            if (xb < zx0) zm &= 0xFFFFFFFFu << (8 * (zx0 - xb));
+            if (xb + 4 > zx1) zm &= 0xFFFFFFFFu >> (8 * (xb + 4 - zx1));
+            gmask &= zm;
+            if (!gmask) continue;
+            const uint32_t wl = S.win[y][wc - 1], wr = S.win[y][wc + 1];
+            gmask &= swar_gt(__vabsdiffu4(__funnelshift_r(v, wr, 24), v), cmpc, small_t) |
+                     swar_gt(__vabsdiffu4(__funnelshift_r(wl, v, 8), v), cmpc, small_t);
+            if (!gmask) continue;
+            const uint32_t r2 = __funnelshift_r(S.win[y + 2][wc], S.win[y + 2][wc + 1], 16);
+            const uint32_t r10 = __funnelshift_r(S.win[y - 2][wc - 1], S.win[y - 2][wc], 16);
+            gmask &= swar_gt(__vabsdiffu4(r2, v), cmpc, small_t) | swar_gt(__vabsdiffu4(r10, v), cmpc, small_t);
+            if (!gmask) continue;
+            const uint32_t r6 = __funnelshift_r(S.win[y - 2][wc], S.win[y - 2][wc + 1], 16);
+            const uint32_t r14 = __funnelshift_r(S.win[y + 2][wc - 1], S.win[y + 2][wc], 16);
+            gmask &= swar_gt(__vabsdiffu4(r6, v), cmpc, small_t) | swar_gt(__vabsdiffu4(r14, v), cmpc, small_t);
+            if (!gmask) continue;
+            const int k = __popc(gmask);
+            int pos = atomicAdd(&S.counter, k);
+#pragma unroll
+            for (int b = 0; b < 4; b++)
+                if (gmask & (0x80u << (8 * b))) S.list[pos++] = (unsigned short)((r << 8) | (xb + b - zx0));
+        }
+        __syncwarp();
+        // ---- stage 2: exact test + strength on the survivors
+        const int ncand = S.counter;
+        __syncwarp();
+        if (lane == 0) S.counter = 0;
+        __syncwarp();
+        for (int base = 0; base < ncand; base += 32) {
+            const int i = base + lane;
+            int e = 0, s = 0;
+            if (i < ncand) e = S.list[i];
+            __syncwarp();
+            if (i < ncand) {
+                const int r = e >> 8, cc = e & 0xFF;
+                s = corner_strength(wb + (r + 3) * (WS * 4) + zx0 + cc, WS * 4, t);
+                if (s) {
+                    S.sc[r + 1][cc + 1] = (uint8_t)s;
+                    S.list[atomicAdd(&S.counter, 1)] = (unsigned short)e;
+                }
+            }
+        }
+        __syncwarp();
+        // ---- stage 3: 3x3 strict maximum inside the zone, survivors into the bitmap
+        const int ncorn = S.counter;
+        for (int i = lane; i < ncorn; i += 32) {
+            const int e = S.list[i], r = e >> 8, cc = e & 0xFF;
+            const int s = S.sc[r + 1][cc + 1];
+            const bool keep = s > S.sc[r][cc] && s > S.sc[r][cc + 1] && s > S.sc[r][cc + 2] &&
+                              s > S.sc[r + 1][cc] && s > S.sc[r + 1][cc + 2] && s > S.sc[r + 2][cc] &&
+                              s > S.sc[r + 2][cc + 1] && s > S.sc[r + 2][cc + 2];
+            if (keep) {
+                const int bit = r * zw + cc;
+                atomicOr(&S.bitmap[bit >> 5], 1u << (bit & 31));
+            }
+        }
+        __syncwarp();
+        // ---- ordered emission: exclusive popc prefix over the bitmap words
+        const int nbw = (zw * zh + 31) >> 5;
+        int carry = 0;
+        for (int base = 0; base < nbw; base += 32) {
+            const int w = base + lane;
+            const int v = w < nbw ? __popc(S.bitmap[w]) : 0;
+            int inc = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int u = __shfl_up_sync(0xFFFFFFFFu, inc, o);
+                if (lane >= o) inc += u;
+            }
+            if (w < nbw) S.bmpre[w] = carry + inc - v;
+            carry += __shfl_sync(0xFFFFFFFFu, inc, 31);
+        }
+        total = carry;
+        __syncwarp();
+        if (total > 0) {
+            for (int i = lane; i < ncorn; i += 32) {
+                const int e = S.list[i], r = e >> 8, cc = e & 0xFF;
+                const int bit = r * zw + cc;
+                const uint32_t word = S.bitmap[bit >> 5];
+                if (word & (1u << (bit & 31))) {
+                    const int pos = S.bmpre[bit >> 5] + __popc(word & ((1u << (bit & 31)) - 1u));
+                    if (pos < L.cellCap)
+                        out[pos] = pack_kp(cc + 3 + cj * L.wCell, r + 3 + ci * L.hCell, S.sc[r + 1][cc + 1] - 1);
+                }
+            }
+            break;
+        }
+        __syncwarp();
+    }
+    if (lane == 0) *out_cnt = min(total, L.cellCap);
+}
+
 }  // namespace
 
 int launch_fast(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
-    fast_cells_kernel<<<dim3(g.ncells, g.batch), kThreads, 0, s>>>(g, d.pyr, d.cellc, d.cellk);
-    return 1;
+    int launches = 0;
+    bool generic = false;
+    for (int l = 0; l < g.nlevels; l++)
+        if (g.lv[l].nCols && (g.lv[l].wCell + 6 > WWIN || g.lv[l].hCell + 6 > WWIN)) generic = true;
+    const long long ncell = (long long)g.ncells * g.batch;
+    if (ncell > 0) {
+        fast_cells_warp_kernel<<<(unsigned)((ncell + kWarpsPerCta - 1) / kWarpsPerCta), kWarpsPerCta * 32, 0, s>>>(
+            g, d.pyr, d.cellc, d.cellk);
+        launches++;
+    }
+    if (generic) {
+        fast_cells_kernel<<<dim3(g.ncells, g.batch), kThreads, 0, s>>>(g, d.pyr, d.cellc, d.cellk);
+        launches++;
+    }
+    return launches;
 }
 
 }  // namespace orbfe

@@ -121,3 +121,424 @@ __device__ void three_maxima(const int* hist, int& ind1, int& ind2, int& ind3) {
     if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
     else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { ind3 = -1; }
 }
+
+// ---------------------------------------------------------------------------------------
+// SearchForInitialization — one warp per frame pair.
+struct InitArgs {
+    const orbfe_keypoint* kps;   // [frames][cap]
+    const uint8_t* desc;         // [frames][cap][32]
+    const int* counts;           // [frames]
+    int cap;
+    const int2* pairs;           // frame indices (F1, F2) per pair, or NULL for (p, p+1)
+    float* prev;                 // [pairs][cap][2] vbPrevMatched in/out, or NULL: F1 keypoint positions
+    int* m12;                    // [pairs][cap] vnMatches12
+    int* nmatches;               // [pairs]
+    GridGeom grid;
+    int window;
+    float ratio;
+    int checkOri;
+};
+
+__global__ void __launch_bounds__(32)
+search_init_kernel(const __grid_constant__ InitArgs a) {
+    extern __shared__ __align__(16) unsigned char sm[];
+    const int lane = threadIdx.x, p = blockIdx.x;
+    const int fa = a.pairs ? a.pairs[p].x : p, fb = a.pairs ? a.pairs[p].y : p + 1;
+    const int n1 = a.counts[fa], n2 = a.counts[fb];
+    const orbfe_keypoint* kp1 = a.kps + (long long)fa * a.cap;
+    const orbfe_keypoint* kp2 = a.kps + (long long)fb * a.cap;
+    const uint8_t* d1 = a.desc + (long long)fa * a.cap * 32;
+    const uint8_t* d2 = a.desc + (long long)fb * a.cap * 32;
+    int* m12 = a.m12 + (long long)p * a.cap;
+    float* prev = a.prev ? a.prev + (long long)p * a.cap * 2 : nullptr;
+
+    int* cell_end = (int*)sm;                                    // NCELL
+    int* hist = cell_end + NCELL;                                // 32
+    unsigned short* items = (unsigned short*)(hist + 32);        // cap
+    unsigned short* m21 = items + a.cap;                         // cap   (0xFFFF = none)
+    unsigned char* mdist = (unsigned char*)(m21 + a.cap);        // cap   (255 = INT_MAX)
+    unsigned char* binof = mdist + a.cap;                        // cap   (255 = not in rotHist)
+
+    for (int i = lane; i < n1; i += 32) { m12[i] = -1; binof[i] = 255; }
+    for (int i = lane; i < n2; i += 32) { m21[i] = 0xFFFF; mdist[i] = 255; }
+    hist[lane] = 0;
+    warp_build_grid(a.grid, kp2, n2, cell_end, items);
+    __syncwarp();
+
+    int nm = 0;
+    const float r = (float)a.window;
+    const float factor = 1.0f / HISTO;                                                  // :476
+    for (int i1 = 0; i1 < n1; i1++) {
+        const orbfe_keypoint k1 = kp1[i1];
+        if (k1.octave > 0) continue;                                                    // :487-489
+        const float qx = prev ? prev[2 * i1] : k1.x, qy = prev ? prev[2 * i1 + 1] : k1.y;
+        int cx0, cx1, cy0, cy1;
+        if (!cell_window(a.grid, qx, qy, r, cx0, cx1, cy0, cy1)) continue;
+        uint32_t q[8];
+        load_row(q, d1 + 32 * (long long)i1);
+        uint32_t b1 = KEY_INF, b2 = KEY_INF;
+        int bi = -1, seq = 0;
+        for (int ix = cx0; ix <= cx1; ix++) {
+            const int c0 = ix * GR + cy0;
+            const int s = c0 ? cell_end[c0 - 1] : 0, e = cell_end[ix * GR + cy1];
+            for (int j = s + lane; j < e; j += 32) {
+                const int i2 = items[j];
+                const orbfe_keypoint k2 = kp2[i2];
+                if (k2.octave != 0) continue;                 // minLevel = maxLevel = 0 (:494, Frame.cc:381-395)
+                if (!(fabsf(__fsub_rn(k2.x, qx)) < r && fabsf(__fsub_rn(k2.y, qy)) < r)) continue;
+                const int dist = hamming256(q, d2 + 32 * (long long)i2);
+                if (mdist[i2] != 255 && (int)mdist[i2] <= dist) continue;           // :515-516
+                const uint32_t key = ((uint32_t)dist << 20) | (uint32_t)(seq + j - s);
+                if (key < b1) { b2 = b1; b1 = key; bi = i2; }                           // :518-527
+                else if (key < b2) b2 = key;
+            }
+            seq += e - s;
+        }
+        const uint32_t g1 = warp_min(b1);
+        if (g1 == KEY_INF) continue;
+        const unsigned own = __ballot_sync(FULL, b1 == g1);
+        const int best = __shfl_sync(FULL, bi, __ffs(own) - 1);
+        const uint32_t g2 = warp_min(b1 == g1 ? b2 : b1);
+        const int bestDist = (int)(g1 >> 20);
+        const float second = g2 == KEY_INF ? (float)INT_MAX : (float)(int)(g2 >> 20);
+        if (bestDist <= TH_LOW && (float)bestDist < __fmul_rn(second, a.ratio)) {       // :532-534
+            if (lane == 0) {
+                if (m21[best] != 0xFFFF) m12[m21[best]] = -1;                           // :536-540
+                m12[i1] = best;
+                m21[best] = (unsigned short)i1;
+                mdist[best] = (unsigned char)bestDist;
+                if (a.checkOri) {                                                       // :549-559
+                    float rot = __fsub_rn(k1.angle, kp2[best].angle);
+                    if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+                    int bin = (int)roundf(__fmul_rn(rot, factor));
+                    if (bin == HISTO) bin = 0;
+                    binof[i1] = (unsigned char)bin;
+                    hist[bin]++;
+                }
+            }
+            __syncwarp();
+        }
+    }
+    __syncwarp();
+    if (a.checkOri) {                                                                   // :566-590
+        int ind1, ind2, ind3;
+        three_maxima(hist, ind1, ind2, ind3);
+        for (int i = lane; i < n1; i += 32) {
+            const int b = binof[i];
+            if (b != 255 && b != ind1 && b != ind2 && b != ind3 && m12[i] >= 0) m12[i] = -1;
+        }
+        __syncwarp();
+    }
+    for (int i = lane; i < n1; i += 32) {                                               // :595-597
+        const int m = m12[i];
+        if (m >= 0) {
+            nm++;
+            if (prev) { prev[2 * i] = kp2[m].x; prev[2 * i + 1] = kp2[m].y; }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) nm += __shfl_xor_sync(FULL, nm, o);
+    if (lane == 0) a.nmatches[p] = nm;
+}
+
+size_t search_init_smem(int cap) { return (size_t)(NCELL + 32) * 4 + (size_t)cap * 6 + 16; }
+
+// ---------------------------------------------------------------------------------------
+// SearchByProjection(Frame&, vector<MapPoint*>&, th)
+struct LocalArgs {
+    const orbfe_keypoint* kps;   // frame keypoints [n]
+    const uint8_t* desc;         // [n][32]
+    const float* uright;         // [n] or NULL
+    int n;
+    const float* scale;          // mvScaleFactors
+    int nlevels;
+    // map points
+    int nmp;
+    const uint8_t* in_view;
+    const float* px; const float* py; const float* pxr;
+    const int* level; const float* view_cos;
+    const uint8_t* mpdesc;
+    const int* obs;
+    float th, ratio;
+    GridGeom grid;
+    // grid CSR of the frame
+    int* cell_end; unsigned short* items;
+    // candidate lists: cand_off[nmp+1] (exclusive scan of counts), cand[] packed idx | dist<<16 | octave<<25
+    int* cand_off; uint32_t* cand;
+    // fixed-point state
+    const uint8_t* occ0;         // keypoint already holds a map point with observations
+    int* owner_prev; int* owner_next; int* choice; int* changed;
+};
+
+__global__ void __launch_bounds__(32) build_grid_kernel(const __grid_constant__ LocalArgs a) {
+    warp_build_grid(a.grid, a.kps, a.n, a.cell_end, a.items);
+}
+
+// Enumerates the candidates of one map point in GetFeaturesInArea order; FILL=false counts,
+// FILL=true writes the packed list (keypoint index, Hamming distance, octave).
+template <bool FILL>
+__global__ void __launch_bounds__(128) local_candidates_kernel(const __grid_constant__ LocalArgs a) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.nmp) return;
+    int count = 0;
+    uint32_t* out = FILL ? a.cand + a.cand_off[i] : nullptr;
+    if (a.in_view[i]) {                                                                 // :58-62
+        const int lvl = a.level[i];
+        float r = (double)a.view_cos[i] > 0.998 ? 2.5f : 4.0f;                          // :146-152 (double compare)
+        if (a.th != 1.0f) r = __fmul_rn(r, a.th);                                       // :56,:69-70
+        const float rs = __fmul_rn(r, a.scale[lvl]);
+        const float x = a.px[i], y = a.py[i];
+        const int minLevel = lvl - 1, maxLevel = lvl;
+        const bool check = (minLevel > 0) || (maxLevel >= 0);                           // Frame.cc:381
+        int cx0, cx1, cy0, cy1;
+        if (cell_window(a.grid, x, y, rs, cx0, cx1, cy0, cy1)) {
+            uint32_t q[8];
+            if (FILL) load_row(q, a.mpdesc + 32 * (long long)i);
+            for (int ix = cx0; ix <= cx1; ix++) {
+                const int c0 = ix * GR + cy0;
+                const int s = c0 ? a.cell_end[c0 - 1] : 0, e = a.cell_end[ix * GR + cy1];
+                for (int j = s; j < e; j++) {
+                    const int idx = a.items[j];
+                    const orbfe_keypoint k = a.kps[idx];
+                    if (check) {
+                        if (k.octave < minLevel) continue;
+                        if (maxLevel >= 0 && k.octave > maxLevel) continue;
+                    }
+                    if (!(fabsf(__fsub_rn(k.x, x)) < rs && fabsf(__fsub_rn(k.y, y)) < rs)) continue;
+                    if (a.uright && a.uright[idx] > 0) {                                // :100-105
+                        const float er = fabsf(__fsub_rn(a.pxr[i], a.uright[idx]));
+                        if (er > rs) continue;
+                    }
+                    if (FILL) {
+                        const int dist = hamming256(q, a.desc + 32 * (long long)idx);
+                        out[count] = (uint32_t)idx | ((uint32_t)dist << 16) | ((uint32_t)(k.octave & 0x3F) << 25);
+                    }
+                    count++;
+                }
+            }
+        }
+    }
+    if (!FILL) a.cand_off[i] = count;
+}
+
+// single-CTA exclusive scan of cand_off[0..n) in place; cand_off[n] = total
+__global__ void __launch_bounds__(1024) scan_kernel(int* data, int n) {
+    __shared__ int wsum[33];
+    __shared__ int carry;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (tid == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < n; base += 1024) {
+        const int i = base + tid;
+        const int v = i < n ? data[i] : 0;
+        int inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int u = __shfl_up_sync(FULL, inc, o); if (lane >= o) inc += u; }
+        if (lane == 31) wsum[wid] = inc;
+        __syncthreads();
+        if (wid == 0) {
+            const int w = wsum[lane];
+            int wi = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int u = __shfl_up_sync(FULL, wi, o); if (lane >= o) wi += u; }
+            wsum[lane] = wi - w;
+            if (lane == 31) wsum[32] = wi;
+        }
+        __syncthreads();
+        if (i < n) data[i] = carry + wsum[wid] + inc - v;
+        __syncthreads();
+        if (tid == 0) carry += wsum[32];
+        __syncthreads();
+    }
+    if (tid == 0) data[n] = carry;
+}
+
+// One fixed-point sweep: map point i ignores keypoints owned by an earlier map point.
+__global__ void __launch_bounds__(128) local_select_kernel(const __grid_constant__ LocalArgs a) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.nmp) return;
+    int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;   // :83-87
+    const int s = a.cand_off[i], e = a.cand_off[i + 1];
+    for (int j = s; j < e; j++) {
+        const uint32_t c = a.cand[j];
+        const int idx = (int)(c & 0xFFFFu), dist = (int)((c >> 16) & 0x1FFu), oct = (int)(c >> 25);
+        if (a.occ0[idx] || a.owner_prev[idx] < i) continue;                             // :95-98
+        if (dist < bestDist) {                                                          // :109-123
+            bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = oct; bestIdx = idx;
+        } else if (dist < bestDist2) {
+            bestLevel2 = oct; bestDist2 = dist;
+        }
+    }
+    int ch = -1;
+    if (bestDist <= TH_HIGH &&                                                          // :127-135
+        !(bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(a.ratio, (float)bestDist2)))
+        ch = bestIdx;
+    a.choice[i] = ch;
+    if (ch >= 0 && a.obs[i] > 0) atomicMin(&a.owner_next[ch], i);
+}
+
+__global__ void __launch_bounds__(256) local_diff_kernel(const __grid_constant__ LocalArgs a) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < a.n && a.owner_prev[i] != a.owner_next[i]) *a.changed = 1;
+}
+
+// results: mp_for_kp[idx] = last map point that took idx, occupied |= owned, nmatches
+__global__ void __launch_bounds__(128)
+local_finalize_kernel(const __grid_constant__ LocalArgs a, int* mp_for_kp, uint8_t* occ_out, int* nmatches) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < a.n && a.owner_prev[i] != INT_MAX) occ_out[i] = 1;
+    if (i < a.nmp && a.choice[i] >= 0) {
+        atomicMax(&mp_for_kp[a.choice[i]], i);
+        atomicAdd(nmatches, 1);
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// K10: Frame::ComputeStereoMatches (src/Frame.cc:512-686).  One warp per left keypoint: the
+// row-band candidate search scans the right keypoints directly (a right keypoint belongs to
+// the band of row (int)vL iff floor(y - r) <= (int)vL <= ceil(y + r), r = 2*scale[octave],
+// which is what the reference's vRowIndices buckets encode, :529-539), keeps the first minimum
+// (ascending iR, strict '<'), then refines by sliding an 11x11 window over 11 shifts with the
+// L1 norm of the centre-subtracted patches (integer-valued, so exact in int32) and fits the
+// parabola in the reference's float op order.  A second single-CTA kernel reproduces the
+// median rule (:671-685) with a rank selection.
+struct StereoArgs {
+    const orbfe_keypoint* kl; const uint8_t* dl; int nl;
+    const orbfe_keypoint* kr; const uint8_t* dr; int nr;
+    const float* scale; const float* inv_scale; int nlevels;
+    // per level: image pointers, pitch, width (left and right pyramids)
+    const uint8_t* imgl[kMaxLevels]; const uint8_t* imgr[kMaxLevels];
+    int pitchl[kMaxLevels], pitchr[kMaxLevels], widthr[kMaxLevels];
+    int nrows;          // rows of level 0 (mvImagePyramid[0].rows)
+    float mbf, mb;
+    float* uright; float* depth;
+    int* sad;           // per left keypoint: truncated best SAD, or -1 when no match
+};
+
+__global__ void __launch_bounds__(128) stereo_match_kernel(const __grid_constant__ StereoArgs a) {
+    const int lane = threadIdx.x & 31;
+    const int iL = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (iL >= a.nl) return;
+    if (lane == 0) { a.uright[iL] = -1.0f; a.depth[iL] = -1.0f; a.sad[iL] = -1; }
+    const orbfe_keypoint kpL = a.kl[iL];
+    const int levelL = kpL.octave;
+    const float vL = kpL.y, uL = kpL.x;
+    const int row = (int)vL;
+    if (row < 0 || row >= a.nrows) return;
+    const float minZ = a.mb, minD = 0.0f, maxD = __fdiv_rn(a.mbf, minZ);                 // :542-545
+    const float minU = __fsub_rn(uL, maxD), maxU = __fsub_rn(uL, minD);
+    uint32_t q[8];
+    load_row(q, a.dl + 32 * (long long)iL);
+    uint32_t best = KEY_INF;
+    int any = 0;
+    for (int iR = lane; iR < a.nr; iR += 32) {
+        const orbfe_keypoint kpR = a.kr[iR];
+        const float r = __fmul_rn(2.0f, a.scale[kpR.octave]);                           // :532
+        const int maxr = (int)ceilf(__fadd_rn(kpR.y, r)), minr = (int)floorf(__fsub_rn(kpR.y, r));
+        if (row < minr || row > maxr) continue;
+        any = 1;
+        if (kpR.octave < levelL - 1 || kpR.octave > levelL + 1) continue;               // :582-583
+        if (!(kpR.x >= minU && kpR.x <= maxU)) continue;                                // :587
+        const int dist = hamming256(q, a.dr + 32 * (long long)iR);
+        best = min(best, ((uint32_t)dist << 20) | (uint32_t)iR);
+    }
+    any = __any_sync(FULL, any);
+    best = warp_min(best);
+    if (!any || maxU < 0) return;                                                       // :565-572
+    const int bestDist = best == KEY_INF ? TH_HIGH : (int)(best >> 20);
+    if (!(bestDist < TH_HIGH)) return;                   // 'dist<bestDist' with bestDist = TH_HIGH (:574,:591)
+    const int thOrbDist = (TH_HIGH + TH_LOW) / 2;                                       // :517
+    if (!(bestDist < thOrbDist)) return;                                                // :598
+    const int bestIdxR = (int)(best & 0xFFFFFu);
+
+    // ---- sub-pixel refinement by correlation (:600-668)
+    const float uR0 = a.kr[bestIdxR].x;
+    const float sf = a.inv_scale[levelL];
+    const float scaleduL = roundf(__fmul_rn(kpL.x, sf)), scaledvL = roundf(__fmul_rn(kpL.y, sf));
+    const float scaleduR0 = roundf(__fmul_rn(uR0, sf));
+    const int w = 5, Lh = 5;
+    const uint8_t* IL = a.imgl[levelL]; const int sl = a.pitchl[levelL];
+    const uint8_t* IR = a.imgr[levelL]; const int sr = a.pitchr[levelL];
+    const int v0 = (int)(scaledvL - w), uL0 = (int)(scaleduL - w);
+    const float iniu = scaleduR0 + Lh - w, endu = scaleduR0 + Lh + w + 1;
+    if (iniu < 0 || endu >= (float)a.widthr[levelL]) return;                            // :621
+    const int cL = IL[(long long)(v0 + w) * sl + uL0 + w];
+    // left patch values of this lane: pixels lane, lane+32, ... of the 121
+    int pl[4], py[4], px[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int i = lane + 32 * k;
+        py[k] = i / 11; px[k] = i - py[k] * 11;
+        pl[k] = i < 121 ? (int)IL[(long long)(v0 + py[k]) * sl + uL0 + px[k]] - cL : 0;
+    }
+    float vDists[11];
+    float sadBestF = (float)INT_MAX;
+    int sadBest = INT_MAX, bestinc = 0;
+#pragma unroll
+    for (int inc = -5; inc <= 5; inc++) {
+        const int uR0i = (int)(scaleduR0 + (float)inc - w);
+        const int cR = IR[(long long)(v0 + w) * sr + uR0i + w];
+        int s = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int i = lane + 32 * k;
+            if (i < 121) s += abs(pl[k] - ((int)IR[(long long)(v0 + py[k]) * sr + uR0i + px[k]] - cR));
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(FULL, s, o);
+        const float dist = (float)s;
+        if (dist < sadBestF) { sadBest = (int)dist; sadBestF = (float)sadBest; bestinc = inc; }   // :630-634 (int bestDist)
+        vDists[inc + 5] = dist;
+    }
+    if (bestinc == -Lh || bestinc == Lh) return;                                        // :640
+    float dist1 = 0, dist2 = 0, dist3 = 0;
+#pragma unroll
+    for (int k = 1; k < 10; k++)
+        if (k == bestinc + 5) { dist1 = vDists[k - 1]; dist2 = vDists[k]; dist3 = vDists[k + 1]; }
+    const float deltaR = __fdiv_rn(__fsub_rn(dist1, dist3),
+                                   __fmul_rn(2.0f, __fsub_rn(__fadd_rn(dist1, dist3), __fmul_rn(2.0f, dist2))));   // :648
+    if (deltaR < -1 || deltaR > 1) return;
+    float bestuR = __fmul_rn(a.scale[levelL], __fadd_rn(__fadd_rn(scaleduR0, (float)bestinc), deltaR));   // :654
+    float disparity = __fsub_rn(uL, bestuR);
+    if (disparity >= minD && disparity < maxD) {                                        // :658-668
+        if (disparity <= 0) { disparity = 0.01f; bestuR = __fsub_rn(uL, 0.01f); }
+        if (lane == 0) {
+            a.depth[iL] = __fdiv_rn(a.mbf, disparity);
+            a.uright[iL] = bestuR;
+            a.sad[iL] = sadBest;
+        }
+    }
+}
+
+// median of the truncated SADs (element size/2 of the sorted list) and the 1.5*1.4*median cut
+__global__ void __launch_bounds__(256) stereo_median_kernel(const __grid_constant__ StereoArgs a) {
+    __shared__ int s_cnt, s_median;
+    const int tid = threadIdx.x;
+    if (tid == 0) { s_cnt = 0; s_median = -1; }
+    __syncthreads();
+    int c = 0;
+    for (int i = tid; i < a.nl; i += 256) c += a.sad[i] >= 0;
+    if (c) atomicAdd(&s_cnt, c);
+    __syncthreads();
+    const int m = s_cnt;
+    if (m == 0) return;
+    const int target = m / 2;                                                           // :672
+    for (int i = tid; i < a.nl; i += 256) {
+        const int v = a.sad[i];
+        if (v < 0) continue;
+        int less = 0, eq = 0;
+        for (int j = 0; j < a.nl; j++) {
+            const int u = a.sad[j];
+            if (u >= 0) { less += u < v; eq += u == v; }
+        }
+        if (less <= target && target < less + eq) s_median = v;
+    }
+    __syncthreads();
+    const float thDist = __fmul_rn(__fmul_rn(1.5f, 1.4f), (float)s_median);             // :673
+    for (int i = tid; i < a.nl; i += 256) {
+        const int v = a.sad[i];
+        if (v >= 0 && !((float)v < thDist)) { a.uright[i] = -1.0f; a.depth[i] = -1.0f; }   // :675-685
+    }
+}
+
+}  // namespace
