@@ -165,6 +165,19 @@ int orbfe_search_init(orbfe_matcher* m, const orbfe_frame_view* f1, const orbfe_
                       float* prev_matched, int32_t* matches12, int window, float nnratio,
                       int check_orientation, int* nmatches);
 
+/* Batched, device-resident SearchForInitialization over a stream of frames laid out as the
+ * extractor's device results ([nframes][cap] keypoints / descriptors, counts[nframes]): pair p
+ * matches frame p (F1) against frame p+1 (F2) with vbPrevMatched = F1's keypoint positions (the
+ * state right after Tracking::MonocularInitialization stores the initial frame,
+ * src/Tracking.cc:609-616).  d_matches12 [nframes-1][cap], d_nmatches [nframes-1].
+ * Asynchronous on the matcher's stream. */
+int orbfe_search_init_consecutive_device(orbfe_matcher* m, const orbfe_keypoint* d_kps,
+                                         const uint8_t* d_desc, const int32_t* d_counts, int cap,
+                                         int nframes, float min_x, float max_x, float min_y,
+                                         float max_y, int window, float nnratio,
+                                         int check_orientation, int32_t* d_matches12,
+                                         int32_t* d_nmatches);
+
 /* Map-point side of SearchByProjection(Frame&, vector<MapPoint*>&, th) (HOST pointers). */
 typedef struct {
     int32_t n;

@@ -85,13 +85,11 @@ SIGNATURES = {
     "orbfe_knn2": (_i, [_vp, _vp, _i, _vp, _i, _i, _f, _vp, _vp, _vp]),
     "orbfe_knn2_device": (_i, [_vp, _vp, _i, _vp, _i, _i, _f, _vp, _vp, _vp]),
     "orbfe_search_init": (_i, [_vp, C.POINTER(FrameView), C.POINTER(FrameView), _vp, _vp, _i, _f, _i, _ip]),
+    "orbfe_search_init_consecutive_device": (_i, [_vp, _vp, _vp, _vp, _i, _i, _f, _f, _f, _f, _i, _f, _i, _vp, _vp]),
     "orbfe_search_local_points": (_i, [_vp, C.POINTER(FrameView), C.POINTER(MapPointsView), _f, _f, _vp, _vp, _ip]),
     "orbfe_stereo_match": (_i, [_vp, C.POINTER(FrameView), C.POINTER(FrameView), C.POINTER(PyramidView),
                                 C.POINTER(PyramidView), _vp, _f, _f, _vp, _vp]),
 }
-
-
-_NOT_YET = {"orbfe_search_init", "orbfe_search_local_points", "orbfe_stereo_match"}
 
 
 def lib() -> C.CDLL:
@@ -103,8 +101,6 @@ def lib() -> C.CDLL:
                              "(make -C orb_slam2_annotate_b200/csrc); there is no CPU fallback")
         L = C.CDLL(LIB_PATH)
         for name, (res, args) in SIGNATURES.items():
-            if name in _NOT_YET:
-                continue
             fn = getattr(L, name)   # AttributeError here means the .so is stale
             fn.restype = res
             fn.argtypes = args

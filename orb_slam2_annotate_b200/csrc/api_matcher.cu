@@ -3,6 +3,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <vector>
 
 #include "api_common.cuh"
 #include "match_internal.cuh"
@@ -99,3 +100,263 @@ int orbfe_knn2(orbfe_matcher* m, const uint8_t* query, int nq, const uint8_t* tr
 }
 
 }  // extern "C"
+
+namespace {
+
+// bump allocator over one grow-only device buffer (256-byte aligned pieces)
+struct Arena {
+    uint8_t* base = nullptr;
+    size_t off = 0, cap = 0;
+    template <class T> T* take(size_t n) {
+        off = (off + 255) & ~size_t(255);
+        T* p = reinterpret_cast<T*>(base + off);
+        off += n * sizeof(T);
+        return p;
+    }
+};
+inline size_t padded(size_t bytes) { return ((bytes + 255) & ~size_t(255)) + 256; }
+
+int check_frame(const orbfe_frame_view* f) {
+    if (!f || f->n < 0 || (f->n && (!f->kps || !f->desc))) return fail(ORBFE_ERR_ARG, "bad frame view");
+    if (f->n > 65000) return fail(ORBFE_ERR_ARG, "more than 65000 keypoints in a frame view");
+    if (!(f->max_x > f->min_x) || !(f->max_y > f->min_y)) return fail(ORBFE_ERR_ARG, "empty image bounds in frame view");
+    return 0;
+}
+
+GridGeom grid_of(const orbfe_frame_view* f) {
+    // mfGridElementWidthInv / HeightInv (src/Frame.cc:86-87)
+    GridGeom g;
+    g.minX = f->min_x; g.minY = f->min_y;
+    g.invW = 64.0f / (f->max_x - f->min_x);
+    g.invH = 48.0f / (f->max_y - f->min_y);
+    return g;
+}
+
+}  // namespace
+
+extern "C" {
+
+int orbfe_search_init(orbfe_matcher* m, const orbfe_frame_view* f1, const orbfe_frame_view* f2,
+                      float* prev_matched, int32_t* matches12, int window, float nnratio,
+                      int check_orientation, int* nmatches) {
+    if (!m || !nmatches) return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_search_init");
+    int rc;
+    if ((rc = check_frame(f1)) || (rc = check_frame(f2))) return rc;
+    *nmatches = 0;
+    const int n1 = f1->n, n2 = f2->n;
+    if (n1 == 0) return ORBFE_OK;
+    if (!prev_matched || !matches12) return fail(ORBFE_ERR_ARG, "prev_matched / matches12 is NULL");
+    CU(cudaSetDevice(m->device));
+    const int cap = std::max(std::max(n1, n2), 1);
+    const size_t total = padded((size_t)2 * cap * sizeof(orbfe_keypoint)) + padded((size_t)2 * cap * 32) +
+                         padded(8) + padded((size_t)cap * 8) + padded((size_t)cap * 4) + padded(4);
+    if ((rc = m->scratch[0].ensure(total))) return rc;
+    Arena A; A.base = m->scratch[0].p;
+    orbfe_keypoint* d_kps = A.take<orbfe_keypoint>((size_t)2 * cap);
+    uint8_t* d_desc = A.take<uint8_t>((size_t)2 * cap * 32);
+    int* d_counts = A.take<int>(2);
+    float* d_prev = A.take<float>((size_t)cap * 2);
+    int* d_m12 = A.take<int>(cap);
+    int* d_nm = A.take<int>(1);
+    if (A.off > total) return fail(ORBFE_ERR_CAPACITY, "internal: matcher arena overflow");
+    cudaStream_t s = m->stream;
+    const int counts[2] = {n1, n2};
+    CU(cudaMemcpyAsync(d_kps, f1->kps, sizeof(orbfe_keypoint) * n1, cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(d_desc, f1->desc, (size_t)32 * n1, cudaMemcpyHostToDevice, s));
+    if (n2) {
+        CU(cudaMemcpyAsync(d_kps + cap, f2->kps, sizeof(orbfe_keypoint) * n2, cudaMemcpyHostToDevice, s));
+        CU(cudaMemcpyAsync(d_desc + (size_t)cap * 32, f2->desc, (size_t)32 * n2, cudaMemcpyHostToDevice, s));
+    }
+    CU(cudaMemcpyAsync(d_counts, counts, sizeof(counts), cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(d_prev, prev_matched, sizeof(float) * 2 * n1, cudaMemcpyHostToDevice, s));
+    InitArgs a{};
+    a.kps = d_kps; a.desc = d_desc; a.counts = d_counts; a.cap = cap; a.pairs = nullptr;
+    a.prev = d_prev; a.m12 = d_m12; a.nmatches = d_nm;
+    a.grid = grid_of(f2);
+    a.window = window; a.ratio = nnratio; a.checkOri = check_orientation;
+    launch_search_init(a, 1, s);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(prev_matched, d_prev, sizeof(float) * 2 * n1, cudaMemcpyDeviceToHost, s));
+    CU(cudaMemcpyAsync(matches12, d_m12, sizeof(int) * n1, cudaMemcpyDeviceToHost, s));
+    CU(cudaMemcpyAsync(nmatches, d_nm, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    return ORBFE_OK;
+}
+
+int orbfe_search_init_consecutive_device(orbfe_matcher* m, const orbfe_keypoint* d_kps,
+                                         const uint8_t* d_desc, const int32_t* d_counts, int cap,
+                                         int nframes, float min_x, float max_x, float min_y, float max_y,
+                                         int window, float nnratio, int check_orientation,
+                                         int32_t* d_matches12, int32_t* d_nmatches) {
+    if (!m || !d_kps || !d_desc || !d_counts || !d_matches12 || !d_nmatches || cap < 1 || cap > 65000 ||
+        !(max_x > min_x) || !(max_y > min_y))
+        return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_search_init_consecutive_device");
+    if (nframes < 2) return ORBFE_OK;
+    CU(cudaSetDevice(m->device));
+    InitArgs a{};
+    a.kps = d_kps; a.desc = d_desc; a.counts = d_counts; a.cap = cap; a.pairs = nullptr;
+    a.prev = nullptr; a.m12 = d_matches12; a.nmatches = d_nmatches;
+    a.grid.minX = min_x; a.grid.minY = min_y;
+    a.grid.invW = 64.0f / (max_x - min_x); a.grid.invH = 48.0f / (max_y - min_y);
+    a.window = window; a.ratio = nnratio; a.checkOri = check_orientation;
+    launch_search_init(a, nframes - 1, m->stream);
+    CU(cudaGetLastError());
+    return ORBFE_OK;
+}
+
+int orbfe_search_local_points(orbfe_matcher* m, const orbfe_frame_view* f, const orbfe_mappoints_view* mps,
+                              float th, float nnratio, uint8_t* kp_occupied, int32_t* mp_for_kp,
+                              int* nmatches) {
+    if (!m || !mps || !nmatches) return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_search_local_points");
+    int rc;
+    if ((rc = check_frame(f))) return rc;
+    *nmatches = 0;
+    const int n = f->n, nmp = mps->n;
+    if (n == 0 || nmp <= 0) return ORBFE_OK;
+    if (!kp_occupied || !mp_for_kp || !f->scale_factors || !mps->track_in_view || !mps->proj_x || !mps->proj_y ||
+        !mps->level || !mps->view_cos || !mps->desc || !mps->observations || (f->uright && !mps->proj_xr))
+        return fail(ORBFE_ERR_ARG, "NULL array in frame / map point view");
+    CU(cudaSetDevice(m->device));
+    cudaStream_t s = m->stream;
+    const size_t total = padded((size_t)n * sizeof(orbfe_keypoint)) + padded((size_t)n * 32) + padded((size_t)n * 4) +
+                         padded((size_t)f->nlevels * 4) + padded(nmp) + 7 * padded((size_t)nmp * 4) +
+                         padded((size_t)nmp * 32) + padded(3072 * 4) + padded((size_t)n * 2) +
+                         padded((size_t)(nmp + 1) * 4) + padded(n) + 3 * padded((size_t)n * 4) +
+                         padded(8) + padded(n);
+    if ((rc = m->scratch[0].ensure(total))) return rc;
+    Arena A; A.base = m->scratch[0].p; A.cap = total;
+    LocalArgs a{};
+    auto up = [&](auto* dst, const void* src, size_t bytes) {
+        return cudaMemcpyAsync((void*)dst, src, bytes, cudaMemcpyHostToDevice, s);
+    };
+    orbfe_keypoint* d_kps = A.take<orbfe_keypoint>(n); CU(up(d_kps, f->kps, sizeof(orbfe_keypoint) * n));
+    uint8_t* d_desc = A.take<uint8_t>((size_t)n * 32); CU(up(d_desc, f->desc, (size_t)n * 32));
+    float* d_ur = A.take<float>(n);
+    if (f->uright) CU(up(d_ur, f->uright, sizeof(float) * n));
+    float* d_scale = A.take<float>(f->nlevels); CU(up(d_scale, f->scale_factors, sizeof(float) * f->nlevels));
+    uint8_t* d_inview = A.take<uint8_t>(nmp); CU(up(d_inview, mps->track_in_view, nmp));
+    float* d_px = A.take<float>(nmp); CU(up(d_px, mps->proj_x, sizeof(float) * nmp));
+    float* d_py = A.take<float>(nmp); CU(up(d_py, mps->proj_y, sizeof(float) * nmp));
+    float* d_pxr = A.take<float>(nmp);
+    if (mps->proj_xr) CU(up(d_pxr, mps->proj_xr, sizeof(float) * nmp));
+    int* d_level = A.take<int>(nmp); CU(up(d_level, mps->level, sizeof(int) * nmp));
+    float* d_cos = A.take<float>(nmp); CU(up(d_cos, mps->view_cos, sizeof(float) * nmp));
+    uint8_t* d_mpdesc = A.take<uint8_t>((size_t)nmp * 32); CU(up(d_mpdesc, mps->desc, (size_t)nmp * 32));
+    int* d_obs = A.take<int>(nmp); CU(up(d_obs, mps->observations, sizeof(int) * nmp));
+    a.cell_end = A.take<int>(3072);
+    a.items = A.take<unsigned short>(n);
+    a.cand_off = A.take<int>(nmp + 1);
+    uint8_t* d_occ = A.take<uint8_t>(n); CU(up(d_occ, kp_occupied, n));
+    int* d_owner[2] = {A.take<int>(n), A.take<int>(n)};
+    int* d_mpkp = A.take<int>(n);
+    a.choice = A.take<int>(nmp);
+    int* d_flags = A.take<int>(2);           // [0] changed, [1] nmatches
+    uint8_t* d_occ_out = A.take<uint8_t>(n);
+    if (A.off > A.cap) return fail(ORBFE_ERR_CAPACITY, "internal: matcher arena overflow");
+    a.kps = d_kps; a.desc = d_desc; a.uright = f->uright ? d_ur : nullptr; a.n = n;
+    a.scale = d_scale; a.nlevels = f->nlevels; a.nmp = nmp; a.in_view = d_inview;
+    a.px = d_px; a.py = d_py; a.pxr = d_pxr; a.level = d_level; a.view_cos = d_cos; a.mpdesc = d_mpdesc;
+    a.obs = d_obs; a.th = th; a.ratio = nnratio; a.grid = grid_of(f); a.occ0 = d_occ; a.changed = d_flags;
+    // levels must index mvScaleFactors
+    for (int i = 0; i < nmp; i++)
+        if (mps->track_in_view[i] && (mps->level[i] < 0 || mps->level[i] >= f->nlevels))
+            return fail(ORBFE_ERR_ARG, "map point scale level outside the frame's pyramid");
+    launch_local_grid_and_count(a, s);
+    int ncand = 0;
+    CU(cudaMemcpyAsync(&ncand, a.cand_off + nmp, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    if ((rc = m->scratch[1].ensure((size_t)std::max(ncand, 1) * 4))) return rc;
+    a.cand = reinterpret_cast<uint32_t*>(m->scratch[1].p);
+    launch_local_fill(a, s);
+    // fixed-point sweeps over the first-owner array (0x7F7F7F7F = no owner)
+    CU(cudaMemsetAsync(d_owner[0], 0x7F, sizeof(int) * n, s));
+    int cur = 0;
+    for (int it = 0; it < nmp + 2; it++) {
+        a.owner_prev = d_owner[cur]; a.owner_next = d_owner[cur ^ 1];
+        CU(cudaMemsetAsync(a.owner_next, 0x7F, sizeof(int) * n, s));
+        CU(cudaMemsetAsync(d_flags, 0, sizeof(int), s));
+        launch_local_sweep(a, s);
+        int changed = 0;
+        CU(cudaMemcpyAsync(&changed, d_flags, sizeof(int), cudaMemcpyDeviceToHost, s));
+        CU(cudaStreamSynchronize(s));
+        cur ^= 1;
+        if (!changed) break;
+    }
+    // a.choice is consistent with d_owner[cur] (== the previous one at the fixed point)
+    a.owner_prev = d_owner[cur];
+    CU(cudaMemsetAsync(d_mpkp, 0xFF, sizeof(int) * n, s));
+    CU(cudaMemsetAsync(d_flags + 1, 0, sizeof(int), s));
+    CU(cudaMemcpyAsync(d_occ_out, d_occ, n, cudaMemcpyDeviceToDevice, s));
+    launch_local_finalize(a, d_mpkp, d_occ_out, d_flags + 1, s);
+    CU(cudaGetLastError());
+    std::vector<int> h_mpkp(n);
+    CU(cudaMemcpyAsync(h_mpkp.data(), d_mpkp, sizeof(int) * n, cudaMemcpyDeviceToHost, s));
+    CU(cudaMemcpyAsync(kp_occupied, d_occ_out, n, cudaMemcpyDeviceToHost, s));
+    CU(cudaMemcpyAsync(nmatches, d_flags + 1, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    for (int i = 0; i < n; i++)
+        if (h_mpkp[i] >= 0) mp_for_kp[i] = h_mpkp[i];   // F.mvpMapPoints[bestIdx] = pMP (:132); others untouched
+    return ORBFE_OK;
+}
+
+}  // extern "C"
+
+extern "C" int orbfe_stereo_match(orbfe_matcher* m, const orbfe_frame_view* left, const orbfe_frame_view* right,
+                                  const orbfe_pyramid_view* pl, const orbfe_pyramid_view* pr,
+                                  const float* inv_scale_factors, float mbf, float mb, float* uright,
+                                  float* depth) {
+    if (!m || !pl || !pr || !inv_scale_factors || !(mb > 0))
+        return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_stereo_match");
+    int rc;
+    if ((rc = check_frame(left)) || (rc = check_frame(right))) return rc;
+    const int nl = left->n, nr = right->n, L = left->nlevels;
+    if (nl == 0) return ORBFE_OK;
+    if (!uright || !depth || !left->scale_factors || L < 1 || L > kMaxLevels || pl->nlevels < L || pr->nlevels < L)
+        return fail(ORBFE_ERR_ARG, "bad pyramid / output arguments to orbfe_stereo_match");
+    for (int i = 0; i < nl; i++)
+        if (left->kps[i].octave < 0 || left->kps[i].octave >= L) return fail(ORBFE_ERR_ARG, "left keypoint octave outside the pyramid");
+    for (int i = 0; i < nr; i++)
+        if (right->kps[i].octave < 0 || right->kps[i].octave >= L) return fail(ORBFE_ERR_ARG, "right keypoint octave outside the pyramid");
+    CU(cudaSetDevice(m->device));
+    cudaStream_t s = m->stream;
+    size_t total = padded((size_t)nl * sizeof(orbfe_keypoint)) + padded((size_t)nl * 32) +
+                   padded((size_t)std::max(nr, 1) * sizeof(orbfe_keypoint)) + padded((size_t)std::max(nr, 1) * 32) +
+                   2 * padded((size_t)L * 4) + 3 * padded((size_t)nl * 4);
+    for (int l = 0; l < L; l++)
+        total += padded((size_t)pl->width[l] * pl->height[l]) + padded((size_t)pr->width[l] * pr->height[l]);
+    if ((rc = m->scratch[0].ensure(total))) return rc;
+    Arena A; A.base = m->scratch[0].p;
+    StereoArgs a{};
+    orbfe_keypoint* d_kl = A.take<orbfe_keypoint>(nl);
+    uint8_t* d_dl = A.take<uint8_t>((size_t)nl * 32);
+    orbfe_keypoint* d_kr = A.take<orbfe_keypoint>(std::max(nr, 1));
+    uint8_t* d_dr = A.take<uint8_t>((size_t)std::max(nr, 1) * 32);
+    float* d_scale = A.take<float>(L);
+    float* d_inv = A.take<float>(L);
+    a.uright = A.take<float>(nl); a.depth = A.take<float>(nl); a.sad = A.take<int>(nl);
+    CU(cudaMemcpyAsync(d_kl, left->kps, sizeof(orbfe_keypoint) * nl, cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(d_dl, left->desc, (size_t)nl * 32, cudaMemcpyHostToDevice, s));
+    if (nr) {
+        CU(cudaMemcpyAsync(d_kr, right->kps, sizeof(orbfe_keypoint) * nr, cudaMemcpyHostToDevice, s));
+        CU(cudaMemcpyAsync(d_dr, right->desc, (size_t)nr * 32, cudaMemcpyHostToDevice, s));
+    }
+    CU(cudaMemcpyAsync(d_scale, left->scale_factors, sizeof(float) * L, cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(d_inv, inv_scale_factors, sizeof(float) * L, cudaMemcpyHostToDevice, s));
+    for (int l = 0; l < L; l++) {
+        uint8_t* dl = A.take<uint8_t>((size_t)pl->width[l] * pl->height[l]);
+        uint8_t* dr = A.take<uint8_t>((size_t)pr->width[l] * pr->height[l]);
+        CU(cudaMemcpy2DAsync(dl, pl->width[l], pl->data[l], pl->stride[l], pl->width[l], pl->height[l], cudaMemcpyHostToDevice, s));
+        CU(cudaMemcpy2DAsync(dr, pr->width[l], pr->data[l], pr->stride[l], pr->width[l], pr->height[l], cudaMemcpyHostToDevice, s));
+        a.imgl[l] = dl; a.imgr[l] = dr; a.pitchl[l] = pl->width[l]; a.pitchr[l] = pr->width[l];
+        a.widthr[l] = pr->width[l];
+    }
+    if (A.off > total) return fail(ORBFE_ERR_CAPACITY, "internal: matcher arena overflow");
+    a.kl = d_kl; a.dl = d_dl; a.nl = nl; a.kr = d_kr; a.dr = d_dr; a.nr = nr;
+    a.scale = d_scale; a.inv_scale = d_inv; a.nlevels = L; a.nrows = pl->height[0]; a.mbf = mbf; a.mb = mb;
+    launch_stereo(a, s);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(uright, a.uright, sizeof(float) * nl, cudaMemcpyDeviceToHost, s));
+    CU(cudaMemcpyAsync(depth, a.depth, sizeof(float) * nl, cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    return ORBFE_OK;
+}

@@ -3,10 +3,75 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "orbfe_internal.cuh"
+
 namespace orbfe {
 
 // brute-force kNN-2; device pointers, rows 32 bytes, 16-byte aligned. returns launches.
 int launch_knn2(const uint8_t* d_query, int nq, const uint8_t* d_train, int nt, int th, float ratio,
                 int* d_idx, int* d_d1, int* d_d2, cudaStream_t s);
+
+struct GridGeom { float minX, minY, invW, invH; };
+
+struct InitArgs {
+    const orbfe_keypoint* kps;   // [frames][cap]
+    const uint8_t* desc;         // [frames][cap][32]
+    const int* counts;           // [frames]
+    int cap;
+    const int2* pairs;           // frame indices (F1, F2) per pair, or NULL for (p, p+1)
+    float* prev;                 // [pairs][cap][2] vbPrevMatched in/out, or NULL: F1 keypoint positions
+    int* m12;                    // [pairs][cap] vnMatches12
+    int* nmatches;               // [pairs]
+    GridGeom grid;
+    int window;
+    float ratio;
+    int checkOri;
+};
+
+struct LocalArgs {
+    const orbfe_keypoint* kps;   // frame keypoints [n]
+    const uint8_t* desc;         // [n][32]
+    const float* uright;         // [n] or NULL
+    int n;
+    const float* scale;          // mvScaleFactors
+    int nlevels;
+    // map points
+    int nmp;
+    const uint8_t* in_view;
+    const float* px; const float* py; const float* pxr;
+    const int* level; const float* view_cos;
+    const uint8_t* mpdesc;
+    const int* obs;
+    float th, ratio;
+    GridGeom grid;
+    // grid CSR of the frame
+    int* cell_end; unsigned short* items;
+    // candidate lists: cand_off[nmp+1] (exclusive scan of counts), cand[] packed idx | dist<<16 | octave<<25
+    int* cand_off; uint32_t* cand;
+    // fixed-point state
+    const uint8_t* occ0;         // keypoint already holds a map point with observations
+    int* owner_prev; int* owner_next; int* choice; int* changed;
+};
+
+struct StereoArgs {
+    const orbfe_keypoint* kl; const uint8_t* dl; int nl;
+    const orbfe_keypoint* kr; const uint8_t* dr; int nr;
+    const float* scale; const float* inv_scale; int nlevels;
+    // per level: image pointers, pitch, width (left and right pyramids)
+    const uint8_t* imgl[kMaxLevels]; const uint8_t* imgr[kMaxLevels];
+    int pitchl[kMaxLevels], pitchr[kMaxLevels], widthr[kMaxLevels];
+    int nrows;          // rows of level 0 (mvImagePyramid[0].rows)
+    float mbf, mb;
+    float* uright; float* depth;
+    int* sad;           // per left keypoint: truncated best SAD, or -1 when no match
+};
+
+size_t search_init_smem(int cap);
+int launch_search_init(const InitArgs& a, int npairs, cudaStream_t st);
+int launch_local_grid_and_count(const LocalArgs& a, cudaStream_t st);
+int launch_local_fill(const LocalArgs& a, cudaStream_t st);
+int launch_local_sweep(const LocalArgs& a, cudaStream_t st);
+int launch_local_finalize(const LocalArgs& a, int* mp_for_kp, uint8_t* occ_out, int* nmatches, cudaStream_t st);
+int launch_stereo(const StereoArgs& a, cudaStream_t st);
 
 }  // namespace orbfe

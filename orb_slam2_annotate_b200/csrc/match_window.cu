@@ -15,8 +15,8 @@
 //     fixed point is the sequential result.
 #include <climits>
 
-#include "match_internal.cuh"
 #include "orbfe_internal.cuh"
+#include "match_internal.cuh"
 
 namespace orbfe {
 
@@ -39,7 +39,6 @@ __device__ __forceinline__ void load_row(uint32_t a[8], const uint8_t* __restric
     a[0] = x.x; a[1] = x.y; a[2] = x.z; a[3] = x.w; a[4] = y.x; a[5] = y.y; a[6] = y.z; a[7] = y.w;
 }
 
-struct GridGeom { float minX, minY, invW, invH; };
 
 // PosInGrid (Frame.cc:419-430): cell = ix*48+iy or -1
 __device__ __forceinline__ int pos_in_grid(const GridGeom& g, float x, float y) {
@@ -124,20 +123,6 @@ __device__ void three_maxima(const int* hist, int& ind1, int& ind2, int& ind3) {
 
 // ---------------------------------------------------------------------------------------
 // SearchForInitialization — one warp per frame pair.
-struct InitArgs {
-    const orbfe_keypoint* kps;   // [frames][cap]
-    const uint8_t* desc;         // [frames][cap][32]
-    const int* counts;           // [frames]
-    int cap;
-    const int2* pairs;           // frame indices (F1, F2) per pair, or NULL for (p, p+1)
-    float* prev;                 // [pairs][cap][2] vbPrevMatched in/out, or NULL: F1 keypoint positions
-    int* m12;                    // [pairs][cap] vnMatches12
-    int* nmatches;               // [pairs]
-    GridGeom grid;
-    int window;
-    float ratio;
-    int checkOri;
-};
 
 __global__ void __launch_bounds__(32)
 search_init_kernel(const __grid_constant__ InitArgs a) {
@@ -241,34 +226,9 @@ search_init_kernel(const __grid_constant__ InitArgs a) {
     if (lane == 0) a.nmatches[p] = nm;
 }
 
-size_t search_init_smem(int cap) { return (size_t)(NCELL + 32) * 4 + (size_t)cap * 6 + 16; }
 
 // ---------------------------------------------------------------------------------------
 // SearchByProjection(Frame&, vector<MapPoint*>&, th)
-struct LocalArgs {
-    const orbfe_keypoint* kps;   // frame keypoints [n]
-    const uint8_t* desc;         // [n][32]
-    const float* uright;         // [n] or NULL
-    int n;
-    const float* scale;          // mvScaleFactors
-    int nlevels;
-    // map points
-    int nmp;
-    const uint8_t* in_view;
-    const float* px; const float* py; const float* pxr;
-    const int* level; const float* view_cos;
-    const uint8_t* mpdesc;
-    const int* obs;
-    float th, ratio;
-    GridGeom grid;
-    // grid CSR of the frame
-    int* cell_end; unsigned short* items;
-    // candidate lists: cand_off[nmp+1] (exclusive scan of counts), cand[] packed idx | dist<<16 | octave<<25
-    int* cand_off; uint32_t* cand;
-    // fixed-point state
-    const uint8_t* occ0;         // keypoint already holds a map point with observations
-    int* owner_prev; int* owner_next; int* choice; int* changed;
-};
 
 __global__ void __launch_bounds__(32) build_grid_kernel(const __grid_constant__ LocalArgs a) {
     warp_build_grid(a.grid, a.kps, a.n, a.cell_end, a.items);
@@ -386,7 +346,7 @@ __global__ void __launch_bounds__(256) local_diff_kernel(const __grid_constant__
 __global__ void __launch_bounds__(128)
 local_finalize_kernel(const __grid_constant__ LocalArgs a, int* mp_for_kp, uint8_t* occ_out, int* nmatches) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < a.n && a.owner_prev[i] != INT_MAX) occ_out[i] = 1;
+    if (i < a.n && a.owner_prev[i] != 0x7F7F7F7F) occ_out[i] = 1;   // 0x7F7F7F7F = no owner
     if (i < a.nmp && a.choice[i] >= 0) {
         atomicMax(&mp_for_kp[a.choice[i]], i);
         atomicAdd(nmatches, 1);
@@ -402,18 +362,6 @@ local_finalize_kernel(const __grid_constant__ LocalArgs a, int* mp_for_kp, uint8
 // L1 norm of the centre-subtracted patches (integer-valued, so exact in int32) and fits the
 // parabola in the reference's float op order.  A second single-CTA kernel reproduces the
 // median rule (:671-685) with a rank selection.
-struct StereoArgs {
-    const orbfe_keypoint* kl; const uint8_t* dl; int nl;
-    const orbfe_keypoint* kr; const uint8_t* dr; int nr;
-    const float* scale; const float* inv_scale; int nlevels;
-    // per level: image pointers, pitch, width (left and right pyramids)
-    const uint8_t* imgl[kMaxLevels]; const uint8_t* imgr[kMaxLevels];
-    int pitchl[kMaxLevels], pitchr[kMaxLevels], widthr[kMaxLevels];
-    int nrows;          // rows of level 0 (mvImagePyramid[0].rows)
-    float mbf, mb;
-    float* uright; float* depth;
-    int* sad;           // per left keypoint: truncated best SAD, or -1 when no match
-};
 
 __global__ void __launch_bounds__(128) stereo_match_kernel(const __grid_constant__ StereoArgs a) {
     const int lane = threadIdx.x & 31;
@@ -542,3 +490,47 @@ __global__ void __launch_bounds__(256) stereo_median_kernel(const __grid_constan
 }
 
 }  // namespace
+
+size_t search_init_smem(int cap) { return (size_t)(NCELL + 32) * 4 + (size_t)cap * 6 + 16; }
+
+int launch_search_init(const InitArgs& a, int npairs, cudaStream_t st) {
+    if (npairs <= 0) return 0;
+    const size_t smem = search_init_smem(a.cap);
+    if (smem > 48 * 1024)
+        cudaFuncSetAttribute(search_init_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    search_init_kernel<<<npairs, 32, smem, st>>>(a);
+    return 1;
+}
+
+int launch_local_grid_and_count(const LocalArgs& a, cudaStream_t st) {
+    build_grid_kernel<<<1, 32, 0, st>>>(a);
+    if (a.nmp > 0) local_candidates_kernel<false><<<(a.nmp + 127) / 128, 128, 0, st>>>(a);
+    scan_kernel<<<1, 1024, 0, st>>>(a.cand_off, a.nmp);
+    return 3;
+}
+
+int launch_local_fill(const LocalArgs& a, cudaStream_t st) {
+    if (a.nmp > 0) local_candidates_kernel<true><<<(a.nmp + 127) / 128, 128, 0, st>>>(a);
+    return 1;
+}
+
+int launch_local_sweep(const LocalArgs& a, cudaStream_t st) {
+    if (a.nmp > 0) local_select_kernel<<<(a.nmp + 127) / 128, 128, 0, st>>>(a);
+    if (a.n > 0) local_diff_kernel<<<(a.n + 255) / 256, 256, 0, st>>>(a);
+    return 2;
+}
+
+int launch_local_finalize(const LocalArgs& a, int* mp_for_kp, uint8_t* occ_out, int* nmatches, cudaStream_t st) {
+    const int m = a.n > a.nmp ? a.n : a.nmp;
+    if (m > 0) local_finalize_kernel<<<(m + 127) / 128, 128, 0, st>>>(a, mp_for_kp, occ_out, nmatches);
+    return 1;
+}
+
+int launch_stereo(const StereoArgs& a, cudaStream_t st) {
+    if (a.nl <= 0) return 0;
+    stereo_match_kernel<<<(a.nl + 3) / 4, 128, 0, st>>>(a);
+    stereo_median_kernel<<<1, 256, 0, st>>>(a);
+    return 2;
+}
+
+}  // namespace orbfe

@@ -106,6 +106,15 @@ class ORBmatcher:
                                         int(self.mbCheckOrientation), C.byref(n)), "orbfe_search_init")
         return n.value, m12[:F1.N]
 
+    def search_init_consecutive_device(self, kps_ptr: int, desc_ptr: int, counts_ptr: int, cap: int, nframes: int,
+                                       width: float, height: float, m12_ptr: int, nm_ptr: int,
+                                       windowSize: int = 100) -> None:
+        """Batched SearchForInitialization over consecutive frames held in HBM (asynchronous)."""
+        check(self._L.orbfe_search_init_consecutive_device(self._h, kps_ptr, desc_ptr, counts_ptr, cap, nframes,
+                                                           0.0, float(width), 0.0, float(height), windowSize,
+                                                           self.mfNNratio, int(self.mbCheckOrientation),
+                                                           m12_ptr, nm_ptr), "orbfe_search_init_consecutive_device")
+
     def SearchByProjection(self, F: Frame, mappoints: dict, th: float = 3.0, occupied: np.ndarray | None = None):
         """SearchByProjection(Frame&, vector<MapPoint*>&, th) — src/ORBmatcher.cc:51-138.
         mappoints: dict of arrays track_in_view u8, proj_x/proj_y/proj_xr f32, level i32,

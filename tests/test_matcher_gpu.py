@@ -1,0 +1,106 @@
+"""GPU parity of the guided searches (C ABI) against the CPU oracle: SearchForInitialization,
+SearchByProjection(Frame, MapPoints) and ComputeStereoMatches.  Match indices, counts and the
+float outputs (updated vbPrevMatched, mvuRight, mvDepth) must be bit-exact."""
+import numpy as np
+import pytest
+
+from orb_slam2_annotate_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+_cache = {}
+
+
+def _frames(oracle, kind, seed, nf):
+    key = (kind, seed, nf)
+    if key not in _cache:
+        if kind == "mono":
+            imgs, _ = synth.sequence(3, 640, 480, seed=seed)
+        else:
+            imgs = np.stack(synth.stereo_pair(1241, 376, seed=seed, disparity=20))
+        out = []
+        for im in imgs:
+            oc = oracle.OracleExtractor(nf)
+            k, d = oc(im)
+            out.append((k, d, [oc.level(l) for l in range(8)], oc.tables()))
+        _cache[key] = out
+    return _cache[key]
+
+
+@pytest.mark.parametrize("seed,ratio,ori,window", [(0, 0.9, True, 100), (1, 0.9, False, 100), (2, 0.7, True, 40), (3, 0.9, True, 300)])
+def test_search_for_initialization(orbfe, oracle, seed, ratio, ori, window):
+    fr = _frames(oracle, "mono", seed, 2000)
+    (k1, d1, _, t), (k2, d2, _, _), (k3, d3, _, _) = fr
+    F1 = orbfe.Frame(k1, d1, 640, 480, t["scale"]); F2 = orbfe.Frame(k2, d2, 640, 480, t["scale"])
+    F3 = orbfe.Frame(k3, d3, 640, 480, t["scale"])
+    mt = orbfe.ORBmatcher(ratio, ori)
+    prev_g = np.ascontiguousarray(np.stack([k1["x"], k1["y"]], 1), np.float32)
+    prev_o = prev_g.copy()
+    for Fg, (ko, do) in ((F2, (k2, d2)), (F3, (k3, d3))):     # second call reuses the updated vbPrevMatched
+        ng, mg = mt.SearchForInitialization(F1, Fg, prev_g, window)
+        o1 = oracle.frame_view(k1, d1, 640, 480, t["scale"]); o2 = oracle.frame_view(ko, do, 640, 480, t["scale"])
+        no, mo = oracle.search_for_initialization(o1, o2, prev_o, window, ratio, ori)
+        assert ng == no and np.array_equal(mg, mo) and prev_g.tobytes() == prev_o.tobytes()
+    assert ng > 50
+
+
+def test_search_init_degenerate(orbfe, oracle):
+    fr = _frames(oracle, "mono", 0, 2000)
+    (k1, d1, _, t), (k2, d2, _, _), _ = fr
+    mt = orbfe.ORBmatcher(0.9, True)
+    empty = orbfe.Frame(k1[:0], d1[:0], 640, 480, t["scale"])
+    F1 = orbfe.Frame(k1, d1, 640, 480, t["scale"])
+    prev = np.ascontiguousarray(np.stack([k1["x"], k1["y"]], 1), np.float32)
+    n, m = mt.SearchForInitialization(F1, empty, prev, 100)
+    assert n == 0 and (m == -1).all()
+    n, m = mt.SearchForInitialization(empty, F1, np.zeros((0, 2), np.float32), 100)
+    assert n == 0 and len(m) == 0
+    # identical frames: every octave-0 keypoint matches itself at distance 0
+    n, m = mt.SearchForInitialization(F1, F1, prev.copy(), 100)
+    o1 = oracle.frame_view(k1, d1, 640, 480, t["scale"])
+    no, mo = oracle.search_for_initialization(o1, o1, prev.copy(), 100, 0.9, True)
+    assert n == no and np.array_equal(m, mo)
+
+
+def _mappoints(k, d, n, seed, scale):
+    rng = np.random.default_rng(seed)
+    src = rng.integers(0, len(k), n)
+    desc = d[src].copy()
+    flips = rng.integers(0, 41, n)
+    for i in range(n):
+        bits = rng.choice(256, flips[i], replace=False)
+        np.bitwise_xor.at(desc[i], bits >> 3, (1 << (bits & 7)).astype(np.uint8))
+    return dict(track_in_view=(rng.random(n) < 0.9).astype(np.uint8),
+                proj_x=(k["x"][src] + rng.uniform(-3, 3, n)).astype(np.float32),
+                proj_y=(k["y"][src] + rng.uniform(-3, 3, n)).astype(np.float32),
+                proj_xr=(k["x"][src] - 20 + rng.uniform(-3, 3, n)).astype(np.float32),
+                level=np.minimum(k["octave"][src] + rng.integers(0, 2, n), 7).astype(np.int32),
+                view_cos=rng.choice(np.array([0.9, 0.999, 0.998], np.float32), n),
+                desc=desc, observations=rng.integers(0, 3, n).astype(np.int32))
+
+
+@pytest.mark.parametrize("nmp,th,stereo", [(20000, 1.0, False), (20000, 3.0, False), (5000, 5.0, True), (300, 15.0, False)])
+def test_search_by_projection_local_points(orbfe, oracle, nmp, th, stereo):
+    (k, d, _, t) = _frames(oracle, "mono", 5, 1000)[0]
+    rng = np.random.default_rng(9)
+    ur = np.where(rng.random(len(k)) < 0.5, k["x"] - 20, -1).astype(np.float32) if stereo else None
+    mps = _mappoints(k, d, nmp, 11, t["scale"])
+    occ_g = (rng.random(len(k)) < 0.05).astype(np.uint8); occ_o = occ_g.copy()
+    F = orbfe.Frame(k, d, 640, 480, t["scale"], uright=ur)
+    ng, mg = orbfe.ORBmatcher(0.8).SearchByProjection(F, mps, th, occ_g)
+    no, mo = oracle.search_by_projection(oracle.frame_view(k, d, 640, 480, t["scale"], ur), mps, th, 0.8, occ_o)
+    assert ng == no and np.array_equal(mg, mo) and np.array_equal(occ_g, occ_o)
+    assert ng > 100
+
+
+def test_compute_stereo_matches(orbfe, oracle):
+    for seed in (0, 1):
+        (kl, dl, pl, t), (kr, dr, pr, _) = _frames(oracle, "stereo", seed, 2000)
+        mbf = 386.1448; mb = mbf / 718.856
+        L = orbfe.Frame(kl, dl, 1241, 376, t["scale"]); R = orbfe.Frame(kr, dr, 1241, 376, t["scale"])
+        ug, dg = orbfe.ORBmatcher().ComputeStereoMatches(L, R, pl, pr, t["inv_scale"], mbf, mb)
+        uo, do = oracle.compute_stereo_matches(oracle.frame_view(kl, dl, 1241, 376, t["scale"]),
+                                               oracle.frame_view(kr, dr, 1241, 376, t["scale"]),
+                                               oracle.pyramid_view(pl), oracle.pyramid_view(pr), t["inv_scale"], mbf, mb)
+        assert ug.tobytes() == uo.tobytes() and dg.tobytes() == do.tobytes()
+        assert (ug >= 0).sum() > 100
