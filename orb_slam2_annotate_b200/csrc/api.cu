@@ -89,6 +89,14 @@ static void build_tables(orbfe_extractor* e, int nfeatures, float scaleFactor, i
     }
 }
 
+// the orientation kernel walks patch columns: needs |u| <= umax[|v|]  <=>  |v| <= umax[|u|]
+static bool umax_symmetric(const int* umax) {
+    for (int u = 0; u <= kHalfPatch; u++)
+        for (int v = 0; v <= kHalfPatch; v++)
+            if ((u <= umax[v]) != (v <= umax[u])) return false;
+    return true;
+}
+
 // cv::resize INTER_LINEAR coefficient tables for one level
 static void resize_tables(int sw, int sh, int dw, int dh, std::vector<int2>& xt, std::vector<int4>& yt) {
     const double scale_x = 1.0 / ((double)dw / sw), scale_y = 1.0 / ((double)dh / sh);
@@ -303,6 +311,7 @@ int orbfe_extractor_create(int nfeatures, float scale_factor, int nlevels, int i
     e->nfeatures = nfeatures; e->nlevels = nlevels; e->iniTh = ini_th; e->minTh = min_th;
     e->device = device;
     build_tables(e, nfeatures, scale_factor, nlevels);
+    if (!umax_symmetric(e->umax)) { delete e; return fail(ORBFE_ERR_ARG, "internal: circular patch table is not symmetric"); }
     cudaError_t ce = cudaSetDevice(device);
     if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
     if (ce != cudaSuccess) { delete e; return fail(ORBFE_ERR_CUDA, "cudaStreamCreate", ce); }

@@ -26,10 +26,9 @@ constexpr int ZONE = WIN - 6;           // max zone side
 // cv::FAST ring order, (dx,dy): (0,3) (1,3) (2,2) (3,1) (3,0) (3,-1) (2,-2) (1,-3) (0,-3)
 // (-1,-3) (-2,-2) (-3,-1) (-3,0) (-3,1) (-2,2) (-1,3)
 
-// packs (d, -d) as two signed 16-bit lanes
-__device__ __forceinline__ uint32_t pack_pm(int d) {
-    return ((uint32_t)d & 0xFFFFu) | ((uint32_t)(-d) << 16);
-}
+// a / b for 0 <= a < 2^16, 0 < b: exact, because (a + 0.5) / b is at least 0.5 / b away from
+// an integer while the float error is a few ulp
+__device__ __forceinline__ int small_div(int a, float rcp_b) { return (int)(((float)a + 0.5f) * rcp_b); }
 
 // corner strength S of the pixel at p (row stride `st`), or 0 when S <= t is already certain
 __device__ __forceinline__ int corner_strength(const uint8_t* p, int st, int t) {
@@ -53,21 +52,26 @@ __device__ __forceinline__ int corner_strength(const uint8_t* p, int st, int t) 
     r[3] = p[st + 3];       r[11] = p[-st - 3];
     r[5] = p[-st + 3];      r[13] = p[st - 3];
     r[7] = p[-3 * st + 1];  r[15] = p[3 * st - 1];
+    // (256 + v - r) in the low half, (256 + r - v) in the high half: one IMAD per ring pixel,
+    // both halves stay positive so signed 16-bit min/max order them like the differences.
+    const uint32_t bias = (uint32_t)(256 + v) | ((uint32_t)(256 - v) << 16);
     uint32_t d[16];
 #pragma unroll
-    for (int k = 0; k < 16; k++) d[k] = pack_pm(v - r[k]);
-    // sliding minimum over 9 contiguous ring positions (circular), both polarities at once
-    uint32_t m2[16], m4[16], m8[16];
+    for (int k = 0; k < 16; k++) d[k] = bias + (uint32_t)r[k] * 0xFFFFu;
+    // minima over ring[k+1..k+8] for even k (the 8 interior pixels shared by the two 9-arcs
+    // starting at k and k+1), by doubling on the odd positions only
+    uint32_t m2[8], m4[8], best = 0;
 #pragma unroll
-    for (int k = 0; k < 16; k++) m2[k] = __vmins2(d[k], d[(k + 1) & 15]);
+    for (int j = 0; j < 8; j++) m2[j] = __vmins2(d[2 * j + 1], d[(2 * j + 2) & 15]);           // [2j+1, 2j+2]
 #pragma unroll
-    for (int k = 0; k < 16; k++) m4[k] = __vmins2(m2[k], m2[(k + 2) & 15]);
+    for (int j = 0; j < 8; j++) m4[j] = __vmins2(m2[j], m2[(j + 1) & 7]);                         // [2j+1 .. 2j+4]
 #pragma unroll
-    for (int k = 0; k < 16; k++) m8[k] = __vmins2(m4[k], m4[(k + 4) & 15]);
-    uint32_t best = __vmins2(m8[0], d[8]);
-#pragma unroll
-    for (int k = 1; k < 16; k++) best = __vmaxs2(best, __vmins2(m8[k], d[(k + 8) & 15]));
-    const int A = (int)(short)(best & 0xFFFFu), B = (int)(short)(best >> 16);
+    for (int j = 0; j < 8; j++) {
+        const uint32_t m8 = __vmins2(m4[j], m4[(j + 2) & 7]);                                     // [2j+1 .. 2j+8]
+        best = __vmaxs2(best, __vmins2(m8, d[2 * j]));
+        best = __vmaxs2(best, __vmins2(m8, d[(2 * j + 9) & 15]));
+    }
+    const int A = (int)(best & 0xFFFFu) - 256, B = (int)(best >> 16) - 256;
     const int S = max(A, B);
     return S > t ? S : 0;
 }
@@ -194,15 +198,14 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __
     __shared__ WarpSmem smem[kWarpsPerCta];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     WarpSmem& S = smem[wid];
-    const long long gcell = (long long)blockIdx.x * kWarpsPerCta + wid;
-    if (gcell >= (long long)g.ncells * g.batch) return;
-    const int frame = (int)(gcell / g.ncells), cell = (int)(gcell - (long long)frame * g.ncells);
+    const int frame = blockIdx.y, cell = blockIdx.x * kWarpsPerCta + wid;
+    if (cell >= g.ncells) return;
     int l = 0;
     while (l + 1 < g.nlevels && cell >= g.lv[l + 1].cellBase) l++;
     const LevelGeom& L = g.lv[l];
     if (L.wCell + 6 > WWIN || L.hCell + 6 > WWIN) return;     // handled by the generic kernel
     const int c = cell - L.cellBase;
-    const int ci = c / L.nCols, cj = c - ci * L.nCols;
+    const int ci = small_div(c, __frcp_rn((float)L.nCols)), cj = c - ci * L.nCols;
     int* out_cnt = cellc + (long long)frame * g.ncells + cell;
     uint32_t* out = cellk + (long long)frame * g.cellSlots + L.cellSlotOff + (long long)c * L.cellCap;
 
@@ -221,9 +224,11 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __
     const int zx0 = iniX + 3 - ax0, zx1 = maxX - 3 - ax0;   // zone columns in window bytes
     const int zc0 = zx0 >> 2, nzc = ((zx1 - 1) >> 2) - zc0 + 1;
     const uint8_t* src = pyr + L.pyrOff + (long long)frame * L.lvBytes + (long long)iniY * L.pitch + ax0;
+    const float rcp_nw = __frcp_rn((float)nw), rcp_nzc = __frcp_rn((float)nzc);
+#pragma unroll 4
     for (int i = lane; i < wh * nw; i += 32) {
-        const int r = i / nw, cc = i - r * nw;
-        S.win[r][cc + 1] = __ldg(reinterpret_cast<const uint32_t*>(src + (long long)r * L.pitch) + cc);
+        const int r = small_div(i, rcp_nw), cc = i - r * nw;
+        S.win[r][cc + 1] = __ldg(reinterpret_cast<const uint32_t*>(src + r * L.pitch) + cc);
     }
     const uint8_t* wb = reinterpret_cast<const uint8_t*>(&S.win[0][0]) + 4;   // byte (r, x) = wb[r*WS*4 + x]
 
@@ -239,7 +244,7 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __
         __syncwarp();
         // ---- stage 1: SIMD rejection, 4 pixels per task
         for (int i = lane; i < zh * nzc; i += 32) {
-            const int r = i / nzc, cc = i - r * nzc;
+            const int r = small_div(i, rcp_nzc), cc = i - r * nzc;
             const int y = r + 3, wc = zc0 + cc + 1;          // window row, word column (+1 pad)
             const uint32_t v = S.win[y][wc];
             uint32_t gmask = swar_gt(__vabsdiffu4(S.win[y + 3][wc], v), cmpc, small_t) |
@@ -346,9 +351,8 @@ int launch_fast(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
     bool generic = false;
     for (int l = 0; l < g.nlevels; l++)
         if (g.lv[l].nCols && (g.lv[l].wCell + 6 > WWIN || g.lv[l].hCell + 6 > WWIN)) generic = true;
-    const long long ncell = (long long)g.ncells * g.batch;
-    if (ncell > 0) {
-        fast_cells_warp_kernel<<<(unsigned)((ncell + kWarpsPerCta - 1) / kWarpsPerCta), kWarpsPerCta * 32, 0, s>>>(
+    if (g.ncells > 0) {
+        fast_cells_warp_kernel<<<dim3((g.ncells + kWarpsPerCta - 1) / kWarpsPerCta, g.batch), kWarpsPerCta * 32, 0, s>>>(
             g, d.pyr, d.cellc, d.cellk);
         launches++;
     }

@@ -13,6 +13,7 @@
 //   * output slot = keypoints of lower levels + position in this level's list, i.e. the
 //     reference's level-by-level concatenation.
 #include "orbfe_internal.cuh"
+#include "sincosf_glibc.h"
 
 namespace orbfe {
 
@@ -71,16 +72,17 @@ orient_desc_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant
     // ---- IC_Angle
     int m10 = 0, m01 = 0;
     if (lane < 31) {
+        // the disc is symmetric (checked on the host): column u holds rows |v| <= umax[|u|]
         const uint8_t* c = d.pyr + off;
-        const int u = lane - kHalfPatch, au = abs(u);
-#pragma unroll 1
-        for (int v = -kHalfPatch; v <= kHalfPatch; v++) {
-            if (au <= __ldg(&umax[abs(v)])) {
-                const int val = c[v * L.pitch + u];
-                m10 += u * val;
-                m01 += v * val;
-            }
+        const int u = lane - kHalfPatch, vm = __ldg(&umax[abs(u)]);
+        int sum = 0;
+#pragma unroll 4
+        for (int v = -vm; v <= vm; v++) {
+            const int val = c[v * L.pitch + u];
+            sum += val;
+            m01 += v * val;
         }
+        m10 = u * sum;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -92,7 +94,12 @@ orient_desc_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant
     // ---- rBRIEF byte `lane`
     const float factorPI = (float)(3.14159265358979323846 / 180.f);   // :108
     const float ang = __fmul_rn(angle, factorPI);
-    const float a = (float)cos((double)ang), b = (float)sin((double)ang);   // see DESIGN.md §float parity
+    // cos/sin resolve to glibc's float routines in the reference (:68,:115-116); sincosf_glibc.h
+    // restates them bit for bit.  Two lanes evaluate, everyone reads the results.
+    float ab = 0.f;
+    if (lane == 0) ab = orbfe_scf::cosf_glibc(ang);
+    else if (lane == 1) ab = orbfe_scf::sinf_glibc(ang);
+    const float a = __shfl_sync(FULL, ab, 0), b = __shfl_sync(FULL, ab, 1);
     const uint8_t* cb = d.blur + off;
     const int4* pat4 = reinterpret_cast<const int4*>(d_pattern) + 2 * lane;
     const int4 w0 = __ldg(pat4), w1 = __ldg(pat4 + 1);
