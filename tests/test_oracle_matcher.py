@@ -1,0 +1,120 @@
+"""Known-answer tests for the oracle's matcher restatements (oracle/orc_matcher.cpp), derived by
+hand from the cited reference lines; the matcher TUs cannot be compiled here (Eigen/g2o/DBoW2)."""
+import numpy as np
+
+from oracle.oracle_py import KP_DTYPE
+
+SCALE = (1.2 ** np.arange(8)).astype(np.float32)
+
+
+def kp(x, y, octave=0, angle=0.0):
+    return (x, y, 31.0, angle, 50.0, octave, -1)
+
+
+def test_descriptor_distance_kats(oracle):
+    z = np.zeros(32, np.uint8); o = np.full(32, 255, np.uint8)
+    assert oracle.descriptor_distance(z, z) == 0 and oracle.descriptor_distance(z, o) == 256      # ORBmatcher.cc:1828-1844
+    for bit in (0, 7, 8, 100, 255):
+        a = z.copy(); a[bit >> 3] = 1 << (bit & 7)
+        assert oracle.descriptor_distance(a, z) == 1
+    rng = np.random.default_rng(0)
+    for _ in range(100):
+        a = rng.integers(0, 256, 32, dtype=np.uint8); b = rng.integers(0, 256, 32, dtype=np.uint8)
+        assert oracle.descriptor_distance(a, b) == int(np.unpackbits(a ^ b).sum())
+
+
+def test_three_maxima(oracle):
+    import ctypes as C
+    def run(counts):
+        c = np.zeros(30, np.int32); c[:len(counts)] = counts
+        a, b, d = C.c_int(), C.c_int(), C.c_int()
+        oracle.lib().orc_three_maxima(c.ctypes.data, 30, C.byref(a), C.byref(b), C.byref(d))
+        return a.value, b.value, d.value
+    assert run([5, 9, 7]) == (1, 2, 0)
+    assert run([100, 9, 7]) == (0, -1, -1)          # second < 10% of first drops second and third (:1808-1812)
+    assert run([100, 50, 7]) == (0, 1, -1)          # third < 10% of first (:1813-1816)
+    assert run([3, 3, 3]) == (0, 1, 2)              # strict '>' keeps the first of equals in front
+
+
+def test_grid_round_vs_floor_quirk(oracle):
+    # PosInGrid rounds (Frame.cc:422-423): x=14.9 at 10 px cells lands in column 1, and a query
+    # window [floor, ceil] still finds it
+    k = np.array([kp(14.9, 5.0), kp(300.0, 200.0, 1)], KP_DTYPE)
+    d = np.zeros((2, 32), np.uint8)
+    fv = oracle.frame_view(k, d, 640, 480, SCALE)
+    cs = np.zeros(3073, np.int32); ci = np.zeros(2, np.int32)
+    oracle.lib().orc_assign_grid(fv[0], cs.ctypes.data, ci.ctypes.data)
+    cell = 1 * 48 + 1    # round(14.9/10)=1, round(5.0/10)=1 (round-half-away: 0.5 -> 1)
+    assert cs[cell + 1] - cs[cell] == 1
+    out = np.zeros(4, np.int32)
+    import ctypes as C
+    n = oracle.lib().orc_features_in_area(C.byref(fv[0]), cs.ctypes.data, ci.ctypes.data, 12.0, 5.0, 5.0, -1, -1, out.ctypes.data, 4)
+    assert n == 1 and out[0] == 0
+    # level filter: minLevel=0,maxLevel=0 checks levels (maxLevel>=0), octave-1 keypoint excluded (Frame.cc:381-395)
+    n = oracle.lib().orc_features_in_area(C.byref(fv[0]), cs.ctypes.data, ci.ctypes.data, 300.0, 200.0, 5.0, 0, 0, out.ctypes.data, 4)
+    assert n == 0
+    # strict '<' on the window: a keypoint exactly r away is excluded (Frame.cc:405)
+    n = oracle.lib().orc_features_in_area(C.byref(fv[0]), cs.ctypes.data, ci.ctypes.data, 295.0, 200.0, 5.0, -1, -1, out.ctypes.data, 4)
+    assert n == 0
+
+
+def test_search_for_initialization_kat(oracle):
+    # F1: two octave-0 keypoints with the same descriptor both near F2[0]; the second query's
+    # candidate is skipped because vMatchedDistance[i2] <= dist (:515-516) -> only the first matches.
+    d0 = np.zeros(32, np.uint8)
+    far = np.full(32, 255, np.uint8)
+    k1 = np.array([kp(100, 100), kp(102, 100), kp(400, 300, 1)], KP_DTYPE)
+    d1 = np.stack([d0, d0, d0])
+    k2 = np.array([kp(101, 100), kp(110, 100)], KP_DTYPE)
+    d2 = np.stack([d0, far])
+    prev = np.ascontiguousarray(np.stack([k1["x"], k1["y"]], 1), np.float32)
+    n, m12 = oracle.search_for_initialization(oracle.frame_view(k1, d1, 640, 480, SCALE),
+                                              oracle.frame_view(k2, d2, 640, 480, SCALE), prev, 100, 0.9, False)
+    assert n == 1 and m12.tolist() == [0, -1, -1]
+    assert prev[0].tolist() == [101.0, 100.0] and prev[1].tolist() == [102.0, 100.0]     # :595-597
+    # a strictly better later query steals the match and un-matches the earlier one (:536-541)
+    d1b = d1.copy(); d1b[0, 0] = 0b111           # query 0 at distance 3, query 1 at distance 0
+    prev = np.ascontiguousarray(np.stack([k1["x"], k1["y"]], 1), np.float32)
+    n, m12 = oracle.search_for_initialization(oracle.frame_view(k1, d1b, 640, 480, SCALE),
+                                              oracle.frame_view(k2, d2, 640, 480, SCALE), prev, 100, 0.9, False)
+    assert n == 1 and m12.tolist() == [-1, 0, -1]
+    # ratio test: best must be < ratio * second (:534)
+    d2c = np.stack([d0, d0]); d2c[1, 0] = 1      # distances 0 and 1 -> 0 < 0.9*1 passes
+    n, m12 = oracle.search_for_initialization(oracle.frame_view(k1[:1], d1[:1], 640, 480, SCALE),
+                                              oracle.frame_view(k2, d2c, 640, 480, SCALE),
+                                              np.array([[100, 100]], np.float32), 100, 0.9, False)
+    assert n == 1 and m12.tolist() == [0]
+    d1d = d1[:1].copy(); d1d[0, 1] = 0xFF         # distances 8 and 9 -> 8 < 8.1 passes; with ratio 0.8 fails
+    n, _ = oracle.search_for_initialization(oracle.frame_view(k1[:1], d1d, 640, 480, SCALE),
+                                            oracle.frame_view(k2, d2c, 640, 480, SCALE),
+                                            np.array([[100, 100]], np.float32), 100, 0.8, False)
+    assert n == 0
+
+
+def test_search_by_projection_kat(oracle):
+    d0 = np.zeros(32, np.uint8)
+    k = np.array([kp(100, 100, 0), kp(103, 100, 0)], KP_DTYPE)
+    d = np.stack([d0, d0]); d[1, 0] = 0xFF     # distance 8 from the map points
+    f = oracle.frame_view(k, d, 640, 480, SCALE)
+    mps = dict(track_in_view=[1, 1, 0], proj_x=[100, 100, 100], proj_y=[100, 100, 100], proj_xr=[0, 0, 0], level=[0, 0, 0],
+               view_cos=[0.9, 0.9, 0.9], desc=np.stack([d0, d0, d0]), observations=[1, 1, 1])
+    occ = np.zeros(2, np.uint8)
+    n, out = oracle.search_by_projection(f, mps, 1.0, 0.8, occ)
+    # r = 4.0 (viewCos <= 0.998), both keypoints inside; same octave and 0 > 0.8*8 false -> accept kp0 (:127-135);
+    # second map point finds kp0 occupied (:95-98), best becomes kp1 at distance 8 with no second -> accepted
+    assert n == 2 and out.tolist() == [0, 1] and occ.tolist() == [1, 1]
+    # viewCos > 0.998 -> r = 2.5: kp1 (3 px away) is outside
+    mps["view_cos"] = [0.999, 0.999, 0.999]
+    occ = np.zeros(2, np.uint8)
+    n, out = oracle.search_by_projection(f, mps, 1.0, 0.8, occ)
+    assert n == 1 and out.tolist() == [0, -1]
+
+
+def test_knn2_kat(oracle):
+    t = np.zeros((3, 32), np.uint8); t[1, 0] = 1; t[2, 0] = 3
+    q = np.zeros((1, 32), np.uint8)
+    idx, d1, d2 = oracle.knn2(q, t, 50, 0.7)
+    assert (idx[0], d1[0], d2[0]) == (0, 0, 1)
+    t[0, 0] = 1        # two rows at distance 1: first wins, d2 == d1, ratio test rejects
+    idx, d1, d2 = oracle.knn2(q, t, 50, 0.7)
+    assert (idx[0], d1[0], d2[0]) == (-1, 1, 1)
