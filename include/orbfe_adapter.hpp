@@ -1,0 +1,231 @@
+// orbfe_adapter.hpp — header-only C++ host side of liborbfe: drop-in classes with the
+// reference's names and signatures, so that Frame.cc / Tracking.cc compile unchanged.
+//
+//   ORB_SLAM2::ORBextractor   replaces include/ORBextractor.h:46-114 + src/ORBextractor.cc
+//   ORB_SLAM2::ORBmatcher     replaces the hot-path members of include/ORBmatcher.h:51-117
+//                             (DescriptorDistance, SearchForInitialization,
+//                             SearchByProjection(Frame&, vector<MapPoint*>&, th)) and offers
+//                             ComputeStereoMatches(Frame&) for src/Frame.cc:512-686
+//
+// Include AFTER the OpenCV core headers (cv::Mat, cv::KeyPoint, cv::InputArray, cv::OutputArray,
+// cv::Point2f must be visible).  The Frame / MapPoint dependent members are templates over the
+// reference's own types, so this header needs neither Frame.h nor MapPoint.h; it reads exactly
+// the fields the reference routines read.  All arithmetic happens in liborbfe's CUDA kernels;
+// this file only flattens objects into the plain views of include/orbfe.h and writes results
+// back.  There is no CPU fallback: a failed call throws std::runtime_error.
+#ifndef ORBFE_ADAPTER_HPP
+#define ORBFE_ADAPTER_HPP
+
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "orbfe.h"
+
+namespace ORB_SLAM2 {
+
+namespace orbfe_detail {
+inline void check(int rc, const char* what) {
+    if (rc != ORBFE_OK) throw std::runtime_error(std::string(what) + ": " + orbfe_last_error());
+}
+}  // namespace orbfe_detail
+
+class ORBextractor {
+public:
+    enum { HARRIS_SCORE = 0, FAST_SCORE = 1 };
+
+    // include/ORBextractor.h:53-54.  `device` and `downloadPyramid` are additions with defaults:
+    // stereo needs mvImagePyramid on the host after every call (src/Frame.cc:519,609-626),
+    // monocular / RGB-D callers can switch the copy off.
+    ORBextractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST,
+                 int device = 0, bool downloadPyramid = true)
+        : mpHandle(nullptr), nlevels(nlevels), mbDownloadPyramid(downloadPyramid) {
+        orbfe_detail::check(orbfe_extractor_create(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, 0, 0, 0,
+                                                   device, &mpHandle), "orbfe_extractor_create");
+        mvScaleFactor.resize(nlevels); mvInvScaleFactor.resize(nlevels);
+        mvLevelSigma2.resize(nlevels); mvInvLevelSigma2.resize(nlevels);
+        orbfe_get_scale_tables(mpHandle, mvScaleFactor.data(), mvInvScaleFactor.data(), mvLevelSigma2.data(),
+                               mvInvLevelSigma2.data(), nullptr, nullptr);
+        this->scaleFactor = scaleFactor;                                   // double member set from a float (:417)
+        mvImagePyramid.resize(nlevels);
+    }
+    ~ORBextractor() { orbfe_extractor_destroy(mpHandle); }
+    ORBextractor(const ORBextractor&) = delete;
+    ORBextractor& operator=(const ORBextractor&) = delete;
+
+    // src/ORBextractor.cc:1119-1197.  Mask is ignored, as in the reference.
+    void operator()(cv::InputArray _image, cv::InputArray /*_mask*/, std::vector<cv::KeyPoint>& _keypoints,
+                    cv::OutputArray _descriptors) {
+        if (_image.empty()) return;                                        // :1122-1123
+        cv::Mat image = _image.getMat();
+        const int cap = orbfe_extractor_max_keypoints(mpHandle) + 4096;
+        mKpBuf.resize(cap); mDescBuf.resize((size_t)cap * 32);
+        int n = 0;
+        orbfe_detail::check(orbfe_extract(mpHandle, image.data, image.cols, image.rows, (ptrdiff_t)(size_t)image.step,
+                                          mKpBuf.data(), mDescBuf.data(), cap, &n), "orbfe_extract");
+        _keypoints.clear();
+        if (n == 0) {
+            _descriptors.release();                                        // :1145-1146
+        } else {
+            _descriptors.create(n, 32, CV_8U);                             // :1149
+            cv::Mat descriptors = _descriptors.getMat();
+            _keypoints.reserve(n);
+            for (int i = 0; i < n; i++) {
+                const orbfe_keypoint& k = mKpBuf[i];
+                _keypoints.push_back(cv::KeyPoint(k.x, k.y, k.size, k.angle, k.response, k.octave, k.class_id));
+                std::memcpy(descriptors.ptr(i), &mDescBuf[(size_t)i * 32], 32);
+            }
+        }
+        if (mbDownloadPyramid) {
+            for (int l = 0; l < nlevels; l++) {
+                int w = 0, h = 0;
+                orbfe_pyramid_level(mpHandle, 0, l, 0, nullptr, 0, &w, &h);
+                mvImagePyramid[l].create(h, w, CV_8UC1);
+                orbfe_detail::check(orbfe_pyramid_level(mpHandle, 0, l, 0, mvImagePyramid[l].data,
+                                                        (ptrdiff_t)(size_t)mvImagePyramid[l].step, &w, &h),
+                                    "orbfe_pyramid_level");
+            }
+        }
+    }
+
+    int inline GetLevels() { return nlevels; }
+    float inline GetScaleFactor() { return (float)scaleFactor; }
+    std::vector<float> inline GetScaleFactors() { return mvScaleFactor; }
+    std::vector<float> inline GetInverseScaleFactors() { return mvInvScaleFactor; }
+    std::vector<float> inline GetScaleSigmaSquares() { return mvLevelSigma2; }
+    std::vector<float> inline GetInverseScaleSigmaSquares() { return mvInvLevelSigma2; }
+
+    std::vector<cv::Mat> mvImagePyramid;   // include/ORBextractor.h:86 (interior pixels of each level)
+
+    orbfe_extractor* Handle() { return mpHandle; }
+
+protected:
+    orbfe_extractor* mpHandle;
+    double scaleFactor;
+    int nlevels;
+    bool mbDownloadPyramid;
+    std::vector<float> mvScaleFactor, mvInvScaleFactor, mvLevelSigma2, mvInvLevelSigma2;
+    std::vector<orbfe_keypoint> mKpBuf;
+    std::vector<uint8_t> mDescBuf;
+};
+
+class ORBmatcher {
+public:
+    static const int TH_LOW = 50, TH_HIGH = 100, HISTO_LENGTH = 30;      // src/ORBmatcher.cc:37-39
+
+    ORBmatcher(float nnratio = 0.6f, bool checkOri = true, int device = 0)
+        : mfNNratio(nnratio), mbCheckOrientation(checkOri), mpHandle(nullptr) {
+        orbfe_detail::check(orbfe_matcher_create(device, &mpHandle), "orbfe_matcher_create");
+    }
+    ~ORBmatcher() { orbfe_matcher_destroy(mpHandle); }
+    ORBmatcher(const ORBmatcher&) = delete;
+    ORBmatcher& operator=(const ORBmatcher&) = delete;
+
+    // src/ORBmatcher.cc:1828-1844
+    static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b) { return orbfe_hamming256(a.data, b.data); }
+
+    // src/ORBmatcher.cc:469-600
+    template <class FrameT>
+    int SearchForInitialization(FrameT& F1, FrameT& F2, std::vector<cv::Point2f>& vbPrevMatched,
+                                std::vector<int>& vnMatches12, int windowSize = 10) {
+        std::vector<orbfe_keypoint> k1, k2;
+        std::vector<uint8_t> d1, d2;
+        orbfe_frame_view v1 = View(F1, k1, d1), v2 = View(F2, k2, d2);
+        vnMatches12.assign(F1.mvKeysUn.size(), -1);
+        std::vector<float> prev(2 * vbPrevMatched.size());
+        for (size_t i = 0; i < vbPrevMatched.size(); i++) { prev[2 * i] = vbPrevMatched[i].x; prev[2 * i + 1] = vbPrevMatched[i].y; }
+        int nmatches = 0;
+        orbfe_detail::check(orbfe_search_init(mpHandle, &v1, &v2, prev.data(), vnMatches12.data(), windowSize,
+                                              mfNNratio, mbCheckOrientation ? 1 : 0, &nmatches), "orbfe_search_init");
+        for (size_t i = 0; i < vbPrevMatched.size(); i++) { vbPrevMatched[i].x = prev[2 * i]; vbPrevMatched[i].y = prev[2 * i + 1]; }
+        return nmatches;
+    }
+
+    // SearchByProjection(Frame&, const vector<MapPoint*>&, th) — src/ORBmatcher.cc:51-138
+    template <class FrameT, class MapPointT>
+    int SearchByProjection(FrameT& F, const std::vector<MapPointT*>& vpMapPoints, const float th = 3) {
+        std::vector<orbfe_keypoint> k;
+        std::vector<uint8_t> d;
+        orbfe_frame_view fv = View(F, k, d);
+        if (!F.mvuRight.empty()) fv.uright = F.mvuRight.data();
+        const int n = (int)vpMapPoints.size();
+        std::vector<uint8_t> inView(n), desc((size_t)n * 32);
+        std::vector<float> px(n), py(n), pxr(n), vcos(n);
+        std::vector<int> level(n), obs(n);
+        for (int i = 0; i < n; i++) {
+            MapPointT* pMP = vpMapPoints[i];
+            inView[i] = pMP && pMP->mbTrackInView && !pMP->isBad();        // :60-64
+            if (!inView[i]) continue;
+            px[i] = pMP->mTrackProjX; py[i] = pMP->mTrackProjY; pxr[i] = pMP->mTrackProjXR;
+            level[i] = pMP->mnTrackScaleLevel; vcos[i] = pMP->mTrackViewCos;
+            const cv::Mat dmp = pMP->GetDescriptor();
+            std::memcpy(&desc[(size_t)i * 32], dmp.data, 32);
+            obs[i] = pMP->Observations();
+        }
+        orbfe_mappoints_view mv = {n, inView.data(), px.data(), py.data(), pxr.data(), level.data(), vcos.data(),
+                                   desc.data(), obs.data()};
+        std::vector<uint8_t> occupied(F.mvpMapPoints.size(), 0);
+        for (size_t i = 0; i < F.mvpMapPoints.size(); i++)                 // :95-98
+            occupied[i] = F.mvpMapPoints[i] && F.mvpMapPoints[i]->Observations() > 0;
+        std::vector<int> mpForKp(F.mvpMapPoints.size(), -1);
+        int nmatches = 0;
+        orbfe_detail::check(orbfe_search_local_points(mpHandle, &fv, &mv, th, mfNNratio, occupied.data(),
+                                                      mpForKp.data(), &nmatches), "orbfe_search_local_points");
+        for (size_t i = 0; i < mpForKp.size(); i++)
+            if (mpForKp[i] >= 0) F.mvpMapPoints[i] = vpMapPoints[mpForKp[i]];   // :132
+        return nmatches;
+    }
+
+    // Frame::ComputeStereoMatches — src/Frame.cc:512-686 (call instead of the member)
+    template <class FrameT>
+    void ComputeStereoMatches(FrameT& F) {
+        const int N = (int)F.mvKeys.size(), L = (int)F.mvScaleFactors.size();
+        F.mvuRight = std::vector<float>(N, -1.0f);
+        F.mvDepth = std::vector<float>(N, -1.0f);
+        if (N == 0) return;
+        std::vector<orbfe_keypoint> kl(N), kr(F.mvKeysRight.size());
+        for (int i = 0; i < N; i++) kl[i] = Kp(F.mvKeys[i]);
+        for (size_t i = 0; i < kr.size(); i++) kr[i] = Kp(F.mvKeysRight[i]);
+        const cv::Mat& p0 = F.mpORBextractorLeft->mvImagePyramid[0];
+        orbfe_frame_view vl = {N, kl.data(), F.mDescriptors.data, nullptr, 0.f, (float)p0.cols, 0.f, (float)p0.rows,
+                               F.mvScaleFactors.data(), L};
+        orbfe_frame_view vr = {(int)kr.size(), kr.data(), F.mDescriptorsRight.data, nullptr, 0.f, (float)p0.cols, 0.f,
+                               (float)p0.rows, F.mvScaleFactors.data(), L};
+        std::vector<const uint8_t*> dl(L), dr(L);
+        std::vector<int32_t> wl(L), hl(L), wr(L), hr(L);
+        std::vector<ptrdiff_t> sl(L), sr(L);
+        for (int l = 0; l < L; l++) {
+            const cv::Mat& a = F.mpORBextractorLeft->mvImagePyramid[l];
+            const cv::Mat& b = F.mpORBextractorRight->mvImagePyramid[l];
+            dl[l] = a.data; wl[l] = a.cols; hl[l] = a.rows; sl[l] = (ptrdiff_t)(size_t)a.step;
+            dr[l] = b.data; wr[l] = b.cols; hr[l] = b.rows; sr[l] = (ptrdiff_t)(size_t)b.step;
+        }
+        orbfe_pyramid_view pl = {L, dl.data(), wl.data(), hl.data(), sl.data()};
+        orbfe_pyramid_view pr = {L, dr.data(), wr.data(), hr.data(), sr.data()};
+        orbfe_detail::check(orbfe_stereo_match(mpHandle, &vl, &vr, &pl, &pr, F.mvInvScaleFactors.data(), F.mbf, F.mb,
+                                               F.mvuRight.data(), F.mvDepth.data()), "orbfe_stereo_match");
+    }
+
+    float mfNNratio;
+    bool mbCheckOrientation;
+
+protected:
+    static orbfe_keypoint Kp(const cv::KeyPoint& k) {
+        orbfe_keypoint o = {k.pt.x, k.pt.y, k.size, k.angle, k.response, k.octave, k.class_id};
+        return o;
+    }
+    // the Frame fields the searches read: mvKeysUn, mDescriptors, mnMinX.., mvScaleFactors
+    template <class FrameT>
+    static orbfe_frame_view View(FrameT& F, std::vector<orbfe_keypoint>& k, std::vector<uint8_t>& /*d*/) {
+        k.resize(F.mvKeysUn.size());
+        for (size_t i = 0; i < k.size(); i++) k[i] = Kp(F.mvKeysUn[i]);
+        orbfe_frame_view v = {(int)k.size(), k.data(), F.mDescriptors.data, nullptr, FrameT::mnMinX, FrameT::mnMaxX,
+                              FrameT::mnMinY, FrameT::mnMaxY, F.mvScaleFactors.data(), (int)F.mvScaleFactors.size()};
+        return v;
+    }
+    orbfe_matcher* mpHandle;
+};
+
+}  // namespace ORB_SLAM2
+#endif  // ORBFE_ADAPTER_HPP

@@ -1,0 +1,65 @@
+// adapter_smoke.cpp — drives include/orbfe_adapter.hpp the way Frame.cc / Tracking.cc drive the
+// reference classes: ORB_SLAM2::ORBextractor::operator()(image, mask, keypoints, descriptors) on
+// two frames, then ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, 100)
+// on a minimal Frame stand-in with the reference's field names.  cv:: types come from the test
+// shim (oracle/cvshim) because OpenCV headers are absent here.
+// usage: adapter_smoke in.bin out.bin     in.bin = int32 w, h, then 2*w*h bytes (two frames)
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
+#include "cvshim.hpp"
+#include "orbfe_adapter.hpp"
+
+struct Frame {   // the members of ORB_SLAM2::Frame the matcher reads (include/Frame.h)
+    std::vector<cv::KeyPoint> mvKeys, mvKeysUn;
+    cv::Mat mDescriptors;
+    std::vector<float> mvScaleFactors;
+    static float mnMinX, mnMaxX, mnMinY, mnMaxY;
+};
+float Frame::mnMinX, Frame::mnMaxX, Frame::mnMinY, Frame::mnMaxY;
+
+int main(int argc, char** argv) {
+    if (argc < 3) return 2;
+    FILE* f = fopen(argv[1], "rb");
+    int wh[2];
+    if (!f || fread(wh, 4, 2, f) != 2) return 2;
+    const int w = wh[0], h = wh[1];
+    std::vector<unsigned char> buf((size_t)2 * w * h);
+    if (fread(buf.data(), 1, buf.size(), f) != buf.size()) return 2;
+    fclose(f);
+    ORB_SLAM2::ORBextractor extractor(2000, 1.2f, 8, 20, 7);       // mpIniORBextractor, Tracking.cc:128
+    Frame F[2];
+    Frame::mnMinX = 0; Frame::mnMaxX = (float)w; Frame::mnMinY = 0; Frame::mnMaxY = (float)h;
+    for (int i = 0; i < 2; i++) {
+        cv::Mat im(h, w, CV_8UC1, buf.data() + (size_t)i * w * h, (size_t)w);
+        extractor(im, cv::Mat(), F[i].mvKeys, F[i].mDescriptors);   // Frame::ExtractORB, Frame.cc:275
+        F[i].mvKeysUn = F[i].mvKeys;
+        F[i].mvScaleFactors = extractor.GetScaleFactors();
+    }
+    if ((int)extractor.mvImagePyramid.size() != 8 || extractor.mvImagePyramid[7].empty()) return 3;
+    std::vector<cv::Point2f> prev(F[0].mvKeysUn.size());
+    for (size_t i = 0; i < prev.size(); i++) prev[i] = F[0].mvKeysUn[i].pt;   // Tracking.cc:609-616
+    std::vector<int> m12;
+    ORB_SLAM2::ORBmatcher matcher(0.9f, true);                      // Tracking.cc:641
+    const int nm = matcher.SearchForInitialization(F[0], F[1], prev, m12, 100);
+    FILE* o = fopen(argv[2], "wb");
+    for (int i = 0; i < 2; i++) {
+        int n = (int)F[i].mvKeys.size();
+        fwrite(&n, 4, 1, o);
+        for (int k = 0; k < n; k++) {
+            const cv::KeyPoint& kp = F[i].mvKeys[k];
+            float v[5] = {kp.pt.x, kp.pt.y, kp.size, kp.angle, kp.response};
+            int q[2] = {kp.octave, kp.class_id};
+            fwrite(v, 4, 5, o); fwrite(q, 4, 2, o);
+        }
+        fwrite(F[i].mDescriptors.data, 1, (size_t)n * 32, o);
+    }
+    int n1 = (int)m12.size();
+    fwrite(&nm, 4, 1, o); fwrite(&n1, 4, 1, o); fwrite(m12.data(), 4, n1, o);
+    fclose(o);
+    printf("adapter_smoke: %zu + %zu keypoints, %d init matches, DescriptorDistance(0,1)=%d\n", F[0].mvKeys.size(),
+           F[1].mvKeys.size(), nm,
+           ORB_SLAM2::ORBmatcher::DescriptorDistance(F[0].mDescriptors.rowRange(0, 1), F[0].mDescriptors.rowRange(1, 2)));
+    return 0;
+}

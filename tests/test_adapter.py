@@ -1,0 +1,60 @@
+"""The C++ host side (include/orbfe_adapter.hpp: ORB_SLAM2::ORBextractor / ORBmatcher with the
+reference's signatures) compiles against a cv:: type shim and, on the GPU box, produces the same
+keypoints, descriptors and initialisation matches as the Python host side and the oracle."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from orb_slam2_annotate_b200 import synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EXE = os.path.join(ROOT, "tests", "cpp", "adapter_smoke")
+
+
+def _build():
+    subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "liborb_oracle.so"], check=True, stdout=subprocess.DEVNULL)
+    subprocess.run(["g++", "-std=c++11", "-O2", "-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(ROOT, "oracle", "cvshim"),
+                    "-I" + os.path.join(ROOT, "oracle"), "-o", EXE, os.path.join(ROOT, "tests", "cpp", "adapter_smoke.cpp"),
+                    "-L" + os.path.join(ROOT, "orb_slam2_annotate_b200"), "-lorbfe", "-L" + os.path.join(ROOT, "oracle"), "-lorb_oracle",
+                    "-Wl,-rpath," + os.path.join(ROOT, "orb_slam2_annotate_b200"), "-Wl,-rpath," + os.path.join(ROOT, "oracle")],
+                   check=True)
+
+
+def test_adapter_compiles_and_links(orbfe):
+    _build()
+    assert os.path.exists(EXE)
+
+
+@pytest.mark.gpu
+def test_adapter_end_to_end(orbfe, oracle, tmp_path):
+    _build()
+    imgs, _ = synth.sequence(2, 640, 480, seed=4)
+    inp, out = str(tmp_path / "in.bin"), str(tmp_path / "out.bin")
+    with open(inp, "wb") as f:
+        f.write(np.array([640, 480], np.int32).tobytes()); f.write(imgs.tobytes())
+    r = subprocess.run([EXE, inp, out], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    print(r.stdout.strip())
+    raw = open(out, "rb").read()
+    off = 0
+    frames = []
+    for i in range(2):
+        n = int(np.frombuffer(raw, np.int32, 1, off)[0]); off += 4
+        k = np.frombuffer(raw, orbfe.KP_DTYPE, n, off); off += 28 * n
+        d = np.frombuffer(raw, np.uint8, 32 * n, off).reshape(n, 32); off += 32 * n
+        frames.append((k, d))
+    nm, n1 = (int(v) for v in np.frombuffer(raw, np.int32, 2, off)); off += 8
+    m12 = np.frombuffer(raw, np.int32, n1, off)
+    t = oracle.OracleExtractor(2000).tables()
+    ref = [oracle.OracleExtractor(2000)(im) for im in imgs]
+    for (k, d), (ko, do) in zip(frames, ref):
+        assert len(k) == len(ko)
+        for f in ("x", "y", "size", "response", "octave", "class_id"):
+            assert np.array_equal(k[f], ko[f])
+        assert np.abs(k["angle"] - ko["angle"]).max() <= 1e-3 and (d != do).any(axis=1).sum() <= 2
+    prev = np.ascontiguousarray(np.stack([ref[0][0]["x"], ref[0][0]["y"]], 1), np.float32)
+    no, mo = oracle.search_for_initialization(oracle.frame_view(ref[0][0], ref[0][1], 640, 480, t["scale"]),
+                                              oracle.frame_view(ref[1][0], ref[1][1], 640, 480, t["scale"]), prev, 100, 0.9, True)
+    assert nm == no and np.array_equal(m12, mo) and nm > 100
