@@ -179,52 +179,102 @@ def main():
     B = args.batch
     frames = make_frames(B, seed=1000 * rank)           # every rank its own stream (weak scaling)
     ex = orbfe.ORBextractor(NFEAT, 1.2, 8, 20, 7, device=local_rank, max_width=W, max_height=H, max_batch=B)
+    mt = orbfe.ORBmatcher(0.9, True, device=local_rank)            # Tracking.cc:641
     d_frames = torch.from_numpy(frames).cuda()
-    stream = torch.cuda.ExternalStream(ex.stream, device=local_rank)
+    xs = torch.cuda.ExternalStream(ex.stream, device=local_rank)   # the library's own streams
+    ms = torch.cuda.ExternalStream(mt.stream, device=local_rank)
     ex.set_profiling(True)
+    cap = ex.max_keypoints()
+    d_m12 = torch.empty((max(B - 1, 1), cap), dtype=torch.int32, device="cuda")
+    d_nm = torch.zeros(max(B - 1, 1), dtype=torch.int32, device="cuda")
+    m_ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    x_done, m_done = torch.cuda.Event(), torch.cuda.Event()
 
-    # ---- device-resident timing: K steps, CUDA events on the extractor's stream
-    for _ in range(args.warmup):
+    def step(timed=None):
+        """extract the batch, then SearchForInitialization between consecutive frames"""
+        xs.wait_event(m_done)                            # the matcher of the previous step read these buffers
         ex.extract_batch_device(d_frames.data_ptr(), B, W, H)
-    ex.sync()
+        x_done.record(xs)
+        ms.wait_event(x_done)
+        kp_ptr, desc_ptr, cnt_ptr, dcap = ex.device_results()
+        m_ev[0].record(ms)
+        mt.search_init_consecutive_device(kp_ptr, desc_ptr, cnt_ptr, dcap, B, W, H, d_m12.data_ptr(), d_nm.data_ptr(), 100)
+        m_ev[1].record(ms)
+        m_done.record(ms)
+        if timed is not None:
+            for k, v in ex.stage_times_ms().items():     # syncs on the step's last extractor event
+                timed[k] = timed.get(k, 0.0) + v
+            m_ev[1].synchronize()
+            timed["search_init"] = timed.get("search_init", 0.0) + m_ev[0].elapsed_time(m_ev[1])
+
+    # ---- device-resident timing: K steps, CUDA events on the library's streams
+    m_done.record(ms)
+    for _ in range(args.warmup):
+        step()
+    ex.sync(); mt.sync()
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     stage_sum = {}
-    e0.record(stream)
+    e0.record(xs)
     for _ in range(args.steps):
-        ex.extract_batch_device(d_frames.data_ptr(), B, W, H)
-        for k, v in ex.stage_times_ms().items():         # syncs on the step's last event
-            stage_sum[k] = stage_sum.get(k, 0.0) + v
-    e1.record(stream)
-    ex.sync()
+        step(stage_sum)
+    e1.record(ms)
+    ex.sync(); mt.sync()
     barrier()
     dev_ms = e0.elapsed_time(e1)
     clocks = sampler.stop()
-    launches = ex.last_launches * args.steps
+    launches = (ex.last_launches + 1) * args.steps
     _, _, counts = ex.fetch()
     mean_kp = float(counts.mean())
+    mean_matches = float(d_nm[:B - 1].float().mean().item()) if B > 1 else 0.0
 
     # ---- end to end through the host-buffer C-ABI call: pinned frames in, results out
     h_frames = orbfe.pinned_empty(frames.shape, np.uint8)
     h_frames[...] = frames
-    cap = ex.max_keypoints()
     out = (orbfe.pinned_empty((B, cap), orbfe.KP_DTYPE), orbfe.pinned_empty((B, cap, 32), np.uint8),
            orbfe.pinned_empty((B,), np.int32))
+    h_m12 = torch.empty((max(B - 1, 1), cap), dtype=torch.int32).pin_memory()
+    h_nm = torch.empty(max(B - 1, 1), dtype=torch.int32).pin_memory()
+
+    def e2e_step():
+        ex.extract_batch(h_frames, out=out)              # H2D frames, kernels, D2H keypoints + descriptors
+        kp_ptr, desc_ptr, cnt_ptr, dcap = ex.device_results()
+        mt.search_init_consecutive_device(kp_ptr, desc_ptr, cnt_ptr, dcap, B, W, H, d_m12.data_ptr(), d_nm.data_ptr(), 100)
+        with torch.cuda.stream(ms):
+            h_m12.copy_(d_m12, non_blocking=True)
+            h_nm.copy_(d_nm, non_blocking=True)
+        mt.sync()
+
     for _ in range(max(1, min(args.warmup, 2))):
-        ex.extract_batch(h_frames, out=out)
+        e2e_step()
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        ex.extract_batch(h_frames, out=out)
+        e2e_step()
     barrier()
     e2e_s = time.perf_counter() - t0
 
-    t = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    # ---- Hamming matcher throughput: brute-force kNN-2, queries sharded per GPU (config 5 shape, sampled)
+    MQ = NT = 131072
+    tq = torch.randint(0, 256, (MQ, 32), dtype=torch.uint8, device="cuda")
+    tt = torch.randint(0, 256, (NT, 32), dtype=torch.uint8, device="cuda")
+    ko = torch.empty((3, MQ), dtype=torch.int32, device="cuda")
+    mt.knn2_device(tq.data_ptr(), MQ, tt.data_ptr(), NT, ko[0].data_ptr(), ko[1].data_ptr(), ko[2].data_ptr(), 50, 0.7)
+    mt.sync()
+    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    k0.record(ms)
+    for _ in range(3):
+        mt.knn2_device(tq.data_ptr(), MQ, tt.data_ptr(), NT, ko[0].data_ptr(), ko[1].data_ptr(), ko[2].data_ptr(), 50, 0.7)
+    k1.record(ms)
+    mt.sync()
+    knn_ms = k0.elapsed_time(k1) / 3
+
+    t = torch.tensor([dev_ms, e2e_s * 1e3, knn_ms], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms, e2e_ms = t.tolist()
+    dev_ms, e2e_ms, knn_ms = t.tolist()
 
     if rank == 0:
         total_frames = B * world * args.steps
@@ -240,17 +290,32 @@ def main():
         achieved = ab[dom] * B / (stage_ms[dom] * 1e-3) / 1e9
         per_kernel = {k: {"ms": stage_ms[k], "gbs": ab[k] * B / (stage_ms[k] * 1e-3) / 1e9 if k in ab else None}
                       for k in stage_ms}
+        popc_peak, popc_src = 557.1, "tools/microbench on this pool (profiles/r01_microbench.json)"
+        try:
+            mb = subprocess.run([os.path.join(ROOT, "tools", "microbench")], capture_output=True, text=True, timeout=60)
+            popc_peak = float(json.loads(mb.stdout.strip().splitlines()[-1])["popc_gcmp_s"])
+            popc_src = "tools/microbench run live"
+        except Exception:
+            pass
+        gcmp = MQ * NT * world / (knn_ms * 1e-3) / 1e9
+        hamming = {"metric": "Hamming Gcmp/s (brute-force kNN-2, 256-bit rows)", "value": gcmp, "unit": "Gcmp/s",
+                   "queries_per_gpu": MQ, "train": NT, "ms": knn_ms,
+                   "roofline": {"bound": "int-popc", "achieved": gcmp / world, "peak": popc_peak, "unit": "Gcmp/s per GPU",
+                                "frac": gcmp / world / popc_peak, "peak_source": popc_src}}
         line = {
             "metric": METRIC, "value": total_frames / (dev_ms * 1e-3), "unit": "frames/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": "configs[1]: monocular stream, 1024 synthetic 640x480 frames per GPU, "
-                                   "ORBextractor(1000,1.2,8,20,7) on every frame",
+                                   "ORBextractor(1000,1.2,8,20,7) on every frame + SearchForInitialization"
+                                   "(window 100, ratio 0.9) between consecutive frames",
                        "frames_per_step_per_gpu": B, "l2": "inputs_larger_than_l2 (315 MB of frames per step)",
-                       "mean_keypoints_per_frame": mean_kp},
+                       "mean_keypoints_per_frame": mean_kp, "mean_init_matches_per_pair": mean_matches},
             "e2e": {"value": total_frames / (e2e_ms * 1e-3), "unit": "frames/s",
                     "h2d_bytes_per_step": int(frames.nbytes),
-                    "d2h_bytes_per_step": int(out[0].nbytes + out[1].nbytes + out[2].nbytes)},
+                    "d2h_bytes_per_step": int(out[0].nbytes + out[1].nbytes + out[2].nbytes
+                                              + h_m12.numel() * 4 + h_nm.numel() * 4)},
+            "hamming": hamming,
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",

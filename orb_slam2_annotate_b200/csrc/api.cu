@@ -34,6 +34,9 @@ struct orbfe_extractor {
     std::vector<int> per_level;
     int umax[16];
     cudaStream_t stream = nullptr;
+    // host-batch pipeline: H2D of chunk c+1 and D2H of chunk c-1 overlap the kernels of chunk c
+    cudaStream_t h2dStream = nullptr, d2hStream = nullptr;
+    std::vector<cudaEvent_t> evUp, evDone;
     // geometry of the current image size / batch capacity
     int geomW = 0, geomH = 0, geomBatchCap = 0;
     FrameSetGeom g;
@@ -240,9 +243,12 @@ static int ensure_geometry(orbfe_extractor* e, int w, int h, int batch) {
 }
 
 // the kernel schedule of operator() on the handle's stream; level 0 is already in d.pyr
-static int enqueue_extract(orbfe_extractor* e) {
+static int enqueue_extract(orbfe_extractor* e, int frame0 = 0, int count = -1) {
     int launches = 0;
-    const bool prof = e->profiling;
+    const bool prof = e->profiling && frame0 == 0;
+    const int fullBatch = e->g.batch;
+    e->g.frame0 = frame0;
+    if (count >= 0) e->g.batch = count;
     if (prof) cudaEventRecord(e->ev[1], e->stream);
     launches += launch_pyramid(e->g, e->d, e->stream);
     if (prof) cudaEventRecord(e->ev[2], e->stream);
@@ -254,7 +260,9 @@ static int enqueue_extract(orbfe_extractor* e) {
     if (prof) cudaEventRecord(e->ev[5], e->stream);
     launches += launch_orient_desc(e->g, e->d, e->umax_d.p, e->stream);
     if (prof) cudaEventRecord(e->ev[6], e->stream);
-    e->lastLaunches = launches;
+    e->g.frame0 = 0;
+    e->g.batch = fullBatch;
+    e->lastLaunches = frame0 == 0 ? launches : e->lastLaunches + launches;
     CU(cudaGetLastError());
     return 0;
 }
@@ -331,6 +339,10 @@ void orbfe_extractor_destroy(orbfe_extractor* e) {
     if (!e) return;
     cudaSetDevice(e->device);
     if (e->stream) { cudaStreamSynchronize(e->stream); cudaStreamDestroy(e->stream); }
+    if (e->h2dStream) cudaStreamDestroy(e->h2dStream);
+    if (e->d2hStream) cudaStreamDestroy(e->d2hStream);
+    for (auto ev : e->evUp) cudaEventDestroy(ev);
+    for (auto ev : e->evDone) cudaEventDestroy(ev);
     for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);
     e->pyr.release(); e->blur.release(); e->desc.release(); e->cellc.release(); e->selc.release();
     e->counts.release(); e->umax_d.release(); e->cellk.release(); e->sel.release();
@@ -423,6 +435,60 @@ int orbfe_extractor_fetch(orbfe_extractor* e, int batch, orbfe_keypoint* kps, ui
     return ORBFE_OK;
 }
 
+// Chunked pipeline for large host batches: three streams, chunk c's kernels overlap the upload of
+// chunk c+1 and the download of chunk c-1.
+static int extract_batch_pipelined(orbfe_extractor* e, const uint8_t* imgs, int batch, int w, int h,
+                                   ptrdiff_t stride, ptrdiff_t frame_stride, orbfe_keypoint* kps,
+                                   uint8_t* desc, int cap, int* counts, int chunk) {
+    const int nchunks = (batch + chunk - 1) / chunk;
+    if (!e->h2dStream) {
+        CU(cudaStreamCreateWithFlags(&e->h2dStream, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&e->d2hStream, cudaStreamNonBlocking));
+    }
+    while ((int)e->evUp.size() < nchunks) {
+        cudaEvent_t a, b;
+        CU(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
+        e->evUp.push_back(a); e->evDone.push_back(b);
+    }
+    const LevelGeom& L0 = e->g.lv[0];
+    const int oc = e->g.outCap;
+    const size_t kb = sizeof(orbfe_keypoint);
+    // everything queued before this call on the main stream must finish before buffers are reused
+    CU(cudaEventRecord(e->evDone[0], e->stream));
+    CU(cudaStreamWaitEvent(e->h2dStream, e->evDone[0], 0));
+    for (int c = 0; c < nchunks; c++) {
+        const int f0 = c * chunk, n = std::min(chunk, batch - f0);
+        uint8_t* dst = e->d.pyr + L0.pyrOff + (long long)f0 * L0.lvBytes;
+        const uint8_t* src = imgs + (long long)f0 * frame_stride;
+        if (frame_stride == (ptrdiff_t)h * stride) {
+            CU(cudaMemcpy2DAsync(dst, L0.pitch, src, stride, w, (size_t)h * n, cudaMemcpyHostToDevice, e->h2dStream));
+        } else {
+            for (int b = 0; b < n; b++)
+                CU(cudaMemcpy2DAsync(dst + (long long)b * L0.lvBytes, L0.pitch, src + b * frame_stride, stride, w, h,
+                                     cudaMemcpyHostToDevice, e->h2dStream));
+        }
+        CU(cudaEventRecord(e->evUp[c], e->h2dStream));
+        CU(cudaStreamWaitEvent(e->stream, e->evUp[c], 0));
+        int rc = enqueue_extract(e, f0, n);
+        if (rc) return rc;
+        CU(cudaEventRecord(e->evDone[c], e->stream));
+        CU(cudaStreamWaitEvent(e->d2hStream, e->evDone[c], 0));
+        const int rowk = std::min(cap, oc);
+        CU(cudaMemcpyAsync(counts + f0, e->d.counts + f0, sizeof(int) * n, cudaMemcpyDeviceToHost, e->d2hStream));
+        CU(cudaMemcpy2DAsync(kps + (size_t)f0 * cap, (size_t)cap * kb, e->d.kps + (size_t)f0 * oc, (size_t)oc * kb,
+                             (size_t)rowk * kb, n, cudaMemcpyDeviceToHost, e->d2hStream));
+        CU(cudaMemcpy2DAsync(desc + (size_t)f0 * cap * 32, (size_t)cap * 32, e->d.desc + (size_t)f0 * oc * 32,
+                             (size_t)oc * 32, (size_t)rowk * 32, n, cudaMemcpyDeviceToHost, e->d2hStream));
+    }
+    CU(cudaStreamSynchronize(e->d2hStream));
+    CU(cudaStreamSynchronize(e->stream));
+    if (cap < oc)
+        for (int b = 0; b < batch; b++)
+            if (counts[b] > cap) return fail(ORBFE_ERR_CAPACITY, "keypoint capacity too small (see orbfe_extractor_max_keypoints)");
+    return ORBFE_OK;
+}
+
 int orbfe_extract_batch(orbfe_extractor* e, const uint8_t* imgs, int batch, int width, int height,
                         ptrdiff_t stride, ptrdiff_t frame_stride, orbfe_keypoint* kps,
                         uint8_t* desc, int cap, int* counts) {
@@ -432,6 +498,11 @@ int orbfe_extract_batch(orbfe_extractor* e, const uint8_t* imgs, int batch, int 
     CU(cudaSetDevice(e->device));
     int rc = ensure_geometry(e, width, height, batch);
     if (rc) return rc;
+    const int chunk = 64;
+    if (batch >= 4 * chunk) {
+        e->lastBatch = batch;
+        return extract_batch_pipelined(e, imgs, batch, width, height, stride, frame_stride, kps, desc, cap, counts, chunk);
+    }
     if ((rc = upload_level0(e, imgs, batch, width, height, stride, frame_stride, cudaMemcpyHostToDevice))) return rc;
     e->lastBatch = batch;
     if ((rc = enqueue_extract(e))) return rc;

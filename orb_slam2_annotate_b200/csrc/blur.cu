@@ -138,7 +138,7 @@ blur_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ Blur
     const int band = active ? task / nwc : 0;
     const int wc = active ? task - band * nwc : 0;
     const int x = wc * 4, y0 = band * RH;
-    const long long off = L.pyrOff + (long long)blockIdx.y * L.lvBytes;
+    const long long off = L.pyrOff + (long long)(blockIdx.y + g.frame0) * L.lvBytes;
     const bool edge = x < 4 || x + 8 > L.w;
     if (L.w < 8) {
         if (active) blur_tiny(pyr + off, blur + off, L.pitch, L.w, L.h, x, y0);

@@ -84,7 +84,7 @@ fast_cells_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __restr
     __shared__ int warp_cnt[kThreads / 32];
     __shared__ int s_total;
 
-    const int cell = blockIdx.x, frame = blockIdx.y;
+    const int cell = blockIdx.x, frame = blockIdx.y + g.frame0;
     int l = 0;
     while (l + 1 < g.nlevels && cell >= g.lv[l + 1].cellBase) l++;
     const LevelGeom& L = g.lv[l];
@@ -198,7 +198,7 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __
     __shared__ WarpSmem smem[kWarpsPerCta];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     WarpSmem& S = smem[wid];
-    const int frame = blockIdx.y, cell = blockIdx.x * kWarpsPerCta + wid;
+    const int frame = blockIdx.y + g.frame0, cell = blockIdx.x * kWarpsPerCta + wid;
     if (cell >= g.ncells) return;
     int l = 0;
     while (l + 1 < g.nlevels && cell >= g.lv[l + 1].cellBase) l++;

@@ -124,10 +124,64 @@ __device__ void three_maxima(const int* hist, int& ind1, int& ind2, int& ind3) {
 // ---------------------------------------------------------------------------------------
 // SearchForInitialization — one warp per frame pair.
 
-__global__ void __launch_bounds__(32)
+constexpr int SI_WARPS = 8;      // warps per frame pair
+constexpr int SI_QB = 256;       // queries per phase-A / phase-B block
+constexpr int SI_K = 8;          // candidates kept per query by the parallel phase
+constexpr int SI_CL = 512;       // per-warp candidate list capacity (longer windows take the direct path)
+
+// Candidates of one query in GetFeaturesInArea order, evaluated across the lanes of a warp.
+// WITH_FILTER applies the reference's running skip rule vMatchedDistance[i2] <= dist (:515-516);
+// without it the caller receives the SI_K smallest (dist, traversal rank) keys instead.
+struct QueryCtx {
+    const orbfe_keypoint* kp2; const uint8_t* d2; const int* cell_end; const unsigned short* items;
+    const unsigned char* mdist; GridGeom grid; float r;
+};
+
+__device__ __forceinline__ bool cand_ok(const QueryCtx& c, int i2, float qx, float qy) {
+    const orbfe_keypoint k2 = c.kp2[i2];
+    if (k2.octave != 0) return false;                     // minLevel = maxLevel = 0 (:494, Frame.cc:381-395)
+    return fabsf(__fsub_rn(k2.x, qx)) < c.r && fabsf(__fsub_rn(k2.y, qy)) < c.r;
+}
+
+// sequential-rule evaluation of one query by one warp: best / second-best key, best index
+__device__ void eval_query_filtered(const QueryCtx& c, const uint32_t q[8], float qx, float qy, uint32_t& g1,
+                                    uint32_t& g2, int& best) {
+    const int lane = threadIdx.x & 31;
+    uint32_t b1 = KEY_INF, b2 = KEY_INF;
+    int bi = -1, seq = 0;
+    int cx0, cx1, cy0, cy1;
+    g1 = g2 = KEY_INF; best = -1;
+    if (!cell_window(c.grid, qx, qy, c.r, cx0, cx1, cy0, cy1)) return;
+    for (int ix = cx0; ix <= cx1; ix++) {
+        const int c0 = ix * GR + cy0;
+        const int s = c0 ? c.cell_end[c0 - 1] : 0, e = c.cell_end[ix * GR + cy1];
+        for (int j = s + lane; j < e; j += 32) {
+            const int i2 = c.items[j];
+            if (!cand_ok(c, i2, qx, qy)) continue;
+            const int dist = hamming256(q, c.d2 + 32 * (long long)i2);
+            if (c.mdist[i2] != 255 && (int)c.mdist[i2] <= dist) continue;           // :515-516
+            const uint32_t key = ((uint32_t)dist << 20) | (uint32_t)(seq + j - s);
+            if (key < b1) { b2 = b1; b1 = key; bi = i2; }                           // :518-527
+            else if (key < b2) b2 = key;
+        }
+        seq += e - s;
+    }
+    g1 = warp_min(b1);
+    if (g1 == KEY_INF) return;
+    const unsigned own = __ballot_sync(FULL, b1 == g1);
+    best = __shfl_sync(FULL, bi, __ffs(own) - 1);
+    g2 = warp_min(b1 == g1 ? b2 : b1);
+}
+
+__global__ void __launch_bounds__(SI_WARPS * 32)
 search_init_kernel(const __grid_constant__ InitArgs a) {
     extern __shared__ __align__(16) unsigned char sm[];
-    const int lane = threadIdx.x, p = blockIdx.x;
+    __shared__ uint32_t tk_key[SI_QB][SI_K];
+    __shared__ unsigned short tk_idx[SI_QB][SI_K];
+    __shared__ unsigned short tk_total[SI_QB];      // candidates passing the static tests (saturated)
+    __shared__ unsigned short clist[SI_WARPS][SI_CL];
+    __shared__ int s_nq;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, p = blockIdx.x;
     const int fa = a.pairs ? a.pairs[p].x : p, fb = a.pairs ? a.pairs[p].y : p + 1;
     const int n1 = a.counts[fa], n2 = a.counts[fb];
     const orbfe_keypoint* kp1 = a.kps + (long long)fa * a.cap;
@@ -141,91 +195,191 @@ search_init_kernel(const __grid_constant__ InitArgs a) {
     int* hist = cell_end + NCELL;                                // 32
     unsigned short* items = (unsigned short*)(hist + 32);        // cap
     unsigned short* m21 = items + a.cap;                         // cap   (0xFFFF = none)
-    unsigned char* mdist = (unsigned char*)(m21 + a.cap);        // cap   (255 = INT_MAX)
+    unsigned short* qlist = m21 + a.cap;                         // cap   octave-0 queries of F1, in order
+    unsigned char* mdist = (unsigned char*)(qlist + a.cap);      // cap   (255 = INT_MAX)
     unsigned char* binof = mdist + a.cap;                        // cap   (255 = not in rotHist)
 
-    for (int i = lane; i < n1; i += 32) { m12[i] = -1; binof[i] = 255; }
-    for (int i = lane; i < n2; i += 32) { m21[i] = 0xFFFF; mdist[i] = 255; }
-    hist[lane] = 0;
-    warp_build_grid(a.grid, kp2, n2, cell_end, items);
-    __syncwarp();
-
-    int nm = 0;
-    const float r = (float)a.window;
-    const float factor = 1.0f / HISTO;                                                  // :476
-    for (int i1 = 0; i1 < n1; i1++) {
-        const orbfe_keypoint k1 = kp1[i1];
-        if (k1.octave > 0) continue;                                                    // :487-489
-        const float qx = prev ? prev[2 * i1] : k1.x, qy = prev ? prev[2 * i1 + 1] : k1.y;
-        int cx0, cx1, cy0, cy1;
-        if (!cell_window(a.grid, qx, qy, r, cx0, cx1, cy0, cy1)) continue;
-        uint32_t q[8];
-        load_row(q, d1 + 32 * (long long)i1);
-        uint32_t b1 = KEY_INF, b2 = KEY_INF;
-        int bi = -1, seq = 0;
-        for (int ix = cx0; ix <= cx1; ix++) {
-            const int c0 = ix * GR + cy0;
-            const int s = c0 ? cell_end[c0 - 1] : 0, e = cell_end[ix * GR + cy1];
-            for (int j = s + lane; j < e; j += 32) {
-                const int i2 = items[j];
-                const orbfe_keypoint k2 = kp2[i2];
-                if (k2.octave != 0) continue;                 // minLevel = maxLevel = 0 (:494, Frame.cc:381-395)
-                if (!(fabsf(__fsub_rn(k2.x, qx)) < r && fabsf(__fsub_rn(k2.y, qy)) < r)) continue;
-                const int dist = hamming256(q, d2 + 32 * (long long)i2);
-                if (mdist[i2] != 255 && (int)mdist[i2] <= dist) continue;           // :515-516
-                const uint32_t key = ((uint32_t)dist << 20) | (uint32_t)(seq + j - s);
-                if (key < b1) { b2 = b1; b1 = key; bi = i2; }                           // :518-527
-                else if (key < b2) b2 = key;
-            }
-            seq += e - s;
+    for (int i = tid; i < n1; i += SI_WARPS * 32) { m12[i] = -1; binof[i] = 255; }
+    for (int i = tid; i < n2; i += SI_WARPS * 32) { m21[i] = 0xFFFF; mdist[i] = 255; }
+    if (tid < 32) hist[tid] = 0;
+    if (wid == 0) {
+        warp_build_grid(a.grid, kp2, n2, cell_end, items);
+        // queries: keypoints of F1 on octave 0, reference order (:483-489)
+        int nq = 0;
+        for (int base = 0; base < n1; base += 32) {
+            const int i = base + lane;
+            const bool ok = i < n1 && kp1[i].octave <= 0;
+            const unsigned b = __ballot_sync(FULL, ok);
+            if (ok) qlist[nq + __popc(b & ((1u << lane) - 1u))] = (unsigned short)i;
+            nq += __popc(b);
         }
-        const uint32_t g1 = warp_min(b1);
-        if (g1 == KEY_INF) continue;
-        const unsigned own = __ballot_sync(FULL, b1 == g1);
-        const int best = __shfl_sync(FULL, bi, __ffs(own) - 1);
-        const uint32_t g2 = warp_min(b1 == g1 ? b2 : b1);
-        const int bestDist = (int)(g1 >> 20);
-        const float second = g2 == KEY_INF ? (float)INT_MAX : (float)(int)(g2 >> 20);
-        if (bestDist <= TH_LOW && (float)bestDist < __fmul_rn(second, a.ratio)) {       // :532-534
-            if (lane == 0) {
-                if (m21[best] != 0xFFFF) m12[m21[best]] = -1;                           // :536-540
-                m12[i1] = best;
-                m21[best] = (unsigned short)i1;
-                mdist[best] = (unsigned char)bestDist;
-                if (a.checkOri) {                                                       // :549-559
-                    float rot = __fsub_rn(k1.angle, kp2[best].angle);
-                    if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
-                    int bin = (int)roundf(__fmul_rn(rot, factor));
-                    if (bin == HISTO) bin = 0;
-                    binof[i1] = (unsigned char)bin;
-                    hist[bin]++;
+        if (lane == 0) s_nq = nq;
+    }
+    __syncthreads();
+    const int nq = s_nq;
+    QueryCtx c{kp2, d2, cell_end, items, mdist, a.grid, (float)a.window};
+    const float factor = 1.0f / HISTO;                                                  // :476
+
+    for (int qb = 0; qb < nq; qb += SI_QB) {
+        const int qn = min(SI_QB, nq - qb);
+        // ---- phase A (all warps): the SI_K best candidates of every query, no running filter
+        for (int qi = wid; qi < qn; qi += SI_WARPS) {
+            const int i1 = qlist[qb + qi];
+            const float qx = prev ? prev[2 * i1] : kp1[i1].x, qy = prev ? prev[2 * i1 + 1] : kp1[i1].y;
+            int cx0, cx1, cy0, cy1, total = 0;
+            bool direct = false;
+            if (cell_window(a.grid, qx, qy, c.r, cx0, cx1, cy0, cy1)) {
+                // item range of every grid column of the window (one lane per column), then the
+                // ranges are concatenated into the warp's candidate list in column order
+                for (int cb = cx0; cb <= cx1 && !direct; cb += 32) {
+                    const int ix = cb + lane;
+                    int s = 0, len = 0;
+                    if (ix <= cx1) {
+                        const int c0 = ix * GR + cy0;
+                        s = c0 ? cell_end[c0 - 1] : 0;
+                        len = cell_end[ix * GR + cy1] - s;
+                    }
+                    int inc = len;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const int u = __shfl_up_sync(FULL, inc, o);
+                        if (lane >= o) inc += u;
+                    }
+                    const int sum = __shfl_sync(FULL, inc, 31);
+                    if (total + sum > SI_CL) { direct = true; break; }
+                    const int off = total + inc - len;
+                    for (int j = 0; j < len; j++) clist[wid][off + j] = items[s + j];
+                    total += sum;
                 }
             }
             __syncwarp();
-        }
-    }
-    __syncwarp();
-    if (a.checkOri) {                                                                   // :566-590
-        int ind1, ind2, ind3;
-        three_maxima(hist, ind1, ind2, ind3);
-        for (int i = lane; i < n1; i += 32) {
-            const int b = binof[i];
-            if (b != 255 && b != ind1 && b != ind2 && b != ind3 && m12[i] >= 0) m12[i] = -1;
-        }
-        __syncwarp();
-    }
-    for (int i = lane; i < n1; i += 32) {                                               // :595-597
-        const int m = m12[i];
-        if (m >= 0) {
-            nm++;
-            if (prev) { prev[2 * i] = kp2[m].x; prev[2 * i + 1] = kp2[m].y; }
-        }
-    }
+            uint32_t keys[SI_CL / 32];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) nm += __shfl_xor_sync(FULL, nm, o);
-    if (lane == 0) a.nmatches[p] = nm;
+            for (int k = 0; k < SI_CL / 32; k++) keys[k] = KEY_INF;
+            int npass = 0;
+            if (!direct) {
+                uint32_t q[8];
+                load_row(q, d1 + 32 * (long long)i1);
+#pragma unroll
+                for (int k = 0; k < SI_CL / 32; k++) {
+                    if (32 * k >= total) break;
+                    const int j = lane + 32 * k;
+                    if (j < total) {
+                        const int i2 = clist[wid][j];
+                        if (cand_ok(c, i2, qx, qy)) {
+                            keys[k] = ((uint32_t)hamming256(q, d2 + 32 * (long long)i2) << 20) | (uint32_t)j;
+                            npass++;
+                        }
+                    }
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) npass += __shfl_xor_sync(FULL, npass, o);
+                // extract the SI_K smallest keys of the warp, in order: warp minimum of the lane
+                // minima; only the owning lane rescans its keys
+                uint32_t lm = KEY_INF;
+#pragma unroll
+                for (int k = 0; k < SI_CL / 32; k++) lm = min(lm, keys[k]);
+                for (int t = 0; t < SI_K; t++) {
+                    const uint32_t gm = warp_min(lm);
+                    if (lane == 0) {
+                        tk_key[qi][t] = gm;
+                        tk_idx[qi][t] = gm == KEY_INF ? 0 : clist[wid][gm & 0xFFFFFu];
+                    }
+                    if (gm == KEY_INF) {
+                        if (lane == 0) for (int tt = t + 1; tt < SI_K; tt++) tk_key[qi][tt] = KEY_INF;
+                        break;
+                    }
+                    if (lm == gm) {
+                        lm = KEY_INF;
+#pragma unroll
+                        for (int k = 0; k < SI_CL / 32; k++) {
+                            if (keys[k] == gm) keys[k] = KEY_INF;
+                            lm = min(lm, keys[k]);
+                        }
+                    }
+                }
+            }
+            if (lane == 0) tk_total[qi] = direct ? 0xFFFF : (unsigned short)npass;
+            __syncwarp();
+        }
+        __syncthreads();
+        // ---- phase B (warp 0): the reference's greedy bookkeeping, queries in order
+        if (wid == 0) {
+            for (int qi = 0; qi < qn; qi++) {
+                const int i1 = qlist[qb + qi];
+                const int total = tk_total[qi];
+                uint32_t g1, g2;
+                int best;
+                bool need_full = total == 0xFFFF;
+                if (!need_full) {
+                    uint32_t key = KEY_INF;
+                    int idx = 0;
+                    if (lane < SI_K) { key = tk_key[qi][lane]; idx = tk_idx[qi][lane]; }
+                    const bool alive = key != KEY_INF && !(mdist[idx] != 255 && (int)mdist[idx] <= (int)(key >> 20));
+                    unsigned m = __ballot_sync(FULL, alive);
+                    const int l1 = __ffs(m) - 1;
+                    g1 = l1 >= 0 ? __shfl_sync(FULL, key, l1) : KEY_INF;
+                    best = l1 >= 0 ? __shfl_sync(FULL, idx, l1) : -1;
+                    if (l1 >= 0) m &= m - 1;
+                    const int l2 = __ffs(m) - 1;
+                    g2 = l2 >= 0 ? __shfl_sync(FULL, key, l2) : KEY_INF;
+                    // the kept list may hide further candidates: only matters when a match is still possible
+                    if (total > SI_K && (l1 < 0 || ((int)(g1 >> 20) <= TH_LOW && l2 < 0))) need_full = true;
+                }
+                if (need_full) {
+                    const float qx = prev ? prev[2 * i1] : kp1[i1].x, qy = prev ? prev[2 * i1 + 1] : kp1[i1].y;
+                    uint32_t q[8];
+                    load_row(q, d1 + 32 * (long long)i1);
+                    eval_query_filtered(c, q, qx, qy, g1, g2, best);
+                }
+                if (g1 == KEY_INF) continue;
+                const int bestDist = (int)(g1 >> 20);
+                const float second = g2 == KEY_INF ? (float)INT_MAX : (float)(int)(g2 >> 20);
+                if (bestDist <= TH_LOW && (float)bestDist < __fmul_rn(second, a.ratio)) {   // :532-534
+                    if (lane == 0) {
+                        if (m21[best] != 0xFFFF) m12[m21[best]] = -1;                       // :536-540
+                        m12[i1] = best;
+                        m21[best] = (unsigned short)i1;
+                        mdist[best] = (unsigned char)bestDist;
+                        if (a.checkOri) {                                                   // :549-559
+                            float rot = __fsub_rn(kp1[i1].angle, kp2[best].angle);
+                            if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+                            int bin = (int)roundf(__fmul_rn(rot, factor));
+                            if (bin == HISTO) bin = 0;
+                            binof[i1] = (unsigned char)bin;
+                            hist[bin]++;
+                        }
+                    }
+                    __syncwarp();
+                }
+            }
+        }
+        __syncthreads();
+    }
+    // the update of vbPrevMatched reads kp2 only; prev of later query blocks was read before any write
+    if (wid == 0) {
+        int nm = 0;
+        if (a.checkOri) {                                                               // :566-590
+            int ind1, ind2, ind3;
+            three_maxima(hist, ind1, ind2, ind3);
+            for (int i = lane; i < n1; i += 32) {
+                const int b = binof[i];
+                if (b != 255 && b != ind1 && b != ind2 && b != ind3 && m12[i] >= 0) m12[i] = -1;
+            }
+            __syncwarp();
+        }
+        for (int i = lane; i < n1; i += 32) {                                           // :595-597
+            const int m = m12[i];
+            if (m >= 0) {
+                nm++;
+                if (prev) { prev[2 * i] = kp2[m].x; prev[2 * i + 1] = kp2[m].y; }
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) nm += __shfl_xor_sync(FULL, nm, o);
+        if (lane == 0) a.nmatches[p] = nm;
+    }
 }
-
 
 // ---------------------------------------------------------------------------------------
 // SearchByProjection(Frame&, vector<MapPoint*>&, th)
@@ -491,14 +645,14 @@ __global__ void __launch_bounds__(256) stereo_median_kernel(const __grid_constan
 
 }  // namespace
 
-size_t search_init_smem(int cap) { return (size_t)(NCELL + 32) * 4 + (size_t)cap * 6 + 16; }
+size_t search_init_smem(int cap) { return (size_t)(NCELL + 32) * 4 + (size_t)cap * 8 + 16; }
 
 int launch_search_init(const InitArgs& a, int npairs, cudaStream_t st) {
     if (npairs <= 0) return 0;
     const size_t smem = search_init_smem(a.cap);
-    if (smem > 48 * 1024)
+    if (smem > 24 * 1024)
         cudaFuncSetAttribute(search_init_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    search_init_kernel<<<npairs, 32, smem, st>>>(a);
+    search_init_kernel<<<npairs, SI_WARPS * 32, smem, st>>>(a);
     return 1;
 }
 

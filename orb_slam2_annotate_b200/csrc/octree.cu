@@ -101,7 +101,7 @@ octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ De
     __shared__ int wsum[QT / 32 + 1];
     __shared__ int s_n, s_cut, s_nexp;
 
-    const int l = blockIdx.x, frame = blockIdx.y;
+    const int l = blockIdx.x, frame = blockIdx.y + g.frame0;
     const LevelGeom& L = g.lv[l];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int N = L.nFeat;

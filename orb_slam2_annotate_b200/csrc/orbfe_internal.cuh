@@ -48,6 +48,7 @@ struct LevelGeom {
 
 struct FrameSetGeom {
     int nlevels, batch;
+    int frame0;                 // first frame this launch processes (chunked pipelining)
     int ncells;                 // cells per frame (all levels)
     int selTotal;               // survivor slots per frame (all levels)
     int outCap;                 // result slots per frame

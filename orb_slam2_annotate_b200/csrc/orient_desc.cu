@@ -52,7 +52,7 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 __global__ void __launch_bounds__(256)
 orient_desc_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ DevBufs d,
                    const int* __restrict__ umax) {
-    const int frame = blockIdx.y;
+    const int frame = blockIdx.y + g.frame0;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int kpi = blockIdx.x * 8 + wid;
     const int* selc = d.selc + (long long)frame * g.nlevels;

@@ -79,7 +79,8 @@ int launch_pyramid(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
         const LevelGeom& L = g.lv[l];
         dim3 block(128);
         dim3 grid((L.w + 511) / 512, (L.h + PR - 1) / PR, g.batch);
-        resize_level_kernel<<<grid, block, 0, s>>>(d.pyr + P.pyrOff, d.pyr + L.pyrOff,
+        resize_level_kernel<<<grid, block, 0, s>>>(d.pyr + P.pyrOff + (long long)g.frame0 * P.lvBytes,
+                                                   d.pyr + L.pyrOff + (long long)g.frame0 * L.lvBytes,
                                                    P.lvBytes, L.lvBytes, P.pitch, L.pitch, L.w, L.h,
                                                    d.xtab[l], d.ytab[l]);
         launches++;

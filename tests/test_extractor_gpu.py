@@ -118,3 +118,21 @@ def test_reference_tu_agrees(orbfe, oracle):
     kr, dr = oracle.RefExtractor(1000)(img)
     kg, dg = orbfe.ORBextractor(1000)(img)
     _compare_frame(kg, dg, kr, dr)
+
+
+def test_pipelined_host_batch(orbfe, oracle):
+    """Host batches of >= 256 frames take the chunked three-stream path (H2D / kernels / D2H overlap)."""
+    distinct = np.stack([synth.frame(320, 240, 20 + s) for s in range(5)])
+    B = 261
+    imgs = np.ascontiguousarray(distinct[np.arange(B) % 5])
+    ex = orbfe.ORBextractor(500)
+    kps, desc, counts = ex.extract_batch(imgs)
+    ref = [oracle.OracleExtractor(500)(distinct[s]) for s in range(5)]
+    for b in (0, 1, 63, 64, 127, 128, 255, 256, 260):
+        ko, do = ref[b % 5]
+        n = counts[b]
+        _compare_frame(kps[b, :n], desc[b, :n], ko, do)
+        assert (desc[b, :n] == do).all()
+    for b in range(5, B):
+        assert counts[b] == counts[b % 5]
+        assert kps[b, :counts[b]].tobytes() == kps[b % 5, :counts[b]].tobytes()
