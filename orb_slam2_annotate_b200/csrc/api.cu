@@ -36,6 +36,9 @@ struct orbfe_extractor {
     cudaStream_t stream = nullptr;
     // host-batch pipeline: H2D of chunk c+1 and D2H of chunk c-1 overlap the kernels of chunk c
     cudaStream_t h2dStream = nullptr, d2hStream = nullptr;
+    // the Gaussian blur only depends on the pyramid: it runs on a side stream beside FAST + quadtree
+    cudaStream_t sideStream = nullptr;
+    cudaEvent_t evPyr = nullptr, evBlur = nullptr;
     std::vector<cudaEvent_t> evUp, evDone;
     // geometry of the current image size / batch capacity
     int geomW = 0, geomH = 0, geomBatchCap = 0;
@@ -252,12 +255,23 @@ static int enqueue_extract(orbfe_extractor* e, int frame0 = 0, int count = -1) {
     if (prof) cudaEventRecord(e->ev[1], e->stream);
     launches += launch_pyramid(e->g, e->d, e->stream);
     if (prof) cudaEventRecord(e->ev[2], e->stream);
-    launches += launch_fast(e->g, e->d, e->stream);
-    if (prof) cudaEventRecord(e->ev[3], e->stream);
-    launches += launch_blur(e->g, e->d, e->stream);
-    if (prof) cudaEventRecord(e->ev[4], e->stream);
-    launches += launch_octree(e->g, e->d, e->stream);
-    if (prof) cudaEventRecord(e->ev[5], e->stream);
+    if (prof) {
+        // profiling mode serialises the stages so that each one can be timed alone
+        launches += launch_fast(e->g, e->d, e->stream);
+        cudaEventRecord(e->ev[3], e->stream);
+        launches += launch_blur(e->g, e->d, e->stream);
+        cudaEventRecord(e->ev[4], e->stream);
+        launches += launch_octree(e->g, e->d, e->stream);
+        cudaEventRecord(e->ev[5], e->stream);
+    } else {
+        CU(cudaEventRecord(e->evPyr, e->stream));
+        CU(cudaStreamWaitEvent(e->sideStream, e->evPyr, 0));
+        launches += launch_blur(e->g, e->d, e->sideStream);
+        CU(cudaEventRecord(e->evBlur, e->sideStream));
+        launches += launch_fast(e->g, e->d, e->stream);
+        launches += launch_octree(e->g, e->d, e->stream);
+        CU(cudaStreamWaitEvent(e->stream, e->evBlur, 0));
+    }
     launches += launch_orient_desc(e->g, e->d, e->umax_d.p, e->stream);
     if (prof) cudaEventRecord(e->ev[6], e->stream);
     e->g.frame0 = 0;
@@ -322,7 +336,10 @@ int orbfe_extractor_create(int nfeatures, float scale_factor, int nlevels, int i
     if (!umax_symmetric(e->umax)) { delete e; return fail(ORBFE_ERR_ARG, "internal: circular patch table is not symmetric"); }
     cudaError_t ce = cudaSetDevice(device);
     if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
-    if (ce != cudaSuccess) { delete e; return fail(ORBFE_ERR_CUDA, "cudaStreamCreate", ce); }
+    if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&e->sideStream, cudaStreamNonBlocking);
+    if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->evPyr, cudaEventDisableTiming);
+    if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&e->evBlur, cudaEventDisableTiming);
+    if (ce != cudaSuccess) { orbfe_extractor_destroy(e); return fail(ORBFE_ERR_CUDA, "cudaStreamCreate", ce); }
     int rc = e->umax_d.ensure(16);
     if (!rc) {
         ce = cudaMemcpy(e->umax_d.p, e->umax, sizeof(e->umax), cudaMemcpyHostToDevice);
@@ -339,6 +356,9 @@ void orbfe_extractor_destroy(orbfe_extractor* e) {
     if (!e) return;
     cudaSetDevice(e->device);
     if (e->stream) { cudaStreamSynchronize(e->stream); cudaStreamDestroy(e->stream); }
+    if (e->sideStream) { cudaStreamSynchronize(e->sideStream); cudaStreamDestroy(e->sideStream); }
+    if (e->evPyr) cudaEventDestroy(e->evPyr);
+    if (e->evBlur) cudaEventDestroy(e->evBlur);
     if (e->h2dStream) cudaStreamDestroy(e->h2dStream);
     if (e->d2hStream) cudaStreamDestroy(e->d2hStream);
     for (auto ev : e->evUp) cudaEventDestroy(ev);

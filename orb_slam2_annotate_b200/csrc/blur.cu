@@ -72,38 +72,42 @@ __device__ __forceinline__ void load3(const uint8_t* row, int x, const WordSrc* 
     }
 }
 
-// one thread: word column x (4 pixels), output rows [y0, y0 + RH)
-template <bool EDGE>
+// one thread: word column x (4 pixels), output rows [y0, y0 + RH).  INSIDE: the band and its 3-row
+// halo lie inside the image, so rows advance by pointer increments and nothing is reflected.
+template <bool EDGE, bool INSIDE>
 __device__ __forceinline__ void blur_column(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
                                             int pitch, int w, int h, int x, int y0, const WordSrc* ws) {
     uint32_t hb[7][4];
-    const bool rows_inside = y0 >= 3 && y0 + RH + 3 <= h;
+    const uint8_t* rp = src + (long long)(y0 - 3) * pitch;     // only dereferenced when INSIDE
 #pragma unroll
     for (int i = 0; i < 6; i++) {
-        const int ry = rows_inside ? y0 + i - 3 : reflect101(y0 + i - 3, h);
+        const uint8_t* row = INSIDE ? rp : src + (long long)reflect101(y0 + i - 3, h) * pitch;
         uint32_t w0, w1, w2;
-        load3<EDGE>(src + (long long)ry * pitch, x, ws, w0, w1, w2);
+        load3<EDGE>(row, x, ws, w0, w1, w2);
         hfilter(w0, w1, w2, hb[i]);
+        rp += pitch;
     }
+    uint8_t* op = dst + (long long)y0 * pitch + x;
 #pragma unroll 1
     for (int grp = 0; grp < K7; grp++) {
 #pragma unroll
         for (int j = 0; j < 7; j++) {
             const int y = y0 + grp * 7 + j;                 // output row; newest input row is y + 3
-            const int ry = rows_inside ? y + 3 : reflect101(y + 3, h);
+            const uint8_t* row = INSIDE ? rp : src + (long long)reflect101(y + 3, h) * pitch;
             uint32_t w0, w1, w2;
-            load3<EDGE>(src + (long long)ry * pitch, x, ws, w0, w1, w2);
+            load3<EDGE>(row, x, ws, w0, w1, w2);
             hfilter(w0, w1, w2, hb[(6 + j) % 7]);
+            rp += pitch;
             // rows y-3 .. y+3 sit in slots j, j+1, ..., j+6 (mod 7)
-            uint32_t out = 0;
+            uint32_t acc[4];
 #pragma unroll
-            for (int k = 0; k < 4; k++) {
-                const uint32_t acc = 18u * (hb[j % 7][k] + hb[(j + 6) % 7][k]) +
-                                     34u * (hb[(j + 1) % 7][k] + hb[(j + 5) % 7][k]) +
-                                     48u * (hb[(j + 2) % 7][k] + hb[(j + 4) % 7][k]) + 56u * hb[(j + 3) % 7][k];
-                out |= ((acc + 32768u) >> 16) << (8 * k);
-            }
-            if (y < h) *reinterpret_cast<uint32_t*>(dst + (long long)y * pitch + x) = out;   // pitch % 16 == 0
+            for (int k = 0; k < 4; k++)
+                acc[k] = 18u * (hb[j % 7][k] + hb[(j + 6) % 7][k]) + 34u * (hb[(j + 1) % 7][k] + hb[(j + 5) % 7][k]) +
+                         48u * (hb[(j + 2) % 7][k] + hb[(j + 4) % 7][k]) + (56u * hb[(j + 3) % 7][k] + 32768u);
+            // (acc + 32768) >> 16 is byte 2 of each sum (acc < 2^24): gather the four bytes with PRMTs
+            const uint32_t out = __byte_perm(__byte_perm(acc[0], acc[1], 0x0062), __byte_perm(acc[2], acc[3], 0x0062), 0x5410);
+            if (INSIDE || y < h) *reinterpret_cast<uint32_t*>(op) = out;   // pitch % 16 == 0
+            op += pitch;
         }
     }
 }
@@ -144,16 +148,20 @@ blur_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ Blur
         if (active) blur_tiny(pyr + off, blur + off, L.pitch, L.w, L.h, x, y0);
         return;
     }
-    if (__any_sync(0xFFFFFFFFu, active && edge)) {
-        if (!active) return;
+    const bool inside = y0 >= 3 && y0 + RH + 3 <= L.h;
+    const bool warp_edge = __any_sync(0xFFFFFFFFu, active && edge);
+    const bool warp_inside = __all_sync(0xFFFFFFFFu, !active || inside);
+    if (!active) return;
+    if (warp_edge) {
         WordSrc ws[3];
         const int last_word = (L.w - 1) >> 2;
 #pragma unroll
         for (int j = 0; j < 3; j++) ws[j] = word_source(x + 4 * (j - 1), L.w, last_word);
-        blur_column<true>(pyr + off, blur + off, L.pitch, L.w, L.h, x, y0, ws);
+        if (warp_inside) blur_column<true, true>(pyr + off, blur + off, L.pitch, L.w, L.h, x, y0, ws);
+        else blur_column<true, false>(pyr + off, blur + off, L.pitch, L.w, L.h, x, y0, ws);
     } else {
-        if (!active) return;
-        blur_column<false>(pyr + off, blur + off, L.pitch, L.w, L.h, x, y0, nullptr);
+        if (warp_inside) blur_column<false, true>(pyr + off, blur + off, L.pitch, L.w, L.h, x, y0, nullptr);
+        else blur_column<false, false>(pyr + off, blur + off, L.pitch, L.w, L.h, x, y0, nullptr);
     }
 }
 
