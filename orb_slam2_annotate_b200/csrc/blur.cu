@@ -139,8 +139,22 @@ blur_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ Blur
     const int nwc = (L.w + 3) >> 2, nbands = (L.h + RH - 1) / RH;
     const int task = (blockIdx.x - t.base[l]) * BT + threadIdx.x;
     const bool active = task < nwc * nbands;
-    const int band = active ? task / nwc : 0;
-    const int wc = active ? task - band * nwc : 0;
+    // interior word columns (all three words inside the row) first, band-major, then the few
+    // edge columns: warps are then either all-interior or all-edge (one mixed warp per level)
+    const int cimax = L.w >= 12 ? (L.w - 8) >> 2 : 0;           // interior columns are 1..cimax
+    const int nint = cimax, nedge = nwc - nint;
+    int band = 0, wc = 0;
+    if (active) {
+        if (task < nint * nbands) {
+            band = task / nint;
+            wc = 1 + task - band * nint;
+        } else {
+            const int te = task - nint * nbands;
+            band = te / nedge;
+            const int e = te - band * nedge;
+            wc = e == 0 ? 0 : cimax + e;
+        }
+    }
     const int x = wc * 4, y0 = band * RH;
     const long long off = L.pyrOff + (long long)(blockIdx.y + g.frame0) * L.lvBytes;
     const bool edge = x < 4 || x + 8 > L.w;
