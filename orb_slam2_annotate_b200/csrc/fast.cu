@@ -20,6 +20,7 @@ namespace orbfe {
 namespace {
 
 constexpr int kThreads = 128;
+constexpr int kWarpWinMax = 48;          // largest window side the warp-per-cell kernel takes
 constexpr int WIN = kFastMaxWin;        // max window side
 constexpr int ZONE = WIN - 6;           // max zone side
 
@@ -31,23 +32,31 @@ constexpr int ZONE = WIN - 6;           // max zone side
 __device__ __forceinline__ int small_div(int a, float rcp_b) { return (int)(((float)a + 0.5f) * rcp_b); }
 
 // corner strength S of the pixel at p (row stride `st`), or 0 when S <= t is already certain
+// QUICK: early exits on the four axis / diagonal pairs (worth it when most pixels fail them; the
+// warp kernel's survivors already passed the unsigned form of those tests and skip them)
+template <bool QUICK>
 __device__ __forceinline__ int corner_strength(const uint8_t* p, int st, int t) {
     const int v = p[0];
     int r[16];
     // opposing pairs first: a 9-arc contains at least one pixel of every pair (k, k+8)
     r[0] = p[3 * st];  r[8] = p[-3 * st];
-    const int lo = v - t, hi = v + t;
-    int m = ((r[0] < lo || r[8] < lo) ? 1 : 0) | ((r[0] > hi || r[8] > hi) ? 2 : 0);
-    if (!m) return 0;
     r[4] = p[3];  r[12] = p[-3];
-    m &= ((r[4] < lo || r[12] < lo) ? 1 : 0) | ((r[4] > hi || r[12] > hi) ? 2 : 0);
-    if (!m) return 0;
-    r[2] = p[2 * st + 2];  r[10] = p[-2 * st - 2];
-    m &= ((r[2] < lo || r[10] < lo) ? 1 : 0) | ((r[2] > hi || r[10] > hi) ? 2 : 0);
-    if (!m) return 0;
-    r[6] = p[-2 * st + 2];  r[14] = p[2 * st - 2];
-    m &= ((r[6] < lo || r[14] < lo) ? 1 : 0) | ((r[6] > hi || r[14] > hi) ? 2 : 0);
-    if (!m) return 0;
+    if (QUICK) {
+        const int lo = v - t, hi = v + t;
+        int m = ((r[0] < lo || r[8] < lo) ? 1 : 0) | ((r[0] > hi || r[8] > hi) ? 2 : 0);
+        if (!m) return 0;
+        m &= ((r[4] < lo || r[12] < lo) ? 1 : 0) | ((r[4] > hi || r[12] > hi) ? 2 : 0);
+        if (!m) return 0;
+        r[2] = p[2 * st + 2];  r[10] = p[-2 * st - 2];
+        m &= ((r[2] < lo || r[10] < lo) ? 1 : 0) | ((r[2] > hi || r[10] > hi) ? 2 : 0);
+        if (!m) return 0;
+        r[6] = p[-2 * st + 2];  r[14] = p[2 * st - 2];
+        m &= ((r[6] < lo || r[14] < lo) ? 1 : 0) | ((r[6] > hi || r[14] > hi) ? 2 : 0);
+        if (!m) return 0;
+    } else {
+        r[2] = p[2 * st + 2];  r[10] = p[-2 * st - 2];
+        r[6] = p[-2 * st + 2];  r[14] = p[2 * st - 2];
+    }
     r[1] = p[3 * st + 1];   r[9] = p[-3 * st - 1];
     r[3] = p[st + 3];       r[11] = p[-st - 3];
     r[5] = p[-st + 3];      r[13] = p[st - 3];
@@ -88,7 +97,7 @@ fast_cells_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __restr
     int l = 0;
     while (l + 1 < g.nlevels && cell >= g.lv[l + 1].cellBase) l++;
     const LevelGeom& L = g.lv[l];
-    if (L.wCell + 6 <= 48 && L.hCell + 6 <= 48) return;       // done by fast_cells_warp_kernel
+    if (L.wCell + 6 <= kWarpWinMax && L.hCell + 6 <= kWarpWinMax) return;   // done by fast_cells_warp_kernel
     const int c = cell - L.cellBase;
     const int ci = c / L.nCols, cj = c - ci * L.nCols;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -124,7 +133,7 @@ fast_cells_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __restr
         const int t = pass == 0 ? g.iniTh : g.minTh;
         for (int i = tid; i < npx; i += kThreads) {
             const int r = i / zw, cc = i - r * zw;
-            sc[r + 1][cc + 1] = (uint8_t)corner_strength(&win[r + 3][cc + 3], WIN + 8, t);
+            sc[r + 1][cc + 1] = (uint8_t)corner_strength<true>(&win[r + 3][cc + 3], WIN + 8, t);
         }
         __syncthreads();
         // 3x3 strict maximum + ordered (row-major) compaction
@@ -171,20 +180,24 @@ fast_cells_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __restr
 // (a dense work list in shared memory).  Stage 3 applies the per-cell 3x3 strict maximum and
 // marks survivors in a bitmap; popc prefix sums over the bitmap give every survivor its
 // row-major output rank, so the emitted order equals cv::FAST's.
-constexpr int WWIN = 48;                 // max window side of the warp kernel
-constexpr int WS = 16;                   // window row stride in 32-bit words (1 pad word left)
-constexpr int WZ = WWIN - 6;             // max zone side
-constexpr int SCS = 48;                  // score-map row stride in bytes
+// Two layouts: windows up to 40x40 (every cell of the usual camera sizes: cells are 30..34 px
+// wide) in 6 KB per warp, which lets 8 CTAs = 32 warps live on an SM, and windows up to 48x48.
 constexpr int kWarpsPerCta = 4;
-constexpr int BMW = (WZ * WZ + 31) / 32; // bitmap words
 
+template <int WWIN_>
 struct WarpSmem {
+    static constexpr int WWIN = WWIN_;                    // max window side
+    static constexpr int WS = WWIN_ == 40 ? 12 : 16;      // window row stride in words (1 pad word left)
+    static constexpr int WZ = WWIN_ - 6;                  // max zone side
+    static constexpr int SCS = WWIN_;                     // score-map row stride in bytes
+    static constexpr int BMW = (WZ * WZ + 31) / 32;       // bitmap words
     uint32_t win[WWIN][WS];
     uint8_t sc[WZ + 2][SCS];
     unsigned short list[WZ * WZ];
     uint32_t bitmap[BMW + 1];
     int bmpre[BMW + 1];
     int counter;
+    uint32_t pad;                                         // the last row's wc + 1 read stays inside
 };
 
 __device__ __forceinline__ uint32_t swar_gt(uint32_t d, uint32_t c, bool small_t) {
@@ -192,18 +205,21 @@ __device__ __forceinline__ uint32_t swar_gt(uint32_t d, uint32_t c, bool small_t
     return (small_t ? (m | d) : (m & d)) & 0x80808080u;
 }
 
+template <int WWIN>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
 fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __restrict__ pyr,
                        int* __restrict__ cellc, uint32_t* __restrict__ cellk) {
-    __shared__ WarpSmem smem[kWarpsPerCta];
+    using Smem = WarpSmem<WWIN>;
+    constexpr int WS = Smem::WS, SCS = Smem::SCS, BMW = Smem::BMW;
+    __shared__ Smem smem[kWarpsPerCta];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    WarpSmem& S = smem[wid];
+    Smem& S = smem[wid];
     const int frame = blockIdx.y + g.frame0, cell = blockIdx.x * kWarpsPerCta + wid;
     if (cell >= g.ncells) return;
     int l = 0;
     while (l + 1 < g.nlevels && cell >= g.lv[l + 1].cellBase) l++;
     const LevelGeom& L = g.lv[l];
-    if (L.wCell + 6 > WWIN || L.hCell + 6 > WWIN) return;     // handled by the generic kernel
+    if (L.wCell + 6 > kWarpWinMax || L.hCell + 6 > kWarpWinMax) return;     // handled by the generic kernel
     const int c = cell - L.cellBase;
     const int ci = small_div(c, __frcp_rn((float)L.nCols)), cj = c - ci * L.nCols;
     int* out_cnt = cellc + (long long)frame * g.ncells + cell;
@@ -287,7 +303,7 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __
             __syncwarp();
             if (i < ncand) {
                 const int r = e >> 8, cc = e & 0xFF;
-                s = corner_strength(wb + (r + 3) * (WS * 4) + zx0 + cc, WS * 4, t);
+                s = corner_strength<false>(wb + (r + 3) * (WS * 4) + zx0 + cc, WS * 4, t);
                 if (s) {
                     S.sc[r + 1][cc + 1] = (uint8_t)s;
                     S.list[atomicAdd(&S.counter, 1)] = (unsigned short)e;
@@ -348,12 +364,17 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __
 
 int launch_fast(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
     int launches = 0;
-    bool generic = false;
-    for (int l = 0; l < g.nlevels; l++)
-        if (g.lv[l].nCols && (g.lv[l].wCell + 6 > WWIN || g.lv[l].hCell + 6 > WWIN)) generic = true;
+    bool generic = false, compact = true;
+    for (int l = 0; l < g.nlevels; l++) {
+        if (!g.lv[l].nCols) continue;
+        const int side = (g.lv[l].wCell > g.lv[l].hCell ? g.lv[l].wCell : g.lv[l].hCell) + 6;
+        if (side > kWarpWinMax) generic = true;
+        else if (side > 40) compact = false;
+    }
     if (g.ncells > 0) {
-        fast_cells_warp_kernel<<<dim3((g.ncells + kWarpsPerCta - 1) / kWarpsPerCta, g.batch), kWarpsPerCta * 32, 0, s>>>(
-            g, d.pyr, d.cellc, d.cellk);
+        const dim3 grid((g.ncells + kWarpsPerCta - 1) / kWarpsPerCta, g.batch);
+        if (compact) fast_cells_warp_kernel<40><<<grid, kWarpsPerCta * 32, 0, s>>>(g, d.pyr, d.cellc, d.cellk);
+        else fast_cells_warp_kernel<48><<<grid, kWarpsPerCta * 32, 0, s>>>(g, d.pyr, d.cellc, d.cellk);
         launches++;
     }
     if (generic) {

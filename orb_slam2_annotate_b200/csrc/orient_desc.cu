@@ -76,11 +76,13 @@ orient_desc_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant
         const uint8_t* c = d.pyr + off;
         const int u = lane - kHalfPatch, vm = __ldg(&umax[abs(u)]);
         int sum = 0;
-#pragma unroll 4
-        for (int v = -vm; v <= vm; v++) {
-            const int val = c[v * L.pitch + u];
-            sum += val;
-            m01 += v * val;
+#pragma unroll
+        for (int v = -kHalfPatch; v <= kHalfPatch; v++) {     // 31 independent predicated loads
+            if (abs(v) <= vm) {
+                const int val = c[v * L.pitch + u];
+                sum += val;
+                m01 += v * val;
+            }
         }
         m10 = u * sum;
     }
@@ -95,11 +97,10 @@ orient_desc_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant
     const float factorPI = (float)(3.14159265358979323846 / 180.f);   // :108
     const float ang = __fmul_rn(angle, factorPI);
     // cos/sin resolve to glibc's float routines in the reference (:68,:115-116); sincosf_glibc.h
-    // restates them bit for bit.  Two lanes evaluate, everyone reads the results.
-    float ab = 0.f;
-    if (lane == 0) ab = orbfe_scf::cosf_glibc(ang);
-    else if (lane == 1) ab = orbfe_scf::sinf_glibc(ang);
-    const float a = __shfl_sync(FULL, ab, 0), b = __shfl_sync(FULL, ab, 1);
+    // restates them bit for bit.  The angle is warp-uniform, so every lane evaluates it without
+    // divergence.
+    float a, b;
+    orbfe_scf::sincosf_glibc(ang, &b, &a);
     const uint8_t* cb = d.blur + off;
     const int4* pat4 = reinterpret_cast<const int4*>(d_pattern) + 2 * lane;
     const int4 w0 = __ldg(pat4), w1 = __ldg(pat4 + 1);
@@ -107,8 +108,9 @@ orient_desc_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant
     int val = 0;
 #pragma unroll
     for (int j = 0; j < 8; j++) {
-        const float x0 = (float)(signed char)(words[j] & 0xFF), y0 = (float)(signed char)((words[j] >> 8) & 0xFF);
-        const float x1 = (float)(signed char)((words[j] >> 16) & 0xFF), y1 = (float)(signed char)((words[j] >> 24) & 0xFF);
+        // I2F of the sign-extended bytes (PRMT-based sign extension keeps this to two ops each)
+        const float x0 = (float)(int)(signed char)(words[j]), y0 = (float)((words[j] << 16) >> 24);
+        const float x1 = (float)((words[j] << 8) >> 24), y1 = (float)(words[j] >> 24);
         const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
         const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
         const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));

@@ -93,4 +93,24 @@ SCF_HD float cosf_glibc(float y) {
     return poly(mul(x, s), mul(x, x), (n & 2) != 0, n ^ 1);
 }
 
+// both at once (one range reduction); bit-identical to sinf_glibc / cosf_glibc
+SCF_HD void sincosf_glibc(float y, float* sn, float* cs) {
+    double x = y;
+    if (abstop12(y) < abstop12(0x1.921FB6p-1f)) {
+        if (abstop12(y) < abstop12(0x1p-12f)) { *sn = y; *cs = 1.0f; return; }
+        const double x2 = mul(x, x);
+        *sn = poly(x, x2, false, 0);
+        *cs = poly(x, x2, false, 1);
+        return;
+    }
+    int n;
+    x = reduce_fast(x, &n);
+    const double s = (n & 3) == 1 || (n & 3) == 2 ? -1.0 : 1.0;
+    const double xs = mul(x, s), x2 = mul(x, x);
+    const bool neg = (n & 2) != 0;
+    const float ps = poly(xs, x2, neg, 0), pc = poly(xs, x2, neg, 1);
+    *sn = (n & 1) ? pc : ps;
+    *cs = (n & 1) ? ps : pc;
+}
+
 }  // namespace orbfe_scf

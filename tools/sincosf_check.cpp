@@ -15,6 +15,9 @@ int main(int argc, char** argv) {
         volatile float vx = x;
         const float s = sinf(vx), c = cosf(vx);
         const float s2 = orbfe_scf::sinf_glibc(x), c2 = orbfe_scf::cosf_glibc(x);
+        float s3, c3;
+        orbfe_scf::sincosf_glibc(x, &s3, &c3);
+        if (memcmp(&s3, &s2, 4) || memcmp(&c3, &c2, 4)) { bad_s++; bad_c++; }
         if (memcmp(&s, &s2, 4)) { if (bad_s < 5) printf("sin %a: libm %a mine %a\n", x, s, s2); bad_s++; }
         if (memcmp(&c, &c2, 4)) { if (bad_c < 5) printf("cos %a: libm %a mine %a\n", x, c, c2); bad_c++; }
         n++;
