@@ -208,14 +208,14 @@ __device__ __forceinline__ uint32_t swar_gt(uint32_t d, uint32_t c, bool small_t
 template <int WWIN>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
 fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __restrict__ pyr,
-                       int* __restrict__ cellc, uint32_t* __restrict__ cellk) {
+                       int* __restrict__ cellc, uint32_t* __restrict__ cellk, int cellLo, int cellHi) {
     using Smem = WarpSmem<WWIN>;
     constexpr int WS = Smem::WS, SCS = Smem::SCS, BMW = Smem::BMW;
     __shared__ Smem smem[kWarpsPerCta];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     Smem& S = smem[wid];
-    const int frame = blockIdx.y + g.frame0, cell = blockIdx.x * kWarpsPerCta + wid;
-    if (cell >= g.ncells) return;
+    const int frame = blockIdx.y + g.frame0, cell = cellLo + blockIdx.x * kWarpsPerCta + wid;
+    if (cell >= cellHi) return;
     int l = 0;
     while (l + 1 < g.nlevels && cell >= g.lv[l + 1].cellBase) l++;
     const LevelGeom& L = g.lv[l];
@@ -364,18 +364,26 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __
 
 int launch_fast(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
     int launches = 0;
-    bool generic = false, compact = true;
-    for (int l = 0; l < g.nlevels; l++) {
-        if (!g.lv[l].nCols) continue;
+    // runs of consecutive levels that share a kernel variant: 0 = generic, 40 / 48 = warp layouts
+    bool generic = false;
+    auto variant = [&](int l) {
+        if (!g.lv[l].nCols) return -1;
         const int side = (g.lv[l].wCell > g.lv[l].hCell ? g.lv[l].wCell : g.lv[l].hCell) + 6;
-        if (side > kWarpWinMax) generic = true;
-        else if (side > 40) compact = false;
-    }
-    if (g.ncells > 0) {
-        const dim3 grid((g.ncells + kWarpsPerCta - 1) / kWarpsPerCta, g.batch);
-        if (compact) fast_cells_warp_kernel<40><<<grid, kWarpsPerCta * 32, 0, s>>>(g, d.pyr, d.cellc, d.cellk);
-        else fast_cells_warp_kernel<48><<<grid, kWarpsPerCta * 32, 0, s>>>(g, d.pyr, d.cellc, d.cellk);
-        launches++;
+        return side > kWarpWinMax ? 0 : side > 40 ? 48 : 40;
+    };
+    for (int l = 0; l < g.nlevels;) {
+        const int v = variant(l);
+        int e = l + 1;
+        while (e < g.nlevels && (variant(e) == v || variant(e) < 0)) e++;
+        const int lo = g.lv[l].cellBase, hi = e < g.nlevels ? g.lv[e].cellBase : g.ncells;
+        if (v == 0) generic = true;
+        if (v > 0 && hi > lo) {
+            const dim3 grid((hi - lo + kWarpsPerCta - 1) / kWarpsPerCta, g.batch);
+            if (v == 40) fast_cells_warp_kernel<40><<<grid, kWarpsPerCta * 32, 0, s>>>(g, d.pyr, d.cellc, d.cellk, lo, hi);
+            else fast_cells_warp_kernel<48><<<grid, kWarpsPerCta * 32, 0, s>>>(g, d.pyr, d.cellc, d.cellk, lo, hi);
+            launches++;
+        }
+        l = e;
     }
     if (generic) {
         fast_cells_kernel<<<dim3(g.ncells, g.batch), kThreads, 0, s>>>(g, d.pyr, d.cellc, d.cellk);
