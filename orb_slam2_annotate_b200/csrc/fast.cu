@@ -184,6 +184,7 @@ fast_cells_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __restr
 // wide) in 6 KB per warp, which lets 8 CTAs = 32 warps live on an SM, and windows up to 48x48.
 constexpr int kWarpsPerCta = 4;
 
+template <int WWIN_> struct S_sc_t { uint8_t b[WWIN_ - 4][WWIN_]; };
 template <int WWIN_>
 struct WarpSmem {
     static constexpr int WWIN = WWIN_;                    // max window side
@@ -211,6 +212,7 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __
                        int* __restrict__ cellc, uint32_t* __restrict__ cellk, int cellLo, int cellHi) {
     using Smem = WarpSmem<WWIN>;
     constexpr int WS = Smem::WS, SCS = Smem::SCS, BMW = Smem::BMW;
+    static_assert(sizeof(S_sc_t<WWIN>) >= 4 * (WWIN - 6) * ((WWIN - 6 + 3) / 4 + 1), "task list must fit the score map");
     __shared__ Smem smem[kWarpsPerCta];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     Smem& S = smem[wid];
@@ -239,12 +241,24 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __
     const int nw = ((maxX + 3) >> 2) - (ax0 >> 2);   // words per window row (<= 14)
     const int zx0 = iniX + 3 - ax0, zx1 = maxX - 3 - ax0;   // zone columns in window bytes
     const int zc0 = zx0 >> 2, nzc = ((zx1 - 1) >> 2) - zc0 + 1;
-    const uint8_t* src = pyr + L.pyrOff + (long long)frame * L.lvBytes + (long long)iniY * L.pitch + ax0;
-    const float rcp_nw = __frcp_rn((float)nw), rcp_nzc = __frcp_rn((float)nzc);
-#pragma unroll 4
-    for (int i = lane; i < wh * nw; i += 32) {
-        const int r = small_div(i, rcp_nw), cc = i - r * nw;
-        S.win[r][cc + 1] = __ldg(reinterpret_cast<const uint32_t*>(src + r * L.pitch) + cc);
+    const float rcp_nzc = __frcp_rn((float)nzc);
+    {   // window rows arrive as 16-byte chunks (level rows are 16-byte aligned); words outside
+        // [ax0, ax0 + 4 nw) are dropped
+        const int a16 = iniX & ~15;
+        const int nq = ((maxX + 15) >> 4) - (a16 >> 4);
+        const int wq0 = (a16 - ax0) >> 2;                // <= 0
+        const uint8_t* src = pyr + L.pyrOff + (long long)frame * L.lvBytes + (long long)iniY * L.pitch + a16;
+        const float rcp_nq = __frcp_rn((float)nq);
+#pragma unroll 2
+        for (int i = lane; i < wh * nq; i += 32) {
+            const int r = small_div(i, rcp_nq), q = i - r * nq;
+            const uint4 v = __ldg(reinterpret_cast<const uint4*>(src + r * L.pitch) + q);
+            const int w = wq0 + q * 4;
+            if ((unsigned)(w + 0) < (unsigned)nw) S.win[r][w + 1] = v.x;
+            if ((unsigned)(w + 1) < (unsigned)nw) S.win[r][w + 2] = v.y;
+            if ((unsigned)(w + 2) < (unsigned)nw) S.win[r][w + 3] = v.z;
+            if ((unsigned)(w + 3) < (unsigned)nw) S.win[r][w + 4] = v.w;
+        }
     }
     const uint8_t* wb = reinterpret_cast<const uint8_t*>(&S.win[0][0]) + 4;   // byte (r, x) = wb[r*WS*4 + x]
 
@@ -253,43 +267,60 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __
         const int t = pass == 0 ? g.iniTh : g.minTh;
         const bool small_t = t < 128;
         const uint32_t cmpc = (uint32_t)(small_t ? 0x7F - t : 0x7F - (t - 128)) * 0x01010101u;
-        // zero score map, bitmap, counters
-        for (int i = lane; i < (zh + 2) * (SCS / 4); i += 32) reinterpret_cast<uint32_t*>(&S.sc[0][0])[i] = 0;
         for (int i = lane; i <= BMW; i += 32) S.bitmap[i] = 0;
         if (lane == 0) S.counter = 0;
+        // ---- stage 1a: vertical pair (0,8) on every zone word; surviving words are compacted
+        // (ballot order) into a task list that borrows the score map's storage
+        uint32_t* tasks = reinterpret_cast<uint32_t*>(&S.sc[0][0]);
+        int ntask = 0;
+        for (int base = 0; base < zh * nzc; base += 32) {
+            const int i = base + lane;
+            uint32_t gmask = 0;
+            int r = 0, cc = 0;
+            if (i < zh * nzc) {
+                r = small_div(i, rcp_nzc), cc = i - r * nzc;
+                const int y = r + 3, wc = zc0 + cc + 1;          // window row, word column (+1 pad)
+                const uint32_t v = S.win[y][wc];
+                gmask = swar_gt(__vabsdiffu4(S.win[y + 3][wc], v), cmpc, small_t) |
+                        swar_gt(__vabsdiffu4(S.win[y - 3][wc], v), cmpc, small_t);
+                // bytes of this word inside the zone
+                const int xb = (zc0 + cc) * 4;
+                uint32_t zm = 0x80808080u;
+                if (xb < zx0) zm &= 0xFFFFFFFFu << (8 * (zx0 - xb));
+                if (xb + 4 > zx1) zm &= 0xFFFFFFFFu >> (8 * (xb + 4 - zx1));
+                gmask &= zm;
+            }
+            const uint32_t bal = __ballot_sync(0xFFFFFFFFu, gmask != 0);
+            if (gmask) tasks[ntask + __popc(bal & ((1u << lane) - 1u))] = gmask | (uint32_t)r | ((uint32_t)cc << 8);
+            ntask += __popc(bal);
+        }
         __syncwarp();
-        // ---- stage 1: SIMD rejection, 4 pixels per task
-        for (int i = lane; i < zh * nzc; i += 32) {
-            const int r = small_div(i, rcp_nzc), cc = i - r * nzc;
-            const int y = r + 3, wc = zc0 + cc + 1;          // window row, word column (+1 pad)
+        // ---- stage 1b: pairs (4,12), (2,10), (6,14) on the surviving words, all lanes busy
+        for (int i = lane; i < ntask; i += 32) {
+            const uint32_t e = tasks[i];
+            uint32_t gmask = e & 0x80808080u;
+            const int r = e & 0x7F, cc = (e >> 8) & 0x7F;
+            const int y = r + 3, wc = zc0 + cc + 1;
             const uint32_t v = S.win[y][wc];
-            uint32_t gmask = swar_gt(__vabsdiffu4(S.win[y + 3][wc], v), cmpc, small_t) |
-                             swar_gt(__vabsdiffu4(S.win[y - 3][wc], v), cmpc, small_t);
-            // bytes of this word inside the zone
-            const int xb = (zc0 + cc) * 4;
-            uint32_t zm = 0x80808080u;
-            if (xb < zx0) zm &= 0xFFFFFFFFu << (8 * (zx0 - xb));
-            if (xb + 4 > zx1) zm &= 0xFFFFFFFFu >> (8 * (xb + 4 - zx1));
-            gmask &= zm;
-            if (!gmask) continue;
             const uint32_t wl = S.win[y][wc - 1], wr = S.win[y][wc + 1];
             gmask &= swar_gt(__vabsdiffu4(__funnelshift_r(v, wr, 24), v), cmpc, small_t) |
                      swar_gt(__vabsdiffu4(__funnelshift_r(wl, v, 8), v), cmpc, small_t);
-            if (!gmask) continue;
             const uint32_t r2 = __funnelshift_r(S.win[y + 2][wc], S.win[y + 2][wc + 1], 16);
             const uint32_t r10 = __funnelshift_r(S.win[y - 2][wc - 1], S.win[y - 2][wc], 16);
             gmask &= swar_gt(__vabsdiffu4(r2, v), cmpc, small_t) | swar_gt(__vabsdiffu4(r10, v), cmpc, small_t);
-            if (!gmask) continue;
             const uint32_t r6 = __funnelshift_r(S.win[y - 2][wc], S.win[y - 2][wc + 1], 16);
             const uint32_t r14 = __funnelshift_r(S.win[y + 2][wc - 1], S.win[y + 2][wc], 16);
             gmask &= swar_gt(__vabsdiffu4(r6, v), cmpc, small_t) | swar_gt(__vabsdiffu4(r14, v), cmpc, small_t);
             if (!gmask) continue;
-            const int k = __popc(gmask);
-            int pos = atomicAdd(&S.counter, k);
+            const int xb = (zc0 + cc) * 4;
+            int pos = atomicAdd(&S.counter, __popc(gmask));
 #pragma unroll
             for (int b = 0; b < 4; b++)
                 if (gmask & (0x80u << (8 * b))) S.list[pos++] = (unsigned short)((r << 8) | (xb + b - zx0));
         }
+        __syncwarp();
+        // the task list is consumed: zero the score map
+        for (int i = lane; i < (zh + 2) * (SCS / 4); i += 32) reinterpret_cast<uint32_t*>(&S.sc[0][0])[i] = 0;
         __syncwarp();
         // ---- stage 2: exact test + strength on the survivors
         const int ncand = S.counter;
