@@ -50,6 +50,7 @@ struct orbfe_extractor {
     DevArray<orbfe_keypoint> kps;
     DevArray<int2> xtab;
     DevArray<int4> ytab;
+    DevArray<int4> xq;
     int lastBatch = 0, lastLaunches = 0;
     // optional per-stage timing (events on the handle's stream)
     bool profiling = false;
@@ -128,6 +129,39 @@ static void resize_tables(int sw, int sh, int dw, int dh, std::vector<int2>& xt,
     }
 }
 
+// Column-group table of the word-gather resize kernel: for output columns 4q..4q+3 the aligned
+// source byte offset of the first tap, PRMT selectors that pull (L, R) tap pairs out of the
+// three words loaded there, and the coefficient pairs.  False when a group spans more than 12
+// source bytes (then the level uses the byte-gather kernel).
+static bool resize_group_table(const std::vector<int2>& xt, int dw, std::vector<int4>& xq) {
+    const int nq = (dw + 3) / 4;
+    xq.assign((size_t)nq * 3, make_int4(0, 0, 0, 0));
+    for (int q = 0; q < nq; q++) {
+        int oL[4], oR[4]; unsigned c[4];
+        const int base = (xt[4 * q].x & 0xFFFF) & ~3;
+        for (int i = 0; i < 4; i++) {
+            const int2 t = xt[std::min(4 * q + i, dw - 1)];
+            oL[i] = (t.x & 0xFFFF) - base; oR[i] = (t.x >> 16) - base; c[i] = (unsigned)t.y;
+            if (oL[i] < 0 || oR[i] < 0 || oL[i] >= 12 || oR[i] >= 12) return false;
+            if ((short)(t.y & 0xFFFF) < 0 || (t.y >> 16) < 0) return false;   // IDP.2A operands are unsigned here
+        }
+        auto sel = [&](int i, int j, unsigned& selA, unsigned& selB) {
+            const int o[4] = {oL[i], oR[i], oL[j], oR[j]};
+            selA = selB = 0;
+            for (int k = 0; k < 4; k++) {
+                selA |= (unsigned)(o[k] < 8 ? o[k] : 0) << (4 * k);
+                selB |= (unsigned)(o[k] < 8 ? k : 4 + o[k] - 8) << (4 * k);
+            }
+        };
+        unsigned a01, b01, a23, b23;
+        sel(0, 1, a01, b01); sel(2, 3, a23, b23);
+        xq[3 * q] = make_int4(base, (int)a01, (int)b01, (int)a23);
+        xq[3 * q + 1] = make_int4((int)b23, (int)c[0], (int)c[1], (int)c[2]);
+        xq[3 * q + 2] = make_int4((int)c[3], 0, 0, 0);
+    }
+    return true;
+}
+
 static inline long long align_up(long long v, long long a) { return (v + a - 1) / a * a; }
 
 // Per-level geometry for a w x h input at batch capacity B: level sizes (:1208), FAST cell
@@ -203,7 +237,7 @@ static int ensure_geometry(orbfe_extractor* e, int w, int h, int batch) {
     if (rc) return rc;
     CU(cudaSetDevice(e->device));
     CU(cudaStreamSynchronize(e->stream));
-    if ((rc = e->pyr.ensure(g.pyrBytes))) return rc;
+    if ((rc = e->pyr.ensure(g.pyrBytes + 256))) return rc;      // slack: the resize kernel loads whole words past a row's last tap
     if ((rc = e->blur.ensure(g.pyrBytes))) return rc;
     if ((rc = e->cellc.ensure((size_t)cap * g.ncells + 1))) return rc;
     if ((rc = e->cellk.ensure((size_t)cap * g.cellSlots + 1))) return rc;
@@ -216,16 +250,22 @@ static int ensure_geometry(orbfe_extractor* e, int w, int h, int batch) {
     if ((rc = e->counts.ensure(cap))) return rc;
     // resize tables
     std::vector<int2> xall; std::vector<int4> yall;
+    std::vector<int4> qall;
     std::vector<size_t> xo(e->nlevels, 0), yo(e->nlevels, 0);
+    std::vector<long long> qo(e->nlevels, -1);
     for (int l = 1; l < e->nlevels; l++) {
         std::vector<int2> xt; std::vector<int4> yt;
         resize_tables(g.lv[l - 1].w, g.lv[l - 1].h, g.lv[l].w, g.lv[l].h, xt, yt);
         xo[l] = xall.size(); yo[l] = yall.size();
+        std::vector<int4> xq;
+        if (resize_group_table(xt, g.lv[l].w, xq)) { qo[l] = (long long)qall.size(); qall.insert(qall.end(), xq.begin(), xq.end()); }
         xall.insert(xall.end(), xt.begin(), xt.end());
         yall.insert(yall.end(), yt.begin(), yt.end());
     }
     if ((rc = e->xtab.ensure(xall.size() + 1))) return rc;
     if ((rc = e->ytab.ensure(yall.size() + 1))) return rc;
+    if ((rc = e->xq.ensure(qall.size() + 1))) return rc;
+    if (!qall.empty()) CU(cudaMemcpy(e->xq.p, qall.data(), qall.size() * sizeof(int4), cudaMemcpyHostToDevice));
     if (!xall.empty()) {
         CU(cudaMemcpy(e->xtab.p, xall.data(), xall.size() * sizeof(int2), cudaMemcpyHostToDevice));
         CU(cudaMemcpy(e->ytab.p, yall.data(), yall.size() * sizeof(int4), cudaMemcpyHostToDevice));
@@ -235,7 +275,10 @@ static int ensure_geometry(orbfe_extractor* e, int w, int h, int batch) {
     d.pyr = e->pyr.p; d.blur = e->blur.p; d.cellc = e->cellc.p; d.cellk = e->cellk.p;
     d.sel = e->sel.p; d.selc = e->selc.p; d.kps = e->kps.p; d.desc = e->desc.p;
     d.counts = e->counts.p; d.qt_xy = e->qt_xy.p; d.qt_node = e->qt_node.p; d.qtCap = g.cellSlots;
-    for (int l = 1; l < e->nlevels; l++) { d.xtab[l] = e->xtab.p + xo[l]; d.ytab[l] = e->ytab.p + yo[l]; }
+    for (int l = 1; l < e->nlevels; l++) {
+        d.xtab[l] = e->xtab.p + xo[l]; d.ytab[l] = e->ytab.p + yo[l];
+        d.xq[l] = qo[l] >= 0 ? e->xq.p + qo[l] : nullptr;
+    }
     g.batch = batch;
     e->g = g;
     e->geomW = w; e->geomH = h; e->geomBatchCap = cap;
@@ -366,7 +409,7 @@ void orbfe_extractor_destroy(orbfe_extractor* e) {
     for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);
     e->pyr.release(); e->blur.release(); e->desc.release(); e->cellc.release(); e->selc.release();
     e->counts.release(); e->umax_d.release(); e->cellk.release(); e->sel.release();
-    e->qt_xy.release(); e->qt_node.release(); e->kps.release(); e->xtab.release(); e->ytab.release();
+    e->qt_xy.release(); e->qt_node.release(); e->kps.release(); e->xtab.release(); e->ytab.release(); e->xq.release();
     delete e;
 }
 

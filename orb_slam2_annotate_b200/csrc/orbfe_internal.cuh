@@ -72,6 +72,7 @@ struct DevBufs {
     // resize tables, per level (level 0 entries unused)
     const int2* xtab[kMaxLevels];   // per dst x: {sx, a0 | a1<<16}
     const int4* ytab[kMaxLevels];   // per dst y: {row0, row1, b0, b1}
+    const int4* xq[kMaxLevels];     // per 4 dst columns: {base, selA01, selB01, selA23}{selB23, c0..c2}{c3,-,-,-}; null = use xtab
     // quadtree point scratch for levels whose corner count exceeds the shared-memory arrays
     uint32_t* qt_xy;                // [B][L][qtCap]
     uint32_t* qt_node;              // [B][L][qtCap]

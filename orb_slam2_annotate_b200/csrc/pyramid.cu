@@ -70,6 +70,70 @@ resize_level_kernel(const uint8_t* __restrict__ src_base, uint8_t* __restrict__ 
     }
 }
 
+
+// Word-gather variant (every level whose four-column groups span at most 12 source bytes, i.e.
+// scale factors up to ~2.6).  Per source row a thread loads the three aligned words that hold
+// its (left, right) taps, two PRMTs per output pair arrange them as (L0, R0, L1, R1) and IDP.2A
+// multiplies them with the 16-bit coefficient pairs: 3 loads + 8 integer instructions per row
+// instead of 8 byte loads + 8 multiplies + their 64-bit addresses.  The vertical pass uses
+// IMAD.HI on coefficients pre-shifted by 16.  Selectors and coefficients come from a host-built
+// table (xq: three int4 per column group) and stay in registers while the thread walks PRQ rows.
+constexpr int PRQ = 16;
+
+__global__ void __launch_bounds__(128)
+resize_level_q_kernel(const uint8_t* __restrict__ src_base, uint8_t* __restrict__ dst_base,
+                      long long sframe_bytes, long long dframe_bytes, int spitch, int dpitch,
+                      int dw, int dh, const int4* __restrict__ xq, const int4* __restrict__ ytab) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    const int x4 = q * 4;
+    const int y0 = blockIdx.y * PRQ;
+    if (x4 >= dw) return;
+    const int4 t0 = __ldg(&xq[3 * q]), t1 = __ldg(&xq[3 * q + 1]), t2 = __ldg(&xq[3 * q + 2]);
+    const uint32_t selA01 = t0.y, selB01 = t0.z, selA23 = t0.w, selB23 = t1.x;
+    const uint32_t c0 = t1.y, c1 = t1.z, c2 = t1.w, c3 = t2.x;
+    const uint8_t* src = src_base + (long long)blockIdx.z * sframe_bytes + t0.x;
+    uint8_t* dst = dst_base + (long long)blockIdx.z * dframe_bytes + x4;
+    auto hrow = [&](int r, uint32_t* h) {
+        const uint32_t* p = reinterpret_cast<const uint32_t*>(src + (long long)r * spitch);
+        const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);
+        const uint32_t p01 = __byte_perm(__byte_perm(w0, w1, selA01), w2, selB01);
+        const uint32_t p23 = __byte_perm(__byte_perm(w0, w1, selA23), w2, selB23);
+        h[0] = __dp2a_lo(c0, p01, 0u) >> 4;
+        h[1] = __dp2a_hi(c1, p01, 0u) >> 4;
+        h[2] = __dp2a_lo(c2, p23, 0u) >> 4;
+        h[3] = __dp2a_hi(c3, p23, 0u) >> 4;
+    };
+    int prev_row = -1;
+    uint32_t hprev[4] = {0, 0, 0, 0};
+    const int yend = min(y0 + PRQ, dh);
+    for (int y = y0; y < yend; y++) {
+        const int4 yt = __ldg(&ytab[y]);          // {row0, row1, b0, b1}
+        uint32_t h0[4], h1[4];
+        if (yt.x == prev_row) {
+#pragma unroll
+            for (int i = 0; i < 4; i++) h0[i] = hprev[i];
+        } else {
+            hrow(yt.x, h0);
+        }
+        if (yt.y == yt.x) {
+#pragma unroll
+            for (int i = 0; i < 4; i++) h1[i] = h0[i];
+        } else {
+            hrow(yt.y, h1);
+        }
+        const uint32_t b0 = (uint32_t)yt.z << 16, b1 = (uint32_t)yt.w << 16;
+        uint32_t v[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            v[i] = (__umulhi(b0, h0[i]) + __umulhi(b1, h1[i]) + 2u) >> 2;      // <= 255
+            hprev[i] = h1[i];
+        }
+        prev_row = yt.y;
+        const uint32_t out = __byte_perm(__byte_perm(v[0], v[1], 0x3340), __byte_perm(v[2], v[3], 0x3340), 0x5410);
+        *reinterpret_cast<uint32_t*>(dst + (long long)y * dpitch) = out;       // pitch % 16 == 0
+    }
+}
+
 }  // namespace
 
 int launch_pyramid(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
@@ -78,6 +142,15 @@ int launch_pyramid(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
         const LevelGeom& P = g.lv[l - 1];
         const LevelGeom& L = g.lv[l];
         dim3 block(128);
+        if (d.xq[l]) {
+            dim3 gridq((L.w + 511) / 512, (L.h + PRQ - 1) / PRQ, g.batch);
+            resize_level_q_kernel<<<gridq, block, 0, s>>>(d.pyr + P.pyrOff + (long long)g.frame0 * P.lvBytes,
+                                                         d.pyr + L.pyrOff + (long long)g.frame0 * L.lvBytes,
+                                                         P.lvBytes, L.lvBytes, P.pitch, L.pitch, L.w, L.h,
+                                                         d.xq[l], d.ytab[l]);
+            launches++;
+            continue;
+        }
         dim3 grid((L.w + 511) / 512, (L.h + PR - 1) / PR, g.batch);
         resize_level_kernel<<<grid, block, 0, s>>>(d.pyr + P.pyrOff + (long long)g.frame0 * P.lvBytes,
                                                    d.pyr + L.pyrOff + (long long)g.frame0 * L.lvBytes,
