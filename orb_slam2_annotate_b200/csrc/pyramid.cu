@@ -87,6 +87,11 @@ resize_level_q_kernel(const uint8_t* __restrict__ src_base, uint8_t* __restrict_
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     const int x4 = q * 4;
     const int y0 = blockIdx.y * PRQ;
+    // the row table of this block goes through shared memory so that a row's pixel loads do not
+    // wait behind a dependent global load
+    __shared__ int4 syt[PRQ];
+    if (threadIdx.x < PRQ) syt[threadIdx.x] = __ldg(&ytab[min(y0 + (int)threadIdx.x, dh - 1)]);
+    __syncthreads();
     if (x4 >= dw) return;
     const int4 t0 = __ldg(&xq[3 * q]), t1 = __ldg(&xq[3 * q + 1]), t2 = __ldg(&xq[3 * q + 2]);
     const uint32_t selA01 = t0.y, selB01 = t0.z, selA23 = t0.w, selB23 = t1.x;
@@ -107,7 +112,7 @@ resize_level_q_kernel(const uint8_t* __restrict__ src_base, uint8_t* __restrict_
     uint32_t hprev[4] = {0, 0, 0, 0};
     const int yend = min(y0 + PRQ, dh);
     for (int y = y0; y < yend; y++) {
-        const int4 yt = __ldg(&ytab[y]);          // {row0, row1, b0, b1}
+        const int4 yt = syt[y - y0];              // {row0, row1, b0, b1}
         uint32_t h0[4], h1[4];
         if (yt.x == prev_row) {
 #pragma unroll
