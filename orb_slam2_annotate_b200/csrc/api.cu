@@ -253,12 +253,17 @@ static int ensure_geometry(orbfe_extractor* e, int w, int h, int batch) {
     std::vector<int4> qall;
     std::vector<size_t> xo(e->nlevels, 0), yo(e->nlevels, 0);
     std::vector<long long> qo(e->nlevels, -1);
+    std::vector<char> qsimple(e->nlevels, 0);
     for (int l = 1; l < e->nlevels; l++) {
         std::vector<int2> xt; std::vector<int4> yt;
         resize_tables(g.lv[l - 1].w, g.lv[l - 1].h, g.lv[l].w, g.lv[l].h, xt, yt);
         xo[l] = xall.size(); yo[l] = yall.size();
         std::vector<int4> xq;
         if (resize_group_table(xt, g.lv[l].w, xq)) { qo[l] = (long long)qall.size(); qall.insert(qall.end(), xq.begin(), xq.end()); }
+        bool simple = true;
+        for (size_t y = 0; y < yt.size(); y++)
+            if (yt[y].y != yt[y].x + 1 || (y > 0 && yt[y].y <= yt[y - 1].y)) simple = false;
+        qsimple[l] = simple;
         xall.insert(xall.end(), xt.begin(), xt.end());
         yall.insert(yall.end(), yt.begin(), yt.end());
     }
@@ -278,6 +283,7 @@ static int ensure_geometry(orbfe_extractor* e, int w, int h, int batch) {
     for (int l = 1; l < e->nlevels; l++) {
         d.xtab[l] = e->xtab.p + xo[l]; d.ytab[l] = e->ytab.p + yo[l];
         d.xq[l] = qo[l] >= 0 ? e->xq.p + qo[l] : nullptr;
+        d.xqSimple[l] = qsimple[l] != 0;
     }
     g.batch = batch;
     e->g = g;

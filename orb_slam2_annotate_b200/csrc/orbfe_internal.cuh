@@ -73,6 +73,7 @@ struct DevBufs {
     const int2* xtab[kMaxLevels];   // per dst x: {sx, a0 | a1<<16}
     const int4* ytab[kMaxLevels];   // per dst y: {row0, row1, b0, b1}
     const int4* xq[kMaxLevels];     // per 4 dst columns: {base, selA01, selB01, selA23}{selB23, c0..c2}{c3,-,-,-}; null = use xtab
+    bool xqSimple[kMaxLevels];      // row table strictly down-scaling: row1 == row0 + 1 and strictly increasing
     // quadtree point scratch for levels whose corner count exceeds the shared-memory arrays
     uint32_t* qt_xy;                // [B][L][qtCap]
     uint32_t* qt_node;              // [B][L][qtCap]

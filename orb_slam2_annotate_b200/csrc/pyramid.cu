@@ -78,8 +78,11 @@ resize_level_kernel(const uint8_t* __restrict__ src_base, uint8_t* __restrict__ 
 // instead of 8 byte loads + 8 multiplies + their 64-bit addresses.  The vertical pass uses
 // IMAD.HI on coefficients pre-shifted by 16.  Selectors and coefficients come from a host-built
 // table (xq: three int4 per column group) and stay in registers while the thread walks PRQ rows.
+// SIMPLE (every down-scaling level): no output row has row0 == row1 and a source row is the lower
+// row of at most one output row, so the emission is a single predicated block per source row.
 constexpr int PRQ = 16;
 
+template <bool SIMPLE>
 __global__ void __launch_bounds__(128)
 resize_level_q_kernel(const uint8_t* __restrict__ src_base, uint8_t* __restrict__ dst_base,
                       long long sframe_bytes, long long dframe_bytes, int spitch, int dpitch,
@@ -89,8 +92,9 @@ resize_level_q_kernel(const uint8_t* __restrict__ src_base, uint8_t* __restrict_
     const int y0 = blockIdx.y * PRQ;
     // the row table of this block goes through shared memory so that a row's pixel loads do not
     // wait behind a dependent global load
-    __shared__ int4 syt[PRQ];
-    if (threadIdx.x < PRQ) syt[threadIdx.x] = __ldg(&ytab[min(y0 + (int)threadIdx.x, dh - 1)]);
+    __shared__ int4 syt[PRQ + 1];
+    if (threadIdx.x <= PRQ)
+        syt[threadIdx.x] = y0 + (int)threadIdx.x < dh && threadIdx.x < PRQ ? __ldg(&ytab[y0 + (int)threadIdx.x]) : make_int4(-1, -1, 0, 0);
     __syncthreads();
     if (x4 >= dw) return;
     const int4 t0 = __ldg(&xq[3 * q]), t1 = __ldg(&xq[3 * q + 1]), t2 = __ldg(&xq[3 * q + 2]);
@@ -98,44 +102,53 @@ resize_level_q_kernel(const uint8_t* __restrict__ src_base, uint8_t* __restrict_
     const uint32_t c0 = t1.y, c1 = t1.z, c2 = t1.w, c3 = t2.x;
     const uint8_t* src = src_base + (long long)blockIdx.z * sframe_bytes + t0.x;
     uint8_t* dst = dst_base + (long long)blockIdx.z * dframe_bytes + x4;
-    auto hrow = [&](int r, uint32_t* h) {
+    struct Raw { uint32_t w0, w1, w2; };
+    auto load_raw = [&](int r) {
         const uint32_t* p = reinterpret_cast<const uint32_t*>(src + (long long)r * spitch);
-        const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);
-        const uint32_t p01 = __byte_perm(__byte_perm(w0, w1, selA01), w2, selB01);
-        const uint32_t p23 = __byte_perm(__byte_perm(w0, w1, selA23), w2, selB23);
+        Raw w; w.w0 = __ldg(p); w.w1 = __ldg(p + 1); w.w2 = __ldg(p + 2);
+        return w;
+    };
+    auto conv = [&](const Raw& w, uint32_t* h) {
+        const uint32_t p01 = __byte_perm(__byte_perm(w.w0, w.w1, selA01), w.w2, selB01);
+        const uint32_t p23 = __byte_perm(__byte_perm(w.w0, w.w1, selA23), w.w2, selB23);
         h[0] = __dp2a_lo(c0, p01, 0u) >> 4;
         h[1] = __dp2a_hi(c1, p01, 0u) >> 4;
         h[2] = __dp2a_lo(c2, p23, 0u) >> 4;
         h[3] = __dp2a_hi(c3, p23, 0u) >> 4;
     };
-    int prev_row = -1;
-    uint32_t hprev[4] = {0, 0, 0, 0};
-    const int yend = min(y0 + PRQ, dh);
-    for (int y = y0; y < yend; y++) {
-        const int4 yt = syt[y - y0];              // {row0, row1, b0, b1}
-        uint32_t h0[4], h1[4];
-        if (yt.x == prev_row) {
+    // Source-row driven walk: the rows row0(y0) .. row1(yend-1) are visited once each, four at
+    // a time with their twelve loads issued together; an output row is emitted when its lower
+    // source row has just been converted (its upper row is that one or the one before).
+    const int n = min(PRQ, dh - y0);
+    const int rl = syt[n - 1].y;
+    int yp = 0;
+    int4 yt = syt[0];                                 // {row0, row1, b0, b1}
+    uint32_t hp[4] = {0, 0, 0, 0};
+    for (int r = yt.x; r <= rl; r += 4) {
+        Raw w[4];
 #pragma unroll
-            for (int i = 0; i < 4; i++) h0[i] = hprev[i];
-        } else {
-            hrow(yt.x, h0);
-        }
-        if (yt.y == yt.x) {
+        for (int k = 0; k < 4; k++) w[k] = load_raw(min(r + k, rl));
 #pragma unroll
-            for (int i = 0; i < 4; i++) h1[i] = h0[i];
-        } else {
-            hrow(yt.y, h1);
-        }
-        const uint32_t b0 = (uint32_t)yt.z << 16, b1 = (uint32_t)yt.w << 16;
-        uint32_t v[4];
+        for (int k = 0; k < 4; k++) {
+            if (r + k > rl) break;                    // warp-uniform
+            uint32_t hc[4];
+            conv(w[k], hc);
+            for (; yt.y == r + k; ) {                 // sentinel row (-1) ends the table
+                const bool same = !SIMPLE && yt.x == yt.y;
+                const uint32_t b0 = (uint32_t)yt.z << 16, b1 = (uint32_t)yt.w << 16;
+                uint32_t v[4];
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-            v[i] = (__umulhi(b0, h0[i]) + __umulhi(b1, h1[i]) + 2u) >> 2;      // <= 255
-            hprev[i] = h1[i];
+                for (int i = 0; i < 4; i++)
+                    v[i] = (__umulhi(b0, same ? hc[i] : hp[i]) + __umulhi(b1, hc[i]) + 2u) >> 2;      // <= 255
+                const uint32_t out = __byte_perm(__byte_perm(v[0], v[1], 0x3340), __byte_perm(v[2], v[3], 0x3340), 0x5410);
+                *reinterpret_cast<uint32_t*>(dst + (long long)(y0 + yp) * dpitch) = out;   // pitch % 16 == 0
+                yp++;
+                yt = syt[yp];
+                if (SIMPLE) break;
+            }
+#pragma unroll
+            for (int i = 0; i < 4; i++) hp[i] = hc[i];
         }
-        prev_row = yt.y;
-        const uint32_t out = __byte_perm(__byte_perm(v[0], v[1], 0x3340), __byte_perm(v[2], v[3], 0x3340), 0x5410);
-        *reinterpret_cast<uint32_t*>(dst + (long long)y * dpitch) = out;       // pitch % 16 == 0
     }
 }
 
@@ -149,10 +162,10 @@ int launch_pyramid(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
         dim3 block(128);
         if (d.xq[l]) {
             dim3 gridq((L.w + 511) / 512, (L.h + PRQ - 1) / PRQ, g.batch);
-            resize_level_q_kernel<<<gridq, block, 0, s>>>(d.pyr + P.pyrOff + (long long)g.frame0 * P.lvBytes,
-                                                         d.pyr + L.pyrOff + (long long)g.frame0 * L.lvBytes,
-                                                         P.lvBytes, L.lvBytes, P.pitch, L.pitch, L.w, L.h,
-                                                         d.xq[l], d.ytab[l]);
+            auto kern = d.xqSimple[l] ? resize_level_q_kernel<true> : resize_level_q_kernel<false>;
+            kern<<<gridq, block, 0, s>>>(d.pyr + P.pyrOff + (long long)g.frame0 * P.lvBytes,
+                                         d.pyr + L.pyrOff + (long long)g.frame0 * L.lvBytes,
+                                         P.lvBytes, L.lvBytes, P.pitch, L.pitch, L.w, L.h, d.xq[l], d.ytab[l]);
             launches++;
             continue;
         }
