@@ -56,6 +56,25 @@ def test_stages_and_end_to_end(orbfe, oracle, W, H, nf, seed):
     assert bad_rows <= max(1, len(kg) // 500)   # residual allowed by north_star, reported above
 
 
+@pytest.mark.parametrize("W,H,nf,scale,nlevels", [
+    (640, 480, 1000, 2.0, 4),      # word-gather resize at its widest tap span
+    (1241, 800, 1500, 3.0, 3),     # tap span > 12 bytes: byte-gather resize kernel; 59-px cells: generic FAST kernel
+    (752, 480, 800, 1.5, 5),
+    (640, 480, 1000, 1.1, 12),
+])
+def test_other_scale_factors(orbfe, oracle, W, H, nf, scale, nlevels):
+    img = synth.frame(W, H, 11)
+    ex = orbfe.ORBextractor(nf, scale, nlevels, 20, 7)
+    oc = oracle.OracleExtractor(nf, scale, nlevels, 20, 7)
+    kg, dg = ex(img)
+    ko, do = oc(img)
+    for l in range(nlevels):
+        assert np.array_equal(ex.pyramid_level(l), oc.level(l)), f"pyramid level {l}"
+        assert np.array_equal(ex.raw_keypoints(l), oc.raw(l)), f"FAST level {l}"
+    bad_rows, bad_bits, dang = _compare_frame(kg, dg, ko, do)
+    assert bad_rows <= max(1, len(kg) // 500)
+
+
 def test_batch_matches_single_and_oracle(orbfe, oracle):
     B = 6
     imgs = np.stack([synth.frame(640, 480, 10 + s) for s in range(B)])
