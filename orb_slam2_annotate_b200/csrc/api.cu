@@ -10,6 +10,7 @@
 
 #include "api_common.cuh"
 #include "orbfe_internal.cuh"
+#include <cuda.h>
 
 namespace orbfe {
 
@@ -51,6 +52,7 @@ struct orbfe_extractor {
     DevArray<int2> xtab;
     DevArray<int4> ytab;
     DevArray<int4> xq;
+    std::vector<CUtensorMap> tmaps;   // {level, blurred level} descriptors, passed to the kernel by value
     int lastBatch = 0, lastLaunches = 0;
     // optional per-stage timing (events on the handle's stream)
     bool profiling = false;
@@ -160,6 +162,32 @@ static bool resize_group_table(const std::vector<int2>& xt, int dw, std::vector<
         xq[3 * q + 2] = make_int4((int)c[3], 0, 0, 0);
     }
     return true;
+}
+
+// TMA descriptor of one level buffer seen as a [frames * h][pitch] byte tensor with a boxW x boxH
+// box (the orientation / descriptor kernel fetches its keypoint windows with it).  The encoder is
+// a driver entry point; it is resolved through the runtime so that liborbfe.so does not link libcuda.
+static int encode_level_map(CUtensorMap* m, void* base, int pitch, long long rows, int boxW, int boxH) {
+    typedef CUresult (*encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static encode_fn encode = nullptr;
+    if (!encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        cudaError_t ce = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+        if (ce != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn)
+            return fail(ORBFE_ERR_CUDA, "cudaGetDriverEntryPoint(cuTensorMapEncodeTiled)", ce);
+        encode = (encode_fn)fn;
+    }
+    const cuuint64_t dims[2] = {(cuuint64_t)pitch, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)pitch};
+    const cuuint32_t box[2] = {(cuuint32_t)boxW, (cuuint32_t)boxH};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = encode(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(ORBFE_ERR_CUDA, "cuTensorMapEncodeTiled failed");
+    return 0;
 }
 
 static inline long long align_up(long long v, long long a) { return (v + a - 1) / a * a; }
@@ -275,8 +303,20 @@ static int ensure_geometry(orbfe_extractor* e, int w, int h, int batch) {
         CU(cudaMemcpy(e->xtab.p, xall.data(), xall.size() * sizeof(int2), cudaMemcpyHostToDevice));
         CU(cudaMemcpy(e->ytab.p, yall.data(), yall.size() * sizeof(int4), cudaMemcpyHostToDevice));
     }
+    // TMA descriptors of the level / blurred-level buffers
+    {
+        static_assert(sizeof(CUtensorMap) == 128, "descriptor stride assumed by the kernel");
+        std::vector<CUtensorMap>& maps = e->tmaps;
+        maps.resize(2 * e->nlevels);
+        for (int l = 0; l < e->nlevels; l++) {
+            const LevelGeom& L = g.lv[l];
+            if ((rc = encode_level_map(&maps[2 * l], e->pyr.p + L.pyrOff, L.pitch, (long long)L.h * cap, kTmaRawW, kTmaRawH))) return rc;
+            if ((rc = encode_level_map(&maps[2 * l + 1], e->blur.p + L.pyrOff, L.pitch, (long long)L.h * cap, kTmaBlurW, kTmaBlurH))) return rc;
+        }
+    }
     DevBufs& d = e->d;
     std::memset(&d, 0, sizeof(d));
+    d.tmaps = e->tmaps.data();
     d.pyr = e->pyr.p; d.blur = e->blur.p; d.cellc = e->cellc.p; d.cellk = e->cellk.p;
     d.sel = e->sel.p; d.selc = e->selc.p; d.kps = e->kps.p; d.desc = e->desc.p;
     d.counts = e->counts.p; d.qt_xy = e->qt_xy.p; d.qt_node = e->qt_node.p; d.qtCap = g.cellSlots;

@@ -21,6 +21,9 @@
 namespace orbfe {
 
 constexpr int kMaxLevels = 16;
+// TMA boxes of the orientation / descriptor kernel.  A box must start on a 16-byte boundary, so
+// the 31 (37) wanted columns sit at offset 0..15 inside 48 (64) fetched ones.
+constexpr int kTmaRawW = 48, kTmaRawH = 31, kTmaBlurW = 64, kTmaBlurH = 37;
 constexpr int kEdgeThreshold = 19;   // ORBextractor.cc:75
 constexpr int kHalfPatch = 15;       // ORBextractor.cc:74
 constexpr int kPatchSize = 31;       // ORBextractor.cc:73
@@ -73,6 +76,7 @@ struct DevBufs {
     const int2* xtab[kMaxLevels];   // per dst x: {sx, a0 | a1<<16}
     const int4* ytab[kMaxLevels];   // per dst y: {row0, row1, b0, b1}
     const int4* xq[kMaxLevels];     // per 4 dst columns: {base, selA01, selB01, selA23}{selB23, c0..c2}{c3,-,-,-}; null = use xtab
+    const void* tmaps;              // HOST array CUtensorMap[2 * nlevels]: {level, blurred level} as [frames * h][pitch] u8 tensors
     bool xqSimple[kMaxLevels];      // row table strictly down-scaling: row1 == row0 + 1 and strictly increasing
     // quadtree point scratch for levels whose corner count exceeds the shared-memory arrays
     uint32_t* qt_xy;                // [B][L][qtCap]
