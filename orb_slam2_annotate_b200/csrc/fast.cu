@@ -195,9 +195,6 @@ struct WarpSmem {
     uint32_t win[WWIN][WS];
     uint8_t sc[WZ + 2][SCS];
     unsigned short list[WZ * WZ];
-    uint32_t bitmap[BMW + 1];
-    int bmpre[BMW + 1];
-    int counter;
     uint32_t pad;                                         // the last row's wc + 1 read stays inside
 };
 
@@ -211,7 +208,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32)
 fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __restrict__ pyr,
                        int* __restrict__ cellc, uint32_t* __restrict__ cellk, int cellLo, int cellHi) {
     using Smem = WarpSmem<WWIN>;
-    constexpr int WS = Smem::WS, SCS = Smem::SCS, BMW = Smem::BMW;
+    constexpr int WS = Smem::WS, SCS = Smem::SCS;
     static_assert(sizeof(S_sc_t<WWIN>) >= 4 * (WWIN - 6) * ((WWIN - 6 + 3) / 4 + 1), "task list must fit the score map");
     __shared__ Smem smem[kWarpsPerCta];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -262,130 +259,121 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __
     }
     const uint8_t* wb = reinterpret_cast<const uint8_t*>(&S.win[0][0]) + 4;   // byte (r, x) = wb[r*WS*4 + x]
 
+    // stage 1a lane mapping: a lane keeps one zone word column and walks the rows rpi at a time
+    const int rpi = small_div(32, rcp_nzc);                      // zone rows per warp step (nzc <= 12)
+    const int rsub = small_div(lane, rcp_nzc), cc1 = lane - rsub * nzc;
+    const bool act = rsub < rpi;
+    const uint32_t* wcol = &S.win[rsub][zc0 + cc1 + 1];
+    uint32_t zm = 0x80808080u;                                   // bytes of the lane's word inside the zone
+    {
+        const int xb = (zc0 + cc1) * 4;
+        if (xb < zx0) zm &= 0xFFFFFFFFu << (8 * (zx0 - xb));
+        if (xb + 4 > zx1) zm &= 0xFFFFFFFFu >> (8 * (xb + 4 - zx1));
+    }
+
     int total = 0;
     for (int pass = 0; pass < 2; pass++) {
         const int t = pass == 0 ? g.iniTh : g.minTh;
         const bool small_t = t < 128;
         const uint32_t cmpc = (uint32_t)(small_t ? 0x7F - t : 0x7F - (t - 128)) * 0x01010101u;
-        for (int i = lane; i <= BMW; i += 32) S.bitmap[i] = 0;
-        if (lane == 0) S.counter = 0;
         // ---- stage 1a: vertical pair (0,8) on every zone word; surviving words are compacted
         // (ballot order) into a task list that borrows the score map's storage
         uint32_t* tasks = reinterpret_cast<uint32_t*>(&S.sc[0][0]);
         int ntask = 0;
-        for (int base = 0; base < zh * nzc; base += 32) {
-            const int i = base + lane;
+        for (int r0 = 0; r0 < zh; r0 += rpi) {
+            const int r = r0 + rsub;
             uint32_t gmask = 0;
-            int r = 0, cc = 0;
-            if (i < zh * nzc) {
-                r = small_div(i, rcp_nzc), cc = i - r * nzc;
-                const int y = r + 3, wc = zc0 + cc + 1;          // window row, word column (+1 pad)
-                const uint32_t v = S.win[y][wc];
-                gmask = swar_gt(__vabsdiffu4(S.win[y + 3][wc], v), cmpc, small_t) |
-                        swar_gt(__vabsdiffu4(S.win[y - 3][wc], v), cmpc, small_t);
-                // bytes of this word inside the zone
-                const int xb = (zc0 + cc) * 4;
-                uint32_t zm = 0x80808080u;
-                if (xb < zx0) zm &= 0xFFFFFFFFu << (8 * (zx0 - xb));
-                if (xb + 4 > zx1) zm &= 0xFFFFFFFFu >> (8 * (xb + 4 - zx1));
-                gmask &= zm;
+            if (act && r < zh) {
+                const uint32_t* pw = wcol + r0 * WS;             // (window row r, word column wc)
+                const uint32_t v = pw[3 * WS];
+                gmask = (swar_gt(__vabsdiffu4(pw[6 * WS], v), cmpc, small_t) |
+                         swar_gt(__vabsdiffu4(pw[0], v), cmpc, small_t)) & zm;
             }
             const uint32_t bal = __ballot_sync(0xFFFFFFFFu, gmask != 0);
-            if (gmask) tasks[ntask + __popc(bal & ((1u << lane) - 1u))] = gmask | (uint32_t)r | ((uint32_t)cc << 8);
+            if (gmask) tasks[ntask + __popc(bal & ((1u << lane) - 1u))] = gmask | (uint32_t)r | ((uint32_t)cc1 << 8);
             ntask += __popc(bal);
         }
         __syncwarp();
-        // ---- stage 1b: pairs (4,12), (2,10), (6,14) on the surviving words, all lanes busy
-        for (int i = lane; i < ntask; i += 32) {
-            const uint32_t e = tasks[i];
-            uint32_t gmask = e & 0x80808080u;
-            const int r = e & 0x7F, cc = (e >> 8) & 0x7F;
-            const int y = r + 3, wc = zc0 + cc + 1;
-            const uint32_t v = S.win[y][wc];
-            const uint32_t wl = S.win[y][wc - 1], wr = S.win[y][wc + 1];
-            gmask &= swar_gt(__vabsdiffu4(__funnelshift_r(v, wr, 24), v), cmpc, small_t) |
-                     swar_gt(__vabsdiffu4(__funnelshift_r(wl, v, 8), v), cmpc, small_t);
-            const uint32_t r2 = __funnelshift_r(S.win[y + 2][wc], S.win[y + 2][wc + 1], 16);
-            const uint32_t r10 = __funnelshift_r(S.win[y - 2][wc - 1], S.win[y - 2][wc], 16);
-            gmask &= swar_gt(__vabsdiffu4(r2, v), cmpc, small_t) | swar_gt(__vabsdiffu4(r10, v), cmpc, small_t);
-            const uint32_t r6 = __funnelshift_r(S.win[y - 2][wc], S.win[y - 2][wc + 1], 16);
-            const uint32_t r14 = __funnelshift_r(S.win[y + 2][wc - 1], S.win[y + 2][wc], 16);
-            gmask &= swar_gt(__vabsdiffu4(r6, v), cmpc, small_t) | swar_gt(__vabsdiffu4(r14, v), cmpc, small_t);
-            if (!gmask) continue;
-            const int xb = (zc0 + cc) * 4;
-            int pos = atomicAdd(&S.counter, __popc(gmask));
-#pragma unroll
-            for (int b = 0; b < 4; b++)
-                if (gmask & (0x80u << (8 * b))) S.list[pos++] = (unsigned short)((r << 8) | (xb + b - zx0));
-        }
-        __syncwarp();
-        // the task list is consumed: zero the score map
-        for (int i = lane; i < (zh + 2) * (SCS / 4); i += 32) reinterpret_cast<uint32_t*>(&S.sc[0][0])[i] = 0;
-        __syncwarp();
-        // ---- stage 2: exact test + strength on the survivors
-        const int ncand = S.counter;
-        __syncwarp();
-        if (lane == 0) S.counter = 0;
-        __syncwarp();
-        for (int base = 0; base < ncand; base += 32) {
+        // ---- stage 1b: pairs (4,12), (2,10), (6,14) on the surviving words, all lanes busy.
+        // Every list from here on is built with warp scans in task order, which is row-major:
+        // the emitted corners come out in cv::FAST's order without sorting or atomics.
+        int ncand = 0;
+        for (int base = 0; base < ntask; base += 32) {
             const int i = base + lane;
-            int e = 0, s = 0;
-            if (i < ncand) e = S.list[i];
-            __syncwarp();
-            if (i < ncand) {
-                const int r = e >> 8, cc = e & 0xFF;
-                s = corner_strength<false>(wb + (r + 3) * (WS * 4) + zx0 + cc, WS * 4, t);
-                if (s) {
-                    S.sc[r + 1][cc + 1] = (uint8_t)s;
-                    S.list[atomicAdd(&S.counter, 1)] = (unsigned short)e;
-                }
+            uint32_t gmask = 0;
+            int r = 0, xz = 0;
+            if (i < ntask) {
+                const uint32_t e = tasks[i];
+                gmask = e & 0x80808080u;
+                r = e & 0x7F;
+                const int cc = (e >> 8) & 0x7F;
+                const int y = r + 3, wc = zc0 + cc + 1;
+                xz = (zc0 + cc) * 4 - zx0;                        // zone column of the word's byte 0
+                const uint32_t v = S.win[y][wc];
+                const uint32_t wl = S.win[y][wc - 1], wr = S.win[y][wc + 1];
+                gmask &= swar_gt(__vabsdiffu4(__funnelshift_r(v, wr, 24), v), cmpc, small_t) |
+                         swar_gt(__vabsdiffu4(__funnelshift_r(wl, v, 8), v), cmpc, small_t);
+                const uint32_t r2 = __funnelshift_r(S.win[y + 2][wc], S.win[y + 2][wc + 1], 16);
+                const uint32_t r10 = __funnelshift_r(S.win[y - 2][wc - 1], S.win[y - 2][wc], 16);
+                gmask &= swar_gt(__vabsdiffu4(r2, v), cmpc, small_t) | swar_gt(__vabsdiffu4(r10, v), cmpc, small_t);
+                const uint32_t r6 = __funnelshift_r(S.win[y - 2][wc], S.win[y - 2][wc + 1], 16);
+                const uint32_t r14 = __funnelshift_r(S.win[y + 2][wc - 1], S.win[y + 2][wc], 16);
+                gmask &= swar_gt(__vabsdiffu4(r6, v), cmpc, small_t) | swar_gt(__vabsdiffu4(r14, v), cmpc, small_t);
             }
-        }
-        __syncwarp();
-        // ---- stage 3: 3x3 strict maximum inside the zone, survivors into the bitmap
-        const int ncorn = S.counter;
-        for (int i = lane; i < ncorn; i += 32) {
-            const int e = S.list[i], r = e >> 8, cc = e & 0xFF;
-            const int s = S.sc[r + 1][cc + 1];
-            const bool keep = s > S.sc[r][cc] && s > S.sc[r][cc + 1] && s > S.sc[r][cc + 2] &&
-                              s > S.sc[r + 1][cc] && s > S.sc[r + 1][cc + 2] && s > S.sc[r + 2][cc] &&
-                              s > S.sc[r + 2][cc + 1] && s > S.sc[r + 2][cc + 2];
-            if (keep) {
-                const int bit = r * zw + cc;
-                atomicOr(&S.bitmap[bit >> 5], 1u << (bit & 31));
-            }
-        }
-        __syncwarp();
-        // ---- ordered emission: exclusive popc prefix over the bitmap words
-        const int nbw = (zw * zh + 31) >> 5;
-        int carry = 0;
-        for (int base = 0; base < nbw; base += 32) {
-            const int w = base + lane;
-            const int v = w < nbw ? __popc(S.bitmap[w]) : 0;
-            int inc = v;
+            const int k = __popc(gmask);
+            int inc = k;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 const int u = __shfl_up_sync(0xFFFFFFFFu, inc, o);
                 if (lane >= o) inc += u;
             }
-            if (w < nbw) S.bmpre[w] = carry + inc - v;
-            carry += __shfl_sync(0xFFFFFFFFu, inc, 31);
+            int pos = ncand + inc - k;
+#pragma unroll
+            for (int b = 0; b < 4; b++)
+                if (gmask & (0x80u << (8 * b))) S.list[pos++] = (unsigned short)((r << 8) | (xz + b));
+            ncand += __shfl_sync(0xFFFFFFFFu, inc, 31);
         }
-        total = carry;
         __syncwarp();
-        if (total > 0) {
-            for (int i = lane; i < ncorn; i += 32) {
-                const int e = S.list[i], r = e >> 8, cc = e & 0xFF;
-                const int bit = r * zw + cc;
-                const uint32_t word = S.bitmap[bit >> 5];
-                if (word & (1u << (bit & 31))) {
-                    const int pos = S.bmpre[bit >> 5] + __popc(word & ((1u << (bit & 31)) - 1u));
-                    if (pos < L.cellCap)
-                        out[pos] = pack_kp(cc + 3 + cj * L.wCell, r + 3 + ci * L.hCell, S.sc[r + 1][cc + 1] - 1);
-                }
+        // the task list is consumed: zero the score map
+        for (int i = lane; i < (zh + 2) * (SCS / 4); i += 32) reinterpret_cast<uint32_t*>(&S.sc[0][0])[i] = 0;
+        __syncwarp();
+        // ---- stage 2: exact test + strength on the survivors, compacted in place
+        int ncorn = 0;
+        for (int base = 0; base < ncand; base += 32) {
+            const int i = base + lane;
+            int e = 0, s = 0;
+            if (i < ncand) {
+                e = S.list[i];
+                const int r = e >> 8, cc = e & 0xFF;
+                s = corner_strength<false>(wb + (r + 3) * (WS * 4) + zx0 + cc, WS * 4, t);
+                if (s) S.sc[r + 1][cc + 1] = (uint8_t)s;
             }
-            break;
+            const uint32_t bal = __ballot_sync(0xFFFFFFFFu, s != 0);
+            __syncwarp();                                 // list reads above before the in-place writes
+            if (s) S.list[ncorn + __popc(bal & ((1u << lane) - 1u))] = (unsigned short)e;
+            ncorn += __popc(bal);
         }
+        __syncwarp();
+        // ---- stage 3: 3x3 strict maximum inside the zone; survivors leave in list order
+        total = 0;
+        for (int base = 0; base < ncorn; base += 32) {
+            const int i = base + lane;
+            bool keep = false;
+            int r = 0, cc = 0, s = 0;
+            if (i < ncorn) {
+                const int e = S.list[i];
+                r = e >> 8, cc = e & 0xFF;
+                s = S.sc[r + 1][cc + 1];
+                keep = s > S.sc[r][cc] && s > S.sc[r][cc + 1] && s > S.sc[r][cc + 2] &&
+                       s > S.sc[r + 1][cc] && s > S.sc[r + 1][cc + 2] && s > S.sc[r + 2][cc] &&
+                       s > S.sc[r + 2][cc + 1] && s > S.sc[r + 2][cc + 2];
+            }
+            const uint32_t bal = __ballot_sync(0xFFFFFFFFu, keep);
+            const int pos = total + __popc(bal & ((1u << lane) - 1u));
+            if (keep && pos < L.cellCap) out[pos] = pack_kp(cc + 3 + cj * L.wCell, r + 3 + ci * L.hCell, s - 1);
+            total += __popc(bal);
+        }
+        if (total > 0) break;
         __syncwarp();
     }
     if (lane == 0) *out_cnt = min(total, L.cellCap);
