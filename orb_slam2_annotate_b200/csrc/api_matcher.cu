@@ -174,6 +174,8 @@ int orbfe_search_init(orbfe_matcher* m, const orbfe_frame_view* f1, const orbfe_
     a.prev = d_prev; a.m12 = d_m12; a.nmatches = d_nm;
     a.grid = grid_of(f2);
     a.window = window; a.ratio = nnratio; a.checkOri = check_orientation;
+    if ((rc = m->scratch[3].ensure(search_init_scratch_bytes(cap, 1)))) return rc;
+    search_init_carve(a, m->scratch[3].p, 1);
     launch_search_init(a, 1, s);
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(prev_matched, d_prev, sizeof(float) * 2 * n1, cudaMemcpyDeviceToHost, s));
@@ -199,6 +201,9 @@ int orbfe_search_init_consecutive_device(orbfe_matcher* m, const orbfe_keypoint*
     a.grid.minX = min_x; a.grid.minY = min_y;
     a.grid.invW = 64.0f / (max_x - min_x); a.grid.invH = 48.0f / (max_y - min_y);
     a.window = window; a.ratio = nnratio; a.checkOri = check_orientation;
+    int rc;
+    if ((rc = m->scratch[3].ensure(search_init_scratch_bytes(cap, nframes - 1)))) return rc;
+    search_init_carve(a, m->scratch[3].p, nframes - 1);
     launch_search_init(a, nframes - 1, m->stream);
     CU(cudaGetLastError());
     return ORBFE_OK;

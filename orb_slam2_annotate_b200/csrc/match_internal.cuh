@@ -22,6 +22,14 @@ struct InitArgs {
     float* prev;                 // [pairs][cap][2] vbPrevMatched in/out, or NULL: F1 keypoint positions
     int* m12;                    // [pairs][cap] vnMatches12
     int* nmatches;               // [pairs]
+    // scratch (search_init_carve): CSR grid of the second frame and per-query candidate lists
+    int* cell_end;               // [pairs][64*48]
+    unsigned short* items;       // [pairs][cap]
+    uint32_t* tk_key;            // [pairs][cap][8]
+    unsigned short* tk_idx;      // [pairs][cap][8]
+    unsigned short* tk_total;    // [pairs][cap]
+    unsigned short* qlist;       // [pairs][cap] octave-0 keypoints of the first frame, in order
+    int* nq;                     // [pairs]
     GridGeom grid;
     int window;
     float ratio;
@@ -66,7 +74,8 @@ struct StereoArgs {
     int* sad;           // per left keypoint: truncated best SAD, or -1 when no match
 };
 
-size_t search_init_smem(int cap);
+size_t search_init_scratch_bytes(int cap, int npairs);
+void search_init_carve(InitArgs& a, void* scratch, int npairs);
 int launch_search_init(const InitArgs& a, int npairs, cudaStream_t st);
 int launch_local_grid_and_count(const LocalArgs& a, cudaStream_t st);
 int launch_local_fill(const LocalArgs& a, cudaStream_t st);

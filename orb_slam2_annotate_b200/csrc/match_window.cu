@@ -122,7 +122,8 @@ __device__ void three_maxima(const int* hist, int& ind1, int& ind2, int& ind3) {
 }
 
 // ---------------------------------------------------------------------------------------
-// SearchForInitialization — one warp per frame pair.
+// SearchForInitialization — three kernels: grids (CTA per pair), candidate lists (warp per
+// query, fully parallel), greedy replay (warp per pair).
 
 constexpr int SI_WARPS = 8;      // warps per frame pair
 constexpr int SI_QB = 256;       // queries per phase-A / phase-B block
@@ -173,212 +174,318 @@ __device__ void eval_query_filtered(const QueryCtx& c, const uint32_t q[8], floa
     g2 = warp_min(b1 == g1 ? b2 : b1);
 }
 
-__global__ void __launch_bounds__(SI_WARPS * 32)
-search_init_kernel(const __grid_constant__ InitArgs a) {
+// ascending sort of one 32-bit key per lane / final merge of a bitonic sequence
+__device__ __forceinline__ uint32_t bitonic_merge32(uint32_t v, int lane) {
+#pragma unroll
+    for (int j = 16; j > 0; j >>= 1) {
+        const uint32_t o = __shfl_xor_sync(FULL, v, j);
+        v = (lane & j) ? max(v, o) : min(v, o);
+    }
+    return v;
+}
+__device__ __forceinline__ uint32_t bitonic_sort32(uint32_t v, int lane) {
+#pragma unroll
+    for (int k = 2; k < 32; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            const uint32_t o = __shfl_xor_sync(FULL, v, j);
+            v = (((lane & k) != 0) != ((lane & j) != 0)) ? max(v, o) : min(v, o);
+        }
+    }
+    return bitonic_merge32(v, lane);
+}
+
+// Kernel G — the CSR grid of every pair's second frame, one CTA per pair: shared-memory
+// histogram, block scan, atomic fill, then every cell's (few) items are put back into keypoint
+// order, which is the order AssignFeaturesToGrid pushes them in.
+constexpr int SG_THREADS = 256;
+__global__ void __launch_bounds__(SG_THREADS)
+search_init_grid_kernel(const __grid_constant__ InitArgs a) {
     extern __shared__ __align__(16) unsigned char sm[];
-    __shared__ uint32_t tk_key[SI_QB][SI_K];
-    __shared__ unsigned short tk_idx[SI_QB][SI_K];
-    __shared__ unsigned short tk_total[SI_QB];      // candidates passing the static tests (saturated)
-    __shared__ unsigned short clist[SI_WARPS][SI_CL];
-    __shared__ int s_nq;
+    int* cur = (int*)sm;                                         // NCELL: count -> start -> end
+    unsigned short* its = (unsigned short*)(cur + NCELL);        // cap
+    __shared__ int wsum[SG_THREADS / 32];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, p = blockIdx.x;
+    const int fb = a.pairs ? a.pairs[p].y : p + 1;
+    const int n2 = a.counts[fb];
+    const orbfe_keypoint* kp2 = a.kps + (long long)fb * a.cap;
+    for (int c = tid; c < NCELL; c += SG_THREADS) cur[c] = 0;
+    __syncthreads();
+    for (int i = tid; i < n2; i += SG_THREADS) {
+        const int c = pos_in_grid(a.grid, kp2[i].x, kp2[i].y);
+        if (c >= 0) atomicAdd(&cur[c], 1);
+    }
+    __syncthreads();
+    constexpr int CPT = NCELL / SG_THREADS;                      // 12 consecutive cells per thread
+    int cnt[CPT], local = 0;
+#pragma unroll
+    for (int k = 0; k < CPT; k++) { cnt[k] = cur[tid * CPT + k]; local += cnt[k]; }
+    int inc = local;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int u = __shfl_up_sync(FULL, inc, o);
+        if (lane >= o) inc += u;
+    }
+    if (lane == 31) wsum[wid] = inc;
+    __syncthreads();
+    int off = inc - local;
+    for (int w = 0; w < wid; w++) off += wsum[w];
+#pragma unroll
+    for (int k = 0; k < CPT; k++) { cur[tid * CPT + k] = off; off += cnt[k]; }
+    __syncthreads();
+    for (int i = tid; i < n2; i += SG_THREADS) {
+        const int c = pos_in_grid(a.grid, kp2[i].x, kp2[i].y);
+        if (c >= 0) its[atomicAdd(&cur[c], 1)] = (unsigned short)i;
+    }
+    __syncthreads();
+    for (int c = tid; c < NCELL; c += SG_THREADS) {              // insertion sort of the cell's items
+        const int s0 = c ? cur[c - 1] : 0, e0 = cur[c];
+        for (int i = s0 + 1; i < e0; i++) {
+            const unsigned short v = its[i];
+            int j = i - 1;
+            while (j >= s0 && its[j] > v) { its[j + 1] = its[j]; j--; }
+            its[j + 1] = v;
+        }
+    }
+    __syncthreads();
+    int* cell_end = a.cell_end + (long long)p * NCELL;
+    unsigned short* items = a.items + (long long)p * a.cap;
+    for (int c = tid; c < NCELL; c += SG_THREADS) cell_end[c] = cur[c];
+    const int nin = cur[NCELL - 1];
+    for (int i = tid; i < nin; i += SG_THREADS) items[i] = its[i];
+    // queries: keypoints of the first frame on octave 0, in index order (:483-489)
+    const int fa = a.pairs ? a.pairs[p].x : p;
+    const int n1 = a.counts[fa];
+    const orbfe_keypoint* kp1 = a.kps + (long long)fa * a.cap;
+    unsigned short* qlist = a.qlist + (long long)p * a.cap;
+    int nq = 0;
+    for (int base = 0; base < n1; base += SG_THREADS) {
+        const int i = base + tid;
+        const bool ok = i < n1 && kp1[i].octave <= 0;
+        const unsigned b = __ballot_sync(FULL, ok);
+        __syncthreads();                                   // wsum of the previous round was consumed
+        if (lane == 0) wsum[wid] = __popc(b);
+        __syncthreads();
+        int off = nq;
+        for (int w = 0; w < wid; w++) off += wsum[w];
+        if (ok) qlist[off + __popc(b & ((1u << lane) - 1u))] = (unsigned short)i;
+        for (int w = 0; w < SG_THREADS / 32; w++) nq += wsum[w];
+    }
+    if (tid == 0) a.nq[p] = nq;
+}
+
+// Kernel A — one warp per query (octave-0 keypoint of the first frame): its SI_K best candidates
+// in the second frame without the running filter (which depends on earlier queries).  SA_CTAS
+// CTAs share a pair; a warp takes every (SA_CTAS * SI_WARPS)-th query.
+constexpr int SA_CTAS = 4;
+__global__ void __launch_bounds__(SI_WARPS * 32)
+search_init_topk_kernel(const __grid_constant__ InitArgs a) {
+    __shared__ unsigned short clist[SI_WARPS][SI_CL];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, p = blockIdx.y;
+    const int nq = a.nq[p];
+    int q = blockIdx.x * SI_WARPS + wid;
+    if (q >= nq) return;
     const int fa = a.pairs ? a.pairs[p].x : p, fb = a.pairs ? a.pairs[p].y : p + 1;
-    const int n1 = a.counts[fa], n2 = a.counts[fb];
+    const orbfe_keypoint* kp1 = a.kps + (long long)fa * a.cap;
+    const orbfe_keypoint* kp2 = a.kps + (long long)fb * a.cap;
+    const uint8_t* d1 = a.desc + (long long)fa * a.cap * 32;
+    const uint8_t* d2 = a.desc + (long long)fb * a.cap * 32;
+    const float* prev = a.prev ? a.prev + (long long)p * a.cap * 2 : nullptr;
+    const int* cell_end = a.cell_end + (long long)p * NCELL;
+    const unsigned short* items = a.items + (long long)p * a.cap;
+    const unsigned short* qlist = a.qlist + (long long)p * a.cap;
+    QueryCtx c{kp2, d2, cell_end, items, nullptr, a.grid, (float)a.window};
+
+    for (; q < nq; q += SA_CTAS * SI_WARPS) {
+        const int i1 = qlist[q];
+        const long long slot = (long long)p * a.cap + q;
+        const float qx = prev ? prev[2 * i1] : kp1[i1].x, qy = prev ? prev[2 * i1 + 1] : kp1[i1].y;
+        int cx0, cx1, cy0, cy1, total = 0;
+        bool direct = false;
+        __syncwarp();                                  // the previous query's clist readers are done
+        if (cell_window(a.grid, qx, qy, c.r, cx0, cx1, cy0, cy1)) {
+            // item range of every grid column of the window (one lane per column), then the
+            // ranges are concatenated into the warp's candidate list in column order
+            for (int cb = cx0; cb <= cx1 && !direct; cb += 32) {
+                const int ix = cb + lane;
+                int s0 = 0, len = 0;
+                if (ix <= cx1) {
+                    const int c0 = ix * GR + cy0;
+                    s0 = c0 ? cell_end[c0 - 1] : 0;
+                    len = cell_end[ix * GR + cy1] - s0;
+                }
+                int inc = len;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int u = __shfl_up_sync(FULL, inc, o);
+                    if (lane >= o) inc += u;
+                }
+                const int sum = __shfl_sync(FULL, inc, 31);
+                if (total + sum > SI_CL) { direct = true; break; }
+                const int off = total + inc - len;
+                for (int j = 0; j < len; j++) clist[wid][off + j] = items[s0 + j];
+                total += sum;
+            }
+        }
+        __syncwarp();
+        if (direct) {
+            if (lane == 0) a.tk_total[slot] = 0xFFFF;
+            continue;
+        }
+        uint32_t qd[8];
+        load_row(qd, d1 + 32 * (long long)i1);
+        uint32_t top = KEY_INF;
+        int npass = 0;
+        for (int kb = 0; kb < total; kb += 32) {       // 32 candidates per round, one per lane
+            const int j = kb + lane;
+            uint32_t key = KEY_INF;
+            if (j < total) {
+                const int i2 = clist[wid][j];
+                if (cand_ok(c, i2, qx, qy)) {
+                    key = ((uint32_t)hamming256(qd, d2 + 32 * (long long)i2) << 20) | (uint32_t)j;
+                    npass++;
+                }
+            }
+            // keep the 32 smallest keys sorted across the lanes: min with the reversed sorted
+            // block is a bitonic sequence holding them; five merge steps sort it
+            const uint32_t blk = bitonic_sort32(key, lane);
+            top = kb == 0 ? blk : bitonic_merge32(min(top, __shfl_sync(FULL, blk, 31 - lane)), lane);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) npass += __shfl_xor_sync(FULL, npass, o);
+        if (lane < SI_K) {
+            a.tk_key[slot * SI_K + lane] = top;
+            a.tk_idx[slot * SI_K + lane] = top == KEY_INF ? 0 : clist[wid][top & 0xFFFFFu];
+        }
+        if (lane == 0) a.tk_total[slot] = (unsigned short)npass;
+    }
+}
+
+// Kernel B — one warp per pair replays the reference's greedy bookkeeping over the queries in
+// order, from the per-query candidate lists of kernel A (staged through shared memory SI_QB
+// queries at a time).  The loop is one long dependent chain, so it is kept short: all state is
+// in shared memory, every lane performs the same scalar updates (no divergent single-lane
+// sections, no warp syncs: a lane only ever reads what it wrote itself), and the rotation
+// histogram is built afterwards from the recorded (query, match) events.  A query whose kept
+// list cannot decide falls back to the filtered scan of its window.
+__global__ void __launch_bounds__(32)
+search_init_greedy_kernel(const __grid_constant__ InitArgs a) {
+    extern __shared__ __align__(16) unsigned char sm[];
+    __shared__ __align__(16) uint32_t tk_key[SI_QB][SI_K];
+    __shared__ __align__(16) unsigned short tk_idx[SI_QB][SI_K];
+    __shared__ unsigned short tk_total[SI_QB];
+    __shared__ unsigned short qi1[SI_QB];
+    __shared__ int hist[32];
+    const int lane = threadIdx.x, p = blockIdx.x;
+    const int fa = a.pairs ? a.pairs[p].x : p, fb = a.pairs ? a.pairs[p].y : p + 1;
+    const int n1 = a.counts[fa], n2 = a.counts[fb], nq = a.nq[p];
     const orbfe_keypoint* kp1 = a.kps + (long long)fa * a.cap;
     const orbfe_keypoint* kp2 = a.kps + (long long)fb * a.cap;
     const uint8_t* d1 = a.desc + (long long)fa * a.cap * 32;
     const uint8_t* d2 = a.desc + (long long)fb * a.cap * 32;
     int* m12 = a.m12 + (long long)p * a.cap;
     float* prev = a.prev ? a.prev + (long long)p * a.cap * 2 : nullptr;
-
-    int* cell_end = (int*)sm;                                    // NCELL
-    int* hist = cell_end + NCELL;                                // 32
-    unsigned short* items = (unsigned short*)(hist + 32);        // cap
-    unsigned short* m21 = items + a.cap;                         // cap   (0xFFFF = none)
-    unsigned short* qlist = m21 + a.cap;                         // cap   octave-0 queries of F1, in order
-    unsigned char* mdist = (unsigned char*)(qlist + a.cap);      // cap   (255 = INT_MAX)
-    unsigned char* binof = mdist + a.cap;                        // cap   (255 = not in rotHist)
-
-    for (int i = tid; i < n1; i += SI_WARPS * 32) { m12[i] = -1; binof[i] = 255; }
-    for (int i = tid; i < n2; i += SI_WARPS * 32) { m21[i] = 0xFFFF; mdist[i] = 255; }
-    if (tid < 32) hist[tid] = 0;
-    if (wid == 0) {
-        warp_build_grid(a.grid, kp2, n2, cell_end, items);
-        // queries: keypoints of F1 on octave 0, reference order (:483-489)
-        int nq = 0;
-        for (int base = 0; base < n1; base += 32) {
-            const int i = base + lane;
-            const bool ok = i < n1 && kp1[i].octave <= 0;
-            const unsigned b = __ballot_sync(FULL, ok);
-            if (ok) qlist[nq + __popc(b & ((1u << lane) - 1u))] = (unsigned short)i;
-            nq += __popc(b);
-        }
-        if (lane == 0) s_nq = nq;
-    }
-    __syncthreads();
-    const int nq = s_nq;
-    QueryCtx c{kp2, d2, cell_end, items, mdist, a.grid, (float)a.window};
-    const float factor = 1.0f / HISTO;                                                  // :476
+    const unsigned short* qlist = a.qlist + (long long)p * a.cap;
+    unsigned short* m12s = (unsigned short*)sm;                  // cap   vnMatches12 (0xFFFF = -1)
+    unsigned short* m21 = m12s + a.cap;                          // cap   vnMatches21 (0xFFFF = none)
+    unsigned short* ev = m21 + a.cap;                            // cap   match made by query i1 at its turn (rotHist entry)
+    unsigned char* mdist = (unsigned char*)(ev + a.cap);         // cap   vMatchedDistance (255 = INT_MAX)
+    for (int i = lane; i < n1; i += 32) { m12s[i] = 0xFFFF; ev[i] = 0xFFFF; }
+    for (int i = lane; i < n2; i += 32) { m21[i] = 0xFFFF; mdist[i] = 255; }
+    hist[lane] = 0;
+    __syncwarp();
+    QueryCtx c{kp2, d2, a.cell_end + (long long)p * NCELL, a.items + (long long)p * a.cap, mdist, a.grid, (float)a.window};
+    const long long slot0 = (long long)p * a.cap;
 
     for (int qb = 0; qb < nq; qb += SI_QB) {
         const int qn = min(SI_QB, nq - qb);
-        // ---- phase A (all warps): the SI_K best candidates of every query, no running filter
-        for (int qi = wid; qi < qn; qi += SI_WARPS) {
-            const int i1 = qlist[qb + qi];
-            const float qx = prev ? prev[2 * i1] : kp1[i1].x, qy = prev ? prev[2 * i1 + 1] : kp1[i1].y;
-            int cx0, cx1, cy0, cy1, total = 0;
-            bool direct = false;
-            if (cell_window(a.grid, qx, qy, c.r, cx0, cx1, cy0, cy1)) {
-                // item range of every grid column of the window (one lane per column), then the
-                // ranges are concatenated into the warp's candidate list in column order
-                for (int cb = cx0; cb <= cx1 && !direct; cb += 32) {
-                    const int ix = cb + lane;
-                    int s = 0, len = 0;
-                    if (ix <= cx1) {
-                        const int c0 = ix * GR + cy0;
-                        s = c0 ? cell_end[c0 - 1] : 0;
-                        len = cell_end[ix * GR + cy1] - s;
-                    }
-                    int inc = len;
-#pragma unroll
-                    for (int o = 1; o < 32; o <<= 1) {
-                        const int u = __shfl_up_sync(FULL, inc, o);
-                        if (lane >= o) inc += u;
-                    }
-                    const int sum = __shfl_sync(FULL, inc, 31);
-                    if (total + sum > SI_CL) { direct = true; break; }
-                    const int off = total + inc - len;
-                    for (int j = 0; j < len; j++) clist[wid][off + j] = items[s + j];
-                    total += sum;
-                }
-            }
-            __syncwarp();
-            uint32_t keys[SI_CL / 32];
-#pragma unroll
-            for (int k = 0; k < SI_CL / 32; k++) keys[k] = KEY_INF;
-            int npass = 0;
-            if (!direct) {
-                uint32_t q[8];
-                load_row(q, d1 + 32 * (long long)i1);
-#pragma unroll
-                for (int k = 0; k < SI_CL / 32; k++) {
-                    if (32 * k >= total) break;
-                    const int j = lane + 32 * k;
-                    if (j < total) {
-                        const int i2 = clist[wid][j];
-                        if (cand_ok(c, i2, qx, qy)) {
-                            keys[k] = ((uint32_t)hamming256(q, d2 + 32 * (long long)i2) << 20) | (uint32_t)j;
-                            npass++;
-                        }
-                    }
-                }
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) npass += __shfl_xor_sync(FULL, npass, o);
-                // extract the SI_K smallest keys of the warp, in order: warp minimum of the lane
-                // minima; only the owning lane rescans its keys
-                uint32_t lm = KEY_INF;
-#pragma unroll
-                for (int k = 0; k < SI_CL / 32; k++) lm = min(lm, keys[k]);
-                for (int t = 0; t < SI_K; t++) {
-                    const uint32_t gm = warp_min(lm);
-                    if (lane == 0) {
-                        tk_key[qi][t] = gm;
-                        tk_idx[qi][t] = gm == KEY_INF ? 0 : clist[wid][gm & 0xFFFFFu];
-                    }
-                    if (gm == KEY_INF) {
-                        if (lane == 0) for (int tt = t + 1; tt < SI_K; tt++) tk_key[qi][tt] = KEY_INF;
-                        break;
-                    }
-                    if (lm == gm) {
-                        lm = KEY_INF;
-#pragma unroll
-                        for (int k = 0; k < SI_CL / 32; k++) {
-                            if (keys[k] == gm) keys[k] = KEY_INF;
-                            lm = min(lm, keys[k]);
-                        }
-                    }
-                }
-            }
-            if (lane == 0) tk_total[qi] = direct ? 0xFFFF : (unsigned short)npass;
-            __syncwarp();
+        {   // stage the block's candidate lists (16-byte pieces; slots are 16-byte multiples)
+            const uint4* gk = reinterpret_cast<const uint4*>(a.tk_key + (slot0 + qb) * SI_K);
+            const uint4* gi = reinterpret_cast<const uint4*>(a.tk_idx + (slot0 + qb) * SI_K);
+            for (int i = lane; i < qn * SI_K / 4; i += 32) reinterpret_cast<uint4*>(&tk_key[0][0])[i] = __ldg(gk + i);
+            for (int i = lane; i < qn * SI_K / 8; i += 32) reinterpret_cast<uint4*>(&tk_idx[0][0])[i] = __ldg(gi + i);
+            for (int i = lane; i < qn; i += 32) { tk_total[i] = a.tk_total[slot0 + qb + i]; qi1[i] = qlist[qb + i]; }
         }
-        __syncthreads();
-        // ---- phase B (warp 0): the reference's greedy bookkeeping, queries in order
-        if (wid == 0) {
-            for (int qi = 0; qi < qn; qi++) {
-                const int i1 = qlist[qb + qi];
-                const int total = tk_total[qi];
-                uint32_t g1, g2;
-                int best;
-                bool need_full = total == 0xFFFF;
-                if (!need_full) {
-                    uint32_t key = KEY_INF;
-                    int idx = 0;
-                    if (lane < SI_K) { key = tk_key[qi][lane]; idx = tk_idx[qi][lane]; }
-                    const bool alive = key != KEY_INF && !(mdist[idx] != 255 && (int)mdist[idx] <= (int)(key >> 20));
-                    unsigned m = __ballot_sync(FULL, alive);
-                    const int l1 = __ffs(m) - 1;
-                    g1 = l1 >= 0 ? __shfl_sync(FULL, key, l1) : KEY_INF;
-                    best = l1 >= 0 ? __shfl_sync(FULL, idx, l1) : -1;
-                    if (l1 >= 0) m &= m - 1;
-                    const int l2 = __ffs(m) - 1;
-                    g2 = l2 >= 0 ? __shfl_sync(FULL, key, l2) : KEY_INF;
-                    // the kept list may hide further candidates: only matters when a match is still possible
-                    if (total > SI_K && (l1 < 0 || ((int)(g1 >> 20) <= TH_LOW && l2 < 0))) need_full = true;
-                }
-                if (need_full) {
-                    const float qx = prev ? prev[2 * i1] : kp1[i1].x, qy = prev ? prev[2 * i1 + 1] : kp1[i1].y;
-                    uint32_t q[8];
-                    load_row(q, d1 + 32 * (long long)i1);
-                    eval_query_filtered(c, q, qx, qy, g1, g2, best);
-                }
-                if (g1 == KEY_INF) continue;
-                const int bestDist = (int)(g1 >> 20);
-                const float second = g2 == KEY_INF ? (float)INT_MAX : (float)(int)(g2 >> 20);
-                if (bestDist <= TH_LOW && (float)bestDist < __fmul_rn(second, a.ratio)) {   // :532-534
-                    if (lane == 0) {
-                        if (m21[best] != 0xFFFF) m12[m21[best]] = -1;                       // :536-540
-                        m12[i1] = best;
-                        m21[best] = (unsigned short)i1;
-                        mdist[best] = (unsigned char)bestDist;
-                        if (a.checkOri) {                                                   // :549-559
-                            float rot = __fsub_rn(kp1[i1].angle, kp2[best].angle);
-                            if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
-                            int bin = (int)roundf(__fmul_rn(rot, factor));
-                            if (bin == HISTO) bin = 0;
-                            binof[i1] = (unsigned char)bin;
-                            hist[bin]++;
-                        }
-                    }
-                    __syncwarp();
-                }
+        __syncwarp();
+        for (int qi = 0; qi < qn; qi++) {
+            const int total = tk_total[qi];
+            uint32_t g1, g2;
+            int best;
+            bool need_full = total == 0xFFFF;
+            if (!need_full) {
+                const uint32_t key = tk_key[qi][lane & (SI_K - 1)];
+                const int idx = tk_idx[qi][lane & (SI_K - 1)];
+                const int md = mdist[idx];
+                const bool alive = lane < SI_K && key != KEY_INF && !(md != 255 && md <= (int)(key >> 20));
+                unsigned m = __ballot_sync(FULL, alive);
+                const int l1 = __ffs(m) - 1;
+                m &= m - 1;
+                const int l2 = __ffs(m) - 1;
+                g1 = __shfl_sync(FULL, key, max(l1, 0));
+                best = __shfl_sync(FULL, idx, max(l1, 0));
+                g2 = __shfl_sync(FULL, key, max(l2, 0));
+                if (l1 < 0) g1 = KEY_INF;
+                if (l2 < 0) g2 = KEY_INF;
+                // the kept list may hide further candidates: only matters when a match is still possible
+                if (total > SI_K && (l1 < 0 || ((int)(g1 >> 20) <= TH_LOW && l2 < 0))) need_full = true;
+            }
+            if (need_full) {
+                const int i1 = qi1[qi];
+                const float qx = prev ? prev[2 * i1] : kp1[i1].x, qy = prev ? prev[2 * i1 + 1] : kp1[i1].y;
+                uint32_t qd[8];
+                load_row(qd, d1 + 32 * (long long)i1);
+                __syncwarp();
+                eval_query_filtered(c, qd, qx, qy, g1, g2, best);
+            }
+            if (g1 == KEY_INF) continue;
+            const int bestDist = (int)(g1 >> 20);
+            const float second = g2 == KEY_INF ? (float)INT_MAX : (float)(int)(g2 >> 20);
+            if (bestDist <= TH_LOW && (float)bestDist < __fmul_rn(second, a.ratio)) {   // :532-534
+                const int i1 = qi1[qi];
+                const int old = m21[best];
+                if (old != 0xFFFF) m12s[old] = 0xFFFF;                                  // :536-540
+                m12s[i1] = (unsigned short)best;
+                m21[best] = (unsigned short)i1;
+                mdist[best] = (unsigned char)bestDist;
+                ev[i1] = (unsigned short)best;
             }
         }
-        __syncthreads();
+        __syncwarp();
     }
-    // the update of vbPrevMatched reads kp2 only; prev of later query blocks was read before any write
-    if (wid == 0) {
-        int nm = 0;
-        if (a.checkOri) {                                                               // :566-590
-            int ind1, ind2, ind3;
-            three_maxima(hist, ind1, ind2, ind3);
-            for (int i = lane; i < n1; i += 32) {
-                const int b = binof[i];
-                if (b != 255 && b != ind1 && b != ind2 && b != ind3 && m12[i] >= 0) m12[i] = -1;
+    // rotation consistency (:549-590): every match event, also one displaced later, is a rotHist entry
+    int ind1 = -1, ind2 = -1, ind3 = -1;
+    if (a.checkOri) {
+        const float factor = 1.0f / HISTO;                                              // :476
+        for (int i = lane; i < n1; i += 32) {
+            int bin = 255;
+            if (ev[i] != 0xFFFF) {
+                float rot = __fsub_rn(kp1[i].angle, kp2[ev[i]].angle);
+                if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+                bin = (int)roundf(__fmul_rn(rot, factor));
+                if (bin == HISTO) bin = 0;
+                atomicAdd(&hist[bin], 1);
             }
-            __syncwarp();
+            ev[i] = (unsigned short)bin;
         }
-        for (int i = lane; i < n1; i += 32) {                                           // :595-597
-            const int m = m12[i];
-            if (m >= 0) {
-                nm++;
-                if (prev) { prev[2 * i] = kp2[m].x; prev[2 * i + 1] = kp2[m].y; }
-            }
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) nm += __shfl_xor_sync(FULL, nm, o);
-        if (lane == 0) a.nmatches[p] = nm;
+        __syncwarp();
+        three_maxima(hist, ind1, ind2, ind3);
     }
+    int nm = 0;
+    for (int i = lane; i < n1; i += 32) {                                               // :566-597
+        int m = m12s[i] == 0xFFFF ? -1 : (int)m12s[i];
+        if (a.checkOri) {
+            const int b = ev[i];
+            if (b != 255 && b != ind1 && b != ind2 && b != ind3) m = -1;
+        }
+        m12[i] = m;
+        if (m >= 0) {
+            nm++;
+            if (prev) { prev[2 * i] = kp2[m].x; prev[2 * i + 1] = kp2[m].y; }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) nm += __shfl_xor_sync(FULL, nm, o);
+    if (lane == 0) a.nmatches[p] = nm;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -645,15 +752,35 @@ __global__ void __launch_bounds__(256) stereo_median_kernel(const __grid_constan
 
 }  // namespace
 
-size_t search_init_smem(int cap) { return (size_t)(NCELL + 32) * 4 + (size_t)cap * 8 + 16; }
+// HBM scratch of the three kernels, per pair: CSR grid, items, and per first-frame keypoint the
+// SI_K kept keys / indices and the candidate count
+size_t search_init_scratch_bytes(int cap, int npairs) {
+    const size_t per = (size_t)NCELL * 4 + (size_t)cap * 2 * 2 + (size_t)cap * SI_K * 4 + (size_t)cap * SI_K * 2 + (size_t)cap * 2 + 4;
+    return per * npairs + 7 * 256;
+}
+
+void search_init_carve(InitArgs& a, void* scratch, int npairs) {
+    auto up = [](size_t v) { return (v + 255) / 256 * 256; };
+    unsigned char* b = (unsigned char*)scratch;
+    a.cell_end = (int*)b;            b += up((size_t)npairs * NCELL * 4);
+    a.tk_key = (uint32_t*)b;         b += up((size_t)npairs * a.cap * SI_K * 4);
+    a.tk_idx = (unsigned short*)b;   b += up((size_t)npairs * a.cap * SI_K * 2);
+    a.items = (unsigned short*)b;    b += up((size_t)npairs * a.cap * 2);
+    a.qlist = (unsigned short*)b;    b += up((size_t)npairs * a.cap * 2);
+    a.tk_total = (unsigned short*)b; b += up((size_t)npairs * a.cap * 2);
+    a.nq = (int*)b;
+}
 
 int launch_search_init(const InitArgs& a, int npairs, cudaStream_t st) {
     if (npairs <= 0) return 0;
-    const size_t smem = search_init_smem(a.cap);
-    if (smem > 24 * 1024)
-        cudaFuncSetAttribute(search_init_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    search_init_kernel<<<npairs, SI_WARPS * 32, smem, st>>>(a);
-    return 1;
+    const size_t gsm = (size_t)NCELL * 4 + (size_t)a.cap * 2;
+    if (gsm > 40 * 1024) cudaFuncSetAttribute(search_init_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsm);
+    search_init_grid_kernel<<<npairs, SG_THREADS, gsm, st>>>(a);
+    search_init_topk_kernel<<<dim3(SA_CTAS, npairs), SI_WARPS * 32, 0, st>>>(a);
+    const size_t bsm = (size_t)a.cap * 7 + 16;
+    if (bsm > 24 * 1024) cudaFuncSetAttribute(search_init_greedy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bsm);
+    search_init_greedy_kernel<<<npairs, 32, bsm, st>>>(a);
+    return 3;
 }
 
 int launch_local_grid_and_count(const LocalArgs& a, cudaStream_t st) {
