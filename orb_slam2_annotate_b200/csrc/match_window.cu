@@ -211,8 +211,10 @@ search_init_grid_kernel(const __grid_constant__ InitArgs a) {
     const orbfe_keypoint* kp2 = a.kps + (long long)fb * a.cap;
     for (int c = tid; c < NCELL; c += SG_THREADS) cur[c] = 0;
     __syncthreads();
+    // only octave-0 keypoints can pass GetFeaturesInArea(.., 0, 0) (:494, Frame.cc:381-395), and
+    // dropping the others keeps the traversal order of those that can
     for (int i = tid; i < n2; i += SG_THREADS) {
-        const int c = pos_in_grid(a.grid, kp2[i].x, kp2[i].y);
+        const int c = kp2[i].octave == 0 ? pos_in_grid(a.grid, kp2[i].x, kp2[i].y) : -1;
         if (c >= 0) atomicAdd(&cur[c], 1);
     }
     __syncthreads();
@@ -234,7 +236,7 @@ search_init_grid_kernel(const __grid_constant__ InitArgs a) {
     for (int k = 0; k < CPT; k++) { cur[tid * CPT + k] = off; off += cnt[k]; }
     __syncthreads();
     for (int i = tid; i < n2; i += SG_THREADS) {
-        const int c = pos_in_grid(a.grid, kp2[i].x, kp2[i].y);
+        const int c = kp2[i].octave == 0 ? pos_in_grid(a.grid, kp2[i].x, kp2[i].y) : -1;
         if (c >= 0) its[atomicAdd(&cur[c], 1)] = (unsigned short)i;
     }
     __syncthreads();
