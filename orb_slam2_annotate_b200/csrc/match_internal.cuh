@@ -25,8 +25,8 @@ struct InitArgs {
     // scratch (search_init_carve): CSR grid of the second frame and per-query candidate lists
     int* cell_end;               // [pairs][64*48]
     unsigned short* items;       // [pairs][cap]
-    uint32_t* tk_key;            // [pairs][cap][8]
-    unsigned short* tk_idx;      // [pairs][cap][8]
+    uint32_t* tk_key;            // [pairs][cap][32]
+    unsigned short* tk_idx;      // [pairs][cap][32]
     unsigned short* tk_total;    // [pairs][cap]
     unsigned short* qlist;       // [pairs][cap] octave-0 keypoints of the first frame, in order
     int* nq;                     // [pairs]

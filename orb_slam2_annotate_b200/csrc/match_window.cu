@@ -126,8 +126,8 @@ __device__ void three_maxima(const int* hist, int& ind1, int& ind2, int& ind3) {
 // query, fully parallel), greedy replay (warp per pair).
 
 constexpr int SI_WARPS = 8;      // warps per frame pair
-constexpr int SI_QB = 256;       // queries per phase-A / phase-B block
-constexpr int SI_K = 8;          // candidates kept per query by the parallel phase
+constexpr int SI_QB = 64;        // queries staged per block by the greedy kernel
+constexpr int SI_K = 32;         // candidates kept per query by the parallel phase (the whole sorted warp)
 constexpr int SI_CL = 512;       // per-warp candidate list capacity (longer windows take the direct path)
 
 // Candidates of one query in GetFeaturesInArea order, evaluated across the lanes of a warp.
