@@ -129,7 +129,7 @@ __device__ void blur_tiny(const uint8_t* __restrict__ src, uint8_t* __restrict__
         }
 }
 
-__global__ void __launch_bounds__(BT)
+__global__ void __launch_bounds__(BT, 8)
 blur_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ BlurTiles t,
             const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur) {
     int l = 0;
