@@ -90,7 +90,10 @@ int orbfe_extract_batch(orbfe_extractor* e, const uint8_t* imgs, int batch, int 
 /* Device-resident variant for pipelines that already hold frames in HBM: enqueues the
  * kernels on the handle's stream and returns without synchronising.  d_imgs is a device
  * pointer (same layout as above).  Results stay on the device; fetch pointers with
- * orbfe_extractor_device_results after orbfe_extractor_sync. */
+ * orbfe_extractor_device_results after orbfe_extractor_sync.  When d_imgs is 16-byte aligned,
+ * stride is a multiple of 16 equal to the padded width and the frames are contiguous, the frames
+ * are used in place as pyramid level 0 (no copy): they must stay valid and unmodified until the
+ * handle has been synchronised, and orbfe_pyramid_level(.., 0, ..) reads them. */
 int orbfe_extract_batch_device(orbfe_extractor* e, const uint8_t* d_imgs, int batch, int width,
                                int height, ptrdiff_t stride, ptrdiff_t frame_stride);
 int orbfe_extractor_sync(orbfe_extractor* e);

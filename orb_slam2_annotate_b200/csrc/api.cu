@@ -207,6 +207,7 @@ static int build_geometry(orbfe_extractor* e, int w, int h, int batchCap, FrameS
         L.pitch = (int)align_up(L.w, 16);
         L.lvBytes = (long long)L.pitch * L.h;
         L.pyrOff = pyrOff;
+        L.blurOff = pyrOff;
         pyrOff = align_up(pyrOff + L.lvBytes * batchCap, 256);
         L.minBX = kEdgeThreshold - 3; L.minBY = L.minBX;
         L.maxBX = L.w - kEdgeThreshold + 3; L.maxBY = L.h - kEdgeThreshold + 3;
@@ -311,7 +312,7 @@ static int ensure_geometry(orbfe_extractor* e, int w, int h, int batch) {
         for (int l = 0; l < e->nlevels; l++) {
             const LevelGeom& L = g.lv[l];
             if ((rc = encode_level_map(&maps[2 * l], e->pyr.p + L.pyrOff, L.pitch, (long long)L.h * cap, kTmaRawW, kTmaRawH))) return rc;
-            if ((rc = encode_level_map(&maps[2 * l + 1], e->blur.p + L.pyrOff, L.pitch, (long long)L.h * cap, kTmaBlurW, kTmaBlurH))) return rc;
+            if ((rc = encode_level_map(&maps[2 * l + 1], e->blur.p + L.blurOff, L.pitch, (long long)L.h * cap, kTmaBlurW, kTmaBlurH))) return rc;
         }
     }
     DevBufs& d = e->d;
@@ -370,9 +371,23 @@ static int enqueue_extract(orbfe_extractor* e, int frame0 = 0, int count = -1) {
     return 0;
 }
 
+// Level 0 either lives in the pyramid buffer (copied there) or aliases the caller's device frames
+// when their layout already is the level layout (16-byte aligned base, stride == pitch, frames
+// contiguous): every kernel addresses level 0 as d.pyr + lv[0].pyrOff, so the alias is just a
+// different offset, plus the level-0 TMA descriptor of the orientation kernel.
+static int set_level0_source(orbfe_extractor* e, const uint8_t* alias) {
+    LevelGeom& L0 = e->g.lv[0];
+    const uint8_t* want = alias ? alias : e->pyr.p + L0.blurOff;       // blurOff keeps the in-buffer offset
+    if (e->d.pyr + L0.pyrOff == want) return 0;
+    L0.pyrOff = want - e->d.pyr;
+    return encode_level_map(&e->tmaps[0], (void*)want, L0.pitch, (long long)L0.h * e->geomBatchCap, kTmaRawW, kTmaRawH);
+}
+
 // copy `batch` frames into level 0 of the pyramid (kind: H2D or D2D)
 static int upload_level0(orbfe_extractor* e, const uint8_t* imgs, int batch, int w, int h,
                          ptrdiff_t stride, ptrdiff_t frame_stride, cudaMemcpyKind kind) {
+    int rc0 = set_level0_source(e, nullptr);
+    if (rc0) return rc0;
     const LevelGeom& L0 = e->g.lv[0];
     uint8_t* dst = e->d.pyr + L0.pyrOff;
     if (e->profiling) cudaEventRecord(e->ev[0], e->stream);
@@ -495,7 +510,15 @@ int orbfe_extract_batch_device(orbfe_extractor* e, const uint8_t* d_imgs, int ba
     CU(cudaSetDevice(e->device));
     int rc = ensure_geometry(e, width, height, batch);
     if (rc) return rc;
-    if ((rc = upload_level0(e, d_imgs, batch, width, height, stride, frame_stride, cudaMemcpyDeviceToDevice))) return rc;
+    const LevelGeom& L0 = e->g.lv[0];
+    if (stride == L0.pitch && (batch == 1 || frame_stride == (ptrdiff_t)height * stride) &&
+        (reinterpret_cast<uintptr_t>(d_imgs) & 15) == 0) {
+        // the frames already are level 0: no copy (they must stay valid until the results are fetched)
+        if ((rc = set_level0_source(e, d_imgs))) return rc;
+        if (e->profiling) cudaEventRecord(e->ev[0], e->stream);
+    } else if ((rc = upload_level0(e, d_imgs, batch, width, height, stride, frame_stride, cudaMemcpyDeviceToDevice))) {
+        return rc;
+    }
     e->lastBatch = batch;
     return enqueue_extract(e);
 }
@@ -550,6 +573,10 @@ static int extract_batch_pipelined(orbfe_extractor* e, const uint8_t* imgs, int 
                                    ptrdiff_t stride, ptrdiff_t frame_stride, orbfe_keypoint* kps,
                                    uint8_t* desc, int cap, int* counts, int chunk) {
     const int nchunks = (batch + chunk - 1) / chunk;
+    {
+        const int rc0 = set_level0_source(e, nullptr);
+        if (rc0) return rc0;
+    }
     if (!e->h2dStream) {
         CU(cudaStreamCreateWithFlags(&e->h2dStream, cudaStreamNonBlocking));
         CU(cudaStreamCreateWithFlags(&e->d2hStream, cudaStreamNonBlocking));
@@ -656,7 +683,7 @@ int orbfe_pyramid_level(orbfe_extractor* e, int frame, int level, int blurred, u
     if (!dst) return ORBFE_OK;
     if (dst_stride < L.w) return fail(ORBFE_ERR_ARG, "dst_stride smaller than the level width");
     CU(cudaSetDevice(e->device));
-    const uint8_t* src = (blurred ? e->d.blur : e->d.pyr) + L.pyrOff + (long long)frame * L.lvBytes;
+    const uint8_t* src = (blurred ? e->d.blur + L.blurOff : e->d.pyr + L.pyrOff) + (long long)frame * L.lvBytes;
     CU(cudaMemcpy2DAsync(dst, dst_stride, src, L.pitch, L.w, L.h, cudaMemcpyDeviceToHost, e->stream));
     CU(cudaStreamSynchronize(e->stream));
     return ORBFE_OK;

@@ -156,10 +156,11 @@ blur_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ Blur
         }
     }
     const int x = wc * 4, y0 = band * RH;
-    const long long off = L.pyrOff + (long long)(blockIdx.y + g.frame0) * L.lvBytes;
+    const long long fo = (long long)(blockIdx.y + g.frame0) * L.lvBytes;
+    const long long off = L.pyrOff + fo, boff = L.blurOff + fo;
     const bool edge = x < 4 || x + 8 > L.w;
     if (L.w < 8) {
-        if (active) blur_tiny(pyr + off, blur + off, L.pitch, L.w, L.h, x, y0);
+        if (active) blur_tiny(pyr + off, blur + boff, L.pitch, L.w, L.h, x, y0);
         return;
     }
     const bool inside = y0 >= 3 && y0 + RH + 3 <= L.h;
@@ -171,11 +172,11 @@ blur_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ Blur
         const int last_word = (L.w - 1) >> 2;
 #pragma unroll
         for (int j = 0; j < 3; j++) ws[j] = word_source(x + 4 * (j - 1), L.w, last_word);
-        if (warp_inside) blur_column<true, true>(pyr + off, blur + off, L.pitch, L.w, L.h, x, y0, ws);
-        else blur_column<true, false>(pyr + off, blur + off, L.pitch, L.w, L.h, x, y0, ws);
+        if (warp_inside) blur_column<true, true>(pyr + off, blur + boff, L.pitch, L.w, L.h, x, y0, ws);
+        else blur_column<true, false>(pyr + off, blur + boff, L.pitch, L.w, L.h, x, y0, ws);
     } else {
-        if (warp_inside) blur_column<false, true>(pyr + off, blur + off, L.pitch, L.w, L.h, x, y0, nullptr);
-        else blur_column<false, false>(pyr + off, blur + off, L.pitch, L.w, L.h, x, y0, nullptr);
+        if (warp_inside) blur_column<false, true>(pyr + off, blur + boff, L.pitch, L.w, L.h, x, y0, nullptr);
+        else blur_column<false, false>(pyr + off, blur + boff, L.pitch, L.w, L.h, x, y0, nullptr);
     }
 }
 

@@ -44,7 +44,8 @@ struct LevelGeom {
     int scaledPatch;            // (int)(PATCH_SIZE * scale)
     float hX;                   // root width
     float scale;                // mvScaleFactor[l]
-    long long pyrOff;           // byte offset of the level's image stack inside pyr / blur
+    long long pyrOff;           // byte offset of the level's image stack from d.pyr (level 0 may alias the caller's device frames)
+    long long blurOff;          // byte offset of the blurred stack inside d.blur
     long long lvBytes;          // bytes per frame of this level (pitch * h)
     long long cellSlotOff;      // u32 offset of the level's cell slots inside a frame
 };

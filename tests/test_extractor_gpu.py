@@ -155,3 +155,27 @@ def test_pipelined_host_batch(orbfe, oracle):
     for b in range(5, B):
         assert counts[b] == counts[b % 5]
         assert kps[b, :counts[b]].tobytes() == kps[b % 5, :counts[b]].tobytes()
+
+
+def test_device_resident_frames(orbfe, oracle):
+    """orbfe_extract_batch_device: frames used in place as level 0 (aligned layout) and copied
+    (odd stride), then the host path again on the same handle."""
+    import torch
+    ex = orbfe.ORBextractor(1000)
+    oc = oracle.OracleExtractor(1000)
+    for (W, H) in ((640, 480), (1241, 376), (640, 480)):
+        B = 3
+        imgs = np.stack([synth.frame(W, H, 20 + b) for b in range(B)])
+        dev = torch.from_numpy(imgs).cuda()
+        ex.extract_batch_device(dev.data_ptr(), B, W, H)
+        ex.sync()
+        kps, desc, counts = ex.fetch(B)
+        assert np.array_equal(ex.pyramid_level(0, frame=1), imgs[1])
+        for b in range(B):
+            ko, do = oc(imgs[b])
+            r, _, _ = _compare_frame(kps[b, :counts[b]], desc[b, :counts[b]], ko, do)
+            assert r <= 1
+        # host path right after (level 0 back inside the pyramid buffer)
+        k1, d1 = ex(imgs[2])
+        assert k1.tobytes() == kps[2, :counts[2]].tobytes() and d1.tobytes() == desc[2, :counts[2]].tobytes()
+        del dev
