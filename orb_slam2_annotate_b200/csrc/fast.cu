@@ -260,7 +260,9 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __
     const uint8_t* wb = reinterpret_cast<const uint8_t*>(&S.win[0][0]) + 4;   // byte (r, x) = wb[r*WS*4 + x]
 
     // stage 1a lane mapping: a lane keeps one zone word column and walks the rows rpi at a time
-    const int rpi = small_div(32, rcp_nzc);                      // zone rows per warp step (nzc <= 12)
+    // (3 rows per step whenever they fit: the ring offset is 3 too, so a lane's centre row becomes
+    // its upper row one step later and one new word per step feeds both comparisons)
+    const int rpi = nzc <= 10 ? 3 : small_div(32, rcp_nzc);      // zone rows per warp step (nzc <= 12)
     const int rsub = small_div(lane, rcp_nzc), cc1 = lane - rsub * nzc;
     const bool act = rsub < rpi;
     const uint32_t* wcol = &S.win[rsub][zc0 + cc1 + 1];
@@ -280,18 +282,39 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __
         // (ballot order) into a task list that borrows the score map's storage
         uint32_t* tasks = reinterpret_cast<uint32_t*>(&S.sc[0][0]);
         int ntask = 0;
-        for (int r0 = 0; r0 < zh; r0 += rpi) {
-            const int r = r0 + rsub;
-            uint32_t gmask = 0;
-            if (act && r < zh) {
-                const uint32_t* pw = wcol + r0 * WS;             // (window row r, word column wc)
-                const uint32_t v = pw[3 * WS];
-                gmask = (swar_gt(__vabsdiffu4(pw[6 * WS], v), cmpc, small_t) |
-                         swar_gt(__vabsdiffu4(pw[0], v), cmpc, small_t)) & zm;
+        if (rpi == 3) {
+            uint32_t ce = 0, g_up = 0;
+            if (act) {
+                ce = wcol[3 * WS];
+                g_up = swar_gt(__vabsdiffu4(wcol[0], ce), cmpc, small_t);
             }
-            const uint32_t bal = __ballot_sync(0xFFFFFFFFu, gmask != 0);
-            if (gmask) tasks[ntask + __popc(bal & ((1u << lane) - 1u))] = gmask | (uint32_t)r | ((uint32_t)cc1 << 8);
-            ntask += __popc(bal);
+            for (int r0 = 0; r0 < zh; r0 += 3) {
+                const int r = r0 + rsub;
+                uint32_t gmask = 0;
+                if (act && r < zh) {
+                    const uint32_t dn = wcol[(r0 + 6) * WS];
+                    const uint32_t g_dn = swar_gt(__vabsdiffu4(dn, ce), cmpc, small_t);
+                    gmask = (g_up | g_dn) & zm;
+                    ce = dn; g_up = g_dn;                        // |centre - below| is |above - centre| of the next step
+                }
+                const uint32_t bal = __ballot_sync(0xFFFFFFFFu, gmask != 0);
+                if (gmask) tasks[ntask + __popc(bal & ((1u << lane) - 1u))] = gmask | (uint32_t)r | ((uint32_t)cc1 << 8);
+                ntask += __popc(bal);
+            }
+        } else {
+            for (int r0 = 0; r0 < zh; r0 += rpi) {
+                const int r = r0 + rsub;
+                uint32_t gmask = 0;
+                if (act && r < zh) {
+                    const uint32_t* pw = wcol + r0 * WS;             // (window row r, word column wc)
+                    const uint32_t v = pw[3 * WS];
+                    gmask = (swar_gt(__vabsdiffu4(pw[6 * WS], v), cmpc, small_t) |
+                             swar_gt(__vabsdiffu4(pw[0], v), cmpc, small_t)) & zm;
+                }
+                const uint32_t bal = __ballot_sync(0xFFFFFFFFu, gmask != 0);
+                if (gmask) tasks[ntask + __popc(bal & ((1u << lane) - 1u))] = gmask | (uint32_t)r | ((uint32_t)cc1 << 8);
+                ntask += __popc(bal);
+            }
         }
         __syncwarp();
         // ---- stage 1b: pairs (4,12), (2,10), (6,14) on the surviving words, all lanes busy.
