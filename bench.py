@@ -283,6 +283,20 @@ def main():
     barrier()
     e2e_s = time.perf_counter() - t0
 
+    # ---- the PCIe leg alone: one pinned H2D copy of the step's frames (what bounds e2e from below)
+    th = torch.from_numpy(h_frames)
+    td = torch.empty_like(th, device="cuda")
+    td.copy_(th, non_blocking=True)
+    torch.cuda.synchronize()
+    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    c0.record()
+    for _ in range(3):
+        td.copy_(th, non_blocking=True)
+    c1.record()
+    torch.cuda.synchronize()
+    h2d_gbs = 3 * th.numel() / (c0.elapsed_time(c1) * 1e-3) / 1e9
+    del td
+
     # ---- Hamming matcher throughput: brute-force kNN-2, queries sharded per GPU (config 5 shape, sampled)
     MQ = NT = 131072
     tq = torch.randint(0, 256, (MQ, 32), dtype=torch.uint8, device="cuda")
@@ -339,7 +353,8 @@ def main():
                        "frames_per_step_per_gpu": B, "l2": "inputs_larger_than_l2 (315 MB of frames per step)",
                        "mean_keypoints_per_frame": mean_kp, "mean_init_matches_per_pair": mean_matches},
             "e2e": {"value": total_frames / (e2e_ms * 1e-3), "unit": "frames/s",
-                    "h2d_bytes_per_step": int(frames.nbytes),
+                    "h2d_bytes_per_step": int(frames.nbytes), "h2d_gbs_measured": h2d_gbs,
+                    "pcie_bound_frames_per_s": h2d_gbs * 1e9 / (W * H) * world,
                     "d2h_bytes_per_step": int(out[0].nbytes + out[1].nbytes + out[2].nbytes
                                               + h_m12.numel() * 4 + h_nm.numel() * 4)},
             "hamming": hamming,

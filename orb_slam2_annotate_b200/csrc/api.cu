@@ -40,6 +40,9 @@ struct orbfe_extractor {
     // the Gaussian blur only depends on the pyramid: it runs on a side stream beside FAST + quadtree
     cudaStream_t sideStream = nullptr;
     cudaEvent_t evPyr = nullptr, evBlur = nullptr;
+    // second kernel lane of the chunked host pipeline (chunks alternate so one chunk's tail overlaps the next one's head)
+    cudaStream_t stream2 = nullptr, sideStream2 = nullptr;
+    cudaEvent_t evPyr2 = nullptr, evBlur2 = nullptr;
     std::vector<cudaEvent_t> evUp, evDone;
     // geometry of the current image size / batch capacity
     int geomW = 0, geomH = 0, geomBatchCap = 0;
@@ -336,34 +339,36 @@ static int ensure_geometry(orbfe_extractor* e, int w, int h, int batch) {
 }
 
 // the kernel schedule of operator() on the handle's stream; level 0 is already in d.pyr
-static int enqueue_extract(orbfe_extractor* e, int frame0 = 0, int count = -1) {
+static int enqueue_extract(orbfe_extractor* e, int frame0 = 0, int count = -1, int lane = 0) {
     int launches = 0;
-    const bool prof = e->profiling && frame0 == 0;
+    const bool prof = e->profiling && frame0 == 0 && lane == 0;
+    cudaStream_t st = lane ? e->stream2 : e->stream, side = lane ? e->sideStream2 : e->sideStream;
+    cudaEvent_t evPyr = lane ? e->evPyr2 : e->evPyr, evBlur = lane ? e->evBlur2 : e->evBlur;
     const int fullBatch = e->g.batch;
     e->g.frame0 = frame0;
     if (count >= 0) e->g.batch = count;
-    if (prof) cudaEventRecord(e->ev[1], e->stream);
-    launches += launch_pyramid(e->g, e->d, e->stream);
-    if (prof) cudaEventRecord(e->ev[2], e->stream);
+    if (prof) cudaEventRecord(e->ev[1], st);
+    launches += launch_pyramid(e->g, e->d, st);
+    if (prof) cudaEventRecord(e->ev[2], st);
     if (prof) {
         // profiling mode serialises the stages so that each one can be timed alone
-        launches += launch_fast(e->g, e->d, e->stream);
-        cudaEventRecord(e->ev[3], e->stream);
-        launches += launch_blur(e->g, e->d, e->stream);
-        cudaEventRecord(e->ev[4], e->stream);
-        launches += launch_octree(e->g, e->d, e->stream);
-        cudaEventRecord(e->ev[5], e->stream);
+        launches += launch_fast(e->g, e->d, st);
+        cudaEventRecord(e->ev[3], st);
+        launches += launch_blur(e->g, e->d, st);
+        cudaEventRecord(e->ev[4], st);
+        launches += launch_octree(e->g, e->d, st);
+        cudaEventRecord(e->ev[5], st);
     } else {
-        CU(cudaEventRecord(e->evPyr, e->stream));
-        CU(cudaStreamWaitEvent(e->sideStream, e->evPyr, 0));
-        launches += launch_blur(e->g, e->d, e->sideStream);
-        CU(cudaEventRecord(e->evBlur, e->sideStream));
-        launches += launch_fast(e->g, e->d, e->stream);
-        launches += launch_octree(e->g, e->d, e->stream);
-        CU(cudaStreamWaitEvent(e->stream, e->evBlur, 0));
+        CU(cudaEventRecord(evPyr, st));
+        CU(cudaStreamWaitEvent(side, evPyr, 0));
+        launches += launch_blur(e->g, e->d, side);
+        CU(cudaEventRecord(evBlur, side));
+        launches += launch_fast(e->g, e->d, st);
+        launches += launch_octree(e->g, e->d, st);
+        CU(cudaStreamWaitEvent(st, evBlur, 0));
     }
-    launches += launch_orient_desc(e->g, e->d, e->umax_d.p, e->stream);
-    if (prof) cudaEventRecord(e->ev[6], e->stream);
+    launches += launch_orient_desc(e->g, e->d, e->umax_d.p, st);
+    if (prof) cudaEventRecord(e->ev[6], st);
     e->g.frame0 = 0;
     e->g.batch = fullBatch;
     e->lastLaunches = frame0 == 0 ? launches : e->lastLaunches + launches;
@@ -465,6 +470,10 @@ void orbfe_extractor_destroy(orbfe_extractor* e) {
     if (e->evBlur) cudaEventDestroy(e->evBlur);
     if (e->h2dStream) cudaStreamDestroy(e->h2dStream);
     if (e->d2hStream) cudaStreamDestroy(e->d2hStream);
+    if (e->stream2) cudaStreamDestroy(e->stream2);
+    if (e->sideStream2) cudaStreamDestroy(e->sideStream2);
+    if (e->evPyr2) cudaEventDestroy(e->evPyr2);
+    if (e->evBlur2) cudaEventDestroy(e->evBlur2);
     for (auto ev : e->evUp) cudaEventDestroy(ev);
     for (auto ev : e->evDone) cudaEventDestroy(ev);
     for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);
@@ -580,6 +589,10 @@ static int extract_batch_pipelined(orbfe_extractor* e, const uint8_t* imgs, int 
     if (!e->h2dStream) {
         CU(cudaStreamCreateWithFlags(&e->h2dStream, cudaStreamNonBlocking));
         CU(cudaStreamCreateWithFlags(&e->d2hStream, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&e->stream2, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&e->sideStream2, cudaStreamNonBlocking));
+        CU(cudaEventCreateWithFlags(&e->evPyr2, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&e->evBlur2, cudaEventDisableTiming));
     }
     while ((int)e->evUp.size() < nchunks) {
         cudaEvent_t a, b;
@@ -597,27 +610,38 @@ static int extract_batch_pipelined(orbfe_extractor* e, const uint8_t* imgs, int 
         const int f0 = c * chunk, n = std::min(chunk, batch - f0);
         uint8_t* dst = e->d.pyr + L0.pyrOff + (long long)f0 * L0.lvBytes;
         const uint8_t* src = imgs + (long long)f0 * frame_stride;
-        if (frame_stride == (ptrdiff_t)h * stride) {
+        if (frame_stride == (ptrdiff_t)h * stride && stride == L0.pitch) {
+            CU(cudaMemcpyAsync(dst, src, (size_t)L0.lvBytes * n, cudaMemcpyHostToDevice, e->h2dStream));   // one flat DMA
+        } else if (frame_stride == (ptrdiff_t)h * stride) {
             CU(cudaMemcpy2DAsync(dst, L0.pitch, src, stride, w, (size_t)h * n, cudaMemcpyHostToDevice, e->h2dStream));
         } else {
             for (int b = 0; b < n; b++)
                 CU(cudaMemcpy2DAsync(dst + (long long)b * L0.lvBytes, L0.pitch, src + b * frame_stride, stride, w, h,
                                      cudaMemcpyHostToDevice, e->h2dStream));
         }
+        const int lane = c & 1;
+        cudaStream_t st = lane ? e->stream2 : e->stream;
         CU(cudaEventRecord(e->evUp[c], e->h2dStream));
-        CU(cudaStreamWaitEvent(e->stream, e->evUp[c], 0));
-        int rc = enqueue_extract(e, f0, n);
+        CU(cudaStreamWaitEvent(st, e->evUp[c], 0));
+        int rc = enqueue_extract(e, f0, n, lane);
         if (rc) return rc;
-        CU(cudaEventRecord(e->evDone[c], e->stream));
+        CU(cudaEventRecord(e->evDone[c], st));
         CU(cudaStreamWaitEvent(e->d2hStream, e->evDone[c], 0));
         const int rowk = std::min(cap, oc);
         CU(cudaMemcpyAsync(counts + f0, e->d.counts + f0, sizeof(int) * n, cudaMemcpyDeviceToHost, e->d2hStream));
-        CU(cudaMemcpy2DAsync(kps + (size_t)f0 * cap, (size_t)cap * kb, e->d.kps + (size_t)f0 * oc, (size_t)oc * kb,
-                             (size_t)rowk * kb, n, cudaMemcpyDeviceToHost, e->d2hStream));
-        CU(cudaMemcpy2DAsync(desc + (size_t)f0 * cap * 32, (size_t)cap * 32, e->d.desc + (size_t)f0 * oc * 32,
-                             (size_t)oc * 32, (size_t)rowk * 32, n, cudaMemcpyDeviceToHost, e->d2hStream));
+        if (cap == oc) {
+            CU(cudaMemcpyAsync(kps + (size_t)f0 * cap, e->d.kps + (size_t)f0 * oc, (size_t)oc * kb * n, cudaMemcpyDeviceToHost, e->d2hStream));
+            CU(cudaMemcpyAsync(desc + (size_t)f0 * cap * 32, e->d.desc + (size_t)f0 * oc * 32, (size_t)oc * 32 * n,
+                               cudaMemcpyDeviceToHost, e->d2hStream));
+        } else {
+            CU(cudaMemcpy2DAsync(kps + (size_t)f0 * cap, (size_t)cap * kb, e->d.kps + (size_t)f0 * oc, (size_t)oc * kb,
+                                 (size_t)rowk * kb, n, cudaMemcpyDeviceToHost, e->d2hStream));
+            CU(cudaMemcpy2DAsync(desc + (size_t)f0 * cap * 32, (size_t)cap * 32, e->d.desc + (size_t)f0 * oc * 32,
+                                 (size_t)oc * 32, (size_t)rowk * 32, n, cudaMemcpyDeviceToHost, e->d2hStream));
+        }
     }
     CU(cudaStreamSynchronize(e->d2hStream));
+    CU(cudaStreamSynchronize(e->stream2));
     CU(cudaStreamSynchronize(e->stream));
     if (cap < oc)
         for (int b = 0; b < batch; b++)
