@@ -359,11 +359,13 @@ static int enqueue_extract(orbfe_extractor* e, int frame0 = 0, int count = -1, i
         launches += launch_octree(e->g, e->d, st);
         cudaEventRecord(e->ev[5], st);
     } else {
+        // FAST saturates the issue slots on its own; the blur runs beside the quadtree, whose
+        // barrier-bound CTAs leave slots free
+        launches += launch_fast(e->g, e->d, st);
         CU(cudaEventRecord(evPyr, st));
         CU(cudaStreamWaitEvent(side, evPyr, 0));
         launches += launch_blur(e->g, e->d, side);
         CU(cudaEventRecord(evBlur, side));
-        launches += launch_fast(e->g, e->d, st);
         launches += launch_octree(e->g, e->d, st);
         CU(cudaStreamWaitEvent(st, evBlur, 0));
     }
