@@ -55,7 +55,9 @@ struct orbfe_extractor {
     DevArray<int2> xtab;
     DevArray<int4> ytab;
     DevArray<int4> xq;
+    DevArray<int4> celltab;
     std::vector<CUtensorMap> tmaps;   // {level, blurred level} descriptors, passed to the kernel by value
+    std::vector<CUtensorMap> fastMaps; // level descriptors with the FAST window box
     int lastBatch = 0, lastLaunches = 0;
     // optional per-stage timing (events on the handle's stream)
     bool profiling = false;
@@ -307,11 +309,37 @@ static int ensure_geometry(orbfe_extractor* e, int w, int h, int batch) {
         CU(cudaMemcpy(e->xtab.p, xall.data(), xall.size() * sizeof(int2), cudaMemcpyHostToDevice));
         CU(cudaMemcpy(e->ytab.p, yall.data(), yall.size() * sizeof(int4), cudaMemcpyHostToDevice));
     }
+    // FAST cell records (ORBextractor.cc:846-869, integer-valued floats there)
+    {
+        std::vector<int4> ct(g.ncells > 0 ? g.ncells : 1, make_int4(0, 0, 0, 0));
+        for (int l = 0; l < e->nlevels; l++) {
+            const LevelGeom& L = g.lv[l];
+            for (int ci = 0; ci < L.nRows; ci++)
+                for (int cj = 0; cj < L.nCols; cj++) {
+                    const int iniY = L.minBY + ci * L.hCell, iniX = L.minBX + cj * L.wCell;
+                    int maxY = iniY + L.hCell + 6, maxX = iniX + L.wCell + 6;
+                    if (maxY > L.maxBY) maxY = L.maxBY;
+                    if (maxX > L.maxBX) maxX = L.maxBX;
+                    int ww = maxX - iniX, wh = maxY - iniY;
+                    if (iniY >= L.maxBY - 3 || iniX >= L.maxBX - 6 || ww < 7 || wh < 7) ww = wh = 0;
+                    ct[L.cellBase + ci * L.nCols + cj] =
+                        make_int4(iniX | (iniY << 16), ww | (wh << 16), (cj * L.wCell) | ((ci * L.hCell) << 16), l);
+                }
+        }
+        if ((rc = e->celltab.ensure(ct.size()))) return rc;
+        CU(cudaMemcpy(e->celltab.p, ct.data(), ct.size() * sizeof(int4), cudaMemcpyHostToDevice));
+    }
     // TMA descriptors of the level / blurred-level buffers
     {
         static_assert(sizeof(CUtensorMap) == 128, "descriptor stride assumed by the kernel");
         std::vector<CUtensorMap>& maps = e->tmaps;
         maps.resize(2 * e->nlevels);
+        e->fastMaps.resize(e->nlevels);
+        for (int l = 0; l < e->nlevels; l++) {
+            const LevelGeom& L = g.lv[l];
+            const int rows = fast_window_rows(L);
+            if ((rc = encode_level_map(&e->fastMaps[l], e->pyr.p + L.pyrOff, L.pitch, (long long)L.h * cap, 64, rows ? rows : 40))) return rc;
+        }
         for (int l = 0; l < e->nlevels; l++) {
             const LevelGeom& L = g.lv[l];
             if ((rc = encode_level_map(&maps[2 * l], e->pyr.p + L.pyrOff, L.pitch, (long long)L.h * cap, kTmaRawW, kTmaRawH))) return rc;
@@ -321,6 +349,8 @@ static int ensure_geometry(orbfe_extractor* e, int w, int h, int batch) {
     DevBufs& d = e->d;
     std::memset(&d, 0, sizeof(d));
     d.tmaps = e->tmaps.data();
+    d.fast_tmaps = e->fastMaps.data();
+    d.celltab = e->celltab.p;
     d.pyr = e->pyr.p; d.blur = e->blur.p; d.cellc = e->cellc.p; d.cellk = e->cellk.p;
     d.sel = e->sel.p; d.selc = e->selc.p; d.kps = e->kps.p; d.desc = e->desc.p;
     d.counts = e->counts.p; d.qt_xy = e->qt_xy.p; d.qt_node = e->qt_node.p; d.qtCap = g.cellSlots;
@@ -387,7 +417,10 @@ static int set_level0_source(orbfe_extractor* e, const uint8_t* alias) {
     const uint8_t* want = alias ? alias : e->pyr.p + L0.blurOff;       // blurOff keeps the in-buffer offset
     if (e->d.pyr + L0.pyrOff == want) return 0;
     L0.pyrOff = want - e->d.pyr;
-    return encode_level_map(&e->tmaps[0], (void*)want, L0.pitch, (long long)L0.h * e->geomBatchCap, kTmaRawW, kTmaRawH);
+    int rc = encode_level_map(&e->tmaps[0], (void*)want, L0.pitch, (long long)L0.h * e->geomBatchCap, kTmaRawW, kTmaRawH);
+    if (rc) return rc;
+    const int rows = fast_window_rows(L0);
+    return encode_level_map(&e->fastMaps[0], (void*)want, L0.pitch, (long long)L0.h * e->geomBatchCap, 64, rows ? rows : 40);
 }
 
 // copy `batch` frames into level 0 of the pyramid (kind: H2D or D2D)
@@ -481,7 +514,7 @@ void orbfe_extractor_destroy(orbfe_extractor* e) {
     for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);
     e->pyr.release(); e->blur.release(); e->desc.release(); e->cellc.release(); e->selc.release();
     e->counts.release(); e->umax_d.release(); e->cellk.release(); e->sel.release();
-    e->qt_xy.release(); e->qt_node.release(); e->kps.release(); e->xtab.release(); e->ytab.release(); e->xq.release();
+    e->qt_xy.release(); e->qt_node.release(); e->kps.release(); e->xtab.release(); e->ytab.release(); e->xq.release(); e->celltab.release();
     delete e;
 }
 

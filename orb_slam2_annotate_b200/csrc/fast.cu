@@ -14,6 +14,8 @@
 // compaction, packed x | y<<12 | score<<24 with coordinates relative to (minBorderX,
 // minBorderY) as the reference stores them (:889-890).
 #include "orbfe_internal.cuh"
+#include <cstring>
+#include <cuda.h>
 
 namespace orbfe {
 
@@ -185,17 +187,18 @@ fast_cells_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __restr
 constexpr int kWarpsPerCta = 4;
 
 template <int WWIN_> struct S_sc_t { uint8_t b[WWIN_ - 4][WWIN_]; };
+// TMA descriptors of the levels (box 64 x window rows), passed by value
+struct alignas(64) FastMaps { CUtensorMap m[kMaxLevels]; };
 template <int WWIN_>
-struct WarpSmem {
+struct alignas(128) WarpSmem {
     static constexpr int WWIN = WWIN_;                    // max window side
-    static constexpr int WS = WWIN_ == 40 ? 12 : 16;      // window row stride in words (1 pad word left)
+    static constexpr int WS = 16;                         // window row stride in words: a 64-byte TMA box row
     static constexpr int WZ = WWIN_ - 6;                  // max zone side
     static constexpr int SCS = WWIN_;                     // score-map row stride in bytes
-    static constexpr int BMW = (WZ * WZ + 31) / 32;       // bitmap words
-    uint32_t win[WWIN][WS];
+    uint32_t win[WWIN][WS];                               // TMA destination (128-byte aligned)
     uint8_t sc[WZ + 2][SCS];
     unsigned short list[WZ * WZ];
-    uint32_t pad;                                         // the last row's wc + 1 read stays inside
+    unsigned long long bar;                               // mbarrier of the window load
 };
 
 __device__ __forceinline__ uint32_t swar_gt(uint32_t d, uint32_t c, bool small_t) {
@@ -205,8 +208,8 @@ __device__ __forceinline__ uint32_t swar_gt(uint32_t d, uint32_t c, bool small_t
 
 template <int WWIN>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
-fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __restrict__ pyr,
-                       int* __restrict__ cellc, uint32_t* __restrict__ cellk, int cellLo, int cellHi) {
+fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ FastMaps maps,
+                       const int4* __restrict__ celltab, int* __restrict__ cellc, uint32_t* __restrict__ cellk, int cellLo, int cellHi) {
     using Smem = WarpSmem<WWIN>;
     constexpr int WS = Smem::WS, SCS = Smem::SCS;
     static_assert(sizeof(S_sc_t<WWIN>) >= 4 * (WWIN - 6) * ((WWIN - 6 + 3) / 4 + 1), "task list must fit the score map");
@@ -215,49 +218,39 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __
     Smem& S = smem[wid];
     const int frame = blockIdx.y + g.frame0, cell = cellLo + blockIdx.x * kWarpsPerCta + wid;
     if (cell >= cellHi) return;
-    int l = 0;
-    while (l + 1 < g.nlevels && cell >= g.lv[l + 1].cellBase) l++;
+    // host-built cell record: window origin / size, zone offset, level (api.cu: build_geometry)
+    const int4 cd = __ldg(&celltab[cell]);
+    const int l = cd.w;
     const LevelGeom& L = g.lv[l];
-    if (L.wCell + 6 > kWarpWinMax || L.hCell + 6 > kWarpWinMax) return;     // handled by the generic kernel
     const int c = cell - L.cellBase;
-    const int ci = small_div(c, __frcp_rn((float)L.nCols)), cj = c - ci * L.nCols;
     int* out_cnt = cellc + (long long)frame * g.ncells + cell;
     uint32_t* out = cellk + (long long)frame * g.cellSlots + L.cellSlotOff + (long long)c * L.cellCap;
-
-    const int iniY = L.minBY + ci * L.hCell, iniX = L.minBX + cj * L.wCell;     // :846-869
-    int maxY = iniY + L.hCell + 6, maxX = iniX + L.wCell + 6;
-    if (maxY > L.maxBY) maxY = L.maxBY;
-    if (maxX > L.maxBX) maxX = L.maxBX;
-    const int ww = maxX - iniX, wh = maxY - iniY;
-    if (iniY >= L.maxBY - 3 || iniX >= L.maxBX - 6 || ww < 7 || wh < 7) {
+    const int iniX = cd.x & 0xFFFF, iniY = cd.x >> 16;                          // :846-869
+    const int ww = cd.y & 0xFFFF, wh = cd.y >> 16;
+    const int offX = cd.z & 0xFFFF, offY = cd.z >> 16;                          // cell origin inside the border box
+    const int maxX = iniX + ww;
+    if (ww == 0) {                                                              // degenerate cell (:861-869)
         if (lane == 0) *out_cnt = 0;
         return;
     }
     const int zw = ww - 6, zh = wh - 6;
-    const int ax0 = iniX & ~3;                       // aligned window origin (level coordinates)
-    const int nw = ((maxX + 3) >> 2) - (ax0 >> 2);   // words per window row (<= 14)
+    // The window arrives as one TMA box: 64 bytes x WWIN rows starting at the 16-byte boundary
+    // left of the cell (rows past the cell are fetched and ignored); window byte (r, x) below is
+    // relative to that origin.
+    const int ax0 = iniX & ~15;
+    const uint32_t barA = (uint32_t)__cvta_generic_to_shared(&S.bar);
+    if (lane == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(barA) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(barA), "r"(WWIN * WS * 4) : "memory");
+        asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                     ::"r"((uint32_t)__cvta_generic_to_shared(&S.win[0][0])), "l"(reinterpret_cast<uint64_t>(&maps.m[l])),
+                       "r"(ax0), "r"(frame * L.h + iniY), "r"(barA) : "memory");
+    }
     const int zx0 = iniX + 3 - ax0, zx1 = maxX - 3 - ax0;   // zone columns in window bytes
     const int zc0 = zx0 >> 2, nzc = ((zx1 - 1) >> 2) - zc0 + 1;
     const float rcp_nzc = __frcp_rn((float)nzc);
-    {   // window rows arrive as 16-byte chunks (level rows are 16-byte aligned); words outside
-        // [ax0, ax0 + 4 nw) are dropped
-        const int a16 = iniX & ~15;
-        const int nq = ((maxX + 15) >> 4) - (a16 >> 4);
-        const int wq0 = (a16 - ax0) >> 2;                // <= 0
-        const uint8_t* src = pyr + L.pyrOff + (long long)frame * L.lvBytes + (long long)iniY * L.pitch + a16;
-        const float rcp_nq = __frcp_rn((float)nq);
-#pragma unroll 2
-        for (int i = lane; i < wh * nq; i += 32) {
-            const int r = small_div(i, rcp_nq), q = i - r * nq;
-            const uint4 v = __ldg(reinterpret_cast<const uint4*>(src + r * L.pitch) + q);
-            const int w = wq0 + q * 4;
-            if ((unsigned)(w + 0) < (unsigned)nw) S.win[r][w + 1] = v.x;
-            if ((unsigned)(w + 1) < (unsigned)nw) S.win[r][w + 2] = v.y;
-            if ((unsigned)(w + 2) < (unsigned)nw) S.win[r][w + 3] = v.z;
-            if ((unsigned)(w + 3) < (unsigned)nw) S.win[r][w + 4] = v.w;
-        }
-    }
-    const uint8_t* wb = reinterpret_cast<const uint8_t*>(&S.win[0][0]) + 4;   // byte (r, x) = wb[r*WS*4 + x]
+    const uint8_t* wb = reinterpret_cast<const uint8_t*>(&S.win[0][0]);       // byte (r, x) = wb[r*WS*4 + x]
 
     // stage 1a lane mapping: a lane keeps one zone word column and walks the rows rpi at a time
     // (3 rows per step whenever they fit: the ring offset is 3 too, so a lane's centre row becomes
@@ -265,12 +258,20 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __
     const int rpi = nzc <= 10 ? 3 : small_div(32, rcp_nzc);      // zone rows per warp step (nzc <= 12)
     const int rsub = small_div(lane, rcp_nzc), cc1 = lane - rsub * nzc;
     const bool act = rsub < rpi;
-    const uint32_t* wcol = &S.win[rsub][zc0 + cc1 + 1];
+    const uint32_t* wcol = &S.win[rsub][zc0 + cc1];
     uint32_t zm = 0x80808080u;                                   // bytes of the lane's word inside the zone
     {
         const int xb = (zc0 + cc1) * 4;
         if (xb < zx0) zm &= 0xFFFFFFFFu << (8 * (zx0 - xb));
         if (xb + 4 > zx1) zm &= 0xFFFFFFFFu >> (8 * (xb + 4 - zx1));
+    }
+
+    __syncwarp();
+    {
+        uint32_t done = 0;
+        while (!done)
+            asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                         : "=r"(done) : "r"(barA), "r"(0) : "memory");
     }
 
     int total = 0;
@@ -330,7 +331,7 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __
                 gmask = e & 0x80808080u;
                 r = e & 0x7F;
                 const int cc = (e >> 8) & 0x7F;
-                const int y = r + 3, wc = zc0 + cc + 1;
+                const int y = r + 3, wc = zc0 + cc;
                 xz = (zc0 + cc) * 4 - zx0;                        // zone column of the word's byte 0
                 const uint32_t v = S.win[y][wc];
                 const uint32_t wl = S.win[y][wc - 1], wr = S.win[y][wc + 1];
@@ -393,7 +394,7 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __
             }
             const uint32_t bal = __ballot_sync(0xFFFFFFFFu, keep);
             const int pos = total + __popc(bal & ((1u << lane) - 1u));
-            if (keep && pos < L.cellCap) out[pos] = pack_kp(cc + 3 + cj * L.wCell, r + 3 + ci * L.hCell, s - 1);
+            if (keep && pos < L.cellCap) out[pos] = pack_kp(cc + 3 + offX, r + 3 + offY, s - 1);
             total += __popc(bal);
         }
         if (total > 0) break;
@@ -404,8 +405,17 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __
 
 }  // namespace
 
+// window rows of the warp kernel that takes level l (0: generic kernel) — also the TMA box height
+int fast_window_rows(const LevelGeom& L) {
+    if (!L.nCols) return 40;
+    const int side = (L.wCell > L.hCell ? L.wCell : L.hCell) + 6;
+    return side > kWarpWinMax ? 0 : side > 40 ? 48 : 40;
+}
+
 int launch_fast(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
     int launches = 0;
+    FastMaps maps;
+    std::memcpy(&maps, d.fast_tmaps, sizeof(CUtensorMap) * g.nlevels);
     // runs of consecutive levels that share a kernel variant: 0 = generic, 40 / 48 = warp layouts
     bool generic = false;
     auto variant = [&](int l) {
@@ -421,8 +431,8 @@ int launch_fast(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
         if (v == 0) generic = true;
         if (v > 0 && hi > lo) {
             const dim3 grid((hi - lo + kWarpsPerCta - 1) / kWarpsPerCta, g.batch);
-            if (v == 40) fast_cells_warp_kernel<40><<<grid, kWarpsPerCta * 32, 0, s>>>(g, d.pyr, d.cellc, d.cellk, lo, hi);
-            else fast_cells_warp_kernel<48><<<grid, kWarpsPerCta * 32, 0, s>>>(g, d.pyr, d.cellc, d.cellk, lo, hi);
+            if (v == 40) fast_cells_warp_kernel<40><<<grid, kWarpsPerCta * 32, 0, s>>>(g, maps, d.celltab, d.cellc, d.cellk, lo, hi);
+            else fast_cells_warp_kernel<48><<<grid, kWarpsPerCta * 32, 0, s>>>(g, maps, d.celltab, d.cellc, d.cellk, lo, hi);
             launches++;
         }
         l = e;

@@ -78,6 +78,8 @@ struct DevBufs {
     const int4* ytab[kMaxLevels];   // per dst y: {row0, row1, b0, b1}
     const int4* xq[kMaxLevels];     // per 4 dst columns: {base, selA01, selB01, selA23}{selB23, c0..c2}{c3,-,-,-}; null = use xtab
     const void* tmaps;              // HOST array CUtensorMap[2 * nlevels]: {level, blurred level} as [frames * h][pitch] u8 tensors
+    const int4* celltab;            // per FAST cell: {iniX | iniY<<16, ww | wh<<16 (0 = degenerate), offX | offY<<16, level}
+    const void* fast_tmaps;         // HOST array CUtensorMap[nlevels]: level as [frames * h][pitch] u8, box 64 x window rows
     bool xqSimple[kMaxLevels];      // row table strictly down-scaling: row1 == row0 + 1 and strictly increasing
     // quadtree point scratch for levels whose corner count exceeds the shared-memory arrays
     uint32_t* qt_xy;                // [B][L][qtCap]
@@ -95,6 +97,7 @@ __host__ __device__ inline int kp_score(uint32_t p) { return (int)(p >> 24); }
 // kernel launchers (each returns the number of kernel launches it enqueued)
 int launch_pyramid(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s);
 int launch_blur(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s);
+int fast_window_rows(const LevelGeom& L);
 int launch_fast(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s);
 int launch_octree(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s);
 int launch_orient_desc(const FrameSetGeom& g, const DevBufs& d, const int* d_umax, cudaStream_t s);
