@@ -17,6 +17,8 @@
  *   orbfe_search_init             ORBmatcher::SearchForInitialization src/ORBmatcher.cc:469-600
  *   orbfe_search_local_points     ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th)
  *                                                                     src/ORBmatcher.cc:51-138
+ *   orbfe_search_frame_points     ORBmatcher::SearchByProjection(Frame& Current, const Frame& Last, th, bMono)
+ *                                                                     src/ORBmatcher.cc:1484-1630
  *   orbfe_stereo_match            Frame::ComputeStereoMatches         src/Frame.cc:512-686
  */
 #ifndef ORBFE_H
@@ -199,6 +201,40 @@ typedef struct {
 int orbfe_search_local_points(orbfe_matcher* m, const orbfe_frame_view* f,
                               const orbfe_mappoints_view* mps, float th, float nnratio,
                               uint8_t* kp_occupied, int32_t* mp_for_kp, int* nmatches);
+
+/* Points of the last frame projected into the current one by the motion model, for
+ * SearchByProjection(CurrentFrame, LastFrame, th, bMono) (src/ORBmatcher.cc:1484-1630).  The
+ * pose arithmetic (x3Dc = Rcw*x3Dw + tcw, u, v, invzc, bForward / bBackward, :1494-1553) stays
+ * with the caller, which passes per point i of the last frame (all HOST arrays of length n):
+ *   valid        LastFrame.mvpMapPoints[i] != NULL && !mvbOutlier[i] && invzc >= 0 && (u, v)
+ *                inside [mnMinX, mnMaxX] x [mnMinY, mnMaxY]                          (:1510-1538)
+ *   u, v         projection                                                           (:1528-1529)
+ *   ur           u - mbf * invzc (only read when the frame has uright)                (:1575)
+ *   radius       th * CurrentFrame.mvScaleFactors[nLastOctave]                        (:1543)
+ *   min_level, max_level   arguments of GetFeaturesInArea: (o, -1) forward, (0, o) backward,
+ *                (o - 1, o + 1) otherwise, o = LastFrame.mvKeys[i].octave             (:1547-1552)
+ *   angle        LastFrame.mvKeysUn[i].angle                                          (:1594)
+ *   desc         pMP->GetDescriptor(), n x 32; observations  pMP->Observations()      (:1557,:1568) */
+typedef struct {
+    int32_t n;
+    const uint8_t* valid;
+    const float* u;
+    const float* v;
+    const float* ur;
+    const float* radius;
+    const int32_t* min_level;
+    const int32_t* max_level;
+    const float* angle;
+    const uint8_t* desc;
+    const int32_t* observations;
+} orbfe_framepoints_view;
+/* kp_occupied[f->n] in: 1 where CurrentFrame.mvpMapPoints[idx] holds a point with
+ * Observations()>0.  match_for_kp[f->n] out: >= 0 index i of the last-frame point whose map
+ * point the keypoint ends up holding, -1 untouched, -2 reset to NULL by the rotation check.
+ * *nmatches = the reference's return value. */
+int orbfe_search_frame_points(orbfe_matcher* m, const orbfe_frame_view* f,
+                              const orbfe_framepoints_view* pts, int check_orientation,
+                              const uint8_t* kp_occupied, int32_t* match_for_kp, int* nmatches);
 
 /* Pyramid of one extractor call, HOST pointers (interior pixels of mvImagePyramid[l]). */
 typedef struct {

@@ -4,7 +4,8 @@
 //   ORB_SLAM2::ORBextractor   replaces include/ORBextractor.h:46-114 + src/ORBextractor.cc
 //   ORB_SLAM2::ORBmatcher     replaces the hot-path members of include/ORBmatcher.h:51-117
 //                             (DescriptorDistance, SearchForInitialization,
-//                             SearchByProjection(Frame&, vector<MapPoint*>&, th)) and offers
+//                             SearchByProjection(Frame&, vector<MapPoint*>&, th),
+//                             SearchByProjection(CurrentFrame, LastFrame, th, bMono)) and offers
 //                             ComputeStereoMatches(Frame&) for src/Frame.cc:512-686
 //
 // Include AFTER the OpenCV core headers (cv::Mat, cv::KeyPoint, cv::InputArray, cv::OutputArray,
@@ -19,6 +20,7 @@
 #include <cstring>
 #include <stdexcept>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "orbfe.h"
@@ -174,6 +176,72 @@ public:
                                                       mpForKp.data(), &nmatches), "orbfe_search_local_points");
         for (size_t i = 0; i < mpForKp.size(); i++)
             if (mpForKp[i] >= 0) F.mvpMapPoints[i] = vpMapPoints[mpForKp[i]];   // :132
+        return nmatches;
+    }
+
+    // SearchByProjection(CurrentFrame, LastFrame, th, bMono) — src/ORBmatcher.cc:1484-1630.  The pose
+    // arithmetic (:1494-1553) is kept verbatim on the host with the reference's own cv::Mat
+    // expressions; candidates, distances, the greedy bookkeeping and the rotation check run on the GPU.
+    template <class FrameT>
+    int SearchByProjection(FrameT& CurrentFrame, const FrameT& LastFrame, const float th, const bool bMono) {
+        // MatT is cv::Mat; spelling it through the frame type keeps these lines dependent, so the
+        // header still parses where only a partial cv:: shim is available (tests/cpp)
+        typedef typename std::decay<decltype(CurrentFrame.mTcw)>::type MatT;
+        const MatT Rcw = CurrentFrame.mTcw.rowRange(0, 3).colRange(0, 3);
+        const MatT tcw = CurrentFrame.mTcw.rowRange(0, 3).col(3);
+        const MatT twc = -Rcw.t() * tcw;
+        const MatT Rlw = LastFrame.mTcw.rowRange(0, 3).colRange(0, 3);
+        const MatT tlw = LastFrame.mTcw.rowRange(0, 3).col(3);
+        const MatT tlc = Rlw * twc + tlw;
+        const bool bForward = tlc.template at<float>(2) > CurrentFrame.mb && !bMono;
+        const bool bBackward = -tlc.template at<float>(2) > CurrentFrame.mb && !bMono;
+
+        const int n = LastFrame.N;
+        std::vector<uint8_t> valid(n, 0), desc((size_t)n * 32);
+        std::vector<float> u(n), v(n), ur(n), radius(n), angle(n);
+        std::vector<int> minL(n), maxL(n), obs(n);
+        for (int i = 0; i < n; i++) {
+            auto* pMP = LastFrame.mvpMapPoints[i];
+            if (!pMP || LastFrame.mvbOutlier[i]) continue;                 // :1510-1514
+            const MatT x3Dw = pMP->GetWorldPos();
+            const MatT x3Dc = Rcw * x3Dw + tcw;
+            const float xc = x3Dc.template at<float>(0);
+            const float yc = x3Dc.template at<float>(1);
+            const float invzc = 1.0 / x3Dc.template at<float>(2);
+            if (invzc < 0) continue;                                       // :1522-1524
+            u[i] = CurrentFrame.fx * xc * invzc + CurrentFrame.cx;         // :1528-1529
+            v[i] = CurrentFrame.fy * yc * invzc + CurrentFrame.cy;
+            if (u[i] < CurrentFrame.mnMinX || u[i] > CurrentFrame.mnMaxX) continue;
+            if (v[i] < CurrentFrame.mnMinY || v[i] > CurrentFrame.mnMaxY) continue;
+            const int nLastOctave = LastFrame.mvKeys[i].octave;
+            radius[i] = th * CurrentFrame.mvScaleFactors[nLastOctave];     // :1543
+            if (bForward) { minL[i] = nLastOctave; maxL[i] = -1; }         // :1547-1552
+            else if (bBackward) { minL[i] = 0; maxL[i] = nLastOctave; }
+            else { minL[i] = nLastOctave - 1; maxL[i] = nLastOctave + 1; }
+            ur[i] = u[i] - CurrentFrame.mbf * invzc;                       // :1575
+            angle[i] = LastFrame.mvKeysUn[i].angle;                        // :1594
+            const MatT dMP = pMP->GetDescriptor();
+            std::memcpy(&desc[(size_t)i * 32], dMP.data, 32);
+            obs[i] = pMP->Observations();
+            valid[i] = 1;
+        }
+        std::vector<orbfe_keypoint> k;
+        std::vector<uint8_t> d;
+        orbfe_frame_view fv = View(CurrentFrame, k, d);
+        if (!CurrentFrame.mvuRight.empty()) fv.uright = CurrentFrame.mvuRight.data();
+        orbfe_framepoints_view pv = {n, valid.data(), u.data(), v.data(), ur.data(), radius.data(), minL.data(),
+                                     maxL.data(), angle.data(), desc.data(), obs.data()};
+        std::vector<uint8_t> occupied(CurrentFrame.mvpMapPoints.size(), 0);
+        for (size_t i = 0; i < occupied.size(); i++)                       // :1567-1569
+            occupied[i] = CurrentFrame.mvpMapPoints[i] && CurrentFrame.mvpMapPoints[i]->Observations() > 0;
+        std::vector<int> matchForKp(occupied.size(), -1);
+        int nmatches = 0;
+        orbfe_detail::check(orbfe_search_frame_points(mpHandle, &fv, &pv, mbCheckOrientation ? 1 : 0, occupied.data(),
+                                                      matchForKp.data(), &nmatches), "orbfe_search_frame_points");
+        for (size_t i = 0; i < matchForKp.size(); i++) {
+            if (matchForKp[i] >= 0) CurrentFrame.mvpMapPoints[i] = LastFrame.mvpMapPoints[matchForKp[i]];   // :1587
+            else if (matchForKp[i] == -2) CurrentFrame.mvpMapPoints[i] = nullptr;                           // :1621
+        }
         return nmatches;
     }
 

@@ -43,6 +43,13 @@ class MapPointsView(C.Structure):
                 ("view_cos", C.c_void_p), ("desc", C.c_void_p), ("observations", C.c_void_p)]
 
 
+class FramePointsView(C.Structure):
+    _fields_ = [("n", C.c_int), ("valid", C.c_void_p), ("u", C.c_void_p), ("v", C.c_void_p),
+                ("ur", C.c_void_p), ("radius", C.c_void_p), ("min_level", C.c_void_p),
+                ("max_level", C.c_void_p), ("angle", C.c_void_p), ("desc", C.c_void_p),
+                ("observations", C.c_void_p)]
+
+
 class PyramidView(C.Structure):
     _fields_ = [("nlevels", C.c_int), ("data", C.c_void_p), ("w", C.c_void_p), ("h", C.c_void_p),
                 ("stride", C.c_void_p)]
@@ -83,6 +90,8 @@ def lib():
         L.orc_features_in_area.argtypes = [C.POINTER(FrameView), C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_int]
         L.orc_three_maxima.argtypes = [C.c_void_p, C.c_int, _ip, _ip, _ip]
         L.orc_search_for_initialization.argtypes = [C.POINTER(FrameView), C.POINTER(FrameView), C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int]
+        L.orc_search_by_projection_frame.argtypes = [C.POINTER(FrameView), C.POINTER(FramePointsView), C.c_int, C.c_void_p, C.c_void_p]
+        L.orc_search_by_projection_frame.restype = C.c_int
         L.orc_search_by_projection.argtypes = [C.POINTER(FrameView), C.POINTER(MapPointsView), C.c_float, C.c_float, C.c_void_p, C.c_void_p]
         L.orc_compute_stereo_matches.argtypes = [C.POINTER(FrameView), C.POINTER(FrameView), C.POINTER(PyramidView), C.POINTER(PyramidView), C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
         L.orc_knn2.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -272,6 +281,19 @@ def search_by_projection(f, mps: dict, th: float, nnratio: float, occupied: np.n
                       ("track_in_view", "proj_x", "proj_y", "proj_xr", "level", "view_cos", "desc", "observations")])
     out = np.full(max(f[0].n, 1), -1, np.int32)
     nm = lib().orc_search_by_projection(C.byref(f[0]), C.byref(v), th, nnratio, occupied.ctypes.data, out.ctypes.data)
+    return nm, out[:f[0].n]
+
+
+def search_by_projection_frame(f, points: dict, check_ori: bool, occupied: np.ndarray):
+    """points: dict of arrays valid u8, u/v/ur/radius f32, min_level/max_level i32, angle f32,
+    desc u8[n,32], observations i32.  -> (nmatches, match_for_kp int32[n]: >=0 / -1 / -2)"""
+    arrs = dict(valid=np.uint8, u=np.float32, v=np.float32, ur=np.float32, radius=np.float32, min_level=np.int32,
+                max_level=np.int32, angle=np.float32, desc=np.uint8, observations=np.int32)
+    keep = {k: np.ascontiguousarray(points[k], t) for k, t in arrs.items()}
+    v = FramePointsView(len(keep["u"]), *[keep[k].ctypes.data for k in arrs])
+    occ = np.ascontiguousarray(occupied, np.uint8)
+    out = np.full(max(f[0].n, 1), -1, np.int32)
+    nm = lib().orc_search_by_projection_frame(C.byref(f[0]), C.byref(v), int(check_ori), occ.ctypes.data, out.ctypes.data)
     return nm, out[:f[0].n]
 
 

@@ -109,6 +109,26 @@ typedef struct {
 int   orc_search_by_projection(const orc_frame_view* f, const orc_mappoints_view* mps,
                                float th, float nnratio, uint8_t* kp_occupied,
                                int* out_mp_for_kp);
+/* SearchByProjection(CurrentFrame, LastFrame, th, bMono) — ORBmatcher.cc:1484-1630.  The pose
+ * arithmetic (:1494-1553) is the caller's: per last-frame point valid flag (map point present,
+ * not outlier, invzc >= 0, projection inside the image bounds), projection (u, v), right
+ * coordinate ur = u - mbf*invzc, radius = th*scale[octave], GetFeaturesInArea level arguments,
+ * keypoint angle, map point descriptor and Observations().  kp_occupied: 1 where
+ * CurrentFrame.mvpMapPoints[idx] holds a point with Observations()>0.  out_match_for_kp:
+ * >= 0 index of the last-frame point the keypoint ends up with, -1 untouched (caller
+ * initialises), -2 reset to NULL by the rotation check.  Returns nmatches. */
+typedef struct {
+    int n;
+    const uint8_t* valid;
+    const float* u; const float* v; const float* ur; const float* radius;
+    const int* min_level; const int* max_level;
+    const float* angle;
+    const uint8_t* desc;
+    const int* observations;
+} orc_framepoints_view;
+int   orc_search_by_projection_frame(const orc_frame_view* f, const orc_framepoints_view* pts,
+                                     int check_orientation, const uint8_t* kp_occupied,
+                                     int* out_match_for_kp);
 /* ComputeStereoMatches. pyramids: arrays of nlevels pointers + dims for left and right. */
 typedef struct {
     int nlevels;

@@ -208,6 +208,64 @@ extern "C" int orc_search_by_projection(const orc_frame_view* f, const orc_mappo
     return nmatches;
 }
 
+// SearchByProjection(CurrentFrame, LastFrame, th, bMono) — ORBmatcher.cc:1484-1630 (the loop body
+// from :1540 on; projection and the forward / backward decision are inputs)
+extern "C" int orc_search_by_projection_frame(const orc_frame_view* f, const orc_framepoints_view* pts,
+                                              int check_orientation, const uint8_t* kp_occupied,
+                                              int* match_for_kp) {
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];                                          // :1489-1492
+    const float factor = 1.0f / HISTO_LENGTH;
+    std::vector<int> cs(GRID_COLS * GRID_ROWS + 1), ci(std::max(f->n, 1)), cand(std::max(f->n, 1));
+    orc_assign_grid(f, cs.data(), ci.data());
+    // CurrentFrame.mvpMapPoints as far as the routine can tell: 0 = NULL or no observations,
+    // 1 = holds a point with observations
+    std::vector<uint8_t> occ(kp_occupied, kp_occupied + f->n);
+    for (int i = 0; i < pts->n; i++) {
+        if (!pts->valid[i]) continue;                                                // :1510-1538
+        const float u = pts->u[i], v = pts->v[i], radius = pts->radius[i];
+        const int nc = orc_features_in_area(f, cs.data(), ci.data(), u, v, radius, pts->min_level[i],
+                                            pts->max_level[i], cand.data(), f->n);      // :1547-1552
+        if (nc == 0) continue;
+        const uint8_t* dMP = pts->desc + 32 * (size_t)i;
+        int bestDist = 256, bestIdx2 = -1;
+        for (int c = 0; c < nc; c++) {
+            const int i2 = cand[c];
+            if (occ[i2]) continue;                                                   // :1567-1569
+            if (f->uright && f->uright[i2] > 0) {                                    // :1571-1577
+                const float er = std::fabs(pts->ur[i] - f->uright[i2]);
+                if (er > radius) continue;
+            }
+            const int dist = orc_descriptor_distance(dMP, f->desc + 32 * (size_t)i2);
+            if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }                 // :1583-1587
+        }
+        if (bestDist <= TH_HIGH) {                                                   // :1590-1608
+            match_for_kp[bestIdx2] = i;
+            occ[bestIdx2] = pts->observations[i] > 0;
+            nmatches++;
+            if (check_orientation) {
+                float rot = pts->angle[i] - f->kps[bestIdx2].angle;
+                if (rot < 0.0) rot += 360.0f;
+                int bin = (int)std::round(rot * factor);
+                if (bin == HISTO_LENGTH) bin = 0;
+                rotHist[bin].push_back(bestIdx2);
+            }
+        }
+    }
+    if (check_orientation) {                                                         // :1611-1628
+        int hist[HISTO_LENGTH], ind1 = -1, ind2 = -1, ind3 = -1;
+        for (int i = 0; i < HISTO_LENGTH; i++) hist[i] = (int)rotHist[i].size();
+        orc_three_maxima(hist, HISTO_LENGTH, &ind1, &ind2, &ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++)
+            if (i != ind1 && i != ind2 && i != ind3)
+                for (size_t j = 0; j < rotHist[i].size(); j++) {
+                    match_for_kp[rotHist[i][j]] = -2;
+                    nmatches--;
+                }
+    }
+    return nmatches;
+}
+
 // ComputeStereoMatches — Frame.cc:512-686
 extern "C" void orc_compute_stereo_matches(const orc_frame_view* L, const orc_frame_view* R,
                                            const orc_pyramid_view* pl, const orc_pyramid_view* pr,

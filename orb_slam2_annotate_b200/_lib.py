@@ -36,6 +36,13 @@ class MapPointsView(C.Structure):
                 ("view_cos", C.c_void_p), ("desc", C.c_void_p), ("observations", C.c_void_p)]
 
 
+class FramePointsView(C.Structure):
+    _fields_ = [("n", C.c_int32), ("valid", C.c_void_p), ("u", C.c_void_p), ("v", C.c_void_p),
+                ("ur", C.c_void_p), ("radius", C.c_void_p), ("min_level", C.c_void_p),
+                ("max_level", C.c_void_p), ("angle", C.c_void_p), ("desc", C.c_void_p),
+                ("observations", C.c_void_p)]
+
+
 class PyramidView(C.Structure):
     _fields_ = [("nlevels", C.c_int32), ("data", C.c_void_p), ("width", C.c_void_p),
                 ("height", C.c_void_p), ("stride", C.c_void_p)]
@@ -87,6 +94,7 @@ SIGNATURES = {
     "orbfe_search_init": (_i, [_vp, C.POINTER(FrameView), C.POINTER(FrameView), _vp, _vp, _i, _f, _i, _ip]),
     "orbfe_search_init_consecutive_device": (_i, [_vp, _vp, _vp, _vp, _i, _i, _f, _f, _f, _f, _i, _f, _i, _vp, _vp]),
     "orbfe_search_local_points": (_i, [_vp, C.POINTER(FrameView), C.POINTER(MapPointsView), _f, _f, _vp, _vp, _ip]),
+    "orbfe_search_frame_points": (_i, [_vp, C.POINTER(FrameView), C.POINTER(FramePointsView), _i, _vp, _vp, _ip]),
     "orbfe_stereo_match": (_i, [_vp, C.POINTER(FrameView), C.POINTER(FrameView), C.POINTER(PyramidView),
                                 C.POINTER(PyramidView), _vp, _f, _f, _vp, _vp]),
 }

@@ -304,6 +304,106 @@ int orbfe_search_local_points(orbfe_matcher* m, const orbfe_frame_view* f, const
     return ORBFE_OK;
 }
 
+
+// ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) — src/ORBmatcher.cc:1484-1630
+int orbfe_search_frame_points(orbfe_matcher* m, const orbfe_frame_view* f, const orbfe_framepoints_view* pts,
+                              int check_orientation, const uint8_t* kp_occupied, int32_t* match_for_kp,
+                              int* nmatches) {
+    if (!m || !pts || !nmatches) return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_search_frame_points");
+    int rc;
+    if ((rc = check_frame(f))) return rc;
+    *nmatches = 0;
+    const int n = f->n, np = pts->n;
+    if (n == 0 || np <= 0) return ORBFE_OK;
+    if (!kp_occupied || !match_for_kp || !pts->valid || !pts->u || !pts->v || !pts->radius || !pts->min_level ||
+        !pts->max_level || !pts->angle || !pts->desc || !pts->observations || (f->uright && !pts->ur))
+        return fail(ORBFE_ERR_ARG, "NULL array in frame / frame points view");
+    CU(cudaSetDevice(m->device));
+    cudaStream_t s = m->stream;
+    const size_t total = padded((size_t)n * sizeof(orbfe_keypoint)) + padded((size_t)n * 32) + padded((size_t)n * 4) +
+                         padded(np) + 7 * padded((size_t)np * 4) + padded((size_t)np * 32) + padded(3072 * 4) +
+                         padded((size_t)n * 2) + padded((size_t)(np + 1) * 4) + padded(n) + 4 * padded((size_t)n * 4) +
+                         padded((size_t)np * 4) + padded(8) + padded(32 * 4);
+    if ((rc = m->scratch[0].ensure(total))) return rc;
+    Arena A; A.base = m->scratch[0].p; A.cap = total;
+    LocalArgs a{};
+    auto up = [&](auto* dst, const void* src, size_t bytes) {
+        return cudaMemcpyAsync((void*)dst, src, bytes, cudaMemcpyHostToDevice, s);
+    };
+    orbfe_keypoint* d_kps = A.take<orbfe_keypoint>(n); CU(up(d_kps, f->kps, sizeof(orbfe_keypoint) * n));
+    uint8_t* d_desc = A.take<uint8_t>((size_t)n * 32); CU(up(d_desc, f->desc, (size_t)n * 32));
+    float* d_ur = A.take<float>(n);
+    if (f->uright) CU(up(d_ur, f->uright, sizeof(float) * n));
+    uint8_t* d_valid = A.take<uint8_t>(np); CU(up(d_valid, pts->valid, np));
+    float* d_u = A.take<float>(np); CU(up(d_u, pts->u, sizeof(float) * np));
+    float* d_v = A.take<float>(np); CU(up(d_v, pts->v, sizeof(float) * np));
+    float* d_pur = A.take<float>(np);
+    if (pts->ur) CU(up(d_pur, pts->ur, sizeof(float) * np));
+    float* d_rad = A.take<float>(np); CU(up(d_rad, pts->radius, sizeof(float) * np));
+    int* d_minl = A.take<int>(np); CU(up(d_minl, pts->min_level, sizeof(int) * np));
+    int* d_maxl = A.take<int>(np); CU(up(d_maxl, pts->max_level, sizeof(int) * np));
+    float* d_ang = A.take<float>(np); CU(up(d_ang, pts->angle, sizeof(float) * np));
+    uint8_t* d_pdesc = A.take<uint8_t>((size_t)np * 32); CU(up(d_pdesc, pts->desc, (size_t)np * 32));
+    a.cell_end = A.take<int>(3072);
+    a.items = A.take<unsigned short>(n);
+    a.cand_off = A.take<int>(np + 1);
+    uint8_t* d_occ = A.take<uint8_t>(n); CU(up(d_occ, kp_occupied, n));
+    int* d_owner[2] = {A.take<int>(n), A.take<int>(n)};
+    int* d_mpkp = A.take<int>(n);
+    a.kp_bad = A.take<int>(n);
+    int* d_obs = A.take<int>(np); CU(up(d_obs, pts->observations, sizeof(int) * np));
+    // (choice reuses the arena after obs)
+    int* d_flags = A.take<int>(2);           // [0] changed, [1] nmatches
+    a.hist = A.take<int>(32);
+    if (A.off > A.cap) return fail(ORBFE_ERR_CAPACITY, "internal: matcher arena overflow");
+    if ((rc = m->scratch[2].ensure((size_t)np * 4))) return rc;
+    a.choice = reinterpret_cast<int*>(m->scratch[2].p);
+    a.kps = d_kps; a.desc = d_desc; a.uright = f->uright ? d_ur : nullptr; a.n = n;
+    a.scale = nullptr; a.nlevels = f->nlevels; a.nmp = np; a.in_view = d_valid;
+    a.px = d_u; a.py = d_v; a.pxr = d_pur; a.level = nullptr; a.view_cos = nullptr; a.mpdesc = d_pdesc;
+    a.obs = d_obs; a.th = 1.0f; a.ratio = 1.0f; a.grid = grid_of(f); a.occ0 = d_occ; a.changed = d_flags;
+    a.mode = 1; a.radius = d_rad; a.min_level = d_minl; a.max_level = d_maxl; a.angle = d_ang;
+    a.checkOri = check_orientation;
+    launch_local_grid_and_count(a, s);
+    int ncand = 0;
+    CU(cudaMemcpyAsync(&ncand, a.cand_off + np, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    if ((rc = m->scratch[1].ensure((size_t)std::max(ncand, 1) * 4))) return rc;
+    a.cand = reinterpret_cast<uint32_t*>(m->scratch[1].p);
+    launch_local_fill(a, s);
+    // fixed-point sweeps over the first-owner array (0x7F7F7F7F = no owner), as in orbfe_search_local_points
+    CU(cudaMemsetAsync(d_owner[0], 0x7F, sizeof(int) * n, s));
+    int cur = 0;
+    for (int it = 0; it < np + 2; it++) {
+        a.owner_prev = d_owner[cur]; a.owner_next = d_owner[cur ^ 1];
+        CU(cudaMemsetAsync(a.owner_next, 0x7F, sizeof(int) * n, s));
+        CU(cudaMemsetAsync(d_flags, 0, sizeof(int), s));
+        launch_local_sweep(a, s);
+        int changed = 0;
+        CU(cudaMemcpyAsync(&changed, d_flags, sizeof(int), cudaMemcpyDeviceToHost, s));
+        CU(cudaStreamSynchronize(s));
+        cur ^= 1;
+        if (!changed) break;
+    }
+    a.owner_prev = d_owner[cur];
+    CU(cudaMemsetAsync(d_mpkp, 0xFF, sizeof(int) * n, s));
+    CU(cudaMemsetAsync(a.kp_bad, 0, sizeof(int) * n, s));
+    CU(cudaMemsetAsync(a.hist, 0, sizeof(int) * 32, s));
+    CU(cudaMemsetAsync(d_flags + 1, 0, sizeof(int), s));
+    launch_frame_finalize(a, d_mpkp, d_flags + 1, s);
+    CU(cudaGetLastError());
+    std::vector<int> h_mpkp(n), h_bad(n);
+    CU(cudaMemcpyAsync(h_mpkp.data(), d_mpkp, sizeof(int) * n, cudaMemcpyDeviceToHost, s));
+    CU(cudaMemcpyAsync(h_bad.data(), a.kp_bad, sizeof(int) * n, cudaMemcpyDeviceToHost, s));
+    CU(cudaMemcpyAsync(nmatches, d_flags + 1, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    for (int i = 0; i < n; i++) {
+        if (h_bad[i]) match_for_kp[i] = -2;              // mvpMapPoints[idx] = NULL (:1621)
+        else if (h_mpkp[i] >= 0) match_for_kp[i] = h_mpkp[i];   // mvpMapPoints[bestIdx2] = pMP (:1587)
+    }
+    return ORBFE_OK;
+}
+
 }  // extern "C"
 
 extern "C" int orbfe_stereo_match(orbfe_matcher* m, const orbfe_frame_view* left, const orbfe_frame_view* right,

@@ -51,6 +51,12 @@ struct LocalArgs {
     const uint8_t* mpdesc;
     const int* obs;
     float th, ratio;
+    // mode 1 = SearchByProjection(CurrentFrame, LastFrame) (ORBmatcher.cc:1484-1630): per point
+    // search radius and octave range come precomputed, best candidate only, rotation histogram
+    int mode;
+    const float* radius; const int* min_level; const int* max_level; const float* angle;
+    int checkOri; int* hist;     // [32] rotation histogram (mode 1)
+    int* kp_bad;                 // [n] keypoint lost its match to the rotation check (mode 1)
     GridGeom grid;
     // grid CSR of the frame
     int* cell_end; unsigned short* items;
@@ -81,6 +87,7 @@ int launch_local_grid_and_count(const LocalArgs& a, cudaStream_t st);
 int launch_local_fill(const LocalArgs& a, cudaStream_t st);
 int launch_local_sweep(const LocalArgs& a, cudaStream_t st);
 int launch_local_finalize(const LocalArgs& a, int* mp_for_kp, uint8_t* occ_out, int* nmatches, cudaStream_t st);
+int launch_frame_finalize(const LocalArgs& a, int* mp_for_kp, int* nmatches, cudaStream_t st);
 int launch_stereo(const StereoArgs& a, cudaStream_t st);
 
 }  // namespace orbfe

@@ -506,12 +506,18 @@ __global__ void __launch_bounds__(128) local_candidates_kernel(const __grid_cons
     int count = 0;
     uint32_t* out = FILL ? a.cand + a.cand_off[i] : nullptr;
     if (a.in_view[i]) {                                                                 // :58-62
-        const int lvl = a.level[i];
-        float r = (double)a.view_cos[i] > 0.998 ? 2.5f : 4.0f;                          // :146-152 (double compare)
-        if (a.th != 1.0f) r = __fmul_rn(r, a.th);                                       // :56,:69-70
-        const float rs = __fmul_rn(r, a.scale[lvl]);
+        float rs;
+        int minLevel, maxLevel;
+        if (a.mode == 0) {
+            const int lvl = a.level[i];
+            float r = (double)a.view_cos[i] > 0.998 ? 2.5f : 4.0f;                      // :146-152 (double compare)
+            if (a.th != 1.0f) r = __fmul_rn(r, a.th);                                   // :56,:69-70
+            rs = __fmul_rn(r, a.scale[lvl]);
+            minLevel = lvl - 1; maxLevel = lvl;
+        } else {                                                                        // :1542-1553
+            rs = a.radius[i]; minLevel = a.min_level[i]; maxLevel = a.max_level[i];
+        }
         const float x = a.px[i], y = a.py[i];
-        const int minLevel = lvl - 1, maxLevel = lvl;
         const bool check = (minLevel > 0) || (maxLevel >= 0);                           // Frame.cc:381
         int cx0, cx1, cy0, cy1;
         if (cell_window(a.grid, x, y, rs, cx0, cx1, cy0, cy1)) {
@@ -593,9 +599,12 @@ __global__ void __launch_bounds__(128) local_select_kernel(const __grid_constant
         }
     }
     int ch = -1;
-    if (bestDist <= TH_HIGH &&                                                          // :127-135
-        !(bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(a.ratio, (float)bestDist2)))
+    if (a.mode == 1) {
+        if (bestDist <= TH_HIGH) ch = bestIdx;                                          // :1585-1589, best only
+    } else if (bestDist <= TH_HIGH &&                                                   // :127-135
+               !(bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(a.ratio, (float)bestDist2))) {
         ch = bestIdx;
+    }
     a.choice[i] = ch;
     if (ch >= 0 && a.obs[i] > 0) atomicMin(&a.owner_next[ch], i);
 }
@@ -614,6 +623,40 @@ local_finalize_kernel(const __grid_constant__ LocalArgs a, int* mp_for_kp, uint8
         atomicMax(&mp_for_kp[a.choice[i]], i);
         atomicAdd(nmatches, 1);
     }
+}
+
+// SearchByProjection(CurrentFrame, LastFrame) epilogue (:1589-1628): every accepted point is a
+// match event (a keypoint can be taken more than once when the earlier taker has no
+// observations); events whose rotation bin is not one of the three maxima clear their keypoint
+// and are subtracted from the count.
+__global__ void __launch_bounds__(128) frame_hist_kernel(const __grid_constant__ LocalArgs a) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.nmp || a.choice[i] < 0) return;
+    float rot = __fsub_rn(a.angle[i], a.kps[a.choice[i]].angle);
+    if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+    int bin = (int)roundf(__fmul_rn(rot, 1.0f / HISTO));
+    if (bin == HISTO) bin = 0;
+    atomicAdd(&a.hist[bin], 1);
+}
+
+__global__ void __launch_bounds__(128)
+frame_finalize_kernel(const __grid_constant__ LocalArgs a, int* mp_for_kp, int* nmatches) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.nmp || a.choice[i] < 0) return;
+    const int k = a.choice[i];
+    bool bad = false;
+    if (a.checkOri) {
+        int ind1, ind2, ind3;
+        three_maxima(a.hist, ind1, ind2, ind3);
+        float rot = __fsub_rn(a.angle[i], a.kps[k].angle);
+        if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+        int bin = (int)roundf(__fmul_rn(rot, 1.0f / HISTO));
+        if (bin == HISTO) bin = 0;
+        bad = bin != ind1 && bin != ind2 && bin != ind3;
+    }
+    if (bad) a.kp_bad[k] = 1;
+    else atomicAdd(nmatches, 1);
+    atomicMax(&mp_for_kp[k], i);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -807,6 +850,13 @@ int launch_local_finalize(const LocalArgs& a, int* mp_for_kp, uint8_t* occ_out, 
     const int m = a.n > a.nmp ? a.n : a.nmp;
     if (m > 0) local_finalize_kernel<<<(m + 127) / 128, 128, 0, st>>>(a, mp_for_kp, occ_out, nmatches);
     return 1;
+}
+
+int launch_frame_finalize(const LocalArgs& a, int* mp_for_kp, int* nmatches, cudaStream_t st) {
+    if (a.nmp <= 0) return 0;
+    if (a.checkOri) frame_hist_kernel<<<(a.nmp + 127) / 128, 128, 0, st>>>(a);
+    frame_finalize_kernel<<<(a.nmp + 127) / 128, 128, 0, st>>>(a, mp_for_kp, nmatches);
+    return a.checkOri ? 2 : 1;
 }
 
 int launch_stereo(const StereoArgs& a, cudaStream_t st) {

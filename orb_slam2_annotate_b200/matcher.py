@@ -10,7 +10,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._lib import KP_DTYPE, FrameView, MapPointsView, PyramidView, check
+from ._lib import KP_DTYPE, FrameView, MapPointsView, FramePointsView, PyramidView, check
 
 
 class Frame:
@@ -36,6 +36,46 @@ class Frame:
                          None if self.uright is None else self.uright.ctypes.data,
                          self.min_x, self.max_x, self.min_y, self.max_y,
                          self.scale_factors.ctypes.data, len(self.scale_factors))
+
+
+def project_last_frame(Tcw_cur: np.ndarray, Tcw_last: np.ndarray, world_pos: np.ndarray, last_octave: np.ndarray,
+                       has_point: np.ndarray, outlier: np.ndarray, *, fx: float, fy: float, cx: float, cy: float,
+                       mbf: float, mb: float, bounds: tuple, scale_factors: np.ndarray, th: float, mono: bool) -> dict:
+    """Host side of SearchByProjection(CurrentFrame, LastFrame, th, bMono), src/ORBmatcher.cc:1494-1553:
+    pose projection of the last frame's map points and the per-point search parameters, in cv::Mat
+    float32 semantics (3x3 * 3x1 products accumulate in double and round once, the translation is a
+    float add).  Returns the arrays `ORBmatcher.SearchByProjectionLast` takes (without angle / desc /
+    observations, which the caller adds) plus the forward / backward flags."""
+    f32 = np.float32
+    Tc, Tl = np.asarray(Tcw_cur, f32), np.asarray(Tcw_last, f32)
+    X = np.asarray(world_pos, f32).reshape(-1, 3)
+    mul = lambda A, b: (A.astype(np.float64) @ b.astype(np.float64)).astype(f32)      # cv::gemm, float data
+    Rcw, tcw = Tc[:3, :3], Tc[:3, 3]
+    twc = (-(Rcw.T.astype(np.float64) @ tcw.astype(np.float64))).astype(f32)             # :1497
+    Rlw, tlw = Tl[:3, :3], Tl[:3, 3]
+    tlc = (mul(Rlw, twc) + tlw).astype(f32)                                               # :1502
+    forward = bool(tlc[2] > f32(mb)) and not mono                                         # :1505-1506
+    backward = bool(-tlc[2] > f32(mb)) and not mono
+    x3Dc = ((Rcw.astype(np.float64) @ X.T.astype(np.float64)).astype(f32).T + tcw).astype(f32)   # :1516
+    xc, yc = x3Dc[:, 0], x3Dc[:, 1]
+    with np.errstate(divide="ignore"):
+        invzc = (1.0 / x3Dc[:, 2].astype(np.float64)).astype(f32)                         # :1520
+    u = (f32(fx) * xc * invzc + f32(cx)).astype(f32)                                      # :1528-1529
+    v = (f32(fy) * yc * invzc + f32(cy)).astype(f32)
+    minx, maxx, miny, maxy = (f32(b) for b in bounds)
+    valid = (np.asarray(has_point, bool) & ~np.asarray(outlier, bool) & ~(invzc < 0) &
+             ~((u < minx) | (u > maxx)) & ~((v < miny) | (v > maxy)))                    # :1510-1538
+    o = np.asarray(last_octave, np.int32)
+    radius = (f32(th) * np.asarray(scale_factors, f32)[o]).astype(f32)                    # :1543
+    if forward:
+        lo, hi = o.copy(), np.full_like(o, -1)                                            # :1547-1548
+    elif backward:
+        lo, hi = np.zeros_like(o), o.copy()                                               # :1549-1550
+    else:
+        lo, hi = o - 1, o + 1                                                             # :1551-1552
+    ur = (u - f32(mbf) * invzc).astype(f32)                                               # :1575
+    return dict(valid=valid.astype(np.uint8), u=u, v=v, ur=ur, radius=radius, min_level=lo.astype(np.int32),
+                max_level=hi.astype(np.int32), forward=forward, backward=backward)
 
 
 class ORBmatcher:
@@ -133,6 +173,27 @@ class ORBmatcher:
         check(self._L.orbfe_search_local_points(self._h, C.byref(fv), C.byref(v), th, self.mfNNratio,
                                                 occupied.ctypes.data, out.ctypes.data, C.byref(n)),
               "orbfe_search_local_points")
+        return n.value, out[:F.N]
+
+    FRAME_POINT_FIELDS = dict(valid=np.uint8, u=np.float32, v=np.float32, ur=np.float32, radius=np.float32,
+                              min_level=np.int32, max_level=np.int32, angle=np.float32, desc=np.uint8,
+                              observations=np.int32)
+
+    def SearchByProjectionLast(self, F: Frame, points: dict, occupied: np.ndarray | None = None):
+        """SearchByProjection(CurrentFrame, LastFrame, th, bMono) — src/ORBmatcher.cc:1484-1630, from the
+        projected last-frame points (see `project_last_frame`).  occupied u8[N]: keypoints whose map
+        point has observations.  -> (nmatches, match_for_kp int32[N]: >=0 last-frame index, -1
+        untouched, -2 cleared by the rotation check)"""
+        keep = {k: np.ascontiguousarray(points[k], t) for k, t in self.FRAME_POINT_FIELDS.items()}
+        v = FramePointsView(len(keep["u"]), *[keep[k].ctypes.data for k in self.FRAME_POINT_FIELDS])
+        if occupied is None:
+            occupied = np.zeros(max(F.N, 1), np.uint8)
+        out = np.full(max(F.N, 1), -1, np.int32)
+        n = C.c_int()
+        fv = F.view()
+        check(self._L.orbfe_search_frame_points(self._h, C.byref(fv), C.byref(v), int(self.mbCheckOrientation),
+                                                occupied.ctypes.data, out.ctypes.data, C.byref(n)),
+              "orbfe_search_frame_points")
         return n.value, out[:F.N]
 
     def ComputeStereoMatches(self, left: Frame, right: Frame, pyr_left: list, pyr_right: list,

@@ -93,6 +93,52 @@ def test_search_by_projection_local_points(orbfe, oracle, nmp, th, stereo):
     assert ng > 100
 
 
+def _last_frame_points(orbfe, k_last, d_last, k_cur, seed, mode, th, stereo):
+    """Last-frame map points placed so that the motion model projects them near their own
+    keypoints: world point = back-projection of the last keypoint at a random depth; the current
+    pose is the last one moved along z (forward / backward) or sideways (mono)."""
+    rng = np.random.default_rng(seed)
+    n = len(k_last)
+    fx = fy = 520.0; cx, cy = 320.0, 240.0
+    mbf = 40.0; mb = mbf / fx
+    z = rng.uniform(4.0, 12.0, n).astype(np.float32)
+    X = np.stack([(k_last["x"] - cx) / fx * z, (k_last["y"] - cy) / fy * z, z], 1).astype(np.float32)
+    T_last = np.eye(4, dtype=np.float32)
+    T_cur = np.eye(4, dtype=np.float32)
+    T_cur[:3, 3] = {"forward": (0.01, 0.0, -0.3), "backward": (0.0, 0.01, 0.3), "mono": (0.05, 0.02, -0.3)}[mode]
+    scale = np.float32(1.2) ** np.arange(8, dtype=np.float32)
+    pts = orbfe.project_last_frame(T_cur, T_last, X, k_last["octave"], rng.random(n) < 0.9, rng.random(n) < 0.05,
+                                   fx=fx, fy=fy, cx=cx, cy=cy, mbf=mbf, mb=mb, bounds=(0, 640, 0, 480),
+                                   scale_factors=scale, th=th, mono=(mode == "mono"))
+    assert pts["forward"] == (mode == "forward") and pts["backward"] == (mode == "backward")
+    desc = d_last.copy()
+    flips = rng.integers(0, 60, n)
+    for i in range(n):
+        bits = rng.choice(256, flips[i], replace=False)
+        np.bitwise_xor.at(desc[i], bits >> 3, (1 << (bits & 7)).astype(np.uint8))
+    pts.update(angle=k_last["angle"].astype(np.float32), desc=desc,
+               observations=rng.integers(0, 3, n).astype(np.int32))
+    return pts
+
+
+@pytest.mark.parametrize("mode,th,stereo,ori", [("mono", 15.0, False, True), ("mono", 7.0, False, False),
+                                                ("forward", 15.0, True, True), ("backward", 30.0, True, True)])
+def test_search_by_projection_last_frame(orbfe, oracle, mode, th, stereo, ori):
+    fr = _frames(oracle, "mono", 7, 2000)
+    (kl, dl, _, t), (kc, dc, _, _) = fr[0], fr[1]
+    rng = np.random.default_rng(3)
+    ur = np.where(rng.random(len(kc)) < 0.5, kc["x"] - 5, -1).astype(np.float32) if stereo else None
+    pts = _last_frame_points(orbfe, kl, dl, kc, 21, mode, th, stereo)
+    occ = (rng.random(len(kc)) < 0.05).astype(np.uint8)
+    F = orbfe.Frame(kc, dc, 640, 480, t["scale"], uright=ur)
+    ng, mg = orbfe.ORBmatcher(0.9, ori).SearchByProjectionLast(F, pts, occ.copy())
+    no, mo = oracle.search_by_projection_frame(oracle.frame_view(kc, dc, 640, 480, t["scale"], ur), pts, ori, occ)
+    assert ng == no and np.array_equal(mg, mo)
+    assert ng > 100 and (mo >= 0).sum() > 100
+    if ori:
+        assert (mo == -2).sum() > 0          # the rotation check removed something
+
+
 def test_compute_stereo_matches(orbfe, oracle):
     for seed in (0, 1):
         (kl, dl, pl, t), (kr, dr, pr, _) = _frames(oracle, "stereo", seed, 2000)

@@ -110,6 +110,44 @@ def test_search_by_projection_kat(oracle):
     assert n == 1 and out.tolist() == [0, -1]
 
 
+def test_search_by_projection_frame_kat(oracle):
+    """SearchByProjection(CurrentFrame, LastFrame) known answers (ORBmatcher.cc:1484-1630)."""
+    d0 = np.zeros(32, np.uint8)
+    # two keypoints 3 px apart, both octave 1; angles 0 and 100 degrees
+    k = np.array([kp(100, 100, 1, 0.0), kp(103, 100, 1, 100.0)], KP_DTYPE)
+    d = np.stack([d0, d0]); d[1, 0] = 0xFF                      # kp1 is 8 bits away from the points
+    f = oracle.frame_view(k, d, 640, 480, SCALE)
+
+    def pts(n, obs, minl, maxl, angle, valid=None, radius=5.0):
+        return dict(valid=valid or [1] * n, u=[100] * n, v=[100] * n, ur=[0] * n, radius=[radius] * n,
+                    min_level=[minl] * n, max_level=[maxl] * n, angle=angle, desc=np.stack([d0] * n), observations=obs)
+
+    occ = np.zeros(2, np.uint8)
+    # point 0 has no observations: it takes kp0 (distance 0) but does not block it, so point 1 takes kp0 again
+    # (two match events, :1587-1588), point 2 (observations) takes it a third time; no orientation check
+    n, out = oracle.search_by_projection_frame(f, pts(3, [0, 0, 2], 0, 2, [0, 0, 0]), False, occ)
+    assert n == 3 and out.tolist() == [2, -1]
+    # with observations the first point blocks kp0 (:1567-1569): the second falls back to kp1
+    n, out = oracle.search_by_projection_frame(f, pts(2, [1, 1], 0, 2, [0, 0]), False, occ)
+    assert n == 2 and out.tolist() == [0, 1]
+    # level window (:1547-1552): octave-1 keypoints are outside (2, -1) = "octave >= 2"
+    n, out = oracle.search_by_projection_frame(f, pts(1, [1], 2, -1, [0]), False, occ)
+    assert n == 0 and out.tolist() == [-1, -1]
+    # invalid points and initially occupied keypoints are skipped
+    n, out = oracle.search_by_projection_frame(f, pts(2, [1, 1], 0, 2, [0, 0], valid=[0, 1]), False, np.array([1, 0], np.uint8))
+    assert n == 1 and out.tolist() == [-1, 1]
+    # rotation check (:1611-1628): three events in bin 0 (rot 0) and one in bin round(260/30) = 9; bin 9 holds
+    # 1 < 0.1 * 3 ... no: 1 >= 0.3, so it survives as second maximum; make it 11 vs 1 to drop it
+    k2 = np.array([kp(100 + 8 * i, 100, 1, 0.0) for i in range(11)] + [kp(300, 100, 1, 100.0)], KP_DTYPE)
+    f2 = oracle.frame_view(k2, np.stack([d0] * 12), 640, 480, SCALE)
+    p = dict(valid=[1] * 12, u=[100 + 8 * i for i in range(11)] + [300], v=[100] * 12, ur=[0] * 12, radius=[2.0] * 12,
+             min_level=[0] * 12, max_level=[2] * 12, angle=[0.0] * 12, desc=np.stack([d0] * 12), observations=[1] * 12)
+    n, out = oracle.search_by_projection_frame(f2, p, True, np.zeros(12, np.uint8))
+    assert n == 11 and out.tolist() == list(range(11)) + [-2]
+    n, out = oracle.search_by_projection_frame(f2, p, False, np.zeros(12, np.uint8))
+    assert n == 12 and out.tolist() == list(range(12))
+
+
 def test_knn2_kat(oracle):
     t = np.zeros((3, 32), np.uint8); t[1, 0] = 1; t[2, 0] = 3
     q = np.zeros((1, 32), np.uint8)
