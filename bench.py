@@ -57,6 +57,50 @@ NCU_DRAM_BYTES_PER_1024 = {
 }
 
 
+def guided_search_timings(frame_img):
+    """The per-call guided searches beside their CPU restatement (part of the cpu_baseline leg):
+    SearchByProjection(Frame, MapPoints) at config 4's shape (20 000 map points against one
+    1000-keypoint frame) and SearchByProjection(CurrentFrame, LastFrame) (one point per last-frame
+    keypoint).  GPU = the host-buffer C-ABI call (copies and synchronisation included), CPU = the
+    oracle port on one core; ms per call, median of 5."""
+    from oracle import oracle_py as O
+    import orb_slam2_annotate_b200 as orbfe
+    rng = np.random.default_rng(4)
+    ex = orbfe.ORBextractor(NFEAT)
+    k, d = ex(frame_img)
+    scale = ex.GetScaleFactors()
+    n, nmp = len(k), 20000
+    src = rng.integers(0, n, nmp)
+    mps = dict(track_in_view=np.ones(nmp, np.uint8), proj_x=(k["x"][src] + rng.uniform(-3, 3, nmp)).astype(np.float32),
+               proj_y=(k["y"][src] + rng.uniform(-3, 3, nmp)).astype(np.float32), proj_xr=np.zeros(nmp, np.float32),
+               level=k["octave"][src].astype(np.int32), view_cos=np.full(nmp, 0.9, np.float32),
+               desc=d[src] ^ rng.integers(0, 2, (nmp, 32), dtype=np.uint8), observations=rng.integers(0, 3, nmp).astype(np.int32))
+    pts = dict(valid=np.ones(n, np.uint8), u=(k["x"] + rng.uniform(-4, 4, n)).astype(np.float32),
+               v=(k["y"] + rng.uniform(-4, 4, n)).astype(np.float32), ur=np.zeros(n, np.float32),
+               radius=(np.float32(15.0) * scale[k["octave"]]).astype(np.float32), min_level=(k["octave"] - 1).astype(np.int32),
+               max_level=(k["octave"] + 1).astype(np.int32), angle=k["angle"].astype(np.float32),
+               desc=d ^ rng.integers(0, 2, (n, 32), dtype=np.uint8), observations=rng.integers(0, 3, n).astype(np.int32))
+    F = orbfe.Frame(k, d, W, H, scale)
+    fo = O.frame_view(k, d, W, H, scale)
+    mt = orbfe.ORBmatcher(0.8, True)
+
+    def med(fn):
+        fn()
+        ts = []
+        for _ in range(5):
+            t0 = time.perf_counter(); fn(); ts.append(time.perf_counter() - t0)
+        return float(np.median(ts)) * 1e3
+
+    return {
+        "search_local_points": {"map_points": nmp, "keypoints": n,
+                                "gpu_ms_per_call": med(lambda: mt.SearchByProjection(F, mps, 3.0, np.zeros(n, np.uint8))),
+                                "cpu_ms_per_call": med(lambda: O.search_by_projection(fo, mps, 3.0, 0.8, np.zeros(n, np.uint8)))},
+        "search_frame_points": {"points": n, "keypoints": n,
+                                "gpu_ms_per_call": med(lambda: mt.SearchByProjectionLast(F, pts, np.zeros(n, np.uint8))),
+                                "cpu_ms_per_call": med(lambda: O.search_by_projection_frame(fo, pts, True, np.zeros(n, np.uint8)))},
+    }
+
+
 def make_frames(batch, seed):
     """`batch` distinct frames: crops of one synthetic canvas with per-frame noise."""
     distinct = min(batch, 256)
@@ -371,6 +415,7 @@ def main():
         if not args.no_cpu_baseline:
             r = cpu_reference_fps(frames[:256], seconds_budget=15.0)
             line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
+            line["guided_searches"] = guided_search_timings(frames[0])
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
