@@ -160,11 +160,13 @@ octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ De
             for (int c = tid; c < m; c += QT) S.tmp[c] = cc[base + c];
             __syncthreads();
             const int tot = block_exscan(S.tmp, m, wsum);
-            for (int c = wid; c < m; c += QT / 32) {
+            // one thread per cell: cells hold a handful of corners, and this way a CTA has
+            // hundreds of independent loads in flight instead of one short row per warp
+            for (int c = tid; c < m; c += QT) {
                 const int k = cc[base + c];
                 const uint32_t* src = ck + (long long)(base + c) * L.cellCap;
                 uint32_t* dst = pxy + run + S.tmp[c];
-                for (int i = lane; i < k; i += 32) dst[i] = src[i];
+                for (int i = 0; i < k; i++) dst[i] = __ldg(src + i);
             }
             run += tot;
             __syncthreads();
