@@ -112,8 +112,9 @@ int orbfe_extractor_last_launches(const orbfe_extractor* e);
 
 /* Per-stage device time of the last extract call, measured with CUDA events on the handle's
  * stream (enable before the call).  Stages, in order: level-0 upload/copy, pyramid resize
- * (all levels), FAST cells, Gaussian blur, quadtree, orientation + descriptors. */
-#define ORBFE_NUM_STAGES 6
+ * (all levels), FAST cells, Gaussian blur, quadtree, orientation + descriptors, Frame epilogue
+ * (undistortion + grid; zero unless orbfe_extractor_set_camera is active). */
+#define ORBFE_NUM_STAGES 7
 int orbfe_extractor_set_profiling(orbfe_extractor* e, int on);
 int orbfe_extractor_stage_times(orbfe_extractor* e, float* ms, int n);
 
@@ -128,6 +129,38 @@ int orbfe_pyramid_level(orbfe_extractor* e, int frame, int level, int blurred, u
  * Test tap for stage-by-stage parity. */
 int orbfe_level_raw_keypoints(orbfe_extractor* e, int frame, int level, int32_t* xys, int cap,
                               int* n);
+
+/* ------------------------------------------------------------------ frame epilogue ----- */
+/* What the Frame constructor does right after the extractor returns (SURVEY.md section 8(f)
+ * rank 2): Frame::UndistortKeyPoints (src/Frame.cc:443-475, cv::undistortPoints with R = I,
+ * P = K), Frame::ComputeImageBounds (:481-512) and Frame::AssignFeaturesToGrid (:246-267).
+ * Camera as Frame holds it: mK entries and mDistCoef = (k1 k2 p1 p2 [k3]); k3 = 0 when the
+ * settings file has none.  As in the reference only k1 decides whether anything is undistorted. */
+typedef struct {
+    float fx, fy, cx, cy;
+    float k1, k2, p1, p2, k3;
+} orbfe_camera;
+
+#define ORBFE_GRID_COLS 64   /* FRAME_GRID_COLS, include/Frame.h:39 */
+#define ORBFE_GRID_ROWS 48   /* FRAME_GRID_ROWS, include/Frame.h:38 */
+#define ORBFE_GRID_CELLS (ORBFE_GRID_COLS * ORBFE_GRID_ROWS)
+
+/* Fuses the epilogue into the extractor: bounds = {mnMinX, mnMaxX, mnMinY, mnMaxY} of a
+ * cols x rows image are computed once (the reference does it for the first frame only,
+ * mbInitialComputations) and every later extract call on the handle also leaves mvKeysUn and
+ * mGrid of each frame in device memory.  cam == NULL switches the epilogue off again. */
+int orbfe_extractor_set_camera(orbfe_extractor* e, const orbfe_camera* cam, int cols, int rows,
+                               float bounds[4]);
+/* device pointers of the last batch: kps_un [batch][cap] (mvKeysUn; cap as reported by
+ * orbfe_extractor_device_results), cell_end [batch][ORBFE_GRID_CELLS] and items [batch][cap]:
+ * mGrid[ix][iy] of a frame is items[cell_end[c-1] .. cell_end[c]) with c = ix*48 + iy
+ * (cell 0 starts at 0), keypoint indices in push_back order. */
+int orbfe_extractor_device_frames(orbfe_extractor* e, const orbfe_keypoint** d_kps_un,
+                                  const int32_t** d_cell_end, const uint16_t** d_items);
+/* the same copied to HOST: kps_un [batch][cap], cell_end [batch][ORBFE_GRID_CELLS],
+ * items [batch][cap]; any pointer may be NULL */
+int orbfe_extractor_fetch_frames(orbfe_extractor* e, int batch, orbfe_keypoint* kps_un, int cap,
+                                 int32_t* cell_end, uint16_t* items);
 
 /* ------------------------------------------------------------------ matcher ------------ */
 /* Scalar Hamming distance between two 256-bit descriptors, host side, for the reference's
@@ -152,6 +185,31 @@ typedef struct {
     const float* scale_factors;       /* mvScaleFactors                                     */
     int32_t nlevels;
 } orbfe_frame_view;
+
+/* Frame::ComputeImageBounds for callers without an extractor handle (HOST output). */
+int orbfe_image_bounds(orbfe_matcher* m, const orbfe_camera* cam, int cols, int rows,
+                       float bounds[4]);
+/* Frame::UndistortKeyPoints + Frame::AssignFeaturesToGrid of one frame, HOST pointers:
+ * kps[n] (mvKeys) -> kps_un[n] (mvKeysUn), cell_end[ORBFE_GRID_CELLS], items[n] (layout as in
+ * orbfe_extractor_device_frames); *n_in_grid = keypoints that landed inside the grid. */
+int orbfe_frame_assign(orbfe_matcher* m, const orbfe_camera* cam, const float bounds[4],
+                       const orbfe_keypoint* kps, int n, orbfe_keypoint* kps_un,
+                       int32_t* cell_end, uint16_t* items, int* n_in_grid);
+
+/* A Frame whose keypoints, descriptors and grid already sit in device memory (the extractor's
+ * results + epilogue): d_kps = mvKeysUn, d_cell_end / d_items = mGrid as above; d_uright may be
+ * NULL.  scale_factors stays a HOST pointer. */
+typedef struct {
+    int32_t n;
+    const orbfe_keypoint* d_kps;
+    const uint8_t* d_desc;
+    const float* d_uright;
+    const int32_t* d_cell_end;
+    const uint16_t* d_items;
+    float min_x, max_x, min_y, max_y;
+    const float* scale_factors;
+    int32_t nlevels;
+} orbfe_device_frame_view;
 
 /* Brute-force 2-nearest-neighbour Hamming search with the reference's acceptance rule
  * (strict '<' updates so the lowest train index wins ties; accept iff d1 <= th and
@@ -202,6 +260,12 @@ int orbfe_search_local_points(orbfe_matcher* m, const orbfe_frame_view* f,
                               const orbfe_mappoints_view* mps, float th, float nnratio,
                               uint8_t* kp_occupied, int32_t* mp_for_kp, int* nmatches);
 
+/* Same search against a device-resident frame: nothing of the frame is uploaded and the grid
+ * is not rebuilt.  The map-point side and the results stay HOST arrays. */
+int orbfe_search_local_points_resident(orbfe_matcher* m, const orbfe_device_frame_view* f,
+                                       const orbfe_mappoints_view* mps, float th, float nnratio,
+                                       uint8_t* kp_occupied, int32_t* mp_for_kp, int* nmatches);
+
 /* Points of the last frame projected into the current one by the motion model, for
  * SearchByProjection(CurrentFrame, LastFrame, th, bMono) (src/ORBmatcher.cc:1484-1630).  The
  * pose arithmetic (x3Dc = Rcw*x3Dw + tcw, u, v, invzc, bForward / bBackward, :1494-1553) stays
@@ -235,6 +299,11 @@ typedef struct {
 int orbfe_search_frame_points(orbfe_matcher* m, const orbfe_frame_view* f,
                               const orbfe_framepoints_view* pts, int check_orientation,
                               const uint8_t* kp_occupied, int32_t* match_for_kp, int* nmatches);
+
+int orbfe_search_frame_points_resident(orbfe_matcher* m, const orbfe_device_frame_view* f,
+                                       const orbfe_framepoints_view* pts, int check_orientation,
+                                       const uint8_t* kp_occupied, int32_t* match_for_kp,
+                                       int* nmatches);
 
 /* Pyramid of one extractor call, HOST pointers (interior pixels of mvImagePyramid[l]). */
 typedef struct {

@@ -94,6 +94,8 @@ def lib():
         L.orc_search_by_projection_frame.restype = C.c_int
         L.orc_search_by_projection.argtypes = [C.POINTER(FrameView), C.POINTER(MapPointsView), C.c_float, C.c_float, C.c_void_p, C.c_void_p]
         L.orc_compute_stereo_matches.argtypes = [C.POINTER(FrameView), C.POINTER(FrameView), C.POINTER(PyramidView), C.POINTER(PyramidView), C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+        L.orc_undistort_points.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_image_bounds.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.orc_knn2.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
@@ -250,14 +252,17 @@ class RefExtractor:
 
 
 # ----------------------------------------------------------------------------- matcher
-def frame_view(kps: np.ndarray, desc: np.ndarray, width: float, height: float, scale_factors: np.ndarray, uright=None):
-    """Returns (FrameView, keepalive list)."""
+def frame_view(kps: np.ndarray, desc: np.ndarray, width: float, height: float, scale_factors: np.ndarray, uright=None,
+               bounds=None):
+    """Returns (FrameView, keepalive list).  bounds = (mnMinX, mnMaxX, mnMinY, mnMaxY) overrides (0, width, 0, height)."""
     kps = np.ascontiguousarray(kps); desc = np.ascontiguousarray(desc, np.uint8)
     sf = np.ascontiguousarray(scale_factors, np.float32)
     keep = [kps, desc, sf]
     v = FrameView(len(kps), kps.ctypes.data, desc.ctypes.data, None, 0.0, float(width), 0.0, float(height), sf.ctypes.data, len(sf))
     if uright is not None:
         ur = np.ascontiguousarray(uright, np.float32); keep.append(ur); v.uright = ur.ctypes.data
+    if bounds is not None:
+        v.min_x, v.max_x, v.min_y, v.max_y = (float(b) for b in bounds)
     return v, keep
 
 
@@ -295,6 +300,31 @@ def search_by_projection_frame(f, points: dict, check_ori: bool, occupied: np.nd
     out = np.full(max(f[0].n, 1), -1, np.int32)
     nm = lib().orc_search_by_projection_frame(C.byref(f[0]), C.byref(v), int(check_ori), occ.ctypes.data, out.ctypes.data)
     return nm, out[:f[0].n]
+
+
+def undistort_points(xy: np.ndarray, cam, dist) -> np.ndarray:
+    """Frame::UndistortKeyPoints on (n, 2) float32 positions; cam = (fx, fy, cx, cy), dist = (k1, k2, p1, p2, k3)."""
+    xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    cam = np.ascontiguousarray(cam, np.float32); dist = np.ascontiguousarray(dist, np.float32)
+    assert cam.size == 4 and dist.size == 5
+    out = np.empty_like(xy)
+    lib().orc_undistort_points(xy.ctypes.data, len(xy), cam.ctypes.data, dist.ctypes.data, out.ctypes.data)
+    return out
+
+
+def image_bounds(cam, dist, cols: int, rows: int) -> np.ndarray:
+    """Frame::ComputeImageBounds -> float32 (mnMinX, mnMaxX, mnMinY, mnMaxY)."""
+    cam = np.ascontiguousarray(cam, np.float32); dist = np.ascontiguousarray(dist, np.float32)
+    b = np.empty(4, np.float32)
+    lib().orc_image_bounds(cam.ctypes.data, dist.ctypes.data, int(cols), int(rows), b.ctypes.data)
+    return b
+
+
+def assign_grid(f):
+    """Frame::AssignFeaturesToGrid of a frame_view -> (cell_start int32[3073], items int32[k]); cell = ix*48+iy."""
+    cs = np.zeros(64 * 48 + 1, np.int32); it = np.zeros(max(f[0].n, 1), np.int32)
+    lib().orc_assign_grid(f[0], cs.ctypes.data, it.ctypes.data)
+    return cs, it[:cs[-1]]
 
 
 def pyramid_view(levels: list[np.ndarray]):

@@ -138,6 +138,11 @@ void  orc_compute_stereo_matches(const orc_frame_view* left, const orc_frame_vie
                                  const orc_pyramid_view* pl, const orc_pyramid_view* pr,
                                  const float* inv_scale_factors, float mbf, float mb,
                                  float* uright_out, float* depth_out);
+/* Frame constructor epilogue (orc_frame.cpp).  cam = {fx, fy, cx, cy}; dist = {k1, k2, p1, p2, k3}.
+ * Frame::UndistortKeyPoints (Frame.cc:443-475): xy / out are n (x, y) pairs. */
+void  orc_undistort_points(const float* xy, int n, const float cam[4], const float dist[5], float* out);
+/* Frame::ComputeImageBounds (Frame.cc:481-512): bounds = {mnMinX, mnMaxX, mnMinY, mnMaxY} */
+void  orc_image_bounds(const float cam[4], const float dist[5], int cols, int rows, float bounds[4]);
 /* brute-force kNN-2 (+ratio): out_idx[m] = best train index or -1 if rejected,
  * out_d1/out_d2 best & second distances (always written). */
 void  orc_knn2(const uint8_t* q, int m, const uint8_t* t, int n, int th, float ratio,

@@ -43,6 +43,22 @@ class FramePointsView(C.Structure):
                 ("observations", C.c_void_p)]
 
 
+class Camera(C.Structure):
+    """mK entries + mDistCoef (k1 k2 p1 p2 k3) as Frame holds them."""
+    _fields_ = [(k, C.c_float) for k in ("fx", "fy", "cx", "cy", "k1", "k2", "p1", "p2", "k3")]
+
+
+class DeviceFrameView(C.Structure):
+    _fields_ = [("n", C.c_int32), ("d_kps", C.c_void_p), ("d_desc", C.c_void_p), ("d_uright", C.c_void_p),
+                ("d_cell_end", C.c_void_p), ("d_items", C.c_void_p),
+                ("min_x", C.c_float), ("max_x", C.c_float), ("min_y", C.c_float), ("max_y", C.c_float),
+                ("scale_factors", C.c_void_p), ("nlevels", C.c_int32)]
+
+
+GRID_COLS, GRID_ROWS = 64, 48
+GRID_CELLS = GRID_COLS * GRID_ROWS
+
+
 class PyramidView(C.Structure):
     _fields_ = [("nlevels", C.c_int32), ("data", C.c_void_p), ("width", C.c_void_p),
                 ("height", C.c_void_p), ("stride", C.c_void_p)]
@@ -95,6 +111,13 @@ SIGNATURES = {
     "orbfe_search_init_consecutive_device": (_i, [_vp, _vp, _vp, _vp, _i, _i, _f, _f, _f, _f, _i, _f, _i, _vp, _vp]),
     "orbfe_search_local_points": (_i, [_vp, C.POINTER(FrameView), C.POINTER(MapPointsView), _f, _f, _vp, _vp, _ip]),
     "orbfe_search_frame_points": (_i, [_vp, C.POINTER(FrameView), C.POINTER(FramePointsView), _i, _vp, _vp, _ip]),
+    "orbfe_extractor_set_camera": (_i, [_vp, C.POINTER(Camera), _i, _i, _vp]),
+    "orbfe_extractor_device_frames": (_i, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp)]),
+    "orbfe_extractor_fetch_frames": (_i, [_vp, _i, _vp, _i, _vp, _vp]),
+    "orbfe_image_bounds": (_i, [_vp, C.POINTER(Camera), _i, _i, _vp]),
+    "orbfe_frame_assign": (_i, [_vp, C.POINTER(Camera), _vp, _vp, _i, _vp, _vp, _vp, _ip]),
+    "orbfe_search_local_points_resident": (_i, [_vp, C.POINTER(DeviceFrameView), C.POINTER(MapPointsView), _f, _f, _vp, _vp, _ip]),
+    "orbfe_search_frame_points_resident": (_i, [_vp, C.POINTER(DeviceFrameView), C.POINTER(FramePointsView), _i, _vp, _vp, _ip]),
     "orbfe_stereo_match": (_i, [_vp, C.POINTER(FrameView), C.POINTER(FrameView), C.POINTER(PyramidView),
                                 C.POINTER(PyramidView), _vp, _f, _f, _vp, _vp]),
 }

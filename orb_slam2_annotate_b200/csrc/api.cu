@@ -9,6 +9,7 @@
 #include <vector>
 
 #include "api_common.cuh"
+#include "frame_internal.cuh"
 #include "orbfe_internal.cuh"
 #include <cuda.h>
 
@@ -59,9 +60,15 @@ struct orbfe_extractor {
     std::vector<CUtensorMap> tmaps;   // {level, blurred level} descriptors, passed to the kernel by value
     std::vector<CUtensorMap> fastMaps; // level descriptors with the FAST window box
     int lastBatch = 0, lastLaunches = 0;
+    // Frame epilogue (orbfe_extractor_set_camera): mvKeysUn + mGrid of every frame of a batch
+    bool haveCam = false;
+    CamGeom camGeom{};
+    DevArray<orbfe_keypoint> kpsUn;
+    DevArray<int> gridEnd;
+    DevArray<unsigned short> gridItems;
     // optional per-stage timing (events on the handle's stream)
     bool profiling = false;
-    cudaEvent_t ev[8] = {};
+    cudaEvent_t ev[ORBFE_NUM_STAGES + 1] = {};
     std::vector<int> h_counts;
 };
 
@@ -101,6 +108,15 @@ static void build_tables(orbfe_extractor* e, int nfeatures, float scaleFactor, i
         e->umax[v] = v0;
         ++v0;
     }
+}
+
+static int ensure_frame_bufs(orbfe_extractor* e, int batchCap, int outCap) {
+    if (outCap > 65535) return fail(ORBFE_ERR_CAPACITY, "frame grid items are 16-bit: more than 65535 keypoint slots per frame");
+    int rc;
+    if ((rc = e->kpsUn.ensure((size_t)batchCap * outCap))) return rc;
+    if ((rc = e->gridEnd.ensure((size_t)batchCap * ORBFE_GRID_CELLS))) return rc;
+    if ((rc = e->gridItems.ensure((size_t)batchCap * outCap))) return rc;
+    return 0;
 }
 
 // the orientation kernel walks patch columns: needs |u| <= umax[|v|]  <=>  |v| <= umax[|u|]
@@ -282,6 +298,7 @@ static int ensure_geometry(orbfe_extractor* e, int w, int h, int batch) {
     if ((rc = e->kps.ensure((size_t)cap * g.outCap))) return rc;
     if ((rc = e->desc.ensure((size_t)cap * g.outCap * 32))) return rc;
     if ((rc = e->counts.ensure(cap))) return rc;
+    if (e->haveCam && (rc = ensure_frame_bufs(e, cap, g.outCap))) return rc;
     // resize tables
     std::vector<int2> xall; std::vector<int4> yall;
     std::vector<int4> qall;
@@ -401,6 +418,10 @@ static int enqueue_extract(orbfe_extractor* e, int frame0 = 0, int count = -1, i
     }
     launches += launch_orient_desc(e->g, e->d, e->umax_d.p, st);
     if (prof) cudaEventRecord(e->ev[6], st);
+    if (e->haveCam)
+        launches += launch_frame_epilogue(e->camGeom, e->d.kps, e->d.counts, e->g.outCap, frame0, e->g.batch, e->kpsUn.p,
+                                          e->gridEnd.p, e->gridItems.p, st);
+    if (prof) cudaEventRecord(e->ev[7], st);
     e->g.frame0 = 0;
     e->g.batch = fullBatch;
     e->lastLaunches = frame0 == 0 ? launches : e->lastLaunches + launches;
@@ -514,7 +535,7 @@ void orbfe_extractor_destroy(orbfe_extractor* e) {
     for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);
     e->pyr.release(); e->blur.release(); e->desc.release(); e->cellc.release(); e->selc.release();
     e->counts.release(); e->umax_d.release(); e->cellk.release(); e->sel.release();
-    e->qt_xy.release(); e->qt_node.release(); e->kps.release(); e->xtab.release(); e->ytab.release(); e->xq.release(); e->celltab.release();
+    e->qt_xy.release(); e->qt_node.release(); e->kps.release(); e->kpsUn.release(); e->gridEnd.release(); e->gridItems.release(); e->xtab.release(); e->ytab.release(); e->xq.release(); e->celltab.release();
     delete e;
 }
 
@@ -724,8 +745,66 @@ int orbfe_extractor_set_profiling(orbfe_extractor* e, int on) {
 int orbfe_extractor_stage_times(orbfe_extractor* e, float* ms, int n) {
     if (!e || !ms || n < ORBFE_NUM_STAGES || !e->ev[0]) return fail(ORBFE_ERR_ARG, "profiling was not enabled");
     CU(cudaSetDevice(e->device));
-    CU(cudaEventSynchronize(e->ev[6]));
+    CU(cudaEventSynchronize(e->ev[ORBFE_NUM_STAGES]));
     for (int i = 0; i < ORBFE_NUM_STAGES; i++) CU(cudaEventElapsedTime(&ms[i], e->ev[i], e->ev[i + 1]));
+    return ORBFE_OK;
+}
+
+// Frame::ComputeImageBounds once per camera (Frame.cc:97-111), then the epilogue rides on every extract call
+int orbfe_extractor_set_camera(orbfe_extractor* e, const orbfe_camera* cam, int cols, int rows, float bounds[4]) {
+    if (!e) return fail(ORBFE_ERR_ARG, "extractor is NULL");
+    CU(cudaSetDevice(e->device));
+    CU(cudaStreamSynchronize(e->stream));
+    if (!cam) { e->haveCam = false; return ORBFE_OK; }
+    if (cols <= 0 || rows <= 0 || !(cam->fx != 0.0f) || !(cam->fy != 0.0f))
+        return fail(ORBFE_ERR_ARG, "bad camera / image size in orbfe_extractor_set_camera");
+    int rc;
+    if ((rc = e->gridEnd.ensure(ORBFE_GRID_CELLS))) return rc;      // doubles as the corner scratch
+    float b[4];
+    if ((rc = image_bounds_device(*cam, cols, rows, e->gridEnd.p, e->stream, b))) return rc;
+    if (!(b[1] > b[0]) || !(b[3] > b[2])) return fail(ORBFE_ERR_ARG, "camera gives empty image bounds");
+    e->camGeom = cam_geom(*cam, b);
+    if (e->geomBatchCap && (rc = ensure_frame_bufs(e, e->geomBatchCap, e->g.outCap))) return rc;
+    e->haveCam = true;
+    if (bounds) std::memcpy(bounds, b, sizeof(b));
+    return ORBFE_OK;
+}
+
+int orbfe_extractor_device_frames(orbfe_extractor* e, const orbfe_keypoint** d_kps_un, const int32_t** d_cell_end,
+                                  const uint16_t** d_items) {
+    if (!e || !e->geomW || !e->haveCam || !e->kpsUn.p)
+        return fail(ORBFE_ERR_ARG, "no extraction with a camera (orbfe_extractor_set_camera) has run on this handle");
+    if (d_kps_un) *d_kps_un = e->kpsUn.p;
+    if (d_cell_end) *d_cell_end = e->gridEnd.p;
+    if (d_items) *d_items = e->gridItems.p;
+    return ORBFE_OK;
+}
+
+int orbfe_extractor_fetch_frames(orbfe_extractor* e, int batch, orbfe_keypoint* kps_un, int cap, int32_t* cell_end,
+                                 uint16_t* items) {
+    if (!e || !e->geomW || !e->haveCam || !e->kpsUn.p || batch < 1 || batch > e->lastBatch)
+        return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_extractor_fetch_frames");
+    const int oc = e->g.outCap;
+    if ((kps_un || items) && cap < oc) {
+        // rows are copied whole: the caller's slots must hold what the device rows hold
+        std::vector<int> counts(batch);
+        CU(cudaSetDevice(e->device));
+        CU(cudaMemcpyAsync(counts.data(), e->d.counts, sizeof(int) * batch, cudaMemcpyDeviceToHost, e->stream));
+        CU(cudaStreamSynchronize(e->stream));
+        for (int b = 0; b < batch; b++)
+            if (counts[b] > cap) return fail(ORBFE_ERR_CAPACITY, "keypoint capacity too small (see orbfe_extractor_max_keypoints)");
+    }
+    CU(cudaSetDevice(e->device));
+    const int w = std::min(cap, oc);
+    if (kps_un)
+        CU(cudaMemcpy2DAsync(kps_un, (size_t)cap * sizeof(orbfe_keypoint), e->kpsUn.p, (size_t)oc * sizeof(orbfe_keypoint),
+                             (size_t)w * sizeof(orbfe_keypoint), batch, cudaMemcpyDeviceToHost, e->stream));
+    if (items)
+        CU(cudaMemcpy2DAsync(items, (size_t)cap * 2, e->gridItems.p, (size_t)oc * 2, (size_t)w * 2, batch,
+                             cudaMemcpyDeviceToHost, e->stream));
+    if (cell_end)
+        CU(cudaMemcpyAsync(cell_end, e->gridEnd.p, sizeof(int) * ORBFE_GRID_CELLS * (size_t)batch, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
     return ORBFE_OK;
 }
 

@@ -6,6 +6,7 @@
 #include <vector>
 
 #include "api_common.cuh"
+#include "frame_internal.cuh"
 #include "match_internal.cuh"
 
 using namespace orbfe;
@@ -209,9 +210,32 @@ int orbfe_search_init_consecutive_device(orbfe_matcher* m, const orbfe_keypoint*
     return ORBFE_OK;
 }
 
-int orbfe_search_local_points(orbfe_matcher* m, const orbfe_frame_view* f, const orbfe_mappoints_view* mps,
-                              float th, float nnratio, uint8_t* kp_occupied, int32_t* mp_for_kp,
-                              int* nmatches) {
+}  // extern "C"
+
+namespace {
+
+// host view standing in for a device-resident frame: sizes, bounds and scale factors are read
+// from it, its kps / desc / uright pointers are only tested for NULL
+orbfe_frame_view host_side_of(const orbfe_device_frame_view* df) {
+    orbfe_frame_view f{};
+    f.n = df->n; f.kps = df->d_kps; f.desc = df->d_desc; f.uright = df->d_uright;
+    f.min_x = df->min_x; f.max_x = df->max_x; f.min_y = df->min_y; f.max_y = df->max_y;
+    f.scale_factors = df->scale_factors; f.nlevels = df->nlevels;
+    return f;
+}
+
+int check_device_frame(const orbfe_device_frame_view* df) {
+    if (!df) return fail(ORBFE_ERR_ARG, "device frame view is NULL");
+    if (df->n > 0 && (!df->d_kps || !df->d_desc || !df->d_cell_end || !df->d_items))
+        return fail(ORBFE_ERR_ARG, "NULL device pointer in device frame view");
+    if ((uintptr_t)df->d_desc & 15) return fail(ORBFE_ERR_ARG, "device descriptors must be 16-byte aligned");
+    return 0;
+}
+
+// df != NULL: the frame side (keypoints, descriptors, uright, grid) is already in device memory
+int search_local_points_impl(orbfe_matcher* m, const orbfe_frame_view* f, const orbfe_device_frame_view* df,
+                             const orbfe_mappoints_view* mps, float th, float nnratio, uint8_t* kp_occupied,
+                             int32_t* mp_for_kp, int* nmatches) {
     if (!m || !mps || !nmatches) return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_search_local_points");
     int rc;
     if ((rc = check_frame(f))) return rc;
@@ -234,10 +258,19 @@ int orbfe_search_local_points(orbfe_matcher* m, const orbfe_frame_view* f, const
     auto up = [&](auto* dst, const void* src, size_t bytes) {
         return cudaMemcpyAsync((void*)dst, src, bytes, cudaMemcpyHostToDevice, s);
     };
-    orbfe_keypoint* d_kps = A.take<orbfe_keypoint>(n); CU(up(d_kps, f->kps, sizeof(orbfe_keypoint) * n));
-    uint8_t* d_desc = A.take<uint8_t>((size_t)n * 32); CU(up(d_desc, f->desc, (size_t)n * 32));
-    float* d_ur = A.take<float>(n);
-    if (f->uright) CU(up(d_ur, f->uright, sizeof(float) * n));
+    const orbfe_keypoint* d_kps; const uint8_t* d_desc; const float* d_ur;
+    if (df) {
+        d_kps = df->d_kps; d_desc = df->d_desc; d_ur = df->d_uright;
+        a.cell_end = const_cast<int*>(df->d_cell_end); a.items = const_cast<unsigned short*>(df->d_items);
+    } else {
+        orbfe_keypoint* k = A.take<orbfe_keypoint>(n); CU(up(k, f->kps, sizeof(orbfe_keypoint) * n));
+        uint8_t* dd = A.take<uint8_t>((size_t)n * 32); CU(up(dd, f->desc, (size_t)n * 32));
+        float* ur = A.take<float>(n);
+        if (f->uright) CU(up(ur, f->uright, sizeof(float) * n));
+        d_kps = k; d_desc = dd; d_ur = ur;
+        a.cell_end = A.take<int>(3072);
+        a.items = A.take<unsigned short>(n);
+    }
     float* d_scale = A.take<float>(f->nlevels); CU(up(d_scale, f->scale_factors, sizeof(float) * f->nlevels));
     uint8_t* d_inview = A.take<uint8_t>(nmp); CU(up(d_inview, mps->track_in_view, nmp));
     float* d_px = A.take<float>(nmp); CU(up(d_px, mps->proj_x, sizeof(float) * nmp));
@@ -248,8 +281,6 @@ int orbfe_search_local_points(orbfe_matcher* m, const orbfe_frame_view* f, const
     float* d_cos = A.take<float>(nmp); CU(up(d_cos, mps->view_cos, sizeof(float) * nmp));
     uint8_t* d_mpdesc = A.take<uint8_t>((size_t)nmp * 32); CU(up(d_mpdesc, mps->desc, (size_t)nmp * 32));
     int* d_obs = A.take<int>(nmp); CU(up(d_obs, mps->observations, sizeof(int) * nmp));
-    a.cell_end = A.take<int>(3072);
-    a.items = A.take<unsigned short>(n);
     a.cand_off = A.take<int>(nmp + 1);
     uint8_t* d_occ = A.take<uint8_t>(n); CU(up(d_occ, kp_occupied, n));
     int* d_owner[2] = {A.take<int>(n), A.take<int>(n)};
@@ -266,7 +297,7 @@ int orbfe_search_local_points(orbfe_matcher* m, const orbfe_frame_view* f, const
     for (int i = 0; i < nmp; i++)
         if (mps->track_in_view[i] && (mps->level[i] < 0 || mps->level[i] >= f->nlevels))
             return fail(ORBFE_ERR_ARG, "map point scale level outside the frame's pyramid");
-    launch_local_grid_and_count(a, s);
+    launch_local_grid_and_count(a, s, df == nullptr);
     int ncand = 0;
     CU(cudaMemcpyAsync(&ncand, a.cand_off + nmp, sizeof(int), cudaMemcpyDeviceToHost, s));
     CU(cudaStreamSynchronize(s));
@@ -306,9 +337,9 @@ int orbfe_search_local_points(orbfe_matcher* m, const orbfe_frame_view* f, const
 
 
 // ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) — src/ORBmatcher.cc:1484-1630
-int orbfe_search_frame_points(orbfe_matcher* m, const orbfe_frame_view* f, const orbfe_framepoints_view* pts,
-                              int check_orientation, const uint8_t* kp_occupied, int32_t* match_for_kp,
-                              int* nmatches) {
+int search_frame_points_impl(orbfe_matcher* m, const orbfe_frame_view* f, const orbfe_device_frame_view* df,
+                             const orbfe_framepoints_view* pts, int check_orientation, const uint8_t* kp_occupied,
+                             int32_t* match_for_kp, int* nmatches) {
     if (!m || !pts || !nmatches) return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_search_frame_points");
     int rc;
     if ((rc = check_frame(f))) return rc;
@@ -330,10 +361,19 @@ int orbfe_search_frame_points(orbfe_matcher* m, const orbfe_frame_view* f, const
     auto up = [&](auto* dst, const void* src, size_t bytes) {
         return cudaMemcpyAsync((void*)dst, src, bytes, cudaMemcpyHostToDevice, s);
     };
-    orbfe_keypoint* d_kps = A.take<orbfe_keypoint>(n); CU(up(d_kps, f->kps, sizeof(orbfe_keypoint) * n));
-    uint8_t* d_desc = A.take<uint8_t>((size_t)n * 32); CU(up(d_desc, f->desc, (size_t)n * 32));
-    float* d_ur = A.take<float>(n);
-    if (f->uright) CU(up(d_ur, f->uright, sizeof(float) * n));
+    const orbfe_keypoint* d_kps; const uint8_t* d_desc; const float* d_ur;
+    if (df) {
+        d_kps = df->d_kps; d_desc = df->d_desc; d_ur = df->d_uright;
+        a.cell_end = const_cast<int*>(df->d_cell_end); a.items = const_cast<unsigned short*>(df->d_items);
+    } else {
+        orbfe_keypoint* k = A.take<orbfe_keypoint>(n); CU(up(k, f->kps, sizeof(orbfe_keypoint) * n));
+        uint8_t* dd = A.take<uint8_t>((size_t)n * 32); CU(up(dd, f->desc, (size_t)n * 32));
+        float* ur = A.take<float>(n);
+        if (f->uright) CU(up(ur, f->uright, sizeof(float) * n));
+        d_kps = k; d_desc = dd; d_ur = ur;
+        a.cell_end = A.take<int>(3072);
+        a.items = A.take<unsigned short>(n);
+    }
     uint8_t* d_valid = A.take<uint8_t>(np); CU(up(d_valid, pts->valid, np));
     float* d_u = A.take<float>(np); CU(up(d_u, pts->u, sizeof(float) * np));
     float* d_v = A.take<float>(np); CU(up(d_v, pts->v, sizeof(float) * np));
@@ -344,8 +384,6 @@ int orbfe_search_frame_points(orbfe_matcher* m, const orbfe_frame_view* f, const
     int* d_maxl = A.take<int>(np); CU(up(d_maxl, pts->max_level, sizeof(int) * np));
     float* d_ang = A.take<float>(np); CU(up(d_ang, pts->angle, sizeof(float) * np));
     uint8_t* d_pdesc = A.take<uint8_t>((size_t)np * 32); CU(up(d_pdesc, pts->desc, (size_t)np * 32));
-    a.cell_end = A.take<int>(3072);
-    a.items = A.take<unsigned short>(n);
     a.cand_off = A.take<int>(np + 1);
     uint8_t* d_occ = A.take<uint8_t>(n); CU(up(d_occ, kp_occupied, n));
     int* d_owner[2] = {A.take<int>(n), A.take<int>(n)};
@@ -364,7 +402,7 @@ int orbfe_search_frame_points(orbfe_matcher* m, const orbfe_frame_view* f, const
     a.obs = d_obs; a.th = 1.0f; a.ratio = 1.0f; a.grid = grid_of(f); a.occ0 = d_occ; a.changed = d_flags;
     a.mode = 1; a.radius = d_rad; a.min_level = d_minl; a.max_level = d_maxl; a.angle = d_ang;
     a.checkOri = check_orientation;
-    launch_local_grid_and_count(a, s);
+    launch_local_grid_and_count(a, s, df == nullptr);
     int ncand = 0;
     CU(cudaMemcpyAsync(&ncand, a.cand_off + np, sizeof(int), cudaMemcpyDeviceToHost, s));
     CU(cudaStreamSynchronize(s));
@@ -401,6 +439,82 @@ int orbfe_search_frame_points(orbfe_matcher* m, const orbfe_frame_view* f, const
         if (h_bad[i]) match_for_kp[i] = -2;              // mvpMapPoints[idx] = NULL (:1621)
         else if (h_mpkp[i] >= 0) match_for_kp[i] = h_mpkp[i];   // mvpMapPoints[bestIdx2] = pMP (:1587)
     }
+    return ORBFE_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int orbfe_search_local_points(orbfe_matcher* m, const orbfe_frame_view* f, const orbfe_mappoints_view* mps,
+                              float th, float nnratio, uint8_t* kp_occupied, int32_t* mp_for_kp, int* nmatches) {
+    return search_local_points_impl(m, f, nullptr, mps, th, nnratio, kp_occupied, mp_for_kp, nmatches);
+}
+
+int orbfe_search_local_points_resident(orbfe_matcher* m, const orbfe_device_frame_view* df,
+                                       const orbfe_mappoints_view* mps, float th, float nnratio,
+                                       uint8_t* kp_occupied, int32_t* mp_for_kp, int* nmatches) {
+    int rc;
+    if ((rc = check_device_frame(df))) return rc;
+    const orbfe_frame_view f = host_side_of(df);
+    return search_local_points_impl(m, &f, df, mps, th, nnratio, kp_occupied, mp_for_kp, nmatches);
+}
+
+int orbfe_search_frame_points(orbfe_matcher* m, const orbfe_frame_view* f, const orbfe_framepoints_view* pts,
+                              int check_orientation, const uint8_t* kp_occupied, int32_t* match_for_kp,
+                              int* nmatches) {
+    return search_frame_points_impl(m, f, nullptr, pts, check_orientation, kp_occupied, match_for_kp, nmatches);
+}
+
+int orbfe_search_frame_points_resident(orbfe_matcher* m, const orbfe_device_frame_view* df,
+                                       const orbfe_framepoints_view* pts, int check_orientation,
+                                       const uint8_t* kp_occupied, int32_t* match_for_kp, int* nmatches) {
+    int rc;
+    if ((rc = check_device_frame(df))) return rc;
+    const orbfe_frame_view f = host_side_of(df);
+    return search_frame_points_impl(m, &f, df, pts, check_orientation, kp_occupied, match_for_kp, nmatches);
+}
+
+// Frame::ComputeImageBounds (src/Frame.cc:481-512)
+int orbfe_image_bounds(orbfe_matcher* m, const orbfe_camera* cam, int cols, int rows, float bounds[4]) {
+    if (!m || !cam || !bounds || cols <= 0 || rows <= 0 || !(cam->fx != 0.0f) || !(cam->fy != 0.0f))
+        return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_image_bounds");
+    CU(cudaSetDevice(m->device));
+    int rc;
+    if ((rc = m->scratch[4].ensure(256))) return rc;
+    return image_bounds_device(*cam, cols, rows, m->scratch[4].p, m->stream, bounds);
+}
+
+// Frame::UndistortKeyPoints + Frame::AssignFeaturesToGrid (src/Frame.cc:443-475, :246-267)
+int orbfe_frame_assign(orbfe_matcher* m, const orbfe_camera* cam, const float bounds[4], const orbfe_keypoint* kps,
+                       int n, orbfe_keypoint* kps_un, int32_t* cell_end, uint16_t* items, int* n_in_grid) {
+    if (!m || !cam || !bounds || n < 0 || !cell_end || (n && (!kps || !kps_un || !items)))
+        return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_frame_assign");
+    if (n > 65535) return fail(ORBFE_ERR_CAPACITY, "frame grid items are 16-bit: more than 65535 keypoints");
+    if (!(bounds[1] > bounds[0]) || !(bounds[3] > bounds[2])) return fail(ORBFE_ERR_ARG, "empty image bounds");
+    CU(cudaSetDevice(m->device));
+    cudaStream_t s = m->stream;
+    const int nn = std::max(n, 1);
+    const size_t total = 2 * padded((size_t)nn * sizeof(orbfe_keypoint)) + padded(3072 * 4) + padded((size_t)nn * 2) + padded(4);
+    int rc;
+    if ((rc = m->scratch[4].ensure(total))) return rc;
+    Arena A; A.base = m->scratch[4].p; A.cap = total;
+    orbfe_keypoint* d_kps = A.take<orbfe_keypoint>(nn);
+    orbfe_keypoint* d_un = A.take<orbfe_keypoint>(nn);
+    int* d_end = A.take<int>(3072);
+    unsigned short* d_items = A.take<unsigned short>(nn);
+    int* d_n = A.take<int>(1);
+    if (n) CU(cudaMemcpyAsync(d_kps, kps, sizeof(orbfe_keypoint) * n, cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(d_n, &n, sizeof(int), cudaMemcpyHostToDevice, s));
+    launch_frame_epilogue(cam_geom(*cam, bounds), d_kps, d_n, nn, 0, 1, d_un, d_end, d_items, s);
+    CU(cudaGetLastError());
+    if (n) {
+        CU(cudaMemcpyAsync(kps_un, d_un, sizeof(orbfe_keypoint) * n, cudaMemcpyDeviceToHost, s));
+        CU(cudaMemcpyAsync(items, d_items, sizeof(uint16_t) * n, cudaMemcpyDeviceToHost, s));
+    }
+    CU(cudaMemcpyAsync(cell_end, d_end, sizeof(int) * 3072, cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    if (n_in_grid) *n_in_grid = cell_end[3071];
     return ORBFE_OK;
 }
 

@@ -83,7 +83,8 @@ struct StereoArgs {
 size_t search_init_scratch_bytes(int cap, int npairs);
 void search_init_carve(InitArgs& a, void* scratch, int npairs);
 int launch_search_init(const InitArgs& a, int npairs, cudaStream_t st);
-int launch_local_grid_and_count(const LocalArgs& a, cudaStream_t st);
+// build_grid = false: a.cell_end / a.items already hold the frame's grid (device-resident frame)
+int launch_local_grid_and_count(const LocalArgs& a, cudaStream_t st, bool build_grid = true);
 int launch_local_fill(const LocalArgs& a, cudaStream_t st);
 int launch_local_sweep(const LocalArgs& a, cudaStream_t st);
 int launch_local_finalize(const LocalArgs& a, int* mp_for_kp, uint8_t* occ_out, int* nmatches, cudaStream_t st);

@@ -828,8 +828,8 @@ int launch_search_init(const InitArgs& a, int npairs, cudaStream_t st) {
     return 3;
 }
 
-int launch_local_grid_and_count(const LocalArgs& a, cudaStream_t st) {
-    build_grid_kernel<<<1, 32, 0, st>>>(a);
+int launch_local_grid_and_count(const LocalArgs& a, cudaStream_t st, bool build_grid) {
+    if (build_grid) build_grid_kernel<<<1, 32, 0, st>>>(a);
     if (a.nmp > 0) local_candidates_kernel<false><<<(a.nmp + 127) / 128, 128, 0, st>>>(a);
     scan_kernel<<<1, 1024, 0, st>>>(a.cand_off, a.nmp);
     return 3;

@@ -40,6 +40,7 @@ class ORBextractor:
                                              self._sigma2.ctypes.data, self._inv_sigma2.ctypes.data,
                                              self._per_level.ctypes.data, self._umax.ctypes.data))
         self._last_batch = 0
+        self._bounds = None
 
     def close(self):
         if getattr(self, "_h", None) and self._h.value:
@@ -125,7 +126,54 @@ class ORBextractor:
               "orbfe_extract_batch_device")
         self._last_batch = B
 
-    STAGES = ("upload", "pyramid", "fast", "blur", "octree", "orient_desc")
+    # --- Frame epilogue: UndistortKeyPoints + AssignFeaturesToGrid fused behind operator()
+    def set_camera(self, camera, cols: int, rows: int) -> np.ndarray:
+        """camera = (fx, fy, cx, cy, k1, k2, p1, p2[, k3]) or None to switch the epilogue off.
+        Returns Frame's (mnMinX, mnMaxX, mnMinY, mnMaxY) for a cols x rows image
+        (ComputeImageBounds, src/Frame.cc:481-512); afterwards every extract call also leaves
+        mvKeysUn and mGrid of each frame on the device (``fetch_frames`` / ``device_frames``)."""
+        bounds = np.zeros(4, np.float32)
+        if camera is None:
+            check(self._L.orbfe_extractor_set_camera(self._h, None, 0, 0, None))
+            self._bounds = None
+            return bounds
+        cam = _lib.Camera(*(list(camera) + [0.0] * (9 - len(camera))))
+        check(self._L.orbfe_extractor_set_camera(self._h, C.byref(cam), cols, rows, bounds.ctypes.data),
+              "orbfe_extractor_set_camera")
+        self._bounds = bounds
+        return bounds.copy()
+
+    def fetch_frames(self, B: int | None = None):
+        """(kps_un [B,cap] KP_DTYPE, cell_end [B,3072] int32, items [B,cap] uint16) of the last batch:
+        mGrid[ix][iy] of frame b = items[b, cell_end[b, c-1]:cell_end[b, c]] with c = ix*48 + iy."""
+        B = self._last_batch if B is None else B
+        cap = self.max_keypoints()
+        kps_un = np.empty((B, cap), KP_DTYPE)
+        cell_end = np.empty((B, _lib.GRID_CELLS), np.int32)
+        items = np.empty((B, cap), np.uint16)
+        check(self._L.orbfe_extractor_fetch_frames(self._h, B, kps_un.ctypes.data, cap, cell_end.ctypes.data,
+                                                   items.ctypes.data), "orbfe_extractor_fetch_frames")
+        return kps_un, cell_end, items
+
+    def device_frames(self):
+        """(kps_un_ptr, cell_end_ptr, items_ptr) device addresses of the last batch."""
+        a, b, c = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        check(self._L.orbfe_extractor_device_frames(self._h, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+    def device_frame_view(self, frame: int, n: int, uright_ptr: int = 0):
+        """``_lib.DeviceFrameView`` of frame ``frame`` of the last batch (n = its keypoint count) for the
+        matcher's *_resident searches.  Keeps the scale-factor array alive on the returned object."""
+        kp, ds, _, cap = self.device_results()
+        ku, ce, it = self.device_frames()
+        b = self._bounds
+        v = _lib.DeviceFrameView(n, ku + frame * cap * KP_DTYPE.itemsize, ds + frame * cap * 32, uright_ptr or None,
+                                 ce + frame * _lib.GRID_CELLS * 4, it + frame * cap * 2,
+                                 float(b[0]), float(b[1]), float(b[2]), float(b[3]), self._scale.ctypes.data, self.nlevels)
+        v._keep = self._scale
+        return v
+
+    STAGES = ("upload", "pyramid", "fast", "blur", "octree", "orient_desc", "frame")
 
     def set_profiling(self, on: bool = True) -> None:
         check(self._L.orbfe_extractor_set_profiling(self._h, int(on)))

@@ -10,7 +10,8 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._lib import KP_DTYPE, FrameView, MapPointsView, FramePointsView, PyramidView, check
+from ._lib import (KP_DTYPE, Camera, DeviceFrameView, FrameView, MapPointsView, FramePointsView, PyramidView,
+                   GRID_CELLS, check)
 
 
 class Frame:
@@ -20,6 +21,7 @@ class Frame:
     def __init__(self, keypoints: np.ndarray, descriptors: np.ndarray, width: float, height: float,
                  scale_factors: np.ndarray, uright: np.ndarray | None = None,
                  min_x: float = 0.0, min_y: float = 0.0):
+        # width / height are mnMaxX / mnMaxY (the image size when the camera has no distortion)
         self.kps = np.ascontiguousarray(keypoints, KP_DTYPE)
         self.desc = np.ascontiguousarray(descriptors if descriptors is not None else np.zeros((0, 32)), np.uint8).reshape(-1, 32)
         assert len(self.kps) == len(self.desc)
@@ -165,15 +167,22 @@ class ORBmatcher:
         keep = {k: np.ascontiguousarray(mappoints[k], t) for k, t in spec.items()}
         v = MapPointsView(len(keep["level"]), *[keep[k].ctypes.data for k in
                           ("track_in_view", "proj_x", "proj_y", "proj_xr", "level", "view_cos", "desc", "observations")])
+        resident = isinstance(F, DeviceFrameView)
+        N = F.n if resident else F.N
         if occupied is None:
-            occupied = np.zeros(max(F.N, 1), np.uint8)
-        out = np.full(max(F.N, 1), -1, np.int32)
+            occupied = np.zeros(max(N, 1), np.uint8)
+        out = np.full(max(N, 1), -1, np.int32)
         n = C.c_int()
-        fv = F.view()
-        check(self._L.orbfe_search_local_points(self._h, C.byref(fv), C.byref(v), th, self.mfNNratio,
-                                                occupied.ctypes.data, out.ctypes.data, C.byref(n)),
-              "orbfe_search_local_points")
-        return n.value, out[:F.N]
+        if resident:      # frame side already in HBM (ORBextractor.device_frame_view)
+            check(self._L.orbfe_search_local_points_resident(self._h, C.byref(F), C.byref(v), th, self.mfNNratio,
+                                                             occupied.ctypes.data, out.ctypes.data, C.byref(n)),
+                  "orbfe_search_local_points_resident")
+        else:
+            fv = F.view()
+            check(self._L.orbfe_search_local_points(self._h, C.byref(fv), C.byref(v), th, self.mfNNratio,
+                                                    occupied.ctypes.data, out.ctypes.data, C.byref(n)),
+                  "orbfe_search_local_points")
+        return n.value, out[:N]
 
     FRAME_POINT_FIELDS = dict(valid=np.uint8, u=np.float32, v=np.float32, ur=np.float32, radius=np.float32,
                               min_level=np.int32, max_level=np.int32, angle=np.float32, desc=np.uint8,
@@ -186,15 +195,44 @@ class ORBmatcher:
         untouched, -2 cleared by the rotation check)"""
         keep = {k: np.ascontiguousarray(points[k], t) for k, t in self.FRAME_POINT_FIELDS.items()}
         v = FramePointsView(len(keep["u"]), *[keep[k].ctypes.data for k in self.FRAME_POINT_FIELDS])
+        resident = isinstance(F, DeviceFrameView)
+        N = F.n if resident else F.N
         if occupied is None:
-            occupied = np.zeros(max(F.N, 1), np.uint8)
-        out = np.full(max(F.N, 1), -1, np.int32)
+            occupied = np.zeros(max(N, 1), np.uint8)
+        out = np.full(max(N, 1), -1, np.int32)
         n = C.c_int()
-        fv = F.view()
-        check(self._L.orbfe_search_frame_points(self._h, C.byref(fv), C.byref(v), int(self.mbCheckOrientation),
-                                                occupied.ctypes.data, out.ctypes.data, C.byref(n)),
-              "orbfe_search_frame_points")
-        return n.value, out[:F.N]
+        if resident:
+            check(self._L.orbfe_search_frame_points_resident(self._h, C.byref(F), C.byref(v), int(self.mbCheckOrientation),
+                                                             occupied.ctypes.data, out.ctypes.data, C.byref(n)),
+                  "orbfe_search_frame_points_resident")
+        else:
+            fv = F.view()
+            check(self._L.orbfe_search_frame_points(self._h, C.byref(fv), C.byref(v), int(self.mbCheckOrientation),
+                                                    occupied.ctypes.data, out.ctypes.data, C.byref(n)),
+                  "orbfe_search_frame_points")
+        return n.value, out[:N]
+
+    # --- Frame constructor epilogue for callers without a batched extractor handle
+    def ComputeImageBounds(self, camera, cols: int, rows: int) -> np.ndarray:
+        """Frame::ComputeImageBounds (src/Frame.cc:481-512) -> float32 (mnMinX, mnMaxX, mnMinY, mnMaxY)."""
+        cam = Camera(*(list(camera) + [0.0] * (9 - len(camera))))
+        b = np.zeros(4, np.float32)
+        check(self._L.orbfe_image_bounds(self._h, C.byref(cam), cols, rows, b.ctypes.data), "orbfe_image_bounds")
+        return b
+
+    def UndistortAndAssign(self, camera, bounds, keypoints: np.ndarray):
+        """Frame::UndistortKeyPoints + AssignFeaturesToGrid (src/Frame.cc:443-475, :246-267).
+        -> (mvKeysUn KP_DTYPE[n], cell_end int32[3072], items uint16[k]); mGrid[ix][iy] =
+        items[cell_end[c-1]:cell_end[c]], c = ix*48 + iy."""
+        cam = Camera(*(list(camera) + [0.0] * (9 - len(camera))))
+        b = np.ascontiguousarray(bounds, np.float32)
+        kps = np.ascontiguousarray(keypoints, KP_DTYPE)
+        n = len(kps)
+        un = np.empty(max(n, 1), KP_DTYPE); ce = np.empty(GRID_CELLS, np.int32); it = np.empty(max(n, 1), np.uint16)
+        k = C.c_int()
+        check(self._L.orbfe_frame_assign(self._h, C.byref(cam), b.ctypes.data, kps.ctypes.data, n, un.ctypes.data,
+                                         ce.ctypes.data, it.ctypes.data, C.byref(k)), "orbfe_frame_assign")
+        return un[:n], ce, it[:k.value]
 
     def ComputeStereoMatches(self, left: Frame, right: Frame, pyr_left: list, pyr_right: list,
                              inv_scale_factors: np.ndarray, mbf: float, mb: float):

@@ -4,6 +4,8 @@
   prim_*.npz      inputs + outputs of the OpenCV primitives the reference calls, produced by
                   cv2 4.13.0 itself (resize INTER_LINEAR, copyMakeBorder REFLECT_101, FAST 9/16
                   with NMS at thresholds 20 and 7, GaussianBlur 7x7 sigma 2, fastAtan2)
+  undistort_cv2.npz  cv2.undistortPoints as Frame::UndistortKeyPoints calls it, for the reference's
+                  shipped TUM1 / TUM2 / EuRoC cameras and a wide-angle one
   ref_extract.npz keypoints + descriptors of the UNMODIFIED reference TU (oracle/_ref/liborbref.so,
                   src/ORBextractor.cc compiled against oracle/cvshim, bump allocator) on seeded
                   synthetic frames, plus per-level pyramid checksums
@@ -69,6 +71,42 @@ def reference_extract():
     print("ref_extract.npz written:", [k for k in out if k.endswith("_cfg")])
 
 
+# the reference's shipped camera files (Examples/Monocular/TUM1.yaml, TUM2.yaml, EuRoC.yaml)
+# plus a strongly distorted wide-angle lens; (fx, fy, cx, cy), (k1, k2, p1, p2, k3), cols, rows
+CAMERAS = {
+    "tum1": ((517.306408, 516.469215, 318.643040, 255.313989), (0.262383, -0.953104, -0.005358, 0.002628, 1.163314), 640, 480),
+    "tum2": ((520.908620, 521.007327, 325.141442, 249.701764), (0.231222, -0.784899, -0.003257, -0.000105, 0.917205), 640, 480),
+    "euroc": ((458.654, 457.296, 367.215, 248.375), (-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05, 0.0), 752, 480),
+    "wide": ((300.0, 300.0, 320.0, 240.0), (-0.45, 0.3, 0.01, -0.02, -0.1), 640, 480),
+}
+
+
+def undistort():
+    """cv::undistortPoints exactly as Frame::UndistortKeyPoints / ComputeImageBounds call it
+    (Frame.cc:463, :493): CV_32FC2 points, float K and distCoef, R empty, P = K."""
+    import cv2
+    rng = np.random.default_rng(7)
+    out = {"cv2_version": np.array(cv2.__version__)}
+    for name, (cam, dist, cols, rows) in CAMERAS.items():
+        fx, fy, cx, cy = cam
+        K = np.array([[fx, 0, cx], [0, fy, cy], [0, 0, 1]], np.float32)
+        D = np.array(dist, np.float32).reshape(-1, 1)
+        # keypoint-like positions (integer pixel * level scale) and arbitrary sub-pixel ones
+        scale = (1.2 ** rng.integers(0, 8, 3000)).astype(np.float32)
+        kp = (rng.integers(16, [cols - 16, rows - 16], (3000, 2)).astype(np.float32) / scale[:, None]).round() * scale[:, None]
+        pts = np.concatenate([kp.astype(np.float32), rng.uniform([-40, -40], [cols + 40, rows + 40], (1000, 2)).astype(np.float32),
+                              np.array([[0, 0], [cols, 0], [0, rows], [cols, rows]], np.float32)])
+        und = cv2.undistortPoints(pts.reshape(-1, 1, 2).copy(), K, D, None, K).reshape(-1, 2)
+        out[name + "_cam"] = np.array(cam, np.float32)
+        out[name + "_dist"] = np.array(dist, np.float32)
+        out[name + "_size"] = np.array([cols, rows], np.int32)
+        out[name + "_pts"] = pts
+        out[name + "_und"] = und.astype(np.float32)
+    np.savez_compressed(os.path.join(HERE, "undistort_cv2.npz"), **out)
+    print("undistort_cv2.npz written with cv2", cv2.__version__)
+
+
 if __name__ == "__main__":
     primitives()
+    undistort()
     reference_extract()
