@@ -91,13 +91,40 @@ def guided_search_timings(frame_img):
             t0 = time.perf_counter(); fn(); ts.append(time.perf_counter() - t0)
         return float(np.median(ts)) * 1e3
 
+    # the same searches against a frame that never left the device (Frame epilogue K11: mvKeysUn + mGrid
+    # written by the extractor; camera without k1, so mvKeysUn == mvKeys and the answers are the same)
+    ex.set_camera([520.0, 520.0, 320.0, 240.0, 0.0, 0.0, 0.0, 0.0, 0.0], W, H)
+    ex.extract_batch(frame_img[None])
+    dv = ex.device_frame_view(0, n)
+    # Frame epilogue itself: 64 copies of the frame through the extractor with the TUM1 camera, stage timer
+    tum1 = [517.306408, 516.469215, 318.643040, 255.313989, 0.262383, -0.953104, -0.005358, 0.002628, 1.163314]
+    ex2 = orbfe.ORBextractor(NFEAT)
+    ex2.set_camera(tum1, W, H)
+    ex2.set_profiling(True)
+    rep = np.ascontiguousarray(np.repeat(frame_img[None], 64, 0))
+    ex2.extract_batch(rep); ex2.extract_batch(rep)
+    epi_us = ex2.stage_times_ms()["frame"] * 1e3 / 64
+    xy = np.stack([k["x"], k["y"]], 1)
+    cam_f, dist_f = np.array(tum1[:4], np.float32), np.array(tum1[4:], np.float32)
+    bnd = O.image_bounds(cam_f, dist_f, W, H)
+
+    def cpu_epilogue():
+        un = k.copy()
+        u = O.undistort_points(xy, cam_f, dist_f)
+        un["x"], un["y"] = u[:, 0], u[:, 1]
+        O.assign_grid(O.frame_view(un, d, W, H, scale, bounds=bnd))
+
     return {
         "search_local_points": {"map_points": nmp, "keypoints": n,
                                 "gpu_ms_per_call": med(lambda: mt.SearchByProjection(F, mps, 3.0, np.zeros(n, np.uint8))),
+                                "gpu_resident_frame_ms_per_call": med(lambda: mt.SearchByProjection(dv, mps, 3.0, np.zeros(n, np.uint8))),
                                 "cpu_ms_per_call": med(lambda: O.search_by_projection(fo, mps, 3.0, 0.8, np.zeros(n, np.uint8)))},
         "search_frame_points": {"points": n, "keypoints": n,
                                 "gpu_ms_per_call": med(lambda: mt.SearchByProjectionLast(F, pts, np.zeros(n, np.uint8))),
+                                "gpu_resident_frame_ms_per_call": med(lambda: mt.SearchByProjectionLast(dv, pts, np.zeros(n, np.uint8))),
                                 "cpu_ms_per_call": med(lambda: O.search_by_projection_frame(fo, pts, True, np.zeros(n, np.uint8)))},
+        "frame_epilogue": {"what": "UndistortKeyPoints + AssignFeaturesToGrid, TUM1 camera", "keypoints": n,
+                           "gpu_us_per_frame_in_batch": epi_us, "cpu_us_per_frame": med(cpu_epilogue) * 1e3},
     }
 
 

@@ -6,7 +6,9 @@
 //                             (DescriptorDistance, SearchForInitialization,
 //                             SearchByProjection(Frame&, vector<MapPoint*>&, th),
 //                             SearchByProjection(CurrentFrame, LastFrame, th, bMono)) and offers
-//                             ComputeStereoMatches(Frame&) for src/Frame.cc:512-686
+//                             ComputeStereoMatches(Frame&) for src/Frame.cc:512-686,
+//                             ComputeImageBounds(Frame&, im) for :481-512 and
+//                             UndistortAndAssign(Frame&) for :443-475 + :246-267
 //
 // Include AFTER the OpenCV core headers (cv::Mat, cv::KeyPoint, cv::InputArray, cv::OutputArray,
 // cv::Point2f must be visible).  The Frame / MapPoint dependent members are templates over the
@@ -245,6 +247,46 @@ public:
         return nmatches;
     }
 
+    // Frame::ComputeImageBounds — src/Frame.cc:481-512 (call instead of the member, inside the
+    // mbInitialComputations block of the Frame constructors, :97-111)
+    template <class FrameT>
+    void ComputeImageBounds(FrameT& F, const cv::Mat& imLeft) {
+        const orbfe_camera cam = Camera(F);
+        float b[4];
+        orbfe_detail::check(orbfe_image_bounds(mpHandle, &cam, imLeft.cols, imLeft.rows, b), "orbfe_image_bounds");
+        FrameT::mnMinX = b[0]; FrameT::mnMaxX = b[1]; FrameT::mnMinY = b[2]; FrameT::mnMaxY = b[3];
+    }
+
+    // Frame::UndistortKeyPoints + Frame::AssignFeaturesToGrid — src/Frame.cc:443-475, :246-267.  One
+    // call where the constructor calls AssignFeaturesToGrid() (the image bounds exist by then); the
+    // earlier UndistortKeyPoints() call goes away.  Fills mvKeysUn and mGrid.
+    template <class FrameT>
+    void UndistortAndAssign(FrameT& F) {
+        const int N = (int)F.mvKeys.size();
+        const orbfe_camera cam = Camera(F);
+        const float b[4] = {FrameT::mnMinX, FrameT::mnMaxX, FrameT::mnMinY, FrameT::mnMaxY};
+        std::vector<orbfe_keypoint> k(N), un(N);
+        for (int i = 0; i < N; i++) k[i] = Kp(F.mvKeys[i]);
+        std::vector<int32_t> cellEnd(ORBFE_GRID_CELLS);
+        std::vector<uint16_t> items(N);
+        int inGrid = 0;
+        orbfe_detail::check(orbfe_frame_assign(mpHandle, &cam, b, k.data(), N, un.data(), cellEnd.data(), items.data(),
+                                               &inGrid), "orbfe_frame_assign");
+        F.mvKeysUn.resize(N);
+        for (int i = 0; i < N; i++) {
+            cv::KeyPoint kp = F.mvKeys[i];                      // :469-472
+            kp.pt.x = un[i].x; kp.pt.y = un[i].y;
+            F.mvKeysUn[i] = kp;
+        }
+        int start = 0;
+        for (int ix = 0; ix < ORBFE_GRID_COLS; ix++)
+            for (int iy = 0; iy < ORBFE_GRID_ROWS; iy++) {
+                const int end = cellEnd[ix * ORBFE_GRID_ROWS + iy];
+                F.mGrid[ix][iy].assign(items.begin() + start, items.begin() + end);
+                start = end;
+            }
+    }
+
     // Frame::ComputeStereoMatches — src/Frame.cc:512-686 (call instead of the member)
     template <class FrameT>
     void ComputeStereoMatches(FrameT& F) {
@@ -282,6 +324,15 @@ protected:
     static orbfe_keypoint Kp(const cv::KeyPoint& k) {
         orbfe_keypoint o = {k.pt.x, k.pt.y, k.size, k.angle, k.response, k.octave, k.class_id};
         return o;
+    }
+    // mK (3x3 CV_32F) and mDistCoef (4x1 or 5x1 CV_32F) as Tracking builds them (src/Tracking.cc:62-85)
+    template <class FrameT>
+    static orbfe_camera Camera(const FrameT& F) {
+        orbfe_camera c = {F.mK.template at<float>(0, 0), F.mK.template at<float>(1, 1), F.mK.template at<float>(0, 2),
+                          F.mK.template at<float>(1, 2), F.mDistCoef.template at<float>(0, 0),
+                          F.mDistCoef.template at<float>(1, 0), F.mDistCoef.template at<float>(2, 0),
+                          F.mDistCoef.template at<float>(3, 0), F.mDistCoef.rows > 4 ? F.mDistCoef.template at<float>(4, 0) : 0.0f};
+        return c;
     }
     // the Frame fields the searches read: mvKeysUn, mDescriptors, mnMinX.., mvScaleFactors
     template <class FrameT>

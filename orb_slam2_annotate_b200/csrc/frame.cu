@@ -1,4 +1,4 @@
-// frame.cu — K10: the Frame constructor's epilogue on the device:
+// frame.cu — K11: the Frame constructor's epilogue on the device:
 // Frame::UndistortKeyPoints (reference src/Frame.cc:443-475) and Frame::AssignFeaturesToGrid /
 // PosInGrid (:246-267, :419-430), one CTA per frame, so that mvKeysUn and mGrid are born in HBM
 // next to the descriptors and the guided searches never upload a frame again.

@@ -15,6 +15,8 @@ struct Frame {   // the members of ORB_SLAM2::Frame the matcher reads (include/F
     std::vector<cv::KeyPoint> mvKeys, mvKeysUn;
     cv::Mat mDescriptors;
     std::vector<float> mvScaleFactors;
+    cv::Mat mK, mDistCoef;
+    std::vector<std::size_t> mGrid[64][48];
     static float mnMinX, mnMaxX, mnMinY, mnMaxY;
 };
 float Frame::mnMinX, Frame::mnMaxX, Frame::mnMinY, Frame::mnMaxY;
@@ -57,6 +59,25 @@ int main(int argc, char** argv) {
     }
     int n1 = (int)m12.size();
     fwrite(&nm, 4, 1, o); fwrite(&n1, 4, 1, o); fwrite(m12.data(), 4, n1, o);
+    // Frame constructor epilogue with the TUM1 camera (Examples/Monocular/TUM1.yaml): bounds, mvKeysUn, mGrid
+    const float Kv[4] = {517.306408f, 516.469215f, 318.643040f, 255.313989f};
+    const float Dv[5] = {0.262383f, -0.953104f, -0.005358f, 0.002628f, 1.163314f};
+    float Kbuf[9] = {Kv[0], 0.f, Kv[2], 0.f, Kv[1], Kv[3], 0.f, 0.f, 1.f}, Dbuf[5];
+    for (int r = 0; r < 5; r++) Dbuf[r] = Dv[r];
+    F[0].mK = cv::Mat(3, 3, CV_32F, Kbuf, 3 * sizeof(float));          // the shim only allocates 8-bit matrices
+    F[0].mDistCoef = cv::Mat(5, 1, CV_32F, Dbuf, sizeof(float));
+    cv::Mat im0(h, w, CV_8UC1, buf.data(), (size_t)w);
+    matcher.ComputeImageBounds(F[0], im0);
+    matcher.UndistortAndAssign(F[0]);
+    const float bnd[4] = {Frame::mnMinX, Frame::mnMaxX, Frame::mnMinY, Frame::mnMaxY};
+    fwrite(bnd, 4, 4, o);
+    for (size_t k = 0; k < F[0].mvKeysUn.size(); k++) { float v[2] = {F[0].mvKeysUn[k].pt.x, F[0].mvKeysUn[k].pt.y}; fwrite(v, 4, 2, o); }
+    for (int ix = 0; ix < 64; ix++)
+        for (int iy = 0; iy < 48; iy++) {
+            int cnt = (int)F[0].mGrid[ix][iy].size();
+            fwrite(&cnt, 4, 1, o);
+            for (int j = 0; j < cnt; j++) { int v = (int)F[0].mGrid[ix][iy][j]; fwrite(&v, 4, 1, o); }
+        }
     fclose(o);
     printf("adapter_smoke: %zu + %zu keypoints, %d init matches, DescriptorDistance(0,1)=%d\n", F[0].mvKeys.size(),
            F[1].mvKeys.size(), nm,

@@ -46,7 +46,7 @@ def test_adapter_end_to_end(orbfe, oracle, tmp_path):
         d = np.frombuffer(raw, np.uint8, 32 * n, off).reshape(n, 32); off += 32 * n
         frames.append((k, d))
     nm, n1 = (int(v) for v in np.frombuffer(raw, np.int32, 2, off)); off += 8
-    m12 = np.frombuffer(raw, np.int32, n1, off)
+    m12 = np.frombuffer(raw, np.int32, n1, off); off += 4 * n1
     t = oracle.OracleExtractor(2000).tables()
     ref = [oracle.OracleExtractor(2000)(im) for im in imgs]
     for (k, d), (ko, do) in zip(frames, ref):
@@ -58,3 +58,19 @@ def test_adapter_end_to_end(orbfe, oracle, tmp_path):
     no, mo = oracle.search_for_initialization(oracle.frame_view(ref[0][0], ref[0][1], 640, 480, t["scale"]),
                                               oracle.frame_view(ref[1][0], ref[1][1], 640, 480, t["scale"]), prev, 100, 0.9, True)
     assert nm == no and np.array_equal(m12, mo) and nm > 100
+    # Frame epilogue through the adapter (TUM1 camera): bounds, mvKeysUn and mGrid of frame 0
+    cam = np.array([517.306408, 516.469215, 318.643040, 255.313989], np.float32)
+    dist = np.array([0.262383, -0.953104, -0.005358, 0.002628, 1.163314], np.float32)
+    bnd = np.frombuffer(raw, np.float32, 4, off); off += 16
+    assert bnd.tobytes() == oracle.image_bounds(cam, dist, 640, 480).tobytes()
+    k0 = frames[0][0]
+    un = np.frombuffer(raw, np.float32, 2 * len(k0), off).reshape(-1, 2); off += 8 * len(k0)
+    want = oracle.undistort_points(np.stack([k0["x"], k0["y"]], 1), cam, dist)
+    assert un.tobytes() == want.tobytes()
+    ku = k0.copy(); ku["x"], ku["y"] = want[:, 0], want[:, 1]
+    cs, items = oracle.assign_grid(oracle.frame_view(ku, frames[0][1], 640, 480, t["scale"], bounds=bnd))
+    for c in range(64 * 48):
+        cnt = int(np.frombuffer(raw, np.int32, 1, off)[0]); off += 4
+        got = np.frombuffer(raw, np.int32, cnt, off); off += 4 * cnt
+        assert np.array_equal(got, items[cs[c]:cs[c + 1]])
+    assert off == len(raw)

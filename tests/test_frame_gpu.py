@@ -1,4 +1,4 @@
-"""GPU parity of the Frame epilogue (K10: Frame::UndistortKeyPoints + ComputeImageBounds +
+"""GPU parity of the Frame epilogue (K11: Frame::UndistortKeyPoints + ComputeImageBounds +
 AssignFeaturesToGrid) through the C ABI: undistorted positions bit-exact against the committed
 cv2 vectors and the oracle, the grid identical to the oracle's, and the guided searches on a
 device-resident frame identical to the same searches on uploaded arrays."""
