@@ -2,6 +2,8 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <stdint.h>
+
 #include <algorithm>
 #include <string>
 
@@ -31,6 +33,23 @@ struct DevArray {
         return 0;
     }
     void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+// grow-only page-locked host buffer
+struct PinnedArray {
+    uint8_t* p = nullptr;
+    size_t cap = 0;
+    int ensure(size_t n) {
+        if (n <= cap) return 0;
+        if (p) cudaFreeHost(p);
+        p = nullptr; cap = 0;
+        n += n / 2;
+        cudaError_t e = cudaMallocHost((void**)&p, n);
+        if (e != cudaSuccess) return fail(ORBFE_ERR_CUDA, "cudaMallocHost", e);
+        cap = n;
+        return 0;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
 };
 
 }  // namespace orbfe

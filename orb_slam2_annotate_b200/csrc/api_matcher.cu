@@ -1,5 +1,7 @@
 // api_matcher.cu — matcher half of the C ABI (include/orbfe.h): handle, scalar Hamming
 // distance and the host/device entry points of the brute-force kNN-2 search.
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -15,6 +17,8 @@ struct orbfe_matcher {
     int device = 0;
     cudaStream_t stream = nullptr;
     DevArray<uint8_t> scratch[8];   // grow-only device staging, reused across calls
+    PinnedArray stage, result;      // page-locked host staging of the guided searches
+    bool trace = std::getenv("ORBFE_TRACE") != nullptr;
 };
 
 extern "C" {
@@ -53,6 +57,7 @@ void orbfe_matcher_destroy(orbfe_matcher* m) {
     cudaSetDevice(m->device);
     if (m->stream) { cudaStreamSynchronize(m->stream); cudaStreamDestroy(m->stream); }
     for (auto& s : m->scratch) s.release();
+    m->stage.release(); m->result.release();
     delete m;
 }
 
@@ -232,7 +237,158 @@ int check_device_frame(const orbfe_device_frame_view* df) {
     return 0;
 }
 
-// df != NULL: the frame side (keypoints, descriptors, uright, grid) is already in device memory
+// ---- the two guided searches share one host schedule --------------------------------------
+// Everything the call uploads is packed into one pinned staging block and sent with a single
+// H2D copy; the kernels of a whole round (grid, candidate count / scan / fill, kSweeps
+// fixed-point sweeps, epilogue) are enqueued without looking at intermediate results, and one
+// D2H copy brings back the answers together with the two facts that validate them: the
+// candidate total (did the list fit the buffer?) and the "changed" flag of the last sweep (did
+// the first-owner fixed point converge?).  Extra sweeps past convergence change nothing, so the
+// common case costs one synchronisation; otherwise the round is repeated from where it stopped.
+constexpr int kSweeps = 2;
+
+struct Upload {
+    uint8_t* host; uint8_t* dev; size_t off = 0, cap = 0;
+    template <class T> T* put(const void* src, size_t n) {       // copies into the staging block
+        off = (off + 255) & ~size_t(255);
+        T* d = reinterpret_cast<T*>(dev + off);
+        if (src && n) std::memcpy(host + off, src, n * sizeof(T));
+        off += n * sizeof(T);
+        return d;
+    }
+};
+
+// df != NULL: the frame side (keypoints, descriptors, uright, grid) is already in device memory.
+// Exactly one of mps (mode 0, SearchByProjection(F, MapPoints)) / pts (mode 1, (Current, Last)).
+int guided_search(orbfe_matcher* m, const orbfe_frame_view* f, const orbfe_device_frame_view* df,
+                  const orbfe_mappoints_view* mps, const orbfe_framepoints_view* pts, float th, float nnratio,
+                  int check_orientation, const uint8_t* occ_in, uint8_t* occ_out_host, int32_t* out_for_kp,
+                  int* nmatches) {
+    const int mode = pts ? 1 : 0;
+    const int n = f->n, np = mode ? pts->n : mps->n, L = f->nlevels;
+    CU(cudaSetDevice(m->device));
+    cudaStream_t s = m->stream;
+    int rc;
+    // ---- uploads
+    const size_t frameBytes = df ? 0 : padded((size_t)n * sizeof(orbfe_keypoint)) + padded((size_t)n * 32) + padded((size_t)n * 4);
+    const size_t upBytes = frameBytes + padded((size_t)std::max(L, 1) * 4) + padded(n) + padded(np) + 8 * padded((size_t)np * 4) +
+                           padded((size_t)np * 32);
+    if ((rc = m->scratch[0].ensure(upBytes))) return rc;
+    if ((rc = m->stage.ensure(upBytes))) return rc;
+    Upload U{m->stage.p, m->scratch[0].p, 0, upBytes};
+    LocalArgs a{};
+    if (df) {
+        a.kps = df->d_kps; a.desc = df->d_desc; a.uright = df->d_uright;
+    } else {
+        a.kps = U.put<orbfe_keypoint>(f->kps, n);
+        a.desc = U.put<uint8_t>(f->desc, (size_t)n * 32);
+        a.uright = f->uright ? U.put<float>(f->uright, n) : nullptr;
+    }
+    a.n = n; a.nlevels = L; a.nmp = np; a.grid = grid_of(f); a.mode = mode;
+    const uint8_t* d_occ = U.put<uint8_t>(occ_in, n);
+    a.occ0 = d_occ;
+    if (mode == 0) {
+        a.scale = U.put<float>(f->scale_factors, L);
+        a.in_view = U.put<uint8_t>(mps->track_in_view, np);
+        a.px = U.put<float>(mps->proj_x, np); a.py = U.put<float>(mps->proj_y, np);
+        a.pxr = a.uright ? U.put<float>(mps->proj_xr, np) : nullptr;
+        a.level = U.put<int>(mps->level, np); a.view_cos = U.put<float>(mps->view_cos, np);
+        a.mpdesc = U.put<uint8_t>(mps->desc, (size_t)np * 32);
+        a.obs = U.put<int>(mps->observations, np);
+        a.th = th; a.ratio = nnratio;
+    } else {
+        a.in_view = U.put<uint8_t>(pts->valid, np);
+        a.px = U.put<float>(pts->u, np); a.py = U.put<float>(pts->v, np);
+        a.pxr = a.uright ? U.put<float>(pts->ur, np) : nullptr;
+        a.radius = U.put<float>(pts->radius, np);
+        a.min_level = U.put<int>(pts->min_level, np); a.max_level = U.put<int>(pts->max_level, np);
+        a.angle = U.put<float>(pts->angle, np);
+        a.mpdesc = U.put<uint8_t>(pts->desc, (size_t)np * 32);
+        a.obs = U.put<int>(pts->observations, np);
+        a.th = 1.0f; a.ratio = 1.0f; a.checkOri = check_orientation;
+    }
+    if (U.off > U.cap) return fail(ORBFE_ERR_CAPACITY, "internal: matcher staging overflow");
+    CU(cudaMemcpyAsync(m->scratch[0].p, m->stage.p, U.off, cudaMemcpyHostToDevice, s));
+    // ---- device scratch.  Result block R = [mpkp n | kp_bad n | flags kSweeps | nmatches | ncand | hist 32] ints + occ_out n bytes
+    const size_t rInts = (size_t)2 * n + kSweeps + 2 + 32;
+    const size_t rBytes = rInts * 4 + (size_t)n;
+    const size_t scBytes = padded(3072 * 4) + padded((size_t)n * 2) + padded((size_t)(np + 1) * 4) +
+                           padded((size_t)(kSweeps + 1) * n * 4) + padded((size_t)np * 4) + padded(rBytes);
+    if ((rc = m->scratch[2].ensure(scBytes))) return rc;
+    if ((rc = m->result.ensure(rBytes))) return rc;
+    Arena A; A.base = m->scratch[2].p; A.cap = scBytes;
+    if (df) {
+        a.cell_end = const_cast<int*>(df->d_cell_end); a.items = const_cast<unsigned short*>(df->d_items);
+    } else {
+        a.cell_end = A.take<int>(3072); a.items = A.take<unsigned short>(n);
+    }
+    a.cand_off = A.take<int>(np + 1);
+    int* d_owner = A.take<int>((size_t)(kSweeps + 1) * n);
+    a.choice = A.take<int>(np);
+    int* R = A.take<int>(rInts + (n + 3) / 4);
+    int* d_mpkp = R; a.kp_bad = R + n;
+    int* d_flags = R + 2 * n; int* d_nm = d_flags + kSweeps; int* d_ncand = d_nm + 1; a.hist = d_ncand + 1;
+    uint8_t* d_occ_out = reinterpret_cast<uint8_t*>(R + rInts);
+    if (A.off > A.cap) return fail(ORBFE_ERR_CAPACITY, "internal: matcher arena overflow");
+    // candidate buffer: start from what earlier calls needed
+    if ((rc = m->scratch[1].ensure(std::max<size_t>((size_t)np * 32, 4096)))) return rc;
+
+    a.ncand_out = d_ncand;
+    launch_local_grid_and_count(a, s, df == nullptr);
+    bool refill = true, fresh = true;
+    const int* hR = reinterpret_cast<const int*>(m->result.p);
+    for (int round = 0;; round++) {
+        if (refill) {
+            a.cand = reinterpret_cast<uint32_t*>(m->scratch[1].p);
+            a.cand_cap = (int)std::min<size_t>(m->scratch[1].cap / 4, 0x7FFFFFFF);
+            launch_local_fill(a, s);
+            refill = false;
+        }
+        // owners to "no owner" (the first one only when starting over), results cleared
+        launch_guided_init(d_owner, n, kSweeps, fresh, d_mpkp, a.kp_bad, (int)(rInts - n), d_occ_out, d_occ, s);
+        fresh = false;
+        for (int k = 0; k < kSweeps; k++) {
+            a.owner_prev = d_owner + (size_t)k * n; a.owner_next = d_owner + (size_t)(k + 1) * n;
+            a.owner_pp = k ? d_owner + (size_t)(k - 1) * n : nullptr;     // sweep k checks whether sweep k-1 moved anything
+            a.diff_flag = k ? d_flags + (k - 1) : nullptr;
+            launch_local_sweep(a, s);
+        }
+        // choice belongs to the last sweep's input, which equals its output at the fixed point
+        a.owner_prev = d_owner + (size_t)kSweeps * n;
+        a.owner_pp = d_owner + (size_t)(kSweeps - 1) * n; a.diff_flag = d_flags + (kSweeps - 1);
+        if (mode == 0) launch_local_finalize(a, d_mpkp, d_occ_out, d_nm, s);
+        else launch_frame_finalize(a, d_mpkp, d_nm, s);
+        CU(cudaGetLastError());
+        CU(cudaMemcpyAsync(m->result.p, R, rBytes, cudaMemcpyDeviceToHost, s));
+        CU(cudaStreamSynchronize(s));
+        const int ncand = hR[2 * n + kSweeps + 1];
+        if (ncand > a.cand_cap) {                                           // list did not fit: grow, start over
+            if ((rc = m->scratch[1].ensure((size_t)ncand * 4 + 4096))) return rc;
+            refill = true; fresh = true;
+            continue;
+        }
+        if (!hR[2 * n + kSweeps - 1]) break;                                // last sweep changed nothing
+        if (round > np / kSweeps + 2) return fail(ORBFE_ERR_CUDA, "internal: first-owner sweeps did not converge");
+        CU(cudaMemcpyAsync(d_owner, d_owner + (size_t)kSweeps * n, sizeof(int) * n, cudaMemcpyDeviceToDevice, s));
+    }
+    *nmatches = hR[2 * n + kSweeps];
+    if (m->trace) std::fprintf(stderr, "orbfe guided_search mode %d: n %d points %d candidates %d flags %d %d\n", mode, n, np,
+                               hR[2 * n + kSweeps + 1], hR[2 * n], hR[2 * n + 1]);
+    const int* h_mpkp = hR; const int* h_bad = hR + n;
+    if (mode == 0) {
+        std::memcpy(occ_out_host, reinterpret_cast<const uint8_t*>(hR + rInts), n);
+        for (int i = 0; i < n; i++)
+            if (h_mpkp[i] >= 0) out_for_kp[i] = h_mpkp[i];   // F.mvpMapPoints[bestIdx] = pMP (:132); others untouched
+    } else {
+        for (int i = 0; i < n; i++) {
+            if (h_bad[i]) out_for_kp[i] = -2;                 // mvpMapPoints[idx] = NULL (:1621)
+            else if (h_mpkp[i] >= 0) out_for_kp[i] = h_mpkp[i];   // mvpMapPoints[bestIdx2] = pMP (:1587)
+        }
+    }
+    return ORBFE_OK;
+}
+
+// ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th) — src/ORBmatcher.cc:51-138
 int search_local_points_impl(orbfe_matcher* m, const orbfe_frame_view* f, const orbfe_device_frame_view* df,
                              const orbfe_mappoints_view* mps, float th, float nnratio, uint8_t* kp_occupied,
                              int32_t* mp_for_kp, int* nmatches) {
@@ -245,96 +401,12 @@ int search_local_points_impl(orbfe_matcher* m, const orbfe_frame_view* f, const 
     if (!kp_occupied || !mp_for_kp || !f->scale_factors || !mps->track_in_view || !mps->proj_x || !mps->proj_y ||
         !mps->level || !mps->view_cos || !mps->desc || !mps->observations || (f->uright && !mps->proj_xr))
         return fail(ORBFE_ERR_ARG, "NULL array in frame / map point view");
-    CU(cudaSetDevice(m->device));
-    cudaStream_t s = m->stream;
-    const size_t total = padded((size_t)n * sizeof(orbfe_keypoint)) + padded((size_t)n * 32) + padded((size_t)n * 4) +
-                         padded((size_t)f->nlevels * 4) + padded(nmp) + 7 * padded((size_t)nmp * 4) +
-                         padded((size_t)nmp * 32) + padded(3072 * 4) + padded((size_t)n * 2) +
-                         padded((size_t)(nmp + 1) * 4) + padded(n) + 3 * padded((size_t)n * 4) +
-                         padded(8) + padded(n);
-    if ((rc = m->scratch[0].ensure(total))) return rc;
-    Arena A; A.base = m->scratch[0].p; A.cap = total;
-    LocalArgs a{};
-    auto up = [&](auto* dst, const void* src, size_t bytes) {
-        return cudaMemcpyAsync((void*)dst, src, bytes, cudaMemcpyHostToDevice, s);
-    };
-    const orbfe_keypoint* d_kps; const uint8_t* d_desc; const float* d_ur;
-    if (df) {
-        d_kps = df->d_kps; d_desc = df->d_desc; d_ur = df->d_uright;
-        a.cell_end = const_cast<int*>(df->d_cell_end); a.items = const_cast<unsigned short*>(df->d_items);
-    } else {
-        orbfe_keypoint* k = A.take<orbfe_keypoint>(n); CU(up(k, f->kps, sizeof(orbfe_keypoint) * n));
-        uint8_t* dd = A.take<uint8_t>((size_t)n * 32); CU(up(dd, f->desc, (size_t)n * 32));
-        float* ur = A.take<float>(n);
-        if (f->uright) CU(up(ur, f->uright, sizeof(float) * n));
-        d_kps = k; d_desc = dd; d_ur = ur;
-        a.cell_end = A.take<int>(3072);
-        a.items = A.take<unsigned short>(n);
-    }
-    float* d_scale = A.take<float>(f->nlevels); CU(up(d_scale, f->scale_factors, sizeof(float) * f->nlevels));
-    uint8_t* d_inview = A.take<uint8_t>(nmp); CU(up(d_inview, mps->track_in_view, nmp));
-    float* d_px = A.take<float>(nmp); CU(up(d_px, mps->proj_x, sizeof(float) * nmp));
-    float* d_py = A.take<float>(nmp); CU(up(d_py, mps->proj_y, sizeof(float) * nmp));
-    float* d_pxr = A.take<float>(nmp);
-    if (mps->proj_xr) CU(up(d_pxr, mps->proj_xr, sizeof(float) * nmp));
-    int* d_level = A.take<int>(nmp); CU(up(d_level, mps->level, sizeof(int) * nmp));
-    float* d_cos = A.take<float>(nmp); CU(up(d_cos, mps->view_cos, sizeof(float) * nmp));
-    uint8_t* d_mpdesc = A.take<uint8_t>((size_t)nmp * 32); CU(up(d_mpdesc, mps->desc, (size_t)nmp * 32));
-    int* d_obs = A.take<int>(nmp); CU(up(d_obs, mps->observations, sizeof(int) * nmp));
-    a.cand_off = A.take<int>(nmp + 1);
-    uint8_t* d_occ = A.take<uint8_t>(n); CU(up(d_occ, kp_occupied, n));
-    int* d_owner[2] = {A.take<int>(n), A.take<int>(n)};
-    int* d_mpkp = A.take<int>(n);
-    a.choice = A.take<int>(nmp);
-    int* d_flags = A.take<int>(2);           // [0] changed, [1] nmatches
-    uint8_t* d_occ_out = A.take<uint8_t>(n);
-    if (A.off > A.cap) return fail(ORBFE_ERR_CAPACITY, "internal: matcher arena overflow");
-    a.kps = d_kps; a.desc = d_desc; a.uright = f->uright ? d_ur : nullptr; a.n = n;
-    a.scale = d_scale; a.nlevels = f->nlevels; a.nmp = nmp; a.in_view = d_inview;
-    a.px = d_px; a.py = d_py; a.pxr = d_pxr; a.level = d_level; a.view_cos = d_cos; a.mpdesc = d_mpdesc;
-    a.obs = d_obs; a.th = th; a.ratio = nnratio; a.grid = grid_of(f); a.occ0 = d_occ; a.changed = d_flags;
     // levels must index mvScaleFactors
     for (int i = 0; i < nmp; i++)
         if (mps->track_in_view[i] && (mps->level[i] < 0 || mps->level[i] >= f->nlevels))
             return fail(ORBFE_ERR_ARG, "map point scale level outside the frame's pyramid");
-    launch_local_grid_and_count(a, s, df == nullptr);
-    int ncand = 0;
-    CU(cudaMemcpyAsync(&ncand, a.cand_off + nmp, sizeof(int), cudaMemcpyDeviceToHost, s));
-    CU(cudaStreamSynchronize(s));
-    if ((rc = m->scratch[1].ensure((size_t)std::max(ncand, 1) * 4))) return rc;
-    a.cand = reinterpret_cast<uint32_t*>(m->scratch[1].p);
-    launch_local_fill(a, s);
-    // fixed-point sweeps over the first-owner array (0x7F7F7F7F = no owner)
-    CU(cudaMemsetAsync(d_owner[0], 0x7F, sizeof(int) * n, s));
-    int cur = 0;
-    for (int it = 0; it < nmp + 2; it++) {
-        a.owner_prev = d_owner[cur]; a.owner_next = d_owner[cur ^ 1];
-        CU(cudaMemsetAsync(a.owner_next, 0x7F, sizeof(int) * n, s));
-        CU(cudaMemsetAsync(d_flags, 0, sizeof(int), s));
-        launch_local_sweep(a, s);
-        int changed = 0;
-        CU(cudaMemcpyAsync(&changed, d_flags, sizeof(int), cudaMemcpyDeviceToHost, s));
-        CU(cudaStreamSynchronize(s));
-        cur ^= 1;
-        if (!changed) break;
-    }
-    // a.choice is consistent with d_owner[cur] (== the previous one at the fixed point)
-    a.owner_prev = d_owner[cur];
-    CU(cudaMemsetAsync(d_mpkp, 0xFF, sizeof(int) * n, s));
-    CU(cudaMemsetAsync(d_flags + 1, 0, sizeof(int), s));
-    CU(cudaMemcpyAsync(d_occ_out, d_occ, n, cudaMemcpyDeviceToDevice, s));
-    launch_local_finalize(a, d_mpkp, d_occ_out, d_flags + 1, s);
-    CU(cudaGetLastError());
-    std::vector<int> h_mpkp(n);
-    CU(cudaMemcpyAsync(h_mpkp.data(), d_mpkp, sizeof(int) * n, cudaMemcpyDeviceToHost, s));
-    CU(cudaMemcpyAsync(kp_occupied, d_occ_out, n, cudaMemcpyDeviceToHost, s));
-    CU(cudaMemcpyAsync(nmatches, d_flags + 1, sizeof(int), cudaMemcpyDeviceToHost, s));
-    CU(cudaStreamSynchronize(s));
-    for (int i = 0; i < n; i++)
-        if (h_mpkp[i] >= 0) mp_for_kp[i] = h_mpkp[i];   // F.mvpMapPoints[bestIdx] = pMP (:132); others untouched
-    return ORBFE_OK;
+    return guided_search(m, f, df, mps, nullptr, th, nnratio, 0, kp_occupied, kp_occupied, mp_for_kp, nmatches);
 }
-
 
 // ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) — src/ORBmatcher.cc:1484-1630
 int search_frame_points_impl(orbfe_matcher* m, const orbfe_frame_view* f, const orbfe_device_frame_view* df,
@@ -349,97 +421,7 @@ int search_frame_points_impl(orbfe_matcher* m, const orbfe_frame_view* f, const 
     if (!kp_occupied || !match_for_kp || !pts->valid || !pts->u || !pts->v || !pts->radius || !pts->min_level ||
         !pts->max_level || !pts->angle || !pts->desc || !pts->observations || (f->uright && !pts->ur))
         return fail(ORBFE_ERR_ARG, "NULL array in frame / frame points view");
-    CU(cudaSetDevice(m->device));
-    cudaStream_t s = m->stream;
-    const size_t total = padded((size_t)n * sizeof(orbfe_keypoint)) + padded((size_t)n * 32) + padded((size_t)n * 4) +
-                         padded(np) + 7 * padded((size_t)np * 4) + padded((size_t)np * 32) + padded(3072 * 4) +
-                         padded((size_t)n * 2) + padded((size_t)(np + 1) * 4) + padded(n) + 4 * padded((size_t)n * 4) +
-                         padded((size_t)np * 4) + padded(8) + padded(32 * 4);
-    if ((rc = m->scratch[0].ensure(total))) return rc;
-    Arena A; A.base = m->scratch[0].p; A.cap = total;
-    LocalArgs a{};
-    auto up = [&](auto* dst, const void* src, size_t bytes) {
-        return cudaMemcpyAsync((void*)dst, src, bytes, cudaMemcpyHostToDevice, s);
-    };
-    const orbfe_keypoint* d_kps; const uint8_t* d_desc; const float* d_ur;
-    if (df) {
-        d_kps = df->d_kps; d_desc = df->d_desc; d_ur = df->d_uright;
-        a.cell_end = const_cast<int*>(df->d_cell_end); a.items = const_cast<unsigned short*>(df->d_items);
-    } else {
-        orbfe_keypoint* k = A.take<orbfe_keypoint>(n); CU(up(k, f->kps, sizeof(orbfe_keypoint) * n));
-        uint8_t* dd = A.take<uint8_t>((size_t)n * 32); CU(up(dd, f->desc, (size_t)n * 32));
-        float* ur = A.take<float>(n);
-        if (f->uright) CU(up(ur, f->uright, sizeof(float) * n));
-        d_kps = k; d_desc = dd; d_ur = ur;
-        a.cell_end = A.take<int>(3072);
-        a.items = A.take<unsigned short>(n);
-    }
-    uint8_t* d_valid = A.take<uint8_t>(np); CU(up(d_valid, pts->valid, np));
-    float* d_u = A.take<float>(np); CU(up(d_u, pts->u, sizeof(float) * np));
-    float* d_v = A.take<float>(np); CU(up(d_v, pts->v, sizeof(float) * np));
-    float* d_pur = A.take<float>(np);
-    if (pts->ur) CU(up(d_pur, pts->ur, sizeof(float) * np));
-    float* d_rad = A.take<float>(np); CU(up(d_rad, pts->radius, sizeof(float) * np));
-    int* d_minl = A.take<int>(np); CU(up(d_minl, pts->min_level, sizeof(int) * np));
-    int* d_maxl = A.take<int>(np); CU(up(d_maxl, pts->max_level, sizeof(int) * np));
-    float* d_ang = A.take<float>(np); CU(up(d_ang, pts->angle, sizeof(float) * np));
-    uint8_t* d_pdesc = A.take<uint8_t>((size_t)np * 32); CU(up(d_pdesc, pts->desc, (size_t)np * 32));
-    a.cand_off = A.take<int>(np + 1);
-    uint8_t* d_occ = A.take<uint8_t>(n); CU(up(d_occ, kp_occupied, n));
-    int* d_owner[2] = {A.take<int>(n), A.take<int>(n)};
-    int* d_mpkp = A.take<int>(n);
-    a.kp_bad = A.take<int>(n);
-    int* d_obs = A.take<int>(np); CU(up(d_obs, pts->observations, sizeof(int) * np));
-    // (choice reuses the arena after obs)
-    int* d_flags = A.take<int>(2);           // [0] changed, [1] nmatches
-    a.hist = A.take<int>(32);
-    if (A.off > A.cap) return fail(ORBFE_ERR_CAPACITY, "internal: matcher arena overflow");
-    if ((rc = m->scratch[2].ensure((size_t)np * 4))) return rc;
-    a.choice = reinterpret_cast<int*>(m->scratch[2].p);
-    a.kps = d_kps; a.desc = d_desc; a.uright = f->uright ? d_ur : nullptr; a.n = n;
-    a.scale = nullptr; a.nlevels = f->nlevels; a.nmp = np; a.in_view = d_valid;
-    a.px = d_u; a.py = d_v; a.pxr = d_pur; a.level = nullptr; a.view_cos = nullptr; a.mpdesc = d_pdesc;
-    a.obs = d_obs; a.th = 1.0f; a.ratio = 1.0f; a.grid = grid_of(f); a.occ0 = d_occ; a.changed = d_flags;
-    a.mode = 1; a.radius = d_rad; a.min_level = d_minl; a.max_level = d_maxl; a.angle = d_ang;
-    a.checkOri = check_orientation;
-    launch_local_grid_and_count(a, s, df == nullptr);
-    int ncand = 0;
-    CU(cudaMemcpyAsync(&ncand, a.cand_off + np, sizeof(int), cudaMemcpyDeviceToHost, s));
-    CU(cudaStreamSynchronize(s));
-    if ((rc = m->scratch[1].ensure((size_t)std::max(ncand, 1) * 4))) return rc;
-    a.cand = reinterpret_cast<uint32_t*>(m->scratch[1].p);
-    launch_local_fill(a, s);
-    // fixed-point sweeps over the first-owner array (0x7F7F7F7F = no owner), as in orbfe_search_local_points
-    CU(cudaMemsetAsync(d_owner[0], 0x7F, sizeof(int) * n, s));
-    int cur = 0;
-    for (int it = 0; it < np + 2; it++) {
-        a.owner_prev = d_owner[cur]; a.owner_next = d_owner[cur ^ 1];
-        CU(cudaMemsetAsync(a.owner_next, 0x7F, sizeof(int) * n, s));
-        CU(cudaMemsetAsync(d_flags, 0, sizeof(int), s));
-        launch_local_sweep(a, s);
-        int changed = 0;
-        CU(cudaMemcpyAsync(&changed, d_flags, sizeof(int), cudaMemcpyDeviceToHost, s));
-        CU(cudaStreamSynchronize(s));
-        cur ^= 1;
-        if (!changed) break;
-    }
-    a.owner_prev = d_owner[cur];
-    CU(cudaMemsetAsync(d_mpkp, 0xFF, sizeof(int) * n, s));
-    CU(cudaMemsetAsync(a.kp_bad, 0, sizeof(int) * n, s));
-    CU(cudaMemsetAsync(a.hist, 0, sizeof(int) * 32, s));
-    CU(cudaMemsetAsync(d_flags + 1, 0, sizeof(int), s));
-    launch_frame_finalize(a, d_mpkp, d_flags + 1, s);
-    CU(cudaGetLastError());
-    std::vector<int> h_mpkp(n), h_bad(n);
-    CU(cudaMemcpyAsync(h_mpkp.data(), d_mpkp, sizeof(int) * n, cudaMemcpyDeviceToHost, s));
-    CU(cudaMemcpyAsync(h_bad.data(), a.kp_bad, sizeof(int) * n, cudaMemcpyDeviceToHost, s));
-    CU(cudaMemcpyAsync(nmatches, d_flags + 1, sizeof(int), cudaMemcpyDeviceToHost, s));
-    CU(cudaStreamSynchronize(s));
-    for (int i = 0; i < n; i++) {
-        if (h_bad[i]) match_for_kp[i] = -2;              // mvpMapPoints[idx] = NULL (:1621)
-        else if (h_mpkp[i] >= 0) match_for_kp[i] = h_mpkp[i];   // mvpMapPoints[bestIdx2] = pMP (:1587)
-    }
-    return ORBFE_OK;
+    return guided_search(m, f, df, nullptr, pts, 1.0f, 1.0f, check_orientation, kp_occupied, nullptr, match_for_kp, nmatches);
 }
 
 }  // namespace

@@ -14,15 +14,14 @@
 // the last item of cell c, items hold keypoint indices in push_back order (ascending).
 #include "api_common.cuh"
 #include "frame_internal.cuh"
+#include "grid_build.cuh"
 
 namespace orbfe {
 
 namespace {
 
-constexpr int FT = 256;                 // threads per frame
-constexpr int NCELLS = 64 * 48;
-constexpr int CPT = NCELLS / FT;        // cells per thread in the scan (12)
-constexpr unsigned FULLM = 0xFFFFFFFFu;
+constexpr int FT = kGridThreads;        // threads per frame
+constexpr int NCELLS = kGridCells;
 
 __device__ __forceinline__ void undistort_one(const CamGeom& c, float px, float py, float& ox, float& oy) {
     const double u = (double)px, v = (double)py;
@@ -69,60 +68,21 @@ frame_epilogue_kernel(const __grid_constant__ CamGeom c, const orbfe_keypoint* _
                       int* __restrict__ cell_end, unsigned short* __restrict__ items) {
     __shared__ int cnt[NCELLS];
     __shared__ int wsum[FT / 32];
-    const int f = frame0 + blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int f = frame0 + blockIdx.x, tid = threadIdx.x;
     const int n = min(counts[f], cap);
     const orbfe_keypoint* src = kps + (long long)f * cap;
     orbfe_keypoint* dst = kps_un + (long long)f * cap;
     int* ce = cell_end + (long long)f * NCELLS;
     unsigned short* it = items + (long long)f * cap;
 
-    for (int i = tid; i < NCELLS; i += FT) cnt[i] = 0;
-    __syncthreads();
-    // mvKeysUn[i] = mvKeys[i] with the undistorted position (:466-473); count the cells
+    // mvKeysUn[i] = mvKeys[i] with the undistorted position (:466-473)
     for (int i = tid; i < n; i += FT) {
         orbfe_keypoint kp = src[i];
         if (c.undistort) undistort_one(c, kp.x, kp.y, kp.x, kp.y);
         dst[i] = kp;
-        const int cell = cell_of(c, kp.x, kp.y);
-        if (cell >= 0) atomicAdd(&cnt[cell], 1);
     }
     __syncthreads();
-    // exclusive scan over the cells: thread t owns cells [t*CPT, (t+1)*CPT)
-    int loc[CPT], s = 0;
-#pragma unroll
-    for (int j = 0; j < CPT; j++) { loc[j] = cnt[tid * CPT + j]; s += loc[j]; }
-    int inc = s;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const int t = __shfl_up_sync(FULLM, inc, o);
-        if (lane >= o) inc += t;
-    }
-    if (lane == 31) wsum[wid] = inc;
-    __syncthreads();
-    int base = inc - s;
-    for (int w = 0; w < wid; w++) base += wsum[w];
-#pragma unroll
-    for (int j = 0; j < CPT; j++) { cnt[tid * CPT + j] = base; base += loc[j]; }   // cell starts = fill cursors
-    __syncthreads();
-    for (int i = tid; i < n; i += FT) {
-        const int cell = cell_of(c, dst[i].x, dst[i].y);     // this thread's own store above
-        if (cell >= 0) it[atomicAdd(&cnt[cell], 1)] = (unsigned short)i;
-    }
-    __syncthreads();
-    // cursors are now the cell ends; restore push_back (index) order inside each cell
-    int start = tid == 0 ? 0 : cnt[tid * CPT - 1];
-#pragma unroll 1
-    for (int j = 0; j < CPT; j++) {
-        const int end = cnt[tid * CPT + j];
-        for (int a = start + 1; a < end; a++) {
-            const unsigned short v = it[a];
-            int b = a - 1;
-            while (b >= start && it[b] > v) { it[b + 1] = it[b]; b--; }
-            it[b + 1] = v;
-        }
-        ce[tid * CPT + j] = end;
-        start = end;
-    }
+    block_grid_csr(cnt, wsum, n, [&](int i) { return cell_of(c, dst[i].x, dst[i].y); }, ce, it);
 }
 
 __global__ void undistort_points_kernel(const __grid_constant__ CamGeom c, const float2* __restrict__ in, int n,

@@ -62,9 +62,14 @@ struct LocalArgs {
     int* cell_end; unsigned short* items;
     // candidate lists: cand_off[nmp+1] (exclusive scan of counts), cand[] packed idx | dist<<16 | octave<<25
     int* cand_off; uint32_t* cand;
+    int cand_cap;                // entries cand can hold; a longer list is not written (the host retries)
     // fixed-point state
     const uint8_t* occ0;         // keypoint already holds a map point with observations
-    int* owner_prev; int* owner_next; int* choice; int* changed;
+    int* owner_prev; int* owner_next; int* choice;
+    // convergence check folded into the next kernel: *diff_flag = 1 where owner_pp != owner_prev
+    // (owner_pp = the sweep before owner_prev; NULL = nothing to compare)
+    const int* owner_pp; int* diff_flag;
+    int* ncand_out;              // the epilogue copies the candidate total here (read back with the results)
 };
 
 struct StereoArgs {
@@ -87,6 +92,10 @@ int launch_search_init(const InitArgs& a, int npairs, cudaStream_t st);
 int launch_local_grid_and_count(const LocalArgs& a, cudaStream_t st, bool build_grid = true);
 int launch_local_fill(const LocalArgs& a, cudaStream_t st);
 int launch_local_sweep(const LocalArgs& a, cudaStream_t st);
+// one launch instead of five memsets / copies: owners (first = first sweep input, included when
+// reset_first) to "no owner", mp_for_kp to -1, `nzero` ints at zero_block to 0, occ_out = occ0
+int launch_guided_init(int* owners, int n, int nsweeps, bool reset_first, int* mp_for_kp, int* zero_block, int nzero,
+                       uint8_t* occ_out, const uint8_t* occ0, cudaStream_t st);
 int launch_local_finalize(const LocalArgs& a, int* mp_for_kp, uint8_t* occ_out, int* nmatches, cudaStream_t st);
 int launch_frame_finalize(const LocalArgs& a, int* mp_for_kp, int* nmatches, cudaStream_t st);
 int launch_stereo(const StereoArgs& a, cudaStream_t st);

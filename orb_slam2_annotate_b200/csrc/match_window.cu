@@ -17,6 +17,7 @@
 
 #include "orbfe_internal.cuh"
 #include "match_internal.cuh"
+#include "grid_build.cuh"
 
 namespace orbfe {
 
@@ -60,45 +61,6 @@ __device__ __forceinline__ bool cell_window(const GridGeom& g, float x, float y,
     cy1 = min(GR - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, g.minY), r), g.invH)));
     if (cy1 < 0) return false;
     return true;
-}
-
-// One warp builds the CSR of a frame: cell_end[c] = end of cell c (start = end of c-1),
-// items in keypoint-index order inside a cell (AssignFeaturesToGrid pushes in index order).
-__device__ void warp_build_grid(const GridGeom& g, const orbfe_keypoint* __restrict__ kps, int n,
-                                int* cell_end, unsigned short* items) {
-    const int lane = threadIdx.x & 31;
-    for (int c = lane; c < NCELL; c += 32) cell_end[c] = 0;
-    __syncwarp();
-    for (int i = lane; i < n; i += 32) {
-        const int c = pos_in_grid(g, kps[i].x, kps[i].y);
-        if (c >= 0) atomicAdd(&cell_end[c], 1);
-    }
-    __syncwarp();
-    int carry = 0;   // exclusive scan: cell_end[c] becomes the start of cell c
-    for (int base = 0; base < NCELL; base += 32) {
-        const int v = cell_end[base + lane];
-        int inc = v;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int u = __shfl_up_sync(FULL, inc, o);
-            if (lane >= o) inc += u;
-        }
-        cell_end[base + lane] = carry + inc - v;
-        carry += __shfl_sync(FULL, inc, 31);
-    }
-    __syncwarp();
-    for (int base = 0; base < n; base += 32) {   // stable fill; cursors end up as cell ends
-        const int i = base + lane;
-        const int c = i < n ? pos_in_grid(g, kps[i].x, kps[i].y) : -1;
-        const unsigned peers = __match_any_sync(FULL, c);
-        if (c >= 0) {
-            const int rank = __popc(peers & ((1u << lane) - 1u));
-            items[cell_end[c] + rank] = (unsigned short)i;
-        }
-        __syncwarp();
-        if (c >= 0 && (peers & ((1u << lane) - 1u)) == 0) cell_end[c] += __popc(peers);
-        __syncwarp();
-    }
 }
 
 __device__ __forceinline__ uint32_t warp_min(uint32_t v) {
@@ -493,16 +455,25 @@ search_init_greedy_kernel(const __grid_constant__ InitArgs a) {
 // ---------------------------------------------------------------------------------------
 // SearchByProjection(Frame&, vector<MapPoint*>&, th)
 
-__global__ void __launch_bounds__(32) build_grid_kernel(const __grid_constant__ LocalArgs a) {
-    warp_build_grid(a.grid, a.kps, a.n, a.cell_end, a.items);
+__global__ void __launch_bounds__(kGridThreads) build_grid_kernel(const __grid_constant__ LocalArgs a) {
+    __shared__ int cnt[kGridCells];
+    __shared__ int wsum[kGridThreads / 32];
+    block_grid_csr(cnt, wsum, a.n, [&](int i) { return pos_in_grid(a.grid, a.kps[i].x, a.kps[i].y); }, a.cell_end, a.items);
 }
 
 // Enumerates the candidates of one map point in GetFeaturesInArea order; FILL=false counts,
-// FILL=true writes the packed list (keypoint index, Hamming distance, octave).
+// FILL=true writes the packed list (keypoint index, Hamming distance, octave).  One warp per
+// point: a window column is one contiguous run of the CSR (cells ix*48+cy0 .. ix*48+cy1), so
+// the lanes take one column each, prefix-sum the run lengths and then walk the concatenated
+// runs 32 items at a time — three dependent loads per round instead of one long serial chain
+// per point.  Survivors keep their order through a ballot.
+constexpr int LC_WARPS = 4;
 template <bool FILL>
-__global__ void __launch_bounds__(128) local_candidates_kernel(const __grid_constant__ LocalArgs a) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(LC_WARPS * 32) local_candidates_kernel(const __grid_constant__ LocalArgs a) {
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * LC_WARPS + (threadIdx.x >> 5);
     if (i >= a.nmp) return;
+    if (FILL && a.cand_off[a.nmp] > a.cand_cap) return;      // list does not fit: the host grows the buffer and retries
     int count = 0;
     uint32_t* out = FILL ? a.cand + a.cand_off[i] : nullptr;
     if (a.in_view[i]) {                                                                 // :58-62
@@ -523,31 +494,58 @@ __global__ void __launch_bounds__(128) local_candidates_kernel(const __grid_cons
         if (cell_window(a.grid, x, y, rs, cx0, cx1, cy0, cy1)) {
             uint32_t q[8];
             if (FILL) load_row(q, a.mpdesc + 32 * (long long)i);
-            for (int ix = cx0; ix <= cx1; ix++) {
-                const int c0 = ix * GR + cy0;
-                const int s = c0 ? a.cell_end[c0 - 1] : 0, e = a.cell_end[ix * GR + cy1];
-                for (int j = s; j < e; j++) {
-                    const int idx = a.items[j];
-                    const orbfe_keypoint k = a.kps[idx];
-                    if (check) {
-                        if (k.octave < minLevel) continue;
-                        if (maxLevel >= 0 && k.octave > maxLevel) continue;
+            const float pxr = a.uright ? a.pxr[i] : 0.0f;
+            for (int cbase = cx0; cbase <= cx1; cbase += 32) {
+                const int ix = cbase + lane;
+                int s = 0, len = 0;
+                if (ix <= cx1) {
+                    const int c0 = ix * GR + cy0;
+                    s = c0 ? a.cell_end[c0 - 1] : 0;
+                    len = a.cell_end[ix * GR + cy1] - s;
+                }
+                int incl = len;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int u = __shfl_up_sync(FULL, incl, o);
+                    if (lane >= o) incl += u;
+                }
+                const int total = __shfl_sync(FULL, incl, 31);
+                for (int t0 = 0; t0 < total; t0 += 32) {
+                    const int t = t0 + lane;
+                    // column of item t: the first lane whose inclusive prefix exceeds t
+                    int c = 0;
+#pragma unroll
+                    for (int step = 16; step > 0; step >>= 1) {
+                        const int v = __shfl_sync(FULL, incl, c + step - 1);
+                        if (v <= t) c += step;
                     }
-                    if (!(fabsf(__fsub_rn(k.x, x)) < rs && fabsf(__fsub_rn(k.y, y)) < rs)) continue;
-                    if (a.uright && a.uright[idx] > 0) {                                // :100-105
-                        const float er = fabsf(__fsub_rn(a.pxr[i], a.uright[idx]));
-                        if (er > rs) continue;
+                    c = min(c, 31);
+                    const int cs = __shfl_sync(FULL, s, c), cincl = __shfl_sync(FULL, incl, c), clen = __shfl_sync(FULL, len, c);
+                    bool pass = t < total;
+                    int idx = 0, oct = 0;
+                    if (pass) {
+                        idx = a.items[cs + (t - (cincl - clen))];
+                        const orbfe_keypoint* kp = a.kps + idx;
+                        oct = kp->octave;
+                        if (check && (oct < minLevel || (maxLevel >= 0 && oct > maxLevel))) pass = false;
+                        if (pass && !(fabsf(__fsub_rn(kp->x, x)) < rs && fabsf(__fsub_rn(kp->y, y)) < rs)) pass = false;
+                        if (pass && a.uright) {                                         // :100-105
+                            const float ur = a.uright[idx];
+                            if (ur > 0 && fabsf(__fsub_rn(pxr, ur)) > rs) pass = false;
+                        }
                     }
-                    if (FILL) {
+                    const unsigned m = __ballot_sync(FULL, pass);
+                    if (FILL && pass) {
                         const int dist = hamming256(q, a.desc + 32 * (long long)idx);
-                        out[count] = (uint32_t)idx | ((uint32_t)dist << 16) | ((uint32_t)(k.octave & 0x3F) << 25);
+                        out[count + __popc(m & ((1u << lane) - 1u))] =
+                            (uint32_t)idx | ((uint32_t)dist << 16) | ((uint32_t)(oct & 0x3F) << 25);
                     }
-                    count++;
+                    count += __popc(m);
                 }
             }
         }
     }
-    if (!FILL) a.cand_off[i] = count;
+    if (!FILL && lane == 0) a.cand_off[i] = count;
 }
 
 // single-CTA exclusive scan of cand_off[0..n) in place; cand_off[n] = total
@@ -585,9 +583,10 @@ __global__ void __launch_bounds__(1024) scan_kernel(int* data, int n) {
 // One fixed-point sweep: map point i ignores keypoints owned by an earlier map point.
 __global__ void __launch_bounds__(128) local_select_kernel(const __grid_constant__ LocalArgs a) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a.owner_pp && i < a.n && a.owner_pp[i] != a.owner_prev[i]) *a.diff_flag = 1;   // did the previous sweep change anything?
     if (i >= a.nmp) return;
     int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;   // :83-87
-    const int s = a.cand_off[i], e = a.cand_off[i + 1];
+    const int s = a.cand_off[i], e = a.cand_off[a.nmp] > a.cand_cap ? s : a.cand_off[i + 1];
     for (int j = s; j < e; j++) {
         const uint32_t c = a.cand[j];
         const int idx = (int)(c & 0xFFFFu), dist = (int)((c >> 16) & 0x1FFu), oct = (int)(c >> 25);
@@ -609,15 +608,22 @@ __global__ void __launch_bounds__(128) local_select_kernel(const __grid_constant
     if (ch >= 0 && a.obs[i] > 0) atomicMin(&a.owner_next[ch], i);
 }
 
-__global__ void __launch_bounds__(256) local_diff_kernel(const __grid_constant__ LocalArgs a) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < a.n && a.owner_prev[i] != a.owner_next[i]) *a.changed = 1;
+__global__ void __launch_bounds__(256)
+guided_init_kernel(int* owners, int nown, int* mp_for_kp, int n, int* zero_block, int nzero, uint8_t* occ_out,
+                   const uint8_t* occ0) {
+    const int stride = gridDim.x * blockDim.x;
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    for (int i = t; i < nown; i += stride) owners[i] = 0x7F7F7F7F;
+    for (int i = t; i < n; i += stride) { mp_for_kp[i] = -1; occ_out[i] = occ0[i]; }
+    for (int i = t; i < nzero; i += stride) zero_block[i] = 0;
 }
 
 // results: mp_for_kp[idx] = last map point that took idx, occupied |= owned, nmatches
 __global__ void __launch_bounds__(128)
 local_finalize_kernel(const __grid_constant__ LocalArgs a, int* mp_for_kp, uint8_t* occ_out, int* nmatches) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) *a.ncand_out = a.cand_off[a.nmp];
+    if (a.owner_pp && i < a.n && a.owner_pp[i] != a.owner_prev[i]) *a.diff_flag = 1;   // last sweep still moving
     if (i < a.n && a.owner_prev[i] != 0x7F7F7F7F) occ_out[i] = 1;   // 0x7F7F7F7F = no owner
     if (i < a.nmp && a.choice[i] >= 0) {
         atomicMax(&mp_for_kp[a.choice[i]], i);
@@ -642,6 +648,8 @@ __global__ void __launch_bounds__(128) frame_hist_kernel(const __grid_constant__
 __global__ void __launch_bounds__(128)
 frame_finalize_kernel(const __grid_constant__ LocalArgs a, int* mp_for_kp, int* nmatches) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) *a.ncand_out = a.cand_off[a.nmp];
+    if (a.owner_pp && i < a.n && a.owner_pp[i] != a.owner_prev[i]) *a.diff_flag = 1;   // last sweep still moving
     if (i >= a.nmp || a.choice[i] < 0) return;
     const int k = a.choice[i];
     bool bad = false;
@@ -829,20 +837,20 @@ int launch_search_init(const InitArgs& a, int npairs, cudaStream_t st) {
 }
 
 int launch_local_grid_and_count(const LocalArgs& a, cudaStream_t st, bool build_grid) {
-    if (build_grid) build_grid_kernel<<<1, 32, 0, st>>>(a);
-    if (a.nmp > 0) local_candidates_kernel<false><<<(a.nmp + 127) / 128, 128, 0, st>>>(a);
+    if (build_grid) build_grid_kernel<<<1, kGridThreads, 0, st>>>(a);
+    if (a.nmp > 0) local_candidates_kernel<false><<<(a.nmp + LC_WARPS - 1) / LC_WARPS, LC_WARPS * 32, 0, st>>>(a);
     scan_kernel<<<1, 1024, 0, st>>>(a.cand_off, a.nmp);
     return 3;
 }
 
 int launch_local_fill(const LocalArgs& a, cudaStream_t st) {
-    if (a.nmp > 0) local_candidates_kernel<true><<<(a.nmp + 127) / 128, 128, 0, st>>>(a);
+    if (a.nmp > 0) local_candidates_kernel<true><<<(a.nmp + LC_WARPS - 1) / LC_WARPS, LC_WARPS * 32, 0, st>>>(a);
     return 1;
 }
 
 int launch_local_sweep(const LocalArgs& a, cudaStream_t st) {
-    if (a.nmp > 0) local_select_kernel<<<(a.nmp + 127) / 128, 128, 0, st>>>(a);
-    if (a.n > 0) local_diff_kernel<<<(a.n + 255) / 256, 256, 0, st>>>(a);
+    const int m = a.n > a.nmp ? a.n : a.nmp;
+    if (m > 0) local_select_kernel<<<(m + 127) / 128, 128, 0, st>>>(a);
     return 2;
 }
 
@@ -855,8 +863,19 @@ int launch_local_finalize(const LocalArgs& a, int* mp_for_kp, uint8_t* occ_out, 
 int launch_frame_finalize(const LocalArgs& a, int* mp_for_kp, int* nmatches, cudaStream_t st) {
     if (a.nmp <= 0) return 0;
     if (a.checkOri) frame_hist_kernel<<<(a.nmp + 127) / 128, 128, 0, st>>>(a);
-    frame_finalize_kernel<<<(a.nmp + 127) / 128, 128, 0, st>>>(a, mp_for_kp, nmatches);
+    const int m = a.n > a.nmp ? a.n : a.nmp;
+    frame_finalize_kernel<<<(m + 127) / 128, 128, 0, st>>>(a, mp_for_kp, nmatches);
     return a.checkOri ? 2 : 1;
+}
+
+int launch_guided_init(int* owners, int n, int nsweeps, bool reset_first, int* mp_for_kp, int* zero_block, int nzero,
+                       uint8_t* occ_out, const uint8_t* occ0, cudaStream_t st) {
+    int* first = reset_first ? owners : owners + n;
+    const int nown = (nsweeps + (reset_first ? 1 : 0)) * n;
+    const int work = nown > nzero ? nown : nzero;
+    guided_init_kernel<<<(work + 1023) / 1024 > 0 ? (work + 1023) / 1024 : 1, 256, 0, st>>>(first, nown, mp_for_kp, n, zero_block, nzero,
+                                                                                         occ_out, occ0);
+    return 1;
 }
 
 int launch_stereo(const StereoArgs& a, cudaStream_t st) {
