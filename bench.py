@@ -114,7 +114,29 @@ def guided_search_timings(frame_img):
         un["x"], un["y"] = u[:, 0], u[:, 1]
         O.assign_grid(O.frame_view(un, d, W, H, scale, bounds=bnd))
 
+    # SearchByBoW(KeyFrame*, Frame&): the frame against a noisy copy of itself, stand-in feature vectors (node =
+    # octave | low 4 bits of the first descriptor byte -> ~128 nodes of ~8 features, the shape DBoW2 gives at levelsup 4)
+    def fvec(dd):
+        fv = {}
+        for i in range(n):
+            fv.setdefault(int((dd[i, 0] & 15) | (k["octave"][i] << 4)), []).append(i)
+        return fv
+    d_noisy = d.copy()
+    flip = rng.integers(0, 256, (n, 12))
+    for j in range(12):
+        d_noisy[np.arange(n), flip[:, j] >> 3] ^= (1 << (flip[:, j] & 7)).astype(np.uint8)
+    d_noisy[:, 0] = (d_noisy[:, 0] & 0xF0) | (d[:, 0] & 0x0F)
+    fv1, fv2 = fvec(d), fvec(d_noisy)
+    valid1 = (rng.random(n) < 0.8).astype(np.uint8)
+    b1, b2 = orbfe.BowSide(d, k["angle"], fv1, valid1), orbfe.BowSide(d_noisy, k["angle"], fv2)
+    o1, o2 = O.bow_view(d, k["angle"], fv1, valid1), O.bow_view(d_noisy, k["angle"], fv2)
+    mtb = orbfe.ORBmatcher(0.75, True)
+    bow_matches = mtb.SearchByBoW(b1, b2)[0]
+
     return {
+        "search_by_bow": {"features": n, "nodes": len(fv1), "matches": bow_matches,
+                          "gpu_ms_per_call": med(lambda: mtb.SearchByBoW(b1, b2)),
+                          "cpu_ms_per_call": med(lambda: O.search_by_bow(o1, o2, 50, 0.75, True))},
         "search_local_points": {"map_points": nmp, "keypoints": n,
                                 "gpu_ms_per_call": med(lambda: mt.SearchByProjection(F, mps, 3.0, np.zeros(n, np.uint8))),
                                 "gpu_resident_frame_ms_per_call": med(lambda: mt.SearchByProjection(dv, mps, 3.0, np.zeros(n, np.uint8))),

@@ -305,6 +305,30 @@ int orbfe_search_frame_points_resident(orbfe_matcher* m, const orbfe_device_fram
                                        const uint8_t* kp_occupied, int32_t* match_for_kp,
                                        int* nmatches);
 
+/* One side of ORBmatcher::SearchByBoW (HOST pointers): descriptors, the keypoint angles the
+ * rotation check reads, "holds a live map point" flags and the side's DBoW2::FeatureVector
+ * (std::map<NodeId, std::vector<unsigned int>>) flattened in map order. */
+typedef struct {
+    int32_t n;                  /* features                                              */
+    const uint8_t* desc;        /* mDescriptors, n x 32                                  */
+    const float* angle;         /* KeyFrame: mvKeysUn[i].angle; Frame: mvKeys[i].angle   */
+    const uint8_t* valid;       /* pMP != NULL && !pMP->isBad(); NULL = every feature    */
+    int32_t nnodes;
+    const uint32_t* node_id;    /* ascending NodeIds                                     */
+    const int32_t* node_start;  /* nnodes + 1 offsets into indices                       */
+    const uint32_t* indices;    /* feature indices, vector order inside a node           */
+} orbfe_bow_view;
+/* SearchByBoW(KeyFrame* pKF, Frame& F, vpMapPointMatches) (src/ORBmatcher.cc:185-325): s1 = pKF,
+ * s2 = F with valid = NULL, th = TH_LOW (accept bestDist1 <= th, :263); the caller sets
+ * vpMapPointMatches[i2] = vpMapPointsKF[matches21[i2]] where matches21[i2] >= 0.
+ * SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vpMatches12) (:610-743): both sides carry valid
+ * flags, th = TH_LOW - 1 (bestDist1 < TH_LOW, :686); vpMatches12[i1] = vpMapPoints2[matches12[i1]].
+ * matches12[s1->n] and matches21[s2->n] are both written (partner index or -1; either may be
+ * NULL); *nmatches = the reference's return value. */
+int orbfe_search_bow(orbfe_matcher* m, const orbfe_bow_view* s1, const orbfe_bow_view* s2, int th,
+                     float nnratio, int check_orientation, int32_t* matches12,
+                     int32_t* matches21, int* nmatches);
+
 /* Pyramid of one extractor call, HOST pointers (interior pixels of mvImagePyramid[l]). */
 typedef struct {
     int32_t nlevels;

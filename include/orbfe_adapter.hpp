@@ -6,6 +6,7 @@
 //                             (DescriptorDistance, SearchForInitialization,
 //                             SearchByProjection(Frame&, vector<MapPoint*>&, th),
 //                             SearchByProjection(CurrentFrame, LastFrame, th, bMono)) and offers
+//                             both SearchByBoW overloads (:185-325, :610-743),
 //                             ComputeStereoMatches(Frame&) for src/Frame.cc:512-686,
 //                             ComputeImageBounds(Frame&, im) for :481-512 and
 //                             UndistortAndAssign(Frame&) for :443-475 + :246-267
@@ -20,6 +21,7 @@
 #define ORBFE_ADAPTER_HPP
 
 #include <cstring>
+#include <map>
 #include <stdexcept>
 #include <string>
 #include <type_traits>
@@ -247,6 +249,40 @@ public:
         return nmatches;
     }
 
+    // SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&) — src/ORBmatcher.cc:185-325.  Reads
+    // pKF->GetMapPointMatches(), mDescriptors, mvKeysUn, mFeatVec and F.N, mDescriptors, mvKeys, mFeatVec.
+    template <class KeyFrameT, class FrameT, class MapPointT>
+    int SearchByBoW(KeyFrameT* pKF, FrameT& F, std::vector<MapPointT*>& vpMapPointMatches) {
+        const std::vector<MapPointT*> vpMapPointsKF = pKF->GetMapPointMatches();
+        vpMapPointMatches = std::vector<MapPointT*>(F.N, static_cast<MapPointT*>(nullptr));
+        BowSide s1(pKF->mDescriptors, pKF->mvKeysUn, pKF->mFeatVec, &vpMapPointsKF);
+        BowSide s2(F.mDescriptors, F.mvKeys, F.mFeatVec, static_cast<const std::vector<MapPointT*>*>(nullptr));
+        std::vector<int32_t> m21(s2.angle.size(), -1);
+        int nmatches = 0;
+        orbfe_detail::check(orbfe_search_bow(mpHandle, &s1.v, &s2.v, TH_LOW, mfNNratio, mbCheckOrientation ? 1 : 0, nullptr,
+                                             m21.data(), &nmatches), "orbfe_search_bow");
+        for (size_t i = 0; i < m21.size() && i < vpMapPointMatches.size(); i++)
+            if (m21[i] >= 0) vpMapPointMatches[i] = vpMapPointsKF[m21[i]];                        // :267
+        return nmatches;
+    }
+
+    // SearchByBoW(KeyFrame*, KeyFrame*, vector<MapPoint*>&) — src/ORBmatcher.cc:610-743
+    template <class KeyFrameT, class MapPointT>
+    int SearchByBoW(KeyFrameT* pKF1, KeyFrameT* pKF2, std::vector<MapPointT*>& vpMatches12) {
+        const std::vector<MapPointT*> vpMapPoints1 = pKF1->GetMapPointMatches();
+        const std::vector<MapPointT*> vpMapPoints2 = pKF2->GetMapPointMatches();
+        vpMatches12 = std::vector<MapPointT*>(vpMapPoints1.size(), static_cast<MapPointT*>(nullptr));
+        BowSide s1(pKF1->mDescriptors, pKF1->mvKeysUn, pKF1->mFeatVec, &vpMapPoints1);
+        BowSide s2(pKF2->mDescriptors, pKF2->mvKeysUn, pKF2->mFeatVec, &vpMapPoints2);
+        std::vector<int32_t> m12(s1.angle.size(), -1);
+        int nmatches = 0;
+        orbfe_detail::check(orbfe_search_bow(mpHandle, &s1.v, &s2.v, TH_LOW - 1, mfNNratio, mbCheckOrientation ? 1 : 0,
+                                             m12.data(), nullptr, &nmatches), "orbfe_search_bow");
+        for (size_t i = 0; i < m12.size() && i < vpMatches12.size(); i++)
+            if (m12[i] >= 0) vpMatches12[i] = vpMapPoints2[m12[i]];                               // :690
+        return nmatches;
+    }
+
     // Frame::ComputeImageBounds — src/Frame.cc:481-512 (call instead of the member, inside the
     // mbInitialComputations block of the Frame constructors, :97-111)
     template <class FrameT>
@@ -325,6 +361,32 @@ protected:
         orbfe_keypoint o = {k.pt.x, k.pt.y, k.size, k.angle, k.response, k.octave, k.class_id};
         return o;
     }
+    // one side of SearchByBoW flattened: angles, live-map-point flags, DBoW2::FeatureVector as CSR
+    struct BowSide {
+        std::vector<float> angle;
+        std::vector<uint8_t> valid;
+        std::vector<uint32_t> nodeId, indices;
+        std::vector<int32_t> nodeStart;
+        orbfe_bow_view v;
+        template <class FeatVecT, class MapPointT>
+        BowSide(const cv::Mat& desc, const std::vector<cv::KeyPoint>& keys, const FeatVecT& fv,
+                const std::vector<MapPointT*>* mps) {
+            angle.resize(keys.size());
+            for (size_t i = 0; i < keys.size(); i++) angle[i] = keys[i].angle;
+            if (mps) {
+                valid.assign(keys.size(), 0);
+                for (size_t i = 0; i < keys.size() && i < mps->size(); i++) valid[i] = (*mps)[i] && !(*mps)[i]->isBad() ? 1 : 0;
+            }
+            nodeStart.push_back(0);
+            for (typename FeatVecT::const_iterator it = fv.begin(); it != fv.end(); ++it) {     // std::map: ascending NodeId
+                nodeId.push_back((uint32_t)it->first);
+                indices.insert(indices.end(), it->second.begin(), it->second.end());
+                nodeStart.push_back((int32_t)indices.size());
+            }
+            v.n = (int32_t)keys.size(); v.desc = desc.data; v.angle = angle.data(); v.valid = mps ? valid.data() : nullptr;
+            v.nnodes = (int32_t)nodeId.size(); v.node_id = nodeId.data(); v.node_start = nodeStart.data(); v.indices = indices.data();
+        }
+    };
     // mK (3x3 CV_32F) and mDistCoef (4x1 or 5x1 CV_32F) as Tracking builds them (src/Tracking.cc:62-85)
     template <class FrameT>
     static orbfe_camera Camera(const FrameT& F) {

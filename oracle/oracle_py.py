@@ -50,6 +50,11 @@ class FramePointsView(C.Structure):
                 ("observations", C.c_void_p)]
 
 
+class BowView(C.Structure):
+    _fields_ = [("n", C.c_int), ("desc", C.c_void_p), ("angle", C.c_void_p), ("valid", C.c_void_p),
+                ("nnodes", C.c_int), ("node_id", C.c_void_p), ("node_start", C.c_void_p), ("indices", C.c_void_p)]
+
+
 class PyramidView(C.Structure):
     _fields_ = [("nlevels", C.c_int), ("data", C.c_void_p), ("w", C.c_void_p), ("h", C.c_void_p),
                 ("stride", C.c_void_p)]
@@ -94,6 +99,7 @@ def lib():
         L.orc_search_by_projection_frame.restype = C.c_int
         L.orc_search_by_projection.argtypes = [C.POINTER(FrameView), C.POINTER(MapPointsView), C.c_float, C.c_float, C.c_void_p, C.c_void_p]
         L.orc_compute_stereo_matches.argtypes = [C.POINTER(FrameView), C.POINTER(FrameView), C.POINTER(PyramidView), C.POINTER(PyramidView), C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+        L.orc_search_by_bow.argtypes = [C.POINTER(BowView), C.POINTER(BowView), C.c_int, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
         L.orc_undistort_points.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_image_bounds.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.orc_knn2.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -300,6 +306,29 @@ def search_by_projection_frame(f, points: dict, check_ori: bool, occupied: np.nd
     out = np.full(max(f[0].n, 1), -1, np.int32)
     nm = lib().orc_search_by_projection_frame(C.byref(f[0]), C.byref(v), int(check_ori), occ.ctypes.data, out.ctypes.data)
     return nm, out[:f[0].n]
+
+
+def bow_view(desc, angle, feat_vec: dict, valid=None):
+    """feat_vec: {node id: [feature indices]} (DBoW2::FeatureVector).  -> (BowView, keepalive)"""
+    desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    angle = np.ascontiguousarray(angle, np.float32)
+    ids = np.array(sorted(feat_vec), np.uint32)
+    start = np.zeros(len(ids) + 1, np.int32)
+    for i, k in enumerate(ids):
+        start[i + 1] = start[i] + len(feat_vec[int(k)])
+    idx = np.array([j for k in ids for j in feat_vec[int(k)]], np.uint32)
+    keep = [desc, angle, ids, start, idx]
+    v = BowView(len(desc), desc.ctypes.data, angle.ctypes.data, None, len(ids), ids.ctypes.data, start.ctypes.data, idx.ctypes.data)
+    if valid is not None:
+        va = np.ascontiguousarray(valid, np.uint8); keep.append(va); v.valid = va.ctypes.data
+    return v, keep
+
+
+def search_by_bow(s1, s2, th: int, nnratio: float, check_ori: bool):
+    """-> (nmatches, m12 int32[n1], m21 int32[n2])"""
+    m12 = np.empty(max(s1[0].n, 1), np.int32); m21 = np.empty(max(s2[0].n, 1), np.int32)
+    nm = lib().orc_search_by_bow(C.byref(s1[0]), C.byref(s2[0]), th, nnratio, int(check_ori), m12.ctypes.data, m21.ctypes.data)
+    return nm, m12[:s1[0].n], m21[:s2[0].n]
 
 
 def undistort_points(xy: np.ndarray, cam, dist) -> np.ndarray:

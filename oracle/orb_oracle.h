@@ -138,6 +138,22 @@ void  orc_compute_stereo_matches(const orc_frame_view* left, const orc_frame_vie
                                  const orc_pyramid_view* pl, const orc_pyramid_view* pr,
                                  const float* inv_scale_factors, float mbf, float mb,
                                  float* uright_out, float* depth_out);
+/* SearchByBoW(KeyFrame*, Frame&, ..) / SearchByBoW(KeyFrame*, KeyFrame*, ..) — ORBmatcher.cc:185-325,
+ * :610-743 (orc_bow.cpp).  A side = descriptors, keypoint angles, "has a live map point" flags
+ * (NULL = all) and its DBoW2::FeatureVector flattened in map order.  th has <= semantics (TH_LOW for
+ * the Frame variant, TH_LOW-1 for the KeyFrame pair).  m12[s1->n], m21[s2->n] out; returns nmatches. */
+typedef struct {
+    int n;
+    const uint8_t* desc;
+    const float* angle;
+    const uint8_t* valid;
+    int nnodes;
+    const uint32_t* node_id;      /* ascending */
+    const int* node_start;        /* nnodes + 1 */
+    const uint32_t* indices;
+} orc_bow_view;
+int   orc_search_by_bow(const orc_bow_view* s1, const orc_bow_view* s2, int th, float nnratio,
+                        int check_orientation, int* m12, int* m21);
 /* Frame constructor epilogue (orc_frame.cpp).  cam = {fx, fy, cx, cy}; dist = {k1, k2, p1, p2, k3}.
  * Frame::UndistortKeyPoints (Frame.cc:443-475): xy / out are n (x, y) pairs. */
 void  orc_undistort_points(const float* xy, int n, const float cam[4], const float dist[5], float* out);

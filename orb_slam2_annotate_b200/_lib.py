@@ -59,6 +59,11 @@ GRID_COLS, GRID_ROWS = 64, 48
 GRID_CELLS = GRID_COLS * GRID_ROWS
 
 
+class BowView(C.Structure):
+    _fields_ = [("n", C.c_int32), ("desc", C.c_void_p), ("angle", C.c_void_p), ("valid", C.c_void_p),
+                ("nnodes", C.c_int32), ("node_id", C.c_void_p), ("node_start", C.c_void_p), ("indices", C.c_void_p)]
+
+
 class PyramidView(C.Structure):
     _fields_ = [("nlevels", C.c_int32), ("data", C.c_void_p), ("width", C.c_void_p),
                 ("height", C.c_void_p), ("stride", C.c_void_p)]
@@ -118,6 +123,7 @@ SIGNATURES = {
     "orbfe_frame_assign": (_i, [_vp, C.POINTER(Camera), _vp, _vp, _i, _vp, _vp, _vp, _ip]),
     "orbfe_search_local_points_resident": (_i, [_vp, C.POINTER(DeviceFrameView), C.POINTER(MapPointsView), _f, _f, _vp, _vp, _ip]),
     "orbfe_search_frame_points_resident": (_i, [_vp, C.POINTER(DeviceFrameView), C.POINTER(FramePointsView), _i, _vp, _vp, _ip]),
+    "orbfe_search_bow": (_i, [_vp, C.POINTER(BowView), C.POINTER(BowView), _i, _f, _i, _vp, _vp, _ip]),
     "orbfe_stereo_match": (_i, [_vp, C.POINTER(FrameView), C.POINTER(FrameView), C.POINTER(PyramidView),
                                 C.POINTER(PyramidView), _vp, _f, _f, _vp, _vp]),
 }

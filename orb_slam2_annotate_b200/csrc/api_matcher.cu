@@ -457,6 +457,70 @@ int orbfe_search_frame_points_resident(orbfe_matcher* m, const orbfe_device_fram
     return search_frame_points_impl(m, &f, df, pts, check_orientation, kp_occupied, match_for_kp, nmatches);
 }
 
+// ORBmatcher::SearchByBoW, both forms — src/ORBmatcher.cc:185-325, :610-743
+int orbfe_search_bow(orbfe_matcher* m, const orbfe_bow_view* s1, const orbfe_bow_view* s2, int th, float nnratio,
+                     int check_orientation, int32_t* matches12, int32_t* matches21, int* nmatches) {
+    if (!m || !s1 || !s2 || !nmatches) return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_search_bow");
+    *nmatches = 0;
+    const orbfe_bow_view* side[2] = {s1, s2};
+    for (const orbfe_bow_view* v : side) {
+        if (v->n < 0 || v->nnodes < 0 || v->n > 65535) return fail(ORBFE_ERR_ARG, "bad feature / node count in bow view (at most 65535 features)");
+        if (v->n && (!v->desc || !v->angle)) return fail(ORBFE_ERR_ARG, "NULL descriptor / angle array in bow view");
+        if (v->nnodes && (!v->node_id || !v->node_start || (v->node_start[v->nnodes] && !v->indices)))
+            return fail(ORBFE_ERR_ARG, "NULL feature vector array in bow view");
+        if (v->nnodes && v->node_start[0] != 0) return fail(ORBFE_ERR_ARG, "bow view: node_start[0] must be 0");
+        for (int k = 0; k < v->nnodes; k++) {
+            if (v->node_start[k + 1] < v->node_start[k]) return fail(ORBFE_ERR_ARG, "bow view: node_start must not decrease");
+            if (k && v->node_id[k] <= v->node_id[k - 1]) return fail(ORBFE_ERR_ARG, "bow view: node ids must ascend");
+        }
+        const int total = v->nnodes ? v->node_start[v->nnodes] : 0;
+        for (int k = 0; k < total; k++)
+            if (v->indices[k] >= (uint32_t)v->n) return fail(ORBFE_ERR_ARG, "bow view: feature index out of range");
+    }
+    const int n1 = s1->n, n2 = s2->n;
+    if (matches12) std::fill(matches12, matches12 + n1, -1);
+    if (matches21) std::fill(matches21, matches21 + n2, -1);
+    if (n1 == 0 || n2 == 0 || s1->nnodes == 0 || s2->nnodes == 0) return ORBFE_OK;
+    CU(cudaSetDevice(m->device));
+    cudaStream_t s = m->stream;
+    int rc;
+    size_t upBytes = 0;
+    for (const orbfe_bow_view* v : side)
+        upBytes += padded((size_t)v->n * 32) + padded((size_t)v->n * 4) + padded(v->n) + padded((size_t)v->nnodes * 4) +
+                   padded((size_t)(v->nnodes + 1) * 4) + padded((size_t)v->node_start[v->nnodes] * 4);
+    if ((rc = m->scratch[0].ensure(upBytes))) return rc;
+    if ((rc = m->stage.ensure(upBytes))) return rc;
+    Upload U{m->stage.p, m->scratch[0].p, 0, upBytes};
+    BowArgs a{};
+    a.n1 = n1; a.n2 = n2; a.nnodes1 = s1->nnodes; a.nnodes2 = s2->nnodes;
+    a.desc1 = U.put<uint8_t>(s1->desc, (size_t)n1 * 32); a.desc2 = U.put<uint8_t>(s2->desc, (size_t)n2 * 32);
+    a.angle1 = U.put<float>(s1->angle, n1); a.angle2 = U.put<float>(s2->angle, n2);
+    a.valid1 = s1->valid ? U.put<uint8_t>(s1->valid, n1) : nullptr;
+    a.valid2 = s2->valid ? U.put<uint8_t>(s2->valid, n2) : nullptr;
+    a.node_id1 = U.put<uint32_t>(s1->node_id, s1->nnodes); a.node_id2 = U.put<uint32_t>(s2->node_id, s2->nnodes);
+    a.node_start1 = U.put<int>(s1->node_start, s1->nnodes + 1); a.node_start2 = U.put<int>(s2->node_start, s2->nnodes + 1);
+    a.indices1 = U.put<uint32_t>(s1->indices, s1->node_start[s1->nnodes]);
+    a.indices2 = U.put<uint32_t>(s2->indices, s2->node_start[s2->nnodes]);
+    if (U.off > U.cap) return fail(ORBFE_ERR_CAPACITY, "internal: matcher staging overflow");
+    CU(cudaMemcpyAsync(m->scratch[0].p, m->stage.p, U.off, cudaMemcpyHostToDevice, s));
+    // result block: [m12 n1 | m21 n2 | hist 30 | nmatches]
+    const size_t rInts = (size_t)n1 + n2 + 31;
+    if ((rc = m->scratch[2].ensure(rInts * 4))) return rc;
+    if ((rc = m->result.ensure(rInts * 4))) return rc;
+    int* R = reinterpret_cast<int*>(m->scratch[2].p);
+    a.m12 = R; a.m21 = R + n1; a.hist = R + n1 + n2; a.nmatches = a.hist + 30;
+    a.th = th; a.ratio = nnratio; a.checkOri = check_orientation;
+    launch_search_bow(a, R, n1 + n2, a.hist, 31, s);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(m->result.p, R, rInts * 4, cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    const int* hR = reinterpret_cast<const int*>(m->result.p);
+    if (matches12) std::memcpy(matches12, hR, sizeof(int) * n1);
+    if (matches21) std::memcpy(matches21, hR + n1, sizeof(int) * n2);
+    *nmatches = hR[n1 + n2 + 30];
+    return ORBFE_OK;
+}
+
 // Frame::ComputeImageBounds (src/Frame.cc:481-512)
 int orbfe_image_bounds(orbfe_matcher* m, const orbfe_camera* cam, int cols, int rows, float bounds[4]) {
     if (!m || !cam || !bounds || cols <= 0 || rows <= 0 || !(cam->fx != 0.0f) || !(cam->fy != 0.0f))

@@ -1,0 +1,145 @@
+// match_bow.cu — K12: ORBmatcher::SearchByBoW, both forms:
+//   SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&)      reference src/ORBmatcher.cc:185-325
+//   SearchByBoW(KeyFrame*, KeyFrame*, vector<MapPoint*>&)   reference src/ORBmatcher.cc:610-743
+// A segmented brute-force 2-nearest-neighbour search: the two DBoW2 feature vectors arrive as CSR
+// (ascending node ids, feature indices in vector order); features only meet inside a common
+// vocabulary node.  One warp per node of side 1: it finds the node on side 2 by binary search
+// (the lower_bound walk of the reference visits exactly the common ids) and then replays the
+// reference's order inside the node — side-1 features one after the other, because each accepted
+// match removes a side-2 feature from the pool (:232 / :662) — while the lanes share the work of
+// one feature: every lane scores its own side-2 candidates and keeps a local best / second-best,
+// a warp min over the keys (distance << 16 | position) picks the winner with the reference's tie
+// rule (strict '<': the first candidate in vector order), the second-best is the smallest among
+// the winner lane's runner-up and the other lanes' bests.  A side-2 feature belongs to one node
+// only, so warps never compete for it.  The rotation histogram (30 bins, only 0..12 reachable,
+// :271-281) is accumulated with atomics; a second small kernel applies ComputeThreeMaxima and
+// clears the matches outside the three leading bins (:298-318).
+#include "match_internal.cuh"
+
+namespace orbfe {
+
+namespace {
+
+constexpr unsigned FULL = 0xFFFFFFFFu;
+constexpr int BW_WARPS = 4;
+constexpr int HISTO = 30;
+
+__device__ __forceinline__ int rot_bin(float a1, float a2) {
+    float rot = __fsub_rn(a1, a2);
+    if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+    int bin = (int)roundf(__fmul_rn(rot, 1.0f / HISTO));
+    if (bin == HISTO) bin = 0;
+    return bin;
+}
+
+// ComputeThreeMaxima (src/ORBmatcher.cc:1777-1821) over bin counts
+__device__ void three_maxima30(const int* hist, int& ind1, int& ind2, int& ind3) {
+    int max1 = 0, max2 = 0, max3 = 0;
+    ind1 = ind2 = ind3 = -1;
+    for (int i = 0; i < HISTO; i++) {
+        const int s = hist[i];
+        if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+        else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+        else if (s > max3) { max3 = s; ind3 = i; }
+    }
+    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if (max3 < 0.1f * (float)max1) ind3 = -1;
+}
+
+__device__ __forceinline__ unsigned warp_min_u32(unsigned v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = min(v, __shfl_xor_sync(FULL, v, o));
+    return v;
+}
+
+__global__ void __launch_bounds__(BW_WARPS * 32) bow_match_kernel(const __grid_constant__ BowArgs a) {
+    const int lane = threadIdx.x & 31;
+    const int node1 = blockIdx.x * BW_WARPS + (threadIdx.x >> 5);
+    if (node1 >= a.nnodes1) return;
+    // the same node on side 2 (std::map::lower_bound over ascending ids)
+    const uint32_t id = a.node_id1[node1];
+    int lo = 0, hi = a.nnodes2;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (a.node_id2[mid] < id) lo = mid + 1; else hi = mid;
+    }
+    if (lo >= a.nnodes2 || a.node_id2[lo] != id) return;
+    const int s1 = a.node_start1[node1], e1 = a.node_start1[node1 + 1];
+    const int s2 = a.node_start2[lo], n2 = a.node_start2[lo + 1] - s2;
+    volatile int* m21 = a.m21;
+    for (int i1 = s1; i1 < e1; i1++) {
+        const int idx1 = (int)a.indices1[i1];
+        if (a.valid1 && !a.valid1[idx1]) continue;                                   // :214-220 / :645-649
+        uint32_t q[8];
+        {
+            const uint4* p = reinterpret_cast<const uint4*>(a.desc1 + 32 * (long long)idx1);
+            const uint4 u = __ldg(p), v = __ldg(p + 1);
+            q[0] = u.x; q[1] = u.y; q[2] = u.z; q[3] = u.w; q[4] = v.x; q[5] = v.y; q[6] = v.z; q[7] = v.w;
+        }
+        unsigned k1 = 0xFFFFFFFFu;       // local best key: distance << 16 | position in the node
+        int d2 = 256;                    // local second-best distance
+        for (int pos = lane; pos < n2; pos += 32) {
+            const int idx2 = (int)a.indices2[s2 + pos];
+            if (m21[idx2] >= 0) continue;                                            // :232 / :662
+            if (a.valid2 && !a.valid2[idx2]) continue;                               // :662-670
+            const uint4* p = reinterpret_cast<const uint4*>(a.desc2 + 32 * (long long)idx2);
+            const uint4 u = __ldg(p), v = __ldg(p + 1);
+            const int dist = __popc(q[0] ^ u.x) + __popc(q[1] ^ u.y) + __popc(q[2] ^ u.z) + __popc(q[3] ^ u.w) +
+                             __popc(q[4] ^ v.x) + __popc(q[5] ^ v.y) + __popc(q[6] ^ v.z) + __popc(q[7] ^ v.w);
+            const unsigned key = ((unsigned)dist << 16) | (unsigned)pos;
+            if (key < k1) { if (k1 != 0xFFFFFFFFu) d2 = (int)(k1 >> 16); k1 = key; }
+            else if (dist < d2) d2 = dist;
+        }
+        const unsigned best = warp_min_u32(k1);
+        if (best == 0xFFFFFFFFu) continue;                                           // no free candidate: bestDist1 = 256
+        const int mine = k1 == best ? d2 : (k1 == 0xFFFFFFFFu ? 256 : (int)(k1 >> 16));
+        const int bestDist2 = (int)warp_min_u32((unsigned)mine);
+        const int bestDist1 = (int)(best >> 16);
+        if (bestDist1 <= a.th && (float)bestDist1 < __fmul_rn(a.ratio, (float)bestDist2)) {   // :263-265 / :686-688
+            const int idx2 = (int)a.indices2[s2 + (int)(best & 0xFFFFu)];
+            if (lane == 0) {
+                a.m12[idx1] = idx2;
+                m21[idx2] = idx1;
+                if (a.checkOri) atomicAdd(&a.hist[rot_bin(a.angle1[idx1], a.angle2[idx2])], 1);   // :271-281
+                atomicAdd(a.nmatches, 1);
+            }
+            __syncwarp();
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) bow_rotation_kernel(const __grid_constant__ BowArgs a) {
+    __shared__ int ind[3];
+    if (threadIdx.x == 0) three_maxima30(a.hist, ind[0], ind[1], ind[2]);
+    __syncthreads();
+    const int idx1 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx1 >= a.n1) return;
+    const int idx2 = a.m12[idx1];
+    if (idx2 < 0) return;
+    const int bin = rot_bin(a.angle1[idx1], a.angle2[idx2]);
+    if (bin == ind[0] || bin == ind[1] || bin == ind[2]) return;
+    a.m12[idx1] = -1; a.m21[idx2] = -1;                                              // :311-315
+    atomicSub(a.nmatches, 1);
+}
+
+// m12 / m21 to -1, histogram and match count to 0 (they sit in one block: see api_matcher.cu)
+__global__ void __launch_bounds__(256) bow_init_kernel(int* minus1, int nminus1, int* zero, int nzero) {
+    const int stride = gridDim.x * blockDim.x, t = blockIdx.x * blockDim.x + threadIdx.x;
+    for (int i = t; i < nminus1; i += stride) minus1[i] = -1;
+    for (int i = t; i < nzero; i += stride) zero[i] = 0;
+}
+
+}  // namespace
+
+int launch_search_bow(const BowArgs& a, int* minus1, int nminus1, int* zero, int nzero, cudaStream_t st) {
+    bow_init_kernel<<<(nminus1 + 1023) / 1024 > 0 ? (nminus1 + 1023) / 1024 : 1, 256, 0, st>>>(minus1, nminus1, zero, nzero);
+    int launches = 1;
+    if (a.nnodes1 > 0 && a.nnodes2 > 0) {
+        bow_match_kernel<<<(a.nnodes1 + BW_WARPS - 1) / BW_WARPS, BW_WARPS * 32, 0, st>>>(a);
+        launches++;
+        if (a.checkOri && a.n1 > 0) { bow_rotation_kernel<<<(a.n1 + 255) / 256, 256, 0, st>>>(a); launches++; }
+    }
+    return launches;
+}
+
+}  // namespace orbfe

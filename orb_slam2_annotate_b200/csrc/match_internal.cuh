@@ -85,6 +85,25 @@ struct StereoArgs {
     int* sad;           // per left keypoint: truncated best SAD, or -1 when no match
 };
 
+// SearchByBoW: two sides = descriptors, keypoint angles, live-map-point flags (NULL = all) and the
+// DBoW2::FeatureVector as CSR (ascending node ids, feature indices in vector order)
+struct BowArgs {
+    int n1, n2;
+    const uint8_t* desc1; const uint8_t* desc2;
+    const float* angle1; const float* angle2;
+    const uint8_t* valid1; const uint8_t* valid2;
+    int nnodes1, nnodes2;
+    const uint32_t* node_id1; const uint32_t* node_id2;
+    const int* node_start1; const int* node_start2;
+    const uint32_t* indices1; const uint32_t* indices2;
+    int th; float ratio; int checkOri;
+    int* m12; int* m21;          // [n1], [n2]: partner index or -1
+    int* hist;                   // [30]
+    int* nmatches;
+};
+// minus1 / zero: the result block's "-1" part (m12, m21) and "0" part (histogram, count)
+int launch_search_bow(const BowArgs& a, int* minus1, int nminus1, int* zero, int nzero, cudaStream_t st);
+
 size_t search_init_scratch_bytes(int cap, int npairs);
 void search_init_carve(InitArgs& a, void* scratch, int npairs);
 int launch_search_init(const InitArgs& a, int npairs, cudaStream_t st);

@@ -10,7 +10,7 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._lib import (KP_DTYPE, Camera, DeviceFrameView, FrameView, MapPointsView, FramePointsView, PyramidView,
+from ._lib import (KP_DTYPE, BowView, Camera, DeviceFrameView, FrameView, MapPointsView, FramePointsView, PyramidView,
                    GRID_CELLS, check)
 
 
@@ -38,6 +38,27 @@ class Frame:
                          None if self.uright is None else self.uright.ctypes.data,
                          self.min_x, self.max_x, self.min_y, self.max_y,
                          self.scale_factors.ctypes.data, len(self.scale_factors))
+
+
+class BowSide:
+    """One side of SearchByBoW: descriptors, keypoint angles, optional live-map-point flags and the
+    DBoW2::FeatureVector as ``{node id: [feature indices]}`` (flattened in map order)."""
+
+    def __init__(self, descriptors: np.ndarray, angles: np.ndarray, feat_vec: dict, valid: np.ndarray | None = None):
+        self.desc = np.ascontiguousarray(descriptors, np.uint8).reshape(-1, 32)
+        self.angle = np.ascontiguousarray(angles, np.float32)
+        assert len(self.desc) == len(self.angle)
+        self.node_id = np.array(sorted(feat_vec), np.uint32)
+        self.node_start = np.zeros(len(self.node_id) + 1, np.int32)
+        for i, k in enumerate(self.node_id):
+            self.node_start[i + 1] = self.node_start[i] + len(feat_vec[int(k)])
+        self.indices = np.array([j for k in self.node_id for j in feat_vec[int(k)]], np.uint32)
+        self.valid = None if valid is None else np.ascontiguousarray(valid, np.uint8)
+
+    def view(self) -> BowView:
+        return BowView(len(self.desc), self.desc.ctypes.data, self.angle.ctypes.data,
+                       None if self.valid is None else self.valid.ctypes.data, len(self.node_id),
+                       self.node_id.ctypes.data, self.node_start.ctypes.data, self.indices.ctypes.data)
 
 
 def project_last_frame(Tcw_cur: np.ndarray, Tcw_last: np.ndarray, world_pos: np.ndarray, last_octave: np.ndarray,
@@ -211,6 +232,19 @@ class ORBmatcher:
                                                     occupied.ctypes.data, out.ctypes.data, C.byref(n)),
                   "orbfe_search_frame_points")
         return n.value, out[:N]
+
+    def SearchByBoW(self, side1: BowSide, side2: BowSide, keyframe_pair: bool = False):
+        """SearchByBoW(KeyFrame*, Frame&, ..) — src/ORBmatcher.cc:185-325 — or, with ``keyframe_pair``,
+        SearchByBoW(KeyFrame*, KeyFrame*, ..) — :610-743 (bestDist1 < TH_LOW instead of <=).
+        -> (nmatches, matches12 int32[n1], matches21 int32[n2]); partner index or -1."""
+        n1, n2 = len(side1.desc), len(side2.desc)
+        m12 = np.empty(max(n1, 1), np.int32); m21 = np.empty(max(n2, 1), np.int32)
+        n = C.c_int()
+        v1, v2 = side1.view(), side2.view()
+        check(self._L.orbfe_search_bow(self._h, C.byref(v1), C.byref(v2), self.TH_LOW - 1 if keyframe_pair else self.TH_LOW,
+                                       self.mfNNratio, int(self.mbCheckOrientation), m12.ctypes.data, m21.ctypes.data,
+                                       C.byref(n)), "orbfe_search_bow")
+        return n.value, m12[:n1], m21[:n2]
 
     # --- Frame constructor epilogue for callers without a batched extractor handle
     def ComputeImageBounds(self, camera, cols: int, rows: int) -> np.ndarray:

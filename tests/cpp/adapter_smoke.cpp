@@ -6,20 +6,45 @@
 // usage: adapter_smoke in.bin out.bin     in.bin = int32 w, h, then 2*w*h bytes (two frames)
 #include <cstdio>
 #include <cstdlib>
+#include <map>
 #include <vector>
 
 #include "cvshim.hpp"
 #include "orbfe_adapter.hpp"
+
+struct MapPoint {
+    bool bad;
+    bool isBad() const { return bad; }
+};
+typedef std::map<unsigned int, std::vector<unsigned int> > FeatureVector;   // DBoW2::FeatureVector
 
 struct Frame {   // the members of ORB_SLAM2::Frame the matcher reads (include/Frame.h)
     std::vector<cv::KeyPoint> mvKeys, mvKeysUn;
     cv::Mat mDescriptors;
     std::vector<float> mvScaleFactors;
     cv::Mat mK, mDistCoef;
+    int N;
+    FeatureVector mFeatVec;
     std::vector<std::size_t> mGrid[64][48];
     static float mnMinX, mnMaxX, mnMinY, mnMaxY;
 };
 float Frame::mnMinX, Frame::mnMaxX, Frame::mnMinY, Frame::mnMaxY;
+
+struct KeyFrame {   // the members SearchByBoW reads (include/KeyFrame.h)
+    std::vector<cv::KeyPoint> mvKeysUn;
+    cv::Mat mDescriptors;
+    FeatureVector mFeatVec;
+    std::vector<MapPoint*> mps;
+    std::vector<MapPoint*> GetMapPointMatches() const { return mps; }
+};
+
+// stand-in for the vocabulary: node id from the octave and the low four bits of the first descriptor byte
+static FeatureVector fake_feat_vec(const std::vector<cv::KeyPoint>& keys, const cv::Mat& desc) {
+    FeatureVector fv;
+    for (size_t i = 0; i < keys.size(); i++)
+        fv[(unsigned)((desc.data[32 * i] & 15) | (keys[i].octave << 4))].push_back((unsigned)i);
+    return fv;
+}
 
 int main(int argc, char** argv) {
     if (argc < 3) return 2;
@@ -78,6 +103,26 @@ int main(int argc, char** argv) {
             fwrite(&cnt, 4, 1, o);
             for (int j = 0; j < cnt; j++) { int v = (int)F[0].mGrid[ix][iy][j]; fwrite(&v, 4, 1, o); }
         }
+    // SearchByBoW(KeyFrame*, Frame&, ..) and SearchByBoW(KeyFrame*, KeyFrame*, ..): frame 0 as key frame (every
+    // third feature without a map point, every seventh with a bad one) against frame 1
+    MapPoint good = {false}, bad = {true};
+    KeyFrame KF[2];
+    for (int i = 0; i < 2; i++) {
+        KF[i].mvKeysUn = F[i].mvKeys; KF[i].mDescriptors = F[i].mDescriptors;
+        KF[i].mFeatVec = fake_feat_vec(F[i].mvKeys, F[i].mDescriptors);
+        KF[i].mps.resize(F[i].mvKeys.size());
+        for (size_t k = 0; k < KF[i].mps.size(); k++) KF[i].mps[k] = k % 3 == 0 ? nullptr : (k % 7 == 0 ? &bad : &good);
+        F[i].N = (int)F[i].mvKeys.size(); F[i].mFeatVec = KF[i].mFeatVec;
+    }
+    ORB_SLAM2::ORBmatcher bow(0.75f, true);                          // Tracking.cc:871 / :1379
+    std::vector<MapPoint*> vpMatches, vpMatches12;
+    const int nb1 = bow.SearchByBoW(&KF[0], F[1], vpMatches);
+    const int nb2 = bow.SearchByBoW(&KF[0], &KF[1], vpMatches12);
+    int cnt1 = 0, cnt2 = 0;
+    for (size_t k = 0; k < vpMatches.size(); k++) cnt1 += vpMatches[k] != nullptr;
+    for (size_t k = 0; k < vpMatches12.size(); k++) cnt2 += vpMatches12[k] != nullptr;
+    const int bowOut[6] = {nb1, cnt1, (int)vpMatches.size(), nb2, cnt2, (int)vpMatches12.size()};
+    fwrite(bowOut, 4, 6, o);
     fclose(o);
     printf("adapter_smoke: %zu + %zu keypoints, %d init matches, DescriptorDistance(0,1)=%d\n", F[0].mvKeys.size(),
            F[1].mvKeys.size(), nm,

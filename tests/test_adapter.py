@@ -73,4 +73,19 @@ def test_adapter_end_to_end(orbfe, oracle, tmp_path):
         cnt = int(np.frombuffer(raw, np.int32, 1, off)[0]); off += 4
         got = np.frombuffer(raw, np.int32, cnt, off); off += 4 * cnt
         assert np.array_equal(got, items[cs[c]:cs[c + 1]])
+    # both SearchByBoW overloads through the adapter: counts against the oracle on the same stand-in feature vectors
+    nb1, cnt1, len1, nb2, cnt2, len2 = (int(v) for v in np.frombuffer(raw, np.int32, 6, off)); off += 24
     assert off == len(raw)
+    sides = []
+    for k, d in frames:
+        fv = {}
+        for i in range(len(k)):
+            fv.setdefault(int((d[i, 0] & 15) | (k["octave"][i] << 4)), []).append(i)
+        idx = np.arange(len(k))
+        valid = ((idx % 3 != 0) & ~((idx % 7 == 0) & (idx % 3 != 0))).astype(np.uint8)
+        sides.append((d, k["angle"], fv, valid))
+    (da, aa, fva, va), (db, ab, fvb, vb) = sides
+    n1, _, o21 = oracle.search_by_bow(oracle.bow_view(da, aa, fva, va), oracle.bow_view(db, ab, fvb), 50, 0.75, True)
+    n2, o12, _ = oracle.search_by_bow(oracle.bow_view(da, aa, fva, va), oracle.bow_view(db, ab, fvb, vb), 49, 0.75, True)
+    assert (nb1, cnt1, len1) == (n1, int((o21 >= 0).sum()), len(db)) and n1 > 30
+    assert (nb2, cnt2, len2) == (n2, int((o12 >= 0).sum()), len(da)) and n2 > 10

@@ -150,3 +150,65 @@ def test_compute_stereo_matches(orbfe, oracle):
                                                oracle.pyramid_view(pl), oracle.pyramid_view(pr), t["inv_scale"], mbf, mb)
         assert ug.tobytes() == uo.tobytes() and dg.tobytes() == do.tobytes()
         assert (ug >= 0).sum() > 100
+
+
+def _feat_vec(desc, octave, nbits, rng=None, drop=0.0):
+    """Stand-in for DBoW2's FeatureVector: node id from the octave and the low `nbits` bits of the first
+    descriptor byte, so that look-alike features of two frames mostly share a node."""
+    node = (desc[:, 0].astype(np.int64) & ((1 << nbits) - 1)) | (octave.astype(np.int64) << nbits)
+    fv = {}
+    for i, k in enumerate(node):
+        fv.setdefault(int(k) * 3 + 1, []).append(i)
+    if rng is not None:
+        for k in list(fv):
+            if rng.random() < drop:
+                del fv[k]                   # nodes present on one side only
+            else:
+                rng.shuffle(fv[k])          # vector order inside a node is arbitrary for the routine
+    return fv
+
+
+@pytest.mark.parametrize("pair,nbits,ratio,ori,shuffle", [(False, 4, 0.7, True, False), (True, 4, 0.75, True, True),
+                                                           (False, 0, 0.9, False, True), (True, 1, 0.6, True, False),
+                                                           (False, 6, 0.75, True, True)])
+def test_search_by_bow(orbfe, oracle, pair, nbits, ratio, ori, shuffle):
+    fr = _frames(oracle, "mono", 7, 2000)
+    (k1, d1, _, _), (k2, d2, _, _) = fr[0], fr[1]
+    rng = np.random.default_rng(31)
+    fv1 = _feat_vec(d1, k1["octave"], nbits, rng if shuffle else None, 0.1)
+    fv2 = _feat_vec(d2, k2["octave"], nbits, rng if shuffle else None, 0.1)
+    v1 = (rng.random(len(k1)) < 0.8).astype(np.uint8)
+    v2 = (rng.random(len(k2)) < 0.8).astype(np.uint8) if pair else None
+    mt = orbfe.ORBmatcher(ratio, ori)
+    ng, g12, g21 = mt.SearchByBoW(orbfe.BowSide(d1, k1["angle"], fv1, v1), orbfe.BowSide(d2, k2["angle"], fv2, v2), keyframe_pair=pair)
+    no, o12, o21 = oracle.search_by_bow(oracle.bow_view(d1, k1["angle"], fv1, v1), oracle.bow_view(d2, k2["angle"], fv2, v2),
+                                        49 if pair else 50, ratio, ori)
+    assert ng == no and np.array_equal(g12, o12) and np.array_equal(g21, o21)
+    assert ng == (o12 >= 0).sum() == (o21 >= 0).sum()
+    assert ng > (5 if nbits == 6 else 40)
+
+
+def test_search_by_bow_degenerate(orbfe, oracle):
+    fr = _frames(oracle, "mono", 7, 2000)
+    (k1, d1, _, _), (k2, d2, _, _) = fr[0], fr[1]
+    mt = orbfe.ORBmatcher(0.7, True)
+    fv1 = _feat_vec(d1, k1["octave"], 4)
+    s1 = orbfe.BowSide(d1, k1["angle"], fv1)
+    # no common node
+    fv2 = {k + 1: v for k, v in _feat_vec(d2, k2["octave"], 4).items()}
+    n, m12, m21 = mt.SearchByBoW(s1, orbfe.BowSide(d2, k2["angle"], fv2))
+    assert n == 0 and (m12 == -1).all() and (m21 == -1).all()
+    # an empty side / an empty feature vector
+    n, m12, m21 = mt.SearchByBoW(s1, orbfe.BowSide(d2[:0], k2["angle"][:0], {}))
+    assert n == 0 and len(m21) == 0 and (m12 == -1).all()
+    n, m12, m21 = mt.SearchByBoW(orbfe.BowSide(d1, k1["angle"], {}), orbfe.BowSide(d2, k2["angle"], fv2))
+    assert n == 0
+    # a frame against itself: every feature finds itself at distance 0, second-best decides
+    n, m12, m21 = mt.SearchByBoW(s1, s1)
+    no, o12, o21 = oracle.search_by_bow(oracle.bow_view(d1, k1["angle"], fv1), oracle.bow_view(d1, k1["angle"], fv1), 50, 0.7, True)
+    assert n == no and np.array_equal(m12, o12) and np.array_equal(m21, o21) and n > 500
+    # malformed feature vectors are rejected
+    bad = orbfe.BowSide(d2, k2["angle"], fv2)
+    bad.indices[0] = len(d2)
+    with pytest.raises(orbfe.OrbfeError):
+        mt.SearchByBoW(s1, bad)

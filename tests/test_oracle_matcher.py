@@ -156,3 +156,64 @@ def test_knn2_kat(oracle):
     t[0, 0] = 1        # two rows at distance 1: first wins, d2 == d1, ratio test rejects
     idx, d1, d2 = oracle.knn2(q, t, 50, 0.7)
     assert (idx[0], d1[0], d2[0]) == (-1, 1, 1)
+
+
+def _bits(k):
+    """descriptor with the first k bits set: Hamming distance k from the zero descriptor"""
+    d = np.zeros(32, np.uint8)
+    for b in range(k):
+        d[b >> 3] |= 1 << (b & 7)
+    return d
+
+
+def test_search_by_bow_kat(oracle):
+    """Hand-derived cases for SearchByBoW (ORBmatcher.cc:185-325 and :610-743)."""
+    z = _bits(0)
+    # side 1: three features, all zero descriptors; nodes {1: [0], 5: [1, 2]}.  side 2: nodes {5: [0, 1, 2], 7: [3]}
+    d2 = np.stack([_bits(3), _bits(10), _bits(30), _bits(0)])
+    s1 = oracle.bow_view(np.stack([z, z, z]), [0, 0, 0], {1: [0], 5: [1, 2]})
+    s2 = oracle.bow_view(d2, [0, 0, 0, 0], {5: [0, 1, 2], 7: [3]})
+    # node 1 has no partner (lower_bound skips it, :289); in node 5 feature 1 takes side-2 feature 0
+    # (3 < 0.7 * 10), then feature 2 sees only {1, 2}: 10 < 0.7 * 30 -> takes 1.  Side-2 feature 3 (node 7,
+    # distance 0) is never looked at.
+    n, m12, m21 = oracle.search_by_bow(s1, s2, 50, 0.7, False)
+    assert n == 2 and m12.tolist() == [-1, 0, 1] and m21.tolist() == [1, 2, -1, -1]
+    # ratio 0.25: 3 < 2.5 fails for feature 1, so side-2 feature 0 stays free and feature 2 fails the same way
+    n, m12, m21 = oracle.search_by_bow(s1, s2, 50, 0.25, False)
+    assert n == 0 and (m12 == -1).all() and (m21 == -1).all()
+    # threshold: best == 50 passes with th = 50 (<= TH_LOW, :263) and fails with th = 49 (< TH_LOW, :686)
+    a = oracle.bow_view(np.stack([z]), [0], {3: [0]})
+    b = oracle.bow_view(np.stack([_bits(50), _bits(200)]), [0, 0], {3: [0, 1]})
+    assert oracle.search_by_bow(a, b, 50, 0.7, False)[0] == 1
+    assert oracle.search_by_bow(a, b, 49, 0.7, False)[0] == 0
+    # two candidates at the same distance: the first is best, the second becomes second-best (:253-256),
+    # and d < ratio * d fails
+    b = oracle.bow_view(np.stack([_bits(8), _bits(8)]), [0, 0], {3: [0, 1]})
+    assert oracle.search_by_bow(a, b, 50, 0.9, False)[0] == 0
+    # a lone candidate: second-best stays 256
+    b = oracle.bow_view(np.stack([_bits(40)]), [0], {3: [0]})
+    n, m12, m21 = oracle.search_by_bow(a, b, 50, 0.7, False)
+    assert n == 1 and m12.tolist() == [0] and m21.tolist() == [0]
+    # map point flags: an invalid side-1 feature is skipped (:214-220), an invalid side-2 feature is not a
+    # candidate in the KeyFrame-pair form (:662-670)
+    s1 = oracle.bow_view(np.stack([z, z]), [0, 0], {2: [0, 1]}, valid=[0, 1])
+    s2 = oracle.bow_view(np.stack([_bits(1), _bits(20)]), [0, 0], {2: [0, 1]}, valid=[0, 1])
+    n, m12, m21 = oracle.search_by_bow(s1, s2, 49, 0.7, False)
+    assert n == 1 and m12.tolist() == [-1, 1] and m21.tolist() == [-1, 1]
+    # feature order inside a node is the vector's order, not the index order
+    s1 = oracle.bow_view(np.stack([z, z]), [0, 0], {2: [1, 0]})
+    s2 = oracle.bow_view(np.stack([_bits(2), _bits(12)]), [0, 0], {2: [1, 0]})
+    n, m12, m21 = oracle.search_by_bow(s1, s2, 50, 0.7, False)
+    assert n == 2 and m12.tolist() == [1, 0]        # feature 1 goes first and takes side-2 feature 0
+    # rotation check (:298-318): eleven matches with rot 0 (bin 0) and one with rot 100 (bin round(100/30) = 3):
+    # 1 < 0.1 * 11, so bin 3 is not a maximum and its match is removed from both result arrays
+    n1 = 12
+    d1 = np.stack([_bits(0)] * n1)
+    d2 = np.stack([_bits(1)] * n1)
+    fv = {i: [i] for i in range(n1)}
+    s1 = oracle.bow_view(d1, [0.0] * 11 + [100.0], fv)
+    s2 = oracle.bow_view(d2, [0.0] * n1, fv)
+    n, m12, m21 = oracle.search_by_bow(s1, s2, 50, 0.7, True)
+    assert n == 11 and m12.tolist() == list(range(11)) + [-1] and m21.tolist() == list(range(11)) + [-1]
+    n, m12, m21 = oracle.search_by_bow(s1, s2, 50, 0.7, False)
+    assert n == 12 and m12.tolist() == list(range(12))
