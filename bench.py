@@ -136,7 +136,10 @@ def guided_search_timings(frame_img):
     return {
         "search_by_bow": {"features": n, "nodes": len(fv1), "matches": bow_matches,
                           "gpu_ms_per_call": med(lambda: mtb.SearchByBoW(b1, b2)),
-                          "cpu_ms_per_call": med(lambda: O.search_by_bow(o1, o2, 50, 0.75, True))},
+                          "cpu_ms_per_call": med(lambda: O.search_by_bow(o1, o2, 50, 0.75, True)),
+                          # relocalisation shape: 32 key frames against the one frame, one call
+                          "gpu_ms_per_32_pairs_batched": med(lambda: mtb.SearchByBoWBatch([b1] * 32, [b2] * 32)),
+                          "cpu_ms_per_32_pairs": med(lambda: [O.search_by_bow(o1, o2, 50, 0.75, True) for _ in range(32)])},
         "search_local_points": {"map_points": nmp, "keypoints": n,
                                 "gpu_ms_per_call": med(lambda: mt.SearchByProjection(F, mps, 3.0, np.zeros(n, np.uint8))),
                                 "gpu_resident_frame_ms_per_call": med(lambda: mt.SearchByProjection(dv, mps, 3.0, np.zeros(n, np.uint8))),

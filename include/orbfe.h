@@ -329,6 +329,14 @@ int orbfe_search_bow(orbfe_matcher* m, const orbfe_bow_view* s1, const orbfe_bow
                      float nnratio, int check_orientation, int32_t* matches12,
                      int32_t* matches21, int* nmatches);
 
+/* npairs searches in one call (s1[p] against s2[p]; matches12[p] / matches21[p] as above, the
+ * pointer arrays or single entries may be NULL; nmatches[npairs]).  A side that appears in several
+ * pairs with the same arrays — the current frame of Tracking::Relocalization against every
+ * candidate key frame, src/Tracking.cc:1486-1510 — is uploaded once. */
+int orbfe_search_bow_batch(orbfe_matcher* m, int npairs, const orbfe_bow_view* s1,
+                           const orbfe_bow_view* s2, int th, float nnratio, int check_orientation,
+                           int32_t* const* matches12, int32_t* const* matches21, int* nmatches);
+
 /* Pyramid of one extractor call, HOST pointers (interior pixels of mvImagePyramid[l]). */
 typedef struct {
     int32_t nlevels;

@@ -457,13 +457,32 @@ int orbfe_search_frame_points_resident(orbfe_matcher* m, const orbfe_device_fram
     return search_frame_points_impl(m, &f, df, pts, check_orientation, kp_occupied, match_for_kp, nmatches);
 }
 
-// ORBmatcher::SearchByBoW, both forms — src/ORBmatcher.cc:185-325, :610-743
-int orbfe_search_bow(orbfe_matcher* m, const orbfe_bow_view* s1, const orbfe_bow_view* s2, int th, float nnratio,
-                     int check_orientation, int32_t* matches12, int32_t* matches21, int* nmatches) {
-    if (!m || !s1 || !s2 || !nmatches) return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_search_bow");
-    *nmatches = 0;
-    const orbfe_bow_view* side[2] = {s1, s2};
-    for (const orbfe_bow_view* v : side) {
+// ORBmatcher::SearchByBoW, both forms — src/ORBmatcher.cc:185-325, :610-743 — for npairs (side 1, side 2)
+// pairs in one go.  Sides that are the same object in several pairs (the current frame of a relocalisation
+// against all its candidate key frames, Tracking.cc:1486-1510) are uploaded once.
+int orbfe_search_bow_batch(orbfe_matcher* m, int npairs, const orbfe_bow_view* s1, const orbfe_bow_view* s2, int th,
+                           float nnratio, int check_orientation, int32_t* const* matches12,
+                           int32_t* const* matches21, int* nmatches) {
+    if (!m || npairs < 0 || (npairs && (!s1 || !s2 || !nmatches))) return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_search_bow_batch");
+    if (npairs == 0) return ORBFE_OK;
+    // distinct sides, by content of the view (same arrays = same side)
+    std::vector<const orbfe_bow_view*> sides;
+    std::vector<int> sideOf((size_t)2 * npairs);
+    auto same = [](const orbfe_bow_view* a, const orbfe_bow_view* b) {
+        return a->n == b->n && a->desc == b->desc && a->angle == b->angle && a->valid == b->valid && a->nnodes == b->nnodes &&
+               a->node_id == b->node_id && a->node_start == b->node_start && a->indices == b->indices;
+    };
+    for (int p = 0; p < npairs; p++)
+        for (int k = 0; k < 2; k++) {
+            const orbfe_bow_view* v = k ? &s2[p] : &s1[p];
+            int found = -1;
+            for (int j = (int)sides.size() - 1; j >= 0 && j >= (int)sides.size() - 4; j--)      // neighbours repeat, if anything does
+                if (same(sides[j], v)) { found = j; break; }
+            if (found < 0) { found = (int)sides.size(); sides.push_back(v); }
+            sideOf[2 * p + k] = found;
+        }
+    size_t upBytes = padded((size_t)npairs * sizeof(BowArgs));
+    for (const orbfe_bow_view* v : sides) {
         if (v->n < 0 || v->nnodes < 0 || v->n > 65535) return fail(ORBFE_ERR_ARG, "bad feature / node count in bow view (at most 65535 features)");
         if (v->n && (!v->desc || !v->angle)) return fail(ORBFE_ERR_ARG, "NULL descriptor / angle array in bow view");
         if (v->nnodes && (!v->node_id || !v->node_start || (v->node_start[v->nnodes] && !v->indices)))
@@ -476,49 +495,73 @@ int orbfe_search_bow(orbfe_matcher* m, const orbfe_bow_view* s1, const orbfe_bow
         const int total = v->nnodes ? v->node_start[v->nnodes] : 0;
         for (int k = 0; k < total; k++)
             if (v->indices[k] >= (uint32_t)v->n) return fail(ORBFE_ERR_ARG, "bow view: feature index out of range");
+        upBytes += padded((size_t)v->n * 32) + padded((size_t)v->n * 4) + padded(v->n) + padded((size_t)v->nnodes * 4) +
+                   padded((size_t)(v->nnodes + 1) * 4) + padded((size_t)total * 4);
     }
-    const int n1 = s1->n, n2 = s2->n;
-    if (matches12) std::fill(matches12, matches12 + n1, -1);
-    if (matches21) std::fill(matches21, matches21 + n2, -1);
-    if (n1 == 0 || n2 == 0 || s1->nnodes == 0 || s2->nnodes == 0) return ORBFE_OK;
     CU(cudaSetDevice(m->device));
     cudaStream_t s = m->stream;
     int rc;
-    size_t upBytes = 0;
-    for (const orbfe_bow_view* v : side)
-        upBytes += padded((size_t)v->n * 32) + padded((size_t)v->n * 4) + padded(v->n) + padded((size_t)v->nnodes * 4) +
-                   padded((size_t)(v->nnodes + 1) * 4) + padded((size_t)v->node_start[v->nnodes] * 4);
     if ((rc = m->scratch[0].ensure(upBytes))) return rc;
     if ((rc = m->stage.ensure(upBytes))) return rc;
     Upload U{m->stage.p, m->scratch[0].p, 0, upBytes};
-    BowArgs a{};
-    a.n1 = n1; a.n2 = n2; a.nnodes1 = s1->nnodes; a.nnodes2 = s2->nnodes;
-    a.desc1 = U.put<uint8_t>(s1->desc, (size_t)n1 * 32); a.desc2 = U.put<uint8_t>(s2->desc, (size_t)n2 * 32);
-    a.angle1 = U.put<float>(s1->angle, n1); a.angle2 = U.put<float>(s2->angle, n2);
-    a.valid1 = s1->valid ? U.put<uint8_t>(s1->valid, n1) : nullptr;
-    a.valid2 = s2->valid ? U.put<uint8_t>(s2->valid, n2) : nullptr;
-    a.node_id1 = U.put<uint32_t>(s1->node_id, s1->nnodes); a.node_id2 = U.put<uint32_t>(s2->node_id, s2->nnodes);
-    a.node_start1 = U.put<int>(s1->node_start, s1->nnodes + 1); a.node_start2 = U.put<int>(s2->node_start, s2->nnodes + 1);
-    a.indices1 = U.put<uint32_t>(s1->indices, s1->node_start[s1->nnodes]);
-    a.indices2 = U.put<uint32_t>(s2->indices, s2->node_start[s2->nnodes]);
+    BowArgs* d_pairs = U.put<BowArgs>(nullptr, npairs);
+    BowArgs* h_pairs = reinterpret_cast<BowArgs*>(m->stage.p + ((uint8_t*)d_pairs - m->scratch[0].p));
+    struct DevSide { const uint8_t* desc; const float* angle; const uint8_t* valid; const uint32_t* node_id; const int* node_start; const uint32_t* indices; };
+    std::vector<DevSide> dev(sides.size());
+    for (size_t j = 0; j < sides.size(); j++) {
+        const orbfe_bow_view* v = sides[j];
+        const int total = v->nnodes ? v->node_start[v->nnodes] : 0;
+        dev[j].desc = U.put<uint8_t>(v->desc, (size_t)v->n * 32);
+        dev[j].angle = U.put<float>(v->angle, v->n);
+        dev[j].valid = v->valid ? U.put<uint8_t>(v->valid, v->n) : nullptr;
+        dev[j].node_id = U.put<uint32_t>(v->node_id, v->nnodes);
+        dev[j].node_start = U.put<int>(v->nnodes ? v->node_start : nullptr, v->nnodes ? v->nnodes + 1 : 0);
+        dev[j].indices = U.put<uint32_t>(v->indices, total);
+    }
     if (U.off > U.cap) return fail(ORBFE_ERR_CAPACITY, "internal: matcher staging overflow");
-    CU(cudaMemcpyAsync(m->scratch[0].p, m->stage.p, U.off, cudaMemcpyHostToDevice, s));
-    // result block: [m12 n1 | m21 n2 | hist 30 | nmatches]
-    const size_t rInts = (size_t)n1 + n2 + 31;
+    // result block: [m12 | m21 of every pair] [hist 30 + nmatches of every pair]
+    size_t nMinus = 0;
+    int maxNodes1 = 0, maxN1 = 0;
+    for (int p = 0; p < npairs; p++) { nMinus += (size_t)s1[p].n + s2[p].n; maxNodes1 = std::max(maxNodes1, s1[p].nnodes); maxN1 = std::max(maxN1, s1[p].n); }
+    const size_t rInts = nMinus + (size_t)31 * npairs;
+    if (rInts > 0x7FFFFFFF) return fail(ORBFE_ERR_CAPACITY, "too many features in one SearchByBoW batch");
     if ((rc = m->scratch[2].ensure(rInts * 4))) return rc;
     if ((rc = m->result.ensure(rInts * 4))) return rc;
     int* R = reinterpret_cast<int*>(m->scratch[2].p);
-    a.m12 = R; a.m21 = R + n1; a.hist = R + n1 + n2; a.nmatches = a.hist + 30;
-    a.th = th; a.ratio = nnratio; a.checkOri = check_orientation;
-    launch_search_bow(a, R, n1 + n2, a.hist, 31, s);
+    int* Z = R + nMinus;
+    size_t off = 0;
+    for (int p = 0; p < npairs; p++) {
+        const DevSide& a1 = dev[sideOf[2 * p]]; const DevSide& a2 = dev[sideOf[2 * p + 1]];
+        BowArgs a{};
+        a.n1 = s1[p].n; a.n2 = s2[p].n; a.nnodes1 = s1[p].nnodes; a.nnodes2 = s2[p].nnodes;
+        a.desc1 = a1.desc; a.angle1 = a1.angle; a.valid1 = a1.valid; a.node_id1 = a1.node_id; a.node_start1 = a1.node_start; a.indices1 = a1.indices;
+        a.desc2 = a2.desc; a.angle2 = a2.angle; a.valid2 = a2.valid; a.node_id2 = a2.node_id; a.node_start2 = a2.node_start; a.indices2 = a2.indices;
+        a.th = th; a.ratio = nnratio; a.checkOri = check_orientation;
+        a.m12 = R + off; a.m21 = R + off + a.n1; off += (size_t)a.n1 + a.n2;
+        a.hist = Z + 31 * p; a.nmatches = a.hist + 30;
+        h_pairs[p] = a;
+    }
+    CU(cudaMemcpyAsync(m->scratch[0].p, m->stage.p, U.off, cudaMemcpyHostToDevice, s));
+    launch_search_bow(d_pairs, npairs, maxNodes1, maxN1, check_orientation != 0, R, (int)nMinus, Z, 31 * npairs, s);
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(m->result.p, R, rInts * 4, cudaMemcpyDeviceToHost, s));
     CU(cudaStreamSynchronize(s));
     const int* hR = reinterpret_cast<const int*>(m->result.p);
-    if (matches12) std::memcpy(matches12, hR, sizeof(int) * n1);
-    if (matches21) std::memcpy(matches21, hR + n1, sizeof(int) * n2);
-    *nmatches = hR[n1 + n2 + 30];
+    off = 0;
+    for (int p = 0; p < npairs; p++) {
+        if (matches12 && matches12[p]) std::memcpy(matches12[p], hR + off, sizeof(int) * s1[p].n);
+        if (matches21 && matches21[p]) std::memcpy(matches21[p], hR + off + s1[p].n, sizeof(int) * s2[p].n);
+        off += (size_t)s1[p].n + s2[p].n;
+        nmatches[p] = hR[nMinus + 31 * p + 30];
+    }
     return ORBFE_OK;
+}
+
+int orbfe_search_bow(orbfe_matcher* m, const orbfe_bow_view* s1, const orbfe_bow_view* s2, int th, float nnratio,
+                     int check_orientation, int32_t* matches12, int32_t* matches21, int* nmatches) {
+    if (!m || !s1 || !s2 || !nmatches) return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_search_bow");
+    *nmatches = 0;
+    return orbfe_search_bow_batch(m, 1, s1, s2, th, nnratio, check_orientation, &matches12, &matches21, nmatches);
 }
 
 // Frame::ComputeImageBounds (src/Frame.cc:481-512)

@@ -52,10 +52,12 @@ __device__ __forceinline__ unsigned warp_min_u32(unsigned v) {
     return v;
 }
 
-__global__ void __launch_bounds__(BW_WARPS * 32) bow_match_kernel(const __grid_constant__ BowArgs a) {
+// grid = (node groups, pairs): pair p reads its own argument record
+__global__ void __launch_bounds__(BW_WARPS * 32) bow_match_kernel(const BowArgs* __restrict__ pairs) {
+    const BowArgs& a = pairs[blockIdx.y];
     const int lane = threadIdx.x & 31;
     const int node1 = blockIdx.x * BW_WARPS + (threadIdx.x >> 5);
-    if (node1 >= a.nnodes1) return;
+    if (node1 >= a.nnodes1 || a.nnodes2 == 0) return;
     // the same node on side 2 (std::map::lower_bound over ascending ids)
     const uint32_t id = a.node_id1[node1];
     int lo = 0, hi = a.nnodes2;
@@ -108,7 +110,8 @@ __global__ void __launch_bounds__(BW_WARPS * 32) bow_match_kernel(const __grid_c
     }
 }
 
-__global__ void __launch_bounds__(256) bow_rotation_kernel(const __grid_constant__ BowArgs a) {
+__global__ void __launch_bounds__(256) bow_rotation_kernel(const BowArgs* __restrict__ pairs) {
+    const BowArgs& a = pairs[blockIdx.y];
     __shared__ int ind[3];
     if (threadIdx.x == 0) three_maxima30(a.hist, ind[0], ind[1], ind[2]);
     __syncthreads();
@@ -122,7 +125,7 @@ __global__ void __launch_bounds__(256) bow_rotation_kernel(const __grid_constant
     atomicSub(a.nmatches, 1);
 }
 
-// m12 / m21 to -1, histogram and match count to 0 (they sit in one block: see api_matcher.cu)
+// every pair's m12 / m21 to -1, histograms and match counts to 0 (two runs of one block: see api_matcher.cu)
 __global__ void __launch_bounds__(256) bow_init_kernel(int* minus1, int nminus1, int* zero, int nzero) {
     const int stride = gridDim.x * blockDim.x, t = blockIdx.x * blockDim.x + threadIdx.x;
     for (int i = t; i < nminus1; i += stride) minus1[i] = -1;
@@ -131,13 +134,16 @@ __global__ void __launch_bounds__(256) bow_init_kernel(int* minus1, int nminus1,
 
 }  // namespace
 
-int launch_search_bow(const BowArgs& a, int* minus1, int nminus1, int* zero, int nzero, cudaStream_t st) {
-    bow_init_kernel<<<(nminus1 + 1023) / 1024 > 0 ? (nminus1 + 1023) / 1024 : 1, 256, 0, st>>>(minus1, nminus1, zero, nzero);
+int launch_search_bow(const BowArgs* d_pairs, int npairs, int max_nodes1, int max_n1, bool check_ori, int* minus1,
+                      int nminus1, int* zero, int nzero, cudaStream_t st) {
+    const int work = nminus1 > nzero ? nminus1 : nzero;
+    const int ib = (work + 1023) / 1024;
+    bow_init_kernel<<<ib > 0 ? (ib < 1024 ? ib : 1024) : 1, 256, 0, st>>>(minus1, nminus1, zero, nzero);
     int launches = 1;
-    if (a.nnodes1 > 0 && a.nnodes2 > 0) {
-        bow_match_kernel<<<(a.nnodes1 + BW_WARPS - 1) / BW_WARPS, BW_WARPS * 32, 0, st>>>(a);
+    if (npairs > 0 && max_nodes1 > 0) {
+        bow_match_kernel<<<dim3((max_nodes1 + BW_WARPS - 1) / BW_WARPS, npairs), BW_WARPS * 32, 0, st>>>(d_pairs);
         launches++;
-        if (a.checkOri && a.n1 > 0) { bow_rotation_kernel<<<(a.n1 + 255) / 256, 256, 0, st>>>(a); launches++; }
+        if (check_ori && max_n1 > 0) { bow_rotation_kernel<<<dim3((max_n1 + 255) / 256, npairs), 256, 0, st>>>(d_pairs); launches++; }
     }
     return launches;
 }

@@ -101,8 +101,10 @@ struct BowArgs {
     int* hist;                   // [30]
     int* nmatches;
 };
-// minus1 / zero: the result block's "-1" part (m12, m21) and "0" part (histogram, count)
-int launch_search_bow(const BowArgs& a, int* minus1, int nminus1, int* zero, int nzero, cudaStream_t st);
+// d_pairs: npairs argument records in device memory; minus1 / zero: the result block's "-1" part
+// (every pair's m12, m21) and "0" part (every pair's histogram + count)
+int launch_search_bow(const BowArgs* d_pairs, int npairs, int max_nodes1, int max_n1, bool check_ori, int* minus1,
+                      int nminus1, int* zero, int nzero, cudaStream_t st);
 
 size_t search_init_scratch_bytes(int cap, int npairs);
 void search_init_carve(InitArgs& a, void* scratch, int npairs);

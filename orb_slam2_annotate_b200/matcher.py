@@ -246,6 +246,27 @@ class ORBmatcher:
                                        C.byref(n)), "orbfe_search_bow")
         return n.value, m12[:n1], m21[:n2]
 
+    def SearchByBoWBatch(self, sides1: list, sides2: list, keyframe_pair: bool = False):
+        """``SearchByBoW`` for every (sides1[p], sides2[p]) in one call; a BowSide object that appears in
+        several pairs is uploaded once (relocalisation: one frame against all candidate key frames).
+        -> list of (nmatches, matches12, matches21)"""
+        P = len(sides1)
+        assert len(sides2) == P
+        if P == 0:
+            return []
+        views = {}
+        v1 = (BowView * P)(*[views.setdefault(id(s), s.view()) for s in sides1])
+        v2 = (BowView * P)(*[views.setdefault(id(s), s.view()) for s in sides2])
+        m12 = [np.empty(max(len(s.desc), 1), np.int32) for s in sides1]
+        m21 = [np.empty(max(len(s.desc), 1), np.int32) for s in sides2]
+        p12 = (C.c_void_p * P)(*[a.ctypes.data for a in m12]); p21 = (C.c_void_p * P)(*[a.ctypes.data for a in m21])
+        nm = np.zeros(P, np.int32)
+        check(self._L.orbfe_search_bow_batch(self._h, P, C.cast(v1, C.c_void_p), C.cast(v2, C.c_void_p),
+                                             self.TH_LOW - 1 if keyframe_pair else self.TH_LOW, self.mfNNratio,
+                                             int(self.mbCheckOrientation), C.cast(p12, C.c_void_p), C.cast(p21, C.c_void_p),
+                                             nm.ctypes.data), "orbfe_search_bow_batch")
+        return [(int(nm[p]), m12[p][:len(sides1[p].desc)], m21[p][:len(sides2[p].desc)]) for p in range(P)]
+
     # --- Frame constructor epilogue for callers without a batched extractor handle
     def ComputeImageBounds(self, camera, cols: int, rows: int) -> np.ndarray:
         """Frame::ComputeImageBounds (src/Frame.cc:481-512) -> float32 (mnMinX, mnMaxX, mnMinY, mnMaxY)."""

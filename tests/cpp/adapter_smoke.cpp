@@ -114,7 +114,7 @@ int main(int argc, char** argv) {
         for (size_t k = 0; k < KF[i].mps.size(); k++) KF[i].mps[k] = k % 3 == 0 ? nullptr : (k % 7 == 0 ? &bad : &good);
         F[i].N = (int)F[i].mvKeys.size(); F[i].mFeatVec = KF[i].mFeatVec;
     }
-    ORB_SLAM2::ORBmatcher bow(0.75f, true);                          // Tracking.cc:871 / :1379
+    ORB_SLAM2::ORBmatcher bow(0.75f, true);                          // Tracking.cc:841 / :1484
     std::vector<MapPoint*> vpMatches, vpMatches12;
     const int nb1 = bow.SearchByBoW(&KF[0], F[1], vpMatches);
     const int nb2 = bow.SearchByBoW(&KF[0], &KF[1], vpMatches12);

@@ -212,3 +212,36 @@ def test_search_by_bow_degenerate(orbfe, oracle):
     bad.indices[0] = len(d2)
     with pytest.raises(orbfe.OrbfeError):
         mt.SearchByBoW(s1, bad)
+
+
+def test_search_by_bow_batch(orbfe, oracle):
+    """Relocalisation shape: one frame against several key frames in one call, plus key-frame pairs."""
+    fr = _frames(oracle, "mono", 7, 2000) + _frames(oracle, "mono", 5, 1000)
+    rng = np.random.default_rng(77)
+    sides, osides = [], []
+    for (k, d, _, _) in fr:
+        fv = _feat_vec(d, k["octave"], 4, rng, 0.05)
+        valid = (rng.random(len(k)) < 0.85).astype(np.uint8)
+        sides.append((orbfe.BowSide(d, k["angle"], fv, valid), orbfe.BowSide(d, k["angle"], fv)))
+        osides.append((oracle.bow_view(d, k["angle"], fv, valid), oracle.bow_view(d, k["angle"], fv)))
+    mt = orbfe.ORBmatcher(0.75, True)
+    F = 1                                                   # the "current frame": same object in every pair
+    kfs = [i for i in range(len(fr)) if i != F]
+    res = mt.SearchByBoWBatch([sides[i][0] for i in kfs], [sides[F][1]] * len(kfs))
+    assert len(res) == len(kfs)
+    for i, (n, m12, m21) in zip(kfs, res):
+        no, o12, o21 = oracle.search_by_bow(osides[i][0], osides[F][1], 50, 0.75, True)
+        assert n == no and np.array_equal(m12, o12) and np.array_equal(m21, o21)
+    assert sum(r[0] for r in res) > 100
+    # key-frame pairs of different sizes in one batch, with an empty pair in the middle
+    empty = orbfe.BowSide(np.zeros((0, 32), np.uint8), np.zeros(0, np.float32), {})
+    a = [sides[0][0], empty, sides[3][0], sides[2][0]]
+    b = [sides[2][0], sides[1][0], sides[4][0], sides[2][0]]
+    res = mt.SearchByBoWBatch(a, b, keyframe_pair=True)
+    for (i, j), (n, m12, m21) in zip([(0, 2), (None, 1), (3, 4), (2, 2)], res):
+        if i is None:
+            assert n == 0 and len(m12) == 0 and (m21 == -1).all()
+            continue
+        no, o12, o21 = oracle.search_by_bow(osides[i][0], osides[j][0], 49, 0.75, True)
+        assert n == no and np.array_equal(m12, o12) and np.array_equal(m21, o21)
+    assert mt.SearchByBoWBatch([], []) == []
