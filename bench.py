@@ -133,7 +133,16 @@ def guided_search_timings(frame_img):
     mtb = orbfe.ORBmatcher(0.75, True)
     bow_matches = mtb.SearchByBoW(b1, b2)[0]
 
+    # MapPoint::ComputeDistinctiveDescriptors for 20 000 map points with 3..20 observations each
+    sizes = rng.integers(3, 21, 20000).astype(np.int32)
+    dstart = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    dobs = d[rng.integers(0, n, int(dstart[-1]))] ^ (rng.random((int(dstart[-1]), 32)) < 0.02).astype(np.uint8)
+    mtd = orbfe.ORBmatcher()
+
     return {
+        "distinctive_descriptors": {"map_points": len(sizes), "observations": int(dstart[-1]),
+                                    "gpu_ms_per_call": med(lambda: mtd.ComputeDistinctiveDescriptors(dobs, dstart)),
+                                    "cpu_ms_per_call": med(lambda: O.distinctive_descriptors(dobs, dstart))},
         "search_by_bow": {"features": n, "nodes": len(fv1), "matches": bow_matches,
                           "gpu_ms_per_call": med(lambda: mtb.SearchByBoW(b1, b2)),
                           "cpu_ms_per_call": med(lambda: O.search_by_bow(o1, o2, 50, 0.75, True)),

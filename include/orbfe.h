@@ -337,6 +337,15 @@ int orbfe_search_bow_batch(orbfe_matcher* m, int npairs, const orbfe_bow_view* s
                            const orbfe_bow_view* s2, int th, float nnratio, int check_orientation,
                            int32_t* const* matches12, int32_t* const* matches21, int* nmatches);
 
+/* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:266-334) for npoints map points in
+ * one call (HOST pointers): point p owns the descriptor rows desc[32*start[p] .. 32*start[p+1])
+ * — the rows the reference gathers from the point's observations, in map order, bad key frames
+ * left out (:283-289).  best[p] = index inside the point's own set of the descriptor with the
+ * least median Hamming distance to the set (median = element (N-1)/2 of the sorted row, the
+ * first row wins ties), -1 for an empty set; the caller copies that row into mDescriptor. */
+int orbfe_distinctive_descriptors(orbfe_matcher* m, const uint8_t* desc, const int32_t* start,
+                                  int npoints, int32_t* best);
+
 /* Pyramid of one extractor call, HOST pointers (interior pixels of mvImagePyramid[l]). */
 typedef struct {
     int32_t nlevels;

@@ -100,6 +100,7 @@ def lib():
         L.orc_search_by_projection.argtypes = [C.POINTER(FrameView), C.POINTER(MapPointsView), C.c_float, C.c_float, C.c_void_p, C.c_void_p]
         L.orc_compute_stereo_matches.argtypes = [C.POINTER(FrameView), C.POINTER(FrameView), C.POINTER(PyramidView), C.POINTER(PyramidView), C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
         L.orc_search_by_bow.argtypes = [C.POINTER(BowView), C.POINTER(BowView), C.c_int, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
+        L.orc_distinctive_descriptors.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orc_undistort_points.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_image_bounds.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.orc_knn2.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -329,6 +330,14 @@ def search_by_bow(s1, s2, th: int, nnratio: float, check_ori: bool):
     m12 = np.empty(max(s1[0].n, 1), np.int32); m21 = np.empty(max(s2[0].n, 1), np.int32)
     nm = lib().orc_search_by_bow(C.byref(s1[0]), C.byref(s2[0]), th, nnratio, int(check_ori), m12.ctypes.data, m21.ctypes.data)
     return nm, m12[:s1[0].n], m21[:s2[0].n]
+
+
+def distinctive_descriptors(desc: np.ndarray, start: np.ndarray) -> np.ndarray:
+    """MapPoint::ComputeDistinctiveDescriptors for a batch: desc u8[total,32], start i32[npoints+1]."""
+    desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32); start = np.ascontiguousarray(start, np.int32)
+    best = np.empty(max(len(start) - 1, 1), np.int32)
+    lib().orc_distinctive_descriptors(desc.ctypes.data, start.ctypes.data, len(start) - 1, best.ctypes.data)
+    return best[:len(start) - 1]
 
 
 def undistort_points(xy: np.ndarray, cam, dist) -> np.ndarray:

@@ -154,6 +154,9 @@ typedef struct {
 } orc_bow_view;
 int   orc_search_by_bow(const orc_bow_view* s1, const orc_bow_view* s2, int th, float nnratio,
                         int check_orientation, int* m12, int* m21);
+/* MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:266-334) for npoints points: point p owns
+ * descriptor rows [start[p], start[p+1]); best[p] = index inside its set, -1 for an empty set. */
+void  orc_distinctive_descriptors(const uint8_t* desc, const int* start, int npoints, int* best);
 /* Frame constructor epilogue (orc_frame.cpp).  cam = {fx, fy, cx, cy}; dist = {k1, k2, p1, p2, k3}.
  * Frame::UndistortKeyPoints (Frame.cc:443-475): xy / out are n (x, y) pairs. */
 void  orc_undistort_points(const float* xy, int n, const float cam[4], const float dist[5], float* out);

@@ -125,6 +125,7 @@ SIGNATURES = {
     "orbfe_search_frame_points_resident": (_i, [_vp, C.POINTER(DeviceFrameView), C.POINTER(FramePointsView), _i, _vp, _vp, _ip]),
     "orbfe_search_bow": (_i, [_vp, C.POINTER(BowView), C.POINTER(BowView), _i, _f, _i, _vp, _vp, _ip]),
     "orbfe_search_bow_batch": (_i, [_vp, _i, _vp, _vp, _i, _f, _i, _vp, _vp, _vp]),
+    "orbfe_distinctive_descriptors": (_i, [_vp, _vp, _vp, _i, _vp]),
     "orbfe_stereo_match": (_i, [_vp, C.POINTER(FrameView), C.POINTER(FrameView), C.POINTER(PyramidView),
                                 C.POINTER(PyramidView), _vp, _f, _f, _vp, _vp]),
 }

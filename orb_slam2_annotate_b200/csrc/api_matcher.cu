@@ -564,6 +564,39 @@ int orbfe_search_bow(orbfe_matcher* m, const orbfe_bow_view* s1, const orbfe_bow
     return orbfe_search_bow_batch(m, 1, s1, s2, th, nnratio, check_orientation, &matches12, &matches21, nmatches);
 }
 
+// MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:266-334) for a batch of map points
+int orbfe_distinctive_descriptors(orbfe_matcher* m, const uint8_t* desc, const int32_t* start, int npoints,
+                                  int32_t* best) {
+    if (!m || npoints < 0 || (npoints && (!start || !best))) return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_distinctive_descriptors");
+    if (npoints == 0) return ORBFE_OK;
+    if (start[0] != 0) return fail(ORBFE_ERR_ARG, "start[0] must be 0");
+    for (int p = 0; p < npoints; p++) {
+        if (start[p + 1] < start[p]) return fail(ORBFE_ERR_ARG, "start must not decrease");
+        if (start[p + 1] - start[p] > 65535) return fail(ORBFE_ERR_CAPACITY, "more than 65535 observations of one map point");
+    }
+    const size_t total = (size_t)start[npoints];
+    if (total && !desc) return fail(ORBFE_ERR_ARG, "desc is NULL");
+    CU(cudaSetDevice(m->device));
+    cudaStream_t s = m->stream;
+    int rc;
+    const size_t upBytes = padded(total * 32) + padded((size_t)(npoints + 1) * 4);
+    if ((rc = m->scratch[0].ensure(upBytes))) return rc;
+    if ((rc = m->stage.ensure(upBytes))) return rc;
+    if ((rc = m->scratch[2].ensure((size_t)npoints * 4))) return rc;
+    if ((rc = m->result.ensure((size_t)npoints * 4))) return rc;
+    Upload U{m->stage.p, m->scratch[0].p, 0, upBytes};
+    const uint8_t* d_desc = U.put<uint8_t>(desc, total * 32);
+    const int* d_start = U.put<int>(start, (size_t)npoints + 1);
+    CU(cudaMemcpyAsync(m->scratch[0].p, m->stage.p, U.off, cudaMemcpyHostToDevice, s));
+    int* d_best = reinterpret_cast<int*>(m->scratch[2].p);
+    launch_distinctive(d_desc, d_start, npoints, d_best, s);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(m->result.p, d_best, (size_t)npoints * 4, cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    std::memcpy(best, m->result.p, (size_t)npoints * 4);
+    return ORBFE_OK;
+}
+
 // Frame::ComputeImageBounds (src/Frame.cc:481-512)
 int orbfe_image_bounds(orbfe_matcher* m, const orbfe_camera* cam, int cols, int rows, float bounds[4]) {
     if (!m || !cam || !bounds || cols <= 0 || rows <= 0 || !(cam->fx != 0.0f) || !(cam->fy != 0.0f))

@@ -106,6 +106,9 @@ struct BowArgs {
 int launch_search_bow(const BowArgs* d_pairs, int npairs, int max_nodes1, int max_n1, bool check_ori, int* minus1,
                       int nminus1, int* zero, int nzero, cudaStream_t st);
 
+// MapPoint::ComputeDistinctiveDescriptors for a batch: point p owns rows [start[p], start[p+1]) of desc
+int launch_distinctive(const uint8_t* d_desc, const int* d_start, int npoints, int* d_best, cudaStream_t st);
+
 size_t search_init_scratch_bytes(int cap, int npairs);
 void search_init_carve(InitArgs& a, void* scratch, int npairs);
 int launch_search_init(const InitArgs& a, int npairs, cudaStream_t st);

@@ -267,6 +267,18 @@ class ORBmatcher:
                                              nm.ctypes.data), "orbfe_search_bow_batch")
         return [(int(nm[p]), m12[p][:len(sides1[p].desc)], m21[p][:len(sides2[p].desc)]) for p in range(P)]
 
+    def ComputeDistinctiveDescriptors(self, descriptors: np.ndarray, start: np.ndarray) -> np.ndarray:
+        """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:266-334) for a batch of map points:
+        point p owns ``descriptors[start[p]:start[p+1]]``.  -> int32[npoints]: index inside each set of
+        the descriptor with the least median distance (-1 for an empty set)."""
+        d = np.ascontiguousarray(descriptors, np.uint8).reshape(-1, 32)
+        st = np.ascontiguousarray(start, np.int32)
+        npts = len(st) - 1
+        best = np.empty(max(npts, 1), np.int32)
+        check(self._L.orbfe_distinctive_descriptors(self._h, d.ctypes.data, st.ctypes.data, npts, best.ctypes.data),
+              "orbfe_distinctive_descriptors")
+        return best[:npts]
+
     # --- Frame constructor epilogue for callers without a batched extractor handle
     def ComputeImageBounds(self, camera, cols: int, rows: int) -> np.ndarray:
         """Frame::ComputeImageBounds (src/Frame.cc:481-512) -> float32 (mnMinX, mnMaxX, mnMinY, mnMaxY)."""

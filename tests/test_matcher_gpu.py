@@ -245,3 +245,28 @@ def test_search_by_bow_batch(orbfe, oracle):
         no, o12, o21 = oracle.search_by_bow(osides[i][0], osides[j][0], 49, 0.75, True)
         assert n == no and np.array_equal(m12, o12) and np.array_equal(m21, o21)
     assert mt.SearchByBoWBatch([], []) == []
+
+
+def test_distinctive_descriptors(orbfe, oracle):
+    (k, d, _, _) = _frames(oracle, "mono", 7, 2000)[0]
+    rng = np.random.default_rng(8)
+    # map points with 0..40 observations (a few with hundreds): noisy copies of one descriptor each, so that medians
+    # collide and the first-wins rule matters
+    sizes = np.concatenate([rng.integers(0, 41, 3000), [150, 333, 1, 2, 0, 64, 33, 32]]).astype(np.int32)
+    start = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    rows = []
+    for n in sizes:
+        base = d[rng.integers(0, len(d))]
+        obs = np.repeat(base[None], n, 0)
+        flips = rng.integers(0, 256, (n, 6))
+        for j in range(6):
+            obs[np.arange(n), flips[:, j] >> 3] ^= (1 << (flips[:, j] & 7)).astype(np.uint8)
+        rows.append(obs)
+    desc = np.concatenate(rows)
+    got = orbfe.ORBmatcher().ComputeDistinctiveDescriptors(desc, start)
+    want = oracle.distinctive_descriptors(desc, start)
+    assert np.array_equal(got, want)
+    assert (got[sizes == 0] == -1).all() and (got[sizes > 0] >= 0).all()
+    assert len(orbfe.ORBmatcher().ComputeDistinctiveDescriptors(np.zeros((0, 32), np.uint8), [0])) == 0
+    with pytest.raises(orbfe.OrbfeError):
+        orbfe.ORBmatcher().ComputeDistinctiveDescriptors(desc, [0, 5, 3])

@@ -217,3 +217,20 @@ def test_search_by_bow_kat(oracle):
     assert n == 11 and m12.tolist() == list(range(11)) + [-1] and m21.tolist() == list(range(11)) + [-1]
     n, m12, m21 = oracle.search_by_bow(s1, s2, 50, 0.7, False)
     assert n == 12 and m12.tolist() == list(range(12))
+
+
+def test_distinctive_descriptors_kat(oracle):
+    """MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:266-334)."""
+    # three descriptors at 0, 10 and 30 bits: rows sorted = [0,10,30], [0,10,20], [0,20,30]; medians (index 1)
+    # 10, 10, 20 -> the first of the two least medians wins (strict '<', :317)
+    d = np.stack([_bits(0), _bits(10), _bits(30)])
+    assert oracle.distinctive_descriptors(d, [0, 3]).tolist() == [0]
+    # even N takes the lower middle: index (int)(0.5*(4-1)) = 1.  Rows of {0,4,6,40}: [0,4,6,40] -> 4,
+    # [0,2,4,36] -> 2, [0,2,6,34] -> 2, [0,34,36,40] -> 34: descriptor 1 (first with median 2)
+    d4 = np.stack([_bits(0), _bits(4), _bits(6), _bits(40)])
+    assert oracle.distinctive_descriptors(d4, [0, 4]).tolist() == [1]
+    # a single observation, an empty set, and several points in one batch
+    both = np.concatenate([d, d4, d[:1]])
+    assert oracle.distinctive_descriptors(both, [0, 3, 7, 7, 8]).tolist() == [0, 1, -1, 0]
+    # two observations: medians are the zero diagonals -> the first
+    assert oracle.distinctive_descriptors(d[1:], [0, 2]).tolist() == [0]
