@@ -305,6 +305,95 @@ int orbfe_search_frame_points_resident(orbfe_matcher* m, const orbfe_device_fram
                                        const uint8_t* kp_occupied, int32_t* match_for_kp,
                                        int* nmatches);
 
+/* The same first-owner search with the accepted best distance as an argument; it serves the two other
+ * SearchByProjection overloads that assign map points to keypoints as they go:
+ *   SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, sAlreadyFound, th, ORBdist)
+ *     (src/ORBmatcher.cc:1641-1770, relocalisation): point i = pKF's i-th map point; valid folds
+ *     pMP != NULL, !isBad, !sAlreadyFound.count, the image-bounds and distance gates (:1663-1698);
+ *     radius = th * mvScaleFactors[nPredictedLevel], min_level / max_level = nPredictedLevel -/+ 1
+ *     (:1703-1705); angle = pKF->mvKeysUn[i].angle; observations = 1 for every point and
+ *     kp_occupied = (CurrentFrame.mvpMapPoints[i2] != NULL), because any held point blocks (:1720);
+ *     max_dist = ORBdist.
+ *   SearchByProjection(KeyFrame* pKF, Scw, vpPoints, vpMatched, th) (:335-451, loop closing): point
+ *     i = vpPoints[i]; valid folds !isBad, !spAlreadyFound.count and the gates of :361-402;
+ *     min_level = nPredictedLevel - 1, max_level = nPredictedLevel (:426); kp_occupied =
+ *     (vpMatched[idx] != NULL) (:421); observations = 1; max_dist = TH_LOW (:440); no orientation
+ *     check, f->uright = NULL.  match_for_kp[idx] = i where vpMatched[idx] = vpPoints[i]. */
+int orbfe_search_projected_points(orbfe_matcher* m, const orbfe_frame_view* f,
+                                  const orbfe_framepoints_view* pts, int max_dist,
+                                  int check_orientation, const uint8_t* kp_occupied,
+                                  int32_t* match_for_kp, int* nmatches);
+int orbfe_search_projected_points_resident(orbfe_matcher* m, const orbfe_device_frame_view* f,
+                                           const orbfe_framepoints_view* pts, int max_dist,
+                                           int check_orientation, const uint8_t* kp_occupied,
+                                           int32_t* match_for_kp, int* nmatches);
+
+/* Map points projected into a key frame by the caller, for the searches in which every point looks
+ * for its best keypoint on its own (HOST arrays of length n):
+ *   valid    every gate in front of the candidate loop passed (isBad / IsInKeyFrame / depth > 0 /
+ *            IsInImage / distance invariance / viewing angle)
+ *   u, v     projection;  ur = u - bf*invz (read only with inv_level_sigma2 and a frame with uright)
+ *   radius   th * pKF->mvScaleFactors[nPredictedLevel];  level = nPredictedLevel: candidates are
+ *            the keypoints of KeyFrame::GetFeaturesInArea(u, v, radius) (src/KeyFrame.cc:611-650)
+ *            with octave in [level-1, level]
+ *   desc     pMP->GetDescriptor(), n x 32 */
+typedef struct {
+    int32_t n;
+    const uint8_t* valid;
+    const float* u;
+    const float* v;
+    const float* ur;
+    const float* radius;
+    const int32_t* level;
+    const uint8_t* desc;
+} orbfe_windowpoints_view;
+/* The search of ORBmatcher::Fuse(KeyFrame*, vpMapPoints, th) (src/ORBmatcher.cc:940-1090; pass
+ * inv_level_sigma2 = pKF->mvInvLevelSigma2, f->nlevels floats, to enable its reprojection gate: e2 *
+ * invSigma2 > 7.8 with a right coordinate, > 5.99 without, :1020-1041) and of Fuse(KeyFrame*, Scw,
+ * vpPoints, th, vpReplacePoint) (:1100-1237; inv_level_sigma2 = NULL).  best_dist[i] = smallest
+ * distance among the candidates (256: none; may be NULL), best_idx[i] = its keypoint when best_dist
+ * <= max_dist (TH_LOW in both overloads), else -1.  What happens to the pair — Replace, AddObservation
+ * / AddMapPoint, vpReplacePoint — is map mutation and stays with the caller, in point order. */
+int orbfe_search_window_best(orbfe_matcher* m, const orbfe_frame_view* f,
+                             const orbfe_windowpoints_view* pts, const float* inv_level_sigma2,
+                             int max_dist, int32_t* best_idx, int32_t* best_dist);
+int orbfe_search_window_best_resident(orbfe_matcher* m, const orbfe_device_frame_view* f,
+                                      const orbfe_windowpoints_view* pts,
+                                      const float* inv_level_sigma2, int max_dist,
+                                      int32_t* best_idx, int32_t* best_dist);
+/* ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1251-1477).  pts1[i1] = map point of key frame 1's
+ * keypoint i1 projected into key frame 2 (pts1->n == f1->n; valid folds pMP != NULL,
+ * !vbAlreadyMatched1, !isBad and the gates of :1300-1326), pts2 the other way round.  Both searches
+ * accept best distance <= max_dist (TH_HIGH); matches12[i1] = idx2 where the two agree (:1446-1460),
+ * else -1; *nfound = the reference's return value. */
+int orbfe_search_by_sim3(orbfe_matcher* m, const orbfe_frame_view* f1, const orbfe_frame_view* f2,
+                         const orbfe_windowpoints_view* pts1, const orbfe_windowpoints_view* pts2,
+                         int max_dist, int32_t* matches12, int* nfound);
+
+/* One key frame of ORBmatcher::SearchForTriangulation (HOST pointers): mvKeysUn, mDescriptors,
+ * has_mappoint[i] = (GetMapPoint(i) != NULL), mvuRight (NULL = monocular, all -1) and mFeatVec
+ * flattened in map order as in orbfe_bow_view. */
+typedef struct {
+    int32_t n;
+    const orbfe_keypoint* kps;
+    const uint8_t* desc;
+    const uint8_t* has_mappoint;
+    const float* uright;
+    int32_t nnodes;
+    const uint32_t* node_id;
+    const int32_t* node_start;
+    const uint32_t* indices;
+} orbfe_tri_side;
+/* SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) (src/ORBmatcher.cc:754-928).
+ * F12 row-major 3x3; (ex, ey) = epipole of key frame 1's centre in key frame 2 (:762-768, computed
+ * by the caller); scale_factors2 / level_sigma2_2 = pKF2->mvScaleFactors / mvLevelSigma2 (nlevels2
+ * floats).  matches12[s1->n]: index in key frame 2 or -1 — vMatchedPairs is its list of (i, >= 0)
+ * entries in ascending i (:918-925); *nmatches = the reference's return value. */
+int orbfe_search_triangulation(orbfe_matcher* m, const orbfe_tri_side* s1, const orbfe_tri_side* s2,
+                               const float F12[9], float ex, float ey, const float* scale_factors2,
+                               const float* level_sigma2_2, int nlevels2, int only_stereo,
+                               int check_orientation, int32_t* matches12, int* nmatches);
+
 /* One side of ORBmatcher::SearchByBoW (HOST pointers): descriptors, the keypoint angles the
  * rotation check reads, "holds a live map point" flags and the side's DBoW2::FeatureVector
  * (std::map<NodeId, std::vector<unsigned int>>) flattened in map order. */

@@ -55,6 +55,18 @@ class BowView(C.Structure):
                 ("nnodes", C.c_int), ("node_id", C.c_void_p), ("node_start", C.c_void_p), ("indices", C.c_void_p)]
 
 
+class ProjPointsView(C.Structure):
+    _fields_ = [("n", C.c_int), ("valid", C.c_void_p), ("u", C.c_void_p), ("v", C.c_void_p),
+                ("ur", C.c_void_p), ("radius", C.c_void_p), ("level", C.c_void_p), ("angle", C.c_void_p),
+                ("desc", C.c_void_p)]
+
+
+class TriSide(C.Structure):
+    _fields_ = [("n", C.c_int), ("kps", C.c_void_p), ("desc", C.c_void_p), ("has_mappoint", C.c_void_p),
+                ("uright", C.c_void_p), ("nnodes", C.c_int), ("node_id", C.c_void_p), ("node_start", C.c_void_p),
+                ("indices", C.c_void_p)]
+
+
 class PyramidView(C.Structure):
     _fields_ = [("nlevels", C.c_int), ("data", C.c_void_p), ("w", C.c_void_p), ("h", C.c_void_p),
                 ("stride", C.c_void_p)]
@@ -100,6 +112,13 @@ def lib():
         L.orc_search_by_projection.argtypes = [C.POINTER(FrameView), C.POINTER(MapPointsView), C.c_float, C.c_float, C.c_void_p, C.c_void_p]
         L.orc_compute_stereo_matches.argtypes = [C.POINTER(FrameView), C.POINTER(FrameView), C.POINTER(PyramidView), C.POINTER(PyramidView), C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
         L.orc_search_by_bow.argtypes = [C.POINTER(BowView), C.POINTER(BowView), C.c_int, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
+        L.orc_sbp_frame_keyframe.argtypes = [C.POINTER(FrameView), C.POINTER(ProjPointsView), C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        L.orc_sbp_keyframe_sim3.argtypes = [C.POINTER(FrameView), C.POINTER(ProjPointsView), C.c_void_p, C.c_void_p]
+        L.orc_fuse_search.argtypes = [C.POINTER(FrameView), C.POINTER(ProjPointsView), C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_fuse_search.restype = None
+        L.orc_search_by_sim3.argtypes = [C.POINTER(FrameView), C.POINTER(FrameView), C.POINTER(ProjPointsView), C.POINTER(ProjPointsView), C.c_void_p]
+        L.orc_search_for_triangulation.argtypes = [C.POINTER(TriSide), C.POINTER(TriSide), C.c_void_p, C.c_float, C.c_float,
+                                                   C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.orc_distinctive_descriptors.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orc_undistort_points.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_image_bounds.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
@@ -330,6 +349,84 @@ def search_by_bow(s1, s2, th: int, nnratio: float, check_ori: bool):
     m12 = np.empty(max(s1[0].n, 1), np.int32); m21 = np.empty(max(s2[0].n, 1), np.int32)
     nm = lib().orc_search_by_bow(C.byref(s1[0]), C.byref(s2[0]), th, nnratio, int(check_ori), m12.ctypes.data, m21.ctypes.data)
     return nm, m12[:s1[0].n], m21[:s2[0].n]
+
+
+PROJ_POINT_FIELDS = dict(valid=np.uint8, u=np.float32, v=np.float32, ur=np.float32, radius=np.float32, level=np.int32,
+                         angle=np.float32, desc=np.uint8)
+
+
+def proj_points_view(points: dict):
+    """points: dict of arrays valid u8, u / v / radius f32, level i32, desc u8[n,32]; ur and angle are
+    optional (zeros).  -> (ProjPointsView, keepalive)"""
+    n = len(points["u"])
+    keep = {}
+    for k, t in PROJ_POINT_FIELDS.items():
+        keep[k] = np.ascontiguousarray(points[k], t) if k in points and points[k] is not None else np.zeros(max(n, 1), t)
+    return ProjPointsView(n, *[keep[k].ctypes.data for k in PROJ_POINT_FIELDS]), keep
+
+
+def search_by_projection_keyframe(f, points: dict, orb_dist: int, check_ori: bool, occupied: np.ndarray):
+    """SearchByProjection(Frame&, KeyFrame*, ...) — -> (nmatches, match_for_kp int32[n]: >=0 / -1 / -2)"""
+    v, keep = proj_points_view(points)
+    occ = np.ascontiguousarray(occupied, np.uint8)
+    out = np.full(max(f[0].n, 1), -1, np.int32)
+    nm = lib().orc_sbp_frame_keyframe(C.byref(f[0]), C.byref(v), int(orb_dist), int(check_ori), occ.ctypes.data, out.ctypes.data)
+    return nm, out[:f[0].n]
+
+
+def search_by_projection_sim3(f, points: dict, matched: np.ndarray):
+    """SearchByProjection(KeyFrame*, Scw, ...) — -> (nmatches, match_for_kp int32[n]: >=0 / -1)"""
+    v, keep = proj_points_view(points)
+    occ = np.ascontiguousarray(matched, np.uint8)
+    out = np.full(max(f[0].n, 1), -1, np.int32)
+    nm = lib().orc_sbp_keyframe_sim3(C.byref(f[0]), C.byref(v), occ.ctypes.data, out.ctypes.data)
+    return nm, out[:f[0].n]
+
+
+def fuse_search(f, points: dict, inv_level_sigma2=None):
+    """search part of the two Fuse overloads -> (best_idx int32[n], best_dist int32[n])"""
+    v, keep = proj_points_view(points)
+    n = v.n
+    bi = np.empty(max(n, 1), np.int32); bd = np.empty(max(n, 1), np.int32)
+    sig = None if inv_level_sigma2 is None else np.ascontiguousarray(inv_level_sigma2, np.float32)
+    lib().orc_fuse_search(C.byref(f[0]), C.byref(v), None if sig is None else sig.ctypes.data, bi.ctypes.data, bd.ctypes.data)
+    return bi[:n], bd[:n]
+
+
+def search_by_sim3(f1, f2, points1: dict, points2: dict):
+    """-> (nFound, matches12 int32[n1])"""
+    v1, k1 = proj_points_view(points1); v2, k2 = proj_points_view(points2)
+    m12 = np.empty(max(v1.n, 1), np.int32)
+    nf = lib().orc_search_by_sim3(C.byref(f1[0]), C.byref(f2[0]), C.byref(v1), C.byref(v2), m12.ctypes.data)
+    return nf, m12[:v1.n]
+
+
+def tri_side(kps, desc, has_mappoint, feat_vec: dict, uright=None):
+    """One key frame of SearchForTriangulation -> (TriSide, keepalive)"""
+    kps = np.ascontiguousarray(kps); desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    hm = np.ascontiguousarray(has_mappoint, np.uint8)
+    ids = np.array(sorted(feat_vec), np.uint32)
+    start = np.zeros(len(ids) + 1, np.int32)
+    for i, k in enumerate(ids):
+        start[i + 1] = start[i] + len(feat_vec[int(k)])
+    idx = np.array([j for k in ids for j in feat_vec[int(k)]], np.uint32)
+    keep = [kps, desc, hm, ids, start, idx]
+    v = TriSide(len(kps), kps.ctypes.data, desc.ctypes.data, hm.ctypes.data, None, len(ids), ids.ctypes.data,
+                start.ctypes.data, idx.ctypes.data)
+    if uright is not None:
+        ur = np.ascontiguousarray(uright, np.float32); keep.append(ur); v.uright = ur.ctypes.data
+    return v, keep
+
+
+def search_for_triangulation(s1, s2, F12, ex: float, ey: float, scale_factors2, level_sigma2_2, only_stereo=False,
+                             check_ori=True):
+    """-> (nmatches, matches12 int32[n1])"""
+    F = np.ascontiguousarray(F12, np.float32).reshape(9)
+    sf = np.ascontiguousarray(scale_factors2, np.float32); sg = np.ascontiguousarray(level_sigma2_2, np.float32)
+    m12 = np.empty(max(s1[0].n, 1), np.int32)
+    nm = lib().orc_search_for_triangulation(C.byref(s1[0]), C.byref(s2[0]), F.ctypes.data, float(ex), float(ey), sf.ctypes.data,
+                                            sg.ctypes.data, int(only_stereo), int(check_ori), m12.ctypes.data)
+    return nm, m12[:s1[0].n]
 
 
 def distinctive_descriptors(desc: np.ndarray, start: np.ndarray) -> np.ndarray:

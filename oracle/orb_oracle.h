@@ -154,6 +154,43 @@ typedef struct {
 } orc_bow_view;
 int   orc_search_by_bow(const orc_bow_view* s1, const orc_bow_view* s2, int th, float nnratio,
                         int check_orientation, int* m12, int* m21);
+/* ---- remaining guided searches (orc_guided.cpp) ----
+ * Map points projected into a frame / key frame by the caller: valid = every gate in front of the
+ * candidate loop passed, (u, v) projection, ur = u - bf*invz (only read by Fuse's reprojection gate),
+ * radius = th * mvScaleFactors[level], level = nPredictedLevel, angle = key frame keypoint angle (only
+ * read by the Frame/KeyFrame SearchByProjection), desc = pMP->GetDescriptor(). */
+typedef struct {
+    int n;
+    const uint8_t* valid;
+    const float* u; const float* v; const float* ur; const float* radius;
+    const int* level;
+    const float* angle;
+    const uint8_t* desc;
+} orc_projpoints_view;
+int   orc_sbp_frame_keyframe(const orc_frame_view* f, const orc_projpoints_view* pts, int orb_dist,
+                             int check_orientation, const uint8_t* kp_occupied, int* match_for_kp);
+int   orc_sbp_keyframe_sim3(const orc_frame_view* f, const orc_projpoints_view* pts,
+                            const uint8_t* kp_matched, int* match_for_kp);
+void  orc_fuse_search(const orc_frame_view* f, const orc_projpoints_view* pts,
+                      const float* inv_level_sigma2, int* best_idx, int* best_dist);
+int   orc_search_by_sim3(const orc_frame_view* f1, const orc_frame_view* f2, const orc_projpoints_view* pts1,
+                         const orc_projpoints_view* pts2, int* matches12);
+/* One key frame of SearchForTriangulation: mvKeysUn, descriptors, "GetMapPoint(idx) != NULL" flags,
+ * mvuRight (NULL = monocular: all -1) and mFeatVec flattened in map order. */
+typedef struct {
+    int n;
+    const orc_keypoint* kps;
+    const uint8_t* desc;
+    const uint8_t* has_mappoint;
+    const float* uright;
+    int nnodes;
+    const uint32_t* node_id;
+    const int* node_start;
+    const uint32_t* indices;
+} orc_tri_side;
+int   orc_search_for_triangulation(const orc_tri_side* s1, const orc_tri_side* s2, const float* F12, float ex,
+                                   float ey, const float* scale_factors2, const float* level_sigma2_2,
+                                   int only_stereo, int check_orientation, int* matches12);
 /* MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:266-334) for npoints points: point p owns
  * descriptor rows [start[p], start[p+1]); best[p] = index inside its set, -1 for an empty set. */
 void  orc_distinctive_descriptors(const uint8_t* desc, const int* start, int npoints, int* best);

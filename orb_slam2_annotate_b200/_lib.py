@@ -64,6 +64,17 @@ class BowView(C.Structure):
                 ("nnodes", C.c_int32), ("node_id", C.c_void_p), ("node_start", C.c_void_p), ("indices", C.c_void_p)]
 
 
+class WindowPointsView(C.Structure):
+    _fields_ = [("n", C.c_int32), ("valid", C.c_void_p), ("u", C.c_void_p), ("v", C.c_void_p),
+                ("ur", C.c_void_p), ("radius", C.c_void_p), ("level", C.c_void_p), ("desc", C.c_void_p)]
+
+
+class TriSideView(C.Structure):
+    _fields_ = [("n", C.c_int32), ("kps", C.c_void_p), ("desc", C.c_void_p), ("has_mappoint", C.c_void_p),
+                ("uright", C.c_void_p), ("nnodes", C.c_int32), ("node_id", C.c_void_p), ("node_start", C.c_void_p),
+                ("indices", C.c_void_p)]
+
+
 class PyramidView(C.Structure):
     _fields_ = [("nlevels", C.c_int32), ("data", C.c_void_p), ("width", C.c_void_p),
                 ("height", C.c_void_p), ("stride", C.c_void_p)]
@@ -123,6 +134,14 @@ SIGNATURES = {
     "orbfe_frame_assign": (_i, [_vp, C.POINTER(Camera), _vp, _vp, _i, _vp, _vp, _vp, _ip]),
     "orbfe_search_local_points_resident": (_i, [_vp, C.POINTER(DeviceFrameView), C.POINTER(MapPointsView), _f, _f, _vp, _vp, _ip]),
     "orbfe_search_frame_points_resident": (_i, [_vp, C.POINTER(DeviceFrameView), C.POINTER(FramePointsView), _i, _vp, _vp, _ip]),
+    "orbfe_search_projected_points": (_i, [_vp, C.POINTER(FrameView), C.POINTER(FramePointsView), _i, _i, _vp, _vp, _ip]),
+    "orbfe_search_projected_points_resident": (_i, [_vp, C.POINTER(DeviceFrameView), C.POINTER(FramePointsView), _i, _i, _vp, _vp, _ip]),
+    "orbfe_search_window_best": (_i, [_vp, C.POINTER(FrameView), C.POINTER(WindowPointsView), _vp, _i, _vp, _vp]),
+    "orbfe_search_window_best_resident": (_i, [_vp, C.POINTER(DeviceFrameView), C.POINTER(WindowPointsView), _vp, _i, _vp, _vp]),
+    "orbfe_search_by_sim3": (_i, [_vp, C.POINTER(FrameView), C.POINTER(FrameView), C.POINTER(WindowPointsView),
+                                  C.POINTER(WindowPointsView), _i, _vp, _ip]),
+    "orbfe_search_triangulation": (_i, [_vp, C.POINTER(TriSideView), C.POINTER(TriSideView), _vp, _f, _f, _vp, _vp, _i, _i, _i,
+                                        _vp, _ip]),
     "orbfe_search_bow": (_i, [_vp, C.POINTER(BowView), C.POINTER(BowView), _i, _f, _i, _vp, _vp, _ip]),
     "orbfe_search_bow_batch": (_i, [_vp, _i, _vp, _vp, _i, _f, _i, _vp, _vp, _vp]),
     "orbfe_distinctive_descriptors": (_i, [_vp, _vp, _vp, _i, _vp]),

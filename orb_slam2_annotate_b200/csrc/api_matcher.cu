@@ -263,7 +263,7 @@ struct Upload {
 int guided_search(orbfe_matcher* m, const orbfe_frame_view* f, const orbfe_device_frame_view* df,
                   const orbfe_mappoints_view* mps, const orbfe_framepoints_view* pts, float th, float nnratio,
                   int check_orientation, const uint8_t* occ_in, uint8_t* occ_out_host, int32_t* out_for_kp,
-                  int* nmatches) {
+                  int* nmatches, int max_dist = 100) {
     const int mode = pts ? 1 : 0;
     const int n = f->n, np = mode ? pts->n : mps->n, L = f->nlevels;
     CU(cudaSetDevice(m->device));
@@ -305,7 +305,7 @@ int guided_search(orbfe_matcher* m, const orbfe_frame_view* f, const orbfe_devic
         a.angle = U.put<float>(pts->angle, np);
         a.mpdesc = U.put<uint8_t>(pts->desc, (size_t)np * 32);
         a.obs = U.put<int>(pts->observations, np);
-        a.th = 1.0f; a.ratio = 1.0f; a.checkOri = check_orientation;
+        a.th = 1.0f; a.ratio = 1.0f; a.checkOri = check_orientation; a.max_dist = max_dist;
     }
     if (U.off > U.cap) return fail(ORBFE_ERR_CAPACITY, "internal: matcher staging overflow");
     CU(cudaMemcpyAsync(m->scratch[0].p, m->stage.p, U.off, cudaMemcpyHostToDevice, s));
@@ -411,7 +411,7 @@ int search_local_points_impl(orbfe_matcher* m, const orbfe_frame_view* f, const 
 // ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) — src/ORBmatcher.cc:1484-1630
 int search_frame_points_impl(orbfe_matcher* m, const orbfe_frame_view* f, const orbfe_device_frame_view* df,
                              const orbfe_framepoints_view* pts, int check_orientation, const uint8_t* kp_occupied,
-                             int32_t* match_for_kp, int* nmatches) {
+                             int32_t* match_for_kp, int* nmatches, int max_dist = 100 /* TH_HIGH, :1590 */) {
     if (!m || !pts || !nmatches) return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_search_frame_points");
     int rc;
     if ((rc = check_frame(f))) return rc;
@@ -421,7 +421,8 @@ int search_frame_points_impl(orbfe_matcher* m, const orbfe_frame_view* f, const 
     if (!kp_occupied || !match_for_kp || !pts->valid || !pts->u || !pts->v || !pts->radius || !pts->min_level ||
         !pts->max_level || !pts->angle || !pts->desc || !pts->observations || (f->uright && !pts->ur))
         return fail(ORBFE_ERR_ARG, "NULL array in frame / frame points view");
-    return guided_search(m, f, df, nullptr, pts, 1.0f, 1.0f, check_orientation, kp_occupied, nullptr, match_for_kp, nmatches);
+    if (max_dist < 0 || max_dist > 256) return fail(ORBFE_ERR_ARG, "max_dist outside 0..256");
+    return guided_search(m, f, df, nullptr, pts, 1.0f, 1.0f, check_orientation, kp_occupied, nullptr, match_for_kp, nmatches, max_dist);
 }
 
 }  // namespace
@@ -455,6 +456,254 @@ int orbfe_search_frame_points_resident(orbfe_matcher* m, const orbfe_device_fram
     if ((rc = check_device_frame(df))) return rc;
     const orbfe_frame_view f = host_side_of(df);
     return search_frame_points_impl(m, &f, df, pts, check_orientation, kp_occupied, match_for_kp, nmatches);
+}
+
+// SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) — src/ORBmatcher.cc:1641-1770 — and
+// SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th) — :335-451: the first-owner search of
+// orbfe_search_frame_points with the accepted distance as an argument
+int orbfe_search_projected_points(orbfe_matcher* m, const orbfe_frame_view* f, const orbfe_framepoints_view* pts,
+                                  int max_dist, int check_orientation, const uint8_t* kp_occupied,
+                                  int32_t* match_for_kp, int* nmatches) {
+    return search_frame_points_impl(m, f, nullptr, pts, check_orientation, kp_occupied, match_for_kp, nmatches, max_dist);
+}
+
+int orbfe_search_projected_points_resident(orbfe_matcher* m, const orbfe_device_frame_view* df,
+                                           const orbfe_framepoints_view* pts, int max_dist, int check_orientation,
+                                           const uint8_t* kp_occupied, int32_t* match_for_kp, int* nmatches) {
+    int rc;
+    if ((rc = check_device_frame(df))) return rc;
+    const orbfe_frame_view f = host_side_of(df);
+    return search_frame_points_impl(m, &f, df, pts, check_orientation, kp_occupied, match_for_kp, nmatches, max_dist);
+}
+
+}  // extern "C"
+
+namespace {
+
+int check_window_points(const orbfe_frame_view* f, const orbfe_windowpoints_view* pts, bool gate) {
+    if (!pts || pts->n < 0) return fail(ORBFE_ERR_ARG, "bad window points view");
+    if (pts->n && (!pts->valid || !pts->u || !pts->v || !pts->radius || !pts->level || !pts->desc))
+        return fail(ORBFE_ERR_ARG, "NULL array in window points view");
+    if (pts->n && gate && f->uright && !pts->ur) return fail(ORBFE_ERR_ARG, "window points need ur for a frame with uright");
+    return 0;
+}
+
+// frame side of a window search: uploaded (and its grid built) unless it is device resident
+struct FrameSide {
+    const orbfe_keypoint* kps; const uint8_t* desc; const float* uright; const int* cell_end; const unsigned short* items;
+};
+size_t frame_side_bytes(const orbfe_frame_view* f, const orbfe_device_frame_view* df) {
+    return df ? 0 : padded((size_t)f->n * sizeof(orbfe_keypoint)) + padded((size_t)f->n * 32) + padded((size_t)f->n * 4);
+}
+size_t window_points_bytes(int np) { return padded(np) + 4 * padded((size_t)np * 4) + padded((size_t)np * 4) + padded((size_t)np * 32); }
+
+void put_window_points(Upload& U, const orbfe_windowpoints_view* pts, bool with_ur, WindowArgs& a) {
+    const int np = pts->n;
+    a.np = np;
+    a.valid = U.put<uint8_t>(pts->valid, np);
+    a.u = U.put<float>(pts->u, np); a.v = U.put<float>(pts->v, np);
+    a.ur = with_ur ? U.put<float>(pts->ur, np) : nullptr;
+    a.radius = U.put<float>(pts->radius, np);
+    a.level = U.put<int>(pts->level, np);
+    a.pdesc = U.put<uint8_t>(pts->desc, (size_t)np * 32);
+}
+
+// Fuse (both overloads): every point's best keypoint inside its window
+int search_window_best_impl(orbfe_matcher* m, const orbfe_frame_view* f, const orbfe_device_frame_view* df,
+                            const orbfe_windowpoints_view* pts, const float* inv_level_sigma2, int max_dist,
+                            int32_t* best_idx, int32_t* best_dist) {
+    if (!m) return fail(ORBFE_ERR_ARG, "matcher is NULL");
+    int rc;
+    if ((rc = check_frame(f))) return rc;
+    if ((rc = check_window_points(f, pts, inv_level_sigma2 != nullptr))) return rc;
+    const int n = f->n, np = pts->n, L = f->nlevels;
+    if (np == 0) return ORBFE_OK;
+    if (!best_idx) return fail(ORBFE_ERR_ARG, "best_idx is NULL");
+    if (max_dist < 0 || max_dist > 256) return fail(ORBFE_ERR_ARG, "max_dist outside 0..256");
+    if (inv_level_sigma2 && L <= 0) return fail(ORBFE_ERR_ARG, "nlevels must be set with inv_level_sigma2");
+    if (n == 0) {
+        for (int i = 0; i < np; i++) { best_idx[i] = -1; if (best_dist) best_dist[i] = 256; }
+        return ORBFE_OK;
+    }
+    CU(cudaSetDevice(m->device));
+    cudaStream_t s = m->stream;
+    const size_t upBytes = frame_side_bytes(f, df) + window_points_bytes(np) + padded((size_t)std::max(L, 1) * 4);
+    if ((rc = m->scratch[0].ensure(upBytes))) return rc;
+    if ((rc = m->stage.ensure(upBytes))) return rc;
+    Upload U{m->stage.p, m->scratch[0].p, 0, upBytes};
+    WindowArgs a{};
+    if (df) { a.kps = df->d_kps; a.desc = df->d_desc; a.uright = df->d_uright; }
+    else {
+        a.kps = U.put<orbfe_keypoint>(f->kps, n);
+        a.desc = U.put<uint8_t>(f->desc, (size_t)n * 32);
+        a.uright = f->uright ? U.put<float>(f->uright, n) : nullptr;
+    }
+    a.n = n; a.grid = grid_of(f);
+    put_window_points(U, pts, inv_level_sigma2 && a.uright, a);
+    a.inv_sigma2 = inv_level_sigma2 ? U.put<float>(inv_level_sigma2, L) : nullptr;
+    a.max_dist = max_dist;
+    if (U.off > U.cap) return fail(ORBFE_ERR_CAPACITY, "internal: matcher staging overflow");
+    CU(cudaMemcpyAsync(m->scratch[0].p, m->stage.p, U.off, cudaMemcpyHostToDevice, s));
+    const size_t scBytes = padded(3072 * 4) + padded((size_t)n * 2) + padded((size_t)np * 8);
+    if ((rc = m->scratch[2].ensure(scBytes))) return rc;
+    if ((rc = m->result.ensure((size_t)np * 8))) return rc;
+    Arena A; A.base = m->scratch[2].p; A.cap = scBytes;
+    if (df) { a.cell_end = df->d_cell_end; a.items = df->d_items; }
+    else {
+        int* ce = A.take<int>(3072); unsigned short* it = A.take<unsigned short>(n);
+        launch_build_grid(a.kps, n, a.grid, ce, it, s);
+        a.cell_end = ce; a.items = it;
+    }
+    int* R = A.take<int>((size_t)np * 2);
+    a.best_idx = R; a.best_dist = R + np;
+    launch_window_best(a, s);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(m->result.p, R, (size_t)np * 8, cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    std::memcpy(best_idx, m->result.p, (size_t)np * 4);
+    if (best_dist) std::memcpy(best_dist, m->result.p + (size_t)np * 4, (size_t)np * 4);
+    return ORBFE_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int orbfe_search_window_best(orbfe_matcher* m, const orbfe_frame_view* f, const orbfe_windowpoints_view* pts,
+                             const float* inv_level_sigma2, int max_dist, int32_t* best_idx, int32_t* best_dist) {
+    return search_window_best_impl(m, f, nullptr, pts, inv_level_sigma2, max_dist, best_idx, best_dist);
+}
+
+int orbfe_search_window_best_resident(orbfe_matcher* m, const orbfe_device_frame_view* df,
+                                      const orbfe_windowpoints_view* pts, const float* inv_level_sigma2, int max_dist,
+                                      int32_t* best_idx, int32_t* best_dist) {
+    int rc;
+    if ((rc = check_device_frame(df))) return rc;
+    const orbfe_frame_view f = host_side_of(df);
+    return search_window_best_impl(m, &f, df, pts, inv_level_sigma2, max_dist, best_idx, best_dist);
+}
+
+// ORBmatcher::SearchBySim3 — src/ORBmatcher.cc:1251-1477: both directions and the agreement test in one go
+int orbfe_search_by_sim3(orbfe_matcher* m, const orbfe_frame_view* f1, const orbfe_frame_view* f2,
+                         const orbfe_windowpoints_view* pts1, const orbfe_windowpoints_view* pts2, int max_dist,
+                         int32_t* matches12, int* nfound) {
+    if (!m || !nfound) return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_search_by_sim3");
+    int rc;
+    if ((rc = check_frame(f1)) || (rc = check_frame(f2))) return rc;
+    if ((rc = check_window_points(f2, pts1, false)) || (rc = check_window_points(f1, pts2, false))) return rc;
+    if (pts1->n != f1->n || pts2->n != f2->n)
+        return fail(ORBFE_ERR_ARG, "SearchBySim3 takes one (possibly invalid) point per keypoint of each key frame");
+    if (max_dist < 0 || max_dist > 256) return fail(ORBFE_ERR_ARG, "max_dist outside 0..256");
+    *nfound = 0;
+    const int n1 = f1->n, n2 = f2->n;
+    if (n1 == 0) return ORBFE_OK;
+    if (!matches12) return fail(ORBFE_ERR_ARG, "matches12 is NULL");
+    if (n2 == 0) { for (int i = 0; i < n1; i++) matches12[i] = -1; return ORBFE_OK; }
+    CU(cudaSetDevice(m->device));
+    cudaStream_t s = m->stream;
+    const size_t upBytes = frame_side_bytes(f1, nullptr) + frame_side_bytes(f2, nullptr) + window_points_bytes(n1) + window_points_bytes(n2);
+    if ((rc = m->scratch[0].ensure(upBytes))) return rc;
+    if ((rc = m->stage.ensure(upBytes))) return rc;
+    Upload U{m->stage.p, m->scratch[0].p, 0, upBytes};
+    WindowArgs a12{}, a21{};        // a12: KF1's points searched in KF2; a21: KF2's points searched in KF1
+    a12.kps = U.put<orbfe_keypoint>(f2->kps, n2); a12.desc = U.put<uint8_t>(f2->desc, (size_t)n2 * 32); a12.n = n2; a12.grid = grid_of(f2);
+    a21.kps = U.put<orbfe_keypoint>(f1->kps, n1); a21.desc = U.put<uint8_t>(f1->desc, (size_t)n1 * 32); a21.n = n1; a21.grid = grid_of(f1);
+    put_window_points(U, pts1, false, a12);
+    put_window_points(U, pts2, false, a21);
+    a12.max_dist = a21.max_dist = max_dist;
+    if (U.off > U.cap) return fail(ORBFE_ERR_CAPACITY, "internal: matcher staging overflow");
+    CU(cudaMemcpyAsync(m->scratch[0].p, m->stage.p, U.off, cudaMemcpyHostToDevice, s));
+    const size_t rInts = (size_t)n1 + 1;
+    const size_t scBytes = 2 * padded(3072 * 4) + padded((size_t)n1 * 2) + padded((size_t)n2 * 2) + 2 * padded((size_t)n1 * 4) +
+                           2 * padded((size_t)n2 * 4) + padded(rInts * 4);
+    if ((rc = m->scratch[2].ensure(scBytes))) return rc;
+    if ((rc = m->result.ensure(rInts * 4))) return rc;
+    Arena A; A.base = m->scratch[2].p; A.cap = scBytes;
+    int* ce2 = A.take<int>(3072); unsigned short* it2 = A.take<unsigned short>(n2);
+    int* ce1 = A.take<int>(3072); unsigned short* it1 = A.take<unsigned short>(n1);
+    a12.best_idx = A.take<int>(n1); a12.best_dist = A.take<int>(n1);
+    a21.best_idx = A.take<int>(n2); a21.best_dist = A.take<int>(n2);
+    int* R = A.take<int>(rInts);
+    launch_build_grid(a12.kps, n2, a12.grid, ce2, it2, s); a12.cell_end = ce2; a12.items = it2;
+    launch_build_grid(a21.kps, n1, a21.grid, ce1, it1, s); a21.cell_end = ce1; a21.items = it1;
+    CU(cudaMemsetAsync(R + n1, 0, 4, s));
+    launch_window_best(a12, s);
+    launch_window_best(a21, s);
+    launch_sim3_agree(a12.best_idx, a21.best_idx, n1, n2, R, R + n1, s);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(m->result.p, R, rInts * 4, cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    std::memcpy(matches12, m->result.p, (size_t)n1 * 4);
+    *nfound = reinterpret_cast<const int*>(m->result.p)[n1];
+    return ORBFE_OK;
+}
+
+// ORBmatcher::SearchForTriangulation — src/ORBmatcher.cc:754-928
+int orbfe_search_triangulation(orbfe_matcher* m, const orbfe_tri_side* s1, const orbfe_tri_side* s2, const float F12[9],
+                               float ex, float ey, const float* scale_factors2, const float* level_sigma2_2, int nlevels2,
+                               int only_stereo, int check_orientation, int32_t* matches12, int* nmatches) {
+    if (!m || !s1 || !s2 || !F12 || !nmatches) return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_search_triangulation");
+    *nmatches = 0;
+    for (const orbfe_tri_side* sd : {s1, s2}) {
+        if (sd->n < 0 || sd->nnodes < 0) return fail(ORBFE_ERR_ARG, "negative size in triangulation side");
+        if (sd->n && (!sd->kps || !sd->desc || !sd->has_mappoint)) return fail(ORBFE_ERR_ARG, "NULL array in triangulation side");
+        if (sd->nnodes && (!sd->node_id || !sd->node_start || !sd->indices)) return fail(ORBFE_ERR_ARG, "NULL feature vector array");
+        if (sd->nnodes && sd->node_start[0] != 0) return fail(ORBFE_ERR_ARG, "node_start[0] must be 0");
+        for (int k = 0; k < sd->nnodes; k++) {
+            if (sd->node_start[k + 1] < sd->node_start[k]) return fail(ORBFE_ERR_ARG, "node_start must not decrease");
+            if (sd->node_start[k + 1] - sd->node_start[k] > 65535) return fail(ORBFE_ERR_CAPACITY, "more than 65535 features in one node");
+            if (k && sd->node_id[k] <= sd->node_id[k - 1]) return fail(ORBFE_ERR_ARG, "node ids must ascend");
+        }
+        const int tot = sd->nnodes ? sd->node_start[sd->nnodes] : 0;
+        for (int j = 0; j < tot; j++)
+            if (sd->indices[j] >= (uint32_t)sd->n) return fail(ORBFE_ERR_ARG, "feature index outside the key frame");
+    }
+    const int n1 = s1->n, n2 = s2->n;
+    if (n1 == 0) return ORBFE_OK;
+    if (!matches12) return fail(ORBFE_ERR_ARG, "matches12 is NULL");
+    const int t1 = s1->nnodes ? s1->node_start[s1->nnodes] : 0, t2 = s2->nnodes ? s2->node_start[s2->nnodes] : 0;
+    if (n2 == 0 || t1 == 0 || t2 == 0) { for (int i = 0; i < n1; i++) matches12[i] = -1; return ORBFE_OK; }
+    if (!scale_factors2 || !level_sigma2_2 || nlevels2 <= 0) return fail(ORBFE_ERR_ARG, "scale tables of key frame 2 missing");
+    for (int i = 0; i < n2; i++)
+        if (s2->kps[i].octave < 0 || s2->kps[i].octave >= nlevels2) return fail(ORBFE_ERR_ARG, "key frame 2 octave outside its scale tables");
+    CU(cudaSetDevice(m->device));
+    cudaStream_t s = m->stream;
+    int rc;
+    auto side_bytes = [](const orbfe_tri_side* sd, int tot) {
+        return padded((size_t)sd->n * sizeof(orbfe_keypoint)) + padded((size_t)sd->n * 32) + padded(sd->n) + padded((size_t)sd->n * 4) +
+               padded((size_t)sd->nnodes * 4) + padded((size_t)(sd->nnodes + 1) * 4) + padded((size_t)tot * 4);
+    };
+    const size_t upBytes = side_bytes(s1, t1) + side_bytes(s2, t2) + 2 * padded((size_t)nlevels2 * 4);
+    if ((rc = m->scratch[0].ensure(upBytes))) return rc;
+    if ((rc = m->stage.ensure(upBytes))) return rc;
+    Upload U{m->stage.p, m->scratch[0].p, 0, upBytes};
+    TriArgs a{};
+    a.n1 = n1; a.n2 = n2; a.nidx1 = t1;
+    a.kps1 = U.put<orbfe_keypoint>(s1->kps, n1); a.desc1 = U.put<uint8_t>(s1->desc, (size_t)n1 * 32);
+    a.has1 = U.put<uint8_t>(s1->has_mappoint, n1); a.ur1 = s1->uright ? U.put<float>(s1->uright, n1) : nullptr;
+    a.nnodes1 = s1->nnodes; a.node_id1 = U.put<uint32_t>(s1->node_id, s1->nnodes);
+    a.node_start1 = U.put<int>(s1->node_start, (size_t)s1->nnodes + 1); a.indices1 = U.put<uint32_t>(s1->indices, t1);
+    a.kps2 = U.put<orbfe_keypoint>(s2->kps, n2); a.desc2 = U.put<uint8_t>(s2->desc, (size_t)n2 * 32);
+    a.has2 = U.put<uint8_t>(s2->has_mappoint, n2); a.ur2 = s2->uright ? U.put<float>(s2->uright, n2) : nullptr;
+    a.nnodes2 = s2->nnodes; a.node_id2 = U.put<uint32_t>(s2->node_id, s2->nnodes);
+    a.node_start2 = U.put<int>(s2->node_start, (size_t)s2->nnodes + 1); a.indices2 = U.put<uint32_t>(s2->indices, t2);
+    a.scale2 = U.put<float>(scale_factors2, nlevels2); a.sigma2_2 = U.put<float>(level_sigma2_2, nlevels2);
+    std::memcpy(a.F, F12, sizeof(a.F)); a.ex = ex; a.ey = ey;
+    a.th = 50; a.onlyStereo = only_stereo; a.checkOri = check_orientation;                // TH_LOW (:816)
+    if (U.off > U.cap) return fail(ORBFE_ERR_CAPACITY, "internal: matcher staging overflow");
+    CU(cudaMemcpyAsync(m->scratch[0].p, m->stage.p, U.off, cudaMemcpyHostToDevice, s));
+    const size_t rInts = (size_t)n1 + 32;
+    if ((rc = m->scratch[2].ensure(rInts * 4))) return rc;
+    if ((rc = m->result.ensure(rInts * 4))) return rc;
+    int* R = reinterpret_cast<int*>(m->scratch[2].p);
+    a.m12 = R; a.hist = R + n1; a.nmatches = R + n1 + 30;
+    launch_search_triangulation(a, R + n1, 32, s);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(m->result.p, R, rInts * 4, cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    std::memcpy(matches12, m->result.p, (size_t)n1 * 4);
+    *nmatches = reinterpret_cast<const int*>(m->result.p)[n1 + 30];
+    return ORBFE_OK;
 }
 
 // ORBmatcher::SearchByBoW, both forms — src/ORBmatcher.cc:185-325, :610-743 — for npairs (side 1, side 2)

@@ -56,6 +56,7 @@ struct LocalArgs {
     int mode;
     const float* radius; const int* min_level; const int* max_level; const float* angle;
     int checkOri; int* hist;     // [32] rotation histogram (mode 1)
+    int max_dist;                // mode 1: accepted best distance (TH_HIGH, ORBdist or TH_LOW depending on the overload)
     int* kp_bad;                 // [n] keypoint lost its match to the rotation check (mode 1)
     GridGeom grid;
     // grid CSR of the frame
@@ -71,6 +72,23 @@ struct LocalArgs {
     const int* owner_pp; int* diff_flag;
     int* ncand_out;              // the epilogue copies the candidate total here (read back with the results)
 };
+
+// K14: independent best-in-window search of projected map points (Fuse x2, SearchBySim3)
+struct WindowArgs {
+    const orbfe_keypoint* kps; const uint8_t* desc; const float* uright; int n;   // key frame side (mvKeysUn, mDescriptors, mvuRight)
+    GridGeom grid; const int* cell_end; const unsigned short* items;               // mGrid as CSR
+    int np;
+    const uint8_t* valid; const float* u; const float* v; const float* ur; const float* radius;
+    const int* level;            // nPredictedLevel: candidates of octave level-1 .. level
+    const uint8_t* pdesc;
+    const float* inv_sigma2;     // mvInvLevelSigma2 (device) or NULL: no reprojection gate
+    int max_dist;                // best_idx = -1 above it
+    int* best_idx; int* best_dist;
+};
+int launch_build_grid(const orbfe_keypoint* kps, int n, const GridGeom& grid, int* cell_end, unsigned short* items,
+                      cudaStream_t st);
+int launch_window_best(const WindowArgs& a, cudaStream_t st);
+int launch_sim3_agree(const int* match1, const int* match2, int n1, int n2, int* m12, int* nfound, cudaStream_t st);
 
 struct StereoArgs {
     const orbfe_keypoint* kl; const uint8_t* dl; int nl;
@@ -105,6 +123,25 @@ struct BowArgs {
 // (every pair's m12, m21) and "0" part (every pair's histogram + count)
 int launch_search_bow(const BowArgs* d_pairs, int npairs, int max_nodes1, int max_n1, bool check_ori, int* minus1,
                       int nminus1, int* zero, int nzero, cudaStream_t st);
+
+// K15: SearchForTriangulation — both key frames' mvKeysUn, descriptors, "has a map point" flags,
+// mvuRight (NULL = monocular) and feature vectors as CSR; F12 row-major, epipole (ex, ey)
+struct TriArgs {
+    int n1, n2, nidx1;           // nidx1 = node_start1[nnodes1]
+    const orbfe_keypoint* kps1; const orbfe_keypoint* kps2;
+    const uint8_t* desc1; const uint8_t* desc2;
+    const uint8_t* has1; const uint8_t* has2;
+    const float* ur1; const float* ur2;
+    int nnodes1, nnodes2;
+    const uint32_t* node_id1; const uint32_t* node_id2;
+    const int* node_start1; const int* node_start2;
+    const uint32_t* indices1; const uint32_t* indices2;
+    float F[9]; float ex, ey;
+    const float* scale2; const float* sigma2_2;   // pKF2->mvScaleFactors / mvLevelSigma2 (device)
+    int th, onlyStereo, checkOri;
+    int* m12; int* hist; int* nmatches;
+};
+int launch_search_triangulation(const TriArgs& a, int* zero, int nzero, cudaStream_t st);
 
 // MapPoint::ComputeDistinctiveDescriptors for a batch: point p owns rows [start[p], start[p+1]) of desc
 int launch_distinctive(const uint8_t* d_desc, const int* d_start, int npoints, int* d_best, cudaStream_t st);

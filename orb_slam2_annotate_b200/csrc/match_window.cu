@@ -599,7 +599,7 @@ __global__ void __launch_bounds__(128) local_select_kernel(const __grid_constant
     }
     int ch = -1;
     if (a.mode == 1) {
-        if (bestDist <= TH_HIGH) ch = bestIdx;                                          // :1585-1589, best only
+        if (bestDist <= a.max_dist) ch = bestIdx;                                       // :1585-1589 / :1734 / :440, best only
     } else if (bestDist <= TH_HIGH &&                                                   // :127-135
                !(bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(a.ratio, (float)bestDist2))) {
         ch = bestIdx;
@@ -665,6 +665,82 @@ frame_finalize_kernel(const __grid_constant__ LocalArgs a, int* mp_for_kp, int* 
     if (bad) a.kp_bad[k] = 1;
     else atomicAdd(nmatches, 1);
     atomicMax(&mp_for_kp[k], i);
+}
+
+// ---------------------------------------------------------------------------------------
+// K14: best keypoint inside the search window of every projected map point, each point on its
+// own — the candidate loops of Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:1007-1052),
+// Fuse(pKF, Scw, ...) (:1180-1204) and both directions of SearchBySim3 (:1333-1365, :1411-1443).
+// One warp per point: window columns of KeyFrame::GetFeaturesInArea (KeyFrame.cc:611-650) are
+// contiguous CSR runs, the lanes stride a run; key = distance << 20 | traversal rank keeps the
+// reference's first-wins rule under the warp minimum.
+constexpr int WB_WARPS = 4;
+__global__ void __launch_bounds__(WB_WARPS * 32) window_best_kernel(const __grid_constant__ WindowArgs a) {
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * WB_WARPS + (threadIdx.x >> 5);
+    if (i >= a.np) return;
+    uint32_t best = KEY_INF;
+    int bi = -1;
+    if (a.valid[i]) {
+        const float x = a.u[i], y = a.v[i], r = a.radius[i];
+        const int lvl = a.level[i];
+        int cx0, cx1, cy0, cy1;
+        if (cell_window(a.grid, x, y, r, cx0, cx1, cy0, cy1)) {
+            uint32_t q[8];
+            load_row(q, a.pdesc + 32 * (long long)i);
+            const float pur = (a.inv_sigma2 && a.uright) ? a.ur[i] : 0.0f;
+            int seq = 0;
+            for (int ix = cx0; ix <= cx1; ix++) {
+                const int c0 = ix * GR + cy0;
+                const int s = c0 ? a.cell_end[c0 - 1] : 0, e = a.cell_end[ix * GR + cy1];
+                for (int j = s + lane; j < e; j += 32) {
+                    const int idx = a.items[j];
+                    const orbfe_keypoint kp = a.kps[idx];
+                    const float dx = __fsub_rn(kp.x, x), dy = __fsub_rn(kp.y, y);
+                    if (!(fabsf(dx) < r && fabsf(dy) < r)) continue;                      // KeyFrame.cc:640-644
+                    if (kp.octave < lvl - 1 || kp.octave > lvl) continue;                 // :1016 / :1187 / :1340
+                    if (a.inv_sigma2) {                                                   // :1020-1041
+                        const float ex = __fsub_rn(x, kp.x), ey = __fsub_rn(y, kp.y);
+                        float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+                        const float kur = a.uright ? a.uright[idx] : -1.0f;
+                        double gate = 5.99;
+                        if (kur >= 0) {
+                            const float er = __fsub_rn(pur, kur);
+                            e2 = __fadd_rn(e2, __fmul_rn(er, er));
+                            gate = 7.8;
+                        }
+                        if ((double)__fmul_rn(e2, a.inv_sigma2[kp.octave]) > gate) continue;
+                    }
+                    const int dist = hamming256(q, a.desc + 32 * (long long)idx);
+                    const uint32_t key = ((uint32_t)dist << 20) | (uint32_t)(seq + j - s);
+                    if (key < best) { best = key; bi = idx; }
+                }
+                seq += e - s;
+            }
+        }
+    }
+    const uint32_t g = warp_min(best);
+    int idx = -1, dist = 256;
+    if (g != KEY_INF) {
+        const unsigned own = __ballot_sync(FULL, best == g);
+        idx = __shfl_sync(FULL, bi, __ffs(own) - 1);
+        dist = (int)(g >> 20);
+    }
+    if (lane == 0) {
+        a.best_dist[i] = dist;
+        a.best_idx[i] = dist <= a.max_dist ? idx : -1;
+    }
+}
+
+// SearchBySim3's agreement test (:1446-1460): keep (i1, idx2) where the reverse search of idx2 returned i1
+__global__ void __launch_bounds__(256) sim3_agree_kernel(const int* match1, const int* match2, int n1, int n2, int* m12,
+                                                         int* nfound) {
+    const int i1 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i1 >= n1) return;
+    const int idx2 = match1[i1];
+    const bool ok = idx2 >= 0 && idx2 < n2 && match2[idx2] == i1;
+    m12[i1] = ok ? idx2 : -1;
+    if (ok) atomicAdd(nfound, 1);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -875,6 +951,26 @@ int launch_guided_init(int* owners, int n, int nsweeps, bool reset_first, int* m
     const int work = nown > nzero ? nown : nzero;
     guided_init_kernel<<<(work + 1023) / 1024 > 0 ? (work + 1023) / 1024 : 1, 256, 0, st>>>(first, nown, mp_for_kp, n, zero_block, nzero,
                                                                                          occ_out, occ0);
+    return 1;
+}
+
+int launch_build_grid(const orbfe_keypoint* kps, int n, const GridGeom& grid, int* cell_end, unsigned short* items,
+                      cudaStream_t st) {
+    LocalArgs a{};
+    a.kps = kps; a.n = n; a.grid = grid; a.cell_end = cell_end; a.items = items;
+    build_grid_kernel<<<1, kGridThreads, 0, st>>>(a);
+    return 1;
+}
+
+int launch_window_best(const WindowArgs& a, cudaStream_t st) {
+    if (a.np <= 0) return 0;
+    window_best_kernel<<<(a.np + WB_WARPS - 1) / WB_WARPS, WB_WARPS * 32, 0, st>>>(a);
+    return 1;
+}
+
+int launch_sim3_agree(const int* match1, const int* match2, int n1, int n2, int* m12, int* nfound, cudaStream_t st) {
+    if (n1 <= 0) return 0;
+    sim3_agree_kernel<<<(n1 + 255) / 256, 256, 0, st>>>(match1, match2, n1, n2, m12, nfound);
     return 1;
 }
 

@@ -11,7 +11,7 @@ import numpy as np
 
 from . import _lib
 from ._lib import (KP_DTYPE, BowView, Camera, DeviceFrameView, FrameView, MapPointsView, FramePointsView, PyramidView,
-                   GRID_CELLS, check)
+                   TriSideView, WindowPointsView, GRID_CELLS, check)
 
 
 class Frame:
@@ -99,6 +99,89 @@ def project_last_frame(Tcw_cur: np.ndarray, Tcw_last: np.ndarray, world_pos: np.
     ur = (u - f32(mbf) * invzc).astype(f32)                                               # :1575
     return dict(valid=valid.astype(np.uint8), u=u, v=v, ur=ur, radius=radius, min_level=lo.astype(np.int32),
                 max_level=hi.astype(np.int32), forward=forward, backward=backward)
+
+
+class TriSide:
+    """One key frame of ``SearchForTriangulation``: mvKeysUn, mDescriptors, "has a map point" flags, mvuRight
+    (None = monocular) and mFeatVec ``{node id: [feature indices]}``, flattened for ``orbfe_tri_side``."""
+
+    def __init__(self, keypoints: np.ndarray, descriptors: np.ndarray, has_mappoint: np.ndarray, feat_vec: dict, uright=None):
+        assert keypoints.dtype == KP_DTYPE
+        self.kps = np.ascontiguousarray(keypoints)
+        self.desc = np.ascontiguousarray(descriptors, np.uint8).reshape(-1, 32)
+        self.has_mappoint = np.ascontiguousarray(has_mappoint, np.uint8)
+        self.uright = None if uright is None else np.ascontiguousarray(uright, np.float32)
+        self.node_id = np.array(sorted(feat_vec), np.uint32)
+        self.node_start = np.zeros(len(self.node_id) + 1, np.int32)
+        for i, k in enumerate(self.node_id):
+            self.node_start[i + 1] = self.node_start[i] + len(feat_vec[int(k)])
+        self.indices = np.array([j for k in self.node_id for j in feat_vec[int(k)]], np.uint32)
+
+    def view(self) -> TriSideView:
+        return TriSideView(len(self.kps), self.kps.ctypes.data, self.desc.ctypes.data, self.has_mappoint.ctypes.data,
+                           None if self.uright is None else self.uright.ctypes.data, len(self.node_id),
+                           self.node_id.ctypes.data, self.node_start.ctypes.data, self.indices.ctypes.data)
+
+
+def project_map_points(Rcw: np.ndarray, tcw: np.ndarray, world_pos: np.ndarray, *, fx: float, fy: float, cx: float, cy: float,
+                       bounds: tuple, scale_factors: np.ndarray, log_scale_factor: float, th: float,
+                       max_distance: np.ndarray, min_distance: np.ndarray, usable: np.ndarray | None = None,
+                       normals: np.ndarray | None = None, Ow: np.ndarray | None = None, bf: float = 0.0,
+                       depth_gate: bool = True, invz_double: bool = True, frame_bounds: bool = False,
+                       camera_norm: bool = False) -> dict:
+    """Host side of the key-frame guided searches: the pose arithmetic and gates the reference runs per map
+    point before it looks at keypoints, in cv::Mat float32 semantics (3x3 * 3x1 products accumulate in double
+    and round once, cv::norm accumulates in double).  One routine, switched by the flags, covers
+      SearchByProjection(F, pKF, ...)   src/ORBmatcher.cc:1663-1703  depth_gate=False, frame_bounds=True
+      SearchByProjection(pKF, Scw, ..)  :361-407                     invz_double=False, normals given
+      Fuse(pKF, vpMapPoints, th)        :955-996                     invz_double=False, normals, bf
+      Fuse(pKF, Scw, ...)               :1127-1168                   normals given
+      SearchBySim3 (one direction)      :1300-1331                   camera_norm=True (Rcw, tcw = the composed
+                                                                     transform into the other key frame)
+    max_distance / min_distance are GetMaxDistanceInvariance() / GetMinDistanceInvariance() (1.2 mfMaxDistance,
+    0.8 mfMinDistance, src/MapPoint.cc:406-416); PredictScale (:418-433) divides mfMaxDistance = max_distance / 1.2f.
+    Returns valid / u / v / ur / radius / level arrays (``usable`` folds isBad, already-found and NULL tests)."""
+    f32, f64 = np.float32, np.float64
+    R, t = np.asarray(Rcw, f32).reshape(3, 3), np.asarray(tcw, f32).reshape(3)
+    X = np.asarray(world_pos, f32).reshape(-1, 3)
+    n = len(X)
+    Xc = ((R.astype(f64) @ X.T.astype(f64)).astype(f32).T + t).astype(f32)
+    z = Xc[:, 2]
+    valid = np.ones(n, bool) if usable is None else np.asarray(usable, bool).copy()
+    if depth_gate:
+        valid &= ~(z < 0)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        invz = (1.0 / z.astype(f64)).astype(f32) if invz_double else (f32(1) / z).astype(f32)
+        if frame_bounds:                                              # u = fx*xc*invzc + cx (:1675-1676)
+            u = (f32(fx) * Xc[:, 0] * invz + f32(cx)).astype(f32); v = (f32(fy) * Xc[:, 1] * invz + f32(cy)).astype(f32)
+        else:                                                         # x = X*invz; u = fx*x + cx
+            u = (f32(fx) * (Xc[:, 0] * invz).astype(f32) + f32(cx)).astype(f32)
+            v = (f32(fy) * (Xc[:, 1] * invz).astype(f32) + f32(cy)).astype(f32)
+        ur = (u - f32(bf) * invz).astype(f32)
+    minx, maxx, miny, maxy = (f32(b) for b in bounds)
+    if frame_bounds:
+        valid &= ~((u < minx) | (u > maxx) | (v < miny) | (v > maxy))
+    else:                                                             # KeyFrame::IsInImage (KeyFrame.cc:653-656)
+        valid &= (u >= minx) & (u < maxx) & (v >= miny) & (v < maxy)
+    if camera_norm:
+        PO = Xc
+    else:
+        if Ow is None:
+            Ow = (-(R.T.astype(f64) @ t.astype(f64))).astype(f32)
+        PO = (X - np.asarray(Ow, f32).reshape(3)).astype(f32)
+    dist = np.sqrt((PO.astype(f64) ** 2).sum(axis=1)).astype(f32)
+    maxd, mind = np.asarray(max_distance, f32), np.asarray(min_distance, f32)
+    valid &= ~((dist < mind) | (dist > maxd))
+    if normals is not None:                                           # PO.dot(Pn) < 0.5*dist
+        dot = (PO.astype(f64) * np.asarray(normals, f32).reshape(-1, 3).astype(f64)).sum(axis=1)
+        valid &= ~(dot < 0.5 * dist.astype(f64))
+    with np.errstate(divide="ignore", invalid="ignore"):
+        ratio = ((maxd / f32(1.2)).astype(f32) / dist).astype(f32)
+        lvl = np.ceil(np.log(ratio).astype(f32) / f32(log_scale_factor))
+    nl = len(scale_factors)
+    lvl = np.clip(np.nan_to_num(lvl, nan=0.0, posinf=nl - 1, neginf=0.0), 0, nl - 1).astype(np.int32)
+    radius = (f32(th) * np.asarray(scale_factors, f32)[lvl]).astype(f32)
+    return dict(valid=valid.astype(np.uint8), u=np.nan_to_num(u), v=np.nan_to_num(v), ur=np.nan_to_num(ur), radius=radius, level=lvl)
 
 
 class ORBmatcher:
@@ -232,6 +315,101 @@ class ORBmatcher:
                                                     occupied.ctypes.data, out.ctypes.data, C.byref(n)),
                   "orbfe_search_frame_points")
         return n.value, out[:N]
+
+    WINDOW_POINT_FIELDS = dict(valid=np.uint8, u=np.float32, v=np.float32, ur=np.float32, radius=np.float32,
+                               level=np.int32, desc=np.uint8)
+
+    def _window_view(self, points: dict):
+        n = len(points["u"])
+        keep = {k: (np.ascontiguousarray(points[k], t) if points.get(k) is not None else np.zeros(max(n, 1), t))
+                for k, t in self.WINDOW_POINT_FIELDS.items()}
+        return WindowPointsView(n, *[keep[k].ctypes.data for k in self.WINDOW_POINT_FIELDS]), keep
+
+    def _projected(self, F, points: dict, max_dist: int, check_ori: bool, occupied):
+        keep = {k: np.ascontiguousarray(points[k], t) for k, t in self.FRAME_POINT_FIELDS.items()}
+        v = FramePointsView(len(keep["u"]), *[keep[k].ctypes.data for k in self.FRAME_POINT_FIELDS])
+        resident = isinstance(F, DeviceFrameView)
+        N = F.n if resident else F.N
+        occ = np.zeros(max(N, 1), np.uint8) if occupied is None else np.ascontiguousarray(occupied, np.uint8)
+        out = np.full(max(N, 1), -1, np.int32)
+        n = C.c_int()
+        if resident:
+            check(self._L.orbfe_search_projected_points_resident(self._h, C.byref(F), C.byref(v), int(max_dist), int(check_ori),
+                                                                 occ.ctypes.data, out.ctypes.data, C.byref(n)),
+                  "orbfe_search_projected_points_resident")
+        else:
+            fv = F.view()
+            check(self._L.orbfe_search_projected_points(self._h, C.byref(fv), C.byref(v), int(max_dist), int(check_ori),
+                                                        occ.ctypes.data, out.ctypes.data, C.byref(n)),
+                  "orbfe_search_projected_points")
+        return n.value, out[:N]
+
+    def SearchByProjectionKeyFrame(self, F: Frame, points: dict, ORBdist: int, occupied: np.ndarray | None = None):
+        """SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, sAlreadyFound, th, ORBdist) — src/ORBmatcher.cc:1641-1770.
+        points: valid / u / v / radius / level (nPredictedLevel) / angle (pKF->mvKeysUn[i].angle) / desc per map point of
+        pKF (see `project_map_points`); occupied u8[N]: CurrentFrame.mvpMapPoints[i] != NULL.
+        -> (nmatches, match_for_kp int32[N]: >= 0 index i of pKF's map point, -1 untouched, -2 cleared by the rotation check)"""
+        lvl = np.asarray(points["level"], np.int32)
+        n = len(lvl)
+        p = dict(points, min_level=lvl - 1, max_level=lvl + 1, observations=np.ones(n, np.int32),      # :1705, :1720
+                 ur=np.zeros(n, np.float32))
+        return self._projected(F, p, ORBdist, self.mbCheckOrientation, occupied)
+
+    def SearchByProjectionSim3(self, KF: Frame, points: dict, matched: np.ndarray | None = None):
+        """SearchByProjection(KeyFrame* pKF, Scw, vpPoints, vpMatched, th) — src/ORBmatcher.cc:335-451.  points as above
+        without angle; matched u8[N]: vpMatched[idx] != NULL on entry.
+        -> (nmatches, match_for_kp int32[N]: index into vpPoints newly written to vpMatched[idx], else -1)"""
+        lvl = np.asarray(points["level"], np.int32)
+        n = len(lvl)
+        p = dict(points, min_level=lvl - 1, max_level=lvl, observations=np.ones(n, np.int32),           # :426, :421
+                 ur=np.zeros(n, np.float32), angle=np.zeros(n, np.float32))
+        return self._projected(KF, p, self.TH_LOW, False, matched)
+
+    def FuseSearch(self, KF, points: dict, inv_level_sigma2: np.ndarray | None = None):
+        """The search of Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:940-1090; pass pKF->mvInvLevelSigma2) and of
+        Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) (:1100-1237; inv_level_sigma2 None).
+        -> (best_idx int32[n]: keypoint to fuse with or -1, best_dist int32[n]); Replace / AddObservation stay with the caller."""
+        v, keep = self._window_view(points)
+        n = v.n
+        bi = np.full(max(n, 1), -1, np.int32); bd = np.full(max(n, 1), 256, np.int32)
+        sig = None if inv_level_sigma2 is None else np.ascontiguousarray(inv_level_sigma2, np.float32)
+        sp = None if sig is None else sig.ctypes.data
+        if isinstance(KF, DeviceFrameView):
+            check(self._L.orbfe_search_window_best_resident(self._h, C.byref(KF), C.byref(v), sp, self.TH_LOW, bi.ctypes.data,
+                                                            bd.ctypes.data), "orbfe_search_window_best_resident")
+        else:
+            fv = KF.view()
+            check(self._L.orbfe_search_window_best(self._h, C.byref(fv), C.byref(v), sp, self.TH_LOW, bi.ctypes.data,
+                                                   bd.ctypes.data), "orbfe_search_window_best")
+        return bi[:n], bd[:n]
+
+    def SearchBySim3(self, KF1: Frame, KF2: Frame, points1: dict, points2: dict):
+        """SearchBySim3 — src/ORBmatcher.cc:1251-1477.  points1[i1]: KF1's map point i1 projected into KF2 (one entry per
+        keypoint of KF1, valid = 0 where there is none / already matched / bad), points2 likewise.
+        -> (nFound, matches12 int32[N1]: index in KF2 or -1)"""
+        v1, k1 = self._window_view(points1); v2, k2 = self._window_view(points2)
+        m12 = np.full(max(v1.n, 1), -1, np.int32)
+        n = C.c_int()
+        f1, f2 = KF1.view(), KF2.view()
+        check(self._L.orbfe_search_by_sim3(self._h, C.byref(f1), C.byref(f2), C.byref(v1), C.byref(v2), self.TH_HIGH,
+                                           m12.ctypes.data, C.byref(n)), "orbfe_search_by_sim3")
+        return n.value, m12[:v1.n]
+
+    def SearchForTriangulation(self, side1: TriSide, side2: TriSide, F12: np.ndarray, ex: float, ey: float,
+                               scale_factors2: np.ndarray, level_sigma2_2: np.ndarray, bOnlyStereo: bool = False):
+        """SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) — src/ORBmatcher.cc:754-928; (ex, ey) is the
+        epipole of :762-768.  -> (nmatches, matches12 int32[N1]); vMatchedPairs = [(i, m) for i, m in enumerate(matches12) if m >= 0]"""
+        F = np.ascontiguousarray(F12, np.float32).reshape(9)
+        sf = np.ascontiguousarray(scale_factors2, np.float32); sg = np.ascontiguousarray(level_sigma2_2, np.float32)
+        n1 = len(side1.kps)
+        m12 = np.full(max(n1, 1), -1, np.int32)
+        n = C.c_int()
+        v1, v2 = side1.view(), side2.view()
+        check(self._L.orbfe_search_triangulation(self._h, C.byref(v1), C.byref(v2), F.ctypes.data, float(ex), float(ey),
+                                                 sf.ctypes.data, sg.ctypes.data, len(sf), int(bOnlyStereo),
+                                                 int(self.mbCheckOrientation), m12.ctypes.data, C.byref(n)),
+              "orbfe_search_triangulation")
+        return n.value, m12[:n1]
 
     def SearchByBoW(self, side1: BowSide, side2: BowSide, keyframe_pair: bool = False):
         """SearchByBoW(KeyFrame*, Frame&, ..) — src/ORBmatcher.cc:185-325 — or, with ``keyframe_pair``,
