@@ -133,6 +133,22 @@ def guided_search_timings(frame_img):
     mtb = orbfe.ORBmatcher(0.75, True)
     bow_matches = mtb.SearchByBoW(b1, b2)[0]
 
+    # key-frame guided searches: 20 000 map points fused into one key frame (Fuse, pose
+    # variant with its reprojection gate), SearchBySim3 between the frame and its noisy twin, SearchForTriangulation
+    # over the stand-in feature vectors with a horizontal-line fundamental matrix
+    tb = ex.GetScaleFactors(); sig2 = (tb * tb).astype(np.float32); inv_sig2 = (np.float32(1.0) / sig2).astype(np.float32)
+    lvl = k["octave"][src].astype(np.int32)
+    wpts = dict(valid=np.ones(nmp, np.uint8), u=mps["proj_x"], v=mps["proj_y"], ur=np.zeros(nmp, np.float32),
+                radius=(np.float32(3.0) * scale[lvl]).astype(np.float32), level=lvl, desc=mps["desc"])
+    kpts = dict(valid=np.ones(n, np.uint8), u=pts["u"], v=pts["v"], ur=np.zeros(n, np.float32),
+                radius=(np.float32(7.5) * scale[k["octave"]]).astype(np.float32), level=k["octave"].astype(np.int32), desc=pts["desc"],
+                angle=k["angle"].astype(np.float32))
+    F2 = orbfe.Frame(k, d_noisy, W, H, scale); fo2 = O.frame_view(k, d_noisy, W, H, scale)
+    F12 = np.array([[0, 0, 0], [0, 0, -1], [0, 1, 0]], np.float32)
+    none = np.zeros(n, np.uint8)
+    t1, t2 = orbfe.TriSide(k, d, none, fv1), orbfe.TriSide(k, d_noisy, none, fv2)
+    ot1, ot2 = O.tri_side(k, d, none, fv1), O.tri_side(k, d_noisy, none, fv2)
+
     # MapPoint::ComputeDistinctiveDescriptors for 20 000 map points with 3..20 observations each
     sizes = rng.integers(3, 21, 20000).astype(np.int32)
     dstart = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
@@ -157,6 +173,20 @@ def guided_search_timings(frame_img):
                                 "gpu_ms_per_call": med(lambda: mt.SearchByProjectionLast(F, pts, np.zeros(n, np.uint8))),
                                 "gpu_resident_frame_ms_per_call": med(lambda: mt.SearchByProjectionLast(dv, pts, np.zeros(n, np.uint8))),
                                 "cpu_ms_per_call": med(lambda: O.search_by_projection_frame(fo, pts, True, np.zeros(n, np.uint8)))},
+        "fuse": {"map_points": nmp, "keypoints": n, "fused": int((mt.FuseSearch(F, wpts, inv_sig2)[0] >= 0).sum()),
+                 "gpu_ms_per_call": med(lambda: mt.FuseSearch(F, wpts, inv_sig2)),
+                 "gpu_resident_frame_ms_per_call": med(lambda: mt.FuseSearch(dv, wpts, inv_sig2)),
+                 "cpu_ms_per_call": med(lambda: O.fuse_search(fo, wpts, inv_sig2))},
+        "search_by_sim3": {"keypoints": n, "found": mt.SearchBySim3(F, F2, kpts, kpts)[0],
+                           "gpu_ms_per_call": med(lambda: mt.SearchBySim3(F, F2, kpts, kpts)),
+                           "cpu_ms_per_call": med(lambda: O.search_by_sim3(fo, fo2, kpts, kpts))},
+        "search_projection_keyframe": {"points": n, "keypoints": n,
+                                       "gpu_ms_per_call": med(lambda: mt.SearchByProjectionKeyFrame(F2, kpts, 100, none)),
+                                       "cpu_ms_per_call": med(lambda: O.search_by_projection_keyframe(fo2, kpts, 100, True, none))},
+        "search_for_triangulation": {"features": n, "nodes": len(fv1),
+                                     "matches": mt.SearchForTriangulation(t1, t2, F12, -5000.0, 0.0, tb, sig2)[0],
+                                     "gpu_ms_per_call": med(lambda: mt.SearchForTriangulation(t1, t2, F12, -5000.0, 0.0, tb, sig2)),
+                                     "cpu_ms_per_call": med(lambda: O.search_for_triangulation(ot1, ot2, F12, -5000.0, 0.0, tb, sig2))},
         "frame_epilogue": {"what": "UndistortKeyPoints + AssignFeaturesToGrid, TUM1 camera", "keypoints": n,
                            "gpu_us_per_frame_in_batch": epi_us, "cpu_us_per_frame": med(cpu_epilogue) * 1e3},
     }

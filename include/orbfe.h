@@ -184,6 +184,12 @@ typedef struct {
     float min_x, max_x, min_y, max_y; /* mnMinX, mnMaxX, mnMinY, mnMaxY                     */
     const float* scale_factors;       /* mvScaleFactors                                     */
     int32_t nlevels;
+    int32_t keyframe_bounds;          /* 1: the view is a KeyFrame.  KeyFrame holds mnMinX.. as int
+                                       * (include/KeyFrame.h:191-194, truncated copies of the
+                                       * Frame's floats, src/KeyFrame.cc:41) while mGrid and
+                                       * mfGridElement*Inv are the Frame's (:33, :48-53): the cell
+                                       * window of KeyFrame::GetFeaturesInArea (:616-628) is then
+                                       * computed from (float)(int)min_x / min_y.  0: Frame.     */
 } orbfe_frame_view;
 
 /* Frame::ComputeImageBounds for callers without an extractor handle (HOST output). */
@@ -209,6 +215,7 @@ typedef struct {
     float min_x, max_x, min_y, max_y;
     const float* scale_factors;
     int32_t nlevels;
+    int32_t keyframe_bounds;          /* as in orbfe_frame_view */
 } orbfe_device_frame_view;
 
 /* Brute-force 2-nearest-neighbour Hamming search with the reference's acceptance rule

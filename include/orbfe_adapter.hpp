@@ -6,7 +6,9 @@
 //                             (DescriptorDistance, SearchForInitialization,
 //                             SearchByProjection(Frame&, vector<MapPoint*>&, th),
 //                             SearchByProjection(CurrentFrame, LastFrame, th, bMono)) and offers
-//                             both SearchByBoW overloads (:185-325, :610-743),
+//                             both SearchByBoW overloads (:185-325, :610-743), the key-frame guided searches
+//                             (SearchByProjection(F, KF) :1641-1770, SearchByProjection(KF, Scw) :335-451, Fuse x2
+//                             :940-1237, SearchBySim3 :1251-1477, SearchForTriangulation :754-928),
 //                             ComputeStereoMatches(Frame&) for src/Frame.cc:512-686,
 //                             ComputeImageBounds(Frame&, im) for :481-512 and
 //                             UndistortAndAssign(Frame&) for :443-475 + :246-267
@@ -21,7 +23,10 @@
 #define ORBFE_ADAPTER_HPP
 
 #include <cstring>
+#include <cmath>
 #include <map>
+#include <set>
+#include <utility>
 #include <stdexcept>
 #include <string>
 #include <type_traits>
@@ -283,6 +288,232 @@ public:
         return nmatches;
     }
 
+    // ------------------------------------------------------------------------------------------
+    // Key-frame guided searches.  As above, the pose arithmetic in front of
+    // each candidate loop is the reference's own cv::Mat code, kept on the host; candidates, Hamming
+    // distances, the first-owner bookkeeping and the rotation check run on the GPU; map mutation
+    // (Replace / AddObservation / AddMapPoint) is replayed on the host in point order.
+
+    // SearchByProjection(Frame&, KeyFrame*, const set<MapPoint*>&, th, ORBdist) — src/ORBmatcher.cc:1641-1770
+    template <class FrameT, class KeyFrameT, class SetT>
+    int SearchByProjection(FrameT& CurrentFrame, KeyFrameT* pKF, const SetT& sAlreadyFound, const float th, const int ORBdist) {
+        typedef typename std::decay<decltype(CurrentFrame.mTcw)>::type MatT;
+        const MatT Rcw = CurrentFrame.mTcw.rowRange(0, 3).colRange(0, 3);
+        const MatT tcw = CurrentFrame.mTcw.rowRange(0, 3).col(3);
+        const MatT Ow = -Rcw.t() * tcw;
+        const auto vpMPs = pKF->GetMapPointMatches();
+        const int n = (int)vpMPs.size();
+        Points P(n);
+        std::vector<float> angle(n, 0.0f);
+        for (int i = 0; i < n; i++) {
+            auto* pMP = vpMPs[i];
+            if (!pMP || pMP->isBad() || sAlreadyFound.count(pMP)) continue;                    // :1663-1667
+            const MatT x3Dw = pMP->GetWorldPos();
+            const MatT x3Dc = Rcw * x3Dw + tcw;
+            const float xc = x3Dc.template at<float>(0), yc = x3Dc.template at<float>(1);
+            const float invzc = 1.0 / x3Dc.template at<float>(2);
+            const float u = CurrentFrame.fx * xc * invzc + CurrentFrame.cx;
+            const float v = CurrentFrame.fy * yc * invzc + CurrentFrame.cy;
+            if (u < CurrentFrame.mnMinX || u > CurrentFrame.mnMaxX) continue;
+            if (v < CurrentFrame.mnMinY || v > CurrentFrame.mnMaxY) continue;
+            const MatT PO = x3Dw - Ow;
+            const float dist3D = norm(PO);   // cv::norm, found by argument-dependent lookup at instantiation
+            if (dist3D < pMP->GetMinDistanceInvariance() || dist3D > pMP->GetMaxDistanceInvariance()) continue;
+            const int nPredictedLevel = pMP->PredictScale(dist3D, &CurrentFrame);
+            P.set(i, u, v, 0.0f, th * CurrentFrame.mvScaleFactors[nPredictedLevel], nPredictedLevel, pMP->GetDescriptor());
+            angle[i] = pKF->mvKeysUn[i].angle;
+        }
+        std::vector<int> minL(n), maxL(n), obs(n, 1);
+        for (int i = 0; i < n; i++) { minL[i] = P.level[i] - 1; maxL[i] = P.level[i] + 1; }      // :1705
+        std::vector<orbfe_keypoint> k;
+        std::vector<uint8_t> d;
+        orbfe_frame_view fv = View(CurrentFrame, k, d);
+        orbfe_framepoints_view pv = {n, P.valid.data(), P.u.data(), P.v.data(), P.ur.data(), P.radius.data(), minL.data(),
+                                     maxL.data(), angle.data(), P.desc.data(), obs.data()};
+        std::vector<uint8_t> occupied(CurrentFrame.mvpMapPoints.size(), 0);
+        for (size_t i = 0; i < occupied.size(); i++) occupied[i] = CurrentFrame.mvpMapPoints[i] != nullptr;   // :1720
+        std::vector<int> matchForKp(occupied.size(), -1);
+        int nmatches = 0;
+        orbfe_detail::check(orbfe_search_projected_points(mpHandle, &fv, &pv, ORBdist, mbCheckOrientation ? 1 : 0, occupied.data(),
+                                                          matchForKp.data(), &nmatches), "orbfe_search_projected_points");
+        for (size_t i = 0; i < matchForKp.size(); i++) {
+            if (matchForKp[i] >= 0) CurrentFrame.mvpMapPoints[i] = vpMPs[matchForKp[i]];       // :1736
+            else if (matchForKp[i] == -2) CurrentFrame.mvpMapPoints[i] = nullptr;              // :1766
+        }
+        return nmatches;
+    }
+
+    // SearchByProjection(KeyFrame*, cv::Mat Scw, vpPoints, vpMatched, th) — src/ORBmatcher.cc:335-451
+    template <class KeyFrameT, class MatT, class MapPointT>
+    int SearchByProjection(KeyFrameT* pKF, MatT Scw, const std::vector<MapPointT*>& vpPoints, std::vector<MapPointT*>& vpMatched, int th) {
+        Sim3Pose<MatT> S(Scw);
+        std::set<MapPointT*> spAlreadyFound(vpMatched.begin(), vpMatched.end());
+        spAlreadyFound.erase(static_cast<MapPointT*>(nullptr));
+        const int n = (int)vpPoints.size();
+        Points P(n);
+        for (int i = 0; i < n; i++) {
+            MapPointT* pMP = vpPoints[i];
+            if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
+            ProjectIntoKeyFrame(pKF, pMP, S.Rcw, S.tcw, S.Ow, false, true, (float)th, 0.0f, i, P);   // :361-407
+        }
+        std::vector<int> minL(n), maxL(n), obs(n, 1);
+        std::vector<float> angle(n, 0.0f);
+        for (int i = 0; i < n; i++) { minL[i] = P.level[i] - 1; maxL[i] = P.level[i]; }          // :426
+        std::vector<orbfe_keypoint> k;
+        orbfe_frame_view fv = KeyFrameView(pKF, k);
+        orbfe_framepoints_view pv = {n, P.valid.data(), P.u.data(), P.v.data(), P.ur.data(), P.radius.data(), minL.data(),
+                                     maxL.data(), angle.data(), P.desc.data(), obs.data()};
+        std::vector<uint8_t> occupied(vpMatched.size(), 0);
+        for (size_t i = 0; i < occupied.size(); i++) occupied[i] = vpMatched[i] != nullptr;      // :421
+        std::vector<int> matchForKp(occupied.size(), -1);
+        int nmatches = 0;
+        orbfe_detail::check(orbfe_search_projected_points(mpHandle, &fv, &pv, TH_LOW, 0, occupied.data(), matchForKp.data(),
+                                                          &nmatches), "orbfe_search_projected_points");
+        for (size_t i = 0; i < matchForKp.size(); i++)
+            if (matchForKp[i] >= 0) vpMatched[i] = vpPoints[matchForKp[i]];                      // :442
+        return nmatches;
+    }
+
+    // Fuse(KeyFrame*, const vector<MapPoint*>&, th) — src/ORBmatcher.cc:940-1090.  The search of every
+    // point runs first (it reads only keypoints, descriptors and the point's own state on entry), the
+    // reference's bookkeeping follows in point order.  A point that an earlier Replace of this very call
+    // turned bad is skipped at replay time, as the sequential loop would (:952).
+    template <class KeyFrameT, class MapPointT>
+    int Fuse(KeyFrameT* pKF, const std::vector<MapPointT*>& vpMapPoints, const float th = 3.0) {
+        typedef typename std::decay<decltype(pKF->GetRotation())>::type MatT;
+        const MatT Rcw = pKF->GetRotation(), tcw = pKF->GetTranslation(), Ow = pKF->GetCameraCenter();
+        const int n = (int)vpMapPoints.size();
+        Points P(n);
+        for (int i = 0; i < n; i++) {
+            MapPointT* pMP = vpMapPoints[i];
+            if (!pMP || pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;                         // :949-953
+            ProjectIntoKeyFrame(pKF, pMP, Rcw, tcw, Ow, false, true, th, pKF->mbf, i, P);          // :955-996
+        }
+        std::vector<int32_t> best(n, -1);
+        std::vector<orbfe_keypoint> k;
+        orbfe_frame_view fv = KeyFrameView(pKF, k);
+        if (!pKF->mvuRight.empty()) fv.uright = pKF->mvuRight.data();
+        orbfe_windowpoints_view wv = {n, P.valid.data(), P.u.data(), P.v.data(), P.ur.data(), P.radius.data(), P.level.data(), P.desc.data()};
+        orbfe_detail::check(orbfe_search_window_best(mpHandle, &fv, &wv, pKF->mvInvLevelSigma2.data(), TH_LOW, best.data(), nullptr),
+                            "orbfe_search_window_best");
+        int nFused = 0;
+        for (int i = 0; i < n; i++) {
+            if (best[i] < 0) continue;
+            MapPointT* pMP = vpMapPoints[i];
+            if (pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;
+            MapPointT* pMPinKF = pKF->GetMapPoint(best[i]);                                       // :1057-1073
+            if (pMPinKF) {
+                if (!pMPinKF->isBad()) {
+                    if (pMPinKF->Observations() > pMP->Observations()) pMP->Replace(pMPinKF);
+                    else pMPinKF->Replace(pMP);
+                }
+            } else {
+                pMP->AddObservation(pKF, best[i]);
+                pKF->AddMapPoint(pMP, best[i]);
+            }
+            nFused++;
+        }
+        return nFused;
+    }
+
+    // Fuse(KeyFrame*, cv::Mat Scw, vpPoints, th, vpReplacePoint) — src/ORBmatcher.cc:1100-1237
+    template <class KeyFrameT, class MatT, class MapPointT>
+    int Fuse(KeyFrameT* pKF, MatT Scw, const std::vector<MapPointT*>& vpPoints, float th, std::vector<MapPointT*>& vpReplacePoint) {
+        Sim3Pose<MatT> S(Scw);
+        const std::set<MapPointT*> spAlreadyFound = pKF->GetMapPoints();
+        const int n = (int)vpPoints.size();
+        Points P(n);
+        for (int i = 0; i < n; i++) {
+            MapPointT* pMP = vpPoints[i];
+            if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
+            ProjectIntoKeyFrame(pKF, pMP, S.Rcw, S.tcw, S.Ow, true, true, th, 0.0f, i, P);         // :1127-1168
+        }
+        std::vector<int32_t> best(n, -1);
+        std::vector<orbfe_keypoint> k;
+        orbfe_frame_view fv = KeyFrameView(pKF, k);
+        orbfe_windowpoints_view wv = {n, P.valid.data(), P.u.data(), P.v.data(), P.ur.data(), P.radius.data(), P.level.data(), P.desc.data()};
+        orbfe_detail::check(orbfe_search_window_best(mpHandle, &fv, &wv, nullptr, TH_LOW, best.data(), nullptr), "orbfe_search_window_best");
+        int nFused = 0;
+        for (int i = 0; i < n; i++) {
+            if (best[i] < 0) continue;
+            MapPointT* pMP = vpPoints[i];
+            MapPointT* pMPinKF = pKF->GetMapPoint(best[i]);                                       // :1208-1222
+            if (pMPinKF) {
+                if (!pMPinKF->isBad()) vpReplacePoint[i] = pMPinKF;
+            } else {
+                pMP->AddObservation(pKF, best[i]);
+                pKF->AddMapPoint(pMP, best[i]);
+            }
+            nFused++;
+        }
+        return nFused;
+    }
+
+    // SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th) — src/ORBmatcher.cc:1251-1477
+    template <class KeyFrameT, class MatT, class MapPointT>
+    int SearchBySim3(KeyFrameT* pKF1, KeyFrameT* pKF2, std::vector<MapPointT*>& vpMatches12, const float& s12, const MatT& R12,
+                     const MatT& t12, const float th) {
+        const MatT R1w = pKF1->GetRotation(), t1w = pKF1->GetTranslation(), R2w = pKF2->GetRotation(), t2w = pKF2->GetTranslation();
+        const MatT sR12 = s12 * R12, sR21 = (1.0 / s12) * R12.t(), t21 = -sR21 * t12;            // :1265-1268
+        const std::vector<MapPointT*> vpMapPoints1 = pKF1->GetMapPointMatches(), vpMapPoints2 = pKF2->GetMapPointMatches();
+        const int N1 = (int)vpMapPoints1.size(), N2 = (int)vpMapPoints2.size();
+        std::vector<bool> vbAlreadyMatched1(N1, false), vbAlreadyMatched2(N2, false);
+        for (int i = 0; i < N1; i++) {                                                           // :1279-1289
+            MapPointT* pMP = vpMatches12[i];
+            if (!pMP) continue;
+            vbAlreadyMatched1[i] = true;
+            const int idx2 = pMP->GetIndexInKeyFrame(pKF2);
+            if (idx2 >= 0 && idx2 < N2) vbAlreadyMatched2[idx2] = true;
+        }
+        Points P1(N1), P2(N2);
+        for (int i1 = 0; i1 < N1; i1++) {                                                        // :1294-1331
+            MapPointT* pMP = vpMapPoints1[i1];
+            if (!pMP || vbAlreadyMatched1[i1] || pMP->isBad()) continue;
+            const MatT p3Dc1 = R1w * pMP->GetWorldPos() + t1w;
+            ProjectCameraPoint(pKF2, pMP, MatT(sR21 * p3Dc1 + t21), th, i1, P1);
+        }
+        for (int i2 = 0; i2 < N2; i2++) {                                                        // :1368-1409
+            MapPointT* pMP = vpMapPoints2[i2];
+            if (!pMP || vbAlreadyMatched2[i2] || pMP->isBad()) continue;
+            const MatT p3Dc2 = R2w * pMP->GetWorldPos() + t2w;
+            ProjectCameraPoint(pKF1, pMP, MatT(sR12 * p3Dc2 + t12), th, i2, P2);
+        }
+        std::vector<orbfe_keypoint> k1, k2;
+        orbfe_frame_view f1 = KeyFrameView(pKF1, k1), f2 = KeyFrameView(pKF2, k2);
+        orbfe_windowpoints_view w1 = {N1, P1.valid.data(), P1.u.data(), P1.v.data(), P1.ur.data(), P1.radius.data(), P1.level.data(), P1.desc.data()};
+        orbfe_windowpoints_view w2 = {N2, P2.valid.data(), P2.u.data(), P2.v.data(), P2.ur.data(), P2.radius.data(), P2.level.data(), P2.desc.data()};
+        std::vector<int32_t> m12(N1, -1);
+        int nFound = 0;
+        orbfe_detail::check(orbfe_search_by_sim3(mpHandle, &f1, &f2, &w1, &w2, TH_HIGH, m12.data(), &nFound), "orbfe_search_by_sim3");
+        for (int i1 = 0; i1 < N1; i1++)
+            if (m12[i1] >= 0) vpMatches12[i1] = vpMapPoints2[m12[i1]];                           // :1455
+        return nFound;
+    }
+
+    // SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) — src/ORBmatcher.cc:754-928
+    template <class KeyFrameT, class MatT>
+    int SearchForTriangulation(KeyFrameT* pKF1, KeyFrameT* pKF2, MatT F12, std::vector<std::pair<size_t, size_t> >& vMatchedPairs,
+                               const bool bOnlyStereo) {
+        const MatT Cw = pKF1->GetCameraCenter(), R2w = pKF2->GetRotation(), t2w = pKF2->GetTranslation();
+        const MatT C2 = R2w * Cw + t2w;                                                          // :762-768
+        const float invz = 1.0f / C2.template at<float>(2);
+        const float ex = pKF2->fx * C2.template at<float>(0) * invz + pKF2->cx;
+        const float ey = pKF2->fy * C2.template at<float>(1) * invz + pKF2->cy;
+        TriSide s1(pKF1), s2(pKF2);
+        float F[9];
+        for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) F[3 * r + c] = F12.template at<float>(r, c);
+        std::vector<int32_t> m12(s1.v.n, -1);
+        int nmatches = 0;
+        orbfe_detail::check(orbfe_search_triangulation(mpHandle, &s1.v, &s2.v, F, ex, ey, pKF2->mvScaleFactors.data(),
+                                                       pKF2->mvLevelSigma2.data(), (int)pKF2->mvScaleFactors.size(), bOnlyStereo ? 1 : 0,
+                                                       mbCheckOrientation ? 1 : 0, m12.data(), &nmatches), "orbfe_search_triangulation");
+        vMatchedPairs.clear();
+        vMatchedPairs.reserve(nmatches);
+        for (size_t i = 0; i < m12.size(); i++)
+            if (m12[i] >= 0) vMatchedPairs.push_back(std::make_pair(i, (size_t)m12[i]));           // :918-925
+        return nmatches;
+    }
+
     // Frame::ComputeImageBounds — src/Frame.cc:481-512 (call instead of the member, inside the
     // mbInitialComputations block of the Frame constructors, :97-111)
     template <class FrameT>
@@ -361,6 +592,101 @@ protected:
         orbfe_keypoint o = {k.pt.x, k.pt.y, k.size, k.angle, k.response, k.octave, k.class_id};
         return o;
     }
+    // per-point arrays of the key-frame searches
+    struct Points {
+        std::vector<uint8_t> valid, desc;
+        std::vector<float> u, v, ur, radius;
+        std::vector<int32_t> level;
+        explicit Points(int n) : valid(n, 0), desc((size_t)n * 32, 0), u(n, 0.f), v(n, 0.f), ur(n, 0.f), radius(n, 0.f), level(n, 0) {}
+        void set(int i, float u_, float v_, float ur_, float r_, int lvl, const cv::Mat& d) {
+            valid[i] = 1; u[i] = u_; v[i] = v_; ur[i] = ur_; radius[i] = r_; level[i] = lvl;
+            std::memcpy(&desc[(size_t)i * 32], d.data, 32);
+        }
+    };
+    // Scw -> Rcw, tcw, Ow (src/ORBmatcher.cc:343-348 / :1108-1113)
+    template <class MatT>
+    struct Sim3Pose {
+        MatT Rcw, tcw, Ow;
+        explicit Sim3Pose(const MatT& Scw) {
+            const MatT sRcw = Scw.rowRange(0, 3).colRange(0, 3);
+            const float scw = std::sqrt(sRcw.row(0).dot(sRcw.row(0)));
+            Rcw = sRcw / scw;
+            tcw = Scw.rowRange(0, 3).col(3) / scw;
+            Ow = -Rcw.t() * tcw;
+        }
+    };
+    // the gates between GetWorldPos() and GetFeaturesInArea() of the world-point searches
+    // (src/ORBmatcher.cc:361-407, :955-996, :1127-1168); invzDouble: "1.0/z" (:1136) versus "1/z" (:371, :966)
+    template <class KeyFrameT, class MapPointT, class MatT>
+    static void ProjectIntoKeyFrame(KeyFrameT* pKF, MapPointT* pMP, const MatT& Rcw, const MatT& tcw, const MatT& Ow, bool invzDouble,
+                                    bool checkNormal, float th, float bf, int i, Points& P) {
+        const MatT p3Dw = pMP->GetWorldPos();
+        const MatT p3Dc = Rcw * p3Dw + tcw;
+        if (p3Dc.template at<float>(2) < 0.0f) return;
+        const float invz = invzDouble ? (float)(1.0 / p3Dc.template at<float>(2)) : 1 / p3Dc.template at<float>(2);
+        const float x = p3Dc.template at<float>(0) * invz, y = p3Dc.template at<float>(1) * invz;
+        const float u = pKF->fx * x + pKF->cx, v = pKF->fy * y + pKF->cy;
+        if (!pKF->IsInImage(u, v)) return;
+        const float ur = u - bf * invz;
+        const MatT PO = p3Dw - Ow;
+        const float dist3D = norm(PO);   // cv::norm, found by argument-dependent lookup at instantiation
+        if (dist3D < pMP->GetMinDistanceInvariance() || dist3D > pMP->GetMaxDistanceInvariance()) return;
+        if (checkNormal) {
+            const MatT Pn = pMP->GetNormal();
+            if (PO.dot(Pn) < 0.5 * dist3D) return;
+        }
+        const int nPredictedLevel = pMP->PredictScale(dist3D, pKF);
+        P.set(i, u, v, ur, th * pKF->mvScaleFactors[nPredictedLevel], nPredictedLevel, pMP->GetDescriptor());
+    }
+    // SearchBySim3's gates on a point already expressed in the other camera (src/ORBmatcher.cc:1305-1331)
+    template <class KeyFrameT, class MapPointT, class MatT>
+    static void ProjectCameraPoint(KeyFrameT* pKF, MapPointT* pMP, const MatT& p3Dc, float th, int i, Points& P) {
+        if (p3Dc.template at<float>(2) < 0.0) return;
+        const float invz = 1.0 / p3Dc.template at<float>(2);
+        const float x = p3Dc.template at<float>(0) * invz, y = p3Dc.template at<float>(1) * invz;
+        const float u = pKF->fx * x + pKF->cx, v = pKF->fy * y + pKF->cy;
+        if (!pKF->IsInImage(u, v)) return;
+        const float dist3D = norm(p3Dc);   // cv::norm (ADL)
+        if (dist3D < pMP->GetMinDistanceInvariance() || dist3D > pMP->GetMaxDistanceInvariance()) return;
+        const int nPredictedLevel = pMP->PredictScale(dist3D, pKF);
+        P.set(i, u, v, 0.0f, th * pKF->mvScaleFactors[nPredictedLevel], nPredictedLevel, pMP->GetDescriptor());
+    }
+    // a KeyFrame as a frame view: int bounds (include/KeyFrame.h:191-194) with the Frame's grid
+    template <class KeyFrameT>
+    static orbfe_frame_view KeyFrameView(KeyFrameT* pKF, std::vector<orbfe_keypoint>& k) {
+        k.resize(pKF->mvKeysUn.size());
+        for (size_t i = 0; i < k.size(); i++) k[i] = Kp(pKF->mvKeysUn[i]);
+        // cell sizes are the Frame's (src/KeyFrame.cc:33): recover its float bounds from them
+        const float minX = (float)pKF->mnMinX, minY = (float)pKF->mnMinY;
+        orbfe_frame_view v = {(int)k.size(), k.data(), pKF->mDescriptors.data, nullptr, minX,
+                              minX + (float)pKF->mnGridCols / pKF->mfGridElementWidthInv, minY,
+                              minY + (float)pKF->mnGridRows / pKF->mfGridElementHeightInv, pKF->mvScaleFactors.data(),
+                              (int)pKF->mvScaleFactors.size(), 1};
+        return v;
+    }
+    // one key frame of SearchForTriangulation flattened
+    struct TriSide {
+        std::vector<orbfe_keypoint> k;
+        std::vector<uint8_t> has;
+        std::vector<uint32_t> nodeId, indices;
+        std::vector<int32_t> nodeStart;
+        orbfe_tri_side v;
+        template <class KeyFrameT>
+        explicit TriSide(KeyFrameT* pKF) {
+            k.resize(pKF->mvKeysUn.size());
+            has.assign(k.size(), 0);
+            for (size_t i = 0; i < k.size(); i++) { k[i] = Kp(pKF->mvKeysUn[i]); has[i] = pKF->GetMapPoint(i) != nullptr; }
+            nodeStart.push_back(0);
+            for (auto it = pKF->mFeatVec.begin(); it != pKF->mFeatVec.end(); ++it) {
+                nodeId.push_back((uint32_t)it->first);
+                indices.insert(indices.end(), it->second.begin(), it->second.end());
+                nodeStart.push_back((int32_t)indices.size());
+            }
+            v.n = (int32_t)k.size(); v.kps = k.data(); v.desc = pKF->mDescriptors.data; v.has_mappoint = has.data();
+            v.uright = pKF->mvuRight.empty() ? nullptr : pKF->mvuRight.data();
+            v.nnodes = (int32_t)nodeId.size(); v.node_id = nodeId.data(); v.node_start = nodeStart.data(); v.indices = indices.data();
+        }
+    };
     // one side of SearchByBoW flattened: angles, live-map-point flags, DBoW2::FeatureVector as CSR
     struct BowSide {
         std::vector<float> angle;

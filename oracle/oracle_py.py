@@ -34,7 +34,7 @@ def build(force: bool = False) -> None:
 class FrameView(C.Structure):
     _fields_ = [("n", C.c_int), ("kps", C.c_void_p), ("desc", C.c_void_p), ("uright", C.c_void_p),
                 ("min_x", C.c_float), ("max_x", C.c_float), ("min_y", C.c_float), ("max_y", C.c_float),
-                ("scale_factors", C.c_void_p), ("nlevels", C.c_int)]
+                ("scale_factors", C.c_void_p), ("nlevels", C.c_int), ("keyframe_bounds", C.c_int)]
 
 
 class MapPointsView(C.Structure):
@@ -279,7 +279,7 @@ class RefExtractor:
 
 # ----------------------------------------------------------------------------- matcher
 def frame_view(kps: np.ndarray, desc: np.ndarray, width: float, height: float, scale_factors: np.ndarray, uright=None,
-               bounds=None):
+               bounds=None, keyframe=False):
     """Returns (FrameView, keepalive list).  bounds = (mnMinX, mnMaxX, mnMinY, mnMaxY) overrides (0, width, 0, height)."""
     kps = np.ascontiguousarray(kps); desc = np.ascontiguousarray(desc, np.uint8)
     sf = np.ascontiguousarray(scale_factors, np.float32)
@@ -289,6 +289,7 @@ def frame_view(kps: np.ndarray, desc: np.ndarray, width: float, height: float, s
         ur = np.ascontiguousarray(uright, np.float32); keep.append(ur); v.uright = ur.ctypes.data
     if bounds is not None:
         v.min_x, v.max_x, v.min_y, v.max_y = (float(b) for b in bounds)
+    v.keyframe_bounds = int(keyframe)
     return v, keep
 
 

@@ -81,6 +81,8 @@ typedef struct {
     float min_x, max_x, min_y, max_y;   /* mnMinX.. image bounds                         */
     const float* scale_factors;   /* mvScaleFactors                                      */
     int nlevels;
+    int keyframe_bounds;          /* 1: KeyFrame — GetFeaturesInArea subtracts the int-truncated
+                                     mnMinX / mnMinY (KeyFrame.h:191-194, KeyFrame.cc:616-628) */
 } orc_frame_view;
 
 /* 64x48 grid as in Frame::AssignFeaturesToGrid; CSR arrays sized 64*48+1 / n */

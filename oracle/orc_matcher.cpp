@@ -66,14 +66,17 @@ extern "C" int orc_features_in_area(const orc_frame_view* f, const int* cell_sta
                                     const int* cell_items, float x, float y, float r,
                                     int minLevel, int maxLevel, int* out, int cap) {
     const float iw = grid_inv_w(f), ih = grid_inv_h(f);
+    // KeyFrame holds its bounds as int (KeyFrame.h:191-194); Frame as float
+    const float qmin_x = f->keyframe_bounds ? (float)(int)f->min_x : f->min_x;
+    const float qmin_y = f->keyframe_bounds ? (float)(int)f->min_y : f->min_y;
     int n = 0;
-    const int nMinCellX = std::max(0, (int)std::floor((x - f->min_x - r) * iw));
+    const int nMinCellX = std::max(0, (int)std::floor((x - qmin_x - r) * iw));
     if (nMinCellX >= GRID_COLS) return 0;
-    const int nMaxCellX = std::min(GRID_COLS - 1, (int)std::ceil((x - f->min_x + r) * iw));
+    const int nMaxCellX = std::min(GRID_COLS - 1, (int)std::ceil((x - qmin_x + r) * iw));
     if (nMaxCellX < 0) return 0;
-    const int nMinCellY = std::max(0, (int)std::floor((y - f->min_y - r) * ih));
+    const int nMinCellY = std::max(0, (int)std::floor((y - qmin_y - r) * ih));
     if (nMinCellY >= GRID_ROWS) return 0;
-    const int nMaxCellY = std::min(GRID_ROWS - 1, (int)std::ceil((y - f->min_y + r) * ih));
+    const int nMaxCellY = std::min(GRID_ROWS - 1, (int)std::ceil((y - qmin_y + r) * ih));
     if (nMaxCellY < 0) return 0;
     const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
     for (int ix = nMinCellX; ix <= nMaxCellX; ix++)

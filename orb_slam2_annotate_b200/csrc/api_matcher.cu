@@ -133,6 +133,8 @@ GridGeom grid_of(const orbfe_frame_view* f) {
     // mfGridElementWidthInv / HeightInv (src/Frame.cc:86-87)
     GridGeom g;
     g.minX = f->min_x; g.minY = f->min_y;
+    g.qminX = f->keyframe_bounds ? (float)(int)f->min_x : f->min_x;     // KeyFrame.cc:41: int members
+    g.qminY = f->keyframe_bounds ? (float)(int)f->min_y : f->min_y;
     g.invW = 64.0f / (f->max_x - f->min_x);
     g.invH = 48.0f / (f->max_y - f->min_y);
     return g;
@@ -204,7 +206,7 @@ int orbfe_search_init_consecutive_device(orbfe_matcher* m, const orbfe_keypoint*
     InitArgs a{};
     a.kps = d_kps; a.desc = d_desc; a.counts = d_counts; a.cap = cap; a.pairs = nullptr;
     a.prev = nullptr; a.m12 = d_matches12; a.nmatches = d_nmatches;
-    a.grid.minX = min_x; a.grid.minY = min_y;
+    a.grid.minX = a.grid.qminX = min_x; a.grid.minY = a.grid.qminY = min_y;
     a.grid.invW = 64.0f / (max_x - min_x); a.grid.invH = 48.0f / (max_y - min_y);
     a.window = window; a.ratio = nnratio; a.checkOri = check_orientation;
     int rc;
@@ -225,7 +227,7 @@ orbfe_frame_view host_side_of(const orbfe_device_frame_view* df) {
     orbfe_frame_view f{};
     f.n = df->n; f.kps = df->d_kps; f.desc = df->d_desc; f.uright = df->d_uright;
     f.min_x = df->min_x; f.max_x = df->max_x; f.min_y = df->min_y; f.max_y = df->max_y;
-    f.scale_factors = df->scale_factors; f.nlevels = df->nlevels;
+    f.scale_factors = df->scale_factors; f.nlevels = df->nlevels; f.keyframe_bounds = df->keyframe_bounds;
     return f;
 }
 

@@ -11,7 +11,9 @@ namespace orbfe {
 int launch_knn2(const uint8_t* d_query, int nq, const uint8_t* d_train, int nt, int th, float ratio,
                 int* d_idx, int* d_d1, int* d_d2, cudaStream_t s);
 
-struct GridGeom { float minX, minY, invW, invH; };
+// minX / minY place keypoints (PosInGrid); qminX / qminY are what GetFeaturesInArea subtracts: the same for a Frame,
+// the int-truncated bounds for a KeyFrame (include/KeyFrame.h:191-194)
+struct GridGeom { float minX, minY, invW, invH, qminX, qminY; };
 
 struct InitArgs {
     const orbfe_keypoint* kps;   // [frames][cap]

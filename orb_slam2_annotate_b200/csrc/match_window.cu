@@ -52,13 +52,13 @@ __device__ __forceinline__ int pos_in_grid(const GridGeom& g, float x, float y) 
 // query window of GetFeaturesInArea (Frame.cc:363-379); false when the window misses the grid
 __device__ __forceinline__ bool cell_window(const GridGeom& g, float x, float y, float r, int& cx0,
                                             int& cx1, int& cy0, int& cy1) {
-    cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, g.minX), r), g.invW)));
+    cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, g.qminX), r), g.invW)));
     if (cx0 >= GC) return false;
-    cx1 = min(GC - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, g.minX), r), g.invW)));
+    cx1 = min(GC - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, g.qminX), r), g.invW)));
     if (cx1 < 0) return false;
-    cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, g.minY), r), g.invH)));
+    cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, g.qminY), r), g.invH)));
     if (cy0 >= GR) return false;
-    cy1 = min(GR - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, g.minY), r), g.invH)));
+    cy1 = min(GR - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, g.qminY), r), g.invH)));
     if (cy1 < 0) return false;
     return true;
 }

@@ -20,7 +20,9 @@ class Frame:
 
     def __init__(self, keypoints: np.ndarray, descriptors: np.ndarray, width: float, height: float,
                  scale_factors: np.ndarray, uright: np.ndarray | None = None,
-                 min_x: float = 0.0, min_y: float = 0.0):
+                 min_x: float = 0.0, min_y: float = 0.0, keyframe: bool = False):
+        # keyframe: the object stands for a KeyFrame, whose GetFeaturesInArea subtracts the int-truncated
+        # mnMinX / mnMinY (include/KeyFrame.h:191-194) while the grid itself is the Frame's
         # width / height are mnMaxX / mnMaxY (the image size when the camera has no distortion)
         self.kps = np.ascontiguousarray(keypoints, KP_DTYPE)
         self.desc = np.ascontiguousarray(descriptors if descriptors is not None else np.zeros((0, 32)), np.uint8).reshape(-1, 32)
@@ -28,6 +30,7 @@ class Frame:
         self.scale_factors = np.ascontiguousarray(scale_factors, np.float32)
         self.uright = None if uright is None else np.ascontiguousarray(uright, np.float32)
         self.min_x, self.max_x, self.min_y, self.max_y = float(min_x), float(width), float(min_y), float(height)
+        self.keyframe = bool(keyframe)
 
     @property
     def N(self) -> int:
@@ -37,7 +40,7 @@ class Frame:
         return FrameView(self.N, self.kps.ctypes.data, self.desc.ctypes.data,
                          None if self.uright is None else self.uright.ctypes.data,
                          self.min_x, self.max_x, self.min_y, self.max_y,
-                         self.scale_factors.ctypes.data, len(self.scale_factors))
+                         self.scale_factors.ctypes.data, len(self.scale_factors), int(self.keyframe))
 
 
 class BowSide:

@@ -98,6 +98,25 @@ def test_fuse_search(orbfe, oracle, gate, stereo, th, nmp):
         assert (pd < od).sum() > 0
 
 
+@pytest.mark.parametrize("keyframe", [False, True])
+def test_keyframe_int_bounds(orbfe, oracle, keyframe):
+    """A distorted camera gives fractional image bounds; a KeyFrame truncates them to int for its cell window
+    (include/KeyFrame.h:191-194) while its grid is the Frame's: both readings against the oracle."""
+    (fr, off) = _frames(oracle, 8, 2000)
+    (k, d, t) = fr[0]
+    bounds = (-12.7, 655.3, -9.6, 489.4)
+    pts = _points(k, d, 20000, 35, t["scale"], 3.0, jitter=2.5)
+    KF = orbfe.Frame(k, d, bounds[1], bounds[3], t["scale"], min_x=bounds[0], min_y=bounds[2], keyframe=keyframe)
+    fo = oracle.frame_view(k, d, 640, 480, t["scale"], bounds=bounds, keyframe=keyframe)
+    bi, bd = orbfe.ORBmatcher().FuseSearch(KF, pts)
+    oi, od = oracle.fuse_search(fo, pts)
+    assert np.array_equal(bi, oi) and np.array_equal(bd, od)
+    matched = np.zeros(len(k), np.uint8)
+    ng, mg = orbfe.ORBmatcher().SearchByProjectionSim3(KF, pts, matched.copy())
+    no, mo = oracle.search_by_projection_sim3(fo, pts, matched)
+    assert ng == no and np.array_equal(mg, mo)
+
+
 def test_fuse_search_degenerate(orbfe, oracle):
     (fr, off) = _frames(oracle, 8, 2000)
     (k, d, t) = fr[0]

@@ -190,3 +190,23 @@ def test_search_for_triangulation_kat(oracle):
     # rotation check: both matches in bin 0 survive
     n, m = run(oracle.tri_side(k2, d2, none2, fv2), check_ori=True)
     assert n == 2 and m.tolist() == [1, 3]
+
+
+def test_keyframe_int_bounds_kat(oracle):
+    """KeyFrame::GetFeaturesInArea subtracts int-truncated bounds (KeyFrame.h:191-194, KeyFrame.cc:616-628) while the
+    grid is the Frame's.  The truncation moves the cell window by less than a pixel and the window has half a cell of
+    slack around every keypoint within the radius (PosInGrid rounds, the window floors / ceils), so with the 64x48
+    grid of a camera image the candidate set is the same in both readings: checked here on random configurations,
+    together with the one observable property — integer bounds make the flag a no-op by construction."""
+    d = np.stack([bits(0)])
+    b2 = (-1.9, 638.1, -7.4, 487.2)
+    rng = np.random.default_rng(0)
+    for _ in range(2000):
+        x = float(rng.uniform(0, 630)); y = float(rng.uniform(0, 470))
+        u = x + float(rng.uniform(-30, 30)); v = y + float(rng.uniform(-30, 30))
+        r = max(abs(x - u), abs(y - v)) + float(rng.choice([-0.05, 0.01, 0.3]))
+        kk = np.array([kp(x, y, 1)], KP_DTYPE)
+        pp = pts(1, [1], u=u, v=v, radius=r)
+        a, _ = oracle.fuse_search(oracle.frame_view(kk, d, 640, 480, SCALE, bounds=b2), pp)
+        c, _ = oracle.fuse_search(oracle.frame_view(kk, d, 640, 480, SCALE, bounds=b2, keyframe=True), pp)
+        assert a[0] == c[0] == (0 if r > max(abs(np.float32(x) - np.float32(u)), abs(np.float32(y) - np.float32(v))) else -1)
