@@ -192,6 +192,55 @@ def guided_search_timings(frame_img):
     }
 
 
+def stereo_timings(npairs=128):
+    """configs[2] beside the CPU: `npairs` KITTI-shape 1241x376 stereo pairs, nFeatures 2000 — both images extracted
+    (one interleaved host batch through the C ABI, copies included) and Frame::ComputeStereoMatches on the
+    device-resident results; CPU = the unmodified reference extractor on both images + the oracle's restatement of
+    ComputeStereoMatches, one core, 2 pairs."""
+    from oracle import oracle_py as O
+    import orb_slam2_annotate_b200 as orbfe
+    from orb_slam2_annotate_b200 import synth
+    distinct = [synth.stereo_pair(1241, 376, seed=s, disparity=20) for s in range(4)]
+    imgs = orbfe.pinned_empty((2 * npairs, 376, 1241), np.uint8)
+    for p in range(npairs):
+        imgs[2 * p], imgs[2 * p + 1] = distinct[p % 4]
+    mbf = 386.1448; mb = mbf / 718.856
+    ex = orbfe.ORBextractor(2000)
+    mt = orbfe.ORBmatcher()
+    cap = ex.max_keypoints()
+    out = (orbfe.pinned_empty((2 * npairs, cap), orbfe.KP_DTYPE), orbfe.pinned_empty((2 * npairs, cap, 32), np.uint8),
+           orbfe.pinned_empty((2 * npairs,), np.int32))
+    ex.extract_batch(imgs, out=out)
+
+    def gpu():
+        ex.extract_batch(imgs, out=out)
+        return mt.ComputeStereoMatchesBatch(ex, npairs, mbf, mb)
+
+    def gpu_match_only():
+        return mt.ComputeStereoMatchesBatch(ex, npairs, mbf, mb)
+    ur, _ = gpu()
+    ts, tm = [], []
+    for _ in range(3):
+        t0 = time.perf_counter(); gpu(); ts.append(time.perf_counter() - t0)
+        t0 = time.perf_counter(); gpu_match_only(); tm.append(time.perf_counter() - t0)
+    kind = "reference" if O.ref_lib("_native") is not None else "port"
+    t0 = time.perf_counter()
+    for p in range(2):
+        fr = []
+        for im in distinct[p]:
+            oc = O.RefExtractor(2000, variant="_native") if kind == "reference" else O.OracleExtractor(2000)
+            k, d = oc(im)
+            fr.append((k, d, [np.ascontiguousarray(oc.level(l)) for l in range(8)]))
+        tb = O.OracleExtractor(2000).tables()
+        O.compute_stereo_matches(O.frame_view(fr[0][0], fr[0][1], 1241, 376, tb["scale"]), O.frame_view(fr[1][0], fr[1][1], 1241, 376, tb["scale"]),
+                                 O.pyramid_view(fr[0][2]), O.pyramid_view(fr[1][2]), tb["inv_scale"], mbf, mb)
+    cpu_ms = (time.perf_counter() - t0) * 1e3 / 2
+    return {"workload": "configs[2]: 1241x376 stereo pairs, nFeatures 2000, extract both + ComputeStereoMatches", "pairs": npairs,
+            "matched_per_pair": float((ur >= 0).sum() / npairs), "gpu_pairs_per_s": npairs / float(np.median(ts)),
+            "gpu_stereo_match_ms_per_pair": float(np.median(tm)) * 1e3 / npairs,
+            "cpu_ms_per_pair_one_core": cpu_ms, "cpu_kind": kind}
+
+
 def make_frames(batch, seed):
     """`batch` distinct frames: crops of one synthetic canvas with per-frame noise."""
     distinct = min(batch, 256)
@@ -507,6 +556,7 @@ def main():
             r = cpu_reference_fps(frames[:256], seconds_budget=15.0)
             line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
             line["guided_searches"] = guided_search_timings(frames[0])
+            line["stereo"] = stereo_timings()
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -457,6 +457,30 @@ int orbfe_stereo_match(orbfe_matcher* m, const orbfe_frame_view* left,
                        const orbfe_pyramid_view* pyr_right, const float* inv_scale_factors,
                        float mbf, float mb, float* uright, float* depth);
 
+/* mvImagePyramid of every frame of the extractor's last batch where it lies, in DEVICE memory: level l
+ * of frame b starts at d_data[l] + b * frame_stride[l], rows pitch[l] bytes apart, interior pixels only.
+ * The arrays belong to the handle and stay valid until its next extract call or size change. */
+typedef struct {
+    int32_t nlevels;
+    const uint8_t* const* d_data;
+    const int32_t* width;
+    const int32_t* height;
+    const ptrdiff_t* pitch;
+    const ptrdiff_t* frame_stride;
+} orbfe_device_pyramid_view;
+int orbfe_extractor_device_pyramid(orbfe_extractor* e, orbfe_device_pyramid_view* out);
+/* Frame::ComputeStereoMatches (src/Frame.cc:512-686) for npairs stereo pairs that went through the
+ * extractor as ONE batch with left and right images interleaved (frame 2p = left, 2p+1 = right of pair
+ * p): keypoints, descriptors, counts (orbfe_extractor_device_results) and both pyramids
+ * (orbfe_extractor_device_pyramid) are read in place, nothing is uploaded.  The extractor's work must
+ * have completed (any host-buffer extract call, or orbfe_extractor_sync).  uright / depth: HOST arrays
+ * [npairs][cap], -1 where there is no match and past the pair's left keypoint count. */
+int orbfe_stereo_match_batch_device(orbfe_matcher* m, const orbfe_device_pyramid_view* pyr,
+                                    const orbfe_keypoint* d_kps, const uint8_t* d_desc,
+                                    const int32_t* d_counts, int cap, int npairs,
+                                    const float* scale_factors, const float* inv_scale_factors,
+                                    int nlevels, float mbf, float mb, float* uright, float* depth);
+
 #ifdef __cplusplus
 }
 #endif

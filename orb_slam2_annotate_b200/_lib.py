@@ -75,6 +75,11 @@ class TriSideView(C.Structure):
                 ("indices", C.c_void_p)]
 
 
+class DevicePyramidView(C.Structure):
+    _fields_ = [("nlevels", C.c_int32), ("d_data", C.c_void_p), ("width", C.c_void_p), ("height", C.c_void_p),
+                ("pitch", C.c_void_p), ("frame_stride", C.c_void_p)]
+
+
 class PyramidView(C.Structure):
     _fields_ = [("nlevels", C.c_int32), ("data", C.c_void_p), ("width", C.c_void_p),
                 ("height", C.c_void_p), ("stride", C.c_void_p)]
@@ -145,6 +150,8 @@ SIGNATURES = {
     "orbfe_search_bow": (_i, [_vp, C.POINTER(BowView), C.POINTER(BowView), _i, _f, _i, _vp, _vp, _ip]),
     "orbfe_search_bow_batch": (_i, [_vp, _i, _vp, _vp, _i, _f, _i, _vp, _vp, _vp]),
     "orbfe_distinctive_descriptors": (_i, [_vp, _vp, _vp, _i, _vp]),
+    "orbfe_extractor_device_pyramid": (_i, [_vp, C.POINTER(DevicePyramidView)]),
+    "orbfe_stereo_match_batch_device": (_i, [_vp, C.POINTER(DevicePyramidView), _vp, _vp, _vp, _i, _i, _vp, _vp, _i, _f, _f, _vp, _vp]),
     "orbfe_stereo_match": (_i, [_vp, C.POINTER(FrameView), C.POINTER(FrameView), C.POINTER(PyramidView),
                                 C.POINTER(PyramidView), _vp, _f, _f, _vp, _vp]),
 }

@@ -6,6 +6,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <cstdlib>
 #include <vector>
 
 #include "api_common.cuh"
@@ -70,6 +71,10 @@ struct orbfe_extractor {
     bool profiling = false;
     cudaEvent_t ev[ORBFE_NUM_STAGES + 1] = {};
     std::vector<int> h_counts;
+    // orbfe_extractor_device_pyramid
+    std::vector<const uint8_t*> pv_data;
+    std::vector<int32_t> pv_w, pv_h;
+    std::vector<ptrdiff_t> pv_pitch, pv_fstride;
 };
 
 namespace orbfe {
@@ -605,6 +610,20 @@ int orbfe_extractor_device_results(orbfe_extractor* e, const orbfe_keypoint** d_
     return ORBFE_OK;
 }
 
+int orbfe_extractor_device_pyramid(orbfe_extractor* e, orbfe_device_pyramid_view* out) {
+    if (!e || !out || !e->geomW || !e->lastBatch) return fail(ORBFE_ERR_ARG, "no extraction has run on this handle");
+    const int L = e->g.nlevels;
+    e->pv_data.resize(L); e->pv_w.resize(L); e->pv_h.resize(L); e->pv_pitch.resize(L); e->pv_fstride.resize(L);
+    for (int l = 0; l < L; l++) {
+        const LevelGeom& G = e->g.lv[l];
+        e->pv_data[l] = e->d.pyr + G.pyrOff;     // level 0 may be the caller's own device frames
+        e->pv_w[l] = G.w; e->pv_h[l] = G.h; e->pv_pitch[l] = G.pitch; e->pv_fstride[l] = (ptrdiff_t)G.lvBytes;
+    }
+    out->nlevels = L; out->d_data = e->pv_data.data(); out->width = e->pv_w.data(); out->height = e->pv_h.data();
+    out->pitch = e->pv_pitch.data(); out->frame_stride = e->pv_fstride.data();
+    return ORBFE_OK;
+}
+
 int orbfe_extractor_fetch(orbfe_extractor* e, int batch, orbfe_keypoint* kps, uint8_t* desc, int cap,
                           int* counts) {
     if (!e || !kps || !desc || !counts || batch < 1 || batch > e->lastBatch)
@@ -637,7 +656,22 @@ int orbfe_extractor_fetch(orbfe_extractor* e, int batch, orbfe_keypoint* kps, ui
 static int extract_batch_pipelined(orbfe_extractor* e, const uint8_t* imgs, int batch, int w, int h,
                                    ptrdiff_t stride, ptrdiff_t frame_stride, orbfe_keypoint* kps,
                                    uint8_t* desc, int cap, int* counts, int chunk) {
-    const int nchunks = (batch + chunk - 1) / chunk;
+    // chunk schedule: the transfer link is the bottleneck, so the pipeline's fill (first upload, nothing to
+    // overlap with) and drain (last kernels + download) are kept short with small chunks at both ends
+    std::vector<int> first, count;
+    {
+        std::vector<int> sz;
+        int rem = batch;
+        const int taper = batch >= 6 * chunk ? 2 : 0;
+        int tail = 0;
+        for (int t = 0; t < taper; t++) { sz.push_back(chunk >> (2 - t)); rem -= sz.back(); tail += chunk >> (2 - t); }
+        rem -= tail;
+        while (rem > 0) { sz.push_back(std::min(chunk, rem)); rem -= sz.back(); }
+        for (int t = taper - 1; t >= 0; t--) sz.push_back(chunk >> (2 - t));
+        int f = 0;
+        for (int v : sz) { first.push_back(f); count.push_back(v); f += v; }
+    }
+    const int nchunks = (int)count.size();
     {
         const int rc0 = set_level0_source(e, nullptr);
         if (rc0) return rc0;
@@ -663,7 +697,7 @@ static int extract_batch_pipelined(orbfe_extractor* e, const uint8_t* imgs, int 
     CU(cudaEventRecord(e->evDone[0], e->stream));
     CU(cudaStreamWaitEvent(e->h2dStream, e->evDone[0], 0));
     for (int c = 0; c < nchunks; c++) {
-        const int f0 = c * chunk, n = std::min(chunk, batch - f0);
+        const int f0 = first[c], n = count[c];
         uint8_t* dst = e->d.pyr + L0.pyrOff + (long long)f0 * L0.lvBytes;
         const uint8_t* src = imgs + (long long)f0 * frame_stride;
         if (frame_stride == (ptrdiff_t)h * stride && stride == L0.pitch) {
@@ -714,7 +748,7 @@ int orbfe_extract_batch(orbfe_extractor* e, const uint8_t* imgs, int batch, int 
     CU(cudaSetDevice(e->device));
     int rc = ensure_geometry(e, width, height, batch);
     if (rc) return rc;
-    const int chunk = 64;
+    static const int chunk = [] { const char* v = std::getenv("ORBFE_CHUNK"); const int c = v ? std::atoi(v) : 0; return c >= 8 ? c : 64; }();
     if (batch >= 4 * chunk) {
         e->lastBatch = batch;
         return extract_batch_pipelined(e, imgs, batch, width, height, stride, frame_stride, kps, desc, cap, counts, chunk);

@@ -952,3 +952,52 @@ extern "C" int orbfe_stereo_match(orbfe_matcher* m, const orbfe_frame_view* left
     CU(cudaStreamSynchronize(s));
     return ORBFE_OK;
 }
+
+// Frame::ComputeStereoMatches for a batch of interleaved stereo pairs, device resident
+extern "C" int orbfe_stereo_match_batch_device(orbfe_matcher* m, const orbfe_device_pyramid_view* pyr,
+                                               const orbfe_keypoint* d_kps, const uint8_t* d_desc, const int32_t* d_counts,
+                                               int cap, int npairs, const float* scale_factors,
+                                               const float* inv_scale_factors, int nlevels, float mbf, float mb,
+                                               float* uright, float* depth) {
+    if (!m || !pyr || !scale_factors || !inv_scale_factors || !(mb > 0) || npairs < 0 || cap < 0)
+        return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_stereo_match_batch_device");
+    if (npairs == 0 || cap == 0) return ORBFE_OK;
+    if (!d_kps || !d_desc || !d_counts || !uright || !depth || nlevels < 1 || nlevels > kMaxLevels || pyr->nlevels < nlevels)
+        return fail(ORBFE_ERR_ARG, "bad device arrays / pyramid in orbfe_stereo_match_batch_device");
+    if ((uintptr_t)d_desc & 15) return fail(ORBFE_ERR_ARG, "device descriptors must be 16-byte aligned");
+    CU(cudaSetDevice(m->device));
+    cudaStream_t s = m->stream;
+    int rc;
+    const size_t outN = (size_t)npairs * cap;
+    const size_t bytes = 2 * padded((size_t)nlevels * 4) + padded(2 * outN * 4) + padded(outN * 4);
+    if ((rc = m->scratch[0].ensure(bytes))) return rc;
+    if ((rc = m->stage.ensure(2 * padded((size_t)nlevels * 4)))) return rc;
+    if ((rc = m->result.ensure(2 * outN * 4))) return rc;
+    Arena A; A.base = m->scratch[0].p;
+    float* d_scale = A.take<float>(nlevels);
+    float* d_inv = A.take<float>(nlevels);
+    StereoArgs a{};
+    float* ud = A.take<float>(2 * outN);           // uright | depth, fetched with one copy
+    a.uright = ud; a.depth = ud + outN; a.sad = A.take<int>(outN);
+    if (A.off > bytes) return fail(ORBFE_ERR_CAPACITY, "internal: matcher arena overflow");
+    float* hs = reinterpret_cast<float*>(m->stage.p);
+    std::memcpy(hs, scale_factors, sizeof(float) * nlevels);
+    std::memcpy(hs + nlevels, inv_scale_factors, sizeof(float) * nlevels);
+    CU(cudaMemcpyAsync(d_scale, hs, sizeof(float) * nlevels, cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(d_inv, hs + nlevels, sizeof(float) * nlevels, cudaMemcpyHostToDevice, s));
+    for (int l = 0; l < nlevels; l++) {
+        a.imgl[l] = a.imgr[l] = pyr->d_data[l];
+        a.pitchl[l] = a.pitchr[l] = (int)pyr->pitch[l];
+        a.widthr[l] = pyr->width[l];
+        a.frameStride[l] = (long long)pyr->frame_stride[l];
+    }
+    a.batched = 1; a.cap = cap; a.counts = d_counts; a.kl = d_kps; a.dl = d_desc;
+    a.scale = d_scale; a.inv_scale = d_inv; a.nlevels = nlevels; a.nrows = pyr->height[0]; a.mbf = mbf; a.mb = mb;
+    launch_stereo(a, s, npairs);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(m->result.p, a.uright, 2 * outN * 4, cudaMemcpyDeviceToHost, s));   // uright and depth are adjacent
+    CU(cudaStreamSynchronize(s));
+    std::memcpy(uright, m->result.p, outN * 4);
+    std::memcpy(depth, m->result.p + outN * 4, outN * 4);
+    return ORBFE_OK;
+}

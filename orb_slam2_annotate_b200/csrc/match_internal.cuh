@@ -103,6 +103,11 @@ struct StereoArgs {
     float mbf, mb;
     float* uright; float* depth;
     int* sad;           // per left keypoint: truncated best SAD, or -1 when no match
+    // batched, device-resident form (orbfe_stereo_match_batch_device): pair p = frames 2p (left) and 2p+1 (right) of
+    // one extractor batch; kl / dl are the batch's [frames][cap] arrays, imgl[l] the level stacks, outputs [pairs][cap]
+    int batched, cap;
+    const int* counts;
+    long long frameStride[kMaxLevels];
 };
 
 // SearchByBoW: two sides = descriptors, keypoint angles, live-map-point flags (NULL = all) and the
@@ -161,6 +166,6 @@ int launch_guided_init(int* owners, int n, int nsweeps, bool reset_first, int* m
                        uint8_t* occ_out, const uint8_t* occ0, cudaStream_t st);
 int launch_local_finalize(const LocalArgs& a, int* mp_for_kp, uint8_t* occ_out, int* nmatches, cudaStream_t st);
 int launch_frame_finalize(const LocalArgs& a, int* mp_for_kp, int* nmatches, cudaStream_t st);
-int launch_stereo(const StereoArgs& a, cudaStream_t st);
+int launch_stereo(const StereoArgs& a, cudaStream_t st, int npairs = 1);
 
 }  // namespace orbfe

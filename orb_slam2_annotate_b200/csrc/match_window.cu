@@ -753,12 +753,38 @@ __global__ void __launch_bounds__(256) sim3_agree_kernel(const int* match1, cons
 // parabola in the reference's float op order.  A second single-CTA kernel reproduces the
 // median rule (:671-685) with a rank selection.
 
+// the operands of one stereo pair: the arguments themselves, or pair p of an interleaved extractor batch
+struct StereoPair {
+    int nl, nr;
+    const orbfe_keypoint* kl; const orbfe_keypoint* kr;
+    const uint8_t* dl; const uint8_t* dr;
+    float* uright; float* depth; int* sad;
+    long long fl, fr;        // frame indices of the left / right image inside the level stacks
+};
+__device__ __forceinline__ StereoPair stereo_pair(const StereoArgs& a, int p) {
+    StereoPair s;
+    if (!a.batched) {
+        s.nl = a.nl; s.nr = a.nr; s.kl = a.kl; s.kr = a.kr; s.dl = a.dl; s.dr = a.dr;
+        s.uright = a.uright; s.depth = a.depth; s.sad = a.sad; s.fl = s.fr = 0;
+        return s;
+    }
+    const long long fl = 2LL * p, fr = fl + 1;
+    s.nl = a.counts[fl]; s.nr = a.counts[fr];
+    s.kl = a.kl + fl * a.cap; s.kr = a.kl + fr * a.cap;
+    s.dl = a.dl + fl * a.cap * 32; s.dr = a.dl + fr * a.cap * 32;
+    s.uright = a.uright + (long long)p * a.cap; s.depth = a.depth + (long long)p * a.cap; s.sad = a.sad + (long long)p * a.cap;
+    s.fl = fl; s.fr = fr;
+    return s;
+}
+
 __global__ void __launch_bounds__(128) stereo_match_kernel(const __grid_constant__ StereoArgs a) {
     const int lane = threadIdx.x & 31;
     const int iL = blockIdx.x * 4 + (threadIdx.x >> 5);
-    if (iL >= a.nl) return;
-    if (lane == 0) { a.uright[iL] = -1.0f; a.depth[iL] = -1.0f; a.sad[iL] = -1; }
-    const orbfe_keypoint kpL = a.kl[iL];
+    const StereoPair P = stereo_pair(a, blockIdx.y);
+    if (a.batched && iL >= P.nl && iL < a.cap && lane == 0) { P.uright[iL] = -1.0f; P.depth[iL] = -1.0f; P.sad[iL] = -1; }
+    if (iL >= P.nl) return;
+    if (lane == 0) { P.uright[iL] = -1.0f; P.depth[iL] = -1.0f; P.sad[iL] = -1; }
+    const orbfe_keypoint kpL = P.kl[iL];
     const int levelL = kpL.octave;
     const float vL = kpL.y, uL = kpL.x;
     const int row = (int)vL;
@@ -766,18 +792,18 @@ __global__ void __launch_bounds__(128) stereo_match_kernel(const __grid_constant
     const float minZ = a.mb, minD = 0.0f, maxD = __fdiv_rn(a.mbf, minZ);                 // :542-545
     const float minU = __fsub_rn(uL, maxD), maxU = __fsub_rn(uL, minD);
     uint32_t q[8];
-    load_row(q, a.dl + 32 * (long long)iL);
+    load_row(q, P.dl + 32 * (long long)iL);
     uint32_t best = KEY_INF;
     int any = 0;
-    for (int iR = lane; iR < a.nr; iR += 32) {
-        const orbfe_keypoint kpR = a.kr[iR];
+    for (int iR = lane; iR < P.nr; iR += 32) {
+        const orbfe_keypoint kpR = P.kr[iR];
         const float r = __fmul_rn(2.0f, a.scale[kpR.octave]);                           // :532
         const int maxr = (int)ceilf(__fadd_rn(kpR.y, r)), minr = (int)floorf(__fsub_rn(kpR.y, r));
         if (row < minr || row > maxr) continue;
         any = 1;
         if (kpR.octave < levelL - 1 || kpR.octave > levelL + 1) continue;               // :582-583
         if (!(kpR.x >= minU && kpR.x <= maxU)) continue;                                // :587
-        const int dist = hamming256(q, a.dr + 32 * (long long)iR);
+        const int dist = hamming256(q, P.dr + 32 * (long long)iR);
         best = min(best, ((uint32_t)dist << 20) | (uint32_t)iR);
     }
     any = __any_sync(FULL, any);
@@ -790,13 +816,13 @@ __global__ void __launch_bounds__(128) stereo_match_kernel(const __grid_constant
     const int bestIdxR = (int)(best & 0xFFFFFu);
 
     // ---- sub-pixel refinement by correlation (:600-668)
-    const float uR0 = a.kr[bestIdxR].x;
+    const float uR0 = P.kr[bestIdxR].x;
     const float sf = a.inv_scale[levelL];
     const float scaleduL = roundf(__fmul_rn(kpL.x, sf)), scaledvL = roundf(__fmul_rn(kpL.y, sf));
     const float scaleduR0 = roundf(__fmul_rn(uR0, sf));
     const int w = 5, Lh = 5;
-    const uint8_t* IL = a.imgl[levelL]; const int sl = a.pitchl[levelL];
-    const uint8_t* IR = a.imgr[levelL]; const int sr = a.pitchr[levelL];
+    const uint8_t* IL = a.imgl[levelL] + P.fl * a.frameStride[levelL]; const int sl = a.pitchl[levelL];
+    const uint8_t* IR = a.imgr[levelL] + P.fr * a.frameStride[levelL]; const int sr = a.pitchr[levelL];
     const int v0 = (int)(scaledvL - w), uL0 = (int)(scaleduL - w);
     const float iniu = scaleduR0 + Lh - w, endu = scaleduR0 + Lh + w + 1;
     if (iniu < 0 || endu >= (float)a.widthr[levelL]) return;                            // :621
@@ -841,41 +867,57 @@ __global__ void __launch_bounds__(128) stereo_match_kernel(const __grid_constant
     if (disparity >= minD && disparity < maxD) {                                        // :658-668
         if (disparity <= 0) { disparity = 0.01f; bestuR = __fsub_rn(uL, 0.01f); }
         if (lane == 0) {
-            a.depth[iL] = __fdiv_rn(a.mbf, disparity);
-            a.uright[iL] = bestuR;
-            a.sad[iL] = sadBest;
+            P.depth[iL] = __fdiv_rn(a.mbf, disparity);
+            P.uright[iL] = bestuR;
+            P.sad[iL] = sadBest;
         }
     }
 }
 
 // median of the truncated SADs (element size/2 of the sorted list) and the 1.5*1.4*median cut
 __global__ void __launch_bounds__(256) stereo_median_kernel(const __grid_constant__ StereoArgs a) {
+    constexpr int MCAP = 4096;                       // matched keypoints staged in shared memory (more: global path)
     __shared__ int s_cnt, s_median;
+    __shared__ int s_vals[MCAP];
     const int tid = threadIdx.x;
+    const StereoPair P = stereo_pair(a, blockIdx.x);
     if (tid == 0) { s_cnt = 0; s_median = -1; }
     __syncthreads();
-    int c = 0;
-    for (int i = tid; i < a.nl; i += 256) c += a.sad[i] >= 0;
-    if (c) atomicAdd(&s_cnt, c);
+    for (int i = tid; i < P.nl; i += 256) {
+        const int v = P.sad[i];
+        if (v >= 0) {
+            const int slot = atomicAdd(&s_cnt, 1);   // the order of the list does not matter to a rank selection
+            if (slot < MCAP) s_vals[slot] = v;
+        }
+    }
     __syncthreads();
     const int m = s_cnt;
     if (m == 0) return;
     const int target = m / 2;                                                           // :672
-    for (int i = tid; i < a.nl; i += 256) {
-        const int v = a.sad[i];
-        if (v < 0) continue;
-        int less = 0, eq = 0;
-        for (int j = 0; j < a.nl; j++) {
-            const int u = a.sad[j];
-            if (u >= 0) { less += u < v; eq += u == v; }
+    if (m <= MCAP) {
+        for (int i = tid; i < m; i += 256) {
+            const int v = s_vals[i];
+            int less = 0, eq = 0;
+            for (int j = 0; j < m; j++) { const int u = s_vals[j]; less += u < v; eq += u == v; }
+            if (less <= target && target < less + eq) s_median = v;
         }
-        if (less <= target && target < less + eq) s_median = v;
+    } else {
+        for (int i = tid; i < P.nl; i += 256) {
+            const int v = P.sad[i];
+            if (v < 0) continue;
+            int less = 0, eq = 0;
+            for (int j = 0; j < P.nl; j++) {
+                const int u = P.sad[j];
+                if (u >= 0) { less += u < v; eq += u == v; }
+            }
+            if (less <= target && target < less + eq) s_median = v;
+        }
     }
     __syncthreads();
     const float thDist = __fmul_rn(__fmul_rn(1.5f, 1.4f), (float)s_median);             // :673
-    for (int i = tid; i < a.nl; i += 256) {
-        const int v = a.sad[i];
-        if (v >= 0 && !((float)v < thDist)) { a.uright[i] = -1.0f; a.depth[i] = -1.0f; }   // :675-685
+    for (int i = tid; i < P.nl; i += 256) {
+        const int v = P.sad[i];
+        if (v >= 0 && !((float)v < thDist)) { P.uright[i] = -1.0f; P.depth[i] = -1.0f; }   // :675-685
     }
 }
 
@@ -974,10 +1016,11 @@ int launch_sim3_agree(const int* match1, const int* match2, int n1, int n2, int*
     return 1;
 }
 
-int launch_stereo(const StereoArgs& a, cudaStream_t st) {
-    if (a.nl <= 0) return 0;
-    stereo_match_kernel<<<(a.nl + 3) / 4, 128, 0, st>>>(a);
-    stereo_median_kernel<<<1, 256, 0, st>>>(a);
+int launch_stereo(const StereoArgs& a, cudaStream_t st, int npairs) {
+    const int rows = a.batched ? a.cap : a.nl;      // batched: one warp per keypoint slot (counts live on the device)
+    if (rows <= 0 || npairs <= 0) return 0;
+    stereo_match_kernel<<<dim3((rows + 3) / 4, npairs), 128, 0, st>>>(a);
+    stereo_median_kernel<<<npairs, 256, 0, st>>>(a);
     return 2;
 }
 

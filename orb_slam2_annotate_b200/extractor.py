@@ -173,6 +173,12 @@ class ORBextractor:
         v._keep = self._scale
         return v
 
+    def device_pyramid(self):
+        """``_lib.DevicePyramidView`` of the last batch (mvImagePyramid of every frame, in device memory)."""
+        v = _lib.DevicePyramidView()
+        check(self._L.orbfe_extractor_device_pyramid(self._h, C.byref(v)), "orbfe_extractor_device_pyramid")
+        return v
+
     STAGES = ("upload", "pyramid", "fast", "blur", "octree", "orient_desc", "frame")
 
     def set_profiling(self, on: bool = True) -> None:

@@ -482,6 +482,20 @@ class ORBmatcher:
                                          ce.ctypes.data, it.ctypes.data, C.byref(k)), "orbfe_frame_assign")
         return un[:n], ce, it[:k.value]
 
+    def ComputeStereoMatchesBatch(self, extractor, npairs: int, mbf: float, mb: float):
+        """Frame::ComputeStereoMatches (src/Frame.cc:512-686) for the ``npairs`` stereo pairs of the extractor's last batch
+        (frames 2p / 2p+1 = left / right of pair p), read where they lie in device memory.
+        -> (mvuRight float32[npairs, cap], mvDepth float32[npairs, cap]); cap = extractor.max_keypoints"""
+        kp, ds, cn, cap = extractor.device_results()
+        pv = extractor.device_pyramid()
+        sf = np.ascontiguousarray(extractor.GetScaleFactors(), np.float32)
+        isf = np.ascontiguousarray(extractor.GetInverseScaleFactors(), np.float32)
+        ur = np.empty((max(npairs, 1), cap), np.float32); dp = np.empty((max(npairs, 1), cap), np.float32)
+        check(self._L.orbfe_stereo_match_batch_device(self._h, C.byref(pv), kp, ds, cn, cap, npairs, sf.ctypes.data, isf.ctypes.data,
+                                                      len(sf), mbf, mb, ur.ctypes.data, dp.ctypes.data),
+              "orbfe_stereo_match_batch_device")
+        return ur[:npairs], dp[:npairs]
+
     def ComputeStereoMatches(self, left: Frame, right: Frame, pyr_left: list, pyr_right: list,
                              inv_scale_factors: np.ndarray, mbf: float, mb: float):
         """Frame::ComputeStereoMatches — src/Frame.cc:512-686. -> (mvuRight f32[N], mvDepth f32[N])"""

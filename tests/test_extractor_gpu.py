@@ -139,15 +139,16 @@ def test_reference_tu_agrees(orbfe, oracle):
     _compare_frame(kg, dg, kr, dr)
 
 
-def test_pipelined_host_batch(orbfe, oracle):
-    """Host batches of >= 256 frames take the chunked three-stream path (H2D / kernels / D2H overlap)."""
+@pytest.mark.parametrize("B", [261, 429])
+def test_pipelined_host_batch(orbfe, oracle, B):
+    """Host batches of >= 256 frames take the chunked three-stream path (H2D / kernels / D2H overlap); from 384
+    frames on the chunk schedule is tapered (16, 32, 64 ... 64, remainder, 32, 16)."""
     distinct = np.stack([synth.frame(320, 240, 20 + s) for s in range(5)])
-    B = 261
     imgs = np.ascontiguousarray(distinct[np.arange(B) % 5])
     ex = orbfe.ORBextractor(500)
     kps, desc, counts = ex.extract_batch(imgs)
     ref = [oracle.OracleExtractor(500)(distinct[s]) for s in range(5)]
-    for b in (0, 1, 63, 64, 127, 128, 255, 256, 260):
+    for b in (0, 1, 15, 16, 47, 48, 63, 64, 127, 128, 255, 256, 260, B - 49, B - 48, B - 17, B - 16, B - 1):
         ko, do = ref[b % 5]
         n = counts[b]
         _compare_frame(kps[b, :n], desc[b, :n], ko, do)

@@ -152,6 +152,35 @@ def test_compute_stereo_matches(orbfe, oracle):
         assert (ug >= 0).sum() > 100
 
 
+def test_compute_stereo_matches_batch_device(orbfe, oracle):
+    """Three stereo pairs through the extractor as one interleaved batch, then ComputeStereoMatches on the
+    device-resident keypoints / descriptors / pyramids: mvuRight and mvDepth bit-exact against the oracle."""
+    pairs = [synth.stereo_pair(1241, 376, seed=s, disparity=20) for s in (0, 1, 2)]
+    imgs = np.ascontiguousarray(np.stack([im for pr in pairs for im in pr]))
+    ex = orbfe.ORBextractor(2000)
+    kps, desc, counts = ex.extract_batch(imgs)
+    mbf = 386.1448; mb = mbf / 718.856
+    ug, dg = orbfe.ORBmatcher().ComputeStereoMatchesBatch(ex, 3, mbf, mb)
+    for p, seed in enumerate((0, 1, 2)):
+        if seed < 2:
+            (kl, dl, pl, t), (kr, dr, pr, _) = _frames(oracle, "stereo", seed, 2000)
+        else:
+            fr = []
+            for im in pairs[p]:
+                oc = oracle.OracleExtractor(2000)
+                k, d = oc(im)
+                fr.append((k, d, [oc.level(l) for l in range(8)], oc.tables()))
+            (kl, dl, pl, t), (kr, dr, pr, _) = fr
+        nl = counts[2 * p]
+        assert nl == len(kl) and counts[2 * p + 1] == len(kr)
+        uo, do = oracle.compute_stereo_matches(oracle.frame_view(kl, dl, 1241, 376, t["scale"]),
+                                               oracle.frame_view(kr, dr, 1241, 376, t["scale"]),
+                                               oracle.pyramid_view(pl), oracle.pyramid_view(pr), t["inv_scale"], mbf, mb)
+        assert ug[p, :nl].tobytes() == uo.tobytes() and dg[p, :nl].tobytes() == do.tobytes()
+        assert (ug[p, nl:] == -1).all() and (dg[p, nl:] == -1).all()
+        assert (ug[p, :nl] >= 0).sum() > 100
+
+
 def _feat_vec(desc, octave, nbits, rng=None, drop=0.0):
     """Stand-in for DBoW2's FeatureVector: node id from the octave and the low `nbits` bits of the first
     descriptor byte, so that look-alike features of two frames mostly share a node."""
