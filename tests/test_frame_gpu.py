@@ -163,3 +163,18 @@ def test_guided_searches_on_resident_frames(orbfe, oracle):
         no, mo = oracle.search_by_projection_frame(oracle.frame_view(k, d, W, H, scale, bounds=bounds), pts, True, occ)
         assert ng == no and np.array_equal(mg, mo)
         assert ng > 20
+        # the key-frame overloads on the resident frame: SearchByProjection(F, KF) and the Fuse search (TUM1 is a
+        # distorted camera, so the bounds are fractional and the KeyFrame reading truncates them)
+        kp = dict(valid=pts["valid"], u=pts["u"], v=pts["v"], radius=(10.0 * scale[ka["octave"]]).astype(np.float32),
+                  level=ka["octave"].astype(np.int32), angle=pts["angle"], desc=da)
+        ng, mg = mt.SearchByProjectionKeyFrame(dv, kp, 80, occ.copy())
+        no, mo = oracle.search_by_projection_keyframe(oracle.frame_view(k, d, W, H, scale, bounds=bounds), kp, 80, True, occ)
+        assert ng == no and np.array_equal(mg, mo) and ng > 20
+        isig = (np.float32(1.0) / (scale * scale)).astype(np.float32)
+        for keyframe in (0, 1):
+            dv.keyframe_bounds = keyframe
+            for sig in (isig, None):             # with Fuse's reprojection gate (few survive: the points come from another frame) / without
+                bi, bd = mt.FuseSearch(dv, kp, sig)
+                oi, od = oracle.fuse_search(oracle.frame_view(k, d, W, H, scale, bounds=bounds, keyframe=bool(keyframe)), kp, sig)
+                assert np.array_equal(bi, oi) and np.array_equal(bd, od) and (bi >= 0).sum() > (0 if sig is not None else 20)
+        dv.keyframe_bounds = 0
