@@ -201,12 +201,15 @@ struct alignas(128) WarpSmem {
     unsigned long long bar;                               // mbarrier of the window load
 };
 
-__device__ __forceinline__ uint32_t swar_gt(uint32_t d, uint32_t c, bool small_t) {
+// per byte d > t: bit 7 of (d & 0x7F) + (0x7F - t) is "low seven bits > t" for t < 128 (then OR the byte's own bit 7),
+// and with c = 0x7F - (t - 128) "low seven bits > t - 128" for t >= 128 (then AND it)
+template <bool SMALL_T>
+__device__ __forceinline__ uint32_t swar_gt_t(uint32_t d, uint32_t c) {
     const uint32_t m = (d & 0x7F7F7F7Fu) + c;       // per byte, no carry across bytes
-    return (small_t ? (m | d) : (m & d)) & 0x80808080u;
+    return (SMALL_T ? (m | d) : (m & d)) & 0x80808080u;
 }
 
-template <int WWIN>
+template <int WWIN, bool SMALL_T>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
 fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ FastMaps maps,
                        const int4* __restrict__ celltab, int* __restrict__ cellc, uint32_t* __restrict__ cellk, int cellLo, int cellHi) {
@@ -277,29 +280,28 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const __grid_cons
     int total = 0;
     for (int pass = 0; pass < 2; pass++) {
         const int t = pass == 0 ? g.iniTh : g.minTh;
-        const bool small_t = t < 128;
+        // SMALL_T: both thresholds are below 128 (every configuration the reference ships); otherwise decided per pass
+        const bool small_t = SMALL_T || t < 128;
         const uint32_t cmpc = (uint32_t)(small_t ? 0x7F - t : 0x7F - (t - 128)) * 0x01010101u;
+        auto swar_gt = [&](uint32_t dd, uint32_t cc, bool) { return SMALL_T ? swar_gt_t<true>(dd, cc) : (small_t ? swar_gt_t<true>(dd, cc) : swar_gt_t<false>(dd, cc)); };
         // ---- stage 1a: vertical pair (0,8) on every zone word; surviving words are compacted
         // (ballot order) into a task list that borrows the score map's storage
         uint32_t* tasks = reinterpret_cast<uint32_t*>(&S.sc[0][0]);
         int ntask = 0;
         if (rpi == 3) {
-            uint32_t ce = 0, g_up = 0;
-            if (act) {
-                ce = wcol[3 * WS];
-                g_up = swar_gt(__vabsdiffu4(wcol[0], ce), cmpc, small_t);
-            }
+            // loads are unconditional (rows past the zone and the idle lanes read other parts of this warp's shared
+            // block and are masked out), so the loop body has no divergent branch
+            uint32_t ce = wcol[3 * WS];
+            uint32_t g_up = swar_gt(__vabsdiffu4(wcol[0], ce), cmpc, small_t);
+            const uint32_t zma = act ? zm : 0u;
+            const uint32_t tag = (uint32_t)rsub | ((uint32_t)cc1 << 8);
             for (int r0 = 0; r0 < zh; r0 += 3) {
-                const int r = r0 + rsub;
-                uint32_t gmask = 0;
-                if (act && r < zh) {
-                    const uint32_t dn = wcol[(r0 + 6) * WS];
-                    const uint32_t g_dn = swar_gt(__vabsdiffu4(dn, ce), cmpc, small_t);
-                    gmask = (g_up | g_dn) & zm;
-                    ce = dn; g_up = g_dn;                        // |centre - below| is |above - centre| of the next step
-                }
+                const uint32_t dn = wcol[(r0 + 6) * WS];
+                const uint32_t g_dn = swar_gt(__vabsdiffu4(dn, ce), cmpc, small_t);
+                const uint32_t gmask = (g_up | g_dn) & (r0 + rsub < zh ? zma : 0u);
+                ce = dn; g_up = g_dn;                            // |centre - below| is |above - centre| of the next step
                 const uint32_t bal = __ballot_sync(0xFFFFFFFFu, gmask != 0);
-                if (gmask) tasks[ntask + __popc(bal & ((1u << lane) - 1u))] = gmask | (uint32_t)r | ((uint32_t)cc1 << 8);
+                if (gmask) tasks[ntask + __popc(bal & ((1u << lane) - 1u))] = gmask | (tag + (uint32_t)r0);
                 ntask += __popc(bal);
             }
         } else {
@@ -431,8 +433,10 @@ int launch_fast(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
         if (v == 0) generic = true;
         if (v > 0 && hi > lo) {
             const dim3 grid((hi - lo + kWarpsPerCta - 1) / kWarpsPerCta, g.batch);
-            if (v == 40) fast_cells_warp_kernel<40><<<grid, kWarpsPerCta * 32, 0, s>>>(g, maps, d.celltab, d.cellc, d.cellk, lo, hi);
-            else fast_cells_warp_kernel<48><<<grid, kWarpsPerCta * 32, 0, s>>>(g, maps, d.celltab, d.cellc, d.cellk, lo, hi);
+            const bool smallT = g.iniTh < 128 && g.minTh < 128;
+            auto kern = v == 40 ? (smallT ? fast_cells_warp_kernel<40, true> : fast_cells_warp_kernel<40, false>)
+                                : (smallT ? fast_cells_warp_kernel<48, true> : fast_cells_warp_kernel<48, false>);
+            kern<<<grid, kWarpsPerCta * 32, 0, s>>>(g, maps, d.celltab, d.cellc, d.cellk, lo, hi);
             launches++;
         }
         l = e;
