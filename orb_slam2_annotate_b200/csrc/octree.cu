@@ -26,7 +26,7 @@ namespace orbfe {
 namespace {
 
 constexpr int QT = 256;            // threads per tree
-constexpr int kPtsSmem = 4096;     // keys held in shared memory; larger levels use HBM scratch
+constexpr int kPtsSmemMax = 4096;  // most keys a tree keeps in shared memory; larger levels use HBM scratch
 constexpr unsigned FULL = 0xFFFFFFFFu;
 
 struct Smem {
@@ -96,7 +96,7 @@ __device__ __forceinline__ int child_count(const int* c4) {
 }
 
 __global__ void __launch_bounds__(QT)
-octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ DevBufs d, int NC) {
+octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ DevBufs d, int NC, int KP) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ int wsum[QT / 32 + 1];
     __shared__ int s_n, s_cut, s_nexp;
@@ -120,7 +120,7 @@ octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ De
         S.prank = (int*)p; p += 4 * NC;
         S.remap = (int*)p; p += 4 * NC;
         S.tmp = (int*)p; p += 4 * NC;
-        S.pxy = (uint32_t*)p; p += 4 * kPtsSmem;
+        S.pxy = (uint32_t*)p; p += 4 * KP;
         S.pnode = (uint32_t*)p;
     }
     int* selc_out = d.selc + (long long)frame * g.nlevels + l;
@@ -148,7 +148,7 @@ octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ De
     }
     uint32_t* pxy = S.pxy;
     uint32_t* pnode = S.pnode;
-    if (n > kPtsSmem) {
+    if (n > KP) {
         const long long off = (long long)frame * g.cellSlots + L.cellSlotOff;
         pxy = d.qt_xy + off;
         pnode = d.qt_node + off;
@@ -327,8 +327,17 @@ int node_capacity(const FrameSetGeom& g) {
 
 }  // namespace
 
+// keys staged in shared memory per tree: twelve times the largest per-level budget (the synthetic and the usual
+// camera frames bring 4-6 raw corners per kept one), at most kPtsSmemMax — sized so that six trees share an SM
+// at nfeatures 1000 instead of four with the fixed 4096 (the kernel is latency / barrier bound: occupancy pays)
+static int key_capacity(const FrameSetGeom& g) {
+    int nmax = 0;
+    for (int l = 0; l < g.nlevels; l++) nmax = max(nmax, g.lv[l].nFeat);
+    return min(kPtsSmemMax, max(1024, (12 * nmax + 63) & ~63));
+}
+
 size_t octree_smem_bytes(const FrameSetGeom& g) {
-    return (size_t)node_capacity(g) * 64 + (size_t)kPtsSmem * 8;
+    return (size_t)node_capacity(g) * 64 + (size_t)key_capacity(g) * 8;
 }
 
 int octree_prepare(const FrameSetGeom& g) {
@@ -337,7 +346,7 @@ int octree_prepare(const FrameSetGeom& g) {
 }
 
 int launch_octree(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
-    octree_kernel<<<dim3(g.nlevels, g.batch), QT, octree_smem_bytes(g), s>>>(g, d, node_capacity(g));
+    octree_kernel<<<dim3(g.nlevels, g.batch), QT, octree_smem_bytes(g), s>>>(g, d, node_capacity(g), key_capacity(g));
     return 1;
 }
 
