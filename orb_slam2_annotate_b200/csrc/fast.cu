@@ -210,6 +210,7 @@ __device__ __forceinline__ uint32_t swar_gt_t(uint32_t d, uint32_t c) {
 }
 
 template <int WWIN, bool SMALL_T>
+// (capping registers at 48 for a ninth CTA does not pay: shared memory already limits an SM to 8 CTAs)
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
 fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ FastMaps maps,
                        const int4* __restrict__ celltab, int* __restrict__ cellc, uint32_t* __restrict__ cellk, int cellLo, int cellHi) {

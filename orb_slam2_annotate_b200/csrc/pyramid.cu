@@ -81,22 +81,33 @@ resize_level_kernel(const uint8_t* __restrict__ src_base, uint8_t* __restrict__ 
 // SIMPLE (every down-scaling level): no output row has row0 == row1 and a source row is the lower
 // row of at most one output row, so the emission is a single predicated block per source row.
 constexpr int PRQ = 16;
+constexpr int kBandsPerCta = 5;   // 128 consecutive tasks span at most 1 + ceil(127 / nq) bands; nq >= 32 is required
 
 template <bool SIMPLE>
 __global__ void __launch_bounds__(128)
 resize_level_q_kernel(const uint8_t* __restrict__ src_base, uint8_t* __restrict__ dst_base,
                       long long sframe_bytes, long long dframe_bytes, int spitch, int dpitch,
                       int dw, int dh, const int4* __restrict__ xq, const int4* __restrict__ ytab) {
-    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    // tasks = (band of PRQ output rows, group of 4 output columns), column group fastest, flattened over the
+    // CTA's 128 threads: every warp is full whatever the level width (a 2-D mapping leaves 6 .. 29 lanes of
+    // the last warp of each row band busy); a CTA then touches up to kBandsPerCta bands
+    const int nq = (dw + 3) >> 2, nbands = (dh + PRQ - 1) / PRQ;
+    const int task0 = blockIdx.x * blockDim.x, task = task0 + threadIdx.x;
+    const int band0 = task0 / nq;
+    const int band = task / nq, q = task - band * nq;
     const int x4 = q * 4;
-    const int y0 = blockIdx.y * PRQ;
-    // the row table of this block goes through shared memory so that a row's pixel loads do not
+    const int y0 = band * PRQ;
+    // the row tables of this block's bands go through shared memory so that a row's pixel loads do not
     // wait behind a dependent global load
-    __shared__ int4 syt[PRQ + 1];
-    if (threadIdx.x <= PRQ)
-        syt[threadIdx.x] = y0 + (int)threadIdx.x < dh && threadIdx.x < PRQ ? __ldg(&ytab[y0 + (int)threadIdx.x]) : make_int4(-1, -1, 0, 0);
+    __shared__ int4 syt_all[kBandsPerCta * (PRQ + 1)];
+    for (int i = threadIdx.x; i < kBandsPerCta * (PRQ + 1); i += blockDim.x) {
+        const int b = i / (PRQ + 1), k = i - b * (PRQ + 1);
+        const int y = (band0 + b) * PRQ + k;
+        syt_all[i] = k < PRQ && band0 + b < nbands && y < dh ? __ldg(&ytab[y]) : make_int4(-1, -1, 0, 0);
+    }
     __syncthreads();
-    if (x4 >= dw) return;
+    if (band >= nbands) return;
+    const int4* syt = syt_all + (band - band0) * (PRQ + 1);
     const int4 t0 = __ldg(&xq[3 * q]), t1 = __ldg(&xq[3 * q + 1]), t2 = __ldg(&xq[3 * q + 2]);
     const uint32_t selA01 = t0.y, selB01 = t0.z, selA23 = t0.w, selB23 = t1.x;
     const uint32_t c0 = t1.y, c1 = t1.z, c2 = t1.w, c3 = t2.x;
@@ -130,7 +141,7 @@ resize_level_q_kernel(const uint8_t* __restrict__ src_base, uint8_t* __restrict_
         for (int k = 0; k < 4; k++) w[k] = load_raw(min(r + k, rl));
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            if (r + k > rl) break;                    // warp-uniform
+            if (r + k > rl) break;                    // uniform except in a warp that straddles two bands
             uint32_t hc[4];
             conv(w[k], hc);
             for (; yt.y == r + k; ) {                 // sentinel row (-1) ends the table
@@ -160,8 +171,9 @@ int launch_pyramid(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
         const LevelGeom& P = g.lv[l - 1];
         const LevelGeom& L = g.lv[l];
         dim3 block(128);
-        if (d.xq[l]) {
-            dim3 gridq((L.w + 511) / 512, (L.h + PRQ - 1) / PRQ, g.batch);
+        if (d.xq[l] && (L.w + 3) / 4 >= 32) {           // narrower levels: a CTA's tasks would span more than kBandsPerCta bands
+            const int tasks = ((L.w + 3) / 4) * ((L.h + PRQ - 1) / PRQ);
+            dim3 gridq((tasks + 127) / 128, 1, g.batch);
             auto kern = d.xqSimple[l] ? resize_level_q_kernel<true> : resize_level_q_kernel<false>;
             kern<<<gridq, block, 0, s>>>(d.pyr + P.pyrOff + (long long)g.frame0 * P.lvBytes,
                                          d.pyr + L.pyrOff + (long long)g.frame0 * L.lvBytes,
