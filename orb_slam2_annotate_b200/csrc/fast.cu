@@ -192,14 +192,22 @@ struct alignas(64) FastMaps { CUtensorMap m[kMaxLevels]; };
 template <int WWIN_>
 struct alignas(128) WarpSmem {
     static constexpr int WWIN = WWIN_;                    // max window side
-    static constexpr int WS = 16;                         // window row stride in words: a 64-byte TMA box row
+    // 40-px windows are re-laid after the TMA load: 64-byte box rows put rows r and r+2 in the same banks (ncu: 2-way
+    // conflicts in stage 1a, 3.8-way in stage 1b, 2.5-way on stage 2's byte loads); a 12-word pitch spreads eight
+    // consecutive rows over distinct bank offsets.  The landing buffer is dead afterwards and becomes the candidate
+    // list, so the block shrinks from 6400 to 6016 bytes and a ninth CTA fits an SM.
+    static constexpr bool RELAY = WWIN_ <= 40;
+    static constexpr int WS = RELAY ? 12 : 16;            // window row stride in words
     static constexpr int WZ = WWIN_ - 6;                  // max zone side
     static constexpr int SCS = WWIN_;                     // score-map row stride in bytes
-    uint32_t win[WWIN][WS];                               // TMA destination (128-byte aligned)
+    uint32_t land[RELAY ? WWIN_ : 1][16];                 // RELAY: TMA destination (64-byte box rows), later the list
+    alignas(128) uint32_t win[WWIN][WS];                  // the window the stages read (the TMA destination otherwise)
     uint8_t sc[WZ + 2][SCS];
-    unsigned short list[WZ * WZ];
+    unsigned short list_[RELAY ? 1 : WZ * WZ];
     unsigned long long bar;                               // mbarrier of the window load
+    __device__ __forceinline__ unsigned short* list() { return RELAY ? reinterpret_cast<unsigned short*>(&land[0][0]) : list_; }
 };
+static_assert(sizeof(uint32_t) * 40 * 16 >= sizeof(unsigned short) * 34 * 34, "the landing buffer must hold the candidate list");
 
 // per byte d > t: bit 7 of (d & 0x7F) + (0x7F - t) is "low seven bits > t" for t < 128 (then OR the byte's own bit 7),
 // and with c = 0x7F - (t - 128) "low seven bits > t - 128" for t >= 128 (then AND it)
@@ -210,8 +218,7 @@ __device__ __forceinline__ uint32_t swar_gt_t(uint32_t d, uint32_t c) {
 }
 
 template <int WWIN, bool SMALL_T>
-// (capping registers at 48 for a ninth CTA does not pay: shared memory already limits an SM to 8 CTAs)
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
+__global__ void __launch_bounds__(kWarpsPerCta * 32, WWIN <= 40 ? 9 : 1)
 fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ FastMaps maps,
                        const int4* __restrict__ celltab, int* __restrict__ cellc, uint32_t* __restrict__ cellk, int cellLo, int cellHi) {
     using Smem = WarpSmem<WWIN>;
@@ -238,18 +245,20 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const __grid_cons
         return;
     }
     const int zw = ww - 6, zh = wh - 6;
-    // The window arrives as one TMA box: 64 bytes x WWIN rows starting at the 16-byte boundary
-    // left of the cell (rows past the cell are fetched and ignored); window byte (r, x) below is
-    // relative to that origin.
-    const int ax0 = iniX & ~15;
+    // The window arrives as one TMA box: 64 bytes x WWIN rows starting at the 16-byte boundary left of the
+    // cell (TMA wants 16-byte aligned row starts; rows past the cell are fetched and ignored).  Window byte
+    // (r, x) below is relative to ax0: that boundary, or after the re-layout the 4-byte boundary left of the cell.
+    constexpr bool RELAY = Smem::RELAY;
+    const int tx0 = iniX & ~15;
+    const int ax0 = RELAY ? iniX & ~3 : tx0;
     const uint32_t barA = (uint32_t)__cvta_generic_to_shared(&S.bar);
     if (lane == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(barA) : "memory");
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(barA), "r"(WWIN * WS * 4) : "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(barA), "r"(WWIN * 64) : "memory");
         asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                     ::"r"((uint32_t)__cvta_generic_to_shared(&S.win[0][0])), "l"(reinterpret_cast<uint64_t>(&maps.m[l])),
-                       "r"(ax0), "r"(frame * L.h + iniY), "r"(barA) : "memory");
+                     ::"r"((uint32_t)__cvta_generic_to_shared(RELAY ? &S.land[0][0] : &S.win[0][0])),
+                       "l"(reinterpret_cast<uint64_t>(&maps.m[l])), "r"(tx0), "r"(frame * L.h + iniY), "r"(barA) : "memory");
     }
     const int zx0 = iniX + 3 - ax0, zx1 = maxX - 3 - ax0;   // zone columns in window bytes
     const int zc0 = zx0 >> 2, nzc = ((zx1 - 1) >> 2) - zc0 + 1;
@@ -262,7 +271,7 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const __grid_cons
     const int rpi = nzc <= 10 ? 3 : small_div(32, rcp_nzc);      // zone rows per warp step (nzc <= 12)
     const int rsub = small_div(lane, rcp_nzc), cc1 = lane - rsub * nzc;
     const bool act = rsub < rpi;
-    const uint32_t* wcol = &S.win[rsub][zc0 + cc1];
+    const uint32_t* wcol = &S.win[act ? rsub : 0][zc0 + cc1];    // idle lanes stay inside the block (their loads are unconditional)
     uint32_t zm = 0x80808080u;                                   // bytes of the lane's word inside the zone
     {
         const int xb = (zc0 + cc1) * 4;
@@ -278,6 +287,16 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const __grid_cons
                          : "=r"(done) : "r"(barA), "r"(0) : "memory");
     }
 
+    if (RELAY) {
+        // two window rows per step: lanes 0-11 copy the 12 words of row r, lanes 12-23 those of row r+1 (conflict free
+        // on both sides); the source starts at the word that holds column ax0
+        const int half = lane >= 12 ? 1 : 0, cw = lane - 12 * half;
+        const uint32_t* srcw = &S.land[half][((iniX & 15) >> 2) + cw];
+        uint32_t* dstw = &S.win[half][cw];
+        if (lane < 24)
+            for (int r = half; r < wh; r += 2, srcw += 32, dstw += 2 * WS) *dstw = *srcw;
+        __syncwarp();
+    }
     int total = 0;
     for (int pass = 0; pass < 2; pass++) {
         const int t = pass == 0 ? g.iniTh : g.minTh;
@@ -357,7 +376,7 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const __grid_cons
             int pos = ncand + inc - k;
 #pragma unroll
             for (int b = 0; b < 4; b++)
-                if (gmask & (0x80u << (8 * b))) S.list[pos++] = (unsigned short)((r << 8) | (xz + b));
+                if (gmask & (0x80u << (8 * b))) S.list()[pos++] = (unsigned short)((r << 8) | (xz + b));
             ncand += __shfl_sync(0xFFFFFFFFu, inc, 31);
         }
         __syncwarp();
@@ -370,14 +389,14 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const __grid_cons
             const int i = base + lane;
             int e = 0, s = 0;
             if (i < ncand) {
-                e = S.list[i];
+                e = S.list()[i];
                 const int r = e >> 8, cc = e & 0xFF;
                 s = corner_strength<false>(wb + (r + 3) * (WS * 4) + zx0 + cc, WS * 4, t);
                 if (s) S.sc[r + 1][cc + 1] = (uint8_t)s;
             }
             const uint32_t bal = __ballot_sync(0xFFFFFFFFu, s != 0);
             __syncwarp();                                 // list reads above before the in-place writes
-            if (s) S.list[ncorn + __popc(bal & ((1u << lane) - 1u))] = (unsigned short)e;
+            if (s) S.list()[ncorn + __popc(bal & ((1u << lane) - 1u))] = (unsigned short)e;
             ncorn += __popc(bal);
         }
         __syncwarp();
@@ -388,7 +407,7 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const __grid_cons
             bool keep = false;
             int r = 0, cc = 0, s = 0;
             if (i < ncorn) {
-                const int e = S.list[i];
+                const int e = S.list()[i];
                 r = e >> 8, cc = e & 0xFF;
                 s = S.sc[r + 1][cc + 1];
                 keep = s > S.sc[r][cc] && s > S.sc[r][cc + 1] && s > S.sc[r][cc + 2] &&
