@@ -14,6 +14,7 @@
 // compaction, packed x | y<<12 | score<<24 with coordinates relative to (minBorderX,
 // minBorderY) as the reference stores them (:889-890).
 #include "orbfe_internal.cuh"
+#include <cstddef>
 #include <cstring>
 #include <cuda.h>
 
@@ -293,8 +294,11 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const __grid_cons
         const int half = lane >= 12 ? 1 : 0, cw = lane - 12 * half;
         const uint32_t* srcw = &S.land[half][((iniX & 15) >> 2) + cw];
         uint32_t* dstw = &S.win[half][cw];
-        if (lane < 24)
-            for (int r = half; r < wh; r += 2, srcw += 32, dstw += 2 * WS) *dstw = *srcw;
+        // all WWIN rows (the box always brings them), fully unrolled: immediate offsets, no loop bookkeeping
+        if (lane < 24) {
+#pragma unroll
+            for (int k = 0; k < WWIN / 2; k++) dstw[k * 2 * WS] = srcw[k * 32];
+        }
         __syncwarp();
     }
     int total = 0;
@@ -381,7 +385,11 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const __grid_cons
         }
         __syncwarp();
         // the task list is consumed: zero the score map
-        for (int i = lane; i < (zh + 2) * (SCS / 4); i += 32) reinterpret_cast<uint32_t*>(&S.sc[0][0])[i] = 0;
+        // (the whole map, 16 bytes per lane and step: three or five steps)
+        static_assert(sizeof(S.sc) % 16 == 0 && offsetof(Smem, sc) % 16 == 0, "score map is cleared with 16-byte stores");
+#pragma unroll
+        for (int i = 0; i < (int)(sizeof(S.sc) / 16 + 31) / 32; i++)
+            if (i * 32 + lane < (int)(sizeof(S.sc) / 16)) reinterpret_cast<uint4*>(&S.sc[0][0])[i * 32 + lane] = make_uint4(0u, 0u, 0u, 0u);
         __syncwarp();
         // ---- stage 2: exact test + strength on the survivors, compacted in place
         int ncorn = 0;
