@@ -51,9 +51,9 @@ def algorithmic_bytes(w, h):
 # dram__bytes_read.sum + dram__bytes_write.sum per 1024-frame launch of each stage's kernels, from the
 # `ncu --set full` capture summarised in profiles/r01_ncu_full_summary.txt (640x480, 8 levels)
 NCU_DRAM_BYTES_PER_1024 = {
-    "pyramid": 1.0037e9 + 460.0e6,
-    "fast": 939.0e6 + 22.8e6 + 41.8e6,
-    "blur": 1.077e9 + 988.3e6,
+    "pyramid": 1.0066e9 + 447.2e6,
+    "fast": 938.8e6 + 22.8e6 + 42.2e6,
+    "blur": 1.077e9 + 985.6e6,
 }
 
 
@@ -548,7 +548,7 @@ def main():
                          "frac": achieved / peak, "algorithmic_bytes": ab[dom] * B,
                          "traffic": NCU_DRAM_BYTES_PER_1024[dom] * B / 1024.0,
                          "traffic_source": "ncu --set full capture at 1024 frames (profiles/r01_ncu_full_summary.txt), scaled to this batch",
-                         "note": "FAST is instruction-issue / shared-memory bound (ncu: issue slots 74% busy, L1-shared pipe 76%, DRAM 13%); the HBM fraction is reported as the contract asks",
+                         "note": "FAST is instruction-issue / shared-memory bound (ncu: issue slots 81% busy, L1-shared pipe 70%, DRAM 17%); the HBM fraction is reported as the contract asks",
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
                          "per_kernel": per_kernel},
         }
