@@ -229,7 +229,7 @@ public:
             else { minL[i] = nLastOctave - 1; maxL[i] = nLastOctave + 1; }
             ur[i] = u[i] - CurrentFrame.mbf * invzc;                       // :1575
             angle[i] = LastFrame.mvKeysUn[i].angle;                        // :1594
-            const MatT dMP = pMP->GetDescriptor();
+            const cv::Mat dMP = pMP->GetDescriptor();
             std::memcpy(&desc[(size_t)i * 32], dMP.data, 32);
             obs[i] = pMP->Observations();
             valid[i] = 1;
