@@ -4,7 +4,13 @@
 //
 //   * windows: the 31x31 patch of the level and the 37x37 patch of the blurred level arrive by
 //     TMA (cp.async.bulk.tensor.2d on [frames * rows][pitch] byte tensors, 16-byte aligned box
-//     starts) into per-warp double buffers, one keypoint ahead; a warp walks KPW keypoints.
+//     starts), one keypoint ahead: the level window into a single buffer (it is dead as soon as the
+//     moments are summed), the blurred window into a double buffer; a warp walks KPW keypoints.  51 KB of
+//     shared memory and 64 registers let four CTAs live on an SM.  Measured alone the window traffic
+//     (154 L2 sectors per keypoint, 9.3 TB/s) and the arithmetic each take 0.55 ms per 1024 frames; the
+//     kernel runs at 0.70, so it is bound by the L2 path as much as by issue (round-1 experiments:
+//     a three-phase variant that evaluates atan2 / sin / cos once per eight keypoints, one per lane,
+//     removes a quarter of the instructions and changes nothing).
 //   * orientation: lanes 0..30 own the patch columns u = -15..15 and walk the row pairs +-v
 //     from shared memory; the int32 moments m10 = sum u*I, m01 = sum v*I over the disc
 //     |u| <= umax[|v|] are reduced with shuffles (integer sums, so the order is free) and fed
@@ -78,23 +84,20 @@ __device__ __align__(16) const PatH d_path = make_path();
 constexpr int RAW_ROWS = 2 * kHalfPatch + 1, RAW_STRIDE = kTmaRawW;   // 31 rows x 48 bytes
 constexpr int BLR_HALF = 18, BLR_ROWS = 2 * BLR_HALF + 1, BLR_STRIDE = kTmaBlurW;   // rotated pattern stays within 18 px: 37 rows x 64 bytes
 constexpr int RAW_BYTES = RAW_ROWS * RAW_STRIDE, BLR_BYTES = BLR_ROWS * BLR_STRIDE;
-constexpr int RAW_SLOT = (RAW_BYTES + 127) / 128 * 128, BUF_BYTES = RAW_SLOT + (BLR_BYTES + 127) / 128 * 128;   // TMA destinations are 128-byte aligned
+constexpr int RAW_SLOT = (RAW_BYTES + 127) / 128 * 128, BLR_SLOT = (BLR_BYTES + 127) / 128 * 128;   // TMA destinations are 128-byte aligned
+constexpr int WARP_BYTES = RAW_SLOT + 2 * BLR_SLOT;   // one level window (dead once the moments are summed) + two blurred windows
 static_assert(RAW_ROWS == kTmaRawH && BLR_ROWS == kTmaBlurH, "TMA boxes are built on the host from orbfe_internal.cuh");
 constexpr int KPW = 4;   // keypoints per warp
 
-// One warp per keypoint.  Both windows the keypoint needs (31x31 of the level for the moments,
-// 37x37 of the blurred level for the rotated pattern) are fetched with eight 16-byte loads per
-// lane issued back to back and parked in shared memory; the moment rows and the 512 pattern
-// lookups then are LDS.U8 with immediate / 32-bit offsets instead of per-access 64-bit global
-// address arithmetic.
+// One warp per keypoint: the moment rows and the 512 pattern lookups are LDS.U8 on the two windows in shared memory.
 // TMA descriptors travel as a kernel parameter: {level, blurred level} per pyramid level
 struct alignas(64) LevelMaps { CUtensorMap m[2 * kMaxLevels]; };
 
-__global__ void __launch_bounds__(256, 3)
+__global__ void __launch_bounds__(256, 4)
 orient_desc_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ DevBufs d,
                    const __grid_constant__ LevelMaps maps, const int* __restrict__ umax) {
     extern __shared__ __align__(128) uint8_t smem_dyn[];
-    __shared__ __align__(8) uint64_t bars[8][2];
+    __shared__ __align__(8) uint64_t bars[8][3];   // per warp: level window, blurred window 0 / 1
     const int frame = blockIdx.y + g.frame0;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     // level and in-level index of a keypoint: inclusive scan of the per-level counts
@@ -107,10 +110,11 @@ orient_desc_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant
     const int total = __shfl_sync(FULL, incl, kMaxLevels - 1);   // lanes < 16 hold complete prefixes
     if (blockIdx.x == 0 && tid == 0) d.counts[frame] = total;
     if ((blockIdx.x * KPW) * 8 + wid >= total) return;
-    uint8_t* wbuf = smem_dyn + wid * (2 * BUF_BYTES);
+    uint8_t* wbuf = smem_dyn + wid * WARP_BYTES;
     if (lane == 0) {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((uint32_t)__cvta_generic_to_shared(&bars[wid][0])) : "memory");
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((uint32_t)__cvta_generic_to_shared(&bars[wid][1])) : "memory");
+#pragma unroll
+        for (int i = 0; i < 3; i++)
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((uint32_t)__cvta_generic_to_shared(&bars[wid][i])) : "memory");
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
@@ -128,21 +132,24 @@ orient_desc_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant
         const int k = kpi - (lvl ? before : 0);
         p = d.sel[(long long)frame * g.selTotal + g.lv[lvl].selBase + k];
     };
+    // the level window has one buffer (free again as soon as the moments are summed), the blurred window two
     auto fetch = [&](int lvl, uint32_t p, int buf) {
         if (lane == 0) {
             const int x = kp_x(p), y = kp_y(p) + frame * g.lv[lvl].h;
-            const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&bars[wid][buf]);
-            const uint32_t rdst = (uint32_t)__cvta_generic_to_shared(wbuf + buf * BUF_BYTES);
+            const uint32_t barR = (uint32_t)__cvta_generic_to_shared(&bars[wid][0]);
+            const uint32_t barB = (uint32_t)__cvta_generic_to_shared(&bars[wid][1 + buf]);
+            const uint32_t rdst = (uint32_t)__cvta_generic_to_shared(wbuf);
             const uint64_t mraw = reinterpret_cast<uint64_t>(&maps.m[2 * lvl]);
-            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(RAW_BYTES + BLR_BYTES) : "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(barR), "r"(RAW_BYTES) : "memory");
             asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                         ::"r"(rdst), "l"(mraw), "r"((x - kHalfPatch) & ~15), "r"(y - kHalfPatch), "r"(bar) : "memory");
+                         ::"r"(rdst), "l"(mraw), "r"((x - kHalfPatch) & ~15), "r"(y - kHalfPatch), "r"(barR) : "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(barB), "r"(BLR_BYTES) : "memory");
             asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                         ::"r"(rdst + RAW_SLOT), "l"(mraw + 128), "r"((x - BLR_HALF) & ~15), "r"(y - BLR_HALF), "r"(bar) : "memory");
+                         ::"r"(rdst + RAW_SLOT + buf * BLR_SLOT), "l"(mraw + 128), "r"((x - BLR_HALF) & ~15), "r"(y - BLR_HALF), "r"(barB) : "memory");
         }
     };
-    auto wait = [&](int buf, int phase) {
-        const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&bars[wid][buf]);
+    auto wait = [&](int which, int phase) {
+        const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&bars[wid][which]);
         uint32_t done = 0;
         while (!done)
             asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
@@ -158,19 +165,14 @@ orient_desc_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant
     const int lvl = lvlN;
     const uint32_t p = pN;
     const bool more = it + 1 < KPW && kpi + 8 < total;
-    __syncwarp();                                     // readers of the other buffer are done
-    if (more) {
-        locate(kpi + 8, lvlN, pN);
-        fetch(lvlN, pN, buf ^ 1);
-    }
-    wait(buf, (it >> 1) & 1);
+    wait(0, it & 1);
     const LevelGeom& L = g.lv[lvl];
     const int x = kp_x(p), y = kp_y(p), score = kp_score(p);
     // ---- IC_Angle
     int m10 = 0, m01 = 0;
     {
         // the disc is symmetric (checked on the host): column u holds rows |v| <= umax[|u|]
-        const uint8_t* c = wbuf + buf * BUF_BYTES + ((x - kHalfPatch) & 15) + min(lane, 30);       // (u, v = -15)
+        const uint8_t* c = wbuf + ((x - kHalfPatch) & 15) + min(lane, 30);       // (u, v = -15)
         // rows +v and -v share their predicate; the selects keep the loop branch-free
         int sum = c[kHalfPatch * RAW_STRIDE];         // v = 0 (every column has it; lane 31 is zeroed below)
 #pragma unroll
@@ -188,6 +190,12 @@ orient_desc_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant
         m10 += __shfl_xor_sync(FULL, m10, o);
         m01 += __shfl_xor_sync(FULL, m01, o);
     }
+    // the shuffles above ordered every lane's reads of the level window, and the previous keypoint's readers of the
+    // other blurred buffer finished before this iteration: the next keypoint's windows can be fetched now
+    if (more) {
+        locate(kpi + 8, lvlN, pN);
+        fetch(lvlN, pN, buf ^ 1);
+    }
     const float angle = fast_atan2_deg((float)m01, (float)m10);
 
     // ---- rBRIEF byte `lane`
@@ -198,16 +206,22 @@ orient_desc_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant
     // divergence.
     float a, b;
     orbfe_scf::sincosf_glibc(ang, &b, &a);
-    const uint8_t* cb = wbuf + buf * BUF_BYTES + RAW_SLOT + BLR_HALF * BLR_STRIDE + BLR_HALF + ((x - BLR_HALF) & 15);   // patch centre
+    wait(1 + buf, (it >> 1) & 1);
+    const uint8_t* cb = wbuf + RAW_SLOT + buf * BLR_SLOT + BLR_HALF * BLR_STRIDE + BLR_HALF + ((x - BLR_HALF) & 15);   // patch centre
     int val = 0;
+    // cvRound without the conversion pipe (F2I issues at a quarter of the FADD rate): for |v| < 2^22 the float
+    // v + 1.5 * 2^23 holds round-half-even(v) in its low mantissa bits, i.e. its bit pattern is kMagicBits + cvRound(v)
+    constexpr float kMagic = 12582912.0f;
+    constexpr int kMagicBits = 0x4B400000;
+    auto cv_round = [](float v) { return __float_as_int(__fadd_rn(v, kMagic)) - kMagicBits; };
 #pragma unroll
     for (int j = 0; j < 8; j++) {
         const float2 q0 = __half22float2(*reinterpret_cast<const __half2*>(&pat[2 * j]));
         const float2 q1 = __half22float2(*reinterpret_cast<const __half2*>(&pat[2 * j + 1]));
-        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(q0.x, b), __fmul_rn(q0.y, a)));
-        const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(q0.x, a), __fmul_rn(q0.y, b)));
-        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(q1.x, b), __fmul_rn(q1.y, a)));
-        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(q1.x, a), __fmul_rn(q1.y, b)));
+        const int r0 = cv_round(__fadd_rn(__fmul_rn(q0.x, b), __fmul_rn(q0.y, a)));
+        const int c0 = cv_round(__fsub_rn(__fmul_rn(q0.x, a), __fmul_rn(q0.y, b)));
+        const int r1 = cv_round(__fadd_rn(__fmul_rn(q1.x, b), __fmul_rn(q1.y, a)));
+        const int c1 = cv_round(__fsub_rn(__fmul_rn(q1.x, a), __fmul_rn(q1.y, b)));
         const int t0 = cb[r0 * BLR_STRIDE + c0], t1 = cb[r1 * BLR_STRIDE + c1];
         val |= (t0 < t1) << j;
     }
@@ -233,7 +247,7 @@ orient_desc_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant
 int launch_orient_desc(const FrameSetGeom& g, const DevBufs& d, const int* d_umax, cudaStream_t s) {
     LevelMaps maps;
     std::memcpy(&maps, d.tmaps, sizeof(CUtensorMap) * 2 * g.nlevels);
-    constexpr int smem = 8 * 2 * BUF_BYTES;
+    constexpr int smem = 8 * WARP_BYTES;
     // per device and cheap, so set on every launch rather than tracked per context
     if (cudaFuncSetAttribute(orient_desc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return 0;
     orient_desc_kernel<<<dim3((g.outCap + 8 * KPW - 1) / (8 * KPW), g.batch), 256, smem, s>>>(g, d, maps, d_umax);
