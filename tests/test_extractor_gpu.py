@@ -180,3 +180,31 @@ def test_device_resident_frames(orbfe, oracle):
         k1, d1 = ex(imgs[2])
         assert k1.tobytes() == kps[2, :counts[2]].tobytes() and d1.tobytes() == desc[2, :counts[2]].tobytes()
         del dev
+
+
+def test_full_size_batch_properties(orbfe, oracle):
+    """BASELINE.json configs[1] at its full size: 1024 frames of 640x480 in one host batch.  Size-independent
+    properties: every copy of a frame gives the bytes of its first copy wherever it sits in the batch (chunk
+    position, pipeline lane), counts stay within the feature budget's reach, and the distinct frames equal the
+    oracle bit for bit (keypoints) / within the stated angle tolerance."""
+    B, D = 1024, 8
+    distinct = np.stack([synth.frame(640, 480, 40 + s) for s in range(D)])
+    order = (np.arange(B) * 5 + np.arange(B) // D) % D               # copies spread over every chunk
+    imgs = np.ascontiguousarray(distinct[order])
+    ex = orbfe.ORBextractor(1000)
+    kps, desc, counts = ex.extract_batch(imgs)
+    first = {int(s): int(np.nonzero(order == s)[0][0]) for s in range(D)}
+    for b in range(B):
+        f = first[int(order[b])]
+        n = counts[f]
+        assert counts[b] == n
+        assert kps[b, :n].tobytes() == kps[f, :n].tobytes() and desc[b, :n].tobytes() == desc[f, :n].tobytes()
+    assert counts.min() > 500 and counts.max() <= 1200
+    oc = oracle.OracleExtractor(1000)
+    rows = 0
+    for s in range(D):
+        ko, do = oc(distinct[s])
+        f = first[s]
+        r, _, _ = _compare_frame(kps[f, :counts[f]], desc[f, :counts[f]], ko, do)
+        rows += r
+    assert rows <= 2

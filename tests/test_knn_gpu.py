@@ -40,3 +40,22 @@ def test_descriptor_distance_host(orbfe, oracle):
     for _ in range(200):
         a = rng.integers(0, 256, 32, dtype=np.uint8); b = rng.integers(0, 256, 32, dtype=np.uint8)
         assert orbfe.ORBmatcher.DescriptorDistance(a, b) == oracle.descriptor_distance(a, b)
+
+
+def test_knn2_full_size_planted_property(orbfe):
+    """The bench's kNN shape (131072 x 131072, one GPU's share of configs[4]) through a size-independent property:
+    every query is a train row with k <= 12 flipped bits, so its best match is that row at distance exactly k, the
+    runner-up is far (random 256-bit rows sit near 128), and the ratio test accepts it."""
+    n = 131072
+    rng = np.random.default_rng(11)
+    t = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    src = rng.permutation(n)
+    q = t[src].copy()
+    k = rng.integers(0, 13, n)
+    for i in np.nonzero(k)[0]:
+        bits = rng.choice(256, k[i], replace=False)
+        np.bitwise_xor.at(q[i], bits >> 3, (1 << (bits & 7)).astype(np.uint8))
+    idx, d1, d2 = orbfe.ORBmatcher(0.7).knn2(q, t, th=50, ratio=0.7)
+    assert np.array_equal(d1, k.astype(d1.dtype))
+    assert np.array_equal(idx, src.astype(idx.dtype))
+    assert d2.min() > 60
