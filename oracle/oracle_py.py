@@ -487,3 +487,84 @@ def knn2(q: np.ndarray, t: np.ndarray, th=50, ratio=0.7):
     idx = np.empty(m, np.int32); d1 = np.empty(m, np.int32); d2 = np.empty(m, np.int32)
     lib().orc_knn2(q.ctypes.data, m, t.ctypes.data, t.shape[0], th, ratio, idx.ctypes.data, d1.ctypes.data, d2.ctypes.data)
     return idx, d1, d2
+
+
+# ----------------------------------------------------------------------------- the reference's own matcher TUs
+# oracle/_ref/liborbref_matcher.so: UNMODIFIED src/ORBmatcher.cc, Frame.cc, KeyFrame.cc, MapPoint.cc, Map.cc (+ DBoW2)
+# behind oracle/ref_matcher_wrap.cpp.  Same argument shapes as the restatement's wrappers above.
+_mref = [False, None]
+
+
+def mref_lib():
+    """None when oracle/_ref/liborbref_matcher.so is not built (reference tree not mounted)."""
+    if not _mref[0]:
+        _mref[0] = True
+        path = os.path.join(HERE, "_ref", "liborbref_matcher.so")
+        if os.path.exists(path):
+            L = C.CDLL(path)
+            L.orm_search_for_initialization.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int]
+            L.orm_search_by_projection.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+            L.orm_search_by_projection_frame.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 8 + [C.c_float, C.c_int, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
+            L.orm_assign_grid.argtypes = [C.c_void_p] * 3
+            L.orm_features_in_area.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_int]
+            _mref[1] = L
+    return _mref[1]
+
+
+def ref_assign_grid(f):
+    cs = np.empty(64 * 48 + 1, np.int32); items = np.empty(max(f[0].n, 1), np.int32)
+    mref_lib().orm_assign_grid(C.byref(f[0]), cs.ctypes.data, items.ctypes.data)
+    mref_lib().orm_reset()
+    return cs, items[:f[0].n]
+
+
+def ref_features_in_area(f, x, y, r, min_level=-1, max_level=-1):
+    out = np.empty(max(f[0].n, 1), np.int32)
+    n = mref_lib().orm_features_in_area(C.byref(f[0]), x, y, r, min_level, max_level, out.ctypes.data, len(out))
+    mref_lib().orm_reset()
+    return out[:n].copy()
+
+
+def features_in_area(f, x, y, r, min_level=-1, max_level=-1):
+    """the restatement's Frame / KeyFrame::GetFeaturesInArea on a view"""
+    cs = np.empty(64 * 48 + 1, np.int32); items = np.empty(max(f[0].n, 1), np.int32)
+    lib().orc_assign_grid(C.byref(f[0]), cs.ctypes.data, items.ctypes.data)
+    out = np.empty(max(f[0].n, 1), np.int32)
+    lib().orc_features_in_area.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_int]
+    n = lib().orc_features_in_area(C.byref(f[0]), cs.ctypes.data, items.ctypes.data, x, y, r, min_level, max_level, out.ctypes.data, len(out))
+    return out[:n].copy()
+
+
+def ref_search_for_initialization(f1, f2, prev_matched: np.ndarray, window=100, nnratio=0.9, check_ori=True):
+    n1 = f1[0].n
+    m12 = np.empty(max(n1, 1), np.int32)
+    nm = mref_lib().orm_search_for_initialization(C.byref(f1[0]), C.byref(f2[0]), prev_matched.ctypes.data, m12.ctypes.data, window, nnratio, int(check_ori))
+    mref_lib().orm_reset()
+    return nm, m12[:n1]
+
+
+def ref_search_by_projection(f, mps: dict, th: float, nnratio: float, occupied: np.ndarray):
+    arrs = dict(track_in_view=np.uint8, proj_x=np.float32, proj_y=np.float32, proj_xr=np.float32,
+                level=np.int32, view_cos=np.float32, desc=np.uint8, observations=np.int32)
+    keep = {k: np.ascontiguousarray(mps[k], t) for k, t in arrs.items()}
+    v = MapPointsView(len(keep["level"]), *[keep[k].ctypes.data for k in
+                      ("track_in_view", "proj_x", "proj_y", "proj_xr", "level", "view_cos", "desc", "observations")])
+    occ = np.ascontiguousarray(occupied, np.uint8)
+    out = np.full(max(f[0].n, 1), -1, np.int32)
+    nm = mref_lib().orm_search_by_projection(C.byref(f[0]), C.byref(v), th, nnratio, occ.ctypes.data, out.ctypes.data)
+    mref_lib().orm_reset()
+    return nm, out[:f[0].n]
+
+
+def ref_search_by_projection_frame(f, last: dict, th: float, mono: bool, bf: float, check_ori: bool, occupied: np.ndarray):
+    """last: dict of arrays has_point / outlier u8, u / v f32, octave i32, angle f32, desc u8[n,32], observations i32
+    (the last frame's keypoints with their map points at (u, v, 1)).  -> (nmatches, final index per keypoint or -1)"""
+    arrs = dict(has_point=np.uint8, outlier=np.uint8, u=np.float32, v=np.float32, octave=np.int32, angle=np.float32, desc=np.uint8,
+                observations=np.int32)
+    keep = {k: np.ascontiguousarray(last[k], t) for k, t in arrs.items()}
+    occ = np.ascontiguousarray(occupied, np.uint8)
+    out = np.full(max(f[0].n, 1), -1, np.int32)
+    nm = mref_lib().orm_search_by_projection_frame(C.byref(f[0]), len(keep["u"]), *[keep[k].ctypes.data for k in arrs], th, int(mono), bf,
+                                                   int(check_ori), occ.ctypes.data, out.ctypes.data)
+    mref_lib().orm_reset()
+    return nm, out[:f[0].n]
