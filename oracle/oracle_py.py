@@ -568,3 +568,115 @@ def ref_search_by_projection_frame(f, last: dict, th: float, mono: bool, bf: flo
                                                    int(check_ori), occ.ctypes.data, out.ctypes.data)
     mref_lib().orm_reset()
     return nm, out[:f[0].n]
+
+
+def _mref_more():
+    L = mref_lib()
+    if getattr(L, "_more", False):
+        return L
+    P, I, F = C.c_void_p, C.c_int, C.c_float
+    L.orm_search_by_bow_frame.argtypes = [P, P, F, I, P]
+    L.orm_search_by_bow_keyframes.argtypes = [P, P, F, I, P]
+    L.orm_sbp_frame_keyframe.argtypes = [P, P, P, P, P, F, I, I, P, P]
+    L.orm_sbp_keyframe_sim3.argtypes = [P, P, P, P, I, P, P]
+    L.orm_fuse.argtypes = [P, P, P, P, F, I, F, P, P, P, P]
+    L.orm_search_by_sim3.argtypes = [P] * 9 + [F, P]
+    L.orm_search_for_triangulation.argtypes = [P, P, P, F, F, P, I, F, F, I, I, P]
+    L.orm_distinctive_descriptors.argtypes = [P, P, I, P]
+    L.orm_compute_stereo_matches.argtypes = [P, P, P, P, I, I, F, F, P, P]
+    L._more = True
+    return L
+
+
+def _u8(a, n, default):
+    return np.ascontiguousarray(a if a is not None else np.full(max(n, 1), default), np.uint8)
+
+
+def ref_search_by_bow(s1, s2, nnratio: float, check_ori: bool, keyframes: bool):
+    """keyframes False: SearchByBoW(KeyFrame*, Frame&, ..) -> (n, m21); True: SearchByBoW(KeyFrame*, KeyFrame*, ..) -> (n, m12)"""
+    L = _mref_more()
+    out = np.empty(max((s1 if keyframes else s2)[0].n, 1), np.int32)
+    fn = L.orm_search_by_bow_keyframes if keyframes else L.orm_search_by_bow_frame
+    n = fn(C.byref(s1[0]), C.byref(s2[0]), nnratio, int(check_ori), out.ctypes.data)
+    L.orm_reset()
+    return n, out[:(s1 if keyframes else s2)[0].n]
+
+
+def ref_sbp_frame_keyframe(f, points: dict, has_point, bad, found, th, orb_dist, check_ori, occupied):
+    L = _mref_more()
+    v, keep = proj_points_view(points)
+    n = v.n
+    a = [_u8(has_point, n, 1), _u8(bad, n, 0), _u8(found, n, 0)]
+    occ = np.ascontiguousarray(occupied, np.uint8)
+    out = np.full(max(f[0].n, 1), -1, np.int32)
+    nm = L.orm_sbp_frame_keyframe(C.byref(f[0]), C.byref(v), a[0].ctypes.data, a[1].ctypes.data, a[2].ctypes.data, th, orb_dist, int(check_ori),
+                                  occ.ctypes.data, out.ctypes.data)
+    L.orm_reset()
+    return nm, out[:f[0].n]
+
+
+def ref_sbp_keyframe_sim3(f, points: dict, bad, normal_ok, th: int, matched):
+    L = _mref_more()
+    v, keep = proj_points_view(points)
+    a = [_u8(bad, v.n, 0), _u8(normal_ok, v.n, 1)]
+    occ = np.ascontiguousarray(matched, np.uint8)
+    out = np.full(max(f[0].n, 1), -1, np.int32)
+    nm = L.orm_sbp_keyframe_sim3(C.byref(f[0]), C.byref(v), a[0].ctypes.data, a[1].ctypes.data, int(th), occ.ctypes.data, out.ctypes.data)
+    L.orm_reset()
+    return nm, out[:f[0].n]
+
+
+def ref_fuse(f, points: dict, bad, normal_ok, th, with_pose: bool, bf=0.0, kp_has_point=None, kp_point_obs=None, point_obs=None):
+    """-> (nFused, keypoint each point was fused with or -1)"""
+    L = _mref_more()
+    v, keep = proj_points_view(points)
+    a = [_u8(bad, v.n, 0), _u8(normal_ok, v.n, 1), _u8(kp_has_point, f[0].n, 0)]
+    ko = np.ascontiguousarray(kp_point_obs if kp_point_obs is not None else np.ones(max(f[0].n, 1)), np.int32)
+    po = np.ascontiguousarray(point_obs if point_obs is not None else np.ones(max(v.n, 1)), np.int32)
+    out = np.full(max(v.n, 1), -1, np.int32)
+    nf = L.orm_fuse(C.byref(f[0]), C.byref(v), a[0].ctypes.data, a[1].ctypes.data, th, int(with_pose), bf, a[2].ctypes.data, ko.ctypes.data,
+                    po.ctypes.data, out.ctypes.data)
+    L.orm_reset()
+    return nf, out[:v.n]
+
+
+def ref_search_by_sim3(f1, f2, points1: dict, points2: dict, has1, has2, bad1, bad2, pre12, th):
+    L = _mref_more()
+    v1, k1 = proj_points_view(points1); v2, k2 = proj_points_view(points2)
+    a = [_u8(has1, v1.n, 1), _u8(has2, v2.n, 1), _u8(bad1, v1.n, 0), _u8(bad2, v2.n, 0)]
+    pre = np.ascontiguousarray(pre12 if pre12 is not None else np.full(max(v1.n, 1), -1), np.int32)
+    out = np.empty(max(v1.n, 1), np.int32)
+    n = L.orm_search_by_sim3(C.byref(f1[0]), C.byref(f2[0]), C.byref(v1), C.byref(v2), *[x.ctypes.data for x in a], pre.ctypes.data, th, out.ctypes.data)
+    L.orm_reset()
+    return n, out[:v1.n]
+
+
+def ref_search_for_triangulation(s1, s2, F12, ex, ey, scale_factors, w, h, only_stereo=False, check_ori=True):
+    L = _mref_more()
+    Fm = np.ascontiguousarray(F12, np.float32).reshape(9)
+    sf = np.ascontiguousarray(scale_factors, np.float32)
+    out = np.empty(max(s1[0].n, 1), np.int32)
+    n = L.orm_search_for_triangulation(C.byref(s1[0]), C.byref(s2[0]), Fm.ctypes.data, ex, ey, sf.ctypes.data, len(sf), w, h, int(only_stereo),
+                                       int(check_ori), out.ctypes.data)
+    L.orm_reset()
+    return n, out[:s1[0].n]
+
+
+def ref_distinctive_descriptors(desc: np.ndarray, start: np.ndarray) -> np.ndarray:
+    L = _mref_more()
+    desc = np.ascontiguousarray(desc, np.uint8); start = np.ascontiguousarray(start, np.int32)
+    best = np.empty(max(len(start) - 1, 1), np.int32)
+    L.orm_distinctive_descriptors(desc.ctypes.data, start.ctypes.data, len(start) - 1, best.ctypes.data)
+    L.orm_reset()
+    return best[:len(start) - 1]
+
+
+def ref_compute_stereo_matches(fl, fr, left: np.ndarray, right: np.ndarray, fx: float, bf: float):
+    """Frame::ComputeStereoMatches of the reference on the given keypoint lists -> (mvuRight, mvDepth)"""
+    L = _mref_more()
+    h, w = left.shape
+    left = np.ascontiguousarray(left); right = np.ascontiguousarray(right)
+    ur = np.empty(max(fl[0].n, 1), np.float32); dp = np.empty(max(fl[0].n, 1), np.float32)
+    L.orm_compute_stereo_matches(C.byref(fl[0]), C.byref(fr[0]), left.ctypes.data, right.ctypes.data, w, h, fx, bf, ur.ctypes.data, dp.ctypes.data)
+    L.orm_reset()
+    return ur[:fl[0].n], dp[:fl[0].n]

@@ -273,4 +273,238 @@ int orm_search_by_projection_frame(const orc_frame_view* f, int npts, const uint
     return n;
 }
 
+
+/* ---- SearchByBoW, both overloads — src/ORBmatcher.cc:185-325, :610-743.  A side is the restatement's orc_bow_view;
+ * keypoints only carry their angle.  valid == NULL on side 1 means every feature has a live map point. */
+static Frame* bow_frame(const orc_bow_view* s, std::vector<orc_keypoint>& k) {
+    static const float scale[8] = {1.f, 1.2f, 1.44f, 1.728f, 2.0736f, 2.48832f, 2.985984f, 3.5831808f};
+    k.resize(s->n);
+    for (int i = 0; i < s->n; i++) k[i] = orc_keypoint{(float)(i % 600) + 10.f, (float)(i / 600) * 7.f + 10.f, 31.f, s->angle[i], 0.f, 0, -1};
+    orc_frame_view v = {s->n, k.data(), s->desc, nullptr, 0.f, 640.f, 0.f, 480.f, scale, 8, 0};
+    Frame* F = make_frame(&v);
+    F->mFeatVec = feat_vec(s->nnodes, s->node_id, s->node_start, s->indices);
+    return F;
+}
+static void bow_points(KeyFrame* K, const orc_bow_view* s) {
+    // valid[i]: a live map point; the others alternate between "no point" and "bad point" (both are skipped)
+    for (int i = 0; i < s->n; i++) {
+        const bool live = !s->valid || s->valid[i];
+        if (live || (i & 1)) K->mvpMapPoints[i] = make_point(vec3(0, 0, 1), s->desc + 32 * (size_t)i, 1, !live, 0, 1.f, 1.2f);
+    }
+}
+int orm_search_by_bow_frame(const orc_bow_view* s1, const orc_bow_view* s2, float nnratio, int check_ori, int* m21) {
+    std::vector<orc_keypoint> k1, k2;
+    KeyFrame* K = make_keyframe(bow_frame(s1, k1));
+    bow_points(K, s1);
+    Frame* F = bow_frame(s2, k2);
+    std::vector<MapPoint*> matches;
+    ORBmatcher matcher(nnratio, check_ori != 0);
+    const int n = matcher.SearchByBoW(K, *F, matches);
+    const std::vector<MapPoint*> kfPoints = K->GetMapPointMatches();
+    for (int i = 0; i < s2->n; i++) m21[i] = matches[i] ? index_of(kfPoints, matches[i]) : -1;
+    return n;
+}
+int orm_search_by_bow_keyframes(const orc_bow_view* s1, const orc_bow_view* s2, float nnratio, int check_ori, int* m12) {
+    std::vector<orc_keypoint> k1, k2;
+    KeyFrame* K1 = make_keyframe(bow_frame(s1, k1));
+    KeyFrame* K2 = make_keyframe(bow_frame(s2, k2));
+    bow_points(K1, s1); bow_points(K2, s2);
+    std::vector<MapPoint*> matches;
+    ORBmatcher matcher(nnratio, check_ori != 0);
+    const int n = matcher.SearchByBoW(K1, K2, matches);
+    const std::vector<MapPoint*> p2 = K2->GetMapPointMatches();
+    for (int i = 0; i < s1->n; i++) m12[i] = matches[i] ? index_of(p2, matches[i]) : -1;
+    return n;
+}
+
+/* ---- key-frame guided searches.  Points come as the restatement's orc_projpoints_view plus the gates the reference
+ * evaluates itself: in_view is NOT consulted here (the reference decides from the projection), `found` marks points of
+ * sAlreadyFound / bad points, normal_ok the viewing-angle gate. */
+static std::vector<MapPoint*> world_points(const orc_projpoints_view* p, const uint8_t* bad, const uint8_t* normal_ok, float scaleFactor) {
+    std::vector<MapPoint*> v(p->n);
+    for (int i = 0; i < p->n; i++) {
+        const float dist = (float)std::sqrt((double)p->u[i] * p->u[i] + (double)p->v[i] * p->v[i] + 1.0);
+        v[i] = make_point(vec3(p->u[i], p->v[i], 1.f), p->desc + 32 * (size_t)i, 1, bad && bad[i], p->level[i], dist, scaleFactor,
+                          normal_ok && !normal_ok[i] ? -1.0f : 1e6f);
+    }
+    return v;
+}
+/* SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) — src/ORBmatcher.cc:1641-1770.  Point i is the map point
+ * of key-frame keypoint i (angle = p->angle[i]); has_point 0 = no map point there. */
+int orm_sbp_frame_keyframe(const orc_frame_view* f, const orc_projpoints_view* p, const uint8_t* has_point, const uint8_t* bad,
+                           const uint8_t* found, float th, int orb_dist, int check_ori, const uint8_t* kp_occupied, int* match_for_kp) {
+    set_camera(1.f, 1.f, 0.f, 0.f);
+    Frame* C = make_frame(f);
+    std::vector<orc_keypoint> kk(p->n);
+    std::vector<uint8_t> kd((size_t)std::max(p->n, 1) * 32, 0);
+    for (int i = 0; i < p->n; i++) kk[i] = orc_keypoint{p->u[i], p->v[i], 31.f, p->angle[i], 0.f, 0, -1};
+    orc_frame_view kv = *f;
+    kv.n = p->n; kv.kps = kk.data(); kv.desc = kd.data(); kv.uright = nullptr;
+    KeyFrame* K = make_keyframe(make_frame(&kv));
+    const std::vector<MapPoint*> pts = world_points(p, bad, nullptr, C->mfScaleFactor);
+    std::set<MapPoint*> already;
+    for (int i = 0; i < p->n; i++) {
+        if (has_point[i]) K->mvpMapPoints[i] = pts[i];
+        if (found[i]) already.insert(pts[i]);
+    }
+    static const uint8_t zero[32] = {0};
+    MapPoint* owner = make_point(vec3(0, 0, 1), zero, 1, false, 0, 1.f, 1.2f);
+    for (int i = 0; i < f->n; i++) if (kp_occupied[i]) C->mvpMapPoints[i] = owner;
+    ORBmatcher matcher(0.9f, check_ori != 0);
+    const int n = matcher.SearchByProjection(*C, K, already, th, orb_dist);
+    for (int i = 0; i < f->n; i++) {
+        MapPoint* q = C->mvpMapPoints[i];
+        match_for_kp[i] = (q && q != owner) ? index_of(pts, q) : -1;
+    }
+    return n;
+}
+/* SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th) — src/ORBmatcher.cc:335-451, Scw = identity */
+int orm_sbp_keyframe_sim3(const orc_frame_view* f, const orc_projpoints_view* p, const uint8_t* bad, const uint8_t* normal_ok, int th,
+                          const uint8_t* kp_matched, int* match_for_kp) {
+    set_camera(1.f, 1.f, 0.f, 0.f);
+    KeyFrame* K = make_keyframe(make_frame(f));
+    const std::vector<MapPoint*> pts = world_points(p, bad, normal_ok, K->mfScaleFactor);
+    static const uint8_t zero[32] = {0};
+    MapPoint* owner = make_point(vec3(0, 0, 1), zero, 1, false, 0, 1.f, 1.2f);
+    std::vector<MapPoint*> matched(f->n, static_cast<MapPoint*>(nullptr));
+    for (int i = 0; i < f->n; i++) if (kp_matched[i]) matched[i] = owner;
+    ORBmatcher matcher(0.75f, true);
+    const int n = matcher.SearchByProjection(K, cv::Mat::eye(4, 4, CV_32F), pts, matched, th);
+    for (int i = 0; i < f->n; i++) match_for_kp[i] = (matched[i] && matched[i] != owner) ? index_of(pts, matched[i]) : -1;
+    return n;
+}
+/* Fuse(KeyFrame*, Scw, vpPoints, th, vpReplacePoint) — src/ORBmatcher.cc:1100-1237 — and Fuse(KeyFrame*, vpMapPoints, th) —
+ * :940-1090 (with_pose = 1: the reprojection gates run, bf / mvuRight as in the view).  kp_has_point: key-frame keypoints that
+ * hold a map point on entry.  best_idx[i] = the keypoint point i was fused with (through AddObservation, a Replace in either
+ * direction, or vpReplacePoint), -1 = not fused. */
+int orm_fuse(const orc_frame_view* f, const orc_projpoints_view* p, const uint8_t* bad, const uint8_t* normal_ok, float th, int with_pose,
+             float bf, const uint8_t* kp_has_point, const int* kp_point_obs, const int* point_obs, int* best_idx) {
+    set_camera(1.f, 1.f, 0.f, 0.f);
+    Frame* F = make_frame(f);
+    F->mbf = bf; F->mb = bf;
+    KeyFrame* K = make_keyframe(F);
+    std::vector<MapPoint*> pts = world_points(p, bad, normal_ok, K->mfScaleFactor);
+    for (int i = 0; i < p->n; i++) pts[i]->nObs = point_obs ? point_obs[i] : 1;
+    std::vector<MapPoint*> own(f->n, static_cast<MapPoint*>(nullptr));
+    for (int i = 0; i < f->n; i++)
+        if (kp_has_point && kp_has_point[i]) {
+            own[i] = make_point(vec3(f->kps[i].x, f->kps[i].y, 1.f), f->desc + 32 * (size_t)i, 0, false, 0, 1.f, 1.2f);
+            own[i]->AddObservation(K, i);
+            own[i]->nObs = kp_point_obs ? kp_point_obs[i] : 1;
+            K->mvpMapPoints[i] = own[i];
+            the_map()->AddMapPoint(own[i]);
+        }
+    for (int i = 0; i < p->n; i++) the_map()->AddMapPoint(pts[i]);
+    ORBmatcher matcher(0.6f, true);
+    int n;
+    std::vector<MapPoint*> replace(p->n, static_cast<MapPoint*>(nullptr));
+    if (with_pose) n = matcher.Fuse(K, pts, th);
+    else n = matcher.Fuse(K, cv::Mat::eye(4, 4, CV_32F), pts, th, replace);
+    for (int i = 0; i < p->n; i++) {
+        MapPoint* q = pts[i];
+        int idx = -1;
+        if (replace[i]) idx = replace[i]->GetIndexInKeyFrame(K);
+        else if (q->IsInKeyFrame(K)) idx = q->GetIndexInKeyFrame(K);
+        else if (q->mbBad && q->mpReplaced) {                       // pMP->Replace(pMPinKF): follow to the survivor
+            MapPoint* r = q->mpReplaced;
+            while (r && !r->IsInKeyFrame(K) && r->mpReplaced) r = r->mpReplaced;
+            if (r && r->IsInKeyFrame(K)) idx = r->GetIndexInKeyFrame(K);
+        }
+        best_idx[i] = idx;
+    }
+    return n;
+}
+/* SearchBySim3(pKF1, pKF2, vpMatches12, s12 = 1, R12 = I, t12 = 0, th) — src/ORBmatcher.cc:1251-1477.  Point i of p1 is the map
+ * point of KF1's keypoint i (projected into KF2 at p1->(u, v)), likewise p2; has1 / has2 = keypoint holds a point;
+ * pre12[i] >= 0: vpMatches12[i] preset to KF2's point pre12[i]. */
+int orm_search_by_sim3(const orc_frame_view* f1, const orc_frame_view* f2, const orc_projpoints_view* p1, const orc_projpoints_view* p2,
+                       const uint8_t* has1, const uint8_t* has2, const uint8_t* bad1, const uint8_t* bad2, const int* pre12, float th,
+                       int* matches12) {
+    set_camera(1.f, 1.f, 0.f, 0.f);
+    KeyFrame* K1 = make_keyframe(make_frame(f1));
+    KeyFrame* K2 = make_keyframe(make_frame(f2));
+    const std::vector<MapPoint*> a = world_points(p1, bad1, nullptr, K1->mfScaleFactor), b = world_points(p2, bad2, nullptr, K2->mfScaleFactor);
+    for (int i = 0; i < f1->n; i++) if (has1[i]) { K1->mvpMapPoints[i] = a[i]; a[i]->mObservations[K1] = i; }
+    for (int i = 0; i < f2->n; i++) if (has2[i]) { K2->mvpMapPoints[i] = b[i]; b[i]->mObservations[K2] = i; }
+    std::vector<MapPoint*> m12(f1->n, static_cast<MapPoint*>(nullptr));
+    for (int i = 0; i < f1->n; i++) if (pre12[i] >= 0) m12[i] = b[pre12[i]];
+    ORBmatcher matcher(0.75f, true);
+    const int n = matcher.SearchBySim3(K1, K2, m12, 1.0f, cv::Mat::eye(3, 3, CV_32F), cv::Mat::zeros(3, 1, CV_32F), th);
+    for (int i = 0; i < f1->n; i++) matches12[i] = m12[i] ? index_of(b, m12[i]) : -1;
+    return n;
+}
+/* SearchForTriangulation — src/ORBmatcher.cc:754-928.  The epipole (ex, ey) is produced by camera 2 sitting at t2w = (ex, ey, 1). */
+int orm_search_for_triangulation(const orc_tri_side* s1, const orc_tri_side* s2, const float* F12, float ex, float ey,
+                                 const float* scale_factors, int nlevels, float w, float h, int only_stereo, int check_ori, int* matches12) {
+    set_camera(1.f, 1.f, 0.f, 0.f);
+    KeyFrame* K[2];
+    const orc_tri_side* s[2] = {s1, s2};
+    static const uint8_t zero[32] = {0};
+    for (int c = 0; c < 2; c++) {
+        orc_frame_view v = {s[c]->n, s[c]->kps, s[c]->desc, s[c]->uright, 0.f, w, 0.f, h, scale_factors, nlevels, 0};
+        Frame* F = make_frame(&v, c ? ex : 0.f, c ? ey : 0.f, c ? 1.f : 0.f);
+        F->mFeatVec = feat_vec(s[c]->nnodes, s[c]->node_id, s[c]->node_start, s[c]->indices);
+        K[c] = make_keyframe(F);
+        for (int i = 0; i < s[c]->n; i++) if (s[c]->has_mappoint[i]) K[c]->mvpMapPoints[i] = make_point(vec3(0, 0, 1), zero, 1, false, 0, 1.f, 1.2f);
+    }
+    cv::Mat Fm(3, 3, CV_32F);
+    for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) Fm.at<float>(r, c) = F12[3 * r + c];
+    std::vector<std::pair<size_t, size_t> > pairs;
+    ORBmatcher matcher(0.6f, check_ori != 0);
+    const int n = matcher.SearchForTriangulation(K[0], K[1], Fm, pairs, only_stereo != 0);
+    for (int i = 0; i < s1->n; i++) matches12[i] = -1;
+    for (size_t i = 0; i < pairs.size(); i++) matches12[pairs[i].first] = (int)pairs[i].second;
+    return n;
+}
+
+/* MapPoint::ComputeDistinctiveDescriptors — src/MapPoint.cc:266-334: point p is observed by one key frame per row of its set */
+void orm_distinctive_descriptors(const uint8_t* desc, const int* start, int npoints, int* best) {
+    static const float one = 1.0f;
+    static const uint8_t zero[32] = {0};
+    for (int p = 0; p < npoints; p++) {
+        const int n = start[p + 1] - start[p];
+        std::vector<orc_keypoint> k(std::max(n, 1), orc_keypoint{5.f, 5.f, 31.f, 0.f, 0.f, 0, -1});
+        orc_frame_view v = {n, k.data(), desc + 32 * (size_t)start[p], nullptr, 0.f, 640.f, 0.f, 480.f, &one, 1, 0};
+        Frame* F = make_frame(&v);
+        MapPoint* mp = make_point(vec3(0, 0, 1), zero, 0, false, 0, 1.f, 1.2f);
+        // one key frame per observation, each seeing the point at its own row
+        std::vector<KeyFrame*> ks(n);
+        for (int i = 0; i < n; i++) ks[i] = make_keyframe(F);
+        std::sort(ks.begin(), ks.end());                       // std::map order = pointer order: row i goes to the i-th key frame
+        for (int i = 0; i < n; i++) mp->mObservations[ks[i]] = i;
+        mp->mDescriptor.release();
+        mp->ComputeDistinctiveDescriptors();
+        best[p] = -1;
+        if (n) {
+            const cv::Mat d = mp->GetDescriptor();
+            // the reference keeps the first row (in its iteration order) with the least median; rows may repeat, so report
+            // the winner by content: the lowest row index holding the chosen bytes
+            for (int i = 0; i < n && best[p] < 0; i++) if (!std::memcmp(d.data, desc + 32 * (size_t)(start[p] + i), 32)) best[p] = i;
+        }
+    }
+}
+
+/* Frame::ComputeStereoMatches (src/Frame.cc:512-686) on given keypoint lists: the two extractors only supply their
+ * mvImagePyramid (built here, single-threaded, by running them on the images; their own keypoints are discarded). */
+void orm_compute_stereo_matches(const orc_frame_view* fl, const orc_frame_view* fr, const uint8_t* left, const uint8_t* right, int w, int h,
+                                float fx, float bf, float* uright, float* depth) {
+    ORBextractor exL(1000, 1.2f, fl->nlevels, 20, 7), exR(1000, 1.2f, fl->nlevels, 20, 7);
+    cv::Mat imL(h, w, CV_8UC1, (void*)left, (size_t)w), imR(h, w, CV_8UC1, (void*)right, (size_t)w);
+    {
+        std::vector<cv::KeyPoint> k; cv::Mat d;
+        exL(imL, cv::Mat(), k, d);
+        exR(imR, cv::Mat(), k, d);
+    }
+    Frame* F = make_frame(fl);
+    F->mvKeysRight.resize(fr->n);
+    for (int i = 0; i < fr->n; i++) F->mvKeysRight[i] = to_cv(fr->kps[i]);
+    F->mDescriptorsRight.create(std::max(fr->n, 1), 32, CV_8UC1);
+    if (fr->n) std::memcpy(F->mDescriptorsRight.data, fr->desc, (size_t)fr->n * 32);
+    F->mpORBextractorLeft = &exL; F->mpORBextractorRight = &exR;
+    F->mbf = bf; F->mb = bf / fx;                                  // src/Frame.cc:109
+    F->ComputeStereoMatches();
+    for (int i = 0; i < fl->n; i++) { uright[i] = F->mvuRight[i]; depth[i] = F->mvDepth[i]; }
+    F->mpORBextractorLeft = F->mpORBextractorRight = nullptr;
+}
+
 }  // extern "C"

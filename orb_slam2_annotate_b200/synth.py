@@ -83,11 +83,12 @@ def sequence(n: int, width: int = 640, height: int = 480, seed: int = 0, max_shi
 
 
 def stereo_pair(width: int = 1241, height: int = 376, seed: int = 0, disparity: int = 20) -> tuple[np.ndarray, np.ndarray]:
-    """Stereo pair (config 3): right = left scene shifted by a global disparity."""
+    """Stereo pair (config 3): one scene seen with a global disparity, uL - uR = disparity > 0 (a scene point sits
+    further left in the right image, as for a rectified pair)."""
     rng = np.random.Generator(np.random.PCG64(seed + 0x57E0))
     base = canvas(width + disparity, height, seed)
-    left = base[:, disparity:disparity + width]
-    right = base[:, :width]
+    left = base[:, :width]
+    right = base[:, disparity:disparity + width]
     nl = rng.normal(0.0, 2.0, left.shape).astype(np.float32)
     nr = rng.normal(0.0, 2.0, left.shape).astype(np.float32)
     return (np.clip(np.rint(left + nl), 0, 255).astype(np.uint8),

@@ -1,0 +1,308 @@
+"""Pins the matcher-side restatements (oracle/orc_matcher.cpp, orc_bow.cpp, orc_guided.cpp, orc_mappoint.cpp and the stereo
+matcher) against the UNMODIFIED reference translation units — src/ORBmatcher.cc, Frame.cc, KeyFrame.cc, MapPoint.cc, Map.cc
+and the vendored DBoW2 sources, compiled in place against oracle/cvshim into oracle/_ref/liborbref_matcher.so
+(oracle/ref_matcher_wrap.cpp builds the reference's own Frame / KeyFrame / MapPoint objects from the same flat arrays).
+Live where that library is built (this container; it travels to the GPU box), and against the committed outputs of the
+same library otherwise (tests/golden/ref_matcher.npz, made by tests/golden/make_ref_matcher_golden.py)."""
+import os
+
+import numpy as np
+import pytest
+
+from orb_slam2_annotate_b200 import synth
+
+W, H = 640, 480
+_cache = {}
+
+
+def frames(oracle, seed=4, nf=1000, n=2):
+    key = (seed, nf, n)
+    if key not in _cache:
+        imgs, off = synth.sequence(n, W, H, seed=seed)
+        out = []
+        for im in imgs:
+            oc = oracle.OracleExtractor(nf)
+            k, d = oc(im)
+            out.append((k, d, oc.tables()))
+        _cache[key] = (out, off)
+    return _cache[key]
+
+
+def flip(desc, rng, maxflips):
+    desc = desc.copy()
+    for i in range(len(desc)):
+        bits = rng.choice(256, rng.integers(0, maxflips + 1), replace=False)
+        np.bitwise_xor.at(desc[i], bits >> 3, (1 << (bits & 7)).astype(np.uint8))
+    return desc
+
+
+def points_near(k, d, scale, rng, n=None, th=4.0, shift=(0.0, 0.0), jitter=3.0, maxflips=50):
+    """map points that project near keypoints of k (one per keypoint when n is None)"""
+    src = np.arange(len(k)) if n is None else rng.integers(0, len(k), n)
+    n = len(src)
+    lvl = np.clip(k["octave"][src] + rng.integers(0, 2, n), 0, 7).astype(np.int32)
+    u = (k["x"][src] + np.float32(shift[0]) + rng.uniform(-jitter, jitter, n)).astype(np.float32)
+    v = (k["y"][src] + np.float32(shift[1]) + rng.uniform(-jitter, jitter, n)).astype(np.float32)
+    return dict(u=u, v=v, ur=u.copy(), radius=(np.float32(th) * scale[lvl]).astype(np.float32), level=lvl,
+                angle=k["angle"][src].astype(np.float32), desc=flip(d[src], rng, maxflips)), src
+
+
+def need_ref(oracle):
+    if oracle.mref_lib() is None:
+        pytest.skip("oracle/_ref/liborbref_matcher.so not built (reference tree not mounted)")
+
+
+# ------------------------------------------------------------------------------------------------ the scenarios
+# Each returns {name: array}: the restatement's outputs.  run(oracle, ref=True) gives the reference's for the same inputs.
+
+def scenario_grid_and_area(oracle, ref):
+    (fr, _) = frames(oracle)
+    k, d, t = fr[0]
+    rng = np.random.default_rng(3)
+    out = {}
+    for kf in (0, 1):
+        f = oracle.frame_view(k, d, W, H, t["scale"], bounds=(-12.7, 655.3, -9.6, 489.4), keyframe=bool(kf))
+        cs, items = (oracle.ref_assign_grid if ref else oracle.assign_grid)(f)
+        out[f"grid{kf}_start"], out[f"grid{kf}_items"] = cs, items
+        got = []
+        for _ in range(200):
+            x, y, r = float(rng.uniform(-30, 680)), float(rng.uniform(-30, 500)), float(rng.uniform(1, 60))
+            lv = (-1, -1) if kf else tuple(int(v) for v in rng.choice([-1, 0, 1, 2, 3, 5], 2))
+            a = (oracle.ref_features_in_area if ref else oracle.features_in_area)(f, x, y, r, *lv)
+            got.append(np.concatenate([[len(a)], a]))
+        out[f"area{kf}"] = np.concatenate(got).astype(np.int32)
+    return out
+
+
+def scenario_search_for_initialization(oracle, ref):
+    out = {}
+    for seed in (4, 9):
+        (fr, _) = frames(oracle, seed)
+        (k1, d1, t), (k2, d2, _) = fr
+        f1 = oracle.frame_view(k1, d1, W, H, t["scale"]); f2 = oracle.frame_view(k2, d2, W, H, t["scale"])
+        for (win, ratio, ori) in [(100, 0.9, True), (40, 0.7, False), (300, 0.9, True)]:
+            prev = np.ascontiguousarray(np.stack([k1["x"], k1["y"]], 1), np.float32)
+            n, m = (oracle.ref_search_for_initialization if ref else oracle.search_for_initialization)(f1, f2, prev, win, ratio, ori)
+            out[f"init_{seed}_{win}"] = np.concatenate([[n], m, prev.view(np.int32).ravel()]).astype(np.int32)
+    return out
+
+
+def scenario_search_by_projection(oracle, ref):
+    (fr, off) = frames(oracle)
+    (k1, d1, t), (k2, d2, _) = fr
+    scale = t["scale"]
+    rng = np.random.default_rng(5)
+    out = {}
+    for (nmp, th, stereo) in [(3000, 3.0, False), (800, 5.0, True), (200, 15.0, False)]:
+        src = rng.integers(0, len(k2), nmp)
+        ur = np.where(rng.random(len(k2)) < 0.5, k2["x"] - 20, -1).astype(np.float32) if stereo else None
+        px = (k2["x"][src] + rng.uniform(-3, 3, nmp)).astype(np.float32)
+        mps = dict(track_in_view=(rng.random(nmp) < 0.9).astype(np.uint8), proj_x=px, proj_y=(k2["y"][src] + rng.uniform(-3, 3, nmp)).astype(np.float32),
+                   proj_xr=(px - 20 + rng.uniform(-2, 2, nmp)).astype(np.float32), level=np.clip(k2["octave"][src] + rng.integers(0, 2, nmp), 0, 7).astype(np.int32),
+                   view_cos=np.where(rng.random(nmp) < 0.5, 0.9995, 0.9).astype(np.float32), desc=flip(d2[src], rng, 60),
+                   observations=rng.integers(0, 4, nmp).astype(np.int32))
+        occ = (rng.random(len(k2)) < 0.1).astype(np.uint8)
+        f = oracle.frame_view(k2, d2, W, H, scale, ur)
+        n, m = (oracle.ref_search_by_projection if ref else oracle.search_by_projection)(f, mps, th, 0.8, occ.copy())
+        out[f"local_{nmp}"] = np.concatenate([[n], m]).astype(np.int32)
+    # SearchByProjection(CurrentFrame, LastFrame, th, bMono = true)
+    sx, sy = float(off[0][0] - off[1][0]), float(off[0][1] - off[1][1])
+    n1 = len(k1)
+    u = (k1["x"] + np.float32(sx) + rng.uniform(-3, 3, n1)).astype(np.float32); v = (k1["y"] + np.float32(sy) + rng.uniform(-3, 3, n1)).astype(np.float32)
+    has = (rng.random(n1) < 0.8).astype(np.uint8); outl = (rng.random(n1) < 0.1).astype(np.uint8)
+    obs = rng.integers(0, 4, n1).astype(np.int32); dsc = flip(d1, rng, 40)
+    for (th, ori) in [(15.0, True), (7.0, False)]:
+        occ = (rng.random(len(k2)) < 0.1).astype(np.uint8)
+        f = oracle.frame_view(k2, d2, W, H, scale)
+        if ref:
+            last = dict(has_point=has, outlier=outl, u=u, v=v, octave=k1["octave"], angle=k1["angle"], desc=dsc, observations=obs)
+            n, m = oracle.ref_search_by_projection_frame(f, last, th, True, 0.0, ori, occ)
+        else:
+            inb = (u >= 0) & (u <= W) & (v >= 0) & (v <= H)
+            pts = dict(valid=(has.astype(bool) & ~outl.astype(bool) & inb).astype(np.uint8), u=u, v=v, ur=u, radius=(np.float32(th) * scale[k1["octave"]]).astype(np.float32),
+                       min_level=k1["octave"] - 1, max_level=k1["octave"] + 1, angle=k1["angle"], desc=dsc, observations=obs)
+            n, m = oracle.search_by_projection_frame(f, pts, ori, occ)
+            m = np.where(m == -2, -1, m)                    # a match the rotation check removed leaves NULL behind
+        out[f"last_{int(th)}"] = np.concatenate([[n], m]).astype(np.int32)
+    return out
+
+
+def _bow_sides(oracle, rng, nbits):
+    (fr, _) = frames(oracle)
+    sides = []
+    for k, d, _ in fr:
+        fv = {}
+        for i in range(len(k)):
+            fv.setdefault(int((d[i, 0] & ((1 << nbits) - 1)) | (k["octave"][i] << nbits)), []).append(i)
+        sides.append((d, k["angle"], fv, (rng.random(len(k)) < 0.7).astype(np.uint8)))
+    return sides
+
+
+def scenario_search_by_bow(oracle, ref):
+    rng = np.random.default_rng(6)
+    out = {}
+    for nbits, ratio, ori in [(4, 0.7, True), (2, 0.75, False), (6, 0.9, True)]:
+        (da, aa, fva, va), (db, ab, fvb, vb) = _bow_sides(oracle, rng, nbits)
+        if ref:
+            n1, m21 = oracle.ref_search_by_bow(oracle.bow_view(da, aa, fva, va), oracle.bow_view(db, ab, fvb), ratio, ori, False)
+            n2, m12 = oracle.ref_search_by_bow(oracle.bow_view(da, aa, fva, va), oracle.bow_view(db, ab, fvb, vb), ratio, ori, True)
+        else:
+            n1, _, m21 = oracle.search_by_bow(oracle.bow_view(da, aa, fva, va), oracle.bow_view(db, ab, fvb), 50, ratio, ori)
+            n2, m12, _ = oracle.search_by_bow(oracle.bow_view(da, aa, fva, va), oracle.bow_view(db, ab, fvb, vb), 49, ratio, ori)
+        out[f"bow_frame_{nbits}"] = np.concatenate([[n1], m21]).astype(np.int32)
+        out[f"bow_kf_{nbits}"] = np.concatenate([[n2], m12]).astype(np.int32)
+    return out
+
+
+def scenario_guided(oracle, ref):
+    (fr, off) = frames(oracle)
+    (k1, d1, t), (k2, d2, _) = fr
+    scale = t["scale"]
+    rng = np.random.default_rng(7)
+    s12 = (float(off[0][0] - off[1][0]), float(off[0][1] - off[1][1]))
+    out = {}
+    in_frame = lambda u, v: (u >= 0) & (u <= W) & (v >= 0) & (v <= H)
+    in_kf = lambda u, v: (u >= 0) & (u < W) & (v >= 0) & (v < H)
+    # SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist): key frame = frame 0's keypoints, current = frame 1
+    for th, orb_dist, ori in [(10.0, 100, True), (6.0, 64, False)]:
+        p, _ = points_near(k1, d1, scale, rng, None, th, s12)
+        has = rng.random(len(k1)) < 0.8; bad = rng.random(len(k1)) < 0.05; found = rng.random(len(k1)) < 0.1
+        occ = (rng.random(len(k2)) < 0.1).astype(np.uint8)
+        f = oracle.frame_view(k2, d2, W, H, scale)
+        if ref:
+            n, m = oracle.ref_sbp_frame_keyframe(f, p, has, bad, found, th, orb_dist, ori, occ)
+        else:
+            n, m = oracle.search_by_projection_keyframe(f, dict(p, valid=(has & ~bad & ~found & in_frame(p["u"], p["v"])).astype(np.uint8)), orb_dist, ori, occ)
+            m = np.where(m == -2, -1, m)
+        out[f"sbp_kf_{int(th)}"] = np.concatenate([[n], m]).astype(np.int32)
+    # SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th), Fuse x 2 into key frame = frame 1 (fractional bounds)
+    bounds = (-12.7, 655.3, -9.6, 489.4)
+    in_kfb = lambda u, v: (u >= int(bounds[0])) & (u < int(bounds[1])) & (v >= int(bounds[2])) & (v < int(bounds[3]))
+    for nmp, th in [(3000, 10), (12000, 4)]:
+        p, _ = points_near(k2, d2, scale, rng, nmp, float(th))
+        bad = rng.random(nmp) < 0.05; nok = rng.random(nmp) < 0.9
+        matched = (rng.random(len(k2)) < 0.2).astype(np.uint8)
+        f = oracle.frame_view(k2, d2, W, H, scale, bounds=bounds, keyframe=True)
+        valid = (~bad & nok & in_kfb(p["u"], p["v"])).astype(np.uint8)
+        if ref:
+            n, m = oracle.ref_sbp_keyframe_sim3(f, p, bad, nok, th, matched)
+        else:
+            n, m = oracle.search_by_projection_sim3(f, dict(p, valid=valid), matched)
+        out[f"sim3_proj_{nmp}"] = np.concatenate([[n], m]).astype(np.int32)
+        # Fuse(pKF, Scw, vpPoints, th, vpReplacePoint): no key-frame point is bad, so "fused" = a best index exists
+        kp_has = (rng.random(len(k2)) < 0.5).astype(np.uint8)
+        if ref:
+            n, bi = oracle.ref_fuse(f, p, bad, nok, float(th), False, 0.0, kp_has)
+        else:
+            bi, _ = oracle.fuse_search(f, dict(p, valid=valid), None)
+            n = int((bi >= 0).sum())
+        out[f"fuse_sim3_{nmp}"] = np.concatenate([[n], bi]).astype(np.int32)
+    for stereo, th, nmp in [(False, 3.0, 8000), (True, 3.0, 4000)]:
+        bf = 20.0 if stereo else 0.0
+        ur = np.where(rng.random(len(k2)) < 0.5, k2["x"] - 20 + rng.uniform(-1.5, 1.5, len(k2)), -1).astype(np.float32) if stereo else None
+        p, _ = points_near(k2, d2, scale, rng, nmp, th, jitter=2.5)
+        p["ur"] = (p["u"] - np.float32(bf)).astype(np.float32)
+        bad = rng.random(nmp) < 0.05; nok = rng.random(nmp) < 0.9
+        kp_has = (rng.random(len(k2)) < 0.5).astype(np.uint8)
+        kobs = rng.integers(1, 5, len(k2)).astype(np.int32); pobs = rng.integers(1, 5, nmp).astype(np.int32)
+        f = oracle.frame_view(k2, d2, W, H, scale, ur, keyframe=True)
+        if ref:
+            n, bi = oracle.ref_fuse(f, p, bad, nok, th, True, bf, kp_has, kobs, pobs)
+        else:
+            bi, _ = oracle.fuse_search(f, dict(p, valid=(~bad & nok & in_kf(p["u"], p["v"])).astype(np.uint8)), t["inv_sigma2"])
+            n = -1
+        out[f"fuse_pose_{int(stereo)}"] = bi.astype(np.int32)
+        if ref:
+            out[f"fuse_pose_{int(stereo)}_n"] = np.array([n], np.int32)
+    # SearchBySim3
+    for th in (7.5, 15.0):
+        p1, _ = points_near(k1, d1, scale, rng, None, th, s12, jitter=2.0, maxflips=30)
+        p2, _ = points_near(k2, d2, scale, rng, None, th, (-s12[0], -s12[1]), jitter=2.0, maxflips=30)
+        has1 = rng.random(len(k1)) < 0.8; has2 = rng.random(len(k2)) < 0.8
+        bad1 = rng.random(len(k1)) < 0.05; bad2 = rng.random(len(k2)) < 0.05
+        pre = np.full(len(k1), -1, np.int32)
+        cand = np.nonzero(has2)[0]
+        sel = rng.choice(len(k1), 60, replace=False)
+        pre[sel] = rng.choice(cand, 60, replace=False)
+        f1 = oracle.frame_view(k1, d1, W, H, scale, keyframe=True); f2 = oracle.frame_view(k2, d2, W, H, scale, keyframe=True)
+        if ref:
+            n, m = oracle.ref_search_by_sim3(f1, f2, p1, p2, has1, has2, bad1, bad2, pre, th)
+        else:
+            done1 = pre >= 0
+            done2 = np.zeros(len(k2), bool); done2[pre[done1]] = True
+            v1 = (has1 & ~done1 & ~bad1 & in_kf(p1["u"], p1["v"])).astype(np.uint8)
+            v2 = (has2 & ~done2 & ~bad2 & in_kf(p2["u"], p2["v"])).astype(np.uint8)
+            n, m = oracle.search_by_sim3(f1, f2, dict(p1, valid=v1), dict(p2, valid=v2))
+            m = np.where(done1, pre, m)                      # preset entries stay in vpMatches12
+        out[f"sim3_{int(th)}"] = np.concatenate([[n], m]).astype(np.int32)
+    # SearchForTriangulation
+    for nbits, only_stereo, ori in [(3, False, True), (2, True, False)]:
+        sides = []
+        for (k, d) in ((k1, d1), (k2, d2)):
+            fv = {}
+            for i in range(len(k)):
+                fv.setdefault(int((d[i, 0] & ((1 << nbits) - 1)) | (k["octave"][i] << nbits)), []).append(i)
+            urr = np.where(rng.random(len(k)) < 0.5, k["x"] - 15, -1).astype(np.float32)
+            sides.append(oracle.tri_side(k, d, (rng.random(len(k)) < 0.3).astype(np.uint8), fv, urr))
+        F12 = np.array([[0, 0, s12[1]], [0, 0, -s12[0]], [-s12[1], s12[0], 0]], np.float32)
+        if ref:
+            n, m = oracle.ref_search_for_triangulation(sides[0], sides[1], F12, 300.0, 200.0, scale, float(W), float(H), only_stereo, ori)
+        else:
+            n, m = oracle.search_for_triangulation(sides[0], sides[1], F12, 300.0, 200.0, scale, t["sigma2"], only_stereo, ori)
+        out[f"tri_{nbits}"] = np.concatenate([[n], m]).astype(np.int32)
+    return out
+
+
+def scenario_distinctive(oracle, ref):
+    rng = np.random.default_rng(8)
+    sizes = np.concatenate([[0, 1, 2, 3], rng.integers(2, 25, 60)])
+    start = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    base = rng.integers(0, 256, (len(sizes), 32), dtype=np.uint8)
+    desc = flip(np.repeat(base, sizes, axis=0), rng, 40)
+    desc[start[10]:start[10] + 2] = desc[start[10]]          # repeated rows: the first wins
+    best = (oracle.ref_distinctive_descriptors if ref else oracle.distinctive_descriptors)(desc, start)
+    return {"distinctive": best.astype(np.int32)}
+
+
+def scenario_stereo(oracle, ref):
+    """Frame::ComputeStereoMatches on the keypoint lists of the (bump-allocator contract) extraction of both images; the
+    reference reads the pyramids of its own extractors, the restatement those of the oracle extractor."""
+    out = {}
+    for (w, h, nf, seed, disp, fx, bf) in [(W, H, 1000, 21, 12, 500.0, 40.0), (1241, 376, 2000, 2, 20, 718.856, 386.1448)]:
+        left, right = synth.stereo_pair(w, h, seed=seed, disparity=disp)
+        ol, orr = oracle.OracleExtractor(nf), oracle.OracleExtractor(nf)
+        k, d = ol(left); kr, dr = orr(right)
+        t = ol.tables()
+        fl = oracle.frame_view(k, d, w, h, t["scale"]); frr = oracle.frame_view(kr, dr, w, h, t["scale"])
+        if ref:
+            ur, dp = oracle.ref_compute_stereo_matches(fl, frr, left, right, fx, bf)
+        else:
+            pl = oracle.pyramid_view([ol.level(l) for l in range(8)]); pr = oracle.pyramid_view([orr.level(l) for l in range(8)])
+            ur, dp = oracle.compute_stereo_matches(fl, frr, pl, pr, t["inv_scale"], bf, np.float32(bf) / np.float32(fx))
+        out[f"stereo_{w}_uright"] = ur.view(np.int32).copy(); out[f"stereo_{w}_depth"] = dp.view(np.int32).copy()
+        out[f"stereo_{w}_matched"] = np.array([(ur >= 0).sum()], np.int32)
+    return out
+
+
+SCENARIOS = [scenario_grid_and_area, scenario_search_for_initialization, scenario_search_by_projection, scenario_search_by_bow,
+             scenario_guided, scenario_distinctive, scenario_stereo]
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "ref_matcher.npz")
+
+
+@pytest.mark.parametrize("scenario", SCENARIOS, ids=lambda s: s.__name__[9:])
+def test_restatement_equals_reference_live(oracle, scenario):
+    need_ref(oracle)
+    mine, theirs = scenario(oracle, False), scenario(oracle, True)
+    for name, a in mine.items():
+        assert np.array_equal(a, theirs[name]), name
+    if scenario is scenario_stereo:
+        assert mine["stereo_640_matched"][0] > 300 and mine["stereo_1241_matched"][0] > 600
+
+
+@pytest.mark.parametrize("scenario", SCENARIOS, ids=lambda s: s.__name__[9:])
+def test_restatement_equals_reference_fixture(oracle, scenario):
+    if not os.path.exists(GOLDEN):
+        pytest.skip("tests/golden/ref_matcher.npz not generated")
+    G = np.load(GOLDEN)
+    for name, a in scenario(oracle, False).items():
+        assert np.array_equal(a, G[name]), name
