@@ -12,9 +12,13 @@
  * fixtures made from it (tests/golden/make_golden.py) for every OpenCV primitive, and
  * (b) the UNMODIFIED reference translation unit src/ORBextractor.cc compiled against
  * oracle/cvshim (oracle/_ref/liborbref.so, built by oracle/Makefile) for the extractor.
- * The matcher restatements follow the reference line by line but the matcher TUs cannot be
- * compiled here (they need Eigen/g2o/DBoW2): for those, parity is "unpinned by execution"
- * and anchored on known-answer tests derived by hand from the cited lines.
+ * The matcher restatements follow the reference line by line and are pinned the same way: the
+ * UNMODIFIED src/ORBmatcher.cc, Frame.cc, KeyFrame.cc, MapPoint.cc, Map.cc and the vendored DBoW2
+ * sources compile in place against oracle/cvshim (plus a stand-in for include/Converter.h, the
+ * one header that needs Eigen / g2o) into oracle/_ref/liborbref_matcher.so; ref_matcher_wrap.cpp
+ * builds the reference's own Frame / KeyFrame / MapPoint objects from the same flat arrays and
+ * tests/test_oracle_vs_ref_matcher.py compares every routine, live and against the committed
+ * fixture tests/golden/ref_matcher.npz.  Hand-derived known-answer tests stay beside that.
  */
 #ifndef ORB_ORACLE_H
 #define ORB_ORACLE_H

@@ -14,8 +14,9 @@
 //   * which index the result vector uses: side 2's (:267) or side 1's (:690)
 //                                            -> both m12 and m21 are returned.
 // DBoW2 itself (vocabulary, transform) is a third-party dependency outside the path: the feature
-// vectors arrive as data.  Like the other matcher routines the TU cannot be compiled here, so
-// parity is anchored on hand-derived known-answer tests (tests/test_oracle_matcher.py).
+// vectors arrive as data.  Parity: pinned against the unmodified src/ORBmatcher.cc with real
+// DBoW2::FeatureVector objects (oracle/_ref/liborbref_matcher.so, tests/test_oracle_vs_ref_matcher.py::search_by_bow)
+// besides the hand-derived known-answer tests (tests/test_oracle_matcher.py).
 #include "orb_oracle.h"
 
 #include <cmath>

@@ -15,8 +15,9 @@
 // per-point `valid`, (u, v), `ur`, `radius` and predicted `level`; what is restated here is the
 // part that reads keypoints and descriptors.  Map mutation (Replace, AddObservation, AddMapPoint)
 // stays with the caller as well: the Fuse routines return the chosen keypoint per map point.
-// The TU cannot be compiled here (Eigen / g2o / DBoW2 headers are absent), so parity is anchored on
-// hand-derived known-answer tests (tests/test_oracle_guided.py): unpinned by execution.
+// Parity: pinned against the unmodified src/ORBmatcher.cc (oracle/_ref/liborbref_matcher.so,
+// tests/test_oracle_vs_ref_matcher.py::guided) besides the hand-derived known-answer tests
+// (tests/test_oracle_guided.py).
 #include "orb_oracle.h"
 
 #include <algorithm>

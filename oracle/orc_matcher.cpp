@@ -9,9 +9,10 @@
 //   Frame::GetFeaturesInArea              src/Frame.cc:358-415
 //   Frame::ComputeStereoMatches           src/Frame.cc:512-686
 //   brute-force kNN-2 + ratio             inner loops of SearchByBoW, src/ORBmatcher.cc:233-269
-// These TUs cannot be compiled here (Frame.cc needs Eigen/g2o/DBoW2 headers), so this file is
-// the only executable statement of them: parity for the matcher is anchored on hand-derived
-// known-answer tests (tests/test_oracle_matcher.py).
+// Parity: every routine here is pinned against the unmodified reference TUs — src/ORBmatcher.cc,
+// Frame.cc, KeyFrame.cc compiled in place against oracle/cvshim (oracle/_ref/liborbref_matcher.so,
+// tests/test_oracle_vs_ref_matcher.py, live and against tests/golden/ref_matcher.npz) — besides the
+// hand-derived known-answer tests (tests/test_oracle_matcher.py).
 #include "orb_oracle.h"
 
 #include <algorithm>

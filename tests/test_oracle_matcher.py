@@ -1,5 +1,6 @@
 """Known-answer tests for the oracle's matcher restatements (oracle/orc_matcher.cpp), derived by
-hand from the cited reference lines; the matcher TUs cannot be compiled here (Eigen/g2o/DBoW2)."""
+hand from the cited reference lines.  (The same routines are compared with the unmodified reference TUs in
+tests/test_oracle_vs_ref_matcher.py.)"""
 import numpy as np
 
 from oracle.oracle_py import KP_DTYPE
