@@ -584,6 +584,7 @@ def _mref_more():
     L.orm_search_for_triangulation.argtypes = [P, P, P, F, F, P, I, F, F, I, I, P]
     L.orm_distinctive_descriptors.argtypes = [P, P, I, P]
     L.orm_compute_stereo_matches.argtypes = [P, P, P, P, I, I, F, F, P, P]
+    L.orm_mono_frame.argtypes = [P, I, I, I, P, P, I, P, P, P, P, P, I]
     L._more = True
     return L
 
@@ -680,3 +681,19 @@ def ref_compute_stereo_matches(fl, fr, left: np.ndarray, right: np.ndarray, fx: 
     L.orm_compute_stereo_matches(C.byref(fl[0]), C.byref(fr[0]), left.ctypes.data, right.ctypes.data, w, h, fx, bf, ur.ctypes.data, dp.ctypes.data)
     L.orm_reset()
     return ur[:fl[0].n], dp[:fl[0].n]
+
+
+def ref_mono_frame(img: np.ndarray, nfeatures: int, cam, dist):
+    """The reference's monocular Frame constructor -> (mvKeys, mvKeysUn, bounds[4], cell_start, cell_items)"""
+    L = _mref_more()
+    h, w = img.shape
+    cap = 4 * nfeatures + 4096
+    img = np.ascontiguousarray(img)
+    k = np.empty(cap, KP_DTYPE); ku = np.empty(cap, KP_DTYPE); b = np.empty(4, np.float32)
+    cs = np.empty(64 * 48 + 1, np.int32); items = np.empty(cap, np.int32)
+    camv = np.ascontiguousarray(cam, np.float32); dv = np.ascontiguousarray(dist, np.float32)
+    n = L.orm_mono_frame(img.ctypes.data, w, h, nfeatures, camv.ctypes.data, dv.ctypes.data, len(dv), k.ctypes.data, ku.ctypes.data, b.ctypes.data,
+                         cs.ctypes.data, items.ctypes.data, cap)
+    L.orm_reset()
+    assert n >= 0
+    return k[:n].copy(), ku[:n].copy(), b, cs, items[:cs[-1]].copy()

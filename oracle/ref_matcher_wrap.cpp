@@ -507,4 +507,37 @@ void orm_compute_stereo_matches(const orc_frame_view* fl, const orc_frame_view* 
     F->mpORBextractorLeft = F->mpORBextractorRight = nullptr;
 }
 
+
+/* Frame::Frame(imGray, timeStamp, extractor, voc, K, distCoef, bf, thDepth) — src/Frame.cc:173-243: extraction, then the
+ * epilogue UndistortKeyPoints (:443-475), ComputeImageBounds (:477-510) and AssignFeaturesToGrid (:246-267).  Returns N;
+ * kps = mvKeys, kps_un = mvKeysUn, bounds = mnMinX, mnMaxX, mnMinY, mnMaxY, grid in CSR form. */
+int orm_mono_frame(const uint8_t* img, int w, int h, int nfeatures, const float* cam, const float* dist, int ndist, orc_keypoint* kps,
+                   orc_keypoint* kps_un, float* bounds, int* cell_start, int* cell_items, int cap) {
+    ORBextractor ex(nfeatures, 1.2f, 8, 20, 7);
+    cv::Mat im(h, w, CV_8UC1, (void*)img, (size_t)w);
+    cv::Mat K = cv::Mat::eye(3, 3, CV_32F);
+    K.at<float>(0, 0) = cam[0]; K.at<float>(1, 1) = cam[1]; K.at<float>(0, 2) = cam[2]; K.at<float>(1, 2) = cam[3];
+    cv::Mat D(ndist, 1, CV_32F);
+    for (int i = 0; i < ndist; i++) D.at<float>(i) = dist[i];
+    Frame::mbInitialComputations = true;
+    Frame* F = new Frame(im, 0.0, &ex, nullptr, K, D, 0.0f, 0.0f);
+    g.frames.push_back(F);
+    F->mpORBextractorLeft = nullptr;
+    if (F->N > cap) return -1;
+    for (int i = 0; i < F->N; i++) {
+        const cv::KeyPoint &a = F->mvKeys[i], &b = F->mvKeysUn[i];
+        kps[i] = orc_keypoint{a.pt.x, a.pt.y, a.size, a.angle, a.response, a.octave, a.class_id};
+        kps_un[i] = orc_keypoint{b.pt.x, b.pt.y, b.size, b.angle, b.response, b.octave, b.class_id};
+    }
+    bounds[0] = Frame::mnMinX; bounds[1] = Frame::mnMaxX; bounds[2] = Frame::mnMinY; bounds[3] = Frame::mnMaxY;
+    int n = 0;
+    for (int ix = 0; ix < FRAME_GRID_COLS; ix++)
+        for (int iy = 0; iy < FRAME_GRID_ROWS; iy++) {
+            cell_start[ix * FRAME_GRID_ROWS + iy] = n;
+            for (size_t j = 0; j < F->mGrid[ix][iy].size(); j++) cell_items[n++] = (int)F->mGrid[ix][iy][j];
+        }
+    cell_start[FRAME_GRID_COLS * FRAME_GRID_ROWS] = n;
+    return F->N;
+}
+
 }  // extern "C"

@@ -284,8 +284,38 @@ def scenario_stereo(oracle, ref):
     return out
 
 
+def scenario_frame_epilogue(oracle, ref):
+    """The reference's monocular Frame constructor: UndistortKeyPoints, ComputeImageBounds, AssignFeaturesToGrid.  The
+    restatement starts from the constructor's own mvKeys (its extractor runs on glibc malloc)."""
+    cams = {"tum1": ((517.306408, 516.469215, 318.643040, 255.313989), (0.262383, -0.953104, -0.005358, 0.002628, 1.163314)),
+            "tum2": ((520.908620, 521.007327, 325.141442, 249.701764), (0.231222, -0.784899, -0.003257, -0.000105, 0.917205)),
+            "plain": ((500.0, 500.0, 320.0, 240.0), (0.0, 0.0, 0.0, 0.0))}
+    out = {}
+    for name, (cam, dist) in cams.items():
+        img = synth.frame(W, H, 50 + len(name))
+        if oracle.mref_lib() is not None:
+            if ("epi", name) not in _cache:                   # once: the malloc-order dependent quadtree ties may fall differently per call
+                _cache[("epi", name)] = oracle.ref_mono_frame(img, 1000, cam, dist)
+            k, ku, b, cs, items = _cache[("epi", name)]
+        else:
+            G = np.load(GOLDEN)
+            k = np.frombuffer(G[f"epi_{name}_keys"].tobytes(), oracle.KP_DTYPE)
+            assert not ref
+        if not ref:
+            camv = np.array(cam, np.float32); dv = np.array(list(dist) + [0.0] * (5 - len(dist)), np.float32)
+            b = oracle.image_bounds(camv, dv, W, H) if any(dist) else np.array([0, W, 0, H], np.float32)
+            un = oracle.undistort_points(np.stack([k["x"], k["y"]], 1), camv, dv) if any(dist) else np.stack([k["x"], k["y"]], 1)
+            ku = k.copy(); ku["x"], ku["y"] = un[:, 0], un[:, 1]
+            cs, items = oracle.assign_grid(oracle.frame_view(ku, np.zeros((len(k), 32), np.uint8), W, H, np.ones(8, np.float32), bounds=b))
+        out[f"epi_{name}_keys"] = np.frombuffer(k.tobytes(), np.int32).copy()
+        out[f"epi_{name}_un"] = np.frombuffer(ku.tobytes(), np.int32).copy()
+        out[f"epi_{name}_bounds"] = np.asarray(b, np.float32).view(np.int32).copy()
+        out[f"epi_{name}_grid"] = np.concatenate([cs, items]).astype(np.int32)
+    return out
+
+
 SCENARIOS = [scenario_grid_and_area, scenario_search_for_initialization, scenario_search_by_projection, scenario_search_by_bow,
-             scenario_guided, scenario_distinctive, scenario_stereo]
+             scenario_guided, scenario_distinctive, scenario_stereo, scenario_frame_epilogue]
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "ref_matcher.npz")
 
 
