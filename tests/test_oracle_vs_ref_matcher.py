@@ -13,6 +13,7 @@ from orb_slam2_annotate_b200 import synth
 
 W, H = 640, 480
 _cache = {}
+_fixture_inputs = [False]      # the fixture test feeds the epilogue scenario the keypoints stored with the fixture
 
 
 def frames(oracle, seed=4, nf=1000, n=2):
@@ -293,7 +294,7 @@ def scenario_frame_epilogue(oracle, ref):
     out = {}
     for name, (cam, dist) in cams.items():
         img = synth.frame(W, H, 50 + len(name))
-        if oracle.mref_lib() is not None:
+        if oracle.mref_lib() is not None and not _fixture_inputs[0]:
             if ("epi", name) not in _cache:                   # once: the malloc-order dependent quadtree ties may fall differently per call
                 _cache[("epi", name)] = oracle.ref_mono_frame(img, 1000, cam, dist)
             k, ku, b, cs, items = _cache[("epi", name)]
@@ -334,5 +335,10 @@ def test_restatement_equals_reference_fixture(oracle, scenario):
     if not os.path.exists(GOLDEN):
         pytest.skip("tests/golden/ref_matcher.npz not generated")
     G = np.load(GOLDEN)
-    for name, a in scenario(oracle, False).items():
+    _fixture_inputs[0] = True
+    try:
+        mine = scenario(oracle, False)
+    finally:
+        _fixture_inputs[0] = False
+    for name, a in mine.items():
         assert np.array_equal(a, G[name]), name
