@@ -288,11 +288,13 @@ def cpu_reference_fps(frames, seconds_budget=20.0, steps=1, warmup=0):
     """The reference's own CPU path for the workload, one thread per host core: extraction by
     the unmodified ORBextractor.cc (oracle/_ref, reference -O3 flags, OpenCV primitives from the
     cv-shim; the oracle port when _ref was not prebuilt) and SearchForInitialization between
-    consecutive frames by the oracle's restatement of ORBmatcher.cc:469-600 (that TU cannot be
-    compiled here).  Every thread owns one extractor and a contiguous run of frames."""
+    consecutive frames by the unmodified ORBmatcher.cc + Frame.cc (oracle/_ref/liborbref_matcher.so; the
+    oracle's restatement when it was not prebuilt).  Every thread owns one extractor and a contiguous run of frames."""
     from oracle import oracle_py as O
     cores = os.cpu_count() or 1
     kind = "reference" if O.ref_lib("_native") is not None else "port"
+    search = O.ref_search_for_initialization if (kind == "reference" and O.mref_lib() is not None) else O.search_for_initialization
+    matcher_kind = "unmodified ORBmatcher.cc / Frame.cc on the cv-shim" if search is O.ref_search_for_initialization else "oracle port"
 
     def make():
         return O.RefExtractor(NFEAT, variant="_native") if kind == "reference" else O.OracleExtractor(NFEAT)
@@ -314,7 +316,7 @@ def cpu_reference_fps(frames, seconds_budget=20.0, steps=1, warmup=0):
                 cur = O.frame_view(k, d, W, H, scale)
                 if prev is not None:
                     pm = np.ascontiguousarray(np.stack([prev[0][0]["x"], prev[0][0]["y"]], 1), np.float32)
-                    O.search_for_initialization(prev[1], cur, pm, 100, 0.9, True)
+                    search(prev[1], cur, pm, 100, 0.9, True)
                 prev = ((k, d), cur)
         th = [threading.Thread(target=work, args=(t,)) for t in range(cores)]
         t0 = time.perf_counter()
@@ -329,7 +331,7 @@ def cpu_reference_fps(frames, seconds_budget=20.0, steps=1, warmup=0):
     return {"value": n / dt, "unit": "frames/s", "cores": cores, "kind": kind,
             "sample": f"{n} of the workload's 640x480 frames ({cores} threads x {run} consecutive frames: extract + "
                       f"SearchForInitialization between neighbours), mean of {max(steps, 1)} pass(es); extractor = "
-                      f"unmodified ORBextractor.cc on the cv-shim, matcher = oracle port",
+                      f"unmodified ORBextractor.cc on the cv-shim, matcher = {matcher_kind}",
             "ms_per_step": dt * 1e3, "frames": n}
 
 

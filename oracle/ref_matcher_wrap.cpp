@@ -58,7 +58,7 @@ struct Arena {
         delete map; map = nullptr; carrier = nullptr;
     }
 };
-Arena g;
+thread_local Arena g;      // one arena per calling thread (bench.py times the reference with one thread per core)
 
 cv::KeyPoint to_cv(const orc_keypoint& k) { return cv::KeyPoint(k.x, k.y, k.size, k.angle, k.response, k.octave, k.class_id); }
 
