@@ -34,6 +34,16 @@
 
 #include "orbfe.h"
 
+// The two classes carry the reference's names by default.  Inside a translation unit that also sees the reference's
+// own class of that name (its ORBextractor.h / ORBmatcher.h), give the adapter another name first:
+//   #define ORBFE_MATCHER_CLASS ORBmatcherFE      (integration/ORBmatcher_orbfe.cc does this)
+#ifndef ORBFE_EXTRACTOR_CLASS
+#define ORBFE_EXTRACTOR_CLASS ORBextractor
+#endif
+#ifndef ORBFE_MATCHER_CLASS
+#define ORBFE_MATCHER_CLASS ORBmatcher
+#endif
+
 namespace ORB_SLAM2 {
 
 namespace orbfe_detail {
@@ -42,14 +52,14 @@ inline void check(int rc, const char* what) {
 }
 }  // namespace orbfe_detail
 
-class ORBextractor {
+class ORBFE_EXTRACTOR_CLASS {
 public:
     enum { HARRIS_SCORE = 0, FAST_SCORE = 1 };
 
     // include/ORBextractor.h:53-54.  `device` and `downloadPyramid` are additions with defaults:
     // stereo needs mvImagePyramid on the host after every call (src/Frame.cc:519,609-626),
     // monocular / RGB-D callers can switch the copy off.
-    ORBextractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST,
+    ORBFE_EXTRACTOR_CLASS(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST,
                  int device = 0, bool downloadPyramid = true)
         : mpHandle(nullptr), nlevels(nlevels), mbDownloadPyramid(downloadPyramid) {
         orbfe_detail::check(orbfe_extractor_create(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, 0, 0, 0,
@@ -61,9 +71,9 @@ public:
         this->scaleFactor = scaleFactor;                                   // double member set from a float (:417)
         mvImagePyramid.resize(nlevels);
     }
-    ~ORBextractor() { orbfe_extractor_destroy(mpHandle); }
-    ORBextractor(const ORBextractor&) = delete;
-    ORBextractor& operator=(const ORBextractor&) = delete;
+    ~ORBFE_EXTRACTOR_CLASS() { orbfe_extractor_destroy(mpHandle); }
+    ORBFE_EXTRACTOR_CLASS(const ORBFE_EXTRACTOR_CLASS&) = delete;
+    ORBFE_EXTRACTOR_CLASS& operator=(const ORBFE_EXTRACTOR_CLASS&) = delete;
 
     // src/ORBextractor.cc:1119-1197.  Mask is ignored, as in the reference.
     void operator()(cv::InputArray _image, cv::InputArray /*_mask*/, std::vector<cv::KeyPoint>& _keypoints,
@@ -121,17 +131,17 @@ protected:
     std::vector<uint8_t> mDescBuf;
 };
 
-class ORBmatcher {
+class ORBFE_MATCHER_CLASS {
 public:
     static const int TH_LOW = 50, TH_HIGH = 100, HISTO_LENGTH = 30;      // src/ORBmatcher.cc:37-39
 
-    ORBmatcher(float nnratio = 0.6f, bool checkOri = true, int device = 0)
+    ORBFE_MATCHER_CLASS(float nnratio = 0.6f, bool checkOri = true, int device = 0)
         : mfNNratio(nnratio), mbCheckOrientation(checkOri), mpHandle(nullptr) {
         orbfe_detail::check(orbfe_matcher_create(device, &mpHandle), "orbfe_matcher_create");
     }
-    ~ORBmatcher() { orbfe_matcher_destroy(mpHandle); }
-    ORBmatcher(const ORBmatcher&) = delete;
-    ORBmatcher& operator=(const ORBmatcher&) = delete;
+    ~ORBFE_MATCHER_CLASS() { orbfe_matcher_destroy(mpHandle); }
+    ORBFE_MATCHER_CLASS(const ORBFE_MATCHER_CLASS&) = delete;
+    ORBFE_MATCHER_CLASS& operator=(const ORBFE_MATCHER_CLASS&) = delete;
 
     // src/ORBmatcher.cc:1828-1844
     static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b) { return orbfe_hamming256(a.data, b.data); }

@@ -1,0 +1,87 @@
+// ORBextractor_orbfe.cc — link-level drop-in for the reference's src/ORBextractor.cc.
+//
+// Defines the members of the reference's OWN class ORB_SLAM2::ORBextractor (include/ORBextractor.h:46-114, header
+// unchanged) on top of liborbfe's C ABI: take src/ORBextractor.cc out of the library's source list
+// (CMakeLists.txt:51-69), add this file and link liborbfe.  Frame::ExtractORB (src/Frame.cc:272-278), the
+// `new ORBextractor(...)` calls in Tracking (src/Tracking.cc:122-128) and the scale-table getters compile and behave
+// unchanged.  The class has no member that could hold the device handle, so handles live in a side table keyed by the
+// object's address; the header's inline destructor cannot release them, they are reclaimed when an extractor is
+// constructed at the same address or at process exit (three extractors per process in the reference).
+// There is no CPU fallback: a failed call throws std::runtime_error.
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+
+#include "ORBextractor.h"
+#include "orbfe.h"
+
+namespace {
+struct Slot { orbfe_extractor* h; std::vector<orbfe_keypoint> kps; std::vector<uint8_t> desc; };
+std::mutex g_mutex;
+std::map<const void*, Slot>& slots() { static std::map<const void*, Slot> s; return s; }
+void check(int rc, const char* what) {
+    if (rc != ORBFE_OK) throw std::runtime_error(std::string(what) + ": " + orbfe_last_error());
+}
+}  // namespace
+
+namespace ORB_SLAM2 {
+
+// src/ORBextractor.cc:415-486
+ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels, int _iniThFAST, int _minThFAST)
+    : nfeatures(_nfeatures), scaleFactor(_scaleFactor), nlevels(_nlevels), iniThFAST(_iniThFAST), minThFAST(_minThFAST) {
+    orbfe_extractor* h = nullptr;
+    check(orbfe_extractor_create(_nfeatures, _scaleFactor, _nlevels, _iniThFAST, _minThFAST, 0, 0, 0, 0, &h), "orbfe_extractor_create");
+    mvScaleFactor.resize(nlevels); mvInvScaleFactor.resize(nlevels);
+    mvLevelSigma2.resize(nlevels); mvInvLevelSigma2.resize(nlevels);
+    mnFeaturesPerLevel.resize(nlevels); umax.resize(16);
+    orbfe_get_scale_tables(h, mvScaleFactor.data(), mvInvScaleFactor.data(), mvLevelSigma2.data(), mvInvLevelSigma2.data(),
+                           mnFeaturesPerLevel.data(), umax.data());
+    mvImagePyramid.resize(nlevels);
+    std::lock_guard<std::mutex> lock(g_mutex);
+    Slot& s = slots()[this];
+    if (s.h) orbfe_extractor_destroy(s.h);          // an earlier extractor lived at this address
+    s.h = h;
+}
+
+// src/ORBextractor.cc:1119-1197.  The mask is ignored, as in the reference.
+void ORBextractor::operator()(cv::InputArray _image, cv::InputArray _mask, std::vector<cv::KeyPoint>& _keypoints,
+                              cv::OutputArray _descriptors) {
+    (void)_mask;
+    if (_image.empty()) return;                                        // :1122-1123
+    Slot* s;
+    {
+        std::lock_guard<std::mutex> lock(g_mutex);
+        s = &slots()[this];                                            // std::map nodes do not move
+    }
+    cv::Mat image = _image.getMat();
+    const int cap = orbfe_extractor_max_keypoints(s->h) + 4096;
+    s->kps.resize(cap); s->desc.resize((size_t)cap * 32);
+    int n = 0;
+    check(orbfe_extract(s->h, image.data, image.cols, image.rows, (ptrdiff_t)(size_t)image.step, s->kps.data(), s->desc.data(), cap, &n),
+          "orbfe_extract");
+    _keypoints.clear();
+    if (n == 0) {
+        _descriptors.release();                                        // :1145-1146
+    } else {
+        _descriptors.create(n, 32, CV_8U);                             // :1149
+        cv::Mat descriptors = _descriptors.getMat();
+        _keypoints.reserve(n);
+        for (int i = 0; i < n; i++) {
+            const orbfe_keypoint& k = s->kps[i];
+            _keypoints.push_back(cv::KeyPoint(k.x, k.y, k.size, k.angle, k.response, k.octave, k.class_id));
+            std::memcpy(descriptors.ptr(i), &s->desc[(size_t)i * 32], 32);
+        }
+    }
+    // Frame::ComputeStereoMatches reads mvImagePyramid (src/Frame.cc:519, :609-626)
+    for (int l = 0; l < nlevels; l++) {
+        int w = 0, h = 0;
+        orbfe_pyramid_level(s->h, 0, l, 0, nullptr, 0, &w, &h);
+        mvImagePyramid[l].create(h, w, CV_8UC1);
+        check(orbfe_pyramid_level(s->h, 0, l, 0, mvImagePyramid[l].data, (ptrdiff_t)(size_t)mvImagePyramid[l].step, &w, &h),
+              "orbfe_pyramid_level");
+    }
+}
+
+}  // namespace ORB_SLAM2

@@ -492,14 +492,21 @@ def knn2(q: np.ndarray, t: np.ndarray, th=50, ratio=0.7):
 # ----------------------------------------------------------------------------- the reference's own matcher TUs
 # oracle/_ref/liborbref_matcher.so: UNMODIFIED src/ORBmatcher.cc, Frame.cc, KeyFrame.cc, MapPoint.cc, Map.cc (+ DBoW2)
 # behind oracle/ref_matcher_wrap.cpp.  Same argument shapes as the restatement's wrappers above.
-_mref = [False, None]
+_mref = [False, None, "liborbref_matcher.so"]
+
+
+def use_mref(name: str = "liborbref_matcher.so"):
+    """Selects which build the ref_* wrappers below drive: the unmodified reference ("liborbref_matcher.so") or the
+    drop-in proof ("liborbref_dropin.so": same TUs with ORBextractor.cc / ORBmatcher.cc replaced by integration/*.cc on
+    liborbfe — needs a GPU)."""
+    _mref[0], _mref[1], _mref[2] = False, None, name
 
 
 def mref_lib():
-    """None when oracle/_ref/liborbref_matcher.so is not built (reference tree not mounted)."""
+    """None when the selected oracle/_ref library is not built (reference tree not mounted)."""
     if not _mref[0]:
         _mref[0] = True
-        path = os.path.join(HERE, "_ref", "liborbref_matcher.so")
+        path = os.path.join(HERE, "_ref", _mref[2])
         if os.path.exists(path):
             L = C.CDLL(path)
             L.orm_search_for_initialization.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int]

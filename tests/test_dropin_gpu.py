@@ -1,0 +1,50 @@
+"""The drop-in proof on the GPU: oracle/_ref/liborbref_dropin.so is the reference's own Frame.cc, KeyFrame.cc, MapPoint.cc,
+Map.cc and DBoW2 (unmodified) linked with integration/ORBextractor_orbfe.cc and integration/ORBmatcher_orbfe.cc — the
+reference's class declarations implemented on liborbfe — in place of src/ORBextractor.cc and src/ORBmatcher.cc.  The
+scenarios of tests/test_oracle_vs_ref_matcher.py are driven through it (reference objects in, reference call sites,
+reference objects out) and must give what the unmodified library gave (tests/golden/ref_matcher.npz)."""
+import os
+
+import numpy as np
+import pytest
+
+import test_oracle_vs_ref_matcher as T
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture()
+def dropin(oracle):
+    oracle.use_mref("liborbref_dropin.so")
+    if oracle.mref_lib() is None:
+        oracle.use_mref()
+        pytest.skip("oracle/_ref/liborbref_dropin.so not built (reference tree not mounted at build time)")
+    T._cache.pop(("epi", "tum1"), None); T._cache.pop(("epi", "tum2"), None); T._cache.pop(("epi", "plain"), None)
+    yield oracle
+    oracle.use_mref()
+    for k in [k for k in T._cache if k[0] == "epi"]:
+        T._cache.pop(k)
+
+
+@pytest.mark.parametrize("scenario", [s for s in T.SCENARIOS if s is not T.scenario_frame_epilogue], ids=lambda s: s.__name__[9:])
+def test_reference_call_sites_on_the_gpu(dropin, scenario):
+    G = np.load(T.GOLDEN)
+    got = scenario(dropin, True)
+    for name, a in got.items():
+        assert np.array_equal(a, G[name]), name
+
+
+def test_frame_constructor_on_the_gpu(dropin):
+    """Frame::Frame(imGray, ...) of the reference with the extraction served by liborbfe through Frame::ExtractORB: the
+    keypoints equal the oracle extractor's, the epilogue (reference code on them) equals the restatement."""
+    from orb_slam2_annotate_b200 import synth
+    theirs = T.scenario_frame_epilogue(dropin, True)
+    mine = T.scenario_frame_epilogue(dropin, False)
+    for name, a in mine.items():
+        assert np.array_equal(a, theirs[name]), name
+    k = np.frombuffer(theirs["epi_tum1_keys"].tobytes(), dropin.KP_DTYPE)
+    ko, _ = dropin.OracleExtractor(1000)(synth.frame(T.W, T.H, 50 + len("tum1")))
+    assert len(k) == len(ko)
+    for f in ("x", "y", "size", "response", "octave", "class_id"):
+        assert np.array_equal(k[f], ko[f]), f
+    assert np.abs(k["angle"] - ko["angle"]).max() <= 1e-3
