@@ -14,9 +14,11 @@ from orb_slam2_annotate_b200 import synth
 W, H = 640, 480
 _cache = {}
 _fixture_inputs = [False]      # the fixture test feeds the epilogue scenario the keypoints stored with the fixture
+_reseed = [0]                  # added to every scenario seed by the live multi-seed sweep (0 = the fixture's scenarios)
 
 
 def frames(oracle, seed=4, nf=1000, n=2):
+    seed += 7 * _reseed[0]
     key = (seed, nf, n)
     if key not in _cache:
         imgs, off = synth.sequence(n, W, H, seed=seed)
@@ -59,7 +61,7 @@ def need_ref(oracle):
 def scenario_grid_and_area(oracle, ref):
     (fr, _) = frames(oracle)
     k, d, t = fr[0]
-    rng = np.random.default_rng(3)
+    rng = np.random.default_rng(3 + 100 * _reseed[0])
     out = {}
     for kf in (0, 1):
         f = oracle.frame_view(k, d, W, H, t["scale"], bounds=(-12.7, 655.3, -9.6, 489.4), keyframe=bool(kf))
@@ -92,7 +94,7 @@ def scenario_search_by_projection(oracle, ref):
     (fr, off) = frames(oracle)
     (k1, d1, t), (k2, d2, _) = fr
     scale = t["scale"]
-    rng = np.random.default_rng(5)
+    rng = np.random.default_rng(5 + 100 * _reseed[0])
     out = {}
     for (nmp, th, stereo) in [(3000, 3.0, False), (800, 5.0, True), (200, 15.0, False)]:
         src = rng.integers(0, len(k2), nmp)
@@ -140,7 +142,7 @@ def _bow_sides(oracle, rng, nbits):
 
 
 def scenario_search_by_bow(oracle, ref):
-    rng = np.random.default_rng(6)
+    rng = np.random.default_rng(6 + 100 * _reseed[0])
     out = {}
     for nbits, ratio, ori in [(4, 0.7, True), (2, 0.75, False), (6, 0.9, True)]:
         (da, aa, fva, va), (db, ab, fvb, vb) = _bow_sides(oracle, rng, nbits)
@@ -159,7 +161,7 @@ def scenario_guided(oracle, ref):
     (fr, off) = frames(oracle)
     (k1, d1, t), (k2, d2, _) = fr
     scale = t["scale"]
-    rng = np.random.default_rng(7)
+    rng = np.random.default_rng(7 + 100 * _reseed[0])
     s12 = (float(off[0][0] - off[1][0]), float(off[0][1] - off[1][1]))
     out = {}
     in_frame = lambda u, v: (u >= 0) & (u <= W) & (v >= 0) & (v <= H)
@@ -255,7 +257,7 @@ def scenario_guided(oracle, ref):
 
 
 def scenario_distinctive(oracle, ref):
-    rng = np.random.default_rng(8)
+    rng = np.random.default_rng(8 + 100 * _reseed[0])
     sizes = np.concatenate([[0, 1, 2, 3], rng.integers(2, 25, 60)])
     start = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
     base = rng.integers(0, 256, (len(sizes), 32), dtype=np.uint8)
@@ -342,3 +344,18 @@ def test_restatement_equals_reference_fixture(oracle, scenario):
         _fixture_inputs[0] = False
     for name, a in mine.items():
         assert np.array_equal(a, G[name]), name
+
+
+@pytest.mark.parametrize("reseed", [1, 2, 3])
+def test_restatement_equals_reference_more_seeds(oracle, reseed):
+    """The same comparisons on other frames and other random points (live only: no fixture for these)."""
+    need_ref(oracle)
+    _reseed[0] = reseed
+    try:
+        for scenario in (scenario_grid_and_area, scenario_search_for_initialization, scenario_search_by_projection, scenario_search_by_bow,
+                         scenario_guided, scenario_distinctive):
+            mine, theirs = scenario(oracle, False), scenario(oracle, True)
+            for name, a in mine.items():
+                assert np.array_equal(a, theirs[name]), (scenario.__name__, name)
+    finally:
+        _reseed[0] = 0
