@@ -192,6 +192,44 @@ def guided_search_timings(frame_img):
     }
 
 
+def single_frame_latency(frames):
+    """The shape Tracking uses: ONE 640x480 frame through the host-buffer C ABI (frame in, keypoints + descriptors
+    out on the host) and SearchForInitialization on two such frames; beside it the unmodified reference on one core."""
+    from oracle import oracle_py as O
+    import orb_slam2_annotate_b200 as orbfe
+    ex = orbfe.ORBextractor(NFEAT, 1.2, 8, 20, 7)
+    mt = orbfe.ORBmatcher(0.9, True)
+    res = [ex(np.ascontiguousarray(frames[i])) for i in range(2)]
+    for _ in range(20):
+        ex(frames[0])
+    te = []
+    for i in range(200):
+        t0 = time.perf_counter(); ex(frames[i & 1]); te.append(time.perf_counter() - t0)
+    scale = ex.GetScaleFactors()
+    F = [orbfe.Frame(k, d, W, H, scale) for k, d in res]
+    prev = np.ascontiguousarray(np.stack([res[0][0]["x"], res[0][0]["y"]], 1), np.float32)
+    tm = []
+    for i in range(110):
+        p = prev.copy()
+        t0 = time.perf_counter(); mt.SearchForInitialization(F[0], F[1], p, 100); tm.append(time.perf_counter() - t0)
+    kind = "reference" if O.ref_lib("_native") is not None else "port"
+    rex = O.RefExtractor(NFEAT, variant="_native") if kind == "reference" else O.OracleExtractor(NFEAT)
+    search = O.ref_search_for_initialization if (kind == "reference" and O.mref_lib() is not None) else O.search_for_initialization
+    rex(frames[0])
+    t0 = time.perf_counter()
+    cpu = [rex(frames[i & 1]) for i in range(6)]
+    cpu_extract = (time.perf_counter() - t0) / 6
+    v = [O.frame_view(k, d, W, H, scale) for k, d in cpu[:2]]
+    t0 = time.perf_counter()
+    for _ in range(6):
+        search(v[0], v[1], np.ascontiguousarray(np.stack([cpu[0][0]["x"], cpu[0][0]["y"]], 1), np.float32), 100, 0.9, True)
+    cpu_search = (time.perf_counter() - t0) / 6
+    return {"what": "one 640x480 frame through the host-buffer C ABI, and SearchForInitialization(window 100) on two such frames",
+            "extract_ms": float(np.median(te)) * 1e3, "extract_ms_p90": float(np.percentile(te, 90)) * 1e3,
+            "search_init_ms": float(np.median(tm[10:])) * 1e3, "cpu_extract_ms_one_core": cpu_extract * 1e3,
+            "cpu_search_init_ms_one_core": cpu_search * 1e3, "cpu_kind": kind}
+
+
 def stereo_timings(npairs=128):
     """configs[2] beside the CPU: `npairs` KITTI-shape 1241x376 stereo pairs, nFeatures 2000 — both images extracted
     (one interleaved host batch through the C ABI, copies included) and Frame::ComputeStereoMatches on the
@@ -559,6 +597,7 @@ def main():
             line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
             line["guided_searches"] = guided_search_timings(frames[0])
             line["stereo"] = stereo_timings()
+            line["latency"] = single_frame_latency(frames)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
