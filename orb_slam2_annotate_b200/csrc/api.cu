@@ -67,6 +67,11 @@ struct orbfe_extractor {
     DevArray<orbfe_keypoint> kpsUn;
     DevArray<int> gridEnd;
     DevArray<unsigned short> gridItems;
+    // single-frame latency path: the kernel schedule of a small batch captured once as a CUDA graph and replayed while
+    // every kernel argument (geometry, device pointers, TMA descriptors, camera) stays what it was at capture time
+    cudaGraphExec_t graphExec = nullptr;
+    std::vector<uint8_t> graphKey;
+    int graphLaunches = 0;
     // optional per-stage timing (events on the handle's stream)
     bool profiling = false;
     cudaEvent_t ev[ORBFE_NUM_STAGES + 1] = {};
@@ -434,6 +439,55 @@ static int enqueue_extract(orbfe_extractor* e, int frame0 = 0, int count = -1, i
     return 0;
 }
 
+// Everything the launchers pass to the kernels, byte for byte: the replay is valid exactly while this is unchanged.
+static void graph_key(const orbfe_extractor* e, std::vector<uint8_t>& key) {
+    key.clear();
+    auto put = [&](const void* p, size_t n) { const uint8_t* b = (const uint8_t*)p; key.insert(key.end(), b, b + n); };
+    put(&e->g, sizeof(e->g)); put(&e->d, sizeof(e->d));
+    put(e->tmaps.data(), e->tmaps.size() * sizeof(CUtensorMap)); put(e->fastMaps.data(), e->fastMaps.size() * sizeof(CUtensorMap));
+    const void* ptrs[4] = {e->umax_d.p, e->kpsUn.p, e->gridEnd.p, e->gridItems.p};
+    put(ptrs, sizeof(ptrs));
+    const int cam = e->haveCam ? 1 : 0;
+    put(&cam, sizeof(cam));
+    if (e->haveCam) put(&e->camGeom, sizeof(e->camGeom));
+}
+
+// Small batches are launch-latency bound (one 640x480 frame: ~25 dependent launches of a few microseconds each), so their
+// schedule is replayed from a graph.  The first call with a given argument set runs eagerly (it also applies the
+// per-function attributes), the second captures, later ones replay.
+static int enqueue_extract_small(orbfe_extractor* e) {
+    static const bool off = std::getenv("ORBFE_NO_GRAPH") != nullptr;
+    if (off || e->profiling) return enqueue_extract(e);
+    std::vector<uint8_t> key;
+    graph_key(e, key);
+    if (e->graphExec && key == e->graphKey) {
+        CU(cudaGraphLaunch(e->graphExec, e->stream));
+        e->lastLaunches = e->graphLaunches;
+        return 0;
+    }
+    if (e->graphExec) { cudaGraphExecDestroy(e->graphExec); e->graphExec = nullptr; }
+    if (key != e->graphKey) {                        // first sight of this argument set: eager
+        e->graphKey.swap(key);
+        return enqueue_extract(e);
+    }
+    cudaGraph_t graph = nullptr;
+    CU(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
+    const int rc = enqueue_extract(e);
+    const cudaError_t ce = cudaStreamEndCapture(e->stream, &graph);
+    if (rc || ce != cudaSuccess || !graph) {
+        if (graph) cudaGraphDestroy(graph);
+        cudaGetLastError();
+        e->graphKey.clear();
+        return rc ? rc : enqueue_extract(e);         // capture refused: stay eager
+    }
+    e->graphLaunches = e->lastLaunches;
+    const cudaError_t ci = cudaGraphInstantiate(&e->graphExec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ci != cudaSuccess) { e->graphExec = nullptr; e->graphKey.clear(); cudaGetLastError(); return enqueue_extract(e); }
+    CU(cudaGraphLaunch(e->graphExec, e->stream));
+    return 0;
+}
+
 // Level 0 either lives in the pyramid buffer (copied there) or aliases the caller's device frames
 // when their layout already is the level layout (16-byte aligned base, stride == pitch, frames
 // contiguous): every kernel addresses level 0 as d.pyr + lv[0].pyrOff, so the alias is just a
@@ -526,6 +580,7 @@ void orbfe_extractor_destroy(orbfe_extractor* e) {
     if (!e) return;
     cudaSetDevice(e->device);
     if (e->stream) { cudaStreamSynchronize(e->stream); cudaStreamDestroy(e->stream); }
+    if (e->graphExec) cudaGraphExecDestroy(e->graphExec);
     if (e->sideStream) { cudaStreamSynchronize(e->sideStream); cudaStreamDestroy(e->sideStream); }
     if (e->evPyr) cudaEventDestroy(e->evPyr);
     if (e->evBlur) cudaEventDestroy(e->evBlur);
@@ -755,7 +810,7 @@ int orbfe_extract_batch(orbfe_extractor* e, const uint8_t* imgs, int batch, int 
     }
     if ((rc = upload_level0(e, imgs, batch, width, height, stride, frame_stride, cudaMemcpyHostToDevice))) return rc;
     e->lastBatch = batch;
-    if ((rc = enqueue_extract(e))) return rc;
+    if ((rc = batch <= 4 ? enqueue_extract_small(e) : enqueue_extract(e))) return rc;
     return orbfe_extractor_fetch(e, batch, kps, desc, cap, counts);
 }
 

@@ -248,8 +248,12 @@ int launch_orient_desc(const FrameSetGeom& g, const DevBufs& d, const int* d_uma
     LevelMaps maps;
     std::memcpy(&maps, d.tmaps, sizeof(CUtensorMap) * 2 * g.nlevels);
     constexpr int smem = 8 * WARP_BYTES;
-    // per device and cheap, so set on every launch rather than tracked per context
-    if (cudaFuncSetAttribute(orient_desc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return 0;
+    // per device and cheap, so set on every eager launch rather than tracked per context (a stream capture replays a
+    // schedule whose eager run already applied it)
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(s, &cap);
+    if (cap == cudaStreamCaptureStatusNone &&
+        cudaFuncSetAttribute(orient_desc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return 0;
     orient_desc_kernel<<<dim3((g.outCap + 8 * KPW - 1) / (8 * KPW), g.batch), 256, smem, s>>>(g, d, maps, d_umax);
     return 1;
 }
