@@ -73,29 +73,8 @@ int ORBmatcher::Fuse(KeyFrame* pKF, cv::Mat Scw, const vector<MapPoint*>& vpPoin
     return fe(mfNNratio, mbCheckOrientation).Fuse(pKF, Scw, vpPoints, th, vpReplacePoint);
 }
 
-// The three protected helpers are only called from inside the routines above in the reference; they are defined for
-// completeness with the reference's semantics (src/ORBmatcher.cc:141-175, :1777-1821).
-float ORBmatcher::RadiusByViewingCos(const float& viewCos) { return viewCos > 0.998 ? 2.5f : 4.0f; }
-bool ORBmatcher::CheckDistEpipolarLine(const cv::KeyPoint& kp1, const cv::KeyPoint& kp2, const cv::Mat& F12, const KeyFrame* pKF2) {
-    const float a = kp1.pt.x * F12.at<float>(0, 0) + kp1.pt.y * F12.at<float>(1, 0) + F12.at<float>(2, 0);
-    const float b = kp1.pt.x * F12.at<float>(0, 1) + kp1.pt.y * F12.at<float>(1, 1) + F12.at<float>(2, 1);
-    const float c = kp1.pt.x * F12.at<float>(0, 2) + kp1.pt.y * F12.at<float>(1, 2) + F12.at<float>(2, 2);
-    const float num = a * kp2.pt.x + b * kp2.pt.y + c;
-    const float den = a * a + b * b;
-    if (den == 0) return false;
-    const float dsqr = num * num / den;
-    return dsqr < 3.84 * pKF2->mvLevelSigma2[kp2.octave];
-}
-void ORBmatcher::ComputeThreeMaxima(vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3) {
-    int max1 = 0, max2 = 0, max3 = 0;
-    for (int i = 0; i < L; i++) {
-        const int s = (int)histo[i].size();
-        if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
-        else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
-        else if (s > max3) { max3 = s; ind3 = i; }
-    }
-    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
-    else if (max3 < 0.1f * (float)max1) ind3 = -1;
-}
+// The three protected helpers of the class (RadiusByViewingCos, CheckDistEpipolarLine, ComputeThreeMaxima) were only ever
+// called from inside src/ORBmatcher.cc; nothing refers to them once that file is out of the build, so they get no
+// definition here — their arithmetic lives in the device kernels.
 
 }  // namespace ORB_SLAM2
