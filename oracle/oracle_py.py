@@ -592,6 +592,7 @@ def _mref_more():
     L.orm_distinctive_descriptors.argtypes = [P, P, I, P]
     L.orm_compute_stereo_matches.argtypes = [P, P, P, P, I, I, F, F, P, P]
     L.orm_mono_frame.argtypes = [P, I, I, I, P, P, I, P, P, P, P, P, I]
+    L.orm_stereo_frame.argtypes = [P, P, I, I, I, F, F, F, F, F, P, P, P, P, P, P, P, I]
     L._more = True
     return L
 
@@ -704,3 +705,19 @@ def ref_mono_frame(img: np.ndarray, nfeatures: int, cam, dist):
     L.orm_reset()
     assert n >= 0
     return k[:n].copy(), ku[:n].copy(), b, cs, items[:cs[-1]].copy()
+
+
+def ref_stereo_frame(left: np.ndarray, right: np.ndarray, nfeatures: int, cam, bf: float):
+    """The reference's stereo Frame constructor (two extraction threads) -> (mvKeys, mDescriptors, mvuRight, mvDepth,
+    mvKeysRight, mDescriptorsRight).  Meant for the drop-in build (see ref_matcher_wrap.cpp)."""
+    L = _mref_more()
+    h, w = left.shape
+    cap = 4 * nfeatures + 4096
+    k = np.empty(cap, KP_DTYPE); d = np.empty((cap, 32), np.uint8); ur = np.empty(cap, np.float32); dp = np.empty(cap, np.float32)
+    kr = np.empty(cap, KP_DTYPE); dr = np.empty((cap, 32), np.uint8); nr = C.c_int(0)
+    left = np.ascontiguousarray(left); right = np.ascontiguousarray(right)
+    n = L.orm_stereo_frame(left.ctypes.data, right.ctypes.data, w, h, nfeatures, *[float(c) for c in cam], bf, k.ctypes.data, d.ctypes.data,
+                           ur.ctypes.data, dp.ctypes.data, kr.ctypes.data, dr.ctypes.data, C.addressof(nr), cap)
+    L.orm_reset()
+    assert n >= 0
+    return k[:n].copy(), d[:n].copy(), ur[:n].copy(), dp[:n].copy(), kr[:nr.value].copy(), dr[:nr.value].copy()

@@ -540,4 +540,38 @@ int orm_mono_frame(const uint8_t* img, int w, int h, int nfeatures, const float*
     return F->N;
 }
 
+
+/* Frame::Frame(imLeft, imRight, ...) — src/Frame.cc:58-117: both extractions on two threads (:78-81), UndistortKeyPoints,
+ * ComputeStereoMatches, AssignFeaturesToGrid.  Used with the drop-in build, whose extraction does not depend on the heap
+ * layout (with the unmodified extractor on glibc malloc the quadtree ties of two concurrent threads vary from run to run).
+ * Returns N; the right image's keypoints come back too. */
+int orm_stereo_frame(const uint8_t* left, const uint8_t* right, int w, int h, int nfeatures, float fx, float fy, float cx, float cy,
+                     float bf, orc_keypoint* kps, uint8_t* desc, float* uright, float* depth, orc_keypoint* kps_right, uint8_t* desc_right,
+                     int* n_right, int cap) {
+    ORBextractor exL(nfeatures, 1.2f, 8, 20, 7), exR(nfeatures, 1.2f, 8, 20, 7);
+    cv::Mat imL(h, w, CV_8UC1, (void*)left, (size_t)w), imR(h, w, CV_8UC1, (void*)right, (size_t)w);
+    cv::Mat K = cv::Mat::eye(3, 3, CV_32F);
+    K.at<float>(0, 0) = fx; K.at<float>(1, 1) = fy; K.at<float>(0, 2) = cx; K.at<float>(1, 2) = cy;
+    cv::Mat D = cv::Mat::zeros(4, 1, CV_32F);
+    Frame::mbInitialComputations = true;
+    Frame* F = new Frame(imL, imR, 0.0, &exL, &exR, nullptr, K, D, bf, 40.0f);
+    g.frames.push_back(F);
+    F->mpORBextractorLeft = F->mpORBextractorRight = nullptr;       // the extractors die with this call
+    const int nr = (int)F->mvKeysRight.size();
+    if (F->N > cap || nr > cap) return -1;
+    for (int i = 0; i < F->N; i++) {
+        const cv::KeyPoint& k = F->mvKeys[i];
+        kps[i] = orc_keypoint{k.pt.x, k.pt.y, k.size, k.angle, k.response, k.octave, k.class_id};
+        uright[i] = F->mvuRight[i]; depth[i] = F->mvDepth[i];
+    }
+    if (F->N) std::memcpy(desc, F->mDescriptors.data, (size_t)F->N * 32);
+    for (int i = 0; i < nr; i++) {
+        const cv::KeyPoint& k = F->mvKeysRight[i];
+        kps_right[i] = orc_keypoint{k.pt.x, k.pt.y, k.size, k.angle, k.response, k.octave, k.class_id};
+    }
+    if (nr) std::memcpy(desc_right, F->mDescriptorsRight.data, (size_t)nr * 32);
+    *n_right = nr;
+    return F->N;
+}
+
 }  // extern "C"

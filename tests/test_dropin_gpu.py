@@ -48,3 +48,26 @@ def test_frame_constructor_on_the_gpu(dropin):
     for f in ("x", "y", "size", "response", "octave", "class_id"):
         assert np.array_equal(k[f], ko[f]), f
     assert np.abs(k["angle"] - ko["angle"]).max() <= 1e-3
+
+
+@pytest.mark.parametrize("w,h,nf,seed,disp,cam,bf", [(640, 480, 1000, 21, 12, (500.0, 500.0, 320.0, 240.0), 40.0),
+                                                     (1241, 376, 2000, 2, 20, (718.856, 718.856, 607.1928, 185.2157), 386.1448)])
+def test_stereo_frame_constructor_on_the_gpu(dropin, w, h, nf, seed, disp, cam, bf):
+    """Frame::Frame(imLeft, imRight, ...) of the reference: its two extraction threads (src/Frame.cc:78-81) run two liborbfe
+    handles concurrently through Frame::ExtractORB."""
+    from orb_slam2_annotate_b200 import synth
+    left, right = synth.stereo_pair(w, h, seed=seed, disparity=disp)
+    for _ in range(3):                                    # the threads race for the device: the result must not depend on it
+        k, d, ur, dp, kr, dr = dropin.ref_stereo_frame(left, right, nf, cam, bf)
+        ol, orr = dropin.OracleExtractor(nf), dropin.OracleExtractor(nf)
+        ko, do = ol(left); kro, dro = orr(right)
+        for (a, b) in ((k, ko), (kr, kro)):
+            assert len(a) == len(b)
+            for f in ("x", "y", "size", "response", "octave", "class_id"):
+                assert np.array_equal(a[f], b[f]), f
+            assert np.abs(a["angle"] - b["angle"]).max() <= 1e-3
+        assert (d != do).any(axis=1).sum() <= 2 and (dr != dro).any(axis=1).sum() <= 2
+        # mvuRight / mvDepth of this constructor are not compared: it calls ComputeStereoMatches() (src/Frame.cc:90) before
+        # `mb = mbf/fx` is assigned (:113), so the search range maxD = mbf/mb comes from an uninitialised member.  The routine
+        # itself, entered with mb set, is compared in test_reference_call_sites_on_the_gpu[stereo].
+        assert len(ur) == len(k) and len(dp) == len(k)
