@@ -18,7 +18,7 @@
 #include "orbfe.h"
 
 namespace {
-struct Slot { orbfe_extractor* h; std::vector<orbfe_keypoint> kps; std::vector<uint8_t> desc; };
+struct Slot { orbfe_extractor* h = nullptr; bool pyramid = true; std::vector<orbfe_keypoint> kps; std::vector<uint8_t> desc; };
 std::mutex g_mutex;
 std::map<const void*, Slot>& slots() { static std::map<const void*, Slot> s; return s; }
 void check(int rc, const char* what) {
@@ -74,8 +74,8 @@ void ORBextractor::operator()(cv::InputArray _image, cv::InputArray _mask, std::
             std::memcpy(descriptors.ptr(i), &s->desc[(size_t)i * 32], 32);
         }
     }
-    // Frame::ComputeStereoMatches reads mvImagePyramid (src/Frame.cc:519, :609-626)
-    for (int l = 0; l < nlevels; l++) {
+    // Frame::ComputeStereoMatches reads mvImagePyramid (src/Frame.cc:519, :609-626); nothing else does
+    for (int l = 0; s->pyramid && l < nlevels; l++) {
         int w = 0, h = 0;
         orbfe_pyramid_level(s->h, 0, l, 0, nullptr, 0, &w, &h);
         mvImagePyramid[l].create(h, w, CV_8UC1);
@@ -85,3 +85,12 @@ void ORBextractor::operator()(cv::InputArray _image, cv::InputArray _mask, std::
 }
 
 }  // namespace ORB_SLAM2
+
+// Monocular and RGB-D systems never read mvImagePyramid: Tracking may switch the device-to-host copy of the eight levels
+// off for its extractors (one call after each `new ORBextractor(...)`, src/Tracking.cc:122-128).  Declare it where used:
+//   extern "C" void orbfe_dropin_set_pyramid_download(const void* extractor, int on);
+extern "C" void orbfe_dropin_set_pyramid_download(const void* extractor, int on) {
+    std::lock_guard<std::mutex> lock(g_mutex);
+    std::map<const void*, Slot>::iterator it = slots().find(extractor);
+    if (it != slots().end()) it->second.pyramid = on != 0;
+}

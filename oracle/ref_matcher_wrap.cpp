@@ -513,7 +513,11 @@ void orm_compute_stereo_matches(const orc_frame_view* fl, const orc_frame_view* 
  * kps = mvKeys, kps_un = mvKeysUn, bounds = mnMinX, mnMaxX, mnMinY, mnMaxY, grid in CSR form. */
 int orm_mono_frame(const uint8_t* img, int w, int h, int nfeatures, const float* cam, const float* dist, int ndist, orc_keypoint* kps,
                    orc_keypoint* kps_un, float* bounds, int* cell_start, int* cell_items, int cap) {
-    ORBextractor ex(nfeatures, 1.2f, 8, 20, 7);
+    // the extractor outlives the call, as Tracking's does (src/Tracking.cc:122-128)
+    static thread_local ORBextractor* pex = nullptr;
+    static thread_local int pexFeatures = 0;
+    if (!pex || pexFeatures != nfeatures) { delete pex; pex = new ORBextractor(nfeatures, 1.2f, 8, 20, 7); pexFeatures = nfeatures; }
+    ORBextractor& ex = *pex;
     cv::Mat im(h, w, CV_8UC1, (void*)img, (size_t)w);
     cv::Mat K = cv::Mat::eye(3, 3, CV_32F);
     K.at<float>(0, 0) = cam[0]; K.at<float>(1, 1) = cam[1]; K.at<float>(0, 2) = cam[2]; K.at<float>(1, 2) = cam[3];
