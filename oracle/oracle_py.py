@@ -721,3 +721,33 @@ def ref_stereo_frame(left: np.ndarray, right: np.ndarray, nfeatures: int, cam, b
     L.orm_reset()
     assert n >= 0
     return k[:n].copy(), d[:n].copy(), ur[:n].copy(), dp[:n].copy(), kr[:nr.value].copy(), dr[:nr.value].copy()
+
+
+def dropin_compute_stereo_matches(fl, fr, left: np.ndarray, right: np.ndarray, fx: float, bf: float):
+    """liborbref_dropin.so only: the adapter's ComputeStereoMatches(Frame&) on a reference Frame -> (mvuRight, mvDepth)"""
+    L = _mref_more()
+    L.orm_dropin_compute_stereo_matches.argtypes = [C.c_void_p] * 4 + [C.c_int, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+    h, w = left.shape
+    left = np.ascontiguousarray(left); right = np.ascontiguousarray(right)
+    ur = np.empty(max(fl[0].n, 1), np.float32); dp = np.empty(max(fl[0].n, 1), np.float32)
+    L.orm_dropin_compute_stereo_matches(C.byref(fl[0]), C.byref(fr[0]), left.ctypes.data, right.ctypes.data, w, h, fx, bf, ur.ctypes.data, dp.ctypes.data)
+    L.orm_reset()
+    return ur[:fl[0].n], dp[:fl[0].n]
+
+
+def dropin_epilogue(img: np.ndarray, nfeatures: int, cam, dist):
+    """liborbref_dropin.so only: the adapter's ComputeImageBounds + UndistortAndAssign on a Frame the reference's monocular
+    constructor built -> (mvKeys, mvKeysUn, bounds[4], cell_start, cell_items)"""
+    L = _mref_more()
+    L.orm_dropin_epilogue.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 5 + [C.c_int]
+    h, w = img.shape
+    cap = 4 * nfeatures + 4096
+    img = np.ascontiguousarray(img)
+    k = np.empty(cap, KP_DTYPE); ku = np.empty(cap, KP_DTYPE); b = np.empty(4, np.float32)
+    cs = np.empty(64 * 48 + 1, np.int32); items = np.empty(cap, np.int32)
+    camv = np.ascontiguousarray(cam, np.float32); dv = np.ascontiguousarray(dist, np.float32)
+    n = L.orm_dropin_epilogue(img.ctypes.data, w, h, nfeatures, camv.ctypes.data, dv.ctypes.data, len(dv), k.ctypes.data, ku.ctypes.data, b.ctypes.data,
+                              cs.ctypes.data, items.ctypes.data, cap)
+    L.orm_reset()
+    assert n >= 0
+    return k[:n].copy(), ku[:n].copy(), b, cs, items[:cs[-1]].copy()

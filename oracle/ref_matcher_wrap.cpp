@@ -38,6 +38,12 @@
 #undef private
 #undef protected
 
+#ifdef ORM_DROPIN            // the drop-in build also drives the adapter's Frame-level replacements on the reference's Frame type
+#define ORBFE_EXTRACTOR_CLASS ORBextractorFE
+#define ORBFE_MATCHER_CLASS ORBmatcherFE
+#include "orbfe_adapter.hpp"
+#endif
+
 using namespace ORB_SLAM2;
 
 namespace {
@@ -577,5 +583,71 @@ int orm_stereo_frame(const uint8_t* left, const uint8_t* right, int w, int h, in
     *n_right = nr;
     return F->N;
 }
+
+
+#ifdef ORM_DROPIN
+/* The adapter's replacement for Frame::ComputeStereoMatches (include/orbfe_adapter.hpp) on a reference
+ * Frame: same setup as orm_compute_stereo_matches, but the device routine runs instead of the member. */
+void orm_dropin_compute_stereo_matches(const orc_frame_view* fl, const orc_frame_view* fr, const uint8_t* left, const uint8_t* right, int w,
+                                       int h, float fx, float bf, float* uright, float* depth) {
+    ORBextractor exL(1000, 1.2f, fl->nlevels, 20, 7), exR(1000, 1.2f, fl->nlevels, 20, 7);
+    cv::Mat imL(h, w, CV_8UC1, (void*)left, (size_t)w), imR(h, w, CV_8UC1, (void*)right, (size_t)w);
+    {
+        std::vector<cv::KeyPoint> k; cv::Mat d;
+        exL(imL, cv::Mat(), k, d);
+        exR(imR, cv::Mat(), k, d);
+    }
+    Frame* F = make_frame(fl);
+    F->mvKeysRight.resize(fr->n);
+    for (int i = 0; i < fr->n; i++) F->mvKeysRight[i] = to_cv(fr->kps[i]);
+    F->mDescriptorsRight.create(std::max(fr->n, 1), 32, CV_8UC1);
+    if (fr->n) std::memcpy(F->mDescriptorsRight.data, fr->desc, (size_t)fr->n * 32);
+    F->mpORBextractorLeft = &exL; F->mpORBextractorRight = &exR;
+    F->mbf = bf; F->mb = bf / fx;
+    ORBmatcherFE fe;
+    fe.ComputeStereoMatches(*F);
+    for (int i = 0; i < fl->n; i++) { uright[i] = F->mvuRight[i]; depth[i] = F->mvDepth[i]; }
+    F->mpORBextractorLeft = F->mpORBextractorRight = nullptr;
+}
+
+/* The adapter's replacements for ComputeImageBounds + UndistortKeyPoints + AssignFeaturesToGrid applied to a
+ * Frame the reference's monocular constructor built: its own epilogue results are wiped first. */
+int orm_dropin_epilogue(const uint8_t* img, int w, int h, int nfeatures, const float* cam, const float* dist, int ndist, orc_keypoint* kps,
+                        orc_keypoint* kps_un, float* bounds, int* cell_start, int* cell_items, int cap) {
+    static thread_local ORBextractor* pex = nullptr;
+    static thread_local int pexFeatures = 0;
+    if (!pex || pexFeatures != nfeatures) { delete pex; pex = new ORBextractor(nfeatures, 1.2f, 8, 20, 7); pexFeatures = nfeatures; }
+    cv::Mat im(h, w, CV_8UC1, (void*)img, (size_t)w);
+    cv::Mat K = cv::Mat::eye(3, 3, CV_32F);
+    K.at<float>(0, 0) = cam[0]; K.at<float>(1, 1) = cam[1]; K.at<float>(0, 2) = cam[2]; K.at<float>(1, 2) = cam[3];
+    cv::Mat D(ndist, 1, CV_32F);
+    for (int i = 0; i < ndist; i++) D.at<float>(i) = dist[i];
+    Frame::mbInitialComputations = true;
+    Frame* F = new Frame(im, 0.0, pex, nullptr, K, D, 0.0f, 0.0f);
+    g.frames.push_back(F);
+    F->mpORBextractorLeft = nullptr;
+    if (F->N > cap) return -1;
+    F->mvKeysUn.clear();
+    for (int ix = 0; ix < FRAME_GRID_COLS; ix++) for (int iy = 0; iy < FRAME_GRID_ROWS; iy++) F->mGrid[ix][iy].clear();
+    Frame::mnMinX = Frame::mnMaxX = Frame::mnMinY = Frame::mnMaxY = 0.0f;
+    ORBmatcherFE fe;
+    fe.ComputeImageBounds(*F, im);
+    fe.UndistortAndAssign(*F);
+    for (int i = 0; i < F->N; i++) {
+        const cv::KeyPoint &a = F->mvKeys[i], &b = F->mvKeysUn[i];
+        kps[i] = orc_keypoint{a.pt.x, a.pt.y, a.size, a.angle, a.response, a.octave, a.class_id};
+        kps_un[i] = orc_keypoint{b.pt.x, b.pt.y, b.size, b.angle, b.response, b.octave, b.class_id};
+    }
+    bounds[0] = Frame::mnMinX; bounds[1] = Frame::mnMaxX; bounds[2] = Frame::mnMinY; bounds[3] = Frame::mnMaxY;
+    int n = 0;
+    for (int ix = 0; ix < FRAME_GRID_COLS; ix++)
+        for (int iy = 0; iy < FRAME_GRID_ROWS; iy++) {
+            cell_start[ix * FRAME_GRID_ROWS + iy] = n;
+            for (size_t j = 0; j < F->mGrid[ix][iy].size(); j++) cell_items[n++] = (int)F->mGrid[ix][iy][j];
+        }
+    cell_start[FRAME_GRID_COLS * FRAME_GRID_ROWS] = n;
+    return F->N;
+}
+#endif
 
 }  // extern "C"

@@ -71,3 +71,32 @@ def test_stereo_frame_constructor_on_the_gpu(dropin, w, h, nf, seed, disp, cam, 
         # `mb = mbf/fx` is assigned (:113), so the search range maxD = mbf/mb comes from an uninitialised member.  The routine
         # itself, entered with mb set, is compared in test_reference_call_sites_on_the_gpu[stereo].
         assert len(ur) == len(k) and len(dp) == len(k)
+
+
+@pytest.mark.parametrize("w,h,nf,seed,disp,fx,bf", [(640, 480, 1000, 21, 12, 500.0, 40.0), (1241, 376, 2000, 2, 20, 718.856, 386.1448)])
+def test_adapter_stereo_on_a_reference_frame(dropin, w, h, nf, seed, disp, fx, bf):
+    """include/orbfe_adapter.hpp's ComputeStereoMatches(Frame&) — the replacement for Frame::ComputeStereoMatches — applied to the
+    reference's own Frame object gives what the reference's member gives (fixture of the unmodified library)."""
+    from orb_slam2_annotate_b200 import synth
+    G = np.load(T.GOLDEN)
+    left, right = synth.stereo_pair(w, h, seed=seed, disparity=disp)
+    ol, orr = dropin.OracleExtractor(nf), dropin.OracleExtractor(nf)
+    k, d = ol(left); kr, dr = orr(right)
+    t = ol.tables()
+    ur, dp = dropin.dropin_compute_stereo_matches(dropin.frame_view(k, d, w, h, t["scale"]), dropin.frame_view(kr, dr, w, h, t["scale"]), left, right, fx, bf)
+    assert np.array_equal(ur.view(np.int32), G[f"stereo_{w}_uright"]) and np.array_equal(dp.view(np.int32), G[f"stereo_{w}_depth"])
+
+
+def test_adapter_epilogue_on_a_reference_frame(dropin):
+    """The adapter's ComputeImageBounds + UndistortAndAssign on a Frame built by the reference's
+    monocular constructor reproduce what the constructor's own UndistortKeyPoints / ComputeImageBounds / AssignFeaturesToGrid left."""
+    from orb_slam2_annotate_b200 import synth
+    cams = {"tum1": ((517.306408, 516.469215, 318.643040, 255.313989), (0.262383, -0.953104, -0.005358, 0.002628, 1.163314)),
+            "plain": ((500.0, 500.0, 320.0, 240.0), (0.0, 0.0, 0.0, 0.0))}
+    for name, (cam, dist) in cams.items():
+        img = synth.frame(T.W, T.H, 61)
+        k, ku, b, cs, items = dropin.ref_mono_frame(img, 1000, cam, dist)
+        k2, ku2, b2, cs2, items2 = dropin.dropin_epilogue(img, 1000, cam, dist)
+        assert k.tobytes() == k2.tobytes()
+        assert ku.tobytes() == ku2.tobytes(), name
+        assert b.tobytes() == b2.tobytes() and np.array_equal(cs, cs2) and np.array_equal(items, items2), name
