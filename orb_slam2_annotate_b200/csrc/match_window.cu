@@ -874,7 +874,7 @@ __global__ void __launch_bounds__(128) stereo_match_kernel(const __grid_constant
     }
 }
 
-// median of the truncated SADs (element size/2 of the sorted list) and the 1.5*1.4*median cut
+// median of the truncated SADs (element size/2 of the sorted list, found by bisection on the value) and the 1.5*1.4*median cut
 __global__ void __launch_bounds__(256) stereo_median_kernel(const __grid_constant__ StereoArgs a) {
     constexpr int MCAP = 4096;                       // matched keypoints staged in shared memory (more: global path)
     __shared__ int s_cnt, s_median;
@@ -894,25 +894,28 @@ __global__ void __launch_bounds__(256) stereo_median_kernel(const __grid_constan
     const int m = s_cnt;
     if (m == 0) return;
     const int target = m / 2;                                                           // :672
-    if (m <= MCAP) {
-        for (int i = tid; i < m; i += 256) {
-            const int v = s_vals[i];
-            int less = 0, eq = 0;
-            for (int j = 0; j < m; j++) { const int u = s_vals[j]; less += u < v; eq += u == v; }
-            if (less <= target && target < less + eq) s_median = v;
-        }
-    } else {
-        for (int i = tid; i < P.nl; i += 256) {
-            const int v = P.sad[i];
-            if (v < 0) continue;
-            int less = 0, eq = 0;
-            for (int j = 0; j < P.nl; j++) {
-                const int u = P.sad[j];
-                if (u >= 0) { less += u < v; eq += u == v; }
+    // element `target` of the sorted list = the smallest value v with #{u <= v} > target: bisection on the value with
+    // block-wide counts (the SADs are < 2^17; the first loop only runs if that ever stops being true)
+    const bool staged = m <= MCAP;
+    auto count_le = [&](int v) {
+        int total = 0;
+        if (staged) {
+            for (int base = 0; base < m; base += 256) total += __syncthreads_count(base + tid < m && s_vals[base + tid] <= v);
+        } else {
+            for (int base = 0; base < P.nl; base += 256) {
+                const int u = base + tid < P.nl ? P.sad[base + tid] : -1;
+                total += __syncthreads_count(u >= 0 && u <= v);
             }
-            if (less <= target && target < less + eq) s_median = v;
         }
+        return total;
+    };
+    int lo = -1, hi = (1 << 17) - 1;
+    while (hi < 0x3FFFFFFF && count_le(hi) <= target) hi = 2 * hi + 1;
+    while (hi - lo > 1) {
+        const int mid = lo + (hi - lo) / 2;
+        if (count_le(mid) > target) hi = mid; else lo = mid;
     }
+    if (tid == 0) s_median = hi;
     __syncthreads();
     const float thDist = __fmul_rn(__fmul_rn(1.5f, 1.4f), (float)s_median);             // :673
     for (int i = tid; i < P.nl; i += 256) {
