@@ -72,6 +72,7 @@ struct orbfe_extractor {
     cudaGraphExec_t graphExec = nullptr;
     std::vector<uint8_t> graphKey;
     int graphLaunches = 0;
+    bool graphRefused = false;     // a capture failed once: stay eager for the life of the handle
     // optional per-stage timing (events on the handle's stream)
     bool profiling = false;
     cudaEvent_t ev[ORBFE_NUM_STAGES + 1] = {};
@@ -457,7 +458,7 @@ static void graph_key(const orbfe_extractor* e, std::vector<uint8_t>& key) {
 // per-function attributes), the second captures, later ones replay.
 static int enqueue_extract_small(orbfe_extractor* e) {
     static const bool off = std::getenv("ORBFE_NO_GRAPH") != nullptr;
-    if (off || e->profiling) return enqueue_extract(e);
+    if (off || e->profiling || e->graphRefused) return enqueue_extract(e);
     std::vector<uint8_t> key;
     graph_key(e, key);
     if (e->graphExec && key == e->graphKey) {
@@ -478,12 +479,13 @@ static int enqueue_extract_small(orbfe_extractor* e) {
         if (graph) cudaGraphDestroy(graph);
         cudaGetLastError();
         e->graphKey.clear();
+        e->graphRefused = true;
         return rc ? rc : enqueue_extract(e);         // capture refused: stay eager
     }
     e->graphLaunches = e->lastLaunches;
     const cudaError_t ci = cudaGraphInstantiate(&e->graphExec, graph, 0);
     cudaGraphDestroy(graph);
-    if (ci != cudaSuccess) { e->graphExec = nullptr; e->graphKey.clear(); cudaGetLastError(); return enqueue_extract(e); }
+    if (ci != cudaSuccess) { e->graphExec = nullptr; e->graphKey.clear(); e->graphRefused = true; cudaGetLastError(); return enqueue_extract(e); }
     CU(cudaGraphLaunch(e->graphExec, e->stream));
     return 0;
 }
