@@ -80,11 +80,13 @@ resize_level_kernel(const uint8_t* __restrict__ src_base, uint8_t* __restrict__ 
 // table (xq: three int4 per column group) and stay in registers while the thread walks PRQ rows.
 // SIMPLE (every down-scaling level): no output row has row0 == row1 and a source row is the lower
 // row of at most one output row, so the emission is a single predicated block per source row.
-constexpr int PRQ = 16;
+constexpr int PRQ_BATCH = 16;      // output rows per thread: large batches (throughput: the row tables amortise over 16 rows)
+constexpr int PRQ_SMALL = 4;       // batches <= 4: four times the threads and a quarter of the dependent load rounds per thread
+                                   // (one 640x480 frame: 7.9 -> about 4 us per level, the levels run one after the other)
 constexpr int kBandsPerCta = 5;   // 128 consecutive tasks span at most 1 + ceil(127 / nq) bands; nq >= 32 is required
 
 // (32 registers for full occupancy spill and run slower: 0.70 vs 0.59 ms)
-template <bool SIMPLE>
+template <bool SIMPLE, int PRQ>
 __global__ void __launch_bounds__(128)
 resize_level_q_kernel(const uint8_t* __restrict__ src_base, uint8_t* __restrict__ dst_base,
                       long long sframe_bytes, long long dframe_bytes, int spitch, int dpitch,
@@ -173,9 +175,12 @@ int launch_pyramid(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
         const LevelGeom& L = g.lv[l];
         dim3 block(128);
         if (d.xq[l] && (L.w + 3) / 4 >= 32) {           // narrower levels: a CTA's tasks would span more than kBandsPerCta bands
-            const int tasks = ((L.w + 3) / 4) * ((L.h + PRQ - 1) / PRQ);
+            const bool small = g.batch <= 4;
+            const int prq = small ? PRQ_SMALL : PRQ_BATCH;
+            const int tasks = ((L.w + 3) / 4) * ((L.h + prq - 1) / prq);
             dim3 gridq((tasks + 127) / 128, 1, g.batch);
-            auto kern = d.xqSimple[l] ? resize_level_q_kernel<true> : resize_level_q_kernel<false>;
+            auto kern = small ? (d.xqSimple[l] ? resize_level_q_kernel<true, PRQ_SMALL> : resize_level_q_kernel<false, PRQ_SMALL>)
+                              : (d.xqSimple[l] ? resize_level_q_kernel<true, PRQ_BATCH> : resize_level_q_kernel<false, PRQ_BATCH>);
             kern<<<gridq, block, 0, s>>>(d.pyr + P.pyrOff + (long long)g.frame0 * P.lvBytes,
                                          d.pyr + L.pyrOff + (long long)g.frame0 * L.lvBytes,
                                          P.lvBytes, L.lvBytes, P.pitch, L.pitch, L.w, L.h, d.xq[l], d.ytab[l]);
