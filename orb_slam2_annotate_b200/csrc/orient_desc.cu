@@ -87,12 +87,14 @@ constexpr int RAW_BYTES = RAW_ROWS * RAW_STRIDE, BLR_BYTES = BLR_ROWS * BLR_STRI
 constexpr int RAW_SLOT = (RAW_BYTES + 127) / 128 * 128, BLR_SLOT = (BLR_BYTES + 127) / 128 * 128;   // TMA destinations are 128-byte aligned
 constexpr int WARP_BYTES = RAW_SLOT + 2 * BLR_SLOT;   // one level window (dead once the moments are summed) + two blurred windows
 static_assert(RAW_ROWS == kTmaRawH && BLR_ROWS == kTmaBlurH, "TMA boxes are built on the host from orbfe_internal.cuh");
-constexpr int KPW = 4;   // keypoints per warp
+constexpr int KPW_BATCH = 4;   // keypoints per warp (the pattern registers and the prologue amortise over them)
+constexpr int KPW_SMALL = 1;   // batches <= 4: one keypoint per warp, four times the warps, no serial walk
 
 // One warp per keypoint: the moment rows and the 512 pattern lookups are LDS.U8 on the two windows in shared memory.
 // TMA descriptors travel as a kernel parameter: {level, blurred level} per pyramid level
 struct alignas(64) LevelMaps { CUtensorMap m[2 * kMaxLevels]; };
 
+template <int KPW>
 __global__ void __launch_bounds__(256, 4)
 orient_desc_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ DevBufs d,
                    const __grid_constant__ LevelMaps maps, const int* __restrict__ umax) {
@@ -250,11 +252,14 @@ int launch_orient_desc(const FrameSetGeom& g, const DevBufs& d, const int* d_uma
     constexpr int smem = 8 * WARP_BYTES;
     // per device and cheap, so set on every eager launch rather than tracked per context (a stream capture replays a
     // schedule whose eager run already applied it)
+    const bool small = g.batch <= 4;
     cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
     cudaStreamIsCapturing(s, &cap);
     if (cap == cudaStreamCaptureStatusNone &&
-        cudaFuncSetAttribute(orient_desc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return 0;
-    orient_desc_kernel<<<dim3((g.outCap + 8 * KPW - 1) / (8 * KPW), g.batch), 256, smem, s>>>(g, d, maps, d_umax);
+        cudaFuncSetAttribute(small ? orient_desc_kernel<KPW_SMALL> : orient_desc_kernel<KPW_BATCH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             smem) != cudaSuccess) return 0;
+    if (small) orient_desc_kernel<KPW_SMALL><<<dim3((g.outCap + 8 * KPW_SMALL - 1) / (8 * KPW_SMALL), g.batch), 256, smem, s>>>(g, d, maps, d_umax);
+    else orient_desc_kernel<KPW_BATCH><<<dim3((g.outCap + 8 * KPW_BATCH - 1) / (8 * KPW_BATCH), g.batch), 256, smem, s>>>(g, d, maps, d_umax);
     return 1;
 }
 
