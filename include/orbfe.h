@@ -95,7 +95,9 @@ int orbfe_extract_batch(orbfe_extractor* e, const uint8_t* imgs, int batch, int 
  * orbfe_extractor_device_results after orbfe_extractor_sync.  When d_imgs is 16-byte aligned,
  * stride is a multiple of 16 equal to the padded width and the frames are contiguous, the frames
  * are used in place as pyramid level 0 (no copy): they must stay valid and unmodified until the
- * handle has been synchronised, and orbfe_pyramid_level(.., 0, ..) reads them. */
+ * handle has been synchronised, and orbfe_pyramid_level(.., 0, ..) reads them.  No byte outside
+ * [d_imgs, d_imgs + batch * height * stride) is read: the kernels' word loads stay inside a row's pitch
+ * and the TMA descriptors of the alias cover exactly `batch` frames (boxes past the end are zero-filled). */
 int orbfe_extract_batch_device(orbfe_extractor* e, const uint8_t* d_imgs, int batch, int width,
                                int height, ptrdiff_t stride, ptrdiff_t frame_stride);
 int orbfe_extractor_sync(orbfe_extractor* e);
@@ -228,6 +230,47 @@ int orbfe_knn2(orbfe_matcher* m, const uint8_t* query, int nq, const uint8_t* tr
 int orbfe_knn2_device(orbfe_matcher* m, const uint8_t* d_query, int nq, const uint8_t* d_train,
                       int nt, int th, float ratio, int32_t* d_out_idx, int32_t* d_out_d1,
                       int32_t* d_out_d2);
+
+/* Which engine serves orbfe_knn2 / _device / _sharded.  ORBFE_KNN_POPC: 8 x (XOR + POPC) per comparison on
+ * the integer pipe, the reference's own form (src/ORBmatcher.cc:1835-1841).  ORBFE_KNN_MMA: the distance as a
+ * contraction, d = |a| + |b| - 2<a,b> over bits expanded to bytes in shared memory, on the tensor cores
+ * (tcgen05.mma kind::i8, accumulators in TMEM).  Both give identical results; ORBFE_KNN_AUTO (default) takes
+ * the tensor cores from 2^26 comparisons per call upwards.  The environment variable ORBFE_KNN_ENGINE = popc |
+ * mma overrides AUTO for a whole process. */
+enum { ORBFE_KNN_AUTO = 0, ORBFE_KNN_POPC = 1, ORBFE_KNN_MMA = 2 };
+int orbfe_matcher_set_knn_engine(orbfe_matcher* m, int engine);
+
+/* ---- BASELINE.json configs[4]: brute-force kNN-2 with the QUERY rows sharded over the GPUs of one node and an
+ * NCCL all-gather of the per-query results (the reference has no counterpart: its
+ * loops are src/ORBmatcher.cc:233-269).  One process per GPU.  NCCL is bound at run time (dlopen of
+ * libnccl.so.2: the copy the host framework already loaded, else the system one), so liborbfe.so does not
+ * link it and every other entry point works without it. */
+typedef struct orbfe_comm orbfe_comm;
+#define ORBFE_COMM_ID_BYTES 128
+/* rank 0 creates the id (ncclGetUniqueId) and hands the 128 bytes to the other ranks by any means */
+int orbfe_comm_unique_id(uint8_t id[ORBFE_COMM_ID_BYTES]);
+/* collective over all ranks (ncclCommInitRank); `device` is this rank's CUDA device */
+int orbfe_comm_create(const uint8_t id[ORBFE_COMM_ID_BYTES], int world, int rank, int device, orbfe_comm** out);
+/* a communicator the caller already owns (ncclComm_t); orbfe_comm_destroy leaves it alive */
+int orbfe_comm_wrap(void* nccl_comm, int world, int rank, int device, orbfe_comm** out);
+void orbfe_comm_destroy(orbfe_comm* c);
+int orbfe_comm_world(const orbfe_comm* c);
+int orbfe_comm_rank(const orbfe_comm* c);
+
+/* one gathered result row: 8 bytes per query */
+typedef struct orbfe_knn_result {
+    int32_t idx;        /* accepted train row, or -1 */
+    uint16_t d1, d2;    /* best and second-best distance (256 when absent) */
+} orbfe_knn_result;
+
+/* Rows per shard: rank r owns query rows [r * per, min((r + 1) * per, nq)). */
+int orbfe_knn2_shard_rows(int nq, int world);
+/* Every rank passes the same nq query rows and the same train set (DEVICE pointers, replicated); rank r
+ * searches its shard, packs (idx, d1, d2) into 8 bytes per query and one in-place ncclAllGather on the matcher's
+ * stream leaves all nq results on every rank.  d_out must hold world * orbfe_knn2_shard_rows(nq, world)
+ * rows (the tail past nq is padding).  Asynchronous: orbfe_matcher_sync before reading. */
+int orbfe_knn2_sharded(orbfe_matcher* m, orbfe_comm* c, const uint8_t* d_query, int nq, const uint8_t* d_train,
+                       int nt, int th, float ratio, orbfe_knn_result* d_out);
 
 /* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize).
  * prev_matched: 2*f1->n floats (x,y), in/out; matches12: f1->n ints out; *nmatches out. */

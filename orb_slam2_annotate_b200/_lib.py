@@ -128,6 +128,15 @@ SIGNATURES = {
     "orbfe_matcher_sync": (_i, [_vp]),
     "orbfe_knn2": (_i, [_vp, _vp, _i, _vp, _i, _i, _f, _vp, _vp, _vp]),
     "orbfe_knn2_device": (_i, [_vp, _vp, _i, _vp, _i, _i, _f, _vp, _vp, _vp]),
+    "orbfe_matcher_set_knn_engine": (_i, [_vp, _i]),
+    "orbfe_comm_unique_id": (_i, [_vp]),
+    "orbfe_comm_create": (_i, [_vp, _i, _i, _i, C.POINTER(_vp)]),
+    "orbfe_comm_wrap": (_i, [_vp, _i, _i, _i, C.POINTER(_vp)]),
+    "orbfe_comm_destroy": (None, [_vp]),
+    "orbfe_comm_world": (_i, [_vp]),
+    "orbfe_comm_rank": (_i, [_vp]),
+    "orbfe_knn2_shard_rows": (_i, [_i, _i]),
+    "orbfe_knn2_sharded": (_i, [_vp, _vp, _vp, _i, _vp, _i, _i, _f, _vp]),
     "orbfe_search_init": (_i, [_vp, C.POINTER(FrameView), C.POINTER(FrameView), _vp, _vp, _i, _f, _i, _ip]),
     "orbfe_search_init_consecutive_device": (_i, [_vp, _vp, _vp, _vp, _i, _i, _f, _f, _f, _f, _i, _f, _i, _vp, _vp]),
     "orbfe_search_local_points": (_i, [_vp, C.POINTER(FrameView), C.POINTER(MapPointsView), _f, _f, _vp, _vp, _ip]),

@@ -61,6 +61,7 @@ struct orbfe_extractor {
     std::vector<CUtensorMap> tmaps;   // {level, blurred level} descriptors, passed to the kernel by value
     std::vector<CUtensorMap> fastMaps; // level descriptors with the FAST window box
     int lastBatch = 0, lastLaunches = 0;
+    int level0MapFrames = 0;       // frames the level-0 tensor maps cover (the batch capacity, or an alias's frame count)
     // Frame epilogue (orbfe_extractor_set_camera): mvKeysUn + mGrid of every frame of a batch
     bool haveCam = false;
     CamGeom camGeom{};
@@ -390,6 +391,7 @@ static int ensure_geometry(orbfe_extractor* e, int w, int h, int batch) {
     g.batch = batch;
     e->g = g;
     e->geomW = w; e->geomH = h; e->geomBatchCap = cap;
+    e->level0MapFrames = cap;
     if (octree_smem_bytes(g) > 200 * 1024) return fail(ORBFE_ERR_ARG, "nfeatures too large for the quadtree kernel's shared memory");
     cudaError_t ce = (cudaError_t)octree_prepare(g);
     if (ce != cudaSuccess) return fail(ORBFE_ERR_CUDA, "cudaFuncSetAttribute(octree)", ce);
@@ -494,15 +496,19 @@ static int enqueue_extract_small(orbfe_extractor* e) {
 // when their layout already is the level layout (16-byte aligned base, stride == pitch, frames
 // contiguous): every kernel addresses level 0 as d.pyr + lv[0].pyrOff, so the alias is just a
 // different offset, plus the level-0 TMA descriptor of the orientation kernel.
-static int set_level0_source(orbfe_extractor* e, const uint8_t* alias) {
+static int set_level0_source(orbfe_extractor* e, const uint8_t* alias, int aliasFrames = 0) {
     LevelGeom& L0 = e->g.lv[0];
     const uint8_t* want = alias ? alias : e->pyr.p + L0.blurOff;       // blurOff keeps the in-buffer offset
-    if (e->d.pyr + L0.pyrOff == want) return 0;
+    // the tensor maps of an alias cover exactly the frames the caller supplied: TMA boxes that reach past the last
+    // frame's last row are zero-filled instead of fetched from behind the caller's allocation
+    const int frames = alias ? aliasFrames : e->geomBatchCap;
+    if (e->d.pyr + L0.pyrOff == want && e->level0MapFrames == frames) return 0;
     L0.pyrOff = want - e->d.pyr;
-    int rc = encode_level_map(&e->tmaps[0], (void*)want, L0.pitch, (long long)L0.h * e->geomBatchCap, kTmaRawW, kTmaRawH);
+    e->level0MapFrames = frames;
+    int rc = encode_level_map(&e->tmaps[0], (void*)want, L0.pitch, (long long)L0.h * frames, kTmaRawW, kTmaRawH);
     if (rc) return rc;
     const int rows = fast_window_rows(L0);
-    return encode_level_map(&e->fastMaps[0], (void*)want, L0.pitch, (long long)L0.h * e->geomBatchCap, 64, rows ? rows : 40);
+    return encode_level_map(&e->fastMaps[0], (void*)want, L0.pitch, (long long)L0.h * frames, 64, rows ? rows : 40);
 }
 
 // copy `batch` frames into level 0 of the pyramid (kind: H2D or D2D)
@@ -641,7 +647,7 @@ int orbfe_extract_batch_device(orbfe_extractor* e, const uint8_t* d_imgs, int ba
     if (stride == L0.pitch && (batch == 1 || frame_stride == (ptrdiff_t)height * stride) &&
         (reinterpret_cast<uintptr_t>(d_imgs) & 15) == 0) {
         // the frames already are level 0: no copy (they must stay valid until the results are fetched)
-        if ((rc = set_level0_source(e, d_imgs))) return rc;
+        if ((rc = set_level0_source(e, d_imgs, batch))) return rc;
         if (e->profiling) cudaEventRecord(e->ev[0], e->stream);
     } else if ((rc = upload_level0(e, d_imgs, batch, width, height, stride, frame_stride, cudaMemcpyDeviceToDevice))) {
         return rc;

@@ -19,7 +19,36 @@ struct orbfe_matcher {
     DevArray<uint8_t> scratch[8];   // grow-only device staging, reused across calls
     PinnedArray stage, result;      // page-locked host staging of the guided searches
     bool trace = std::getenv("ORBFE_TRACE") != nullptr;
+    int knnEngine = ORBFE_KNN_AUTO;   // orbfe_matcher_set_knn_engine
+    DevArray<uint8_t> knnScratch;   // per-segment partial results of the tensor-core kNN engine
 };
+
+namespace {
+
+// which brute-force engine serves a kNN call: the tensor-core kernel needs enough work to fill its pipeline
+bool knn_use_mma(const orbfe_matcher* m, int nq, int nt) {
+    static const char* env = std::getenv("ORBFE_KNN_ENGINE");
+    int eng = m->knnEngine;
+    if (eng == ORBFE_KNN_AUTO && env) eng = !std::strcmp(env, "popc") ? ORBFE_KNN_POPC : !std::strcmp(env, "mma") ? ORBFE_KNN_MMA : eng;
+    if (eng == ORBFE_KNN_POPC) return false;
+    if (eng == ORBFE_KNN_MMA) return true;
+    return nq >= 256 && (long long)nq * nt >= (1ll << 26);
+}
+
+int knn2_dispatch(orbfe_matcher* m, const uint8_t* d_query, int nq, const uint8_t* d_train, int nt, int th, float ratio,
+                  int* d_idx, int* d_d1, int* d_d2) {
+    if (nq > 0 && knn_use_mma(m, nq, nt)) {
+        int rc = m->knnScratch.ensure(knn2_mma_scratch_bytes(nq, std::max(nt, 1)) + 256);
+        if (rc) return rc;
+        launch_knn2_mma(d_query, nq, d_train, nt, th, ratio, d_idx, d_d1, d_d2, m->knnScratch.p, m->stream);
+    } else {
+        launch_knn2(d_query, nq, d_train, nt, th, ratio, d_idx, d_d1, d_d2, m->stream);
+    }
+    CU(cudaGetLastError());
+    return ORBFE_OK;
+}
+
+}  // namespace
 
 extern "C" {
 
@@ -57,8 +86,15 @@ void orbfe_matcher_destroy(orbfe_matcher* m) {
     cudaSetDevice(m->device);
     if (m->stream) { cudaStreamSynchronize(m->stream); cudaStreamDestroy(m->stream); }
     for (auto& s : m->scratch) s.release();
+    m->knnScratch.release();
     m->stage.release(); m->result.release();
     delete m;
+}
+
+int orbfe_matcher_set_knn_engine(orbfe_matcher* m, int engine) {
+    if (!m || engine < ORBFE_KNN_AUTO || engine > ORBFE_KNN_MMA) return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_matcher_set_knn_engine");
+    m->knnEngine = engine;
+    return ORBFE_OK;
 }
 
 void* orbfe_matcher_stream(orbfe_matcher* m) { return m ? (void*)m->stream : nullptr; }
@@ -76,9 +112,7 @@ int orbfe_knn2_device(orbfe_matcher* m, const uint8_t* d_query, int nq, const ui
         return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_knn2_device");
     if (((uintptr_t)d_query | (uintptr_t)d_train) & 15) return fail(ORBFE_ERR_ARG, "descriptor arrays must be 16-byte aligned");
     CU(cudaSetDevice(m->device));
-    launch_knn2(d_query, nq, d_train, nt, th, ratio, d_out_idx, d_out_d1, d_out_d2, m->stream);
-    CU(cudaGetLastError());
-    return ORBFE_OK;
+    return knn2_dispatch(m, d_query, nq, d_train, nt, th, ratio, d_out_idx, d_out_d1, d_out_d2);
 }
 
 int orbfe_knn2(orbfe_matcher* m, const uint8_t* query, int nq, const uint8_t* train, int nt, int th,
@@ -96,8 +130,7 @@ int orbfe_knn2(orbfe_matcher* m, const uint8_t* query, int nq, const uint8_t* tr
     int* d_d2 = d_d1 + nq;
     CU(cudaMemcpyAsync(m->scratch[0].p, query, (size_t)nq * 32, cudaMemcpyHostToDevice, m->stream));
     if (nt) CU(cudaMemcpyAsync(m->scratch[1].p, train, (size_t)nt * 32, cudaMemcpyHostToDevice, m->stream));
-    launch_knn2(m->scratch[0].p, nq, m->scratch[1].p, nt, th, ratio, d_idx, d_d1, d_d2, m->stream);
-    CU(cudaGetLastError());
+    if ((rc = knn2_dispatch(m, m->scratch[0].p, nq, m->scratch[1].p, nt, th, ratio, d_idx, d_d1, d_d2))) return rc;
     CU(cudaMemcpyAsync(out_idx, d_idx, (size_t)nq * 4, cudaMemcpyDeviceToHost, m->stream));
     CU(cudaMemcpyAsync(out_d1, d_d1, (size_t)nq * 4, cudaMemcpyDeviceToHost, m->stream));
     CU(cudaMemcpyAsync(out_d2, d_d2, (size_t)nq * 4, cudaMemcpyDeviceToHost, m->stream));

@@ -11,6 +11,14 @@ namespace orbfe {
 int launch_knn2(const uint8_t* d_query, int nq, const uint8_t* d_train, int nt, int th, float ratio,
                 int* d_idx, int* d_d1, int* d_d2, cudaStream_t s);
 
+// tensor-core engine (match_knn_mma.cu: tcgen05.mma kind::i8 on bit -> byte expanded rows, accumulators in TMEM);
+// scratch = knn2_mma_scratch_bytes(nq, nt) bytes of device memory for the per-segment partial results
+size_t knn2_mma_scratch_bytes(int nq, int nt);
+int launch_knn2_mma(const uint8_t* d_query, int nq, const uint8_t* d_train, int nt, int th, float ratio,
+                    int* d_idx, int* d_d1, int* d_d2, void* scratch, cudaStream_t s);
+// (idx, d1, d2) of rows [first, first + n) -> packed orbfe_knn_result rows (the sharded search's gather payload)
+int launch_knn2_pack(const int* d_idx, const int* d_d1, const int* d_d2, int n, void* d_packed, cudaStream_t s);
+
 // minX / minY place keypoints (PosInGrid); qminX / qminY are what GetFeaturesInArea subtracts: the same for a Frame,
 // the int-truncated bounds for a KeyFrame (include/KeyFrame.h:191-194)
 struct GridGeom { float minX, minY, invW, invH, qminX, qminY; };

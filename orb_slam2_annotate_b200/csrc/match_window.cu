@@ -948,11 +948,12 @@ void search_init_carve(InitArgs& a, void* scratch, int npairs) {
 int launch_search_init(const InitArgs& a, int npairs, cudaStream_t st) {
     if (npairs <= 0) return 0;
     const size_t gsm = (size_t)NCELL * 4 + (size_t)a.cap * 2;
-    if (gsm > 40 * 1024) cudaFuncSetAttribute(search_init_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)gsm);
+    // per function and device, shared by every handle and thread: always the one worst case, never a per-call size
+    if (gsm > 40 * 1024) cudaFuncSetAttribute(search_init_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     search_init_grid_kernel<<<npairs, SG_THREADS, gsm, st>>>(a);
     search_init_topk_kernel<<<dim3(SA_CTAS, npairs), SI_WARPS * 32, 0, st>>>(a);
     const size_t bsm = (size_t)a.cap * 7 + 16;
-    if (bsm > 24 * 1024) cudaFuncSetAttribute(search_init_greedy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bsm);
+    if (bsm > 24 * 1024) cudaFuncSetAttribute(search_init_greedy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     search_init_greedy_kernel<<<npairs, 32, bsm, st>>>(a);
     return 3;
 }

@@ -340,9 +340,12 @@ size_t octree_smem_bytes(const FrameSetGeom& g) {
     return (size_t)node_capacity(g) * 64 + (size_t)key_capacity(g) * 8;
 }
 
+// The attribute is per function and per device, not per handle: it is always set to the one worst case
+// ensure_geometry admits (200 KB), so a handle with a small feature budget cannot lower the limit under a
+// live handle with a large one (mono Tracking keeps ORBextractor(2 * nFeatures) and ORBextractor(nFeatures)).
 int octree_prepare(const FrameSetGeom& g) {
-    return (int)cudaFuncSetAttribute(octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)octree_smem_bytes(g));
+    (void)g;
+    return (int)cudaFuncSetAttribute(octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
 }
 
 int launch_octree(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {

@@ -117,9 +117,12 @@ resize_level_q_kernel(const uint8_t* __restrict__ src_base, uint8_t* __restrict_
     const uint8_t* src = src_base + (long long)blockIdx.z * sframe_bytes + t0.x;
     uint8_t* dst = dst_base + (long long)blockIdx.z * dframe_bytes + x4;
     struct Raw { uint32_t w0, w1, w2; };
+    // the second / third word never leave the row (the last column group's taps are clamped to the row, so what the
+    // repeated word holds is not selected): level 0 may alias a caller buffer with nothing mapped behind it
+    const int o1 = min(4, spitch - 4 - t0.x) >> 2, o2 = min(8, spitch - 4 - t0.x) >> 2;
     auto load_raw = [&](int r) {
         const uint32_t* p = reinterpret_cast<const uint32_t*>(src + (long long)r * spitch);
-        Raw w; w.w0 = __ldg(p); w.w1 = __ldg(p + 1); w.w2 = __ldg(p + 2);
+        Raw w; w.w0 = __ldg(p); w.w1 = __ldg(p + o1); w.w2 = __ldg(p + o2);
         return w;
     };
     auto conv = [&](const Raw& w, uint32_t* h) {

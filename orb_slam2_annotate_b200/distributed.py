@@ -51,3 +51,67 @@ def knn2_sharded(knn2_fn, query: np.ndarray, train: np.ndarray, group=None, devi
         rb, re = shard_range(m, r, world)
         res[:, rb:re] = out[r].cpu().numpy()[:, :re - rb]
     return res[0], res[1], res[2]
+
+
+# ---- configs[4] on the device, behind the C ABI (orbfe_comm_*, orbfe_knn2_sharded) ---------------------------
+
+KNN_RESULT_DTYPE = np.dtype([("idx", np.int32), ("d1", np.uint16), ("d2", np.uint16)])   # orbfe_knn_result, 8 bytes
+
+
+def shard_rows(n: int, world: int) -> int:
+    """Rows per shard of the device path (orbfe_knn2_shard_rows): rank r owns [r * per, min((r + 1) * per, n))."""
+    return (n + world - 1) // world if n > 0 and world > 0 else 0
+
+
+class Comm:
+    """The library's NCCL communicator (``orbfe_comm``).  ``Comm.from_torch()`` builds one for the ranks of the
+    default torch.distributed group: rank 0 draws the NCCL unique id through the C ABI and the 128 bytes travel by
+    ``dist.broadcast`` (any backend; gloo or nccl), then every rank calls ncclCommInitRank inside the library."""
+
+    def __init__(self, unique_id: bytes, world: int, rank: int, device: int):
+        import ctypes as C
+        from . import _lib
+        self._L = _lib.lib()
+        self._h = C.c_void_p()
+        buf = (C.c_uint8 * 128).from_buffer_copy(unique_id)
+        _lib.check(self._L.orbfe_comm_create(buf, world, rank, device, C.byref(self._h)), "orbfe_comm_create")
+        self.world, self.rank, self.device = world, rank, device
+
+    @staticmethod
+    def unique_id() -> bytes:
+        import ctypes as C
+        from . import _lib
+        buf = (C.c_uint8 * 128)()
+        _lib.check(_lib.lib().orbfe_comm_unique_id(buf), "orbfe_comm_unique_id")
+        return bytes(buf)
+
+    @classmethod
+    def from_torch(cls, device: int, group=None):
+        import torch
+        import torch.distributed as dist
+        if not dist.is_initialized():
+            return cls(cls.unique_id(), 1, 0, device)
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        on_gpu = dist.get_backend(group) == "nccl"
+        t = torch.zeros(128, dtype=torch.uint8, device=f"cuda:{device}" if on_gpu else "cpu")
+        if rank == 0:
+            t.copy_(torch.frombuffer(bytearray(cls.unique_id()), dtype=torch.uint8))
+        dist.broadcast(t, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        return cls(bytes(t.cpu().numpy().tobytes()), world, rank, device)
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._L.orbfe_comm_destroy(self._h)
+            self._h.value = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def unpack_results(packed: np.ndarray, n: int):
+    """Gathered orbfe_knn_result rows (padded to world * shard_rows) -> (idx, d1, d2) int32 of the n queries."""
+    r = packed.view(KNN_RESULT_DTYPE).reshape(-1)[:n]
+    return r["idx"].astype(np.int32), r["d1"].astype(np.int32), r["d2"].astype(np.int32)

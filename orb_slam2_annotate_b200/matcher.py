@@ -243,6 +243,20 @@ class ORBmatcher:
         check(self._L.orbfe_knn2_device(self._h, q_ptr, m, t_ptr, n, th, ratio, idx_ptr, d1_ptr, d2_ptr),
               "orbfe_knn2_device")
 
+    KNN_ENGINES = {"auto": 0, "popc": 1, "mma": 2}
+
+    def set_knn_engine(self, engine: str) -> None:
+        """"popc": XOR + POPC on the integer pipe; "mma": tcgen05.mma on bit -> byte expanded rows; "auto" (default)."""
+        check(self._L.orbfe_matcher_set_knn_engine(self._h, self.KNN_ENGINES[engine]), "orbfe_matcher_set_knn_engine")
+
+    def knn2_sharded(self, comm, q_ptr: int, m: int, t_ptr: int, n: int, out_ptr: int,
+                     th: int | None = None, ratio: float | None = None) -> None:
+        """configs[4]: this rank's query shard on device pointers + one NCCL all-gather of 8-byte result rows
+        (asynchronous on the matcher's stream; out_ptr: world * shard_rows(m, world) rows of KNN_RESULT_DTYPE)."""
+        th = self.TH_LOW if th is None else th
+        ratio = self.mfNNratio if ratio is None else ratio
+        check(self._L.orbfe_knn2_sharded(self._h, comm._h, q_ptr, m, t_ptr, n, th, ratio, out_ptr), "orbfe_knn2_sharded")
+
     def SearchForInitialization(self, F1: Frame, F2: Frame, vbPrevMatched: np.ndarray, windowSize: int = 10):
         """src/ORBmatcher.cc:469-600.  vbPrevMatched float32 [N1,2] is updated in place.
         -> (nmatches, vnMatches12 int32[N1])"""

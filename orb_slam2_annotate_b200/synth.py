@@ -123,3 +123,25 @@ def planted_descriptors(train: np.ndarray, m: int, seed: int, frac: float = 0.1,
             dup[i, b >> 3] ^= np.uint8(1 << (b & 7))
     q[rows] = dup
     return q
+
+
+def planted_descriptors_fast(train: np.ndarray, m: int, seed: int, frac: float = 0.1, max_flips: int = 30):
+    """Vectorised planted_descriptors for the 1M x 1M shape of config 5.  Returns (query, rows, src, nflip): query
+    rows `rows` are train rows `src` with exactly `nflip` distinct bits flipped; all other rows are i.i.d. uniform."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    q = rng.integers(0, 256, (m, 32), dtype=np.uint8)
+    k = int(m * frac)
+    rows = np.sort(rng.choice(m, k, replace=False))
+    src = rng.integers(0, train.shape[0], k)
+    nflip = rng.integers(0, max_flips + 1, k)
+    dup = train[src].copy()
+    for c0 in range(0, k, 8192):                      # distinct bit positions per row: the smallest keys of a random table
+        c1 = min(k, c0 + 8192)
+        pos = np.argsort(rng.random((c1 - c0, 256)), axis=1)[:, :max_flips]
+        use = np.arange(max_flips)[None, :] < nflip[c0:c1, None]
+        bits = np.zeros((c1 - c0, 256), np.uint8)
+        r = np.repeat(np.arange(c1 - c0), max_flips)[use.ravel()]
+        bits[r, pos.ravel()[use.ravel()]] = 1
+        dup[c0:c1] ^= np.packbits(bits, axis=1, bitorder="little")
+    q[rows] = dup
+    return q, rows, src, nflip
