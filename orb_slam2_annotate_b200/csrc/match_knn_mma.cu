@@ -14,7 +14,7 @@
 //               into the packed key  (|b| + 256 - 2 <a,b>) << 20 | train index  (the per-column constant
 //               (|b| + 256) << 20 | index comes from shared memory, written by the producers), and the
 //               exact strict-'<' best / second-best rule  k2' = min(k2, max(k1, key)), k1' = min(k1, key)
-//               runs only for groups of four columns whose minimum beats the current second best
+//               runs only for groups of sixteen columns whose minimum beats the current second best
 //               (a key >= k2 changes nothing, so the filter is exact).
 //   warps 8-11  producers: one train row per thread and tile: two 16-byte loads, popcount, 64 expanded
 //               words written as sixteen conflict-free 16-byte stores at the swizzled chunk positions,
@@ -122,6 +122,32 @@ __device__ __forceinline__ int popc_row(const uint32_t w[8]) {
                    "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])                      \
                  : "r"(taddr) : "memory")
 
+// 32 accumulators of one query -> packed keys, folded into (k1, k2).  A key >= k2 changes neither k1 nor k2, so
+// sixteen keys at a time are screened with a min tree (about two instructions per comparison) and the exact
+// strict-'<' update runs behind a real branch only when one of them beats the current second best — after the
+// first tiles that is rare (the expected number of updates over n random rows grows like 2 ln n).
+__device__ __forceinline__ void fold32(const uint32_t (&v)[32], const uint32_t* ccs, uint32_t& k1, uint32_t& k2) {
+    constexpr uint32_t NEG2 = 0u - (2u << 20);
+    const uint4* ccp = reinterpret_cast<const uint4*>(ccs);
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        uint32_t key[16];
+#pragma unroll
+        for (int g = 0; g < 4; g++) {
+            const uint4 cc = ccp[4 * h + g];
+            key[4 * g] = v[16 * h + 4 * g] * NEG2 + cc.x;         key[4 * g + 1] = v[16 * h + 4 * g + 1] * NEG2 + cc.y;
+            key[4 * g + 2] = v[16 * h + 4 * g + 2] * NEG2 + cc.z; key[4 * g + 3] = v[16 * h + 4 * g + 3] * NEG2 + cc.w;
+        }
+        uint32_t m = key[0];
+#pragma unroll
+        for (int i = 1; i < 16; i++) m = min(m, key[i]);
+        if (m < k2) {
+#pragma unroll
+            for (int i = 0; i < 16; i++) { k2 = min(k2, max(k1, key[i])); k1 = min(k1, key[i]); }
+        }
+    }
+}
+
 // Slot reuse of the cc ring: the producers fill tile t only after the MMAs of tile t - STAGES completed
 // (empty_b), the MMAs of tile u are issued only after the epilogue released the accumulator of tile u - 2
 // (acc_empty), so when cc[t & 7] is rewritten the epilogue has finished tile t - STAGES - 2 >= t - 8 + 3:
@@ -130,8 +156,11 @@ __device__ __forceinline__ int popc_row(const uint32_t w[8]) {
 __global__ void __launch_bounds__(THREADS, 1)
 knn2_mma_kernel(const uint4* __restrict__ query, int nq, const uint4* __restrict__ train, int nt, int segLen,
                 int* __restrict__ part_idx, int* __restrict__ part_d1, int* __restrict__ part_d2) {
-    extern __shared__ uint8_t smem_raw[];
-    MmaSmem& S = *reinterpret_cast<MmaSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    // SWIZZLE_128B wants 1024-byte aligned operand blocks; the dynamic shared window of a CTA without static
+    // shared memory starts that aligned (checked: a misplaced block traps rather than computes garbage)
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    MmaSmem& S = *reinterpret_cast<MmaSmem*>(smem_raw);
+    if ((smem_u32(smem_raw) & 1023u) != 0) __trap();
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int q0 = blockIdx.x * MQ;
     const int seg = blockIdx.y;
@@ -168,32 +197,23 @@ knn2_mma_kernel(const uint4* __restrict__ query, int nq, const uint4* __restrict
         const int mtile = warp >> 2;
         const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
         uint32_t k1 = KEY_NONE, k2 = KEY_NONE;
-        constexpr uint32_t NEG2 = 0u - (2u << 20);
         for (int t = 0; t < ntiles; t++) {
             const int a = t & 1, slot = t & (CCSLOTS - 1);
             mbar_wait(&S.cc_full[slot], (t >> 3) & 1);
             mbar_wait(&S.acc_full[a], (t >> 1) & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t tbase = tmem + lane_base + (uint32_t)(a * 256 + mtile * 128);
-#pragma unroll 1
-            for (int c = 0; c < NT; c += 32) {
-                uint32_t v[32];
-                TMEM_LD32(tbase + c, v);
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                const uint4* ccp = reinterpret_cast<const uint4*>(&S.cc[slot][c]);
+            // 32 columns per tcgen05.ld, the next load in flight while the current registers are folded
+            uint32_t v0[32], v1[32];
+            TMEM_LD32(tbase, v0);
 #pragma unroll
-                for (int g = 0; g < 8; g++) {
-                    const uint4 cc = ccp[g];
-                    const uint32_t ka = v[4 * g] * NEG2 + cc.x, kb = v[4 * g + 1] * NEG2 + cc.y;
-                    const uint32_t kc = v[4 * g + 2] * NEG2 + cc.z, kd = v[4 * g + 3] * NEG2 + cc.w;
-                    const uint32_t m = min(min(ka, kb), min(kc, kd));
-                    if (m < k2) {                      // rare after the first tiles: a key >= k2 changes nothing
-                        k2 = min(k2, max(k1, ka)); k1 = min(k1, ka);
-                        k2 = min(k2, max(k1, kb)); k1 = min(k1, kb);
-                        k2 = min(k2, max(k1, kc)); k1 = min(k1, kc);
-                        k2 = min(k2, max(k1, kd)); k1 = min(k1, kd);
-                    }
-                }
+            for (int c = 0; c < NT; c += 64) {
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                TMEM_LD32(tbase + c + 32, v1);
+                fold32(v0, &S.cc[slot][c], k1, k2);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (c + 64 < NT) TMEM_LD32(tbase + c + 64, v0);
+                fold32(v1, &S.cc[slot][c + 32], k1, k2);
             }
             // this warp's accumulator reads of stage a are complete (wait::ld above)
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -314,7 +334,7 @@ int launch_knn2_mma(const uint8_t* d_query, int nq, const uint8_t* d_train, int 
     int* part_idx = (int*)scratch;
     int* part_d1 = part_idx + (size_t)nseg * nq;
     int* part_d2 = part_d1 + (size_t)nseg * nq;
-    constexpr int smem = (int)sizeof(MmaSmem) + 1024;
+    constexpr int smem = (int)sizeof(MmaSmem);
     cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
     cudaStreamIsCapturing(s, &cap);
     if (cap == cudaStreamCaptureStatusNone)
