@@ -240,6 +240,22 @@ int orbfe_knn2_device(orbfe_matcher* m, const uint8_t* d_query, int nq, const ui
 enum { ORBFE_KNN_AUTO = 0, ORBFE_KNN_POPC = 1, ORBFE_KNN_MMA = 2 };
 int orbfe_matcher_set_knn_engine(orbfe_matcher* m, int engine);
 
+/* Allocation-free variant of orbfe_knn2_device.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  No handle: `device` is the CUDA device, `cuda_stream` a cudaStream_t of that device (NULL = the
+ * default stream); inputs and outputs are the caller's DEVICE buffers as in orbfe_knn2_device; the search always runs
+ * on the tensor-core engine.  The call performs no cudaMalloc / cudaFree or any other allocation: the engine's scratch
+ * (12 bytes x nq x train segments) is a static device array of ORBFE_KNN2_NOALLOC_SCRATCH_BYTES that
+ * every GPU loading the library holds until the process exits.  Sizes that need more are refused with
+ * ORBFE_ERR_CAPACITY and a message (one segment per 2^20 train rows once nq >= 37 633, so up to 699 050 queries
+ * against up to 1 048 576 train rows; smaller query sets use up to 148 / ceil(nq / 256) segments).  All calls on one
+ * GPU share the array, which keeps the previous call's contents (nothing in it needs clearing: every slot read is
+ * written first by the same call); calls that OVERLAP on one GPU — different streams without an event between
+ * them, or different threads — race on it and return garbage.  Asynchronous on `cuda_stream`. */
+#define ORBFE_KNN2_NOALLOC_SCRATCH_BYTES (8 << 20)
+int orbfe_knn2_device_noalloc(int device, void* cuda_stream, const uint8_t* d_query, int nq, const uint8_t* d_train,
+                              int nt, int th, float ratio, int32_t* d_out_idx, int32_t* d_out_d1, int32_t* d_out_d2);
+
 /* ---- BASELINE.json configs[4]: brute-force kNN-2 with the QUERY rows sharded over the GPUs of one node and an
  * NCCL all-gather of the per-query results (the reference has no counterpart: its
  * loops are src/ORBmatcher.cc:233-269).  One process per GPU.  NCCL is bound at run time (dlopen of

@@ -26,6 +26,10 @@
 // Train sets are cut into segments (grid.y) of at most 2^20 rows — the key's index field — which also
 // gives small query sets enough CTAs; a merge kernel folds the per-segment (d1, d2, idx) in ascending
 // train order with the popc kernel's rule and applies TH_LOW and the ratio test.
+#include <cstdio>
+#include <mutex>
+
+#include "api_common.cuh"
 #include "orbfe_internal.cuh"
 #include "match_internal.cuh"
 
@@ -346,3 +350,55 @@ int launch_knn2_mma(const uint8_t* d_query, int nq, const uint8_t* d_train, int 
 }
 
 }  // namespace orbfe
+
+// ---------------------------------------------------------------------------------------------------------------
+// orbfe_knn2_device_noalloc — the tensor-core kNN-2 for callers that must not allocate (stream capture, tight
+// serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The per-segment partial results, the one piece of scratch this engine needs, live in a
+// file-scope device array instead of the matcher handle's grow-only buffer: every GPU that loads liborbfe.so
+// holds these 8 MiB until the process exits.  All calls on a device share the array and it keeps the last call's
+// contents; nothing in it has to start at zero (the kernel writes every (segment, query) slot the merge reads), but
+// two calls that overlap on one GPU race on it — serialise them on one stream or with events.
+static __device__ __align__(256) unsigned char g_knn2_noalloc_scratch[ORBFE_KNN2_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kNoallocMaxDevices = 64;
+// device address of the array per device: the name above is a host-side stand-in in host code, so the address a
+// kernel may use comes from cudaGetSymbolAddress, asked once per device with that device current
+void* g_noalloc_ptr[kNoallocMaxDevices] = {};
+std::mutex g_noalloc_mu;
+}  // namespace
+
+extern "C" int orbfe_knn2_device_noalloc(int device, void* cuda_stream, const uint8_t* d_query, int nq,
+                                         const uint8_t* d_train, int nt, int th, float ratio,
+                                         int32_t* d_out_idx, int32_t* d_out_d1, int32_t* d_out_d2) {
+    using namespace orbfe;
+    if (device < 0 || device >= kNoallocMaxDevices || nq < 0 || nt < 0 ||
+        (nq && (!d_query || !d_out_idx || !d_out_d1 || !d_out_d2)) || (nt && !d_train))
+        return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_knn2_device_noalloc");
+    if (((uintptr_t)d_query | (uintptr_t)d_train) & 15) return fail(ORBFE_ERR_ARG, "descriptor arrays must be 16-byte aligned");
+    if (nq == 0) return ORBFE_OK;
+    const size_t need = knn2_mma_scratch_bytes(nq, nt > 0 ? nt : 1);
+    if (need > (size_t)ORBFE_KNN2_NOALLOC_SCRATCH_BYTES) {
+        static thread_local char msg[256];
+        snprintf(msg, sizeof(msg), "orbfe_knn2_device_noalloc: %d queries x %d train rows need %zu bytes of scratch, the static "
+                 "array holds %d (12 bytes x queries x train segments): split the queries or use orbfe_knn2_device",
+                 nq, nt, need, (int)ORBFE_KNN2_NOALLOC_SCRATCH_BYTES);
+        return fail(ORBFE_ERR_CAPACITY, msg);
+    }
+    CU(cudaSetDevice(device));
+    void* scratch;
+    {
+        std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        if (!g_noalloc_ptr[device]) {
+            void* p = nullptr;
+            const cudaError_t ce = cudaGetSymbolAddress(&p, g_knn2_noalloc_scratch);
+            if (ce != cudaSuccess || !p) return fail(ORBFE_ERR_CUDA, "cudaGetSymbolAddress(g_knn2_noalloc_scratch)", ce);
+            g_noalloc_ptr[device] = p;
+        }
+        scratch = g_noalloc_ptr[device];
+    }
+    launch_knn2_mma(d_query, nq, d_train, nt, th, ratio, d_out_idx, d_out_d1, d_out_d2, scratch, (cudaStream_t)cuda_stream);
+    CU(cudaGetLastError());
+    return ORBFE_OK;
+}
