@@ -3,22 +3,25 @@
 // match_knn.cu (inner loops of ORBmatcher::SearchByBoW, src/ORBmatcher.cc:233-269; distance =
 // ORBmatcher::DescriptorDistance, :1828-1844).
 //
-// A Hamming distance over 256 bits is a contraction:  d(a, b) = |a| + |b| - 2 <a, b>  with a, b in
-// {0,1}^256.  HBM carries the 32-byte rows; the bit -> byte expansion happens on the way into shared
-// memory, so the tensor core sees u8 operands (K = 256) in the canonical K-major SWIZZLE_128B layout:
+// A Hamming distance over 256 bits is a contraction: with the bits mapped to signed bytes, 0 -> +1 and 1 -> -1,
+//     <a', b'> = 256 - 2 d(a, b)
+// so the tensor core returns the distance itself (no |a|, |b| correction terms) and the nearest row is the largest
+// accumulator.  HBM carries the 32-byte rows; the bit -> byte expansion happens on the way into shared memory, so
+// the tensor core sees s8 operands (K = 256) in the canonical K-major SWIZZLE_128B layout:
 //
 //   CTA = 256 query rows (two M = 128 tiles: rows 0-127 and 128-255, expanded once) against one
 //   segment of the train set, streamed in tiles of 128 rows through a 3-stage shared-memory ring.
 //   warps 0-7   epilogue: warp w owns TMEM lanes 32 (w & 3) .. +31 of M tile (w >> 2), one query row per
-//               thread; tcgen05.ld brings 32 accumulator columns at a time, one IMAD turns an accumulator
-//               into the packed key  (|b| + 256 - 2 <a,b>) << 20 | train index  (the per-column constant
-//               (|b| + 256) << 20 | index comes from shared memory, written by the producers), and the
-//               exact strict-'<' best / second-best rule  k2' = min(k2, max(k1, key)), k1' = min(k1, key)
-//               runs only for groups of sixteen columns whose minimum beats the current second best
-//               (a key >= k2 changes nothing, so the filter is exact).
-//   warps 8-11  producers: one train row per thread and tile: two 16-byte loads, popcount, 64 expanded
-//               words written as sixteen conflict-free 16-byte stores at the swizzled chunk positions,
-//               fence.proxy.async, mbarrier arrive.
+//               thread; tcgen05.ld brings 32 accumulator columns at a time (the next load in flight while the
+//               current one is folded).  The common case is a max tree over the 32 accumulators and ONE compare
+//               against thr = 256 - 2 * (current second-best distance): columns arrive in ascending train index,
+//               so a later row changes (best, second best) iff its distance is STRICTLY below the second best —
+//               the screen is exact.  Only then the packed keys  d << 20 | train index  are formed and the
+//               strict-'<' rule  k2' = min(k2, max(k1, key)), k1' = min(k1, key)  runs on the 32 columns
+//               (about 2 ln n times per query over n random rows).
+//   warps 8-11  producers: one train row per thread and tile: two 16-byte loads, 64 expanded words written as
+//               sixteen conflict-free 16-byte stores at the swizzled chunk positions, fence.proxy.async,
+//               mbarrier arrive.
 //   warp 12     TMEM allocation (all 512 columns: two accumulator stages x two M tiles x 128 columns) and
 //               the MMA issue: per tile 2 x 8 tcgen05.mma (M 128, N 128, K 32) from one elected lane,
 //               tcgen05.commit onto the stage's "empty" barrier and the accumulator's "full" barrier.
@@ -26,6 +29,7 @@
 // Train sets are cut into segments (grid.y) of at most 2^20 rows — the key's index field — which also
 // gives small query sets enough CTAs; a merge kernel folds the per-segment (d1, d2, idx) in ascending
 // train order with the popc kernel's rule and applies TH_LOW and the ratio test.
+#include <climits>
 #include <cstdio>
 #include <mutex>
 
@@ -40,7 +44,6 @@ namespace {
 constexpr int MQ = 256;                 // query rows per CTA (two M = 128 tiles)
 constexpr int NT = 128;                 // train rows per tile
 constexpr int STAGES = 3;               // shared-memory ring of expanded train tiles
-constexpr int CCSLOTS = 8;              // ring of per-column constants (see the slot-reuse argument below)
 constexpr int EPI_WARPS = 8, PROD_WARPS = 4;
 constexpr int THREADS = (EPI_WARPS + PROD_WARPS + 1) * 32;
 constexpr uint32_t KEY_NONE = 0xFFFFFFFFu;
@@ -50,8 +53,7 @@ constexpr int KBLOCK_BYTES_B = NT * 128;   // one 128-byte K block of a train ti
 struct alignas(1024) MmaSmem {
     uint8_t a[2][KBLOCK_BYTES_A];                  // [K block][row][128 B], 8-row groups swizzled (64 KB)
     uint8_t b[STAGES][2][KBLOCK_BYTES_B];          // 3 x 32 KB
-    uint32_t cc[CCSLOTS][NT];                      // (|b| + 256) << 20 | index in segment, or KEY_NONE for padding rows
-    unsigned long long full_b[STAGES], empty_b[STAGES], acc_full[2], acc_empty[2], cc_full[CCSLOTS];
+    unsigned long long full_b[STAGES], empty_b[STAGES], acc_full[2], acc_empty[2];
     uint32_t tmem_base;
 };
 
@@ -76,8 +78,8 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
     return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) |
            ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
 }
-// instruction descriptor: u8 x u8 -> s32, A and B K-major, M = 128, N = NT
-constexpr uint32_t kIdesc = (2u << 4) | (0u << 7) | (0u << 10) | ((uint32_t)(NT >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+// instruction descriptor: s8 x s8 -> s32, A and B K-major, M = 128, N = NT
+constexpr uint32_t kIdesc = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(NT >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 
 __device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
@@ -88,8 +90,14 @@ __device__ __forceinline__ void umma_commit(unsigned long long* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-// four descriptor bits -> four bytes of 0 / 1 (bit i to byte i): the shifted copies of the nibble do not overlap
-__device__ __forceinline__ uint32_t expand4(uint32_t nibble) { return (nibble * 0x00204081u) & 0x01010101u; }
+// four descriptor bits -> four signed bytes, bit i to byte i: 0 -> +1 (0x01), 1 -> -1 (0xFF).  The multiply puts
+// bit i at bit 7 of byte i (the shifted copies of the nibble do not overlap), PRMT's sign-replicate mode turns every
+// byte into 0x00 / 0xFF from that bit alone, and the OR leaves 0x01 / 0xFF.
+__device__ __forceinline__ uint32_t expand4(uint32_t nibble) {
+    uint32_t r;
+    asm("prmt.b32 %0, %1, 0, 0xBA98;" : "=r"(r) : "r"(nibble * 0x10204080u));
+    return r | 0x01010101u;
+}
 
 // one 256-bit row -> 256 bytes at row r of a [2][rows][128] swizzled operand block; blockBytes = rows * 128
 __device__ __forceinline__ void expand_row(uint8_t* base, int blockBytes, int r, const uint32_t w[8]) {
@@ -113,10 +121,6 @@ __device__ __forceinline__ void load_row(const uint4* __restrict__ rows, long lo
     if (valid) { x = __ldg(&rows[2 * r]); y = __ldg(&rows[2 * r + 1]); }
     w[0] = x.x; w[1] = x.y; w[2] = x.z; w[3] = x.w; w[4] = y.x; w[5] = y.y; w[6] = y.z; w[7] = y.w;
 }
-__device__ __forceinline__ int popc_row(const uint32_t w[8]) {
-    return __popc(w[0]) + __popc(w[1]) + __popc(w[2]) + __popc(w[3]) + __popc(w[4]) + __popc(w[5]) + __popc(w[6]) + __popc(w[7]);
-}
-
 #define TMEM_LD32(taddr, v)                                                                                             \
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "                                                              \
                  "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];" \
@@ -126,37 +130,25 @@ __device__ __forceinline__ int popc_row(const uint32_t w[8]) {
                    "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])                      \
                  : "r"(taddr) : "memory")
 
-// 32 accumulators of one query -> packed keys, folded into (k1, k2).  A key >= k2 changes neither k1 nor k2, so
-// sixteen keys at a time are screened with a min tree (about two instructions per comparison) and the exact
-// strict-'<' update runs behind a real branch only when one of them beats the current second best — after the
-// first tiles that is rare (the expected number of updates over n random rows grows like 2 ln n).
-__device__ __forceinline__ void fold32(const uint32_t (&v)[32], const uint32_t* ccs, uint32_t& k1, uint32_t& k2) {
-    constexpr uint32_t NEG2 = 0u - (2u << 20);
-    const uint4* ccp = reinterpret_cast<const uint4*>(ccs);
+// 32 accumulators (256 - 2 d) of one query against train rows idx0 .. idx0 + 31 of the segment, folded into the
+// packed keys (k1, k2) = (best, second best); thr = 256 - 2 * (k2 >> 20).  `valid` < 32 only in a segment's last tile.
+__device__ __forceinline__ void fold32(const uint32_t (&v)[32], uint32_t idx0, int valid, uint32_t& k1, uint32_t& k2, int& thr) {
+    int m01 = max((int)v[0], (int)v[1]);
 #pragma unroll
-    for (int h = 0; h < 2; h++) {
-        uint32_t key[16];
+    for (int i = 2; i < 32; i += 2) m01 = max(m01, max((int)v[i], (int)v[i + 1]));
+    if (m01 > thr) {
+        constexpr uint32_t NEG = 0u - (1u << 19);                 // (256 - acc) << 19 == d << 20
+        const uint32_t c0 = (256u << 19) + idx0;
 #pragma unroll
-        for (int g = 0; g < 4; g++) {
-            const uint4 cc = ccp[4 * h + g];
-            key[4 * g] = v[16 * h + 4 * g] * NEG2 + cc.x;         key[4 * g + 1] = v[16 * h + 4 * g + 1] * NEG2 + cc.y;
-            key[4 * g + 2] = v[16 * h + 4 * g + 2] * NEG2 + cc.z; key[4 * g + 3] = v[16 * h + 4 * g + 3] * NEG2 + cc.w;
+        for (int i = 0; i < 32; i++) {
+            const uint32_t key = i < valid ? v[i] * NEG + (c0 + (uint32_t)i) : KEY_NONE;
+            k2 = min(k2, max(k1, key));
+            k1 = min(k1, key);
         }
-        uint32_t m = key[0];
-#pragma unroll
-        for (int i = 1; i < 16; i++) m = min(m, key[i]);
-        if (m < k2) {
-#pragma unroll
-            for (int i = 0; i < 16; i++) { k2 = min(k2, max(k1, key[i])); k1 = min(k1, key[i]); }
-        }
+        thr = 256 - 2 * (int)(k2 >> 20);
     }
 }
 
-// Slot reuse of the cc ring: the producers fill tile t only after the MMAs of tile t - STAGES completed
-// (empty_b), the MMAs of tile u are issued only after the epilogue released the accumulator of tile u - 2
-// (acc_empty), so when cc[t & 7] is rewritten the epilogue has finished tile t - STAGES - 2 >= t - 8 + 3:
-// the previous user of the slot (tile t - 8) is long done, and cc_full[slot] never runs two phases ahead
-// of a waiting epilogue warp.
 __global__ void __launch_bounds__(THREADS, 1)
 knn2_mma_kernel(const uint4* __restrict__ query, int nq, const uint4* __restrict__ train, int nt, int segLen,
                 int* __restrict__ part_idx, int* __restrict__ part_d1, int* __restrict__ part_d2) {
@@ -175,7 +167,6 @@ knn2_mma_kernel(const uint4* __restrict__ query, int nq, const uint4* __restrict
     if (tid == 0) {
         for (int i = 0; i < STAGES; i++) { mbar_init(&S.full_b[i], PROD_WARPS); mbar_init(&S.empty_b[i], 1); }
         for (int i = 0; i < 2; i++) { mbar_init(&S.acc_full[i], 1); mbar_init(&S.acc_empty[i], EPI_WARPS); }
-        for (int i = 0; i < CCSLOTS; i++) mbar_init(&S.cc_full[i], PROD_WARPS);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == EPI_WARPS + PROD_WARPS) {
@@ -183,11 +174,9 @@ knn2_mma_kernel(const uint4* __restrict__ query, int nq, const uint4* __restrict
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     // the query tile, expanded once: thread i < 256 owns row i
-    int pa = 0;
     if (tid < MQ) {
         uint32_t w[8];
         load_row(query, q0 + tid, q0 + tid < nq, w);
-        pa = popc_row(w);
         expand_row(&S.a[0][0], KBLOCK_BYTES_A, tid, w);
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -201,23 +190,27 @@ knn2_mma_kernel(const uint4* __restrict__ query, int nq, const uint4* __restrict
         const int mtile = warp >> 2;
         const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
         uint32_t k1 = KEY_NONE, k2 = KEY_NONE;
+        int thr = 256 - 2 * (int)(KEY_NONE >> 20);                 // below every accumulator: the first groups take the exact path
         for (int t = 0; t < ntiles; t++) {
-            const int a = t & 1, slot = t & (CCSLOTS - 1);
-            mbar_wait(&S.cc_full[slot], (t >> 3) & 1);
+            const int a = t & 1;
             mbar_wait(&S.acc_full[a], (t >> 1) & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t tbase = tmem + lane_base + (uint32_t)(a * 256 + mtile * 128);
-            // 32 columns per tcgen05.ld, the next load in flight while the current registers are folded
+            const uint32_t idx0 = (uint32_t)t * NT;
+            const int left = segn - (int)idx0;                       // valid columns of this tile (>= NT except in the last one)
+            if (left < NT) thr = INT_MIN;                            // padding columns must never win: exact path with masking
             uint32_t v0[32], v1[32];
             TMEM_LD32(tbase, v0);
 #pragma unroll
             for (int c = 0; c < NT; c += 64) {
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                 TMEM_LD32(tbase + c + 32, v1);
-                fold32(v0, &S.cc[slot][c], k1, k2);
+                fold32(v0, idx0 + c, left - c, k1, k2, thr);
+                if (left < NT) thr = INT_MIN;
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                 if (c + 64 < NT) TMEM_LD32(tbase + c + 64, v0);
-                fold32(v1, &S.cc[slot][c + 32], k1, k2);
+                fold32(v1, idx0 + c + 32, left - c - 32, k1, k2, thr);
+                if (left < NT) thr = INT_MIN;
             }
             // this warp's accumulator reads of stage a are complete (wait::ld above)
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -228,8 +221,8 @@ knn2_mma_kernel(const uint4* __restrict__ query, int nq, const uint4* __restrict
         if (q < nq) {
             const long long o = (long long)seg * nq + q;
             const bool h1 = k1 != KEY_NONE, h2 = k2 != KEY_NONE;
-            part_d1[o] = h1 ? (int)(k1 >> 20) - 256 + pa : 256;
-            part_d2[o] = h2 ? (int)(k2 >> 20) - 256 + pa : 256;
+            part_d1[o] = h1 ? (int)(k1 >> 20) : 256;
+            part_d2[o] = h2 ? (int)(k2 >> 20) : 256;
             part_idx[o] = h1 ? (int)(seg0 + (k1 & 0xFFFFFu)) : -1;
         }
     } else if (warp < EPI_WARPS + PROD_WARPS) {
@@ -238,16 +231,15 @@ knn2_mma_kernel(const uint4* __restrict__ query, int nq, const uint4* __restrict
         uint32_t w[8];
         load_row(train, seg0 + p, p < segn, w);
         for (int t = 0; t < ntiles; t++) {
-            const int s = t % STAGES, slot = t & (CCSLOTS - 1);
+            const int s = t % STAGES;
             const int r = t * NT + p;
             uint32_t wn[8];
             load_row(train, seg0 + r + NT, r + NT < segn, wn);          // next tile's row, in flight during the expansion
             mbar_wait(&S.empty_b[s], ((t / STAGES) & 1) ^ 1);
             expand_row(&S.b[s][0][0], KBLOCK_BYTES_B, p, w);
-            S.cc[slot][p] = r < segn ? ((uint32_t)(popc_row(w) + 256) << 20) | (uint32_t)r : KEY_NONE;
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
-            if (lane == 0) { mbar_arrive(&S.full_b[s]); mbar_arrive(&S.cc_full[slot]); }
+            if (lane == 0) mbar_arrive(&S.full_b[s]);
 #pragma unroll
             for (int i = 0; i < 8; i++) w[i] = wn[i];
         }
