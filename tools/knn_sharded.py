@@ -23,7 +23,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
-def run(nq, nt, engine="auto", steps=3, warmup=1, check=False, rank=None, world=None, local_rank=None):
+def run(nq, nt, engine="auto", steps=3, warmup=1, check=False, rank=None, world=None, local_rank=None, oracle_sub=4096):
     import torch
     import torch.distributed as dist
     import orb_slam2_annotate_b200 as orbfe
@@ -108,8 +108,7 @@ def run(nq, nt, engine="auto", steps=3, warmup=1, check=False, rank=None, world=
             if not (np.array_equal(o[0], idx) and np.array_equal(o[1], d1) and np.array_equal(o[2], d2)):
                 problems.append("sharded != single GPU")
             from oracle import oracle_py as O
-            sub = np.random.default_rng(3).choice(nq, min(4096, nq), replace=False)
-            t0 = time.perf_counter()
+            sub = np.random.default_rng(3).choice(nq, min(oracle_sub, nq), replace=False)
             oi, o1, o2 = O.knn2(query[sub], train, 50, 0.7)
             if not (np.array_equal(oi, idx[sub]) and np.array_equal(o1, d1[sub]) and np.array_equal(o2, d2[sub])):
                 problems.append("!= oracle on the subsample")
