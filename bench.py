@@ -432,6 +432,7 @@ def main():
     ap.add_argument("--impl", default="orbfe", choices=["orbfe", "reference"])
     ap.add_argument("--batch", type=int, default=1024)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-knn", action="store_true", help="profiling runs only: skip the configs[4] Hamming leg (the line then lacks it)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -577,8 +578,10 @@ def main():
     del d_frames
     torch.cuda.empty_cache()
     from tools.knn_sharded import run as knn_run
-    knn_line, knn_ok = knn_run(KNN_N, KNN_N, engine="auto", steps=3, warmup=1, check=True, oracle_sub=256,
+    knn_n = 8192 if args.no_knn else KNN_N
+    knn_line, knn_ok = knn_run(knn_n, knn_n, engine="auto", steps=3, warmup=1, check=True, oracle_sub=256,
                                rank=rank, world=world, local_rank=local_rank)
+    knn_line = knn_line or {"value": 0.0, "ms_per_step": 0.0, "gather_us": 0.0, "gather_bytes_total": 0, "parity": "other rank"}
     if not knn_ok:
         raise SystemExit("bench.py: sharded kNN results differ from the single-GPU / oracle results")
     # the integer-pipe engine north_star names, on one GPU's sample (131072 x 131072): its fraction of the popc pipe
