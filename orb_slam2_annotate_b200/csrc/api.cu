@@ -46,6 +46,11 @@ struct orbfe_extractor {
     cudaStream_t stream2 = nullptr, sideStream2 = nullptr;
     cudaEvent_t evPyr2 = nullptr, evBlur2 = nullptr;
     std::vector<cudaEvent_t> evUp, evDone;
+    // single-frame schedule: per pyramid level one branch for FAST + quadtree and one for the blur, forked off the
+    // pyramid chain as soon as the level exists and joined in front of the descriptor kernel
+    PinnedArray stageIn, stageOut;               // single-frame path: page-locked staging for pageable caller buffers
+    std::vector<cudaStream_t> lvStream;          // [2 * nlevels]
+    std::vector<cudaEvent_t> lvReady, lvDone;    // [nlevels], [2 * nlevels]
     // geometry of the current image size / batch capacity
     int geomW = 0, geomH = 0, geomBatchCap = 0;
     FrameSetGeom g;
@@ -442,6 +447,43 @@ static int enqueue_extract(orbfe_extractor* e, int frame0 = 0, int count = -1, i
     return 0;
 }
 
+// Small batches are bound by the latency of their dependent kernels, not by throughput: FAST, the quadtree and the
+// blur of level l only need level l, so they fork off the pyramid chain level by level (eight short parallel branches
+// instead of pyramid -> FAST -> quadtree in sequence) and join in front of the orientation / descriptor kernel.  Under
+// stream capture the branch streams become edges of the graph.
+static int enqueue_extract_forked(orbfe_extractor* e) {
+    const int L = e->g.nlevels;
+    if ((int)e->lvStream.size() < 2 * L) {
+        e->lvStream.resize(2 * L, nullptr); e->lvReady.resize(L, nullptr); e->lvDone.resize(2 * L, nullptr);
+        for (auto& st : e->lvStream) if (!st) CU(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        for (auto& ev : e->lvReady) if (!ev) CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        for (auto& ev : e->lvDone) if (!ev) CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    }
+    cudaStream_t st = e->stream;
+    int launches = 0;
+    e->g.frame0 = 0;
+    for (int l = 0; l < L; l++) {
+        if (l > 0) launches += launch_pyramid(e->g, e->d, st, l, l + 1);
+        CU(cudaEventRecord(e->lvReady[l], st));
+        cudaStream_t a = e->lvStream[2 * l], b = e->lvStream[2 * l + 1];
+        CU(cudaStreamWaitEvent(a, e->lvReady[l], 0));
+        launches += launch_fast(e->g, e->d, a, l, l + 1);
+        launches += launch_octree(e->g, e->d, a, l, l + 1);
+        CU(cudaEventRecord(e->lvDone[2 * l], a));
+        CU(cudaStreamWaitEvent(b, e->lvReady[l], 0));
+        launches += launch_blur(e->g, e->d, b, l, l + 1);
+        CU(cudaEventRecord(e->lvDone[2 * l + 1], b));
+    }
+    for (int i = 0; i < 2 * L; i++) CU(cudaStreamWaitEvent(st, e->lvDone[i], 0));
+    launches += launch_orient_desc(e->g, e->d, e->umax_d.p, st);
+    if (e->haveCam)
+        launches += launch_frame_epilogue(e->camGeom, e->d.kps, e->d.counts, e->g.outCap, 0, e->g.batch, e->kpsUn.p,
+                                          e->gridEnd.p, e->gridItems.p, st);
+    e->lastLaunches = launches;
+    CU(cudaGetLastError());
+    return 0;
+}
+
 // Everything the launchers pass to the kernels, byte for byte: the replay is valid exactly while this is unchanged.
 static void graph_key(const orbfe_extractor* e, std::vector<uint8_t>& key) {
     key.clear();
@@ -460,7 +502,10 @@ static void graph_key(const orbfe_extractor* e, std::vector<uint8_t>& key) {
 // per-function attributes), the second captures, later ones replay.
 static int enqueue_extract_small(orbfe_extractor* e) {
     static const bool off = std::getenv("ORBFE_NO_GRAPH") != nullptr;
-    if (off || e->profiling || e->graphRefused) return enqueue_extract(e);
+    static const bool nofork = std::getenv("ORBFE_NO_FORK") != nullptr;
+    auto enqueue = [&](orbfe_extractor* x) { return nofork ? enqueue_extract(x) : enqueue_extract_forked(x); };
+    if (e->profiling) return enqueue_extract(e);
+    if (off || e->graphRefused) return enqueue(e);
     std::vector<uint8_t> key;
     graph_key(e, key);
     if (e->graphExec && key == e->graphKey) {
@@ -471,23 +516,23 @@ static int enqueue_extract_small(orbfe_extractor* e) {
     if (e->graphExec) { cudaGraphExecDestroy(e->graphExec); e->graphExec = nullptr; }
     if (key != e->graphKey) {                        // first sight of this argument set: eager
         e->graphKey.swap(key);
-        return enqueue_extract(e);
+        return enqueue(e);
     }
     cudaGraph_t graph = nullptr;
     CU(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
-    const int rc = enqueue_extract(e);
+    const int rc = enqueue(e);
     const cudaError_t ce = cudaStreamEndCapture(e->stream, &graph);
     if (rc || ce != cudaSuccess || !graph) {
         if (graph) cudaGraphDestroy(graph);
         cudaGetLastError();
         e->graphKey.clear();
         e->graphRefused = true;
-        return rc ? rc : enqueue_extract(e);         // capture refused: stay eager
+        return rc ? rc : enqueue(e);         // capture refused: stay eager
     }
     e->graphLaunches = e->lastLaunches;
     const cudaError_t ci = cudaGraphInstantiate(&e->graphExec, graph, 0);
     cudaGraphDestroy(graph);
-    if (ci != cudaSuccess) { e->graphExec = nullptr; e->graphKey.clear(); e->graphRefused = true; cudaGetLastError(); return enqueue_extract(e); }
+    if (ci != cudaSuccess) { e->graphExec = nullptr; e->graphKey.clear(); e->graphRefused = true; cudaGetLastError(); return enqueue(e); }
     CU(cudaGraphLaunch(e->graphExec, e->stream));
     return 0;
 }
@@ -598,9 +643,13 @@ void orbfe_extractor_destroy(orbfe_extractor* e) {
     if (e->sideStream2) cudaStreamDestroy(e->sideStream2);
     if (e->evPyr2) cudaEventDestroy(e->evPyr2);
     if (e->evBlur2) cudaEventDestroy(e->evBlur2);
+    for (auto st : e->lvStream) if (st) cudaStreamDestroy(st);
+    for (auto ev : e->lvReady) if (ev) cudaEventDestroy(ev);
+    for (auto ev : e->lvDone) if (ev) cudaEventDestroy(ev);
     for (auto ev : e->evUp) cudaEventDestroy(ev);
     for (auto ev : e->evDone) cudaEventDestroy(ev);
     for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);
+    e->stageIn.release(); e->stageOut.release();
     e->pyr.release(); e->blur.release(); e->desc.release(); e->cellc.release(); e->selc.release();
     e->counts.release(); e->umax_d.release(); e->cellk.release(); e->sel.release();
     e->qt_xy.release(); e->qt_node.release(); e->kps.release(); e->kpsUn.release(); e->gridEnd.release(); e->gridItems.release(); e->xtab.release(); e->ytab.release(); e->xq.release(); e->celltab.release();
@@ -653,7 +702,7 @@ int orbfe_extract_batch_device(orbfe_extractor* e, const uint8_t* d_imgs, int ba
         return rc;
     }
     e->lastBatch = batch;
-    return enqueue_extract(e);
+    return batch <= 4 ? enqueue_extract_small(e) : enqueue_extract(e);
 }
 
 int orbfe_extractor_sync(orbfe_extractor* e) {
@@ -802,6 +851,56 @@ static int extract_batch_pipelined(orbfe_extractor* e, const uint8_t* imgs, int 
     return ORBFE_OK;
 }
 
+// Pageable caller memory (a cv::Mat, a std::vector, a numpy array) makes the driver stage every copy itself and
+// synchronise around it: measured 64 us of a 170 us single-frame call.  Small batches therefore go through the handle's
+// own page-locked buffers: one CPU memcpy in, one DMA each way, and only the valid result rows are copied out.
+static bool is_pageable(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return true; }
+    return a.type == cudaMemoryTypeUnregistered;
+}
+
+static int extract_small_staged(orbfe_extractor* e, const uint8_t* imgs, int batch, int w, int h, ptrdiff_t stride,
+                                ptrdiff_t frame_stride, orbfe_keypoint* kps, uint8_t* desc, int cap, int* counts) {
+    int rc;
+    const uint8_t* src = imgs;
+    ptrdiff_t sstride = stride, sframe = frame_stride;
+    if (is_pageable(imgs)) {
+        if ((rc = e->stageIn.ensure((size_t)batch * h * w))) return rc;
+        CU(cudaStreamSynchronize(e->stream));                      // the previous call's DMA out of the staging buffer
+        for (int b = 0; b < batch; b++) {
+            uint8_t* dst = e->stageIn.p + (size_t)b * h * w;
+            const uint8_t* from = imgs + b * frame_stride;
+            if (stride == w) std::memcpy(dst, from, (size_t)h * w);
+            else for (int y = 0; y < h; y++) std::memcpy(dst + (size_t)y * w, from + y * stride, w);
+        }
+        src = e->stageIn.p; sstride = w; sframe = (ptrdiff_t)h * w;
+    }
+    if ((rc = upload_level0(e, src, batch, w, h, sstride, sframe, cudaMemcpyHostToDevice))) return rc;
+    e->lastBatch = batch;
+    if ((rc = enqueue_extract_small(e))) return rc;
+    if (!is_pageable(kps) && !is_pageable(desc)) return orbfe_extractor_fetch(e, batch, kps, desc, cap, counts);
+    const int oc = e->g.outCap;
+    const size_t kb = sizeof(orbfe_keypoint);
+    const size_t need = 256 + (size_t)batch * oc * (kb + 32);
+    if ((rc = e->stageOut.ensure(need))) return rc;
+    int* h_counts = reinterpret_cast<int*>(e->stageOut.p);
+    orbfe_keypoint* h_kps = reinterpret_cast<orbfe_keypoint*>(e->stageOut.p + 256);
+    uint8_t* h_desc = e->stageOut.p + 256 + (size_t)batch * oc * kb;
+    CU(cudaMemcpyAsync(h_counts, e->d.counts, sizeof(int) * batch, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaMemcpyAsync(h_kps, e->d.kps, (size_t)batch * oc * kb, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaMemcpyAsync(h_desc, e->d.desc, (size_t)batch * oc * 32, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    for (int b = 0; b < batch; b++) {
+        const int n = h_counts[b];
+        counts[b] = n;
+        if (n > cap) return fail(ORBFE_ERR_CAPACITY, "keypoint capacity too small (see orbfe_extractor_max_keypoints)");
+        std::memcpy(kps + (size_t)b * cap, h_kps + (size_t)b * oc, (size_t)n * kb);
+        std::memcpy(desc + (size_t)b * cap * 32, h_desc + (size_t)b * oc * 32, (size_t)n * 32);
+    }
+    return ORBFE_OK;
+}
+
 int orbfe_extract_batch(orbfe_extractor* e, const uint8_t* imgs, int batch, int width, int height,
                         ptrdiff_t stride, ptrdiff_t frame_stride, orbfe_keypoint* kps,
                         uint8_t* desc, int cap, int* counts) {
@@ -816,9 +915,10 @@ int orbfe_extract_batch(orbfe_extractor* e, const uint8_t* imgs, int batch, int 
         e->lastBatch = batch;
         return extract_batch_pipelined(e, imgs, batch, width, height, stride, frame_stride, kps, desc, cap, counts, chunk);
     }
+    if (batch <= 4) return extract_small_staged(e, imgs, batch, width, height, stride, frame_stride, kps, desc, cap, counts);
     if ((rc = upload_level0(e, imgs, batch, width, height, stride, frame_stride, cudaMemcpyHostToDevice))) return rc;
     e->lastBatch = batch;
-    if ((rc = batch <= 4 ? enqueue_extract_small(e) : enqueue_extract(e))) return rc;
+    if ((rc = enqueue_extract(e))) return rc;
     return orbfe_extractor_fetch(e, batch, kps, desc, cap, counts);
 }
 

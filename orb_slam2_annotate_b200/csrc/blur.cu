@@ -131,13 +131,14 @@ __device__ void blur_tiny(const uint8_t* __restrict__ src, uint8_t* __restrict__
 
 __global__ void __launch_bounds__(BT, 8)
 blur_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ BlurTiles t,
-            const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur) {
+            const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur, int block0) {
+    const int bx = (int)blockIdx.x + block0;       // block0: first block of the launched level range
     int l = 0;
-    while (l + 1 < g.nlevels && (int)blockIdx.x >= t.base[l + 1]) l++;
+    while (l + 1 < g.nlevels && bx >= t.base[l + 1]) l++;
     const LevelGeom& L = g.lv[l];
     // tasks of a level: (band, word column), word column fastest
     const int nwc = (L.w + 3) >> 2, nbands = (L.h + RH - 1) / RH;
-    const int task = (blockIdx.x - t.base[l]) * BT + threadIdx.x;
+    const int task = (bx - t.base[l]) * BT + threadIdx.x;
     const bool active = task < nwc * nbands;
     // interior word columns (all three words inside the row) first, band-major, then the few
     // edge columns: warps are then either all-interior or all-edge (one mixed warp per level)
@@ -182,7 +183,7 @@ blur_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ Blur
 
 }  // namespace
 
-int launch_blur(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
+int launch_blur(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s, int l0, int l1) {
     BlurTiles t;
     int total = 0;
     for (int l = 0; l < g.nlevels; l++) {
@@ -191,7 +192,11 @@ int launch_blur(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
         total += (tasks + BT - 1) / BT;
     }
     t.base[g.nlevels] = total;
-    blur_kernel<<<dim3(total, g.batch), BT, 0, s>>>(g, t, d.pyr, d.blur);
+    if (l1 < 0 || l1 > g.nlevels) l1 = g.nlevels;
+    if (l0 < 0) l0 = 0;
+    const int nblk = t.base[l1] - t.base[l0];
+    if (nblk <= 0) return 0;
+    blur_kernel<<<dim3(nblk, g.batch), BT, 0, s>>>(g, t, d.pyr, d.blur, t.base[l0]);
     return 1;
 }
 

@@ -90,13 +90,13 @@ __device__ __forceinline__ int corner_strength(const uint8_t* p, int st, int t) 
 
 __global__ void __launch_bounds__(kThreads)
 fast_cells_kernel(const __grid_constant__ FrameSetGeom g, const uint8_t* __restrict__ pyr,
-                  int* __restrict__ cellc, uint32_t* __restrict__ cellk) {
+                  int* __restrict__ cellc, uint32_t* __restrict__ cellk, int cell0) {
     __shared__ uint8_t win[WIN][WIN + 8];
     __shared__ uint8_t sc[ZONE + 2][ZONE + 2 + 2];
     __shared__ int warp_cnt[kThreads / 32];
     __shared__ int s_total;
 
-    const int cell = blockIdx.x, frame = blockIdx.y + g.frame0;
+    const int cell = blockIdx.x + cell0, frame = blockIdx.y + g.frame0;
     int l = 0;
     while (l + 1 < g.nlevels && cell >= g.lv[l + 1].cellBase) l++;
     const LevelGeom& L = g.lv[l];
@@ -442,8 +442,10 @@ int fast_window_rows(const LevelGeom& L) {
     return side > kWarpWinMax ? 0 : side > 40 ? 48 : 40;
 }
 
-int launch_fast(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
+int launch_fast(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s, int l0, int l1) {
     int launches = 0;
+    if (l1 < 0 || l1 > g.nlevels) l1 = g.nlevels;
+    if (l0 < 0) l0 = 0;
     FastMaps maps;
     std::memcpy(&maps, d.fast_tmaps, sizeof(CUtensorMap) * g.nlevels);
     // runs of consecutive levels that share a kernel variant: 0 = generic, 40 / 48 = warp layouts
@@ -453,11 +455,12 @@ int launch_fast(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
         const int side = (g.lv[l].wCell > g.lv[l].hCell ? g.lv[l].wCell : g.lv[l].hCell) + 6;
         return side > kWarpWinMax ? 0 : side > 40 ? 48 : 40;
     };
-    for (int l = 0; l < g.nlevels;) {
+    auto cell_end = [&](int l) { return l < g.nlevels ? g.lv[l].cellBase : g.ncells; };
+    for (int l = l0; l < l1;) {
         const int v = variant(l);
         int e = l + 1;
-        while (e < g.nlevels && (variant(e) == v || variant(e) < 0)) e++;
-        const int lo = g.lv[l].cellBase, hi = e < g.nlevels ? g.lv[e].cellBase : g.ncells;
+        while (e < l1 && (variant(e) == v || variant(e) < 0)) e++;
+        const int lo = g.lv[l].cellBase, hi = cell_end(e);
         if (v == 0) generic = true;
         if (v > 0 && hi > lo) {
             const dim3 grid((hi - lo + kWarpsPerCta - 1) / kWarpsPerCta, g.batch);
@@ -470,8 +473,12 @@ int launch_fast(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
         l = e;
     }
     if (generic) {
-        fast_cells_kernel<<<dim3(g.ncells, g.batch), kThreads, 0, s>>>(g, d.pyr, d.cellc, d.cellk);
-        launches++;
+        // the generic kernel skips the cells the warp kernels took
+        const int lo = g.lv[l0].cellBase, hi = cell_end(l1);
+        if (hi > lo) {
+            fast_cells_kernel<<<dim3(hi - lo, g.batch), kThreads, 0, s>>>(g, d.pyr, d.cellc, d.cellk, lo);
+            launches++;
+        }
     }
     return launches;
 }

@@ -96,12 +96,12 @@ __device__ __forceinline__ int child_count(const int* c4) {
 }
 
 __global__ void __launch_bounds__(QT)
-octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ DevBufs d, int NC, int KP) {
+octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ DevBufs d, int NC, int KP, int level0) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ int wsum[QT / 32 + 1];
     __shared__ int s_n, s_cut, s_nexp;
 
-    const int l = blockIdx.x, frame = blockIdx.y + g.frame0;
+    const int l = blockIdx.x + level0, frame = blockIdx.y + g.frame0;
     const LevelGeom& L = g.lv[l];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int N = L.nFeat;
@@ -348,8 +348,11 @@ int octree_prepare(const FrameSetGeom& g) {
     return (int)cudaFuncSetAttribute(octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
 }
 
-int launch_octree(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
-    octree_kernel<<<dim3(g.nlevels, g.batch), QT, octree_smem_bytes(g), s>>>(g, d, node_capacity(g), key_capacity(g));
+int launch_octree(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s, int l0, int l1) {
+    if (l1 < 0 || l1 > g.nlevels) l1 = g.nlevels;
+    if (l0 < 0) l0 = 0;
+    if (l1 <= l0) return 0;
+    octree_kernel<<<dim3(l1 - l0, g.batch), QT, octree_smem_bytes(g), s>>>(g, d, node_capacity(g), key_capacity(g), l0);
     return 1;
 }
 

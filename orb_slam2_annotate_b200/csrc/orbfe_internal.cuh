@@ -95,11 +95,13 @@ __host__ __device__ inline int kp_y(uint32_t p) { return (int)((p >> 12) & 0xFFF
 __host__ __device__ inline int kp_score(uint32_t p) { return (int)(p >> 24); }
 
 // kernel launchers (each returns the number of kernel launches it enqueued)
-int launch_pyramid(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s);
-int launch_blur(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s);
+// [l0, l1) restricts a launcher to a range of pyramid levels (l1 < 0: up to the last level): the single-frame
+// schedule forks per level, so that FAST / quadtree / blur of level l start as soon as level l exists
+int launch_pyramid(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s, int l0 = 1, int l1 = -1);
+int launch_blur(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s, int l0 = 0, int l1 = -1);
 int fast_window_rows(const LevelGeom& L);
-int launch_fast(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s);
-int launch_octree(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s);
+int launch_fast(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s, int l0 = 0, int l1 = -1);
+int launch_octree(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s, int l0 = 0, int l1 = -1);
 int launch_orient_desc(const FrameSetGeom& g, const DevBufs& d, const int* d_umax, cudaStream_t s);
 size_t octree_smem_bytes(const FrameSetGeom& g);
 int octree_prepare(const FrameSetGeom& g);   // cudaFuncSetAttribute; returns 0 / cudaError

@@ -171,9 +171,10 @@ resize_level_q_kernel(const uint8_t* __restrict__ src_base, uint8_t* __restrict_
 
 }  // namespace
 
-int launch_pyramid(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s) {
+int launch_pyramid(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s, int l0, int l1) {
     int launches = 0;
-    for (int l = 1; l < g.nlevels; l++) {
+    if (l1 < 0 || l1 > g.nlevels) l1 = g.nlevels;
+    for (int l = l0 < 1 ? 1 : l0; l < l1; l++) {
         const LevelGeom& P = g.lv[l - 1];
         const LevelGeom& L = g.lv[l];
         dim3 block(128);
