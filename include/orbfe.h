@@ -10,7 +10,7 @@
  *   orbfe_extractor_create        ORBextractor::ORBextractor          src/ORBextractor.cc:415-486
  *   orbfe_extract / _batch        ORBextractor::operator()            src/ORBextractor.cc:1119-1197
  *                                 (called from Frame::ExtractORB      src/Frame.cc:272-278)
- *   orbfe_pyramid_level           public member mvImagePyramid        include/ORBextractor.h:86
+ *   orbfe_pyramid_level / _host   public member mvImagePyramid        include/ORBextractor.h:86
  *   orbfe_get_scale_tables        GetScaleFactors() & friends         include/ORBextractor.h:64-84
  *   orbfe_hamming256              ORBmatcher::DescriptorDistance      src/ORBmatcher.cc:1828-1844
  *   orbfe_knn2                    best/second-best loop + ratio test  src/ORBmatcher.cc:233-269
@@ -126,6 +126,14 @@ int orbfe_extractor_stage_times(orbfe_extractor* e, float* ms, int n);
  * 7x7 Gaussian-blurred working image instead (src/ORBextractor.cc:1169-1175). */
 int orbfe_pyramid_level(orbfe_extractor* e, int frame, int level, int blurred, uint8_t* dst,
                         ptrdiff_t dst_stride, int* width, int* height);
+
+/* All levels of frame `frame` of the last call in ONE device-to-host transfer group with a single synchronisation,
+ * into page-locked memory owned by the handle (include/ORBextractor.h:86: what Frame::ComputeStereoMatches reads,
+ * src/Frame.cc:519, :609-626).  levels[l] points at the first pixel of level l (rows stride[l] bytes apart, width[l] x
+ * height[l] pixels); the memory stays valid until the next call of this function on the handle — the same lifetime the
+ * reference's mvImagePyramid has, which the next operator() overwrites.  A cv::Mat header over it costs nothing. */
+int orbfe_pyramid_host(orbfe_extractor* e, int frame, const uint8_t** levels, int32_t* width, int32_t* height,
+                       ptrdiff_t* stride);
 /* raw per-level FAST corners of frame `frame` (before the quadtree), reference order
  * (cell row, cell col, y, x); triplets (x, y, score) relative to minBorder. *n = count.
  * Test tap for stage-by-stage parity. */

@@ -81,32 +81,30 @@ public:
         if (_image.empty()) return;                                        // :1122-1123
         cv::Mat image = _image.getMat();
         const int cap = orbfe_extractor_max_keypoints(mpHandle) + 4096;
-        mKpBuf.resize(cap); mDescBuf.resize((size_t)cap * 32);
+        // cv::KeyPoint and orbfe_keypoint are the same 28 bytes: the library writes straight into the caller's vector
+        static_assert(sizeof(cv::KeyPoint) == sizeof(orbfe_keypoint), "cv::KeyPoint layout");
+        _keypoints.resize(cap);
+        mDescBuf.resize((size_t)cap * 32);
         int n = 0;
         orbfe_detail::check(orbfe_extract(mpHandle, image.data, image.cols, image.rows, (ptrdiff_t)(size_t)image.step,
-                                          mKpBuf.data(), mDescBuf.data(), cap, &n), "orbfe_extract");
-        _keypoints.clear();
+                                          reinterpret_cast<orbfe_keypoint*>(_keypoints.data()), mDescBuf.data(), cap, &n),
+                            "orbfe_extract");
+        _keypoints.resize(n);
         if (n == 0) {
             _descriptors.release();                                        // :1145-1146
         } else {
             _descriptors.create(n, 32, CV_8U);                             // :1149
             cv::Mat descriptors = _descriptors.getMat();
-            _keypoints.reserve(n);
-            for (int i = 0; i < n; i++) {
-                const orbfe_keypoint& k = mKpBuf[i];
-                _keypoints.push_back(cv::KeyPoint(k.x, k.y, k.size, k.angle, k.response, k.octave, k.class_id));
-                std::memcpy(descriptors.ptr(i), &mDescBuf[(size_t)i * 32], 32);
-            }
+            if ((size_t)descriptors.step == 32) std::memcpy(descriptors.data, mDescBuf.data(), (size_t)n * 32);
+            else for (int i = 0; i < n; i++) std::memcpy(descriptors.ptr(i), &mDescBuf[(size_t)i * 32], 32);
         }
         if (mbDownloadPyramid) {
-            for (int l = 0; l < nlevels; l++) {
-                int w = 0, h = 0;
-                orbfe_pyramid_level(mpHandle, 0, l, 0, nullptr, 0, &w, &h);
-                mvImagePyramid[l].create(h, w, CV_8UC1);
-                orbfe_detail::check(orbfe_pyramid_level(mpHandle, 0, l, 0, mvImagePyramid[l].data,
-                                                        (ptrdiff_t)(size_t)mvImagePyramid[l].step, &w, &h),
-                                    "orbfe_pyramid_level");
-            }
+            // one transfer group + one synchronisation into the handle's page-locked buffer; the headers alias it
+            // (valid until the next call, like the reference's pyramid, which the next operator() overwrites)
+            const uint8_t* lv[16]; int32_t w[16], h[16]; ptrdiff_t st[16];
+            orbfe_detail::check(orbfe_pyramid_host(mpHandle, 0, lv, w, h, st), "orbfe_pyramid_host");
+            for (int l = 0; l < nlevels; l++)
+                mvImagePyramid[l] = cv::Mat(h[l], w[l], CV_8UC1, const_cast<uint8_t*>(lv[l]), (size_t)st[l]);
         }
     }
 
@@ -127,7 +125,6 @@ protected:
     int nlevels;
     bool mbDownloadPyramid;
     std::vector<float> mvScaleFactor, mvInvScaleFactor, mvLevelSigma2, mvInvLevelSigma2;
-    std::vector<orbfe_keypoint> mKpBuf;
     std::vector<uint8_t> mDescBuf;
 };
 

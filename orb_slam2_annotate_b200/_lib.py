@@ -120,6 +120,7 @@ SIGNATURES = {
     "orbfe_extractor_set_profiling": (_i, [_vp, _i]),
     "orbfe_extractor_stage_times": (_i, [_vp, _vp, _i]),
     "orbfe_pyramid_level": (_i, [_vp, _i, _i, _i, _vp, _ss, _ip, _ip]),
+    "orbfe_pyramid_host": (_i, [_vp, _i, _vp, _vp, _vp, _vp]),
     "orbfe_level_raw_keypoints": (_i, [_vp, _i, _i, _vp, _i, _ip]),
     "orbfe_hamming256": (_i, [_vp, _vp]),
     "orbfe_matcher_create": (_i, [_i, C.POINTER(_vp)]),

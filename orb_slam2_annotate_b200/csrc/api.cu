@@ -49,6 +49,7 @@ struct orbfe_extractor {
     // single-frame schedule: per pyramid level one branch for FAST + quadtree and one for the blur, forked off the
     // pyramid chain as soon as the level exists and joined in front of the descriptor kernel
     PinnedArray stageIn, stageOut;               // single-frame path: page-locked staging for pageable caller buffers
+    PinnedArray stagePyr;                        // orbfe_pyramid_host
     std::vector<cudaStream_t> lvStream;          // [2 * nlevels]
     std::vector<cudaEvent_t> lvReady, lvDone;    // [nlevels], [2 * nlevels]
     // geometry of the current image size / batch capacity
@@ -649,7 +650,7 @@ void orbfe_extractor_destroy(orbfe_extractor* e) {
     for (auto ev : e->evUp) cudaEventDestroy(ev);
     for (auto ev : e->evDone) cudaEventDestroy(ev);
     for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);
-    e->stageIn.release(); e->stageOut.release();
+    e->stageIn.release(); e->stageOut.release(); e->stagePyr.release();
     e->pyr.release(); e->blur.release(); e->desc.release(); e->cellc.release(); e->selc.release();
     e->counts.release(); e->umax_d.release(); e->cellk.release(); e->sel.release();
     e->qt_xy.release(); e->qt_node.release(); e->kps.release(); e->kpsUn.release(); e->gridEnd.release(); e->gridItems.release(); e->xtab.release(); e->ytab.release(); e->xq.release(); e->celltab.release();
@@ -1020,6 +1021,31 @@ int orbfe_pyramid_level(orbfe_extractor* e, int frame, int level, int blurred, u
     CU(cudaSetDevice(e->device));
     const uint8_t* src = (blurred ? e->d.blur + L.blurOff : e->d.pyr + L.pyrOff) + (long long)frame * L.lvBytes;
     CU(cudaMemcpy2DAsync(dst, dst_stride, src, L.pitch, L.w, L.h, cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    return ORBFE_OK;
+}
+
+int orbfe_pyramid_host(orbfe_extractor* e, int frame, const uint8_t** levels, int32_t* width, int32_t* height,
+                       ptrdiff_t* stride) {
+    if (!e || !e->geomW || !levels || frame < 0 || frame >= e->lastBatch)
+        return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_pyramid_host");
+    CU(cudaSetDevice(e->device));
+    size_t total = 0;
+    for (int l = 0; l < e->nlevels; l++) total += ((size_t)e->g.lv[l].lvBytes + 255) & ~size_t(255);
+    int rc = e->stagePyr.ensure(total);
+    if (rc) return rc;
+    size_t off = 0;
+    for (int l = 0; l < e->nlevels; l++) {
+        const LevelGeom& L = e->g.lv[l];
+        // a level of one frame is contiguous on the device (rows at the level's pitch): one flat copy per level
+        CU(cudaMemcpyAsync(e->stagePyr.p + off, e->d.pyr + L.pyrOff + (long long)frame * L.lvBytes, (size_t)L.lvBytes,
+                           cudaMemcpyDeviceToHost, e->stream));
+        levels[l] = e->stagePyr.p + off;
+        if (width) width[l] = L.w;
+        if (height) height[l] = L.h;
+        if (stride) stride[l] = L.pitch;
+        off += ((size_t)L.lvBytes + 255) & ~size_t(255);
+    }
     CU(cudaStreamSynchronize(e->stream));
     return ORBFE_OK;
 }
