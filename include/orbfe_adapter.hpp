@@ -731,10 +731,11 @@ protected:
     }
     // the Frame fields the searches read: mvKeysUn, mDescriptors, mnMinX.., mvScaleFactors
     template <class FrameT>
-    static orbfe_frame_view View(FrameT& F, std::vector<orbfe_keypoint>& k, std::vector<uint8_t>& /*d*/) {
-        k.resize(F.mvKeysUn.size());
-        for (size_t i = 0; i < k.size(); i++) k[i] = Kp(F.mvKeysUn[i]);
-        orbfe_frame_view v = {(int)k.size(), k.data(), F.mDescriptors.data, nullptr, FrameT::mnMinX, FrameT::mnMaxX,
+    static orbfe_frame_view View(FrameT& F, std::vector<orbfe_keypoint>& /*k*/, std::vector<uint8_t>& /*d*/) {
+        // cv::KeyPoint and orbfe_keypoint are the same 28 bytes: the view points into the frame's own vector
+        static_assert(sizeof(F.mvKeysUn[0]) == sizeof(orbfe_keypoint), "cv::KeyPoint layout");
+        orbfe_frame_view v = {(int)F.mvKeysUn.size(), reinterpret_cast<const orbfe_keypoint*>(F.mvKeysUn.data()), F.mDescriptors.data,
+                              nullptr, FrameT::mnMinX, FrameT::mnMaxX,
                               FrameT::mnMinY, FrameT::mnMaxY, F.mvScaleFactors.data(), (int)F.mvScaleFactors.size()};
         return v;
     }

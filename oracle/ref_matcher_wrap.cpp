@@ -43,6 +43,8 @@
 #define ORBFE_MATCHER_CLASS ORBmatcherFE
 #include "orbfe_adapter.hpp"
 #endif
+#include <chrono>
+static double g_last_call_ms = 0.0;
 
 using namespace ORB_SLAM2;
 
@@ -216,10 +218,15 @@ int orm_search_for_initialization(const orc_frame_view* f1, const orc_frame_view
     for (int i = 0; i < f1->n; i++) prev[i] = cv::Point2f(prev_matched[2 * i], prev_matched[2 * i + 1]);
     std::vector<int> m12;
     ORBmatcher matcher(nnratio, check_ori != 0);
+    const auto t0 = std::chrono::steady_clock::now();
     const int n = matcher.SearchForInitialization(*F1, *F2, prev, m12, window);
+    g_last_call_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     for (int i = 0; i < f1->n; i++) { matches12[i] = m12[i]; prev_matched[2 * i] = prev[i].x; prev_matched[2 * i + 1] = prev[i].y; }
     return n;
 }
+
+/* duration of the reference call itself inside the last wrapper above (without building the Frame objects around it) */
+double orm_last_call_ms(void) { return g_last_call_ms; }
 
 /* ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th) — src/ORBmatcher.cc:51-138 */
 int orm_search_by_projection(const orc_frame_view* f, const orc_mappoints_view* mps, float th, float nnratio,
