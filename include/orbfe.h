@@ -239,6 +239,11 @@ int orbfe_knn2_device(orbfe_matcher* m, const uint8_t* d_query, int nq, const ui
                       int nt, int th, float ratio, int32_t* d_out_idx, int32_t* d_out_d1,
                       int32_t* d_out_d2);
 
+/* Results of the device-resident entry points (orbfe_knn2_device, orbfe_search_init_consecutive_device, ...) to HOST
+ * memory: an asynchronous copy of `bytes` bytes on the matcher's stream, ordered behind the searches enqueued before it;
+ * orbfe_matcher_sync makes it visible.  Page-locked `dst` (orbfe_host_alloc) keeps it asynchronous. */
+int orbfe_matcher_fetch(orbfe_matcher* m, void* dst, const void* d_src, size_t bytes);
+
 /* Which engine serves orbfe_knn2 / _device / _sharded.  ORBFE_KNN_POPC: 8 x (XOR + POPC) per comparison on
  * the integer pipe, the reference's own form (src/ORBmatcher.cc:1835-1841).  ORBFE_KNN_MMA: the distance as a
  * contraction, d = |a| + |b| - 2<a,b> over bits expanded to bytes in shared memory, on the tensor cores

@@ -129,6 +129,7 @@ SIGNATURES = {
     "orbfe_matcher_sync": (_i, [_vp]),
     "orbfe_knn2": (_i, [_vp, _vp, _i, _vp, _i, _i, _f, _vp, _vp, _vp]),
     "orbfe_knn2_device": (_i, [_vp, _vp, _i, _vp, _i, _i, _f, _vp, _vp, _vp]),
+    "orbfe_matcher_fetch": (_i, [_vp, _vp, _vp, C.c_size_t]),
     "orbfe_matcher_set_knn_engine": (_i, [_vp, _i]),
     "orbfe_knn2_device_noalloc": (_i, [_i, _vp, _vp, _i, _vp, _i, _i, _f, _vp, _vp, _vp]),
     "orbfe_comm_unique_id": (_i, [_vp]),

@@ -91,6 +91,14 @@ void orbfe_matcher_destroy(orbfe_matcher* m) {
     delete m;
 }
 
+int orbfe_matcher_fetch(orbfe_matcher* m, void* dst, const void* d_src, size_t bytes) {
+    if (!m || (bytes && (!dst || !d_src))) return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_matcher_fetch");
+    if (!bytes) return ORBFE_OK;
+    CU(cudaSetDevice(m->device));
+    CU(cudaMemcpyAsync(dst, d_src, bytes, cudaMemcpyDeviceToHost, m->stream));
+    return ORBFE_OK;
+}
+
 int orbfe_matcher_set_knn_engine(orbfe_matcher* m, int engine) {
     if (!m || engine < ORBFE_KNN_AUTO || engine > ORBFE_KNN_MMA) return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_matcher_set_knn_engine");
     m->knnEngine = engine;

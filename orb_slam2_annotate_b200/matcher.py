@@ -243,6 +243,10 @@ class ORBmatcher:
         check(self._L.orbfe_knn2_device(self._h, q_ptr, m, t_ptr, n, th, ratio, idx_ptr, d1_ptr, d2_ptr),
               "orbfe_knn2_device")
 
+    def fetch(self, dst_ptr: int, src_dev_ptr: int, nbytes: int) -> None:
+        """Asynchronous device-to-host copy on the matcher's stream (orbfe_matcher_fetch); sync() makes it visible."""
+        check(self._L.orbfe_matcher_fetch(self._h, dst_ptr, src_dev_ptr, nbytes), "orbfe_matcher_fetch")
+
     KNN_ENGINES = {"auto": 0, "popc": 1, "mma": 2}
 
     def set_knn_engine(self, engine: str) -> None:
