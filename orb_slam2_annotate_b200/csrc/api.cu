@@ -66,6 +66,7 @@ struct orbfe_extractor {
     DevArray<int4> celltab;
     std::vector<CUtensorMap> tmaps;   // {level, blurred level} descriptors, passed to the kernel by value
     std::vector<CUtensorMap> fastMaps; // level descriptors with the FAST window box
+    std::vector<CUtensorMap> fastMaps48; // the same with a 48-byte box (windows that fit skip the re-layout)
     int lastBatch = 0, lastLaunches = 0;
     int level0MapFrames = 0;       // frames the level-0 tensor maps cover (the batch capacity, or an alias's frame count)
     // Frame epilogue (orbfe_extractor_set_camera): mvKeysUn + mGrid of every frame of a batch
@@ -357,8 +358,20 @@ static int ensure_geometry(orbfe_extractor* e, int w, int h, int batch) {
                     if (maxX > L.maxBX) maxX = L.maxBX;
                     int ww = maxX - iniX, wh = maxY - iniY;
                     if (iniY >= L.maxBY - 3 || iniX >= L.maxBX - 6 || ww < 7 || wh < 7) ww = wh = 0;
+                    // what the warp kernel's prologue would otherwise derive per cell (fast.cu): whether the window fits
+                    // a 48-byte TMA box (40-row layout only), and the multiply-shift constant of its lane -> (row, word
+                    // column) mapping, 65536 / nzc + 1 with nzc = word columns of the zone
+                    const int rowsK = fast_window_rows(L);
+                    const bool direct = rowsK == 40 && ww > 0 && (iniX & 15) + ww <= 48;
+                    const int ax0 = rowsK == 40 && !direct ? iniX & ~3 : iniX & ~15;
+                    const int zx0 = iniX + 3 - ax0, zx1 = iniX + ww - 3 - ax0;
+                    const int nzc = ww > 0 ? ((zx1 - 1) >> 2) - (zx0 >> 2) + 1 : 1;
+                    const unsigned mdiv = 65536u / (unsigned)nzc + 1u;
+                    for (int a = 0; a <= 32; a++)
+                        if ((int)((a * mdiv) >> 16) != a / nzc) return fail(ORBFE_ERR_ARG, "internal: FAST lane-mapping constant is not exact");
                     ct[L.cellBase + ci * L.nCols + cj] =
-                        make_int4(iniX | (iniY << 16), ww | (wh << 16), (cj * L.wCell) | ((ci * L.hCell) << 16), l);
+                        make_int4(iniX | (iniY << 16), ww | (wh << 16), (cj * L.wCell) | ((ci * L.hCell) << 16),
+                                  l | (direct ? 16 : 0) | (int)(mdiv << 8));
                 }
         }
         if ((rc = e->celltab.ensure(ct.size()))) return rc;
@@ -370,10 +383,12 @@ static int ensure_geometry(orbfe_extractor* e, int w, int h, int batch) {
         std::vector<CUtensorMap>& maps = e->tmaps;
         maps.resize(2 * e->nlevels);
         e->fastMaps.resize(e->nlevels);
+        e->fastMaps48.resize(e->nlevels);
         for (int l = 0; l < e->nlevels; l++) {
             const LevelGeom& L = g.lv[l];
             const int rows = fast_window_rows(L);
             if ((rc = encode_level_map(&e->fastMaps[l], e->pyr.p + L.pyrOff, L.pitch, (long long)L.h * cap, 64, rows ? rows : 40))) return rc;
+            if ((rc = encode_level_map(&e->fastMaps48[l], e->pyr.p + L.pyrOff, L.pitch, (long long)L.h * cap, 48, rows ? rows : 40))) return rc;
         }
         for (int l = 0; l < e->nlevels; l++) {
             const LevelGeom& L = g.lv[l];
@@ -385,6 +400,7 @@ static int ensure_geometry(orbfe_extractor* e, int w, int h, int batch) {
     std::memset(&d, 0, sizeof(d));
     d.tmaps = e->tmaps.data();
     d.fast_tmaps = e->fastMaps.data();
+    d.fast_tmaps48 = e->fastMaps48.data();
     d.celltab = e->celltab.p;
     d.pyr = e->pyr.p; d.blur = e->blur.p; d.cellc = e->cellc.p; d.cellk = e->cellk.p;
     d.sel = e->sel.p; d.selc = e->selc.p; d.kps = e->kps.p; d.desc = e->desc.p;
@@ -491,6 +507,7 @@ static void graph_key(const orbfe_extractor* e, std::vector<uint8_t>& key) {
     auto put = [&](const void* p, size_t n) { const uint8_t* b = (const uint8_t*)p; key.insert(key.end(), b, b + n); };
     put(&e->g, sizeof(e->g)); put(&e->d, sizeof(e->d));
     put(e->tmaps.data(), e->tmaps.size() * sizeof(CUtensorMap)); put(e->fastMaps.data(), e->fastMaps.size() * sizeof(CUtensorMap));
+    put(e->fastMaps48.data(), e->fastMaps48.size() * sizeof(CUtensorMap));
     const void* ptrs[4] = {e->umax_d.p, e->kpsUn.p, e->gridEnd.p, e->gridItems.p};
     put(ptrs, sizeof(ptrs));
     const int cam = e->haveCam ? 1 : 0;
@@ -554,7 +571,8 @@ static int set_level0_source(orbfe_extractor* e, const uint8_t* alias, int alias
     int rc = encode_level_map(&e->tmaps[0], (void*)want, L0.pitch, (long long)L0.h * frames, kTmaRawW, kTmaRawH);
     if (rc) return rc;
     const int rows = fast_window_rows(L0);
-    return encode_level_map(&e->fastMaps[0], (void*)want, L0.pitch, (long long)L0.h * frames, 64, rows ? rows : 40);
+    if ((rc = encode_level_map(&e->fastMaps[0], (void*)want, L0.pitch, (long long)L0.h * frames, 64, rows ? rows : 40))) return rc;
+    return encode_level_map(&e->fastMaps48[0], (void*)want, L0.pitch, (long long)L0.h * frames, 48, rows ? rows : 40);
 }
 
 // copy `batch` frames into level 0 of the pyramid (kind: H2D or D2D)

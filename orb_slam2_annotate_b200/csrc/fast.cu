@@ -189,7 +189,9 @@ constexpr int kWarpsPerCta = 4;
 
 template <int WWIN_> struct S_sc_t { uint8_t b[WWIN_ - 4][WWIN_]; };
 // TMA descriptors of the levels (box 64 x window rows), passed by value
-struct alignas(64) FastMaps { CUtensorMap m[kMaxLevels]; };
+// m: box 64 x window rows; m48: box 48 x window rows — a 48-byte box row is exactly the 12-word pitch the stages read,
+// so a cell whose window fits it ((iniX & 15) + width <= 48) lands in place and skips the re-layout
+struct alignas(64) FastMaps { CUtensorMap m[kMaxLevels]; CUtensorMap m48[kMaxLevels]; };
 template <int WWIN_>
 struct alignas(128) WarpSmem {
     static constexpr int WWIN = WWIN_;                    // max window side
@@ -218,6 +220,8 @@ __device__ __forceinline__ uint32_t swar_gt_t(uint32_t d, uint32_t c) {
     return (SMALL_T ? (m | d) : (m & d)) & 0x80808080u;
 }
 
+template <int WWIN_> struct RELAY_OF { static constexpr bool value = WarpSmem<WWIN_>::RELAY; };
+
 template <int WWIN, bool SMALL_T>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, WWIN <= 40 ? 9 : 1)
 fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ FastMaps maps,
@@ -232,7 +236,9 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const __grid_cons
     if (cell >= cellHi) return;
     // host-built cell record: window origin / size, zone offset, level (api.cu: build_geometry)
     const int4 cd = __ldg(&celltab[cell]);
-    const int l = cd.w;
+    const int l = cd.w & 15;
+    const bool direct = RELAY_OF<WWIN>::value && (cd.w & 16);        // host: the window fits a 48-byte TMA box
+    const uint32_t mdiv = (uint32_t)cd.w >> 8;                       // host: 65536 / nzc + 1
     const LevelGeom& L = g.lv[l];
     const int c = cell - L.cellBase;
     int* out_cnt = cellc + (long long)frame * g.ncells + cell;
@@ -251,26 +257,27 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const __grid_cons
     // (r, x) below is relative to ax0: that boundary, or after the re-layout the 4-byte boundary left of the cell.
     constexpr bool RELAY = Smem::RELAY;
     const int tx0 = iniX & ~15;
-    const int ax0 = RELAY ? iniX & ~3 : tx0;
+    const int ax0 = RELAY && !direct ? iniX & ~3 : tx0;
     const uint32_t barA = (uint32_t)__cvta_generic_to_shared(&S.bar);
     if (lane == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(barA) : "memory");
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(barA), "r"(WWIN * 64) : "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(barA), "r"(WWIN * (direct ? 48 : 64)) : "memory");
         asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                     ::"r"((uint32_t)__cvta_generic_to_shared(RELAY ? &S.land[0][0] : &S.win[0][0])),
-                       "l"(reinterpret_cast<uint64_t>(&maps.m[l])), "r"(tx0), "r"(frame * L.h + iniY), "r"(barA) : "memory");
+                     ::"r"((uint32_t)__cvta_generic_to_shared(RELAY && !direct ? &S.land[0][0] : &S.win[0][0])),
+                       "l"(reinterpret_cast<uint64_t>(direct ? &maps.m48[l] : &maps.m[l])), "r"(tx0), "r"(frame * L.h + iniY), "r"(barA) : "memory");
     }
     const int zx0 = iniX + 3 - ax0, zx1 = maxX - 3 - ax0;   // zone columns in window bytes
     const int zc0 = zx0 >> 2, nzc = ((zx1 - 1) >> 2) - zc0 + 1;
-    const float rcp_nzc = __frcp_rn((float)nzc);
+    // floor(a / nzc) for 0 <= a <= 32 and 1 <= nzc <= 16 is (a * mdiv) >> 16 with mdiv = 65536 / nzc + 1 from the host's
+    // cell record (checked exhaustively there): no float reciprocal in the per-cell prologue
     const uint8_t* wb = reinterpret_cast<const uint8_t*>(&S.win[0][0]);       // byte (r, x) = wb[r*WS*4 + x]
 
     // stage 1a lane mapping: a lane keeps one zone word column and walks the rows rpi at a time
     // (3 rows per step whenever they fit: the ring offset is 3 too, so a lane's centre row becomes
     // its upper row one step later and one new word per step feeds both comparisons)
-    const int rpi = nzc <= 10 ? 3 : small_div(32, rcp_nzc);      // zone rows per warp step (nzc <= 12)
-    const int rsub = small_div(lane, rcp_nzc), cc1 = lane - rsub * nzc;
+    const int rpi = nzc <= 10 ? 3 : (int)((32u * mdiv) >> 16);   // zone rows per warp step (nzc <= 12)
+    const int rsub = (int)(((uint32_t)lane * mdiv) >> 16), cc1 = lane - rsub * nzc;
     const bool act = rsub < rpi;
     const uint32_t* wcol = &S.win[act ? rsub : 0][zc0 + cc1];    // idle lanes stay inside the block (their loads are unconditional)
     uint32_t zm = 0x80808080u;                                   // bytes of the lane's word inside the zone
@@ -288,7 +295,7 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const __grid_cons
                          : "=r"(done) : "r"(barA), "r"(0) : "memory");
     }
 
-    if (RELAY) {
+    if (RELAY && !direct) {
         // two window rows per step: lanes 0-11 copy the 12 words of row r, lanes 12-23 those of row r+1 (conflict free
         // on both sides); the source starts at the word that holds column ax0
         const int half = lane >= 12 ? 1 : 0, cw = lane - 12 * half;
@@ -314,20 +321,29 @@ fast_cells_warp_kernel(const __grid_constant__ FrameSetGeom g, const __grid_cons
         int ntask = 0;
         if (rpi == 3) {
             // loads are unconditional (rows past the zone and the idle lanes read other parts of this warp's shared
-            // block and are masked out), so the loop body has no divergent branch
+            // block and are masked out), so the loop body has no divergent branch.  Steps whose three rows all lie in
+            // the zone need no row test; at most one tail step does.
             uint32_t ce = wcol[3 * WS];
             uint32_t g_up = swar_gt(__vabsdiffu4(wcol[0], ce), cmpc, small_t);
             const uint32_t zma = act ? zm : 0u;
-            const uint32_t tag = (uint32_t)rsub | ((uint32_t)cc1 << 8);
-            for (int r0 = 0; r0 < zh; r0 += 3) {
-                const uint32_t dn = wcol[(r0 + 6) * WS];
+            uint32_t tagr = (uint32_t)rsub | ((uint32_t)cc1 << 8);          // tag + r0 of the current step
+            const uint32_t lt = (1u << lane) - 1u;
+            uint32_t* tp = tasks;                                            // tasks + ntask
+            const uint32_t* wp = wcol + 6 * WS;                              // (r0 + 6) * WS
+            auto step1a = [&](uint32_t rowmask) {
+                const uint32_t dn = *wp;
                 const uint32_t g_dn = swar_gt(__vabsdiffu4(dn, ce), cmpc, small_t);
-                const uint32_t gmask = (g_up | g_dn) & (r0 + rsub < zh ? zma : 0u);
+                const uint32_t gmask = (g_up | g_dn) & rowmask;
                 ce = dn; g_up = g_dn;                            // |centre - below| is |above - centre| of the next step
                 const uint32_t bal = __ballot_sync(0xFFFFFFFFu, gmask != 0);
-                if (gmask) tasks[ntask + __popc(bal & ((1u << lane) - 1u))] = gmask | (tag + (uint32_t)r0);
-                ntask += __popc(bal);
-            }
+                if (gmask) tp[__popc(bal & lt)] = gmask | tagr;
+                tp += __popc(bal);
+                tagr += 3; wp += 3 * WS;
+            };
+            int r0 = 0;
+            for (; r0 + 3 <= zh; r0 += 3) step1a(zma);
+            if (r0 < zh) step1a(r0 + rsub < zh ? zma : 0u);
+            ntask = (int)(tp - tasks);
         } else {
             for (int r0 = 0; r0 < zh; r0 += rpi) {
                 const int r = r0 + rsub;
@@ -447,7 +463,8 @@ int launch_fast(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s, int l0,
     if (l1 < 0 || l1 > g.nlevels) l1 = g.nlevels;
     if (l0 < 0) l0 = 0;
     FastMaps maps;
-    std::memcpy(&maps, d.fast_tmaps, sizeof(CUtensorMap) * g.nlevels);
+    std::memcpy(maps.m, d.fast_tmaps, sizeof(CUtensorMap) * g.nlevels);
+    std::memcpy(maps.m48, d.fast_tmaps48, sizeof(CUtensorMap) * g.nlevels);
     // runs of consecutive levels that share a kernel variant: 0 = generic, 40 / 48 = warp layouts
     bool generic = false;
     auto variant = [&](int l) {

@@ -78,8 +78,9 @@ struct DevBufs {
     const int4* ytab[kMaxLevels];   // per dst y: {row0, row1, b0, b1}
     const int4* xq[kMaxLevels];     // per 4 dst columns: {base, selA01, selB01, selA23}{selB23, c0..c2}{c3,-,-,-}; null = use xtab
     const void* tmaps;              // HOST array CUtensorMap[2 * nlevels]: {level, blurred level} as [frames * h][pitch] u8 tensors
-    const int4* celltab;            // per FAST cell: {iniX | iniY<<16, ww | wh<<16 (0 = degenerate), offX | offY<<16, level}
+    const int4* celltab;            // per FAST cell: {iniX | iniY<<16, ww | wh<<16 (0 = degenerate), offX | offY<<16, level | direct<<4 | mdiv<<8}
     const void* fast_tmaps;         // HOST array CUtensorMap[nlevels]: level as [frames * h][pitch] u8, box 64 x window rows
+    const void* fast_tmaps48;       // the same with a 48-byte box (cells whose window fits it skip the re-layout)
     bool xqSimple[kMaxLevels];      // row table strictly down-scaling: row1 == row0 + 1 and strictly increasing
     // quadtree point scratch for levels whose corner count exceeds the shared-memory arrays
     uint32_t* qt_xy;                // [B][L][qtCap]
