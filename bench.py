@@ -703,6 +703,8 @@ def main():
                          "knn_gather_bytes": int(knn_line["gather_bytes_total"]),
                          "knn_x_popc_peak": knn_gcmp / world / popc_peak, "knn_tensor_tops": knn_tops, "knn_tensor_peak_tops": i8_peak_tops,
                          "knn_frac_tensor": knn_tops / i8_peak_tops,
+                         # the same against twice the BURST bf16 figure (a 0.2 s kernel timed alone sits between the two)
+                         "knn_frac_tensor_burst": knn_tops / (2.0 * float(peaks.get("bf16_tflops", 1650.0))),
                          "knn_popc_gcmps": popc_gcmp, "knn_popc_peak": popc_peak, "knn_frac_popc": popc_gcmp / popc_peak,
                          "note": "kernels are integer-issue bound, not HBM bound (ncu, profiles/); kNN: tcgen05 s8 engine vs 2x sustained bf16 cuBLAS",
                          "per_kernel": per_kernel},

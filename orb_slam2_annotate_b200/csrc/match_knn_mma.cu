@@ -297,16 +297,26 @@ __global__ void knn2_merge_kernel(int nq, int nseg, int th, float ratio, const i
 
 }  // namespace
 
-// segments of the train set for the tensor-core engine: at most 2^20 rows each, and enough of them that
-// small query sets still fill the SMs
+// segments of the train set for the tensor-core engine: at most 2^20 rows each, enough of them that small query
+// sets still fill the SMs, and — one CTA per SM, every CTA the same work — a count that leaves the last wave of
+// (query tiles x segments) CTAs as full as possible: 489 query tiles (1M queries over eight GPUs) are 3.3 waves in
+// one segment (82 % of four) and 9.9 waves in three (99 % of ten)
 int knn2_mma_segments(int nq, int nt, int* segLen) {
+    constexpr int kSms = 148;
     const int qtiles = (nq + MQ - 1) / MQ;
-    int want = qtiles >= 148 ? 1 : (148 + qtiles - 1) / qtiles;
+    int want = qtiles >= kSms ? 1 : (kSms + qtiles - 1) / qtiles;
     const int maxSeg = nt / 2048 > 1 ? nt / 2048 : 1;                  // no segment shorter than 16 tiles
     if (want > maxSeg) want = maxSeg;
     const int minSeg = (nt + (1 << 20) - 1) >> 20;
     if (want < minSeg) want = minSeg;
-    int len = ((nt + want - 1) / want + NT - 1) / NT * NT;
+    int best = want;
+    double bestEff = 0.0;
+    for (int c = want; c <= want + 7 && c <= (maxSeg > want ? maxSeg : want); c++) {
+        const long long ctas = (long long)qtiles * c, waves = (ctas + kSms - 1) / kSms;
+        const double eff = (double)ctas / (double)(waves * kSms);
+        if (eff > bestEff + 0.01) { bestEff = eff; best = c; }          // more segments only for a fuller tail
+    }
+    int len = ((nt + best - 1) / best + NT - 1) / NT * NT;
     if (len > (1 << 20)) len = 1 << 20;
     *segLen = len;
     return (nt + len - 1) / len;
