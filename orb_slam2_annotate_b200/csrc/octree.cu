@@ -19,30 +19,20 @@
 //   * the early break at size >= N (:774) is the first prefix of the processing order whose
 //     running size reaches N, found with a prefix sum over the children counts.
 // Prefix sums, the stable rank sort and the per-key updates are block-parallel (256 threads).
+#include <cstdio>
+#include <cstdlib>
+
 #include "orbfe_internal.cuh"
 
 namespace orbfe {
 
 namespace {
 
-constexpr int QT = 256;            // threads per tree
 constexpr int kPtsSmemMax = 4096;  // most keys a tree keeps in shared memory; larger levels use HBM scratch
 constexpr unsigned FULL = 0xFFFFFFFFu;
 
-struct Smem {
-    short4* box[2];
-    int* cnt[2];
-    int* cnt4;      // 4 per node: keys per quadrant of a candidate
-    int* cand;      // compacted candidate positions (list order)
-    int* order;     // processing order -> node position
-    int* pex;       // exclusive prefix of children counts, in processing order
-    int* prank;     // per node: processing rank if split this step, else -1
-    int* remap;     // per node: new position (survivor) or first child position (split)
-    int* tmp;       // scan scratch
-    uint32_t* pxy;
-    uint32_t* pnode;
-};
 
+template <int QT>
 __device__ __forceinline__ int block_exscan(int* a, int n, int* wsum) {
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int per = (n + QT - 1) / QT;
@@ -95,6 +85,7 @@ __device__ __forceinline__ int child_count(const int* c4) {
     return (c4[0] > 0) + (c4[1] > 0) + (c4[2] > 0) + (c4[3] > 0);
 }
 
+template <int QT>
 __global__ void __launch_bounds__(QT)
 octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ DevBufs d, int NC, int KP, int level0) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -106,23 +97,21 @@ octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ De
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int N = L.nFeat;
 
-    Smem S;
-    {
-        unsigned char* p = smem_raw;
-        S.box[0] = (short4*)p; p += sizeof(short4) * NC;
-        S.box[1] = (short4*)p; p += sizeof(short4) * NC;
-        S.cnt[0] = (int*)p; p += 4 * NC;
-        S.cnt[1] = (int*)p; p += 4 * NC;
-        S.cnt4 = (int*)p; p += 16 * NC;
-        S.cand = (int*)p; p += 4 * NC;
-        S.order = (int*)p; p += 4 * NC;
-        S.pex = (int*)p; p += 4 * NC;
-        S.prank = (int*)p; p += 4 * NC;
-        S.remap = (int*)p; p += 4 * NC;
-        S.tmp = (int*)p; p += 4 * NC;
-        S.pxy = (uint32_t*)p; p += 4 * KP;
-        S.pnode = (uint32_t*)p;
-    }
+    // the arena as plain locals (a struct with box[cur] indexing ends up in local memory: every access then reloads
+    // its pointer from the stack and loses the shared address space)
+    short4* const box0 = (short4*)smem_raw;
+    short4* const box1 = box0 + NC;
+    int* const cnt0 = (int*)(box1 + NC);
+    int* const cnt1 = cnt0 + NC;
+    int* const s_cnt4 = cnt1 + NC;      // 4 per node: keys per quadrant of a candidate
+    int* const s_cand = s_cnt4 + 4 * NC;   // compacted candidate positions (list order)
+    int* const s_order = s_cand + NC;   // processing order -> node position
+    int* const s_pex = s_order + NC;    // exclusive prefix of children counts, in processing order
+    int* const s_prank = s_pex + NC;    // per node: processing rank if split this step, else -1
+    int* const s_remap = s_prank + NC;  // per node: new position (survivor) or first child position (split)
+    int* const s_tmp = s_remap + NC;    // scan scratch
+    uint32_t* const s_pxy = (uint32_t*)(s_tmp + NC);
+    uint32_t* const s_pnode = s_pxy + KP;
     int* selc_out = d.selc + (long long)frame * g.nlevels + l;
     uint32_t* sel_out = d.sel + (long long)frame * g.selTotal + L.selBase;
 
@@ -146,8 +135,8 @@ octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ De
         if (tid == 0) *selc_out = 0;
         return;
     }
-    uint32_t* pxy = S.pxy;
-    uint32_t* pnode = S.pnode;
+    uint32_t* pxy = s_pxy;
+    uint32_t* pnode = s_pnode;
     if (n > KP) {
         const long long off = (long long)frame * g.cellSlots + L.cellSlotOff;
         pxy = d.qt_xy + off;
@@ -157,15 +146,15 @@ octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ De
         int run = 0;
         for (int base = 0; base < ncell; base += NC) {
             const int m = min(NC, ncell - base);
-            for (int c = tid; c < m; c += QT) S.tmp[c] = cc[base + c];
+            for (int c = tid; c < m; c += QT) s_tmp[c] = cc[base + c];
             __syncthreads();
-            const int tot = block_exscan(S.tmp, m, wsum);
+            const int tot = block_exscan<QT>(s_tmp, m, wsum);
             // one thread per cell: cells hold a handful of corners, and this way a CTA has
             // hundreds of independent loads in flight instead of one short row per warp
             for (int c = tid; c < m; c += QT) {
                 const int k = cc[base + c];
                 const uint32_t* src = ck + (long long)(base + c) * L.cellCap;
-                uint32_t* dst = pxy + run + S.tmp[c];
+                uint32_t* dst = pxy + run + s_tmp[c];
                 for (int i = 0; i < k; i++) dst[i] = __ldg(src + i);
             }
             run += tot;
@@ -176,101 +165,108 @@ octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ De
     // ---- roots (:570-615): nIni boxes of width hX; empty roots are erased
     const int nIni = L.nIni;
     for (int i = tid; i < nIni; i += QT) {
-        S.box[1][i] = make_short4((short)(int)__fmul_rn(L.hX, (float)i), 0,
+        box1[i] = make_short4((short)(int)__fmul_rn(L.hX, (float)i), 0,
                                   (short)(int)__fmul_rn(L.hX, (float)(i + 1)),
                                   (short)(L.maxBY - L.minBY));
-        S.cnt[1][i] = 0;
+        cnt1[i] = 0;
     }
     __syncthreads();
     for (int i = tid; i < n; i += QT) {
         const int r = min((int)__fdiv_rn((float)kp_x(pxy[i]), L.hX), nIni - 1);   // :598
         pnode[i] = r;
-        atomicAdd(&S.cnt[1][r], 1);
+        atomicAdd(&cnt1[r], 1);
     }
     __syncthreads();
-    for (int i = tid; i < nIni; i += QT) S.tmp[i] = S.cnt[1][i] > 0;
+    for (int i = tid; i < nIni; i += QT) s_tmp[i] = cnt1[i] > 0;
     __syncthreads();
-    int size = block_exscan(S.tmp, nIni, wsum);
+    int size = block_exscan<QT>(s_tmp, nIni, wsum);
     for (int i = tid; i < nIni; i += QT)
-        if (S.cnt[1][i] > 0) {
-            S.box[0][S.tmp[i]] = S.box[1][i];
-            S.cnt[0][S.tmp[i]] = S.cnt[1][i];
+        if (cnt1[i] > 0) {
+            box0[s_tmp[i]] = box1[i];
+            cnt0[s_tmp[i]] = cnt1[i];
         }
     __syncthreads();
-    for (int i = tid; i < n; i += QT) pnode[i] = S.tmp[pnode[i]];
+    for (int i = tid; i < n; i += QT) pnode[i] = s_tmp[pnode[i]];
     __syncthreads();
 
     int cur = 0, phase = 1;
     bool finish = false;
     while (!finish) {                                                     // :625
         const int prevSize = size;
-        const short4* boxc = S.box[cur];
-        const int* cntc = S.cnt[cur];
-        short4* boxn = S.box[cur ^ 1];
-        int* cntn = S.cnt[cur ^ 1];
+        const short4* boxc = (cur ? box1 : box0);
+        const int* cntc = (cur ? cnt1 : cnt0);
+        short4* boxn = (cur ? box0 : box1);
+        int* cntn = (cur ? cnt0 : cnt1);
         // a. keys per quadrant of every candidate (a node with more than one key)
-        for (int i = tid; i < 4 * size; i += QT) S.cnt4[i] = 0;
-        for (int i = tid; i < size; i += QT) { S.prank[i] = -1; S.tmp[i] = cntc[i] > 1; }
+        for (int i = tid; i < 4 * size; i += QT) s_cnt4[i] = 0;
+        for (int i = tid; i < size; i += QT) { s_prank[i] = -1; s_tmp[i] = cntc[i] > 1; }
         if (tid == 0) { s_cut = 0x7FFFFFFF; s_nexp = 0; }
         __syncthreads();
         for (int i = tid; i < n; i += QT) {
             const int nd = pnode[i];
-            if (cntc[nd] > 1) atomicAdd(&S.cnt4[4 * nd + quadrant(pxy[i], boxc[nd])], 1);
+            if (cntc[nd] > 1) atomicAdd(&s_cnt4[4 * nd + quadrant(pxy[i], boxc[nd])], 1);
         }
         // b. compact the candidates in list order
-        const int k0 = block_exscan(S.tmp, size, wsum);
+        const int k0 = block_exscan<QT>(s_tmp, size, wsum);
         for (int i = tid; i < size; i += QT)
-            if (cntc[i] > 1) S.cand[S.tmp[i]] = i;
+            if (cntc[i] > 1) s_cand[s_tmp[i]] = i;
         __syncthreads();
         // c. processing order
         if (phase == 1) {
-            for (int ci = tid; ci < k0; ci += QT) S.order[ci] = S.cand[ci];
+            for (int ci = tid; ci < k0; ci += QT) s_order[ci] = s_cand[ci];
         } else {
             // sort (count, creation order) ascending, walk from the back (:728-731): count
             // descending, then newest (= smaller list position) first.
+            // Rank sort on one packed key per candidate, count << 12 | (4095 - list rank): "count larger, or equal
+            // and earlier in the list" is one unsigned compare; the keys are read four at a time (broadcast LDS.128)
+            uint32_t* key = reinterpret_cast<uint32_t*>(s_tmp);           // free between the compaction and step e
+            for (int ci = tid; ci < ((k0 + 3) & ~3); ci += QT)
+                key[ci] = ci < k0 ? ((uint32_t)cntc[s_cand[ci]] << 12) | (uint32_t)(4095 - ci) : 0u;
+            __syncthreads();
+            const uint4* key4 = reinterpret_cast<const uint4*>(key);
             for (int ci = tid; ci < k0; ci += QT) {
-                const int me = cntc[S.cand[ci]];
+                const uint32_t me = key[ci];
                 int r = 0;
-                for (int j = 0; j < k0; j++) {
-                    const int cj = cntc[S.cand[j]];
-                    r += (cj > me) || (cj == me && j < ci);
+                for (int j = 0; j < (k0 + 3) >> 2; j++) {
+                    const uint4 kj = key4[j];
+                    r += (kj.x > me) + (kj.y > me) + (kj.z > me) + (kj.w > me);
                 }
-                S.order[r] = S.cand[ci];
+                s_order[r] = s_cand[ci];
             }
         }
         __syncthreads();
         // d. children per processed node, prefix sums, early break (:774)
-        for (int r = tid; r < k0; r += QT) S.pex[r] = child_count(&S.cnt4[4 * S.order[r]]);
+        for (int r = tid; r < k0; r += QT) s_pex[r] = child_count(&s_cnt4[4 * s_order[r]]);
         __syncthreads();
-        block_exscan(S.pex, k0, wsum);
+        block_exscan<QT>(s_pex, k0, wsum);
         int k = k0;
         if (phase == 2) {
             for (int r = tid; r < k0; r += QT) {
-                const int c = child_count(&S.cnt4[4 * S.order[r]]);
-                if (size + S.pex[r] + c - (r + 1) >= N) atomicMin(&s_cut, r);
+                const int c = child_count(&s_cnt4[4 * s_order[r]]);
+                if (size + s_pex[r] + c - (r + 1) >= N) atomicMin(&s_cut, r);
             }
             __syncthreads();
             if (s_cut < k0) k = s_cut + 1;
         }
-        const int T = k > 0 ? S.pex[k - 1] + child_count(&S.cnt4[4 * S.order[k - 1]]) : 0;
-        for (int r = tid; r < k; r += QT) S.prank[S.order[r]] = r;
+        const int T = k > 0 ? s_pex[k - 1] + child_count(&s_cnt4[4 * s_order[k - 1]]) : 0;
+        for (int r = tid; r < k; r += QT) s_prank[s_order[r]] = r;
         __syncthreads();
         // e. survivors keep their relative order behind the new children
-        for (int i = tid; i < size; i += QT) S.tmp[i] = S.prank[i] < 0;
+        for (int i = tid; i < size; i += QT) s_tmp[i] = s_prank[i] < 0;
         __syncthreads();
-        const int ns = block_exscan(S.tmp, size, wsum);
+        const int ns = block_exscan<QT>(s_tmp, size, wsum);
         int nexp = 0;
         for (int i = tid; i < size; i += QT) {
-            const int r = S.prank[i];
+            const int r = s_prank[i];
             if (r < 0) {
-                const int np = T + S.tmp[i];
+                const int np = T + s_tmp[i];
                 boxn[np] = boxc[i];
                 cntn[np] = cntc[i];
-                S.remap[i] = np;
+                s_remap[i] = np;
             } else {
-                const int* c4 = &S.cnt4[4 * i];
-                const int base = T - (S.pex[r] + child_count(c4));
-                S.remap[i] = base;
+                const int* c4 = &s_cnt4[4 * i];
+                const int base = T - (s_pex[r] + child_count(c4));
+                s_remap[i] = base;
                 int j = 0;
 #pragma unroll
                 for (int q = 3; q >= 0; q--)
@@ -287,14 +283,14 @@ octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ De
         // f. keys follow their nodes
         for (int i = tid; i < n; i += QT) {
             const int nd = pnode[i];
-            if (S.prank[nd] >= 0) {
+            if (s_prank[nd] >= 0) {
                 const int q = quadrant(pxy[i], boxc[nd]);
-                const int* c4 = &S.cnt4[4 * nd];
+                const int* c4 = &s_cnt4[4 * nd];
                 int j = 0;
                 for (int qq = q + 1; qq < 4; qq++) j += c4[qq] > 0;
-                pnode[i] = S.remap[nd] + j;
+                pnode[i] = s_remap[nd] + j;
             } else {
-                pnode[i] = S.remap[nd];
+                pnode[i] = s_remap[nd];
             }
         }
         const int nToExpand = s_nexp;
@@ -306,38 +302,56 @@ octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ De
     }
 
     // ---- one keypoint per node: maximum response, first in vKeys order wins ties (:789-805)
-    for (int i = tid; i < size; i += QT) S.tmp[i] = 0;
+    for (int i = tid; i < size; i += QT) s_tmp[i] = 0;
     __syncthreads();
     for (int i = tid; i < n; i += QT)
-        atomicMax((unsigned*)&S.tmp[pnode[i]],
+        atomicMax((unsigned*)&s_tmp[pnode[i]],
                   ((unsigned)(kp_score(pxy[i]) + 1) << 20) | (0xFFFFFu - (unsigned)i));
     __syncthreads();
     for (int pos = tid; pos < size; pos += QT) {
-        const uint32_t p = pxy[0xFFFFFu - ((unsigned)S.tmp[pos] & 0xFFFFFu)];
+        const uint32_t p = pxy[0xFFFFFu - ((unsigned)s_tmp[pos] & 0xFFFFFu)];
         sel_out[pos] = pack_kp(kp_x(p) + L.minBX, kp_y(p) + L.minBY, kp_score(p));   // :912-913
     }
     if (tid == 0) *selc_out = size;
 }
 
-int node_capacity(const FrameSetGeom& g) {
-    int nc = 0;
-    for (int l = 0; l < g.nlevels; l++) nc = max(nc, g.lv[l].selCap);
-    return nc;
+// threads per tree by the level's feature budget: the per-step cost of a tree is a fixed number of block-wide
+// loops, scans and barriers, paid once per warp, so the small trees of the upper levels run on fewer warps
+int tree_threads(const LevelGeom& L) {
+    // measured at nfeatures 1000 (budgets 217 181 151 126 105 87 73 60): 256/128/64 threads split at 170 / 90 gives
+    // 0.308 ms per 1024 frames; all 256: 0.328, all 128: 0.343, all 64: 0.410, 512 for the two largest: 0.319.  The
+    // single-frame latency does not depend on it (0.075 ms with 128 ... 1024 threads: the pyramid chain is as long)
+    static int t_hi = -1, t_lo = -1;
+    if (t_hi < 0) {
+        const char* e = std::getenv("ORBFE_OCTREE_SPLIT");        // "hi,lo": budgets above hi -> 256, above lo -> 128, else 64
+        int a = 170, b = 90;
+        if (e && std::sscanf(e, "%d,%d", &a, &b) != 2) { a = 170; b = 90; }
+        t_hi = a; t_lo = b;
+    }
+    return L.nFeat > t_hi ? 256 : L.nFeat > t_lo ? 128 : 64;
+}
+
+template <int T>
+void launch_tree(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s, dim3 grid, size_t smem, int NC, int KP, int a) {
+    octree_kernel<T><<<grid, T, smem, s>>>(g, d, NC, KP, a);
+}
+
+// shared-memory arena of a launch over levels [l0, l1): node arrays for the largest selection capacity, keys for twelve
+// times the largest budget (the synthetic and the usual camera frames bring 4-6 raw corners per kept one; more go
+// through the HBM scratch), at most kPtsSmemMax
+void group_capacity(const FrameSetGeom& g, int l0, int l1, int* NC, int* KP) {
+    int nc = 0, nmax = 0;
+    for (int l = l0; l < l1; l++) { nc = max(nc, g.lv[l].selCap); nmax = max(nmax, g.lv[l].nFeat); }
+    *NC = (nc + 3) & ~3;           // the int arrays behind the boxes stay 16-byte aligned (uint4 reads of the sort keys)
+    *KP = min(kPtsSmemMax, max(256, (12 * nmax + 63) & ~63));
 }
 
 }  // namespace
 
-// keys staged in shared memory per tree: twelve times the largest per-level budget (the synthetic and the usual
-// camera frames bring 4-6 raw corners per kept one), at most kPtsSmemMax — sized so that six trees share an SM
-// at nfeatures 1000 instead of four with the fixed 4096 (the kernel is latency / barrier bound: occupancy pays)
-static int key_capacity(const FrameSetGeom& g) {
-    int nmax = 0;
-    for (int l = 0; l < g.nlevels; l++) nmax = max(nmax, g.lv[l].nFeat);
-    return min(kPtsSmemMax, max(1024, (12 * nmax + 63) & ~63));
-}
-
 size_t octree_smem_bytes(const FrameSetGeom& g) {
-    return (size_t)node_capacity(g) * 64 + (size_t)key_capacity(g) * 8;
+    int NC, KP;
+    group_capacity(g, 0, g.nlevels, &NC, &KP);
+    return (size_t)NC * 64 + (size_t)KP * 8;
 }
 
 // The attribute is per function and per device, not per handle: it is always set to the one worst case
@@ -345,15 +359,33 @@ size_t octree_smem_bytes(const FrameSetGeom& g) {
 // live handle with a large one (mono Tracking keeps ORBextractor(2 * nFeatures) and ORBextractor(nFeatures)).
 int octree_prepare(const FrameSetGeom& g) {
     (void)g;
-    return (int)cudaFuncSetAttribute(octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(octree_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(octree_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(octree_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    return (int)e;
 }
 
 int launch_octree(const FrameSetGeom& g, const DevBufs& d, cudaStream_t s, int l0, int l1) {
     if (l1 < 0 || l1 > g.nlevels) l1 = g.nlevels;
     if (l0 < 0) l0 = 0;
-    if (l1 <= l0) return 0;
-    octree_kernel<<<dim3(l1 - l0, g.batch), QT, octree_smem_bytes(g), s>>>(g, d, node_capacity(g), key_capacity(g), l0);
-    return 1;
+    int launches = 0;
+    for (int a = l0; a < l1;) {                          // runs of levels with the same thread count
+        const int T = tree_threads(g.lv[a]);
+        int b = a + 1;
+        while (b < l1 && tree_threads(g.lv[b]) == T) b++;
+        int NC, KP;
+        group_capacity(g, a, b, &NC, &KP);
+        const size_t smem = (size_t)NC * 64 + (size_t)KP * 8;
+        const dim3 grid(b - a, g.batch);
+        switch (T) {
+            case 256: launch_tree<256>(g, d, s, grid, smem, NC, KP, a); break;
+            case 128: launch_tree<128>(g, d, s, grid, smem, NC, KP, a); break;
+            default: launch_tree<64>(g, d, s, grid, smem, NC, KP, a); break;
+        }
+        launches++;
+        a = b;
+    }
+    return launches;
 }
 
 }  // namespace orbfe

@@ -1,7 +1,8 @@
 """Where the single-frame call spends its time: pageable vs pinned host buffers vs device-resident frames."""
-import json, time
+import json, os, sys, time
 import numpy as np
 import torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import orb_slam2_annotate_b200 as orbfe
 from orb_slam2_annotate_b200 import synth
 
