@@ -245,12 +245,13 @@ int orbfe_knn2_device(orbfe_matcher* m, const uint8_t* d_query, int nq, const ui
 int orbfe_matcher_fetch(orbfe_matcher* m, void* dst, const void* d_src, size_t bytes);
 
 /* Which engine serves orbfe_knn2 / _device / _sharded.  ORBFE_KNN_POPC: 8 x (XOR + POPC) per comparison on
- * the integer pipe, the reference's own form (src/ORBmatcher.cc:1835-1841).  ORBFE_KNN_MMA: the distance as a
- * contraction, d = |a| + |b| - 2<a,b> over bits expanded to bytes in shared memory, on the tensor cores
- * (tcgen05.mma kind::i8, accumulators in TMEM).  Both give identical results; ORBFE_KNN_AUTO (default) takes
- * the tensor cores from 2^26 comparisons per call upwards.  The environment variable ORBFE_KNN_ENGINE = popc |
- * mma overrides AUTO for a whole process. */
-enum { ORBFE_KNN_AUTO = 0, ORBFE_KNN_POPC = 1, ORBFE_KNN_MMA = 2 };
+ * the integer pipe, the reference's own form (src/ORBmatcher.cc:1835-1841).  ORBFE_KNN_MMA and ORBFE_KNN_FP4: the
+ * distance as a contraction on the tensor cores, <a', b'> = 256 - 2 d over bits mapped to +-1 — as signed bytes expanded
+ * in shared memory (tcgen05.mma kind::i8) or as E2M1 values with unit block scales written once by a pre-pass
+ * (tcgen05.mma kind::mxf4.block_scale, twice the rate; needs 128 bytes of scratch per row), accumulators in TMEM.  All
+ * three give identical results; ORBFE_KNN_AUTO (default) takes the FP4 engine from 2^26 comparisons per call upwards.
+ * The environment variable ORBFE_KNN_ENGINE = popc | mma | fp4 overrides AUTO for a whole process. */
+enum { ORBFE_KNN_AUTO = 0, ORBFE_KNN_POPC = 1, ORBFE_KNN_MMA = 2, ORBFE_KNN_FP4 = 3 };
 int orbfe_matcher_set_knn_engine(orbfe_matcher* m, int engine);
 
 /* Allocation-free variant of orbfe_knn2_device.  NO COUNTERPART IN THE REFERENCE: added

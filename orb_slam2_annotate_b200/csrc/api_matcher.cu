@@ -26,18 +26,26 @@ struct orbfe_matcher {
 namespace {
 
 // which brute-force engine serves a kNN call: the tensor-core kernel needs enough work to fill its pipeline
-bool knn_use_mma(const orbfe_matcher* m, int nq, int nt) {
+// which engine serves a kNN-2 call: the handle's choice, else ORBFE_KNN_ENGINE, else by size (the tensor cores from
+// 2^26 comparisons upwards: below that the launch of the pre-pass / merge kernels and the half-empty waves cost more
+// than the popc kernel's whole run)
+int knn_engine(const orbfe_matcher* m, int nq, int nt) {
     static const char* env = std::getenv("ORBFE_KNN_ENGINE");
     int eng = m->knnEngine;
-    if (eng == ORBFE_KNN_AUTO && env) eng = !std::strcmp(env, "popc") ? ORBFE_KNN_POPC : !std::strcmp(env, "mma") ? ORBFE_KNN_MMA : eng;
-    if (eng == ORBFE_KNN_POPC) return false;
-    if (eng == ORBFE_KNN_MMA) return true;
-    return nq >= 256 && (long long)nq * nt >= (1ll << 26);
+    if (eng == ORBFE_KNN_AUTO && env)
+        eng = !std::strcmp(env, "popc") ? ORBFE_KNN_POPC : !std::strcmp(env, "mma") ? ORBFE_KNN_MMA : !std::strcmp(env, "fp4") ? ORBFE_KNN_FP4 : eng;
+    if (eng != ORBFE_KNN_AUTO) return eng;
+    return nq >= 256 && (long long)nq * nt >= (1ll << 26) ? ORBFE_KNN_FP4 : ORBFE_KNN_POPC;
 }
 
 int knn2_dispatch(orbfe_matcher* m, const uint8_t* d_query, int nq, const uint8_t* d_train, int nt, int th, float ratio,
                   int* d_idx, int* d_d1, int* d_d2) {
-    if (nq > 0 && knn_use_mma(m, nq, nt)) {
+    const int eng = nq > 0 ? knn_engine(m, nq, nt) : ORBFE_KNN_POPC;
+    if (eng == ORBFE_KNN_FP4) {
+        int rc = m->knnScratch.ensure(knn2_fp4_scratch_bytes(nq, std::max(nt, 1)) + 256);
+        if (rc) return rc;
+        if (launch_knn2_fp4(d_query, nq, d_train, nt, th, ratio, d_idx, d_d1, d_d2, m->knnScratch.p, m->stream) < 0) return ORBFE_ERR_CUDA;
+    } else if (eng == ORBFE_KNN_MMA) {
         int rc = m->knnScratch.ensure(knn2_mma_scratch_bytes(nq, std::max(nt, 1)) + 256);
         if (rc) return rc;
         launch_knn2_mma(d_query, nq, d_train, nt, th, ratio, d_idx, d_d1, d_d2, m->knnScratch.p, m->stream);
@@ -100,7 +108,7 @@ int orbfe_matcher_fetch(orbfe_matcher* m, void* dst, const void* d_src, size_t b
 }
 
 int orbfe_matcher_set_knn_engine(orbfe_matcher* m, int engine) {
-    if (!m || engine < ORBFE_KNN_AUTO || engine > ORBFE_KNN_MMA) return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_matcher_set_knn_engine");
+    if (!m || engine < ORBFE_KNN_AUTO || engine > ORBFE_KNN_FP4) return fail(ORBFE_ERR_ARG, "bad arguments to orbfe_matcher_set_knn_engine");
     m->knnEngine = engine;
     return ORBFE_OK;
 }

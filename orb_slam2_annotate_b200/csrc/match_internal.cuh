@@ -16,6 +16,16 @@ int launch_knn2(const uint8_t* d_query, int nq, const uint8_t* d_train, int nt, 
 size_t knn2_mma_scratch_bytes(int nq, int nt);
 int launch_knn2_mma(const uint8_t* d_query, int nq, const uint8_t* d_train, int nt, int th, float ratio,
                     int* d_idx, int* d_d1, int* d_d2, void* scratch, cudaStream_t s);
+// block-scaled FP4 engine (match_knn_fp4.cu: tcgen05.mma kind::mxf4 on +-1 E2M1 rows written by a pre-pass, operands by
+// TMA); scratch = knn2_fp4_scratch_bytes(nq, nt): partial results + both row sets at 128 bytes per row
+size_t knn2_fp4_scratch_bytes(int nq, int nt);
+int launch_knn2_fp4(const uint8_t* d_query, int nq, const uint8_t* d_train, int nt, int th, float ratio,
+                    int* d_idx, int* d_d1, int* d_d2, void* scratch, cudaStream_t s);
+// shared by the two tensor-core engines: train segments for CTAs of mq queries and tiles of ntile rows; the merge of
+// the per-segment partial results (TH_LOW / ratio test included)
+int knn2_tile_segments(int nq, int nt, int mq, int ntile, int* segLen);
+int launch_knn2_merge(int nq, int nseg, int th, float ratio, const int* part_idx, const int* part_d1, const int* part_d2,
+                      int* d_idx, int* d_d1, int* d_d2, cudaStream_t s);
 // (idx, d1, d2) of rows [first, first + n) -> packed orbfe_knn_result rows (the sharded search's gather payload)
 int launch_knn2_pack(const int* d_idx, const int* d_d1, const int* d_d2, int n, void* d_packed, cudaStream_t s);
 

@@ -301,11 +301,11 @@ __global__ void knn2_merge_kernel(int nq, int nseg, int th, float ratio, const i
 // sets still fill the SMs, and — one CTA per SM, every CTA the same work — a count that leaves the last wave of
 // (query tiles x segments) CTAs as full as possible: 489 query tiles (1M queries over eight GPUs) are 3.3 waves in
 // one segment (82 % of four) and 9.9 waves in three (99 % of ten)
-int knn2_mma_segments(int nq, int nt, int* segLen) {
+int knn2_tile_segments(int nq, int nt, int mq, int ntile, int* segLen) {
     constexpr int kSms = 148;
-    const int qtiles = (nq + MQ - 1) / MQ;
+    const int qtiles = (nq + mq - 1) / mq;
     int want = qtiles >= kSms ? 1 : (kSms + qtiles - 1) / qtiles;
-    const int maxSeg = nt / 2048 > 1 ? nt / 2048 : 1;                  // no segment shorter than 16 tiles
+    const int maxSeg = nt / (16 * ntile) > 1 ? nt / (16 * ntile) : 1;  // no segment shorter than 16 tiles
     if (want > maxSeg) want = maxSeg;
     const int minSeg = (nt + (1 << 20) - 1) >> 20;
     if (want < minSeg) want = minSeg;
@@ -316,10 +316,17 @@ int knn2_mma_segments(int nq, int nt, int* segLen) {
         const double eff = (double)ctas / (double)(waves * kSms);
         if (eff > bestEff + 0.01) { bestEff = eff; best = c; }          // more segments only for a fuller tail
     }
-    int len = ((nt + best - 1) / best + NT - 1) / NT * NT;
-    if (len > (1 << 20)) len = 1 << 20;
+    int len = ((nt + best - 1) / best + ntile - 1) / ntile * ntile;
+    if (len > (1 << 20)) len = (1 << 20) / ntile * ntile;
     *segLen = len;
     return (nt + len - 1) / len;
+}
+int knn2_mma_segments(int nq, int nt, int* segLen) { return knn2_tile_segments(nq, nt, MQ, NT, segLen); }
+
+int launch_knn2_merge(int nq, int nseg, int th, float ratio, const int* part_idx, const int* part_d1, const int* part_d2,
+                      int* d_idx, int* d_d1, int* d_d2, cudaStream_t s) {
+    knn2_merge_kernel<<<(nq + 255) / 256, 256, 0, s>>>(nq, nseg, th, ratio, part_idx, part_d1, part_d2, d_idx, d_d1, d_d2);
+    return 1;
 }
 
 size_t knn2_mma_scratch_bytes(int nq, int nt) {

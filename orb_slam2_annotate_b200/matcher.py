@@ -247,10 +247,11 @@ class ORBmatcher:
         """Asynchronous device-to-host copy on the matcher's stream (orbfe_matcher_fetch); sync() makes it visible."""
         check(self._L.orbfe_matcher_fetch(self._h, dst_ptr, src_dev_ptr, nbytes), "orbfe_matcher_fetch")
 
-    KNN_ENGINES = {"auto": 0, "popc": 1, "mma": 2}
+    KNN_ENGINES = {"auto": 0, "popc": 1, "mma": 2, "fp4": 3}
 
     def set_knn_engine(self, engine: str) -> None:
-        """"popc": XOR + POPC on the integer pipe; "mma": tcgen05.mma on bit -> byte expanded rows; "auto" (default)."""
+        """"popc": XOR + POPC on the integer pipe; "mma": tcgen05.mma kind::i8 on bit -> byte expanded rows; "fp4": tcgen05.mma
+        kind::mxf4 on +-1 E2M1 rows; "auto" (default)."""
         check(self._L.orbfe_matcher_set_knn_engine(self._h, self.KNN_ENGINES[engine]), "orbfe_matcher_set_knn_engine")
 
     def knn2_sharded(self, comm, q_ptr: int, m: int, t_ptr: int, n: int, out_ptr: int,

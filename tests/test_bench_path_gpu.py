@@ -75,7 +75,7 @@ def _knn_device(orbfe, q, t, engine, th=50, ratio=0.7):
     return o[0], o[1], o[2]
 
 
-@pytest.mark.parametrize("engine", ["popc", "mma"])
+@pytest.mark.parametrize("engine", ["popc", "mma", "fp4"])
 @pytest.mark.parametrize("m,n", [(1, 1), (7, 1), (300, 127), (257, 129), (1000, 20000), (5000, 777), (4096, 4096), (70000, 3000)])
 def test_knn2_device_engines_match_oracle(orbfe, oracle, engine, m, n):
     t = synth.descriptors(n, 1)
@@ -85,7 +85,7 @@ def test_knn2_device_engines_match_oracle(orbfe, oracle, engine, m, n):
     assert np.array_equal(d1, o1) and np.array_equal(d2, o2) and np.array_equal(idx, oi)
 
 
-@pytest.mark.parametrize("engine", ["popc", "mma"])
+@pytest.mark.parametrize("engine", ["popc", "mma", "fp4"])
 def test_knn2_device_ties_extremes_empty(orbfe, oracle, engine):
     t = np.zeros((300, 32), np.uint8)
     t[10:] = 0xFF
@@ -100,7 +100,7 @@ def test_knn2_device_ties_extremes_empty(orbfe, oracle, engine):
     assert (idx == -1).all() and (d1 == 256).all() and (d2 == 256).all()
 
 
-@pytest.mark.parametrize("engine", ["popc", "mma"])
+@pytest.mark.parametrize("engine", ["popc", "mma", "fp4"])
 def test_knn2_device_q4_variant(orbfe, oracle, engine):
     """nq >= 303 104 takes knn2_popc_kernel<4>; the tensor-core engine runs 1250 query tiles x 1 segment."""
     t = synth.descriptors(2000, 3)
@@ -114,7 +114,7 @@ def test_knn2_device_q4_variant(orbfe, oracle, engine):
     assert (idx >= 0).sum() > 10000
 
 
-@pytest.mark.parametrize("engine", ["popc", "mma"])
+@pytest.mark.parametrize("engine", ["popc", "mma", "fp4"])
 def test_knn2_device_train_over_2_20_rows_ties_across_segments(orbfe, oracle, engine):
     """1 100 000 train rows (> 2^20: the popc kernel merges two index segments, the tensor-core engine 148 train
     segments of 7 552 rows) x 64 queries whose best distance is reached by three rows planted in different segments:
@@ -123,7 +123,7 @@ def test_knn2_device_train_over_2_20_rows_ties_across_segments(orbfe, oracle, en
     rng = np.random.default_rng(9)
     t = rng.integers(0, 256, (n, 32), dtype=np.uint8)
     q = rng.integers(0, 256, (64, 32), dtype=np.uint8)
-    spots = [(1 << 20) - 1, 1 << 20, (1 << 20) + 1, 7551, 7552, 15104, n - 1, 0]
+    spots = [(1 << 20) - 1, 1 << 20, (1 << 20) + 1, 7551, 7552, 15104, n - 1, 0, 7503, 7504]     # 7504: the FP4 engine's segment length here
     for i in range(64):
         near = q[i].copy()
         near[i % 32] ^= np.uint8(1 << (i % 8))                       # distance 1

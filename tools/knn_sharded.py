@@ -4,7 +4,7 @@ sharded over the GPUs of one node, one NCCL all-gather of 8-byte result rows —
 (orbfe_comm_create / orbfe_knn2_sharded).  Strong scaling: the problem is fixed, every rank holds the same inputs
 (i.i.d. rows, seeds 1 and 2, 10 % planted near-duplicates, ratio 0.7, TH_LOW 50).
 
-  python tools/knn_sharded.py [--nq 1000000 --nt 1000000 --engine auto|popc|mma --steps 3 --check]
+  python tools/knn_sharded.py [--nq 1000000 --nt 1000000 --engine auto|popc|mma|fp4 --steps 3 --check]
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P tools/knn_sharded.py ...
 
 Rank 0 prints one JSON line.  --check: sharded result == single-GPU result of rank 0 on all queries == CPU oracle on a
@@ -135,7 +135,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--nq", type=int, default=1_000_000)
     ap.add_argument("--nt", type=int, default=1_000_000)
-    ap.add_argument("--engine", default="auto", choices=["auto", "popc", "mma"])
+    ap.add_argument("--engine", default="auto", choices=["auto", "popc", "mma", "fp4"])
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=1)
     ap.add_argument("--check", action="store_true")
