@@ -23,7 +23,7 @@ int launch_knn2_fp4(const uint8_t* d_query, int nq, const uint8_t* d_train, int 
                     int* d_idx, int* d_d1, int* d_d2, void* scratch, cudaStream_t s);
 // shared by the two tensor-core engines: train segments for CTAs of mq queries and tiles of ntile rows; the merge of
 // the per-segment partial results (TH_LOW / ratio test included)
-int knn2_tile_segments(int nq, int nt, int mq, int ntile, int* segLen);
+int knn2_tile_segments(int nq, int nt, int mq, int ntile, int* segLen, int minWant = 1);
 int launch_knn2_merge(int nq, int nseg, int th, float ratio, const int* part_idx, const int* part_d1, const int* part_d2,
                       int* d_idx, int* d_d1, int* d_d2, cudaStream_t s);
 // (idx, d1, d2) of rows [first, first + n) -> packed orbfe_knn_result rows (the sharded search's gather payload)

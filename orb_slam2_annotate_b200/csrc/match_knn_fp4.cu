@@ -12,17 +12,26 @@
 // with the 128-byte swizzle, i.e. directly in the canonical K-major layout the MMA descriptors name).  All CTAs walk the
 // train set in step, so a tile is fetched from HBM once and from L2 by everyone else.
 //
-//   CTA = 256 query rows (two M = 128 tiles, one 32 KB TMA box) against one segment of the train set in tiles of 112 rows
-//   (TMEM: 2 accumulator stages x 2 M tiles x 112 columns = 448, the unit scale factors in the columns behind them).
-//   warps 0-7  epilogue, one query row per thread: tcgen05.ld 16 columns at a time (next load in flight), max tree over
-//              the 16 fp32 accumulators and ONE compare against thr = 256 - 2 * (second-best distance) — exact for the
-//              same reason as in match_knn_mma.cu (columns arrive in ascending train index) —, the packed-key update
-//              d << 20 | index only behind it.
-//   warp 8     TMA producer (one lane): query box once, then train boxes through a 6-stage ring.
-//   warp 9     TMEM allocation and the MMA issue: per tile 2 x 4 tcgen05.mma (M 128, N 112, K 64), tcgen05.commit onto
-//              the stage's "empty" barrier and the accumulator's "full" barrier.
+//   CTA = 256 query rows (two M = 128 tiles, one 32 KB TMA box) against one segment of the train set in tiles of 192 rows.
+//   One MMA covers a whole tile (M 128, N 192, K 64): an SS-mode MMA reads both operands from shared memory every time,
+//   and with narrow N the 128 B/clk of shared memory, not the tensor pipe, sets the pace (measured without an epilogue:
+//   N 112 -> 10.4 T comparisons/s, N 160 -> 11.5 T, N 192 -> 14.7 T, N 224 -> 15.5 T).  TMEM then holds two
+//   accumulators of 192 columns (+ the unit scale factors in the columns behind them); the (tile, M tile) pairs take them
+//   in turn, so the epilogue of one M tile runs under the MMAs of the other.
+//   warps 0-15 epilogue, two threads per query row (a warp reads the TMEM lanes of its quadrant: warps w and w + 8 share
+//              32 rows and take 96 columns each): tcgen05.ld 32 columns at a time (next load in flight), a balanced tree
+//              of three-input integer maxima over the accumulators' bit patterns and ONE compare against the pattern of
+//              256 - 2 * (second-best distance) — exact for the same reason as in match_knn_mma.cu (columns arrive in
+//              ascending train index).  A group that passes revisits only the triples whose own maximum passed (the
+//              packed-key update d << 20 | index, key formed without F2I); the accumulator is handed back as soon as the
+//              last columns are in registers.  Measured: hand-off latency, not arithmetic, is what separates the kernel
+//              (10.4 T) from its MMA pipeline (14.7 T): three accumulators would hide it but do not fit TMEM at this N.
+//   warp 16    TMA producer (one lane): query box once, then train boxes through a 4-stage ring.
+//   warp 17    TMEM allocation and the MMA issue: per tile 2 x 4 tcgen05.mma, tcgen05.commit onto the accumulator's
+//              "full" barrier and the stage's "empty" barrier.
 #include <climits>
 #include <cstdio>
+#include <cstdlib>
 
 #include <cuda.h>
 
@@ -35,20 +44,26 @@ namespace orbfe {
 namespace {
 
 constexpr int MQ = 256;                 // query rows per CTA
-constexpr int NT = 112;                 // train rows per tile (multiple of 16; 4 x 112 accumulator columns + scale factors <= 512)
-constexpr int STAGES = 6;
-constexpr int EPI_WARPS = 8;
+#ifndef KNN_FP4_NT
+#define KNN_FP4_NT 192
+#define KNN_FP4_NACC 2
+#endif
+constexpr int NT = KNN_FP4_NT;          // train rows per tile = N of one MMA; NACC accumulators of NT columns + scale factors <= 512
+constexpr int NACC = KNN_FP4_NACC;      // accumulators, taken in turn by the (tile, M tile) pairs
+constexpr int STAGES = NT > 170 ? 4 : 5;
+static_assert(NACC * NT + 32 <= 512 && NT % 16 == 0, "TMEM budget / MMA shape");
+constexpr int EPI_WARPS = 16;             // two per (M tile, lane quadrant): each takes half of a tile's columns
 constexpr int THREADS = (EPI_WARPS + 2) * 32;
 constexpr uint32_t KEY_NONE = 0xFFFFFFFFu;
 constexpr int A_BYTES = MQ * 128, B_BYTES = NT * 128;
-constexpr int ACC_STAGE_COLS = 2 * NT;  // two M tiles
-constexpr int SF_COL = 2 * ACC_STAGE_COLS;   // 448: 32 columns of 0x7F in every lane serve as SFA and SFB
+constexpr int SF_COL = NACC * NT;       // 480: 32 columns of 0x7F in every lane serve as SFA and SFB
 
 struct alignas(1024) Fp4Smem {
     uint8_t a[A_BYTES];                           // 256 rows x 128 B, 8-row groups swizzled (as TMA writes them)
-    uint8_t b[STAGES][B_BYTES];                   // 6 x 14 KB
-    unsigned long long full_b[STAGES], empty_b[STAGES], acc_full[2], acc_empty[2], a_full;
+    uint8_t b[STAGES][B_BYTES];                   // 5 x 20 KB
+    unsigned long long full_b[STAGES], empty_b[STAGES], acc_full[NACC], acc_empty[NACC], a_full;
     uint32_t tmem_base;
+    uint32_t xk1[MQ], xk2[MQ];                    // the second column half's (best, second best) on its way to the first
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -95,23 +110,104 @@ __device__ __forceinline__ void umma_commit(unsigned long long* bar) {
                    "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])                 \
                  : "r"(taddr) : "memory")
 
-// 16 accumulators (256 - 2 d, exact in fp32) of one query against train rows idx0 .. idx0 + 15 of the segment, folded
-// into the packed keys (k1, k2) = (best, second best); thr = 256 - 2 * (k2 >> 20).  valid < 16 only in a segment's last tile.
-__device__ __forceinline__ void fold16(const uint32_t (&v)[16], uint32_t idx0, int valid, uint32_t& k1, uint32_t& k2, float& thr) {
-    float m = fmaxf(__uint_as_float(v[0]), __uint_as_float(v[1]));
+#define TMEM_LD32(taddr, v)                                                                                              \
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "                                                               \
+                 "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];" \
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),       \
+                   "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),           \
+                   "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),          \
+                   "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])                       \
+                 : "r"(taddr) : "memory")
+
+// The accumulators are fp32 but the screen runs on their bit patterns as signed integers (three-input integer max,
+// VIMNMX3: the fp32 three-input max measured four times slower here): non-negative floats order like their patterns,
+// and every negative float is a negative integer.  So the integer maximum IS the float maximum whenever that is >= 0;
+// otherwise it is merely some negative number — which decides "max > thr" correctly for every thr >= 0.  While the
+// threshold is still negative (no second best yet, or one beyond distance 128) the caller passes INT_MIN and every
+// group takes the exact path.
+__device__ __forceinline__ int imax3(int a, int b, int c) { return max(max(a, b), c); }
+// the screen's threshold for a second-best key k2: bit pattern of 256 - 2 d2 when that is >= 0, else "always"
+__device__ __forceinline__ int screen_threshold(uint32_t k2) {
+    const int t = 256 - 2 * (int)(k2 >> 20);
+    return t >= 0 ? __float_as_int((float)t) : INT_MIN;
+}
+// one accumulator into (best, second best): the key d << 20 | index from the fp32 value without a conversion
+// instruction (adding 1.5 * 2^23 leaves the integer in the low mantissa bits; F2I runs on the quarter-rate pipe), then
+// the strict-'<' rule  k2' = min(k2, max(k1, key)), k1' = min(k1, key)
+__device__ __forceinline__ void take(uint32_t bits, uint32_t cidx, uint32_t& k1, uint32_t& k2) {
+    constexpr uint32_t NEG = 0u - (1u << 19);                     // (256 - acc) << 19 == d << 20
+    constexpr uint32_t MAGIC = 0x4B400000u;                       // bit pattern of 12582912.0f
+    const uint32_t key = __float_as_uint(__fadd_rn(__uint_as_float(bits), 12582912.0f)) * NEG + (cidx - MAGIC * NEG);
+    k2 = min(k2, max(k1, key));
+    k1 = min(k1, key);
+}
+
+// N accumulators (256 - 2 d, exact in fp32) of one query against train rows idx0 .. idx0 + N - 1 of the segment, folded
+// into the packed keys (k1, k2) = (best, second best); thr = screen_threshold(k2).  The common case is a balanced tree of
+// three-input maxima (depth 4) and one compare.  A thread whose group passes does not walk all N columns — the other
+// lanes of its warp, and the seven other warps that share the accumulator, wait for it —: it revisits the tree's first
+// level and updates only the triples whose own maximum passed.  MASK: only the first `valid` columns exist (a segment's
+// last tile); then, and while there is no usable threshold yet, every column is taken in turn.
+template <int N, bool MASK>
+__device__ __forceinline__ void fold(const uint32_t (&v)[N], uint32_t idx0, int valid, uint32_t& k1, uint32_t& k2, int& thr) {
+    const uint32_t c0 = (256u << 19) + idx0;
+    if (MASK || thr == INT_MIN) {
 #pragma unroll
-    for (int i = 2; i < 16; i += 2) m = fmaxf(m, fmaxf(__uint_as_float(v[i]), __uint_as_float(v[i + 1])));
+        for (int i = 0; i < N; i++)
+            if (!MASK || i < valid) take(v[i], c0 + (uint32_t)i, k1, k2);
+        thr = screen_threshold(k2);
+        return;
+    }
+    constexpr int T = N / 3;                                      // 10 triples + 2 columns, or 5 triples + 1 column
+    int b[T];
+#pragma unroll
+    for (int j = 0; j < T; j++) b[j] = imax3((int)v[3 * j], (int)v[3 * j + 1], (int)v[3 * j + 2]);
+    int m;
+    if (N == 32) m = max(imax3(imax3(b[0], b[1], b[2]), imax3(b[3], b[4], b[5]), imax3(b[6], b[7], b[8])), imax3(b[9 % T], (int)v[30 % N], (int)v[31 % N]));
+    else m = max(imax3(b[0], b[1], b[2]), imax3(b[3], b[4], (int)v[15]));
     if (m > thr) {
-        constexpr uint32_t NEG = 0u - (1u << 19);                 // (256 - acc) << 19 == d << 20
-        const uint32_t c0 = (256u << 19) + idx0;
+        const int thr0 = thr;                                     // looser than the running one: never skips a column that matters
 #pragma unroll
-        for (int i = 0; i < 16; i++) {
-            const uint32_t acc = (uint32_t)__float2int_rn(__uint_as_float(v[i]));
-            const uint32_t key = i < valid ? acc * NEG + (c0 + (uint32_t)i) : KEY_NONE;
-            k2 = min(k2, max(k1, key));
-            k1 = min(k1, key);
-        }
-        thr = (float)(256 - 2 * (int)(k2 >> 20));
+        for (int j = 0; j < T; j++)
+            if (b[j] > thr0) {
+                take(v[3 * j], c0 + 3u * j, k1, k2);
+                take(v[3 * j + 1], c0 + 3u * j + 1u, k1, k2);
+                take(v[3 * j + 2], c0 + 3u * j + 2u, k1, k2);
+            }
+#pragma unroll
+        for (int i = 3 * T; i < N; i++)
+            if ((int)v[i] > thr0) take(v[i], c0 + (uint32_t)i, k1, k2);
+        thr = screen_threshold(k2);
+    }
+}
+
+// one thread's half of an accumulator of one query row (NT / 2 columns = G groups of 32 and, if NT / 2 is not a multiple
+// of 32, one of 16): the next tcgen05.ld is in flight while a group folds
+template <bool MASK>
+__device__ __forceinline__ void fold_half_tile(uint32_t tbase, uint32_t idx0, int left, uint32_t& k1, uint32_t& k2, int& thr,
+                                               unsigned long long* release, int lane) {
+    constexpr int HALF = NT / 2, G = HALF / 32, R = HALF % 32;
+    static_assert(R == 0 || R == 16, "column groups are 32 wide plus at most one of 16");
+    uint32_t v[2][32], vr[16];
+    // the accumulator goes back to the MMA warp as soon as this warp's last columns are in registers, before they fold
+    auto give_back = [&]() {
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) mbar_arrive(release);
+    };
+    TMEM_LD32(tbase, v[0]);
+#pragma unroll
+    for (int g = 0; g < G; g++) {
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        if (g + 1 < G) TMEM_LD32(tbase + 32 * (g + 1), v[(g + 1) & 1]);
+        else if (R) TMEM_LD16(tbase + 32 * G, vr);
+        else give_back();
+        fold<32, MASK>(v[g & 1], idx0 + 32 * g, left - 32 * g, k1, k2, thr);
+    }
+    if (R) {
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        give_back();
+        fold<16, MASK>(vr, idx0 + 32 * G, left - 32 * G, k1, k2, thr);
     }
 }
 
@@ -138,15 +234,19 @@ knn2_fp4_kernel(const __grid_constant__ CUtensorMap qmap, const __grid_constant_
     Fp4Smem& S = *reinterpret_cast<Fp4Smem*>(smem_raw);
     if ((smem_u32(smem_raw) & 1023u) != 0) __trap();
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int q0 = blockIdx.x * MQ;
-    const int seg = blockIdx.y;
+    // consecutive CTAs (one wave) take different train segments: every tile is then wanted by 148 / nseg SMs at a time
+    // instead of all of them (the few L2 slices that hold a tile's 112 lines could not serve 148 readers in step)
+    const int nseg = (int)gridDim.y;
+    const int lin = (int)(blockIdx.y * gridDim.x + blockIdx.x);
+    const int seg = lin % nseg;
+    const int q0 = (lin / nseg) * MQ;
     const long long seg0 = (long long)seg * segLen;
     const int segn = (int)min((long long)segLen, (long long)nt - seg0);        // > 0 by construction of the grid
     const int ntiles = (segn + NT - 1) / NT;
 
     if (tid == 0) {
         for (int i = 0; i < STAGES; i++) { mbar_init(&S.full_b[i], 1); mbar_init(&S.empty_b[i], 1); }
-        for (int i = 0; i < 2; i++) { mbar_init(&S.acc_full[i], 1); mbar_init(&S.acc_empty[i], EPI_WARPS); }
+        for (int i = 0; i < NACC; i++) { mbar_init(&S.acc_full[i], 1); mbar_init(&S.acc_empty[i], EPI_WARPS / 2); }
         mbar_init(&S.a_full, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -172,43 +272,30 @@ knn2_fp4_kernel(const __grid_constant__ CUtensorMap qmap, const __grid_constant_
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 
     if (warp < EPI_WARPS) {
-        // ---------------- epilogue: thread <-> query row q0 + tid (TMEM lane tid & 127 of M tile tid >> 7)
-        const int mtile = warp >> 2;
+        // ---------------- epilogue: thread <-> (query row q0 + row, column half): TMEM lane row & 127 of M tile row >> 7
+        const int mtile = (warp >> 2) & 1, half = warp >> 3;
+        const int row = mtile * 128 + (warp & 3) * 32 + lane;
         const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
         uint32_t k1 = KEY_NONE, k2 = KEY_NONE;
-        float thr = (float)(256 - 2 * (int)(KEY_NONE >> 20));      // below every accumulator: the first groups take the exact path
+        int thr = screen_threshold(KEY_NONE);                      // INT_MIN: the first groups take the exact path
         for (int t = 0; t < ntiles; t++) {
-            const int a = t & 1;
-            mbar_wait(&S.acc_full[a], (t >> 1) & 1);
+            const int j = 2 * t + mtile, b = j % NACC;               // this (tile, M tile) pair's accumulator
+            mbar_wait(&S.acc_full[b], (j / NACC) & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint32_t tbase = tmem + lane_base + (uint32_t)(a * ACC_STAGE_COLS + mtile * NT);
-            const uint32_t idx0 = (uint32_t)t * NT;
-            const int left = segn - (int)idx0;                       // valid columns of this tile (>= NT except in the last one)
-            const bool tail = left < NT;                             // padding columns must never win: exact path with masking
-            if (tail) thr = -1e30f;
-            uint32_t v0[16], v1[16];
-            TMEM_LD16(tbase, v0);
-#pragma unroll
-            for (int c = 0; c < NT; c += 32) {
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                if (c + 16 < NT) TMEM_LD16(tbase + c + 16, v1);
-                fold16(v0, idx0 + c, left - c, k1, k2, thr);
-                if (tail) thr = -1e30f;
-                if (c + 16 < NT) {
-                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                    if (c + 32 < NT) TMEM_LD16(tbase + c + 32, v0);
-                    fold16(v1, idx0 + c + 16, left - c - 16, k1, k2, thr);
-                    if (tail) thr = -1e30f;
-                }
-            }
-            if (tail) thr = (float)(256 - 2 * (int)(k2 >> 20));
-            // this warp's accumulator reads of stage a are complete (wait::ld above)
-            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&S.acc_empty[a]);
+            const uint32_t tbase = tmem + lane_base + (uint32_t)(b * NT + half * (NT / 2));
+            const uint32_t idx0 = (uint32_t)t * NT + half * (NT / 2);
+            const int left = segn - (int)idx0;                       // valid columns from idx0 on (>= NT / 2 except in the last tile)
+            if (left >= NT / 2) fold_half_tile<false>(tbase, idx0, NT / 2, k1, k2, thr, &S.acc_empty[b], lane);
+            else fold_half_tile<true>(tbase, idx0, left, k1, k2, thr, &S.acc_empty[b], lane);   // padding columns must never win: masked exact path
         }
-        const int q = q0 + tid;
-        if (q < nq) {
+        // the two column halves of a row meet: keys are (distance, index), so the merge is order free
+        if (half) { S.xk1[row] = k1; S.xk2[row] = k2; }
+        asm volatile("bar.sync 1, %0;" ::"n"(EPI_WARPS * 32) : "memory");
+        const int q = q0 + row;
+        if (!half && q < nq) {
+            const uint32_t o1 = S.xk1[row], o2 = S.xk2[row];
+            k2 = min(min(k2, o2), max(k1, o1));
+            k1 = min(k1, o1);
             const long long o = (long long)seg * nq + q;
             const bool h1 = k1 != KEY_NONE, h2 = k2 != KEY_NONE;
             part_d1[o] = h1 ? (int)(k1 >> 20) : 256;
@@ -233,20 +320,21 @@ knn2_fp4_kernel(const __grid_constant__ CUtensorMap qmap, const __grid_constant_
             const uint32_t sfa = tmem + SF_COL, sfb = tmem + SF_COL + 16;
             mbar_wait(&S.a_full, 0);
             for (int t = 0; t < ntiles; t++) {
-                const int s = t % STAGES, a = t & 1;
+                const int s = t % STAGES;
                 mbar_wait(&S.full_b[s], (t / STAGES) & 1);
-                mbar_wait(&S.acc_empty[a], ((t >> 1) & 1) ^ 1);
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint64_t bd = umma_desc(smem_u32(S.b[s]));
-#pragma unroll
                 for (int m = 0; m < 2; m++) {
-                    const uint32_t d = tmem + (uint32_t)(a * ACC_STAGE_COLS + m * NT);
+                    // three accumulators in turn: the epilogue of a pair runs under the MMAs of the next two
+                    const int j = 2 * t + m, b = j % NACC;
+                    mbar_wait(&S.acc_empty[b], ((j / NACC) & 1) ^ 1);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t d = tmem + (uint32_t)(b * NT);
                     const uint64_t ad = umma_desc(aaddr + m * 128 * 128);
 #pragma unroll
                     for (int k = 0; k < 4; k++) umma_mxf4(d, ad + 2 * k, bd + 2 * k, k != 0, sfa, sfb);   // +32 bytes = 64 FP4 of K
+                    umma_commit(&S.acc_full[b]);
                 }
                 umma_commit(&S.empty_b[s]);
-                umma_commit(&S.acc_full[a]);
             }
         }
         __syncwarp();

@@ -301,12 +301,13 @@ __global__ void knn2_merge_kernel(int nq, int nseg, int th, float ratio, const i
 // sets still fill the SMs, and — one CTA per SM, every CTA the same work — a count that leaves the last wave of
 // (query tiles x segments) CTAs as full as possible: 489 query tiles (1M queries over eight GPUs) are 3.3 waves in
 // one segment (82 % of four) and 9.9 waves in three (99 % of ten)
-int knn2_tile_segments(int nq, int nt, int mq, int ntile, int* segLen) {
+int knn2_tile_segments(int nq, int nt, int mq, int ntile, int* segLen, int minWant) {
     constexpr int kSms = 148;
     const int qtiles = (nq + mq - 1) / mq;
     int want = qtiles >= kSms ? 1 : (kSms + qtiles - 1) / qtiles;
     const int maxSeg = nt / (16 * ntile) > 1 ? nt / (16 * ntile) : 1;  // no segment shorter than 16 tiles
     if (want > maxSeg) want = maxSeg;
+    if (want < minWant) want = minWant < maxSeg ? minWant : maxSeg;
     const int minSeg = (nt + (1 << 20) - 1) >> 20;
     if (want < minSeg) want = minSeg;
     int best = want;
@@ -321,7 +322,7 @@ int knn2_tile_segments(int nq, int nt, int mq, int ntile, int* segLen) {
     *segLen = len;
     return (nt + len - 1) / len;
 }
-int knn2_mma_segments(int nq, int nt, int* segLen) { return knn2_tile_segments(nq, nt, MQ, NT, segLen); }
+int knn2_mma_segments(int nq, int nt, int* segLen) { return knn2_tile_segments(nq, nt, MQ, NT, segLen, 1); }
 
 int launch_knn2_merge(int nq, int nseg, int th, float ratio, const int* part_idx, const int* part_d1, const int* part_d2,
                       int* d_idx, int* d_d1, int* d_d2, cudaStream_t s) {

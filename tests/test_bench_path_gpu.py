@@ -123,7 +123,7 @@ def test_knn2_device_train_over_2_20_rows_ties_across_segments(orbfe, oracle, en
     rng = np.random.default_rng(9)
     t = rng.integers(0, 256, (n, 32), dtype=np.uint8)
     q = rng.integers(0, 256, (64, 32), dtype=np.uint8)
-    spots = [(1 << 20) - 1, 1 << 20, (1 << 20) + 1, 7551, 7552, 15104, n - 1, 0, 7503, 7504]     # 7504: the FP4 engine's segment length here
+    spots = [(1 << 20) - 1, 1 << 20, (1 << 20) + 1, 7551, 7552, 15104, n - 1, 0, 7487, 7488]     # 7488: the FP4 engine's segment length here
     for i in range(64):
         near = q[i].copy()
         near[i % 32] ^= np.uint8(1 << (i % 8))                       # distance 1
