@@ -661,9 +661,19 @@ def main():
             pass
         popc_gcmp = MQ * NT / (knn_ms * 1e-3) / 1e9                       # one GPU, integer-pipe engine
         knn_gcmp = float(knn_line["value"])                               # whole job, configs[4], gather included
-        # a 256-bit comparison on the tensor cores is 256 s8 MACs; int8 runs at twice the bf16 rate, and MEASURED_PEAKS has
-        # the sustained bf16 cuBLAS figure (the kNN step is a 0.2 s kernel under the power cap)
-        i8_peak_tops = 2.0 * float(peaks.get("bf16_tflops_sustained", 1400.0))
+        # a 256-bit comparison on the tensor cores is 256 multiply-adds.  The AUTO engine at this size is the block-scaled
+        # FP4 one (kind::mxf4), nominally four times the bf16 rate; MEASURED_PEAKS has the sustained bf16 cuBLAS figure.
+        # Beside that paper peak: the raw mxf4 issue rate of this very MMA shape family measured on this box, no epilogue,
+        # no operand traffic (tools/mma_rate_probe, about 2 s), which is the kernel's own ceiling
+        fp4_peak_tops = 4.0 * float(peaks.get("bf16_tflops_sustained", 1400.0))
+        i8_peak_tops = fp4_peak_tops                                      # key name kept from the s8 engine's rounds
+        probe_tcmps, probe_src = 16.4, "tools/mma_rate_probe on this pool (profiles/r02_mma_rate_probe.json)"
+        try:
+            pr = subprocess.run([os.path.join(ROOT, "tools", "mma_rate_probe")], capture_output=True, text=True, timeout=60)
+            probe_tcmps = float(json.loads(pr.stdout)["mxf4_m128_n128"]["tcmp_s"])
+            probe_src = "tools/mma_rate_probe run live"
+        except Exception:
+            pass
         knn_tops = knn_gcmp / world * 512.0 / 1e3
         desc_bytes = mean_kp * 544.0                                      # N_kp x (512 B gathered + 32 B out)
         frac = {k: ab[k] * B / (stage_ms[k] * 1e-3) / 1e9 / peak for k in ("pyramid", "fast", "blur")}
@@ -703,10 +713,11 @@ def main():
                          "knn_gather_bytes": int(knn_line["gather_bytes_total"]),
                          "knn_x_popc_peak": knn_gcmp / world / popc_peak, "knn_tensor_tops": knn_tops, "knn_tensor_peak_tops": i8_peak_tops,
                          "knn_frac_tensor": knn_tops / i8_peak_tops,
-                         # the same against twice the BURST bf16 figure (a 0.2 s kernel timed alone sits between the two)
-                         "knn_frac_tensor_burst": knn_tops / (2.0 * float(peaks.get("bf16_tflops", 1650.0))),
+                         # the same against four times the BURST bf16 figure (a 0.1 s kernel timed alone sits between the two)
+                         "knn_frac_tensor_burst": knn_tops / (4.0 * float(peaks.get("bf16_tflops", 1650.0))),
+                         "knn_mma_probe_gcmps": probe_tcmps * 1e3, "knn_frac_mma_probe": knn_gcmp / world / (probe_tcmps * 1e3),
                          "knn_popc_gcmps": popc_gcmp, "knn_popc_peak": popc_peak, "knn_frac_popc": popc_gcmp / popc_peak,
-                         "note": "kernels are integer-issue bound, not HBM bound (ncu, profiles/); kNN: tcgen05 s8 engine vs 2x sustained bf16 cuBLAS",
+                         "note": "kernels are integer-issue bound, not HBM bound (ncu, profiles/); kNN: tcgen05 mxf4 engine vs 4x sustained bf16 cuBLAS",
                          "per_kernel": per_kernel},
         }
         if not args.no_cpu_baseline:
