@@ -181,12 +181,12 @@ __device__ __forceinline__ void fold(const uint32_t (&v)[N], uint32_t idx0, int 
     }
 }
 
-// one thread's half of an accumulator of one query row (NT / 2 columns = G groups of 32 and, if NT / 2 is not a multiple
+// one thread's share of an accumulator of one query row (COLS columns = G groups of 32 and, if COLS is not a multiple
 // of 32, one of 16): the next tcgen05.ld is in flight while a group folds
-template <bool MASK>
+template <bool MASK, int COLS>
 __device__ __forceinline__ void fold_half_tile(uint32_t tbase, uint32_t idx0, int left, uint32_t& k1, uint32_t& k2, int& thr,
                                                unsigned long long* release, int lane) {
-    constexpr int HALF = NT / 2, G = HALF / 32, R = HALF % 32;
+    constexpr int G = COLS / 32, R = COLS % 32;
     static_assert(R == 0 || R == 16, "column groups are 32 wide plus at most one of 16");
     uint32_t v[2][32], vr[16];
     // the accumulator goes back to the MMA warp as soon as this warp's last columns are in registers, before they fold
@@ -282,11 +282,17 @@ knn2_fp4_kernel(const __grid_constant__ CUtensorMap qmap, const __grid_constant_
             const int j = 2 * t + mtile, b = j % NACC;               // this (tile, M tile) pair's accumulator
             mbar_wait(&S.acc_full[b], (j / NACC) & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint32_t tbase = tmem + lane_base + (uint32_t)(b * NT + half * (NT / 2));
-            const uint32_t idx0 = (uint32_t)t * NT + half * (NT / 2);
-            const int left = segn - (int)idx0;                       // valid columns from idx0 on (>= NT / 2 except in the last tile)
-            if (left >= NT / 2) fold_half_tile<false>(tbase, idx0, NT / 2, k1, k2, thr, &S.acc_empty[b], lane);
-            else fold_half_tile<true>(tbase, idx0, left, k1, k2, thr, &S.acc_empty[b], lane);   // padding columns must never win: masked exact path
+            constexpr int C0 = (NT / 2 + 31) / 32 * 32, C1 = NT - C0;     // the two threads' column shares (96 + 96 of 192)
+            const uint32_t tbase = tmem + lane_base + (uint32_t)(b * NT + half * C0);
+            const uint32_t idx0 = (uint32_t)t * NT + half * C0;
+            const int left = segn - (int)idx0;                       // valid columns from idx0 on (>= the share except in the last tile)
+            if (half == 0) {
+                if (left >= C0) fold_half_tile<false, C0>(tbase, idx0, C0, k1, k2, thr, &S.acc_empty[b], lane);
+                else fold_half_tile<true, C0>(tbase, idx0, left, k1, k2, thr, &S.acc_empty[b], lane);   // padding columns must never win: masked exact path
+            } else {
+                if (left >= C1) fold_half_tile<false, C1>(tbase, idx0, C1, k1, k2, thr, &S.acc_empty[b], lane);
+                else fold_half_tile<true, C1>(tbase, idx0, left, k1, k2, thr, &S.acc_empty[b], lane);
+            }
         }
         // the two column halves of a row meet: keys are (distance, index), so the merge is order free
         if (half) { S.xk1[row] = k1; S.xk2[row] = k2; }
