@@ -200,6 +200,10 @@ typedef struct {
                                        * mfGridElement*Inv are the Frame's (:33, :48-53): the cell
                                        * window of KeyFrame::GetFeaturesInArea (:616-628) is then
                                        * computed from (float)(int)min_x / min_y.  0: Frame.     */
+    float grid_inv_w, grid_inv_h;     /* mfGridElementWidthInv / HeightInv when the caller holds them
+                                       * (a KeyFrame copies its Frame's, src/KeyFrame.cc:33, and has
+                                       * no float bounds to derive them from bit for bit); 0 = derive
+                                       * 64 / (max_x - min_x), 48 / (max_y - min_y) as Frame.cc:86-87 */
 } orbfe_frame_view;
 
 /* Frame::ComputeImageBounds for callers without an extractor handle (HOST output). */
@@ -226,6 +230,7 @@ typedef struct {
     const float* scale_factors;
     int32_t nlevels;
     int32_t keyframe_bounds;          /* as in orbfe_frame_view */
+    float grid_inv_w, grid_inv_h;     /* as in orbfe_frame_view (0 = derive) */
 } orbfe_device_frame_view;
 
 /* Brute-force 2-nearest-neighbour Hamming search with the reference's acceptance rule

@@ -668,7 +668,8 @@ protected:
         orbfe_frame_view v = {(int)k.size(), k.data(), pKF->mDescriptors.data, nullptr, minX,
                               minX + (float)pKF->mnGridCols / pKF->mfGridElementWidthInv, minY,
                               minY + (float)pKF->mnGridRows / pKF->mfGridElementHeightInv, pKF->mvScaleFactors.data(),
-                              (int)pKF->mvScaleFactors.size(), 1};
+                              (int)pKF->mvScaleFactors.size(), 1,
+                              pKF->mfGridElementWidthInv, pKF->mfGridElementHeightInv};   // the Frame's own values, bit for bit
         return v;
     }
     // one key frame of SearchForTriangulation flattened

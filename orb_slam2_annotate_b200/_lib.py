@@ -27,7 +27,8 @@ class OrbfeError(RuntimeError):
 class FrameView(C.Structure):
     _fields_ = [("n", C.c_int32), ("kps", C.c_void_p), ("desc", C.c_void_p), ("uright", C.c_void_p),
                 ("min_x", C.c_float), ("max_x", C.c_float), ("min_y", C.c_float), ("max_y", C.c_float),
-                ("scale_factors", C.c_void_p), ("nlevels", C.c_int32), ("keyframe_bounds", C.c_int32)]
+                ("scale_factors", C.c_void_p), ("nlevels", C.c_int32), ("keyframe_bounds", C.c_int32),
+                ("grid_inv_w", C.c_float), ("grid_inv_h", C.c_float)]
 
 
 class MapPointsView(C.Structure):
@@ -52,7 +53,8 @@ class DeviceFrameView(C.Structure):
     _fields_ = [("n", C.c_int32), ("d_kps", C.c_void_p), ("d_desc", C.c_void_p), ("d_uright", C.c_void_p),
                 ("d_cell_end", C.c_void_p), ("d_items", C.c_void_p),
                 ("min_x", C.c_float), ("max_x", C.c_float), ("min_y", C.c_float), ("max_y", C.c_float),
-                ("scale_factors", C.c_void_p), ("nlevels", C.c_int32), ("keyframe_bounds", C.c_int32)]
+                ("scale_factors", C.c_void_p), ("nlevels", C.c_int32), ("keyframe_bounds", C.c_int32),
+                ("grid_inv_w", C.c_float), ("grid_inv_h", C.c_float)]
 
 
 GRID_COLS, GRID_ROWS = 64, 48

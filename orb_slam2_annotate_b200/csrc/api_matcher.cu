@@ -184,8 +184,8 @@ GridGeom grid_of(const orbfe_frame_view* f) {
     g.minX = f->min_x; g.minY = f->min_y;
     g.qminX = f->keyframe_bounds ? (float)(int)f->min_x : f->min_x;     // KeyFrame.cc:41: int members
     g.qminY = f->keyframe_bounds ? (float)(int)f->min_y : f->min_y;
-    g.invW = 64.0f / (f->max_x - f->min_x);
-    g.invH = 48.0f / (f->max_y - f->min_y);
+    g.invW = f->grid_inv_w > 0.0f ? f->grid_inv_w : 64.0f / (f->max_x - f->min_x);
+    g.invH = f->grid_inv_h > 0.0f ? f->grid_inv_h : 48.0f / (f->max_y - f->min_y);
     return g;
 }
 
@@ -277,6 +277,7 @@ orbfe_frame_view host_side_of(const orbfe_device_frame_view* df) {
     f.n = df->n; f.kps = df->d_kps; f.desc = df->d_desc; f.uright = df->d_uright;
     f.min_x = df->min_x; f.max_x = df->max_x; f.min_y = df->min_y; f.max_y = df->max_y;
     f.scale_factors = df->scale_factors; f.nlevels = df->nlevels; f.keyframe_bounds = df->keyframe_bounds;
+    f.grid_inv_w = df->grid_inv_w; f.grid_inv_h = df->grid_inv_h;
     return f;
 }
 
