@@ -56,7 +56,7 @@ def test_adapter_end_to_end(orbfe, oracle, tmp_path):
         assert len(k) == len(ko)
         for f in ("x", "y", "size", "response", "octave", "class_id"):
             assert np.array_equal(k[f], ko[f])
-        assert np.abs(k["angle"] - ko["angle"]).max() <= 1e-3 and (d != do).any(axis=1).sum() <= 2
+        assert np.array_equal(k["angle"], ko["angle"]) and np.array_equal(d, do)
     prev = np.ascontiguousarray(np.stack([ref[0][0]["x"], ref[0][0]["y"]], 1), np.float32)
     no, mo = oracle.search_for_initialization(oracle.frame_view(ref[0][0], ref[0][1], 640, 480, t["scale"]),
                                               oracle.frame_view(ref[1][0], ref[1][1], 640, 480, t["scale"]), prev, 100, 0.9, True)

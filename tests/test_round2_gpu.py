@@ -29,9 +29,7 @@ def test_two_live_extractors_of_different_budgets_alternate(orbfe, oracle):
         ks, ds = small(img)
         for (k, d), (ko, do) in (((kb, db), ref_big), ((ks, ds), ref_small)):
             assert len(k) == len(ko)
-            for f in ("x", "y", "size", "response", "octave"):
-                assert np.array_equal(k[f], ko[f]), f
-            assert (d != do).any(axis=1).sum() <= 2
+            assert k.tobytes() == ko.tobytes() and np.array_equal(d, do)
     # batched path of the large handle after the small one ran (eager launches, not the graph)
     imgs = np.ascontiguousarray(np.repeat(img[None], 6, 0))
     small.extract_batch(imgs)
