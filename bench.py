@@ -560,9 +560,9 @@ def main():
             self.mt.fetch(self.h_nm.data_ptr(), self.d_nm.data_ptr(), self.h_nm.numel() * 4)
             self.mt.sync()
 
-    in_flight = 1 if os.environ.get("ORBFE_BENCH_E2E_SINGLE") else 2
+    in_flight = 1 if os.environ.get("ORBFE_BENCH_E2E_SINGLE") else int(os.environ.get("ORBFE_BENCH_E2E_INFLIGHT", "2"))
     workers = [E2EWorker(ex, mt)]
-    if in_flight == 2:
+    for _ in range(in_flight - 1):
         workers.append(E2EWorker(orbfe.ORBextractor(NFEAT, 1.2, 8, 20, 7, device=local_rank, max_width=W, max_height=H, max_batch=B),
                                  orbfe.ORBmatcher(0.9, True, device=local_rank)))
     out = workers[0].out
