@@ -422,10 +422,32 @@ def run_reference(args, rank, world):
             "roofline": {"knn_cpu_gcmps": k["gcmps"]},
             "gpu_launches": 0,
             "note": "unmodified ORBextractor.cc / ORBmatcher.cc / Frame.cc on the scalar cv-shim OpenCV stand-ins (a SIMD OpenCV build would be about 2x faster)"}
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_JSON_FD = None
+
+
+def _claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries underneath write there too (NCCL prints its version line when the
+    first communicator is created): from here on file descriptor 1 goes to stderr and the JSON line to the real stdout."""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
 
 
 def main():
+    _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
@@ -730,7 +752,7 @@ def main():
             line["guided_searches"] = guided_search_timings(frames[0])
             line["stereo"] = stereo_timings()
             line["latency"] = single_frame_latency(frames)
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
