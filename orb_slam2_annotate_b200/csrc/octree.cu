@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(QT)
 octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ DevBufs d, int NC, int KP, int level0) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ int wsum[QT / 32 + 1];
-    __shared__ int s_n, s_cut, s_nexp;
+    __shared__ int s_n, s_k0, s_T, s_ns, s_nexp;
 
     const int l = blockIdx.x + level0, frame = blockIdx.y + g.frame0;
     const LevelGeom& L = g.lv[l];
@@ -189,6 +189,9 @@ octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ De
     for (int i = tid; i < n; i += QT) pnode[i] = s_tmp[pnode[i]];
     __syncthreads();
 
+    // The per-step bookkeeping over the NODES (a few dozen to a few hundred) runs on warp 0 alone with ballots and
+    // shuffles — a block-wide version of it is a dozen short loops, three block scans and twenty barriers per step, paid
+    // by every warp of the tree; the per-KEY passes (a, f) and the quadratic rank sort of the budgeted phase use all threads.
     int cur = 0, phase = 1;
     bool finish = false;
     while (!finish) {                                                     // :625
@@ -199,27 +202,107 @@ octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ De
         int* cntn = (cur ? cnt0 : cnt1);
         // a. keys per quadrant of every candidate (a node with more than one key)
         for (int i = tid; i < 4 * size; i += QT) s_cnt4[i] = 0;
-        for (int i = tid; i < size; i += QT) { s_prank[i] = -1; s_tmp[i] = cntc[i] > 1; }
-        if (tid == 0) { s_cut = 0x7FFFFFFF; s_nexp = 0; }
         __syncthreads();
         for (int i = tid; i < n; i += QT) {
             const int nd = pnode[i];
             if (cntc[nd] > 1) atomicAdd(&s_cnt4[4 * nd + quadrant(pxy[i], boxc[nd])], 1);
         }
-        // b. compact the candidates in list order
-        const int k0 = block_exscan<QT>(s_tmp, size, wsum);
-        for (int i = tid; i < size; i += QT)
-            if (cntc[i] > 1) s_cand[s_tmp[i]] = i;
         __syncthreads();
-        // c. processing order
+        // b. (warp 0) the candidates compacted in list order
+        auto compact = [&]() {
+            int k0 = 0;
+            for (int base = 0; base < size; base += 32) {
+                const int i = base + lane;
+                const bool f = i < size && cntc[i] > 1;
+                const unsigned bal = __ballot_sync(FULL, f);
+                if (f) s_cand[k0 + __popc(bal & ((1u << lane) - 1u))] = i;
+                k0 += __popc(bal);
+            }
+            __syncwarp();
+            return k0;
+        };
+        // d, e. (warp 0) children per processed node in processing order, running prefix, early break (:774); then the
+        //       new list: children of the processed nodes in front (last processed first), survivors behind in their old order
+        auto node_step = [&](const int* order, int k0) {
+            for (int i = lane; i < size; i += 32) s_prank[i] = -1;
+            int carry = 0, k = k0, T = 0;
+            bool cut = false;
+            for (int base = 0; base < k0; base += 32) {
+                const int r = base + lane;
+                const int c = r < k0 ? child_count(&s_cnt4[4 * order[r]]) : 0;
+                int inc = c;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int u = __shfl_up_sync(FULL, inc, o);
+                    if (lane >= o) inc += u;
+                }
+                const int ex = carry + inc - c;
+                if (r < k0) s_pex[r] = ex;
+                if (phase == 2) {
+                    const unsigned bal = __ballot_sync(FULL, r < k0 && size + ex + c - (r + 1) >= N);
+                    if (bal) {
+                        const int first = __ffs(bal) - 1;
+                        k = base + first + 1;
+                        T = __shfl_sync(FULL, ex + c, first);
+                        cut = true;
+                        break;
+                    }
+                }
+                carry += __shfl_sync(FULL, inc, 31);
+            }
+            if (!cut) T = carry;
+            __syncwarp();
+            for (int r = lane; r < k; r += 32) s_prank[order[r]] = r;
+            __syncwarp();
+            int ns = 0, nexp = 0;
+            for (int base = 0; base < size; base += 32) {
+                const int i = base + lane;
+                const int r = i < size ? s_prank[i] : 0;
+                const bool surv = i < size && r < 0;
+                const unsigned bal = __ballot_sync(FULL, surv);
+                if (surv) {
+                    const int np = T + ns + __popc(bal & ((1u << lane) - 1u));
+                    boxn[np] = boxc[i];
+                    cntn[np] = cntc[i];
+                    s_remap[i] = np;
+                } else if (i < size) {
+                    const int* c4 = &s_cnt4[4 * i];
+                    const int base2 = T - (s_pex[r] + child_count(c4));
+                    s_remap[i] = base2;
+                    int j = 0;
+#pragma unroll
+                    for (int q = 3; q >= 0; q--)
+                        if (c4[q] > 0) {
+                            boxn[base2 + j] = child_box(boxc[i], q);
+                            cntn[base2 + j] = c4[q];
+                            nexp += c4[q] > 1;
+                            j++;
+                        }
+                }
+                ns += __popc(bal);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) nexp += __shfl_xor_sync(FULL, nexp, o);
+            if (lane == 0) { s_T = T; s_ns = ns; s_nexp = nexp; }
+        };
         if (phase == 1) {
-            for (int ci = tid; ci < k0; ci += QT) s_order[ci] = s_cand[ci];
+            // c. processing order = list order
+            if (wid == 0) {
+                const int k0 = compact();
+                node_step(s_cand, k0);
+            }
         } else {
-            // sort (count, creation order) ascending, walk from the back (:728-731): count
-            // descending, then newest (= smaller list position) first.
-            // Rank sort on one packed key per candidate, count << 12 | (4095 - list rank): "count larger, or equal
-            // and earlier in the list" is one unsigned compare; the keys are read four at a time (broadcast LDS.128)
-            uint32_t* key = reinterpret_cast<uint32_t*>(s_tmp);           // free between the compaction and step e
+            if (wid == 0) {
+                const int k0 = compact();
+                if (lane == 0) s_k0 = k0;
+            }
+            __syncthreads();
+            const int k0 = s_k0;
+            // c. sort (count, creation order) ascending, walk from the back (:728-731): count descending, then newest
+            // (= smaller list position) first.  Rank sort on one packed key per candidate, count << 12 | (4095 - list
+            // rank): "count larger, or equal and earlier in the list" is one unsigned compare; the keys are read four at a
+            // time (broadcast LDS.128)
+            uint32_t* key = reinterpret_cast<uint32_t*>(s_tmp);
             for (int ci = tid; ci < ((k0 + 3) & ~3); ci += QT)
                 key[ci] = ci < k0 ? ((uint32_t)cntc[s_cand[ci]] << 12) | (uint32_t)(4095 - ci) : 0u;
             __syncthreads();
@@ -233,52 +316,9 @@ octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ De
                 }
                 s_order[r] = s_cand[ci];
             }
-        }
-        __syncthreads();
-        // d. children per processed node, prefix sums, early break (:774)
-        for (int r = tid; r < k0; r += QT) s_pex[r] = child_count(&s_cnt4[4 * s_order[r]]);
-        __syncthreads();
-        block_exscan<QT>(s_pex, k0, wsum);
-        int k = k0;
-        if (phase == 2) {
-            for (int r = tid; r < k0; r += QT) {
-                const int c = child_count(&s_cnt4[4 * s_order[r]]);
-                if (size + s_pex[r] + c - (r + 1) >= N) atomicMin(&s_cut, r);
-            }
             __syncthreads();
-            if (s_cut < k0) k = s_cut + 1;
+            if (wid == 0) node_step(s_order, k0);
         }
-        const int T = k > 0 ? s_pex[k - 1] + child_count(&s_cnt4[4 * s_order[k - 1]]) : 0;
-        for (int r = tid; r < k; r += QT) s_prank[s_order[r]] = r;
-        __syncthreads();
-        // e. survivors keep their relative order behind the new children
-        for (int i = tid; i < size; i += QT) s_tmp[i] = s_prank[i] < 0;
-        __syncthreads();
-        const int ns = block_exscan<QT>(s_tmp, size, wsum);
-        int nexp = 0;
-        for (int i = tid; i < size; i += QT) {
-            const int r = s_prank[i];
-            if (r < 0) {
-                const int np = T + s_tmp[i];
-                boxn[np] = boxc[i];
-                cntn[np] = cntc[i];
-                s_remap[i] = np;
-            } else {
-                const int* c4 = &s_cnt4[4 * i];
-                const int base = T - (s_pex[r] + child_count(c4));
-                s_remap[i] = base;
-                int j = 0;
-#pragma unroll
-                for (int q = 3; q >= 0; q--)
-                    if (c4[q] > 0) {
-                        boxn[base + j] = child_box(boxc[i], q);
-                        cntn[base + j] = c4[q];
-                        nexp += c4[q] > 1;
-                        j++;
-                    }
-            }
-        }
-        if (nexp) atomicAdd(&s_nexp, nexp);
         __syncthreads();
         // f. keys follow their nodes
         for (int i = tid; i < n; i += QT) {
@@ -294,8 +334,8 @@ octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ De
             }
         }
         const int nToExpand = s_nexp;
+        size = s_T + s_ns;
         __syncthreads();
-        size = T + ns;
         cur ^= 1;
         if (size >= N || size == prevSize) finish = true;                 // :707, :778
         else if (phase == 1 && size + nToExpand * 3 > N) phase = 2;       // :714
@@ -318,14 +358,15 @@ octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ De
 // threads per tree by the level's feature budget: the per-step cost of a tree is a fixed number of block-wide
 // loops, scans and barriers, paid once per warp, so the small trees of the upper levels run on fewer warps
 int tree_threads(const LevelGeom& L) {
-    // measured at nfeatures 1000 (budgets 217 181 151 126 105 87 73 60): 256/128/64 threads split at 170 / 90 gives
-    // 0.308 ms per 1024 frames; all 256: 0.328, all 128: 0.343, all 64: 0.410, 512 for the two largest: 0.319.  The
-    // single-frame latency does not depend on it (0.075 ms with 128 ... 1024 threads: the pyramid chain is as long)
+    // measured at nfeatures 1000 (budgets 217 181 151 126 105 87 73 60) with the node bookkeeping on warp 0: 256 threads
+    // above a budget of 100 and 128 below gives 0.248 ms per 1024 frames; 256 / 128 / 64 split at 170 / 90: 0.254, at
+    // 140 / 80: 0.249; all 256: 0.264.  (With block-wide bookkeeping the split mattered more: 0.308 against 0.328 for all
+    // 256 and 0.410 for all 64.)  The single-frame latency does not depend on it (the pyramid chain is as long).
     static int t_hi = -1, t_lo = -1;
     if (t_hi < 0) {
         const char* e = std::getenv("ORBFE_OCTREE_SPLIT");        // "hi,lo": budgets above hi -> 256, above lo -> 128, else 64
-        int a = 170, b = 90;
-        if (e && std::sscanf(e, "%d,%d", &a, &b) != 2) { a = 170; b = 90; }
+        int a = 100, b = 0;
+        if (e && std::sscanf(e, "%d,%d", &a, &b) != 2) { a = 100; b = 0; }
         t_hi = a; t_lo = b;
     }
     return L.nFeat > t_hi ? 256 : L.nFeat > t_lo ? 128 : 64;
