@@ -205,7 +205,11 @@ octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ De
         __syncthreads();
         for (int i = tid; i < n; i += QT) {
             const int nd = pnode[i];
-            if (cntc[nd] > 1) atomicAdd(&s_cnt4[4 * nd + quadrant(pxy[i], boxc[nd])], 1);
+            if (cntc[nd] > 1) {
+                const int q = quadrant(pxy[i], boxc[nd]);
+                atomicAdd(&s_cnt4[4 * nd + q], 1);
+                pnode[i] = (uint32_t)nd | ((uint32_t)q << 28);       // pass f takes the quadrant from here (node positions < 2^12)
+            }
         }
         __syncthreads();
         // b. (warp 0) the candidates compacted in list order
@@ -269,15 +273,17 @@ octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ De
                     const int* c4 = &s_cnt4[4 * i];
                     const int base2 = T - (s_pex[r] + child_count(c4));
                     s_remap[i] = base2;
-                    int j = 0;
+                    int j = 0, cw = 0;
 #pragma unroll
                     for (int q = 3; q >= 0; q--)
                         if (c4[q] > 0) {
                             boxn[base2 + j] = child_box(boxc[i], q);
                             cntn[base2 + j] = c4[q];
                             nexp += c4[q] > 1;
+                            cw |= j << (8 * q);                          // list slot of quadrant q's child behind base2
                             j++;
                         }
+                    s_tmp[i] = cw;
                 }
                 ns += __popc(bal);
             }
@@ -322,16 +328,10 @@ octree_kernel(const __grid_constant__ FrameSetGeom g, const __grid_constant__ De
         __syncthreads();
         // f. keys follow their nodes
         for (int i = tid; i < n; i += QT) {
-            const int nd = pnode[i];
-            if (s_prank[nd] >= 0) {
-                const int q = quadrant(pxy[i], boxc[nd]);
-                const int* c4 = &s_cnt4[4 * nd];
-                int j = 0;
-                for (int qq = q + 1; qq < 4; qq++) j += c4[qq] > 0;
-                pnode[i] = s_remap[nd] + j;
-            } else {
-                pnode[i] = s_remap[nd];
-            }
+            const uint32_t pq = pnode[i];
+            const int nd = (int)(pq & 0x0FFFFFFFu);
+            // a split node's key moves to the child of its quadrant (recorded by pass a; s_tmp holds the children's slots)
+            pnode[i] = s_remap[nd] + (s_prank[nd] >= 0 ? (s_tmp[nd] >> (8 * (pq >> 28))) & 0xFF : 0);
         }
         const int nToExpand = s_nexp;
         size = s_T + s_ns;
